@@ -1,0 +1,127 @@
+/* lazac_b200.h -- C ABI of the B200-native ZCNT hot path (liblazac_b200.so).
+ *
+ * The reference (raphael-group/lazac-copy-number) has no FFI layer; its hot path is reached by
+ * direct C++ calls with value semantics.  Each entry point below names the reference call site
+ * it replaces (paths relative to the reference repository).  INTEGRATION.md shows the few
+ * lines a maintainer of the reference would change to bind them.
+ *
+ * Conventions
+ *   - every function returns an lzg_status (0 = ok); no exception crosses this boundary;
+ *   - plain pointers and sizes only; the caller owns every host buffer, the library owns all
+ *     device memory behind opaque handles; no host pointer is retained after a call returns;
+ *   - one context per (process, GPU); a context is not thread-safe; calls are synchronous on
+ *     return unless the name ends in _async;
+ *   - breakpoint vectors are int32 [N][L] row-major on the host (rows in the caller's order:
+ *     the reference sorts cell names, src/lazac.cxx:69) and int8 (+128 bias) in HBM;
+ *   - trees are rooted, binary, node ids 0..n_nodes-1 with root 0 (as the reference assumes,
+ *     include/copy_number.hpp:183), child0/child1 = -1 for leaves.
+ */
+#ifndef LAZAC_B200_H
+#define LAZAC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum lzg_status {
+    LZG_OK = 0,
+    LZG_ERR_ARG = 1,        /* null pointer, bad size, bad handle, id out of range            */
+    LZG_ERR_NOT_BINARY = 2, /* std::logic_error("every child must have exactly two children"),
+                               src/copy_number.cxx:241-242                                     */
+    LZG_ERR_RANGE = 3,      /* a breakpoint value does not fit the int8 device format          */
+    LZG_ERR_CUDA = 4,       /* CUDA runtime error; text in lzg_last_error                      */
+    LZG_ERR_NO_DEVICE = 5,  /* no usable GPU: there is no CPU fallback                         */
+    LZG_ERR_STATE = 6,      /* tree not scored yet / profiles freed / wrong context            */
+    LZG_ERR_NOT_A_MOVE = 7  /* (u,w,v,z) is not an NNI move of the current topology            */
+} lzg_status;
+
+typedef struct lzg_ctx lzg_ctx;
+typedef struct lzg_profiles lzg_profiles;
+typedef struct lzg_tree lzg_tree;
+
+/* ---- context ------------------------------------------------------------------------------ */
+int lzg_init(int device, lzg_ctx** out);
+int lzg_shutdown(lzg_ctx* ctx);
+const char* lzg_last_error(const lzg_ctx* ctx); /* valid until the next failing call */
+const char* lzg_status_string(int status);
+const char* lzg_version(void);
+/* Kernel launches issued by this context since lzg_init (bench.py's gpu_launches). */
+int lzg_launch_count(const lzg_ctx* ctx, int64_t* out);
+/* Device timing on the context's own stream (CUDA events): start, ..., stop -> milliseconds. */
+int lzg_timer_start(lzg_ctx* ctx);
+int lzg_timer_stop(lzg_ctx* ctx, float* ms);
+int lzg_sync(lzg_ctx* ctx);
+/* Writes a scratch buffer larger than L2 (timing hygiene between timed iterations). */
+int lzg_flush_l2(lzg_ctx* ctx);
+/* Pinned host memory for callers that want asynchronous copies to overlap. */
+int lzg_host_alloc(lzg_ctx* ctx, uint64_t bytes, void** out);
+int lzg_host_free(lzg_ctx* ctx, void* p);
+
+/* ---- profiles: the output of convert_to_breakpoint_profile (src/copy_number.cxx:25-59) for
+ *      all N cells, uploaded once.  Replaces the std::map<std::string, breakpoint_profile>
+ *      handed to build_distance_matrix (src/lazac.cxx:63) and the leaf start/end vectors set at
+ *      src/lazac.cxx:222-226. ------------------------------------------------------------- */
+int lzg_profiles_upload(lzg_ctx* ctx, const int32_t* bp, int32_t n_cells, int32_t n_pos,
+                        lzg_profiles** out);
+/* Same, from a compact int8 host matrix (large synthetic configs). */
+int lzg_profiles_upload_i8(lzg_ctx* ctx, const int8_t* bp, int32_t n_cells, int32_t n_pos,
+                           lzg_profiles** out);
+int lzg_profiles_free(lzg_profiles* p);
+int lzg_profiles_shape(const lzg_profiles* p, int32_t* n_cells, int32_t* n_pos);
+
+/* ---- all-pairs ZCNT distance: replaces the pair loop of build_distance_matrix,
+ *      src/lazac.cxx:81-91 (operator- include/copy_number.hpp:74-83 + breakpoint_magnitude
+ *      src/copy_number.cxx:100-113).  D is the full symmetric N x N int32 matrix. ---------- */
+int lzg_distance_matrix(lzg_ctx* ctx, const lzg_profiles* p, int32_t* D_host);
+/* Result left in HBM (d_D = device pointer to N*N int32); asynchronous on the context stream. */
+int lzg_distance_matrix_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t* d_D);
+/* One shard of the tile rows (multi-GPU: shard = rank, n_shards = world size).  Tile rows are
+ * dealt in pairs (r, R-1-r) so every shard gets the same triangle area.  Only tiles on or above
+ * the diagonal of the shard's tile rows are computed; both D[i][j] and D[j][i] are written into
+ * the caller's full N x N host matrix, other entries are left untouched. */
+int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard, int32_t n_shards,
+                       int32_t* D_host, int64_t* pairs_done);
+int lzg_distance_shard_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard,
+                                    int32_t n_shards, int32_t* d_D, int64_t* pairs_done);
+
+/* ---- small parsimony on a resident tree: replaces digraph<rectilinear_vertex_data>
+ *      (include/copy_number.hpp:98-105) and the functions that walk it. -------------------- */
+/* leaf_row[u] = profile row of leaf u, -1 for internal nodes (src/lazac.cxx:212-235). */
+int lzg_tree_create(lzg_ctx* ctx, const lzg_profiles* p, int32_t n_nodes, const int32_t* child0,
+                    const int32_t* child1, const int32_t* leaf_row, lzg_tree** out);
+int lzg_tree_clone(lzg_ctx* ctx, const lzg_tree* t, lzg_tree** out); /* digraph copy-ctor */
+int lzg_tree_free(lzg_tree* t);
+/* New topology from the host (after stochastic_nni, src/copy_number.cxx:419-462, whose
+ * unvisit(t,0) invalidates every interval). */
+int lzg_tree_set_topology(lzg_ctx* ctx, lzg_tree* t, const int32_t* child0, const int32_t* child1);
+int lzg_tree_get_topology(const lzg_tree* t, int32_t* child0, int32_t* child1);
+/* small_rectilinear(t, 0), src/copy_number.cxx:227-277: level-scheduled bottom-up interval
+ * DP over every un-scored node; root_score = t[0].data.score. */
+int lzg_tree_score(lzg_ctx* ctx, lzg_tree* t, int32_t* root_score);
+/* The candidate loop of greedy_nni, src/copy_number.cxx:331-370: scores all n_moves candidates
+ * (u,w,v,z) (moves = int32 [n_moves][4], in the host's enumeration order) in one launch and
+ * reduces them on the device.  best_index = first candidate with the strictly smallest score
+ * below the current root score (greedy != 0: first candidate below it), -1 if none.
+ * all_scores (optional, [n_moves]) receives every candidate's root score. */
+int lzg_nni_best(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int32_t greedy,
+                 int32_t* best_index, int32_t* best_score, int32_t* all_scores);
+/* nni(t,u,w,v,z); unvisit(t,0,v); small_rectilinear(t,0) -- src/copy_number.cxx:397,408-409. */
+int lzg_tree_apply_nni(lzg_ctx* ctx, lzg_tree* t, int32_t u, int32_t w, int32_t v, int32_t z,
+                       int32_t* root_score);
+/* start/end: int32 [n_nodes][L]; score: int32 [n_nodes] (any may be NULL). */
+int lzg_tree_get_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end,
+                           int32_t* score);
+/* ancestral_labeling's per-position math, src/copy_number.cxx:165-225: labels int32
+ * [n_nodes][L] and in_branch_len int32 [n_nodes] (-1 for the root), indexed by THIS tree's node
+ * ids; the pre-order renumbering of :215 is host logic. */
+int lzg_tree_ancestral(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* in_branch_len);
+/* Algorithmic work of the last lzg_nni_best on this tree: merges (= sum over candidates of
+ * depth(v)+1) and bytes read (= (merges + n_moves) * 2 * L). */
+int lzg_tree_last_nni_work(const lzg_tree* t, int64_t* merges, int64_t* bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LAZAC_B200_H */

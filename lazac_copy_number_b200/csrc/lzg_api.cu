@@ -1,0 +1,300 @@
+// lzg_api.cu -- the C ABI declared in include/lazac_b200.h.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "lzg_common.cuh"
+#include "lzg_tree.cuh"
+
+int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
+int lzg_pack_rows_i8(lzg_ctx* ctx, const int8_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
+int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v);
+
+static thread_local std::string g_init_error;
+
+int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e) {
+    std::string msg = what ? what : "";
+    if (e != cudaSuccess) {
+        msg += ": ";
+        msg += cudaGetErrorString(e);
+        cudaGetLastError();  // clear the sticky-less error state
+    }
+    if (ctx) ctx->err = msg;
+    else g_init_error = msg;
+    return status;
+}
+
+int lzg_ensure_scratch(lzg_ctx* ctx, size_t ints) {
+    if (ints <= ctx->d_scratch_ints) return LZG_OK;
+    if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+    ctx->d_scratch = nullptr;
+    ctx->d_scratch_ints = 0;
+    size_t want = std::max<size_t>(ints, 1 << 16);
+    LZG_CUDA(ctx, cudaMalloc(&ctx->d_scratch, sizeof(int32_t) * want));
+    ctx->d_scratch_ints = want;
+    return LZG_OK;
+}
+
+extern "C" {
+
+const char* lzg_version(void) { return "lazac_b200 0.1 (sm_100a)"; }
+
+const char* lzg_status_string(int s) {
+    switch (s) {
+        case LZG_OK: return "ok";
+        case LZG_ERR_ARG: return "bad argument";
+        case LZG_ERR_NOT_BINARY: return "every child must have exactly two children";
+        case LZG_ERR_RANGE: return "breakpoint value outside the int8 device format";
+        case LZG_ERR_CUDA: return "CUDA error";
+        case LZG_ERR_NO_DEVICE: return "no usable GPU (there is no CPU fallback)";
+        case LZG_ERR_STATE: return "invalid state";
+        case LZG_ERR_NOT_A_MOVE: return "not an NNI move of the current topology";
+    }
+    return "unknown status";
+}
+
+const char* lzg_last_error(const lzg_ctx* ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
+
+int lzg_init(int device, lzg_ctx** out) {
+    if (!out) return LZG_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return lzg_fail(nullptr, LZG_ERR_NO_DEVICE, "cudaGetDeviceCount", e);
+    if (device < 0 || device >= count) return lzg_fail(nullptr, LZG_ERR_ARG, "device index out of range");
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return lzg_fail(nullptr, LZG_ERR_NO_DEVICE, "cudaSetDevice", e);
+    lzg_ctx* ctx = new (std::nothrow) lzg_ctx();
+    if (!ctx) return LZG_ERR_ARG;
+    ctx->device = device;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
+    if (e == cudaSuccess) e = cudaMalloc(&ctx->d_flag, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(ctx->d_flag, 0, sizeof(int));
+    ctx->h_pinned_ints = 1 << 16;
+    if (e == cudaSuccess) e = cudaHostAlloc(&ctx->h_pinned, sizeof(int32_t) * ctx->h_pinned_ints, cudaHostAllocDefault);
+    if (e == cudaSuccess && lzg_ensure_scratch(ctx, 1 << 16) != LZG_OK) e = cudaErrorMemoryAllocation;
+    if (e != cudaSuccess) {
+        int rc = lzg_fail(nullptr, LZG_ERR_CUDA, "lzg_init", e);
+        delete ctx;
+        return rc;
+    }
+    *out = ctx;
+    return LZG_OK;
+}
+
+int lzg_shutdown(lzg_ctx* ctx) {
+    if (!ctx) return LZG_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->flush_buf) cudaFree(ctx->flush_buf);
+    if (ctx->d_flag) cudaFree(ctx->d_flag);
+    if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return LZG_OK;
+}
+
+int lzg_launch_count(const lzg_ctx* ctx, int64_t* out) {
+    if (!ctx || !out) return LZG_ERR_ARG;
+    *out = ctx->launches;
+    return LZG_OK;
+}
+
+int lzg_timer_start(lzg_ctx* ctx) {
+    if (!ctx) return LZG_ERR_ARG;
+    LZG_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    return LZG_OK;
+}
+
+int lzg_timer_stop(lzg_ctx* ctx, float* ms) {
+    if (!ctx || !ms) return LZG_ERR_ARG;
+    LZG_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    LZG_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    LZG_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return LZG_OK;
+}
+
+int lzg_sync(lzg_ctx* ctx) {
+    if (!ctx) return LZG_ERR_ARG;
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LZG_OK;
+}
+
+int lzg_flush_l2(lzg_ctx* ctx) {
+    if (!ctx) return LZG_ERR_ARG;
+    if (!ctx->flush_buf) {
+        ctx->flush_bytes = (size_t)256 << 20;  // 2x the 126 MB L2
+        LZG_CUDA(ctx, cudaMalloc(&ctx->flush_buf, ctx->flush_bytes));
+    }
+    return lzg_fill_bytes(ctx, (uint8_t*)ctx->flush_buf, ctx->flush_bytes, 0);
+}
+
+int lzg_host_alloc(lzg_ctx* ctx, uint64_t bytes, void** out) {
+    if (!ctx || !out) return LZG_ERR_ARG;
+    LZG_CUDA(ctx, cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    return LZG_OK;
+}
+
+int lzg_host_free(lzg_ctx* ctx, void* p) {
+    if (!ctx) return LZG_ERR_ARG;
+    LZG_CUDA(ctx, cudaFreeHost(p));
+    return LZG_OK;
+}
+
+// ---- profiles ----------------------------------------------------------------------------------
+static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32_t n, int32_t L, lzg_profiles** out) {
+    if (!ctx || !out || n < 0 || L < 0 || ((n > 0 && L > 0) && !host)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_profiles_upload: bad argument");
+    *out = nullptr;
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    lzg_profiles* p = new (std::nothrow) lzg_profiles();
+    if (!p) return LZG_ERR_ARG;
+    p->ctx = ctx;
+    p->n = n;
+    p->L = L;
+    p->n_pad = std::max(128, (n + 127) / 128 * 128);
+    p->l_pad = std::max(128, (L + 127) / 128 * 128);
+    const size_t bytes = (size_t)p->n_pad * p->l_pad;
+    cudaError_t e = cudaMalloc(&p->d, bytes);
+    if (e != cudaSuccess) {
+        delete p;
+        return lzg_fail(ctx, LZG_ERR_CUDA, "profiles cudaMalloc", e);
+    }
+    int rc = lzg_fill_bytes(ctx, p->d + (size_t)n * p->l_pad, bytes - (size_t)n * p->l_pad, LZG_BIAS);
+    // stage the host matrix through a bounded device buffer (<= 256 MiB) and pack on the device
+    const size_t elt = is_i8 ? 1 : 4;
+    void* d_stage = nullptr;
+    if (rc == LZG_OK && n > 0 && L > 0) {
+        size_t row_bytes = (size_t)L * elt;
+        int block_rows = (int)std::max<size_t>(1, std::min<size_t>(n, ((size_t)256 << 20) / row_bytes));
+        e = cudaMalloc(&d_stage, (size_t)block_rows * row_bytes);
+        if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "staging cudaMalloc", e);
+        e = cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), ctx->stream);
+        for (int r0 = 0; rc == LZG_OK && r0 < n; r0 += block_rows) {
+            int nr = std::min(block_rows, n - r0);
+            e = cudaMemcpyAsync(d_stage, (const uint8_t*)host + (size_t)r0 * row_bytes, (size_t)nr * row_bytes, cudaMemcpyHostToDevice, ctx->stream);
+            if (e != cudaSuccess) {
+                rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles H2D", e);
+                break;
+            }
+            rc = is_i8 ? lzg_pack_rows_i8(ctx, (const int8_t*)d_stage, p->d + (size_t)r0 * p->l_pad, nr, L, p->l_pad)
+                       : lzg_pack_rows_i32(ctx, (const int32_t*)d_stage, p->d + (size_t)r0 * p->l_pad, nr, L, p->l_pad);
+            if (rc == LZG_OK && r0 + block_rows < n) cudaStreamSynchronize(ctx->stream);  // staging buffer is reused
+        }
+    } else if (rc == LZG_OK && n > 0) {
+        rc = lzg_fill_bytes(ctx, p->d, (size_t)n * p->l_pad, LZG_BIAS);
+    }
+    if (rc == LZG_OK) {
+        e = cudaMemcpyAsync(ctx->h_pinned, ctx->d_flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles pack", e);
+        else if (n > 0 && L > 0 && ctx->h_pinned[0]) rc = lzg_fail(ctx, LZG_ERR_RANGE, "breakpoint value outside [-127, 127]");
+    }
+    if (d_stage) cudaFree(d_stage);
+    if (rc != LZG_OK) {
+        cudaFree(p->d);
+        delete p;
+        return rc;
+    }
+    *out = p;
+    return LZG_OK;
+}
+
+int lzg_profiles_upload(lzg_ctx* ctx, const int32_t* bp, int32_t n, int32_t L, lzg_profiles** out) {
+    return profiles_upload_any(ctx, bp, false, n, L, out);
+}
+
+int lzg_profiles_upload_i8(lzg_ctx* ctx, const int8_t* bp, int32_t n, int32_t L, lzg_profiles** out) {
+    return profiles_upload_any(ctx, bp, true, n, L, out);
+}
+
+int lzg_profiles_free(lzg_profiles* p) {
+    if (!p) return LZG_ERR_ARG;
+    cudaSetDevice(p->ctx->device);
+    cudaStreamSynchronize(p->ctx->stream);
+    for (auto& tl : p->tile_lists)
+        if (tl.d_tiles) cudaFree(tl.d_tiles);
+    if (p->d_D) cudaFree(p->d_D);
+    cudaFree(p->d);
+    delete p;
+    return LZG_OK;
+}
+
+int lzg_profiles_shape(const lzg_profiles* p, int32_t* n, int32_t* L) {
+    if (!p) return LZG_ERR_ARG;
+    if (n) *n = p->n;
+    if (L) *L = p->L;
+    return LZG_OK;
+}
+
+// ---- distance ----------------------------------------------------------------------------------
+int lzg_distance_shard_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard, int32_t n_shards, int32_t* d_D, int64_t* pairs_done) {
+    if (!ctx || !p || p->ctx != ctx || n_shards < 1 || shard < 0 || shard >= n_shards || (p->n > 0 && !d_D))
+        return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance: bad argument");
+    return lzg_distance_run(ctx, const_cast<lzg_profiles*>(p), shard, n_shards, d_D, pairs_done);
+}
+
+int lzg_distance_matrix_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t* d_D) {
+    return lzg_distance_shard_device_async(ctx, p, 0, 1, d_D, nullptr);
+}
+
+static int ensure_dD(lzg_ctx* ctx, lzg_profiles* p) {
+    if (p->d_D || p->n == 0) return LZG_OK;
+    LZG_CUDA(ctx, cudaMalloc(&p->d_D, sizeof(int32_t) * (size_t)p->n * p->n));
+    return LZG_OK;
+}
+
+int lzg_distance_matrix(lzg_ctx* ctx, const lzg_profiles* cp, int32_t* D) {
+    if (!ctx || !cp || cp->ctx != ctx || (cp->n > 0 && !D)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance_matrix: bad argument");
+    lzg_profiles* p = const_cast<lzg_profiles*>(cp);
+    if (p->n == 0) return LZG_OK;
+    int rc = ensure_dD(ctx, p);
+    if (rc != LZG_OK) return rc;
+    rc = lzg_distance_run(ctx, p, 0, 1, p->d_D, nullptr);
+    if (rc != LZG_OK) return rc;
+    LZG_CUDA(ctx, cudaMemcpyAsync(D, p->d_D, sizeof(int32_t) * (size_t)p->n * p->n, cudaMemcpyDeviceToHost, ctx->stream));
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LZG_OK;
+}
+
+int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* cp, int32_t shard, int32_t n_shards, int32_t* D, int64_t* pairs_done) {
+    if (!ctx || !cp || cp->ctx != ctx || n_shards < 1 || shard < 0 || shard >= n_shards || (cp->n > 0 && !D))
+        return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance_shard: bad argument");
+    lzg_profiles* p = const_cast<lzg_profiles*>(cp);
+    if (pairs_done) *pairs_done = 0;
+    if (p->n == 0) return LZG_OK;
+    int rc = ensure_dD(ctx, p);
+    if (rc != LZG_OK) return rc;
+    rc = lzg_distance_run(ctx, p, shard, n_shards, p->d_D, pairs_done);
+    if (rc != LZG_OK) return rc;
+    // copy back the strips this shard owns: for tile row r the row strip [r*bm, ..) x [r*bm, n) and
+    // its mirror, the column strip [r*bm, n) x [r*bm, ..)
+    const lzg_tile_list* tl = nullptr;
+    for (auto& c : p->tile_lists)
+        if (c.shard == shard && c.n_shards == n_shards) tl = &c;  // the list lzg_distance_run just used (last match)
+    if (!tl) return lzg_fail(ctx, LZG_ERR_STATE, "tile list missing");
+    const int bm = tl->bm, n = p->n, R = (n + bm - 1) / bm;
+    const size_t pitch = sizeof(int32_t) * (size_t)n;
+    for (int r = 0; r < R; r++) {
+        if (std::min(r, R - 1 - r) % n_shards != shard) continue;
+        int r0 = r * bm, nr = std::min(n, r0 + bm) - r0;
+        size_t o_row = (size_t)r0 * n + r0;
+        LZG_CUDA(ctx, cudaMemcpy2DAsync(D + o_row, pitch, p->d_D + o_row, pitch, sizeof(int32_t) * (size_t)(n - r0), nr, cudaMemcpyDeviceToHost, ctx->stream));
+        if (r0 + nr < n) {
+            size_t o_col = (size_t)(r0 + nr) * n + r0;
+            LZG_CUDA(ctx, cudaMemcpy2DAsync(D + o_col, pitch, p->d_D + o_col, pitch, sizeof(int32_t) * (size_t)nr, n - r0 - nr, cudaMemcpyDeviceToHost, ctx->stream));
+        }
+    }
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LZG_OK;
+}
+
+}  // extern "C"

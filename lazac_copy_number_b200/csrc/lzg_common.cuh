@@ -1,0 +1,64 @@
+// lzg_common.cuh -- shared definitions of liblazac_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "lazac_b200.h"
+
+#define LZG_BIAS 128  // int8 value v is stored as the byte v + 128 (exact unsigned abs-diff / min / max)
+
+struct lzg_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    int64_t launches = 0;
+    void* flush_buf = nullptr;
+    size_t flush_bytes = 0;
+    int* d_flag = nullptr;          // range-check flag
+    int32_t* h_pinned = nullptr;    // small pinned staging area (results, path arrays)
+    size_t h_pinned_ints = 0;
+    int32_t* d_scratch = nullptr;   // small device scratch (path arrays, results)
+    size_t d_scratch_ints = 0;
+};
+
+struct lzg_tile_list {
+    int bm = 0, shard = 0, n_shards = 0;
+    int n_tiles = 0;
+    int64_t pairs = 0;
+    int2* d_tiles = nullptr;
+};
+
+struct lzg_profiles {
+    lzg_ctx* ctx = nullptr;
+    int32_t n = 0, L = 0;
+    int32_t n_pad = 0, l_pad = 0;  // rows padded to 128, positions padded to 128 (pad byte = LZG_BIAS)
+    uint8_t* d = nullptr;          // [n_pad][l_pad]
+    int32_t* d_D = nullptr;        // lazily allocated N x N result used by the host-output entry points
+    std::vector<lzg_tile_list> tile_lists;
+};
+
+int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuccess);
+
+#define LZG_CUDA(ctx, call)                                               \
+    do {                                                                  \
+        cudaError_t e__ = (call);                                         \
+        if (e__ != cudaSuccess) return lzg_fail((ctx), LZG_ERR_CUDA, #call, e__); \
+    } while (0)
+
+#define LZG_LAUNCH_CHECK(ctx)                                             \
+    do {                                                                  \
+        (ctx)->launches++;                                                \
+        cudaError_t e__ = cudaGetLastError();                             \
+        if (e__ != cudaSuccess) return lzg_fail((ctx), LZG_ERR_CUDA, "kernel launch", e__); \
+    } while (0)
+
+// distance module (lzg_distance.cu)
+int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int32_t* d_D,
+                     int64_t* pairs_done);
+// pinned / scratch helpers (lzg_api.cu)
+int lzg_ensure_scratch(lzg_ctx* ctx, size_t ints);

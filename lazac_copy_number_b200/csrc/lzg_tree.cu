@@ -1,0 +1,386 @@
+// lzg_tree.cu -- ZCNT small parsimony on a resident tree (sm_100a).
+//
+// Per position the reference's sankoff()/overlap() (/root/reference/src/copy_number.cxx:116-158)
+// merges child intervals [s1,e1], [s2,e2] into
+//     lo = max(s1,s2), hi = min(e1,e2), start = min(lo,hi), end = max(lo,hi), cost = max(0, lo-hi)
+// (checked branch by branch against the reference in tests/).  Positions are
+// independent, values are biased bytes in HBM, so every thread owns 16 consecutive positions
+// (one 128-bit load per interval vector), widens them to eight u16x2 words with PRMT and runs the
+// merge with the native VIMNMX.U16x2 min/max (there is no native u8x4 min/max on sm_100a).
+#include "lzg_tree.cuh"
+
+#include <algorithm>
+
+namespace {
+
+struct iv16 {  // 16 positions of an interval vector, widened to u16x2 lanes
+    uint32_t s[8], e[8];
+};
+
+__device__ __forceinline__ void widen(const uint4& v, uint32_t* o) {
+    o[0] = __byte_perm(v.x, 0, 0x4140);
+    o[1] = __byte_perm(v.x, 0, 0x4342);
+    o[2] = __byte_perm(v.y, 0, 0x4140);
+    o[3] = __byte_perm(v.y, 0, 0x4342);
+    o[4] = __byte_perm(v.z, 0, 0x4140);
+    o[5] = __byte_perm(v.z, 0, 0x4342);
+    o[6] = __byte_perm(v.w, 0, 0x4140);
+    o[7] = __byte_perm(v.w, 0, 0x4342);
+}
+
+__device__ __forceinline__ uint4 narrow(const uint32_t* o) {
+    uint4 v;
+    v.x = __byte_perm(o[0], o[1], 0x6420);
+    v.y = __byte_perm(o[2], o[3], 0x6420);
+    v.z = __byte_perm(o[4], o[5], 0x6420);
+    v.w = __byte_perm(o[6], o[7], 0x6420);
+    return v;
+}
+
+__device__ __forceinline__ uint4 ldg16(const uint8_t* base, size_t off) {
+    return __ldg(reinterpret_cast<const uint4*>(base + off));
+}
+
+// acc := merge(acc, other); returns the cost of these 16 positions.
+__device__ __forceinline__ uint32_t merge16(iv16& acc, const uint32_t* os, const uint32_t* oe) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        uint32_t lo = __vmaxu2(acc.s[k], os[k]);
+        uint32_t hi = __vminu2(acc.e[k], oe[k]);
+        uint32_t st = __vminu2(lo, hi);
+        acc.e[k] = __vmaxu2(lo, hi);
+        acc.s[k] = st;
+        c += lo - st;  // per-lane lo >= st: no borrow between the two 16-bit lanes
+    }
+    return (c & 0xffffu) + (c >> 16);  // each lane <= 8 * 254
+}
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---- leaves ------------------------------------------------------------------------------------
+__global__ void k_gather_leaves(const uint8_t* __restrict__ prof, int prof_lpad, const int32_t* __restrict__ leaf_row,
+                                uint8_t* __restrict__ start, uint8_t* __restrict__ end, int l_pad) {
+    int u = blockIdx.y;
+    int row = leaf_row[u];
+    int chunk = blockIdx.x * blockDim.x + threadIdx.x;
+    if (chunk * 16 >= l_pad) return;
+    uint4 v = row >= 0 ? ldg16(prof, (size_t)row * prof_lpad + chunk * 16)
+                       : make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
+    *reinterpret_cast<uint4*>(start + (size_t)u * l_pad + chunk * 16) = v;
+    *reinterpret_cast<uint4*>(end + (size_t)u * l_pad + chunk * 16) = v;
+}
+
+// ---- bottom-up, one launch per level (small_rectilinear, src/copy_number.cxx:227-277) -------------
+__global__ void k_merge_level(const int32_t* __restrict__ order, const int32_t* __restrict__ child0,
+                              const int32_t* __restrict__ child1, uint8_t* __restrict__ start,
+                              uint8_t* __restrict__ end, int32_t* __restrict__ cost, int l_pad) {
+    int u = order[blockIdx.y];
+    int c0 = child0[u], c1 = child1[u];
+    int chunk = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t c = 0;
+    if (chunk * 16 < l_pad) {
+        size_t o0 = (size_t)c0 * l_pad + chunk * 16, o1 = (size_t)c1 * l_pad + chunk * 16;
+        uint4 s0 = ldg16(start, o0), e0 = ldg16(end, o0), s1 = ldg16(start, o1), e1 = ldg16(end, o1);
+        iv16 acc;
+        uint32_t os[8], oe[8];
+        widen(s0, acc.s);
+        widen(e0, acc.e);
+        widen(s1, os);
+        widen(e1, oe);
+        c = merge16(acc, os, oe);
+        size_t ou = (size_t)u * l_pad + chunk * 16;
+        *reinterpret_cast<uint4*>(start + ou) = narrow(acc.s);
+        *reinterpret_cast<uint4*>(end + ou) = narrow(acc.e);
+    }
+    c = warp_sum(c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(cost + u, (int32_t)c);
+}
+
+// score[u] = cost[u] + score[c0] + score[c1], level by level (src/copy_number.cxx:264).
+__global__ void k_level_scores(const int32_t* __restrict__ order, const int32_t* __restrict__ level_off, int n_levels,
+                               const int32_t* __restrict__ child0, const int32_t* __restrict__ child1,
+                               const int32_t* __restrict__ cost, int32_t* __restrict__ score) {
+    for (int lv = 0; lv < n_levels; lv++) {
+        int b = level_off[lv], e = level_off[lv + 1];
+        for (int i = b + threadIdx.x; i < e; i += blockDim.x) {
+            int u = order[i];
+            int c0 = child0[u];
+            score[u] = c0 < 0 ? 0 : cost[u] + score[c0] + score[child1[u]];
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+#include "lzg_tree_nni.cuh"
+
+static inline int chunk_threads(int l_pad, int* groups) {
+    int chunks = l_pad / 16;
+    int g = (chunks + 255) / 256;
+    int per = (chunks + g - 1) / g;
+    *groups = g;
+    return ((per + 31) / 32) * 32;
+}
+
+int lzg_tree_upload_topology(lzg_ctx* ctx, lzg_tree* t) {
+    const int n = t->n_nodes;
+    std::vector<int2> up(n, make_int2(-1, -1));
+    t->parent.assign(n, -1);
+    for (int u = 0; u < n; u++) {
+        int a = t->child0[u], b = t->child1[u];
+        if (a >= 0) {
+            t->parent[a] = u;
+            up[a] = make_int2(u, b);
+        }
+        if (b >= 0) {
+            t->parent[b] = u;
+            up[b] = make_int2(u, a);
+        }
+    }
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_child0, t->child0.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_child1, t->child1.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_up, up.data(), sizeof(int2) * n, cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // sources are pageable host vectors
+    return LZG_OK;
+}
+
+int lzg_tree_gather_leaves(lzg_ctx* ctx, lzg_tree* t, const lzg_profiles* p, const int32_t* leaf_row) {
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_order, leaf_row, sizeof(int32_t) * t->n_nodes, cudaMemcpyHostToDevice, ctx->stream));
+    int groups, threads = chunk_threads(t->l_pad, &groups);
+    k_gather_leaves<<<dim3(groups, t->n_nodes), threads, 0, ctx->stream>>>(p->d, p->l_pad, t->d_order, t->d_start, t->d_end, t->l_pad);
+    LZG_LAUNCH_CHECK(ctx);
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LZG_OK;
+}
+
+// Level schedule by height above the leaves; one merge launch per level, deepest first.
+int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t) {
+    const int n = t->n_nodes;
+    std::vector<int32_t> height(n, 0), order;
+    std::vector<int32_t> stack;
+    // post-order without recursion
+    std::vector<int32_t> post;
+    post.reserve(n);
+    stack.push_back(0);
+    while (!stack.empty()) {
+        int u = stack.back();
+        stack.pop_back();
+        post.push_back(u);
+        if (t->child0[u] >= 0) {
+            stack.push_back(t->child0[u]);
+            stack.push_back(t->child1[u]);
+        }
+    }
+    if ((int)post.size() != n) return lzg_fail(ctx, LZG_ERR_ARG, "tree is not connected from node 0");
+    int max_h = 0;
+    for (int i = n - 1; i >= 0; i--) {
+        int u = post[i];
+        if (t->child0[u] >= 0) height[u] = 1 + std::max(height[t->child0[u]], height[t->child1[u]]);
+        max_h = std::max(max_h, height[u]);
+    }
+    std::vector<int32_t> level_off(max_h + 2, 0);
+    for (int u = 0; u < n; u++) level_off[height[u] + 1]++;
+    for (int h = 0; h <= max_h; h++) level_off[h + 1] += level_off[h];
+    order.resize(n);
+    {
+        std::vector<int32_t> fill(level_off.begin(), level_off.end() - 1);
+        for (int u = 0; u < n; u++) order[fill[height[u]]++] = u;
+    }
+    LZG_CUDA(ctx, lzg_ensure_scratch(ctx, level_off.size()) == LZG_OK ? cudaSuccess : cudaErrorMemoryAllocation);
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_order, order.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->d_scratch, level_off.data(), sizeof(int32_t) * level_off.size(), cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cost, 0, sizeof(int32_t) * n, ctx->stream));
+    int groups, threads = chunk_threads(t->l_pad, &groups);
+    for (int h = 1; h <= max_h; h++) {
+        int cnt = level_off[h + 1] - level_off[h];
+        for (int done = 0; done < cnt; done += 65535) {  // gridDim.y limit
+            int part = std::min(65535, cnt - done);
+            k_merge_level<<<dim3(groups, part), threads, 0, ctx->stream>>>(t->d_order + level_off[h] + done, t->d_child0, t->d_child1,
+                                                                           t->d_start, t->d_end, t->d_cost, t->l_pad);
+            LZG_LAUNCH_CHECK(ctx);
+        }
+    }
+    k_level_scores<<<1, 1024, 0, ctx->stream>>>(t->d_order, ctx->d_scratch, max_h + 1, t->d_child0, t->d_child1, t->d_cost, t->d_score);
+    LZG_LAUNCH_CHECK(ctx);
+    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_score, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    t->root_score = ctx->h_pinned[0];
+    t->scored = true;
+    return LZG_OK;
+}
+
+static int ensure_cand_buffers(lzg_ctx* ctx, lzg_tree* t, int n_moves) {
+    if (n_moves <= t->cand_cap) return LZG_OK;
+    int cap = std::max(n_moves, 2 * t->n_nodes);
+    if (t->d_moves) cudaFree(t->d_moves);
+    if (t->d_cand_score) cudaFree(t->d_cand_score);
+    t->d_moves = nullptr;
+    t->d_cand_score = nullptr;
+    t->cand_cap = 0;
+    LZG_CUDA(ctx, cudaMalloc(&t->d_moves, sizeof(int32_t) * 4 * (size_t)cap));
+    LZG_CUDA(ctx, cudaMalloc(&t->d_cand_score, sizeof(int32_t) * (size_t)cap));
+    t->cand_cap = cap;
+    return LZG_OK;
+}
+
+static bool is_move(const lzg_tree* t, int u, int w, int v, int z) {
+    const int n = t->n_nodes;
+    if (u < 0 || u >= n || v < 0 || v >= n || w < 0 || w >= n || z < 0 || z >= n) return false;
+    if (t->child0[v] < 0) return false;                       // v must be internal
+    if (t->parent[v] != u || t->parent[w] != u || w == v) return false;
+    if (t->parent[z] != v) return false;
+    return true;
+}
+
+int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
+                        int32_t* best_index, int32_t* best_score, int32_t* all_scores) {
+    t->last_v.resize(n_moves);
+    for (int i = 0; i < n_moves; i++) {
+        const int32_t* m = moves + 4 * (size_t)i;
+        if (!is_move(t, m[0], m[1], m[2], m[3])) return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "candidate is not an NNI move of this topology");
+        t->last_v[i] = m[2];
+    }
+    if (n_moves == 0) {
+        *best_index = -1;
+        *best_score = t->root_score;
+        return LZG_OK;
+    }
+    int rc = ensure_cand_buffers(ctx, t, n_moves);
+    if (rc != LZG_OK) return rc;
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_moves, moves, sizeof(int32_t) * 4 * (size_t)n_moves, cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand_score, 0, sizeof(int32_t) * (size_t)n_moves, ctx->stream));
+    int groups, threads = chunk_threads(t->l_pad, &groups);
+    k_nni_scores<<<dim3(n_moves, groups), threads, 0, ctx->stream>>>(t->d_moves, t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end,
+                                                                       t->d_score, t->d_cand_score, t->l_pad);
+    LZG_LAUNCH_CHECK(ctx);
+    k_nni_argmin<<<1, 1024, 0, ctx->stream>>>(t->d_cand_score, n_moves, t->d_score, greedy, ctx->d_scratch);
+    LZG_LAUNCH_CHECK(ctx);
+    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, ctx->d_scratch, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    if (all_scores)
+        LZG_CUDA(ctx, cudaMemcpyAsync(all_scores, t->d_cand_score, sizeof(int32_t) * (size_t)n_moves, cudaMemcpyDeviceToHost, ctx->stream));
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *best_index = ctx->h_pinned[0];
+    *best_score = ctx->h_pinned[1];
+    return LZG_OK;
+}
+
+int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
+    if (!is_move(t, u, w, v, z)) return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "not an NNI move of this topology");
+    // host mirror
+    int y = t->child0[v] == z ? t->child1[v] : t->child0[v];
+    t->child0[v] = std::min(w, y);
+    t->child1[v] = std::max(w, y);
+    t->child0[u] = std::min(v, z);
+    t->child1[u] = std::max(v, z);
+    t->parent[w] = v;
+    t->parent[z] = u;
+    int depth = 0;
+    for (int a = v; a != 0; a = t->parent[a]) depth++;
+    k_apply_topology<<<1, 1, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, u, w, v, z);
+    LZG_LAUNCH_CHECK(ctx);
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cost, 0, sizeof(int32_t) * (size_t)(depth + 1), ctx->stream));
+    int groups, threads = chunk_threads(t->l_pad, &groups);
+    k_rescore_path<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_cost, v, t->l_pad);
+    LZG_LAUNCH_CHECK(ctx);
+    k_path_scores<<<1, 1, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_cost, t->d_score, v);
+    LZG_LAUNCH_CHECK(ctx);
+    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_score, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    t->root_score = ctx->h_pinned[0];
+    return LZG_OK;
+}
+
+static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, int L, int l_pad, int32_t* h_dst) {
+    // convert on the device in row blocks of <= 64 MiB of int32, then copy out
+    const size_t max_ints = (size_t)16 << 20;
+    int block_rows = (int)std::max<size_t>(1, std::min<size_t>(rows, max_ints / std::max(1, L)));
+    int32_t* d_tmp = nullptr;
+    LZG_CUDA(ctx, cudaMalloc(&d_tmp, sizeof(int32_t) * (size_t)block_rows * L));
+    for (int r0 = 0; r0 < rows; r0 += block_rows) {
+        int nr = std::min(block_rows, rows - r0);
+        dim3 grid(std::max(1, std::min(64, (L + 255) / 256)), nr);
+        k_unpack_i32<<<grid, 256, 0, ctx->stream>>>(d_src + (size_t)r0 * l_pad, d_tmp, L, l_pad);
+        ctx->launches++;
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h_dst + (size_t)r0 * L, d_tmp, sizeof(int32_t) * (size_t)nr * L, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) {
+            cudaFree(d_tmp);
+            return lzg_fail(ctx, LZG_ERR_CUDA, "interval download", e);
+        }
+    }
+    cudaFree(d_tmp);
+    return LZG_OK;
+}
+
+int lzg_tree_download(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end, int32_t* score) {
+    int rc = LZG_OK;
+    if (start) rc = download_bytes_as_i32(ctx, t->d_start, t->n_nodes, t->L, t->l_pad, start);
+    if (rc == LZG_OK && end) rc = download_bytes_as_i32(ctx, t->d_end, t->n_nodes, t->L, t->l_pad, end);
+    if (rc == LZG_OK && score) {
+        LZG_CUDA(ctx, cudaMemcpyAsync(score, t->d_score, sizeof(int32_t) * t->n_nodes, cudaMemcpyDeviceToHost, ctx->stream));
+        LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return rc;
+}
+
+// Depth-level schedule, root first.
+int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* branch) {
+    const int n = t->n_nodes;
+    std::vector<int32_t> order, level_off;
+    order.reserve(n);
+    order.push_back(0);
+    level_off.push_back(0);
+    size_t b = 0;
+    while (b < order.size()) {
+        size_t e = order.size();
+        level_off.push_back((int32_t)e);
+        for (size_t i = b; i < e; i++) {
+            int u = order[i];
+            if (t->child0[u] >= 0) {
+                order.push_back(t->child0[u]);
+                order.push_back(t->child1[u]);
+            }
+        }
+        b = e;
+    }
+    uint8_t* d_label = nullptr;
+    int32_t* d_branch = nullptr;
+    LZG_CUDA(ctx, cudaMalloc(&d_label, (size_t)n * t->l_pad));
+    cudaError_t e = cudaMalloc(&d_branch, sizeof(int32_t) * n);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_branch, 0, sizeof(int32_t) * n, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(t->d_order, order.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream);
+    int rc = LZG_OK;
+    if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "labeling setup", e);
+    int groups, threads = chunk_threads(t->l_pad, &groups);
+    for (size_t lv = 0; rc == LZG_OK && lv + 1 < level_off.size(); lv++) {
+        int cnt = level_off[lv + 1] - level_off[lv];
+        for (int done = 0; done < cnt; done += 65535) {
+            int part = std::min(65535, cnt - done);
+            k_label_level<<<dim3(groups, part), threads, 0, ctx->stream>>>(t->d_order + level_off[lv] + done, t->d_up, t->d_start, t->d_end,
+                                                                           d_label, d_branch, t->l_pad);
+            ctx->launches++;
+        }
+    }
+    if (rc == LZG_OK) {
+        e = cudaGetLastError();
+        if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "labeling launch", e);
+    }
+    if (rc == LZG_OK && labels) rc = download_bytes_as_i32(ctx, d_label, n, t->L, t->l_pad, labels);
+    if (rc == LZG_OK && branch) {
+        e = cudaMemcpyAsync(branch, d_branch, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "branch download", e);
+        else branch[0] = -1;
+    }
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_label);
+    cudaFree(d_branch);
+    return rc;
+}

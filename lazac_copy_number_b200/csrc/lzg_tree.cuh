@@ -1,0 +1,35 @@
+// lzg_tree.cuh -- resident tree state for ZCNT small parsimony (sm_100a).
+#pragma once
+#include "lzg_common.cuh"
+
+// Replaces digraph<rectilinear_vertex_data> (/root/reference/include/copy_number.hpp:98-105,
+// include/digraph.hpp:24-109): topology as flat arrays (host mirror + device copy), the
+// per-node interval vectors start/end as biased bytes [n_nodes][l_pad] in HBM, cumulative
+// subtree scores as int32.
+struct lzg_tree {
+    lzg_ctx* ctx = nullptr;
+    int32_t n_nodes = 0, L = 0, l_pad = 0;
+    std::vector<int32_t> child0, child1, parent;  // host mirror (child0 < child1, -1 for leaves)
+    int32_t *d_child0 = nullptr, *d_child1 = nullptr;
+    int2* d_up = nullptr;       // (parent, sibling) per node, (-1,-1) for the root
+    uint8_t *d_start = nullptr, *d_end = nullptr;
+    int32_t* d_score = nullptr;  // cumulative subtree score (t[u].data.score)
+    int32_t* d_cost = nullptr;   // per-node merge cost / per-step path cost scratch [n_nodes]
+    int32_t* d_order = nullptr;  // level-ordered node list scratch [n_nodes]
+    bool scored = false;         // == every node visited
+    int32_t root_score = 0;
+    // candidate buffers, grown on demand
+    int32_t cand_cap = 0;
+    int32_t* d_moves = nullptr;       // [cand_cap][4]
+    int32_t* d_cand_score = nullptr;  // [cand_cap]
+    std::vector<int32_t> last_v;      // v of every candidate of the last lzg_nni_best
+};
+
+int lzg_tree_upload_topology(lzg_ctx* ctx, lzg_tree* t);
+int lzg_tree_gather_leaves(lzg_ctx* ctx, lzg_tree* t, const lzg_profiles* p, const int32_t* leaf_row);
+int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t);
+int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
+                        int32_t* best_index, int32_t* best_score, int32_t* all_scores);
+int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z);
+int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* branch);
+int lzg_tree_download(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end, int32_t* score);

@@ -1,0 +1,79 @@
+"""GPU parity: all-pairs ZCNT distance through the C ABI vs the oracle (bit-exact)."""
+import numpy as np
+import pytest
+
+from lazac_copy_number_b200 import synth
+from lazac_copy_number_b200._capi import LazacGpuError
+from lazac_copy_number_b200.api import Profiles
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,L", [(1, 1), (2, 3), (10, 255), (63, 129), (64, 128), (65, 127), (130, 1000),
+                                 (257, 513), (300, 2048), (1000, 700)])
+def test_distance_matches_oracle(ctx, port, n, L):
+    bp = synth.random_bp(n, L, seed=n * 7 + L, lo=-9, hi=9, density=0.3)
+    prof = Profiles(ctx, bp)
+    D = prof.distance_matrix()
+    prof.free()
+    assert D.dtype == np.int32 and D.shape == (n, n)
+    assert np.array_equal(D, port.distance_matrix(bp))
+
+
+def test_distance_extreme_values(ctx, port):
+    rng = np.random.default_rng(5)
+    bp = rng.choice(np.array([-127, 127, 0, 1, -1], np.int32), size=(70, 333))
+    prof = Profiles(ctx, bp)
+    assert np.array_equal(prof.distance_matrix(), port.distance_matrix(bp))
+    prof.free()
+
+
+def test_distance_int8_upload(ctx, port):
+    bp = synth.random_bp(90, 777, seed=3).astype(np.int8)
+    prof = Profiles(ctx, bp)
+    assert np.array_equal(prof.distance_matrix(), port.distance_matrix(bp.astype(np.int32)))
+    prof.free()
+
+
+def test_range_error(ctx):
+    bp = np.zeros((4, 10), np.int32)
+    bp[2, 3] = 128
+    with pytest.raises(LazacGpuError) as e:
+        Profiles(ctx, bp)
+    assert e.value.status == 3
+
+
+def test_empty(ctx):
+    prof = Profiles(ctx, np.zeros((0, 5), np.int32))
+    assert prof.distance_matrix().shape == (0, 0)
+    prof.free()
+    prof = Profiles(ctx, np.zeros((3, 0), np.int32))
+    assert np.array_equal(prof.distance_matrix(), np.zeros((3, 3), np.int32))
+    prof.free()
+
+
+def test_large_tile_path_vs_properties(ctx, port):
+    """128x128-tile path (many cells): rows checked against the oracle, whole matrix by properties."""
+    n, L = 2500, 640
+    bp = synth.random_bp(n, L, seed=11, density=0.2)
+    prof = Profiles(ctx, bp)
+    D = prof.distance_matrix()
+    prof.free()
+    assert np.array_equal(D, D.T) and not D.diagonal().any()
+    rows = port.distance_rows(bp, 1234, 1250)
+    for k in range(16):
+        assert np.array_equal(D[1234 + k, 1234 + k:], rows[k, 1234 + k:])
+    assert np.array_equal(D[0], np.abs(bp - bp[0]).sum(1))
+    assert np.array_equal(D[n - 1], np.abs(bp - bp[n - 1]).sum(1))
+
+
+@pytest.mark.parametrize("n_shards", [2, 3, 8])
+def test_shards_union_is_full_matrix(ctx, port, n_shards):
+    n, L = 700, 300
+    bp = synth.random_bp(n, L, seed=2)
+    prof = Profiles(ctx, bp)
+    D = np.full((n, n), -1, np.int32)
+    pairs = sum(prof.distance_shard(s, n_shards, D) for s in range(n_shards))
+    prof.free()
+    assert pairs == n * (n + 1) // 2
+    assert np.array_equal(D, port.distance_matrix(bp))

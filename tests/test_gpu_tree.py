@@ -1,0 +1,143 @@
+"""GPU parity: small parsimony, NNI neighbourhood scoring, move application and labeling through
+the C ABI vs the oracle (bit-exact intervals, scores, chosen moves, labels)."""
+import numpy as np
+import pytest
+
+from lazac_copy_number_b200 import synth
+from lazac_copy_number_b200._capi import LazacGpuError
+from lazac_copy_number_b200.api import Profiles, Tree
+from oracle import PortTree
+
+pytestmark = pytest.mark.gpu
+
+
+def make_case(n_leaves, bins, alleles, seed, shuffle_tree=True):
+    prof = synth.make_profiles(n_leaves, bins, alleles, seed=seed, want_tree=True)
+    bp = synth.bp_from_cn(prof["cn"], prof["seg"])
+    rng = np.random.default_rng(seed + 100)
+    c0, c1 = (synth.random_tree(n_leaves, rng) if shuffle_tree else (prof["child0"], prof["child1"]))
+    n = 2 * n_leaves - 1
+    leaf_row = np.full(n, -1, np.int32)
+    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
+    leaf_bp = np.zeros((n, bp.shape[1]), np.int32)
+    leaf_bp[n_leaves - 1:] = bp
+    return bp, c0, c1, leaf_row, leaf_bp
+
+
+def assert_same_state(gt, pt):
+    S, E, sc = gt.intervals()
+    assert np.array_equal(sc, pt.score)
+    assert np.array_equal(S, pt.start)
+    assert np.array_equal(E, pt.end)
+
+
+@pytest.mark.parametrize("n_leaves,bins,alleles", [(2, 5, 1), (3, 40, 1), (10, 255, 1), (40, 300, 2), (150, 1000, 2)])
+def test_full_score_and_intervals(ctx, port, n_leaves, bins, alleles):
+    bp, c0, c1, leaf_row, leaf_bp = make_case(n_leaves, bins, alleles, seed=n_leaves)
+    prof = Profiles(ctx, bp)
+    gt = Tree(ctx, prof, c0, c1, leaf_row)
+    pt = PortTree(port, c0, c1, leaf_bp)
+    assert gt.small_rectilinear() == pt.small_rectilinear()
+    assert_same_state(gt, pt)
+    gt.free()
+    prof.free()
+
+
+@pytest.mark.parametrize("n_leaves,bins,alleles,greedy", [(4, 30, 1, False), (10, 255, 1, False), (60, 500, 2, False),
+                                                          (60, 500, 2, True), (200, 1200, 1, False)])
+def test_neighbourhood_scores_and_choice(ctx, port, n_leaves, bins, alleles, greedy):
+    bp, c0, c1, leaf_row, leaf_bp = make_case(n_leaves, bins, alleles, seed=3 * n_leaves)
+    prof = Profiles(ctx, bp)
+    gt = Tree(ctx, prof, c0, c1, leaf_row)
+    pt = PortTree(port, c0, c1, leaf_bp)
+    gt.small_rectilinear()
+    pt.small_rectilinear()
+    eu, ev = pt.edges()
+    geu, gev = gt.edges()
+    assert np.array_equal(eu, geu) and np.array_equal(ev, gev)
+    order = np.random.default_rng(1).permutation(len(eu)).astype(np.int32)
+    full = pt.greedy_nni(eu, ev, order, greedy=False)           # every candidate's score
+    want = pt.greedy_nni(eu, ev, order, greedy=greedy, want_all=False)
+    moves = gt.enumerate_moves(eu, ev, order)
+    assert np.array_equal(moves, full["moves"])
+    idx, score, allsc = gt.nni_best(moves, greedy=greedy, want_all=True)
+    assert np.array_equal(allsc, full["scores"])
+    assert idx == want["index"]
+    if want["found"]:
+        assert score == want["score"] and tuple(moves[idx]) == want["move"]
+    merges, nbytes = gt.last_nni_work()
+    assert merges >= 2 * len(moves) and nbytes == (merges + len(moves)) * 2 * gt.L
+    gt.free()
+    prof.free()
+
+
+def test_hill_climb_trajectory(ctx, port):
+    """Repeated greedy_nni + apply: identical move sequence, scores and intervals at every step."""
+    bp, c0, c1, leaf_row, leaf_bp = make_case(50, 600, 2, seed=9)
+    prof = Profiles(ctx, bp)
+    gt = Tree(ctx, prof, c0, c1, leaf_row)
+    pt = PortTree(port, c0, c1, leaf_bp)
+    assert gt.small_rectilinear() == pt.small_rectilinear()
+    eu, ev = pt.edges()
+    order = np.random.default_rng(4).permutation(len(eu)).astype(np.int32)
+    steps = 0
+    for _ in range(60):
+        eu, ev = pt.edges()  # re-indexing every step is fine here: both sides use the same lists
+        want = pt.greedy_nni(eu, ev, order, want_all=False)
+        got = gt.greedy_nni(eu, ev, order)
+        assert got == want["move"]
+        if got is None:
+            break
+        assert gt.apply_nni(*got) == pt.apply_nni(*got)
+        assert_same_state(gt, pt)
+        steps += 1
+    assert steps >= 3
+    gt.free()
+    prof.free()
+
+
+def test_clone_set_topology_and_labeling(ctx, port):
+    bp, c0, c1, leaf_row, leaf_bp = make_case(35, 400, 2, seed=21)
+    prof = Profiles(ctx, bp)
+    gt = Tree(ctx, prof, c0, c1, leaf_row)
+    gt.small_rectilinear()
+    g2 = gt.clone()
+    rng = np.random.default_rng(8)
+    d0, d1 = synth.random_tree(35, rng)
+    g2.set_topology(d0, d1)
+    p2 = PortTree(port, d0, d1, leaf_bp)
+    assert g2.small_rectilinear() == p2.small_rectilinear()
+    assert_same_state(g2, p2)
+    p1 = PortTree(port, c0, c1, leaf_bp)
+    p1.small_rectilinear()
+    assert_same_state(gt, p1)  # the clone's re-scoring did not touch the original
+    for g, p in ((gt, p1), (g2, p2)):
+        got, want = g.ancestral_labeling(), p.ancestral_labeling()
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b)
+        assert int(want[3][1:].sum()) == int(p.score[0])  # score = sum of branch lengths
+    gt.free()
+    g2.free()
+    prof.free()
+
+
+def test_errors(ctx):
+    bp = synth.random_bp(3, 20, seed=1)
+    prof = Profiles(ctx, bp)
+    c0 = np.array([1, 3, -1, -1, -1], np.int32)
+    c1 = np.array([2, 4, -1, -1, -1], np.int32)
+    rows = np.array([-1, -1, 0, 1, 2], np.int32)
+    with pytest.raises(LazacGpuError) as e:  # unary node: the reference's logic_error
+        Tree(ctx, prof, np.array([1, 3, -1, -1, -1]), np.array([2, -1, -1, -1, -1]), rows)
+    assert e.value.status == 2
+    t = Tree(ctx, prof, c0, c1, rows)
+    with pytest.raises(LazacGpuError) as e:  # not scored yet
+        t.nni_best([(0, 2, 1, 3)])
+    assert e.value.status == 6
+    t.small_rectilinear()
+    with pytest.raises(LazacGpuError) as e:  # w is not a child of u
+        t.nni_best([(0, 3, 1, 4)])
+    assert e.value.status == 7
+    assert t.nni_best(np.zeros((0, 4), np.int32))[0] == -1
+    t.free()
+    prof.free()
