@@ -1,0 +1,412 @@
+#!/usr/bin/env python
+"""bench.py -- ZCNT hot-path throughput on B200 (contract: one JSON line on stdout from rank 0).
+
+    python bench.py --gpus 1 --steps K --warmup W            # 1 GPU: BASELINE.json configs[1]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference ...                     # the reference's own CPU code
+
+Workloads (BASELINE.json `configs`); a step = one whole distance matrix:
+  cfg2  1,000 cells x 5,000 bins x 2 alleles (L = 10,000)   default at --gpus 1
+  cfg3  20,000 cells x 10,000 bins x 2 alleles (L = 20,000)  default at --gpus > 1: tile rows of
+        the ONE matrix are dealt to the ranks (strong scaling, no data-path collective; every
+        rank ends with its own row/column strips)
+The NNI path (cfg4: 1,000 cells x 5,000 bins, NJ seed tree, one neighbourhood pass per step) is
+reported under "nni" in the same line at --gpus 1.
+
+value   = cell pairs (n(n+1)/2, as the reference's loop counts them, src/lazac.cxx:81-91) per
+          second with the packed profiles already resident in HBM; device time (CUDA events on
+          the library's stream), summed over the K steps, max over ranks; L2 flushed between steps.
+e2e     = the same through the host-buffer C-ABI calls a caller of build_distance_matrix would
+          make (lzg_profiles_upload_i8 + lzg_distance_matrix / lzg_distance_shard), pinned host
+          buffers, H2D and D2H inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "cfg2": dict(cells=1000, bins=5000, alleles=2),
+    "cfg3": dict(cells=20000, bins=10000, alleles=2),
+    "tiny": dict(cells=200, bins=500, alleles=2),       # CPU-side plumbing tests only
+}
+NNI_WORKLOADS = {
+    "cfg4": dict(cells=1000, bins=5000, alleles=1),
+    "tiny": dict(cells=60, bins=300, alleles=1),
+}
+# VABSDIFF4.U8.ACC issue rate measured on this pool's B200 (tools/microbench.cu,
+# profiles/r01_microbench_int_pipes.jsonl): 62.94 lane-instr/clk/SM x 148 SMs x 1.965 GHz.
+SAD4_PEAK_LANE_INSTR_PER_S = 1.8304e13
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, local, world
+
+
+def make_workload(name):
+    from lazac_copy_number_b200 import synth
+    w = WORKLOADS[name]
+    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)
+    bp = synth.bp_from_cn(prof["cn"], prof["seg"]).astype(np.int8)  # |bp| <= 8: int8 exact
+    return bp
+
+
+def bp_int8_chunked(cn, seg, rows=2000):
+    from lazac_copy_number_b200 import synth
+    out = np.empty(cn.shape, np.int8)
+    for r0 in range(0, cn.shape[0], rows):
+        out[r0:r0 + rows] = synth.bp_from_cn(cn[r0:r0 + rows], seg).astype(np.int8)
+    return out
+
+
+def cpu_distance_sample(bp, n_sample):
+    """The reference's pair loop on the first n_sample cells, single-threaded (the reference has
+    no threads).  Uses oracle/_ref (the unmodified reference functions) when it was built, else
+    the C port.  Returns (pairs/s, kind, seconds, pairs)."""
+    from oracle import Port, have_ref
+    sub = np.ascontiguousarray(bp[:n_sample].astype(np.int32))
+    if have_ref():
+        from oracle.ref import Ref
+        fn, kind = Ref().distance_matrix, "reference"
+    else:
+        fn, kind = Port().distance_matrix, "port"
+    t0 = time.perf_counter()
+    fn(sub)
+    dt = time.perf_counter() - t0
+    pairs = n_sample * (n_sample + 1) // 2
+    return pairs / dt, kind, dt, pairs
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on this box's host
+    cores (1 thread: the reference is single-threaded), each step a bounded sample."""
+    rank, local, world = dist_env()
+    if rank != 0:
+        return
+    name = args.workload or ("cfg2" if args.gpus == 1 else "cfg3")
+    w = WORKLOADS[name]
+    from lazac_copy_number_b200 import synth
+    # the sample only needs the first cells: generate a smaller tree of the same shape per cell
+    n_sample = min(w["cells"], args.ref_cells or (160 if w["bins"] * w["alleles"] <= 10000 else 110))
+    prof = synth.make_profiles(n_sample, w["bins"], w["alleles"], seed=0)
+    bp = bp_int8_chunked(prof["cn"], prof["seg"])
+    for _ in range(args.warmup):
+        cpu_distance_sample(bp, max(8, n_sample // 4))
+    tot_pairs, tot_t, kind = 0, 0.0, "port"
+    for _ in range(args.steps):
+        v, kind, dt, pairs = cpu_distance_sample(bp, n_sample)
+        tot_pairs += pairs
+        tot_t += dt
+    value = tot_pairs / tot_t
+    sample = "%d cells x %d positions of %s (%d pairs per step)" % (n_sample, bp.shape[1], name, n_sample * (n_sample + 1) // 2)
+    line = {
+        "impl": "reference", "metric": "zcnt_cell_pairs_per_sec", "value": value, "unit": "cell-pairs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps),
+        "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None,
+        "dtype": "int32", "data": "synthetic",
+        "config": {"workload": name, "cells": w["cells"], "bins": w["bins"], "alleles": w["alleles"],
+                   "positions": bp.shape[1], "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "cell-pairs/s", "cores": 1, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "cell-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def nni_section(ctx, args, peaks, peaks_kind):
+    """cfg4: one NNI neighbourhood pass per step on an NJ seed tree (1 GPU)."""
+    from lazac_copy_number_b200 import nj, synth
+    from lazac_copy_number_b200.api import Profiles, Tree
+    name = "tiny" if args.workload == "tiny" else "cfg4"
+    w = NNI_WORKLOADS[name]
+    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)
+    bp = bp_int8_chunked(prof["cn"], prof["seg"])
+    n_leaves, L = bp.shape
+    gp = Profiles(ctx, bp)
+    D = gp.distance_matrix()
+    c0, c1 = nj.neighbor_joining(D)
+    n = 2 * n_leaves - 1
+    leaf_row = np.full(n, -1, np.int32)
+    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
+    t = Tree(ctx, gp, c0, c1, leaf_row)
+    root = t.small_rectilinear()
+    eu, ev = t.edges()
+    order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
+    moves = t.enumerate_moves(eu, ev, order)
+    dep = nj.depths(c0, c1)
+    for _ in range(max(3, args.warmup)):
+        idx, score, _ = t.nni_best(moves)
+    # device time of the pass (upload of the move list, scorer, argmin, 8-byte read-back)
+    dev_ms, wall = 0.0, 0.0
+    for _ in range(args.steps):
+        ctx.flush_l2()
+        ctx.sync()
+        t0 = time.perf_counter()
+        ctx.timer_start()
+        idx, score, _ = t.nni_best(moves)
+        dev_ms += ctx.timer_stop()
+        wall += time.perf_counter() - t0
+    merges, nbytes = t.last_nni_work()
+    C_ = len(moves)
+    out = {
+        "metric": "nni_candidates_scored_per_sec", "value": C_ * args.steps / (dev_ms * 1e-3), "unit": "candidates/s",
+        "e2e": {"value": C_ * args.steps / wall, "unit": "candidates/s", "h2d_bytes_per_step": int(moves.nbytes), "d2h_bytes_per_step": 8},
+        "ms_per_step": dev_ms / args.steps,
+        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_, "seed_tree": "NJ (numpy float64) of the GPU distance matrix",
+                   "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()), "merges_per_pass": int(merges),
+                   "root_score": int(root), "best_index": int(idx), "best_score": int(score), "l2": "flushed between steps"},
+        "roofline": {"bound": "hbm", "achieved": nbytes / (dev_ms / args.steps * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": nbytes / (dev_ms / args.steps * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
+                     "algorithmic_bytes_per_pass": int(nbytes),
+                     "note": "tree state (%.1f MB) fits the 126 MB L2: path re-reads hit L2, so achieved can exceed the HBM peak" % (2 * n * L / 1e6)},
+    }
+    if not args.no_cpu:
+        # the reference's candidate loop (src/copy_number.cxx:347-366) on the same tree, 1 thread
+        from oracle import Port, PortTree, have_ref
+        leaf_bp = np.zeros((n, L), np.int32)
+        leaf_bp[n_leaves - 1:] = bp
+        if have_ref():
+            from oracle.ref import Ref
+            rt = Ref().tree(c0, c1, leaf_bp)
+            rt.small_rectilinear()
+            t0 = time.perf_counter()
+            mv, sc = rt.candidate_scores(eu, ev, order)
+            dt = time.perf_counter() - t0
+            kind = "reference"
+        else:
+            pt = PortTree(Port(), c0, c1, leaf_bp)
+            pt.small_rectilinear()
+            t0 = time.perf_counter()
+            r = pt.greedy_nni(eu, ev, order)
+            dt = time.perf_counter() - t0
+            sc, kind = r["scores"], "port"
+        _, _, allsc = t.nni_best(moves, want_all=True)
+        out["cpu_baseline"] = {"value": C_ / dt, "unit": "candidates/s", "cores": 1, "kind": kind, "sample": "the same full pass (%d candidates)" % C_,
+                               "scores_equal_gpu": bool(np.array_equal(sc, allsc))}
+    t.free()
+    gp.free()
+    return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from lazac_copy_number_b200.api import Context, Profiles
+
+    rank, local, world = dist_env()
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d" % (args.gpus, args.gpus))
+    if not torch.cuda.is_available():
+        sys.exit("no GPU: the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    peaks, peaks_kind = measured_peaks()
+
+    name = args.workload or ("cfg2" if world == 1 else "cfg3")
+    w = WORKLOADS[name]
+    from lazac_copy_number_b200 import synth
+    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)   # same seed on every rank
+    bp = bp_int8_chunked(prof["cn"], prof["seg"])
+    del prof
+    n, L = bp.shape
+    P = n * (n + 1) // 2
+
+    ctx = Context(local)
+    gp = Profiles(ctx, bp)
+    d_D = torch.empty((n, n), dtype=torch.int32, device="cuda")
+    shard, n_shards = rank, world
+
+    def barrier():
+        ctx.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def step_device():
+        ctx.flush_l2()
+        ctx.timer_start()
+        pairs = gp.distance_device_async(d_D.data_ptr(), shard, n_shards)
+        return ctx.timer_stop(), pairs
+
+    for _ in range(max(3, args.warmup)):
+        step_device()
+    barrier()
+    launches0 = ctx.launch_count()
+    clocks = ClockSampler(local)
+    clocks.start()
+    t_wall0 = time.perf_counter()
+    ms_list, my_pairs = [], 0
+    for _ in range(args.steps):
+        ms, my_pairs = step_device()
+        ms_list.append(ms)
+    barrier()
+    wall = time.perf_counter() - t_wall0
+    clk = clocks.stop()
+    launches = ctx.launch_count() - launches0
+    dev_ms = float(sum(ms_list))
+    tt = torch.tensor([dev_ms, float(my_pairs)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = tt.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dev_ms_max, pairs_total = float(mx[0]), int(sm[1])
+    else:
+        dev_ms_max, pairs_total = dev_ms, my_pairs
+    assert pairs_total == P, (pairs_total, P)
+    value = P * args.steps / (dev_ms_max * 1e-3)
+
+    # ---- e2e: host buffers through the C ABI (upload + compute + download), pinned memory ----
+    h_bp = ctx.pinned(bp.shape, np.int8)
+    h_bp[...] = bp
+    h_D = ctx.pinned((n, n), np.int32)
+    def step_e2e():
+        p = Profiles(ctx, h_bp)
+        if world == 1:
+            p.distance_matrix(h_D)
+        else:
+            p.distance_shard(shard, n_shards, h_D)
+        p.free()
+    for _ in range(3):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te[0])
+    d2h = 4 * n * n if world == 1 else None
+
+    line = None
+    if rank == 0:
+        ms_step = dev_ms_max / args.steps
+        lane_instr = P * (L / 4.0)                       # one VABSDIFF4.ACC per 4 positions of a pair
+        achieved = lane_instr / world / (ms_step * 1e-3)  # per GPU
+        hbm_bytes = n * L + 4 * n * n
+        line = {
+            "metric": "zcnt_cell_pairs_per_sec", "value": value, "unit": "cell-pairs/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u8 (int8 + 128 bias), int32 accumulate",
+            "data": "synthetic",
+            "config": {"workload": name, "cells": n, "bins": w["bins"], "alleles": w["alleles"], "positions": L, "pairs": P,
+                       "position_ops_per_step": P * L, "sharding": "tile rows dealt in pairs (r, R-1-r) to %d rank(s)" % world,
+                       "l2": "flushed between timed steps (256 MiB write)", "timing": "CUDA events on the library stream, summed over steps, max over ranks"},
+            "e2e": {"value": P * args.steps / e2e_s, "unit": "cell-pairs/s", "h2d_bytes_per_step": int(n * L),
+                    "d2h_bytes_per_step": int(d2h) if d2h is not None else int(4 * n * n // world),
+                    "ms_per_step": 1e3 * e2e_s / args.steps,
+                    "call": "lzg_profiles_upload_i8 + %s + lzg_profiles_free, pinned host buffers" % ("lzg_distance_matrix" if world == 1 else "lzg_distance_shard (every rank keeps its strips)")},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+            "roofline": {"bound": "int_alu", "kernel": "k_zcnt_distance", "achieved": achieved / 1e9, "peak": SAD4_PEAK_LANE_INSTR_PER_S / 1e9,
+                         "unit": "G lane-instr/s (VABSDIFF4.U8.ACC, 4 positions each) per GPU", "frac": achieved / SAD4_PEAK_LANE_INSTR_PER_S,
+                         "peak_kind": "measured (tools/microbench.cu on this pool, profiles/r01_microbench_int_pipes.jsonl)",
+                         "traffic": None,
+                         "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / world / (ms_step * 1e-3) / 1e9, "peak_gbs": peaks["hbm_gbs"],
+                                 "frac": hbm_bytes / world / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_kind": peaks_kind}},
+            "wall_s_timed_region": wall,
+        }
+    if world == 1 and not args.no_cpu:
+        n_sample = args.ref_cells or (160 if L <= 10000 else 110)
+        v, kind, dt, pairs = cpu_distance_sample(bp, min(n, n_sample))
+        line["cpu_baseline"] = {"value": v, "unit": "cell-pairs/s", "cores": 1, "kind": kind,
+                                "sample": "first %d cells of the same input (%d pairs, %.1f s)" % (min(n, n_sample), pairs, dt)}
+    gp.free()
+    del d_D
+    if world == 1 and not args.no_nni:
+        line["nni"] = nni_section(ctx, args, peaks, peaks_kind)
+    ctx.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
+    ap.add_argument("--ref-cells", type=int, default=0, help="cells in the CPU sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-nni", action="store_true", help="skip the NNI section")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
