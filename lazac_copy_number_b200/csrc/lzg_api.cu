@@ -1,5 +1,6 @@
 // lzg_api.cu -- the C ABI declared in include/lazac_b200.h.
 #include <algorithm>
+#include <climits>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -10,6 +11,7 @@
 int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
 int lzg_pack_rows_i8(lzg_ctx* ctx, const int8_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
 int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v);
+int lzg_bias_rows_i8(lzg_ctx* ctx, uint8_t* d, int n, int n_pad, int L, int l_pad);
 
 static thread_local std::string g_init_error;
 
@@ -72,6 +74,15 @@ int lzg_init(int device, lzg_ctx** out) {
     e = cudaGetDeviceProperties(&prop, device);
     if (e == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_group, cudaEventDisableTiming);
+    if (e == cudaSuccess) {
+        // keep freed blocks in the device's default pool (see lzg_dev_alloc)
+        cudaMemPool_t pool;
+        uint64_t keep = UINT64_MAX;
+        e = cudaDeviceGetDefaultMemPool(&pool, device);
+        if (e == cudaSuccess) e = cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
     if (e == cudaSuccess) e = cudaMalloc(&ctx->d_flag, sizeof(int));
@@ -96,6 +107,8 @@ int lzg_shutdown(lzg_ctx* ctx) {
     if (ctx->d_flag) cudaFree(ctx->d_flag);
     if (ctx->d_scratch) cudaFree(ctx->d_scratch);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->ev_group) cudaEventDestroy(ctx->ev_group);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
@@ -151,6 +164,8 @@ int lzg_host_free(lzg_ctx* ctx, void* p) {
 }
 
 // ---- profiles ----------------------------------------------------------------------------------
+// int8 input: rows are copied straight into the padded device layout (one pitched H2D copy) and
+// biased in place.  int32 input: staged through a bounded device buffer (<= 256 MiB) and packed.
 static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32_t n, int32_t L, lzg_profiles** out) {
     if (!ctx || !out || n < 0 || L < 0 || ((n > 0 && L > 0) && !host)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_profiles_upload: bad argument");
     *out = nullptr;
@@ -162,45 +177,51 @@ static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32
     p->L = L;
     p->n_pad = std::max(128, (n + 127) / 128 * 128);
     p->l_pad = std::max(128, (L + 127) / 128 * 128);
-    const size_t bytes = (size_t)p->n_pad * p->l_pad;
-    cudaError_t e = cudaMalloc(&p->d, bytes);
+    p->d_bytes = (size_t)p->n_pad * p->l_pad;
+    cudaError_t e = lzg_dev_alloc(ctx, (void**)&p->d, p->d_bytes);
     if (e != cudaSuccess) {
         delete p;
-        return lzg_fail(ctx, LZG_ERR_CUDA, "profiles cudaMalloc", e);
+        return lzg_fail(ctx, LZG_ERR_CUDA, "profiles allocation", e);
     }
-    int rc = lzg_fill_bytes(ctx, p->d + (size_t)n * p->l_pad, bytes - (size_t)n * p->l_pad, LZG_BIAS);
-    // stage the host matrix through a bounded device buffer (<= 256 MiB) and pack on the device
-    const size_t elt = is_i8 ? 1 : 4;
+    int rc = LZG_OK;
+    e = cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), ctx->stream);
+    if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "flag reset", e);
     void* d_stage = nullptr;
-    if (rc == LZG_OK && n > 0 && L > 0) {
-        size_t row_bytes = (size_t)L * elt;
-        int block_rows = (int)std::max<size_t>(1, std::min<size_t>(n, ((size_t)256 << 20) / row_bytes));
-        e = cudaMalloc(&d_stage, (size_t)block_rows * row_bytes);
-        if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "staging cudaMalloc", e);
-        e = cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), ctx->stream);
-        for (int r0 = 0; rc == LZG_OK && r0 < n; r0 += block_rows) {
-            int nr = std::min(block_rows, n - r0);
-            e = cudaMemcpyAsync(d_stage, (const uint8_t*)host + (size_t)r0 * row_bytes, (size_t)nr * row_bytes, cudaMemcpyHostToDevice, ctx->stream);
-            if (e != cudaSuccess) {
-                rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles H2D", e);
-                break;
-            }
-            rc = is_i8 ? lzg_pack_rows_i8(ctx, (const int8_t*)d_stage, p->d + (size_t)r0 * p->l_pad, nr, L, p->l_pad)
-                       : lzg_pack_rows_i32(ctx, (const int32_t*)d_stage, p->d + (size_t)r0 * p->l_pad, nr, L, p->l_pad);
-            if (rc == LZG_OK && r0 + block_rows < n) cudaStreamSynchronize(ctx->stream);  // staging buffer is reused
+    if (rc == LZG_OK && is_i8) {
+        if (n > 0 && L > 0) {
+            e = cudaMemcpy2DAsync(p->d, p->l_pad, host, L, L, n, cudaMemcpyHostToDevice, ctx->stream);
+            if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles H2D", e);
         }
-    } else if (rc == LZG_OK && n > 0) {
-        rc = lzg_fill_bytes(ctx, p->d, (size_t)n * p->l_pad, LZG_BIAS);
+        if (rc == LZG_OK) rc = lzg_bias_rows_i8(ctx, p->d, L > 0 ? n : 0, p->n_pad, L, p->l_pad);
+    } else if (rc == LZG_OK) {
+        rc = lzg_fill_bytes(ctx, p->d + (size_t)n * p->l_pad, p->d_bytes - (size_t)n * p->l_pad, LZG_BIAS);
+        if (rc == LZG_OK && n > 0 && L > 0) {
+            const size_t row_bytes = (size_t)L * 4;
+            int block_rows = (int)std::max<size_t>(1, std::min<size_t>(n, ((size_t)256 << 20) / row_bytes));
+            e = lzg_dev_alloc(ctx, &d_stage, (size_t)block_rows * row_bytes);
+            if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "staging allocation", e);
+            for (int r0 = 0; rc == LZG_OK && r0 < n; r0 += block_rows) {
+                int nr = std::min(block_rows, n - r0);
+                e = cudaMemcpyAsync(d_stage, (const uint8_t*)host + (size_t)r0 * row_bytes, (size_t)nr * row_bytes, cudaMemcpyHostToDevice, ctx->stream);
+                if (e != cudaSuccess) {
+                    rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles H2D", e);
+                    break;
+                }
+                rc = lzg_pack_rows_i32(ctx, (const int32_t*)d_stage, p->d + (size_t)r0 * p->l_pad, nr, L, p->l_pad);
+            }
+        } else if (rc == LZG_OK && n > 0) {
+            rc = lzg_fill_bytes(ctx, p->d, (size_t)n * p->l_pad, LZG_BIAS);
+        }
     }
     if (rc == LZG_OK) {
         e = cudaMemcpyAsync(ctx->h_pinned, ctx->d_flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // the host buffer is not retained past this call
         if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles pack", e);
         else if (n > 0 && L > 0 && ctx->h_pinned[0]) rc = lzg_fail(ctx, LZG_ERR_RANGE, "breakpoint value outside [-127, 127]");
     }
-    if (d_stage) cudaFree(d_stage);
+    lzg_dev_free(ctx, d_stage);
     if (rc != LZG_OK) {
-        cudaFree(p->d);
+        lzg_dev_free(ctx, p->d);
         delete p;
         return rc;
     }
@@ -218,12 +239,12 @@ int lzg_profiles_upload_i8(lzg_ctx* ctx, const int8_t* bp, int32_t n, int32_t L,
 
 int lzg_profiles_free(lzg_profiles* p) {
     if (!p) return LZG_ERR_ARG;
-    cudaSetDevice(p->ctx->device);
-    cudaStreamSynchronize(p->ctx->stream);
-    for (auto& tl : p->tile_lists)
-        if (tl.d_tiles) cudaFree(tl.d_tiles);
-    if (p->d_D) cudaFree(p->d_D);
-    cudaFree(p->d);
+    lzg_ctx* ctx = p->ctx;
+    cudaSetDevice(ctx->device);
+    // stream-ordered frees: no synchronisation, the blocks go back to the pool
+    for (auto& sc : p->schedules) lzg_dev_free(ctx, sc.d_block);
+    lzg_dev_free(ctx, p->d_D);
+    lzg_dev_free(ctx, p->d);
     delete p;
     return LZG_OK;
 }
@@ -239,7 +260,8 @@ int lzg_profiles_shape(const lzg_profiles* p, int32_t* n, int32_t* L) {
 int lzg_distance_shard_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard, int32_t n_shards, int32_t* d_D, int64_t* pairs_done) {
     if (!ctx || !p || p->ctx != ctx || n_shards < 1 || shard < 0 || shard >= n_shards || (p->n > 0 && !d_D))
         return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance: bad argument");
-    return lzg_distance_run(ctx, const_cast<lzg_profiles*>(p), shard, n_shards, d_D, pairs_done);
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    return lzg_distance_run(ctx, const_cast<lzg_profiles*>(p), shard, n_shards, 0, INT32_MAX, d_D, pairs_done);
 }
 
 int lzg_distance_matrix_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t* d_D) {
@@ -248,21 +270,47 @@ int lzg_distance_matrix_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_
 
 static int ensure_dD(lzg_ctx* ctx, lzg_profiles* p) {
     if (p->d_D || p->n == 0) return LZG_OK;
-    LZG_CUDA(ctx, cudaMalloc(&p->d_D, sizeof(int32_t) * (size_t)p->n * p->n));
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&p->d_D, sizeof(int32_t) * (size_t)p->n * p->n));
     return LZG_OK;
 }
 
+// Whole matrix to the host.  Large matrices are computed in groups of tile rows; rows of a group
+// are final once the group is done (mirrors of earlier groups are already in place), so their
+// device-to-host copy runs on the copy stream while the next group computes.
 int lzg_distance_matrix(lzg_ctx* ctx, const lzg_profiles* cp, int32_t* D) {
     if (!ctx || !cp || cp->ctx != ctx || (cp->n > 0 && !D)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance_matrix: bad argument");
     lzg_profiles* p = const_cast<lzg_profiles*>(cp);
     if (p->n == 0) return LZG_OK;
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = ensure_dD(ctx, p);
     if (rc != LZG_OK) return rc;
-    rc = lzg_distance_run(ctx, p, 0, 1, p->d_D, nullptr);
-    if (rc != LZG_OK) return rc;
-    LZG_CUDA(ctx, cudaMemcpyAsync(D, p->d_D, sizeof(int32_t) * (size_t)p->n * p->n, cudaMemcpyDeviceToHost, ctx->stream));
-    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return LZG_OK;
+    const int n = p->n, bm = lzg_distance_tile(p), R = (n + bm - 1) / bm;
+    const size_t bytes = sizeof(int32_t) * (size_t)n * n;
+    const int groups = bytes < ((size_t)64 << 20) ? 1 : std::min(16, R);
+    if (groups == 1) {
+        rc = lzg_distance_run(ctx, p, 0, 1, 0, INT32_MAX, p->d_D, nullptr);
+        if (rc != LZG_OK) return rc;
+        LZG_CUDA(ctx, cudaMemcpyAsync(D, p->d_D, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        return LZG_OK;
+    }
+    for (int g = 0; g < groups; g++) {
+        const int ra = (int)((int64_t)R * g / groups), rb = (int)((int64_t)R * (g + 1) / groups);
+        if (ra == rb) continue;
+        rc = lzg_distance_run(ctx, p, 0, 1, ra, rb, p->d_D, nullptr);
+        if (rc != LZG_OK) break;
+        const size_t r0 = (size_t)ra * bm, r1 = std::min<size_t>(n, (size_t)rb * bm);
+        cudaError_t e = cudaEventRecord(ctx->ev_group, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_group, 0);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(D + r0 * n, p->d_D + r0 * n, sizeof(int32_t) * (r1 - r0) * n, cudaMemcpyDeviceToHost, ctx->copy_stream);
+        if (e != cudaSuccess) {
+            rc = lzg_fail(ctx, LZG_ERR_CUDA, "row-group D2H", e);
+            break;
+        }
+    }
+    cudaError_t e1 = cudaStreamSynchronize(ctx->copy_stream), e2 = cudaStreamSynchronize(ctx->stream);
+    if (rc == LZG_OK && (e1 != cudaSuccess || e2 != cudaSuccess)) rc = lzg_fail(ctx, LZG_ERR_CUDA, "lzg_distance_matrix", e1 != cudaSuccess ? e1 : e2);
+    return rc;
 }
 
 int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* cp, int32_t shard, int32_t n_shards, int32_t* D, int64_t* pairs_done) {
@@ -271,17 +319,14 @@ int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* cp, int32_t shard, int3
     lzg_profiles* p = const_cast<lzg_profiles*>(cp);
     if (pairs_done) *pairs_done = 0;
     if (p->n == 0) return LZG_OK;
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = ensure_dD(ctx, p);
     if (rc != LZG_OK) return rc;
-    rc = lzg_distance_run(ctx, p, shard, n_shards, p->d_D, pairs_done);
+    rc = lzg_distance_run(ctx, p, shard, n_shards, 0, INT32_MAX, p->d_D, pairs_done);
     if (rc != LZG_OK) return rc;
     // copy back the strips this shard owns: for tile row r the row strip [r*bm, ..) x [r*bm, n) and
     // its mirror, the column strip [r*bm, n) x [r*bm, ..)
-    const lzg_tile_list* tl = nullptr;
-    for (auto& c : p->tile_lists)
-        if (c.shard == shard && c.n_shards == n_shards) tl = &c;  // the list lzg_distance_run just used (last match)
-    if (!tl) return lzg_fail(ctx, LZG_ERR_STATE, "tile list missing");
-    const int bm = tl->bm, n = p->n, R = (n + bm - 1) / bm;
+    const int bm = lzg_distance_tile(p), n = p->n, R = (n + bm - 1) / bm;
     const size_t pitch = sizeof(int32_t) * (size_t)n;
     for (int r = 0; r < R; r++) {
         if (std::min(r, R - 1 - r) % n_shards != shard) continue;

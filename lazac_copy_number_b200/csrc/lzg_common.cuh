@@ -24,13 +24,30 @@ struct lzg_ctx {
     size_t h_pinned_ints = 0;
     int32_t* d_scratch = nullptr;   // small device scratch (path arrays, results)
     size_t d_scratch_ints = 0;
+    cudaStream_t copy_stream = nullptr;  // D2H of finished row groups while later groups compute
+    cudaEvent_t ev_group = nullptr;
 };
 
-struct lzg_tile_list {
-    int bm = 0, shard = 0, n_shards = 0;
-    int n_tiles = 0;
+// Stream-ordered device allocation from the device's default memory pool, whose release threshold
+// lzg_init raises so that freed blocks stay cached: upload -> distance -> free cycles then cost no
+// cudaMalloc/cudaFree.  Everything is ordered on ctx->stream.
+inline cudaError_t lzg_dev_alloc(lzg_ctx* ctx, void** out, size_t bytes) {
+    return cudaMallocAsync(out, bytes ? bytes : 1, ctx->stream);
+}
+inline void lzg_dev_free(lzg_ctx* ctx, void* p) {
+    if (p) cudaFreeAsync(p, ctx->stream);
+}
+
+// Persistent-grid work schedule of the distance kernel for one (tile size, shard) (lzg_distance.cu).
+struct lzg_schedule {
+    int bm = 0, shard = 0, n_shards = 0, row_lo = 0, row_hi = 0;
+    int n_ctas = 0, n_segs = 0, n_split = 0;
     int64_t pairs = 0;
-    int2* d_tiles = nullptr;
+    void* d_block = nullptr;        // one pooled allocation holding the three arrays below
+    size_t bytes = 0;
+    void* d_segs = nullptr;         // lzg_seg[n_segs]
+    int32_t* d_seg_off = nullptr;   // [n_ctas + 1]
+    int2* d_split = nullptr;        // tiles accumulated with atomics (zeroed first)
 };
 
 struct lzg_profiles {
@@ -38,8 +55,9 @@ struct lzg_profiles {
     int32_t n = 0, L = 0;
     int32_t n_pad = 0, l_pad = 0;  // rows padded to 128, positions padded to 128 (pad byte = LZG_BIAS)
     uint8_t* d = nullptr;          // [n_pad][l_pad]
+    size_t d_bytes = 0;
     int32_t* d_D = nullptr;        // lazily allocated N x N result used by the host-output entry points
-    std::vector<lzg_tile_list> tile_lists;
+    std::vector<lzg_schedule> schedules;
 };
 
 int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuccess);
@@ -58,7 +76,9 @@ int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuc
     } while (0)
 
 // distance module (lzg_distance.cu)
-int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int32_t* d_D,
-                     int64_t* pairs_done);
+int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int row_lo, int row_hi,
+                     int32_t* d_D, int64_t* pairs_done);
+// tile edge of the pair kernel for this input: one 64 x 64 tile when n <= 64, else 128 x 128
+inline int lzg_distance_tile(const lzg_profiles* p) { return p->n <= 64 ? 64 : 128; }
 // pinned / scratch helpers (lzg_api.cu)
 int lzg_ensure_scratch(lzg_ctx* ctx, size_t ints);

@@ -12,6 +12,10 @@
 // cp.async (LDGSTS) ring of XOR-swizzled shared-memory tiles read with conflict-free LDS.128.
 // Only tiles on or above the diagonal are computed; the epilogue transposes through shared memory
 // so that both D[i][j] and D[j][i] are written with coalesced stores.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
 #include "lzg_common.cuh"
 
 namespace {
@@ -75,116 +79,214 @@ __global__ void k_fill_bytes(uint8_t* dst, size_t n, uint8_t v) {
         dst[i] = v;
 }
 
-// One CTA = one BM x BN tile of cell pairs (rows of tile-row bi against rows of tile-row bj),
-// over k-iterations [k_begin, k_end) of KC positions each (split-K when the tile count is small).
-template <int BM, int BN, int STAGES, bool ATOMIC>
-__global__ void __launch_bounds__((BM / 8) * (BN / 8))
-k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const int2* __restrict__ tiles,
-                int k_iters_total, int k_splits, int32_t* __restrict__ D) {
+// In-place finish of an int8 upload: rows were copied raw (two's complement) into the padded
+// [n_pad][l_pad] layout; v + 128 == v ^ 0x80 for a byte, padding columns and rows become 128.
+// -128 (0x80) is out of range (keeps |a - b| <= 254).
+__global__ void k_bias_rows_i8(uint8_t* __restrict__ d, int n, int L, int l_pad, int* flag) {
+    const int r = blockIdx.y;
+    uint4* row = reinterpret_cast<uint4*>(d + (size_t)r * l_pad);
+    int bad = 0;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < l_pad / 16; w += gridDim.x * blockDim.x) {
+        uint4 v = make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
+        const int k0 = w * 16;
+        if (r < n && k0 < L) {
+            uint4 x = row[w];
+            uint32_t in[4] = {x.x, x.y, x.z, x.w}, out[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                uint32_t word = in[q], o = 0x80808080u;
+                if (k0 + 4 * q + 4 <= L) {
+                    bad |= __vcmpeq4(word, 0x80808080u) != 0;
+                    o = word ^ 0x80808080u;
+                } else {
+#pragma unroll
+                    for (int b = 0; b < 4; b++) {
+                        if (k0 + 4 * q + b < L) {
+                            uint32_t byte = (word >> (8 * b)) & 0xffu;
+                            bad |= byte == 0x80u;
+                            o = (o & ~(0xffu << (8 * b))) | ((byte ^ 0x80u) << (8 * b));
+                        }
+                    }
+                }
+                out[q] = o;
+            }
+            v = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+        row[w] = v;
+    }
+    if (bad) atomicOr(flag, 1);
+}
+
+// ---- the pair kernel ---------------------------------------------------------------------------
+// Work is described by SEGMENTS built on the host (build_schedule below): a segment is one
+// BM x BN tile of cell pairs (rows of tile-row r against rows of tile-row c, c >= r) over the
+// k-iterations [k0, k1) of KC positions each.  The grid is persistent -- one CTA per resident
+// slot (2 per SM for 128 x 128 tiles) -- and CTA b executes segments seg_off[b] .. seg_off[b+1].
+// The host cuts the (tile, k) iteration space into equal-cost contiguous ranges (stream-K), so
+// every SM finishes together whatever the number of tiles; a tile cut across CTAs is
+// accumulated with integer atomics (exact, order-free) into cells zeroed by k_zero_tiles.
+//
+// Diagonal tiles (r == c) skip their lower-left quadrant: thread (ty, tx) owns rows ty + TY*i and
+// columns tx + TX*j, so "row >= BM/2 and column < BN/2" is i >= 4 && j < 4 for every thread
+// alike -- a quarter of the SADs of those tiles, with no divergence; the quadrant is filled
+// from the mirror of the upper-right one.
+struct lzg_seg {
+    int32_t r, c, k0, k1;  // k1 < 0: accumulate with atomics into pre-zeroed cells, k-range [k0, -k1)
+};
+
+// One k-iteration (KC positions) of a thread's 8 x 8 pairs.  DIAG skips the lower-left quadrant.
+// (Measured on B200: reordering the SADs, streaming the row operands, or 8-byte operands with
+// two CTAs per SM are all within +-2 % or slower -- the loop is VABSDIFF4-issue bound.)
+template <int BM, int BN, bool DIAG>
+__device__ __forceinline__ void tile_step(uint32_t (&acc)[8][8], const uint8_t* sA, const uint8_t* sB, int tx, int ty) {
+    constexpr int TX = BN / 8, TY = BM / 8;
+    const int swa = ty & 7, swb = tx & 7;  // (row & 7) of every row this thread reads
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        uint4 a[8], b[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            a[i] = *reinterpret_cast<const uint4*>(sA + (ty + TY * i) * KC + ((c ^ swa) << 4));
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            b[j] = *reinterpret_cast<const uint4*>(sB + (tx + TX * j) * KC + ((c ^ swb) << 4));
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                if (DIAG && i >= 4 && j < 4) continue;  // lower-left quadrant: taken from the mirror
+                acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]);
+                acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
+                acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]);
+                acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
+            }
+    }
+}
+
+template <int BM, int BN, int STAGES>
+__global__ void __launch_bounds__((BM / 8) * (BN / 8), 1)
+k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_seg* __restrict__ segs,
+                const int32_t* __restrict__ seg_off, int32_t* __restrict__ D) {
     constexpr int TX = BN / 8, TY = BM / 8, T = TX * TY;
     constexpr int A_BYTES = BM * KC, B_BYTES = BN * KC, STAGE_BYTES = A_BYTES + B_BYTES;
     extern __shared__ __align__(128) uint8_t smem[];
 
     const int tid = threadIdx.x;
     const int tx = tid % TX, ty = tid / TX;
-    const int2 tile = tiles[blockIdx.x];
-    const int row0 = tile.x * BM, col0 = tile.y * BN;
-    const int per = (k_iters_total + k_splits - 1) / k_splits;
-    const int k_begin = blockIdx.y * per;
-    const int k_end = min(k_iters_total, k_begin + per);
-    const int n_it = k_end - k_begin;
-    if (n_it <= 0) return;
+    const int s_begin = seg_off[blockIdx.x], s_end = seg_off[blockIdx.x + 1];
 
-    const uint8_t* gA = prof + (size_t)row0 * l_pad + (size_t)k_begin * KC;
-    const uint8_t* gB = prof + (size_t)col0 * l_pad + (size_t)k_begin * KC;
+    for (int s = s_begin; s < s_end; s++) {
+        const lzg_seg sg = segs[s];
+        const bool atomic = sg.k1 < 0;
+        const int k_begin = sg.k0, n_it = (atomic ? -sg.k1 : sg.k1) - sg.k0;
+        const bool diag = sg.r == sg.c;
+        const int row0 = sg.r * BM, col0 = sg.c * BN;
+        const uint8_t* gA = prof + (size_t)row0 * l_pad + (size_t)k_begin * KC;
+        const uint8_t* gB = prof + (size_t)col0 * l_pad + (size_t)k_begin * KC;
 
-    auto load_stage = [&](int it, int slot) {
-        uint8_t* sA = smem + slot * STAGE_BYTES;
-        uint8_t* sB = sA + A_BYTES;
-        const uint8_t* a = gA + (size_t)it * KC;
-        const uint8_t* b = gB + (size_t)it * KC;
+        auto load_stage = [&](int it, int slot) {
+            uint8_t* sA = smem + slot * STAGE_BYTES;
+            uint8_t* sB = sA + A_BYTES;
+            const uint8_t* a = gA + (size_t)it * KC;
+            const uint8_t* b = gB + (size_t)it * KC;
 #pragma unroll
-        for (int q = tid; q < BM * 8; q += T) {
-            int r = q >> 3, c = q & 7;
-            cp_async16(sA + r * KC + ((c ^ (r & 7)) << 4), a + (size_t)r * l_pad + (c << 4));
-        }
+            for (int q = tid; q < BM * 8; q += T) {
+                int r = q >> 3, c = q & 7;
+                cp_async16(sA + r * KC + ((c ^ (r & 7)) << 4), a + (size_t)r * l_pad + (c << 4));
+            }
 #pragma unroll
-        for (int q = tid; q < BN * 8; q += T) {
-            int r = q >> 3, c = q & 7;
-            cp_async16(sB + r * KC + ((c ^ (r & 7)) << 4), b + (size_t)r * l_pad + (c << 4));
-        }
-    };
+            for (int q = tid; q < BN * 8; q += T) {
+                int r = q >> 3, c = q & 7;
+                cp_async16(sB + r * KC + ((c ^ (r & 7)) << 4), b + (size_t)r * l_pad + (c << 4));
+            }
+        };
 
-    uint32_t acc[8][8];
+        uint32_t acc[8][8];
 #pragma unroll
-    for (int i = 0; i < 8; i++)
+        for (int i = 0; i < 8; i++)
 #pragma unroll
-        for (int j = 0; j < 8; j++) acc[i][j] = 0;
+            for (int j = 0; j < 8; j++) acc[i][j] = 0;
 
 #pragma unroll
-    for (int s = 0; s < STAGES - 1; s++) {
-        if (s < n_it) load_stage(s, s);
-        cp_async_commit();
-    }
-
-    const int swa = ty & 7, swb = tx & 7;  // (row & 7) of every row this thread reads
-    for (int it = 0; it < n_it; it++) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        {
-            int nx = it + STAGES - 1;
-            if (nx < n_it) load_stage(nx, nx % STAGES);
+        for (int st = 0; st < STAGES - 1; st++) {
+            if (st < n_it) load_stage(st, st);
             cp_async_commit();
         }
-        const uint8_t* sA = smem + (it % STAGES) * STAGE_BYTES;
-        const uint8_t* sB = sA + A_BYTES;
-#pragma unroll
-        for (int c = 0; c < 8; c++) {
-            uint4 a[8], b[8];
-#pragma unroll
-            for (int i = 0; i < 8; i++)
-                a[i] = *reinterpret_cast<const uint4*>(sA + (ty + TY * i) * KC + ((c ^ swa) << 4));
-#pragma unroll
-            for (int j = 0; j < 8; j++)
-                b[j] = *reinterpret_cast<const uint4*>(sB + (tx + TX * j) * KC + ((c ^ swb) << 4));
-#pragma unroll
-            for (int i = 0; i < 8; i++)
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]);
-                    acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
-                    acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]);
-                    acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
-                }
-        }
-    }
-    cp_async_wait<0>();
-    __syncthreads();
 
-    // Epilogue: stage the tile in shared memory, then coalesced stores of the tile and its mirror.
-    int32_t* tbuf = reinterpret_cast<int32_t*>(smem);
-    constexpr int LD = BN + 1;
+        for (int it = 0; it < n_it; it++) {
+            cp_async_wait<STAGES - 2>();
+            __syncthreads();
+            {
+                int nx = it + STAGES - 1;
+                if (nx < n_it) load_stage(nx, nx % STAGES);
+                cp_async_commit();
+            }
+            const uint8_t* sA = smem + (it % STAGES) * STAGE_BYTES;
+            const uint8_t* sB = sA + A_BYTES;
+            if (!diag) tile_step<BM, BN, false>(acc, sA, sB, tx, ty);
+            else tile_step<BM, BN, true>(acc, sA, sB, tx, ty);
+        }
+        cp_async_wait<0>();
+        __syncthreads();
+
+        // Epilogue: stage the tile in shared memory, then coalesced stores of the tile and its mirror.
+        int32_t* tbuf = reinterpret_cast<int32_t*>(smem);
+        constexpr int LD = BN + 1;
 #pragma unroll
-    for (int i = 0; i < 8; i++)
+        for (int i = 0; i < 8; i++)
 #pragma unroll
-        for (int j = 0; j < 8; j++) tbuf[(ty + TY * i) * LD + tx + TX * j] = (int32_t)acc[i][j];
-    __syncthreads();
-    for (int q = tid; q < BM * BN; q += T) {
+            for (int j = 0; j < 8; j++) tbuf[(ty + TY * i) * LD + tx + TX * j] = (int32_t)acc[i][j];
+        __syncthreads();
+        {
+            // tile: thread owns column tid % BN, rows (tid / BN) + k * (T / BN); pointers advance by rows
+            constexpr int RS = T / BN;
+            const int c = tid % BN, rmax = min(BM, n - row0);
+            const bool col_ok = col0 + c < n;
+            const int32_t* src = tbuf + (tid / BN) * LD + c;
+            int32_t* dst = D + (size_t)(row0 + tid / BN) * n + col0 + c;
+            const int r_skip = (diag && c < BN / 2) ? BM / 2 : BM;  // lower-left quadrant of a diagonal tile
+            const int r_end = col_ok ? min(rmax, r_skip) : 0;
+            if (atomic) {
+#pragma unroll 4
+                for (int r = tid / BN; r < r_end; r += RS, src += RS * LD, dst += (size_t)RS * n) atomicAdd(dst, *src);
+            } else {
+#pragma unroll 4
+                for (int r = tid / BN; r < r_end; r += RS, src += RS * LD, dst += (size_t)RS * n) *dst = *src;
+            }
+        }
+        {
+            // mirror: thread owns tile row tid % BM (a column of D), tile columns (tid / BM) + k * (T / BM)
+            constexpr int CS = T / BM;
+            const int r = tid % BM, cmax = min(BN, n - col0);
+            const bool row_ok = row0 + r < n && !(diag && r >= BM / 2);
+            int c = tid / BM;
+            if (diag) c += BN / 2;  // only the upper-right quadrant of a diagonal tile is mirrored
+            const int32_t* src = tbuf + r * LD + c;
+            int32_t* dst = D + (size_t)(col0 + c) * n + row0 + r;
+            const int c_end = row_ok ? cmax : 0;
+            if (atomic) {
+#pragma unroll 4
+                for (; c < c_end; c += CS, src += CS, dst += (size_t)CS * n) atomicAdd(dst, *src);
+            } else {
+#pragma unroll 4
+                for (; c < c_end; c += CS, src += CS, dst += (size_t)CS * n) *dst = *src;
+            }
+        }
+        __syncthreads();  // tbuf aliases the pipeline buffers of the next segment
+    }
+}
+
+// Zeroes the cells (tile and mirror) of the tiles that are accumulated with atomics.
+template <int BM, int BN>
+__global__ void k_zero_tiles(const int2* __restrict__ tiles, int n, int32_t* __restrict__ D) {
+    const int2 t = tiles[blockIdx.x];
+    const int row0 = t.x * BM, col0 = t.y * BN;
+    for (int q = blockIdx.y * blockDim.x + threadIdx.x; q < BM * BN; q += gridDim.y * blockDim.x) {
         int r = q / BN, c = q % BN;
         int gi = row0 + r, gj = col0 + c;
         if (gi < n && gj < n) {
-            if (ATOMIC) atomicAdd(D + (size_t)gi * n + gj, tbuf[r * LD + c]);
-            else D[(size_t)gi * n + gj] = tbuf[r * LD + c];
-        }
-    }
-    if (tile.x != tile.y) {
-        for (int q = tid; q < BM * BN; q += T) {
-            int c = q / BM, r = q % BM;
-            int gi = row0 + r, gj = col0 + c;
-            if (gi < n && gj < n) {
-                if (ATOMIC) atomicAdd(D + (size_t)gj * n + gi, tbuf[r * LD + c]);
-                else D[(size_t)gj * n + gi] = tbuf[r * LD + c];
-            }
+            D[(size_t)gi * n + gj] = 0;
+            D[(size_t)gj * n + gi] = 0;
         }
     }
 }
@@ -196,57 +298,100 @@ constexpr int dist_smem_bytes() {
     return pipe > epi ? pipe : epi;
 }
 
-// Tile rows are dealt to shards in pairs (r, R-1-r): every pair has R+1 tiles.
-const lzg_tile_list* get_tiles(lzg_ctx* ctx, lzg_profiles* p, int bm, int shard, int n_shards, int* status) {
-    for (auto& tl : p->tile_lists)
-        if (tl.bm == bm && tl.shard == shard && tl.n_shards == n_shards) return &tl;
+// Cuts the shard's (tile, k-iteration) space into n_ctas contiguous ranges of equal cost.
+// Tile rows are dealt to shards in pairs (r, R-1-r): every pair has R+1 tiles, so every shard
+// gets the same triangle area.  Cost of one k-iteration: 4 units, 3 for a diagonal tile.
+const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slots_per_sm, int shard, int n_shards,
+                                 int row_lo, int row_hi, int* status) {
+    for (auto& sc : p->schedules)
+        if (sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
     const int R = (p->n + bm - 1) / bm;
+    const int K = p->l_pad / KC;
     std::vector<int2> tiles;
-    int64_t pairs = 0;
+    int64_t pairs = 0, units = 0;
     auto rows_in = [&](int r) { return (int64_t)(std::min(p->n, (r + 1) * bm) - r * bm); };
     for (int r = 0; r < R; r++) {
         int pr = std::min(r, R - 1 - r);
-        if (pr % n_shards != shard) continue;
+        if (pr % n_shards != shard || r < row_lo || r >= row_hi) continue;
         for (int c = r; c < R; c++) {
             tiles.push_back(make_int2(r, c));
             pairs += (c == r) ? rows_in(r) * (rows_in(r) + 1) / 2 : rows_in(r) * rows_in(c);
+            units += (int64_t)K * (c == r ? 3 : 4);
         }
     }
-    lzg_tile_list tl;
-    tl.bm = bm;
-    tl.shard = shard;
-    tl.n_shards = n_shards;
-    tl.n_tiles = (int)tiles.size();
-    tl.pairs = pairs;
-    if (tl.n_tiles > 0) {
-        cudaError_t e = cudaMalloc(&tl.d_tiles, sizeof(int2) * tiles.size());
-        if (e == cudaSuccess)
-            e = cudaMemcpyAsync(tl.d_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    lzg_schedule sc;
+    sc.bm = bm;
+    sc.shard = shard;
+    sc.n_shards = n_shards;
+    sc.row_lo = row_lo;
+    sc.row_hi = row_hi;
+    sc.pairs = pairs;
+    const int64_t iters = (int64_t)tiles.size() * K;
+    const int G = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * slots_per_sm, iters));
+    std::vector<lzg_seg> segs;
+    std::vector<int32_t> seg_off(G + 1, 0);
+    std::vector<int2> split;
+    int cur = 0;
+    int64_t cum = 0;
+    auto boundary = [&](int b) { return units * (int64_t)(b + 1) / G; };
+    for (const int2& t : tiles) {
+        const int u = t.x == t.y ? 3 : 4;
+        const size_t first = segs.size();
+        int k = 0;
+        while (k < K) {
+            int64_t rem = boundary(cur) - cum;
+            int it = (int)std::min<int64_t>(K - k, std::max<int64_t>(1, (rem + u - 1) / u));
+            segs.push_back(lzg_seg{t.x, t.y, k, k + it});
+            cum += (int64_t)it * u;
+            k += it;
+            while (cur < G - 1 && cum >= boundary(cur)) seg_off[++cur] = (int32_t)segs.size();
+        }
+        if (segs.size() - first > 1) {
+            for (size_t q = first; q < segs.size(); q++) segs[q].k1 = -segs[q].k1;
+            split.push_back(t);
+        }
+    }
+    while (cur < G) seg_off[++cur] = (int32_t)segs.size();
+    sc.n_ctas = G;
+    sc.n_segs = (int)segs.size();
+    sc.n_split = (int)split.size();
+    if (sc.n_segs > 0) {
+        // one pooled device block: [segs | seg_off | split tiles], one copy
+        const size_t b_segs = sizeof(lzg_seg) * segs.size(), b_off = sizeof(int32_t) * seg_off.size();
+        const size_t o_off = b_segs, o_split = (o_off + b_off + 15) / 16 * 16;
+        sc.bytes = o_split + sizeof(int2) * split.size();
+        std::vector<uint8_t> blob(sc.bytes);
+        memcpy(blob.data(), segs.data(), b_segs);
+        memcpy(blob.data() + o_off, seg_off.data(), b_off);
+        if (!split.empty()) memcpy(blob.data() + o_split, split.data(), sizeof(int2) * split.size());
+        cudaError_t e = lzg_dev_alloc(ctx, &sc.d_block, sc.bytes);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(sc.d_block, blob.data(), sc.bytes, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // the source is a pageable host vector
         if (e != cudaSuccess) {
-            *status = lzg_fail(ctx, LZG_ERR_CUDA, "tile list upload", e);
+            lzg_dev_free(ctx, sc.d_block);
+            *status = lzg_fail(ctx, LZG_ERR_CUDA, "distance schedule upload", e);
             return nullptr;
         }
+        sc.d_segs = sc.d_block;
+        sc.d_seg_off = reinterpret_cast<int32_t*>((uint8_t*)sc.d_block + o_off);
+        sc.d_split = reinterpret_cast<int2*>((uint8_t*)sc.d_block + o_split);
     }
-    p->tile_lists.push_back(tl);
-    return &p->tile_lists.back();
+    p->schedules.push_back(sc);
+    return &p->schedules.back();
 }
 
 template <int BM, int BN, int STAGES>
-int launch_distance(lzg_ctx* ctx, const lzg_profiles* p, const lzg_tile_list* tl, int k_splits, int32_t* d_D) {
+int launch_distance(lzg_ctx* ctx, const lzg_profiles* p, const lzg_schedule* sc, int32_t* d_D) {
     constexpr int smem = dist_smem_bytes<BM, BN, STAGES>();
     constexpr int T = (BM / 8) * (BN / 8);
-    const int k_iters = p->l_pad / KC;
-    dim3 grid(tl->n_tiles, k_splits);
-    if (k_splits > 1) {
-        auto kern = k_zcnt_distance<BM, BN, STAGES, true>;
-        LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        kern<<<grid, T, smem, ctx->stream>>>(p->d, p->l_pad, p->n, tl->d_tiles, k_iters, k_splits, d_D);
-    } else {
-        auto kern = k_zcnt_distance<BM, BN, STAGES, false>;
-        LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        kern<<<grid, T, smem, ctx->stream>>>(p->d, p->l_pad, p->n, tl->d_tiles, k_iters, k_splits, d_D);
+    if (sc->n_split > 0) {
+        k_zero_tiles<BM, BN><<<dim3(sc->n_split, 16), 256, 0, ctx->stream>>>(sc->d_split, p->n, d_D);
+        LZG_LAUNCH_CHECK(ctx);
     }
+    auto kern = k_zcnt_distance<BM, BN, STAGES>;
+    LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    kern<<<sc->n_ctas, T, smem, ctx->stream>>>(p->d, p->l_pad, p->n, (const lzg_seg*)sc->d_segs, sc->d_seg_off, d_D);
     LZG_LAUNCH_CHECK(ctx);
     return LZG_OK;
 }
@@ -267,6 +412,13 @@ int lzg_pack_rows_i8(lzg_ctx* ctx, const int8_t* d_src, uint8_t* d_dst, int rows
     return LZG_OK;
 }
 
+int lzg_bias_rows_i8(lzg_ctx* ctx, uint8_t* d, int n, int n_pad, int L, int l_pad) {
+    dim3 grid(std::max(1, std::min(16, (l_pad / 16 + 255) / 256)), n_pad);
+    k_bias_rows_i8<<<grid, 256, 0, ctx->stream>>>(d, n, L, l_pad, ctx->d_flag);
+    LZG_LAUNCH_CHECK(ctx);
+    return LZG_OK;
+}
+
 int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v) {
     if (n == 0) return LZG_OK;
     int blocks = (int)std::min<size_t>(4096, (n + 255) / 256);
@@ -275,34 +427,19 @@ int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v) {
     return LZG_OK;
 }
 
-// Computes the shard's tiles into the full N x N device matrix d_D (asynchronous).
-int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int32_t* d_D, int64_t* pairs_done) {
-    if (p->n == 0) {
-        if (pairs_done) *pairs_done = 0;
-        return LZG_OK;
-    }
-    const int R128 = (p->n + 127) / 128;
-    const int64_t tiles128 = (int64_t)R128 * (R128 + 1) / 2 / n_shards;
+// Computes the shard's tiles of tile rows [row_lo, row_hi) into the full N x N device matrix d_D
+// (asynchronous on ctx->stream).
+int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int row_lo, int row_hi, int32_t* d_D,
+                     int64_t* pairs_done) {
+    if (pairs_done) *pairs_done = 0;
+    if (p->n == 0) return LZG_OK;
     int status = LZG_OK;
-    if (tiles128 >= 2 * (int64_t)ctx->sm_count) {
-        const lzg_tile_list* tl = get_tiles(ctx, p, 128, shard, n_shards, &status);
-        if (!tl) return status;
-        if (pairs_done) *pairs_done = tl->pairs;
-        if (tl->n_tiles == 0) return LZG_OK;
-        return launch_distance<128, 128, 3>(ctx, p, tl, 1, d_D);
-    }
-    // Few cells: 64 x 64 tiles and split the position axis so that every SM gets several CTAs.
-    const lzg_tile_list* tl = get_tiles(ctx, p, 64, shard, n_shards, &status);
-    if (!tl) return status;
-    if (pairs_done) *pairs_done = tl->pairs;
-    if (tl->n_tiles == 0) return LZG_OK;
-    const int k_iters = p->l_pad / KC;
-    int want = (ctx->sm_count * 4 + tl->n_tiles - 1) / tl->n_tiles;
-    int k_splits = std::max(1, std::min(want, k_iters / 4 > 0 ? k_iters / 4 : 1));
-    if (k_splits > 1) {
-        // the split-K partial sums are accumulated with integer atomics: clear the shard's cells first
-        // (whole matrix for the single-shard case; per-tile clearing is not worth a kernel here)
-        LZG_CUDA(ctx, cudaMemsetAsync(d_D, 0, sizeof(int32_t) * (size_t)p->n * p->n, ctx->stream));
-    }
-    return launch_distance<64, 64, 4>(ctx, p, tl, k_splits, d_D);
+    const int bm = lzg_distance_tile(p);
+    // one persistent CTA per SM: 8 warps x 254 registers fill the register file (3 CTAs of 2 warps for
+    // the single-tile 64 x 64 case)
+    const lzg_schedule* sc = get_schedule(ctx, p, bm, bm == 64 ? 3 : 1, shard, n_shards, row_lo, row_hi, &status);
+    if (!sc) return status;
+    if (pairs_done) *pairs_done = sc->pairs;
+    if (sc->n_segs == 0) return LZG_OK;
+    return bm == 64 ? launch_distance<64, 64, 4>(ctx, p, sc, d_D) : launch_distance<128, 128, 3>(ctx, p, sc, d_D);
 }

@@ -77,3 +77,34 @@ def test_shards_union_is_full_matrix(ctx, port, n_shards):
     prof.free()
     assert pairs == n * (n + 1) // 2
     assert np.array_equal(D, port.distance_matrix(bp))
+
+
+def test_row_group_overlap_path(ctx):
+    """>= 64 MiB of output: computed in tile-row groups with the D2H of finished rows overlapped."""
+    n, L = 4200, 200
+    bp = synth.random_bp(n, L, seed=13, density=0.3)
+    prof = Profiles(ctx, bp.astype(np.int8))
+    D = ctx.pinned((n, n), np.int32)
+    D[...] = -1
+    prof.distance_matrix(D)
+    prof.free()
+    assert np.array_equal(D, D.T) and not D.diagonal().any()
+    for i in (0, 1, 127, 128, 2047, 2100, 4095, 4096, 4199):
+        assert np.array_equal(D[i], np.abs(bp - bp[i]).sum(1))
+
+
+def test_repeated_upload_free_cycles(ctx, port):
+    """The pooled allocations are reused across upload/distance/free cycles of different shapes."""
+    for k, (n, L) in enumerate([(300, 1000), (50, 77), (300, 1000), (129, 4097), (300, 1000)]):
+        bp = synth.random_bp(n, L, seed=20 + k, density=0.2)
+        prof = Profiles(ctx, bp.astype(np.int8) if k % 2 else bp)
+        assert np.array_equal(prof.distance_matrix(), port.distance_matrix(bp))
+        prof.free()
+
+
+def test_int8_minus_128_is_out_of_range(ctx):
+    bp = np.zeros((3, 40), np.int8)
+    bp[1, 39] = -128
+    with pytest.raises(LazacGpuError) as e:
+        Profiles(ctx, bp)
+    assert e.value.status == 3
