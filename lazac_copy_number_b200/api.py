@@ -247,3 +247,9 @@ class Tree:
         m, b = C.c_int64(0), C.c_int64(0)
         self.ctx.check(self.ctx.lib.lzg_tree_last_nni_work(self.h, C.byref(m), C.byref(b)))
         return m.value, b.value
+
+    def last_nni_traffic(self):
+        """(candidate bytes, UP-pass bytes) of the last nni_best as executed on the GPU."""
+        c, u = C.c_int64(0), C.c_int64(0)
+        self.ctx.check(self.ctx.lib.lzg_tree_last_nni_traffic(self.h, C.byref(c), C.byref(u)))
+        return c.value, u.value

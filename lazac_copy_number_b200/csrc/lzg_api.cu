@@ -38,6 +38,18 @@ int lzg_ensure_scratch(lzg_ctx* ctx, size_t ints) {
     return LZG_OK;
 }
 
+int lzg_ensure_pinned(lzg_ctx* ctx, size_t ints) {
+    if (ints <= ctx->h_pinned_ints) return LZG_OK;
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    ctx->h_pinned = nullptr;
+    ctx->h_pinned_ints = 0;
+    size_t want = std::max<size_t>(ints * 2, 1 << 16);
+    LZG_CUDA(ctx, cudaHostAlloc(&ctx->h_pinned, sizeof(int32_t) * want, cudaHostAllocDefault));
+    ctx->h_pinned_ints = want;
+    return LZG_OK;
+}
+
 extern "C" {
 
 const char* lzg_version(void) { return "lazac_b200 0.1 (sm_100a)"; }

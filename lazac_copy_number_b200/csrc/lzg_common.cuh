@@ -82,3 +82,4 @@ int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int
 inline int lzg_distance_tile(const lzg_profiles* p) { return p->n <= 64 ? 64 : 128; }
 // pinned / scratch helpers (lzg_api.cu)
 int lzg_ensure_scratch(lzg_ctx* ctx, size_t ints);
+int lzg_ensure_pinned(lzg_ctx* ctx, size_t ints);  // synchronises the stream when it has to grow

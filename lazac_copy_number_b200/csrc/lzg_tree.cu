@@ -212,6 +212,53 @@ int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t) {
     LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     t->root_score = ctx->h_pinned[0];
     t->scored = true;
+    t->up_valid = false;
+    return LZG_OK;
+}
+
+// UP intervals for every internal non-root node: one dependency-driven launch (see k_up_chain).
+int lzg_tree_up_pass(lzg_ctx* ctx, lzg_tree* t) {
+    const int n = t->n_nodes;
+    const size_t nb = (size_t)n * t->l_pad;
+    int groups, threads = chunk_threads(t->l_pad, &groups);
+    if (!t->d_ustart) {
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ustart, nb));
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_uend, nb));
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_upscore, sizeof(int32_t) * n));
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_upcost, sizeof(int32_t) * n));
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ready, sizeof(int) * ((size_t)n * groups + 1)));
+        LZG_CUDA(ctx, cudaMemsetAsync(t->d_ready, 0, sizeof(int) * ((size_t)n * groups + 1), ctx->stream));
+        t->epoch = 0;
+    }
+    // parents-first order of the internal non-root nodes, staged in pinned memory (no sync needed:
+    // every public entry point ends with a synchronising read-back before the staging area is reused)
+    int rc = lzg_ensure_pinned(ctx, (size_t)n + 64);
+    if (rc != LZG_OK) return rc;
+    int32_t* order = ctx->h_pinned + 64;
+    int cnt = 0;
+    if (t->child0[0] >= 0) {
+        for (int c : {t->child0[0], t->child1[0]})
+            if (t->child0[c] >= 0) order[cnt++] = c;
+        for (int i = 0; i < cnt; i++) {
+            const int a = order[i];
+            for (int c : {t->child0[a], t->child1[a]})
+                if (t->child0[c] >= 0) order[cnt++] = c;
+        }
+    }
+    t->up_nodes = cnt;
+    if (cnt > 0) {
+        t->epoch++;
+        int* ticket = t->d_ready + (size_t)n * groups;
+        LZG_CUDA(ctx, cudaMemcpyAsync(t->d_order, order, sizeof(int32_t) * cnt, cudaMemcpyHostToDevice, ctx->stream));
+        LZG_CUDA(ctx, cudaMemsetAsync(t->d_upcost, 0, sizeof(int32_t) * n, ctx->stream));
+        LZG_CUDA(ctx, cudaMemsetAsync(ticket, 0, sizeof(int), ctx->stream));
+        k_up_chain<<<cnt * groups, threads, 0, ctx->stream>>>(t->d_order, groups, t->d_up, t->d_start, t->d_end, t->d_ustart, t->d_uend,
+                                                              t->d_upcost, t->d_ready, t->epoch, ticket, t->l_pad);
+        LZG_LAUNCH_CHECK(ctx);
+        k_up_scores<<<(cnt + 255) / 256, 256, 0, ctx->stream>>>(t->d_order, cnt, t->d_up, t->d_upcost, t->d_score, t->d_upscore);
+        LZG_LAUNCH_CHECK(ctx);
+    }
+    t->up_valid = true;
     return LZG_OK;
 }
 
@@ -241,10 +288,13 @@ static bool is_move(const lzg_tree* t, int u, int w, int v, int z) {
 int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
                         int32_t* best_index, int32_t* best_score, int32_t* all_scores) {
     t->last_v.resize(n_moves);
+    t->last_root_moves = 0;
+    t->last_up_ran = false;
     for (int i = 0; i < n_moves; i++) {
         const int32_t* m = moves + 4 * (size_t)i;
         if (!is_move(t, m[0], m[1], m[2], m[3])) return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "candidate is not an NNI move of this topology");
         t->last_v[i] = m[2];
+        t->last_root_moves += m[0] == 0;
     }
     if (n_moves == 0) {
         *best_index = -1;
@@ -253,11 +303,16 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     }
     int rc = ensure_cand_buffers(ctx, t, n_moves);
     if (rc != LZG_OK) return rc;
+    t->last_up_ran = !t->up_valid;
+    if (!t->up_valid) {
+        rc = lzg_tree_up_pass(ctx, t);
+        if (rc != LZG_OK) return rc;
+    }
     LZG_CUDA(ctx, cudaMemcpyAsync(t->d_moves, moves, sizeof(int32_t) * 4 * (size_t)n_moves, cudaMemcpyHostToDevice, ctx->stream));
     LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand_score, 0, sizeof(int32_t) * (size_t)n_moves, ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
-    k_nni_scores<<<dim3(n_moves, groups), threads, 0, ctx->stream>>>(t->d_moves, t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end,
-                                                                       t->d_score, t->d_cand_score, t->l_pad);
+    k_nni_scores<<<dim3(n_moves, groups), threads, 0, ctx->stream>>>(t->d_moves, t->d_child0, t->d_child1, t->d_start, t->d_end, t->d_ustart,
+                                                                       t->d_uend, t->d_score, t->d_upscore, t->d_cand_score, t->l_pad);
     LZG_LAUNCH_CHECK(ctx);
     k_nni_argmin<<<1, 1024, 0, ctx->stream>>>(t->d_cand_score, n_moves, t->d_score, greedy, ctx->d_scratch);
     LZG_LAUNCH_CHECK(ctx);
@@ -280,6 +335,7 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     t->child1[u] = std::max(v, z);
     t->parent[w] = v;
     t->parent[z] = u;
+    t->up_valid = false;
     int depth = 0;
     for (int a = v; a != 0; a = t->parent[a]) depth++;
     k_apply_topology<<<1, 1, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, u, w, v, z);

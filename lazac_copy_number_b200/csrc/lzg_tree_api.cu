@@ -16,6 +16,11 @@ static void tree_release(lzg_tree* t) {
     cudaFree(t->d_order);
     cudaFree(t->d_moves);
     cudaFree(t->d_cand_score);
+    lzg_dev_free(t->ctx, t->d_ustart);
+    lzg_dev_free(t->ctx, t->d_uend);
+    lzg_dev_free(t->ctx, t->d_upscore);
+    lzg_dev_free(t->ctx, t->d_upcost);
+    lzg_dev_free(t->ctx, t->d_ready);
     delete t;
 }
 
@@ -164,6 +169,7 @@ int lzg_tree_set_topology(lzg_ctx* ctx, lzg_tree* t, const int32_t* child0, cons
         return rc;
     }
     t->scored = false;
+    t->up_valid = false;
     return lzg_tree_upload_topology(ctx, t);
 }
 
@@ -238,6 +244,14 @@ int lzg_tree_last_nni_work(const lzg_tree* t, int64_t* merges, int64_t* bytes) {
     }
     if (merges) *merges = m;
     if (bytes) *bytes = (m + (int64_t)t->last_v.size()) * 2 * (int64_t)t->L;
+    return LZG_OK;
+}
+
+int lzg_tree_last_nni_traffic(const lzg_tree* t, int64_t* cand_bytes, int64_t* up_bytes) {
+    if (!t) return LZG_ERR_ARG;
+    const int64_t c = (int64_t)t->last_v.size(), L = t->L;
+    if (cand_bytes) *cand_bytes = (c * 8 - (int64_t)t->last_root_moves * 2) * L;
+    if (up_bytes) *up_bytes = t->last_up_ran ? (int64_t)t->up_nodes * 6 * L : 0;
     return LZG_OK;
 }
 

@@ -5,79 +5,57 @@
 namespace {
 
 // ---- neighbourhood scorer ----------------------------------------------------------------------
-// One CTA column (blockIdx.x) per candidate (u,w,v,z), blockIdx.y = group of 16-position chunks.
-// Reproduces nni -> unvisit(v) -> small_rectilinear -> read t[0].score -> undo
-// (/root/reference/src/copy_number.cxx:349-366) without touching the tree: with y = the child v
-// keeps,   I = merge(w, y)            (the new v)
-//          I = merge(I, z)            (the new u)
-//          I = merge(I, sibling(a))   for a = u, parent(u), ... up to the root,
-// every other node keeps its stored interval.  The running interval lives in
-// registers; each step reads one stored (start,end) pair; nothing is written but 4 bytes per CTA.
-// Topology hops (parent, sibling) are fetched four ahead so their latency overlaps the loads.
+// The reference scores a candidate (u,w,v,z) by nni -> unvisit(v) -> small_rectilinear -> read
+// t[0].score -> undo (/root/reference/src/copy_number.cxx:349-366): depth(v)+1 merges along the
+// path v .. root.  That root score is the optimum of the small-parsimony problem on the
+// candidate topology, and the interval DP is exact for it under ANY rooting (per position every
+// partial cost function has integer slopes, so min-plus convolution with |x| collapses to
+// "minimum + distance to the arg-min interval").  We therefore root the candidate at the edge
+// above u and need three merges only:
+//     I1 = merge(w, y)   (the new v; y = the child v keeps)      cost c1
+//     I2 = merge(I1, z)  (the new u)                              cost c2
+//     c3 = cost(merge(I2, UP(u)))                                 (skipped when u is the root)
+//     score = c1 + c2 + c3 + score[w] + score[y] + score[z] + upscore[u]
+// where UP(u) / upscore[u] are the interval and cumulative score of the rest of the tree seen
+// from the edge above u (k_up_level below).  8 L bytes per candidate instead of
+// (depth(v)+2) 2 L, nothing written but 4 bytes per CTA.  tests/ check every candidate's score
+// against the reference's path algorithm.
 __global__ void __launch_bounds__(256)
 k_nni_scores(const int32_t* __restrict__ moves, const int32_t* __restrict__ child0, const int32_t* __restrict__ child1,
-             const int2* __restrict__ up, const uint8_t* __restrict__ start, const uint8_t* __restrict__ end,
-             const int32_t* __restrict__ score, int32_t* __restrict__ cand_score, int l_pad) {
+             const uint8_t* __restrict__ start, const uint8_t* __restrict__ end, const uint8_t* __restrict__ ustart,
+             const uint8_t* __restrict__ uend, const int32_t* __restrict__ score, const int32_t* __restrict__ upscore,
+             int32_t* __restrict__ cand_score, int l_pad) {
     const int cand = blockIdx.x;
     const int4 mv = *reinterpret_cast<const int4*>(moves + 4 * cand);
     const int u = mv.x, w = mv.y, v = mv.z, z = mv.w;
     const int vc0 = child0[v], vc1 = child1[v];
     const int y = vc0 == z ? vc1 : vc0;
     const int chunk = blockIdx.y * blockDim.x + threadIdx.x;
-    const bool active = chunk * 16 < l_pad;
     const size_t off = (size_t)chunk * 16;
-
     uint32_t cost = 0;
-    int32_t node_scores = 0;
-    int a = u;
-    if (active) {
+    if (chunk * 16 < l_pad) {
+        uint4 sw = ldg16(start, (size_t)w * l_pad + off), ew = ldg16(end, (size_t)w * l_pad + off);
+        uint4 sy = ldg16(start, (size_t)y * l_pad + off), ey = ldg16(end, (size_t)y * l_pad + off);
+        uint4 sz = ldg16(start, (size_t)z * l_pad + off), ez = ldg16(end, (size_t)z * l_pad + off);
+        uint4 su = sz, eu = ez;
+        if (u != 0) {
+            su = ldg16(ustart, (size_t)u * l_pad + off);
+            eu = ldg16(uend, (size_t)u * l_pad + off);
+        }
         iv16 acc;
         uint32_t os[8], oe[8];
-        {
-            uint4 sw = ldg16(start, (size_t)w * l_pad + off), ew = ldg16(end, (size_t)w * l_pad + off);
-            uint4 sy = ldg16(start, (size_t)y * l_pad + off), ey = ldg16(end, (size_t)y * l_pad + off);
-            uint4 sz = ldg16(start, (size_t)z * l_pad + off), ez = ldg16(end, (size_t)z * l_pad + off);
-            widen(sw, acc.s);
-            widen(ew, acc.e);
-            widen(sy, os);
-            widen(ey, oe);
+        widen(sw, acc.s);
+        widen(ew, acc.e);
+        widen(sy, os);
+        widen(ey, oe);
+        cost += merge16(acc, os, oe);
+        widen(sz, os);
+        widen(ez, oe);
+        cost += merge16(acc, os, oe);
+        if (u != 0) {
+            widen(su, os);
+            widen(eu, oe);
             cost += merge16(acc, os, oe);
-            widen(sz, os);
-            widen(ez, oe);
-            cost += merge16(acc, os, oe);
-        }
-        node_scores = score[w] + score[y] + score[z];
-        while (a != 0) {
-            int sib[4];
-            int cnt = 0;
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                if (a != 0) {
-                    int2 ps = up[a];
-                    sib[q] = ps.y;
-                    a = ps.x;
-                    cnt++;
-                } else {
-                    sib[q] = 0;
-                }
-            }
-            uint4 S[4], E[4];
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                if (q < cnt) {
-                    S[q] = ldg16(start, (size_t)sib[q] * l_pad + off);
-                    E[q] = ldg16(end, (size_t)sib[q] * l_pad + off);
-                    node_scores += score[sib[q]];
-                }
-            }
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                if (q < cnt) {
-                    widen(S[q], os);
-                    widen(E[q], oe);
-                    cost += merge16(acc, os, oe);
-                }
-            }
         }
     }
     cost = warp_sum(cost);
@@ -87,9 +65,102 @@ k_nni_scores(const int32_t* __restrict__ moves, const int32_t* __restrict__ chil
     if (threadIdx.x == 0) {
         uint32_t tot = 0;
         for (int k = 0; k < (blockDim.x + 31) / 32; k++) tot += wsum[k];
-        int32_t add = (int32_t)tot + (blockIdx.y == 0 ? node_scores : 0);
+        int32_t add = (int32_t)tot;
+        if (blockIdx.y == 0) add += score[w] + score[y] + score[z] + (u != 0 ? upscore[u] : 0);
         if (add) atomicAdd(cand_score + cand, add);
     }
+}
+
+// ---- UP intervals: ONE dependency-driven launch ----------------------------------------------------
+// For a non-root node a with parent p and sibling s:
+//     p is the root:  UP(a) = DOWN(s),                 upscore[a] = score[s]
+//     otherwise:      UP(a) = merge(UP(p), DOWN(s)),   upscore[a] = cost + upscore[p] + score[s]
+// (the root has two children and no data of its own, so seen from one child the rest of the tree
+// is just the other child).  Only internal nodes are listed: a leaf is never the u of a move.
+//
+// A level-by-level schedule costs one launch per tree level (27 at cfg4, hundreds on a deep NJ
+// tree), each a few microseconds of mostly idle GPU.  Instead the work items (node, chunk group)
+// are listed parents-first (BFS order from the host mirror) and CTAs draw them from an atomic
+// ticket counter; an item waits on a per-(parent, group) epoch flag.  A ticket is only drawn by
+// a CTA that is already running and only waits for smaller tickets, so the spin cannot deadlock
+// whatever the number of resident CTAs.  Cross-CTA data goes through L2 (st + __threadfence +
+// release flag on one side, acquire flag + ld.cg on the other).
+__device__ __forceinline__ int ld_acquire(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 ldcg16(const uint8_t* base, size_t off) {
+    return __ldcg(reinterpret_cast<const uint4*>(base + off));
+}
+
+__global__ void __launch_bounds__(256)
+k_up_chain(const int32_t* __restrict__ order, int groups, const int2* __restrict__ up, const uint8_t* __restrict__ start,
+           const uint8_t* __restrict__ end, uint8_t* __restrict__ ustart, uint8_t* __restrict__ uend,
+           int32_t* __restrict__ upcost, int* __restrict__ ready, int epoch, int* __restrict__ ticket, int l_pad) {
+    __shared__ int s_item;
+    if (threadIdx.x == 0) s_item = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int item = s_item;
+    const int a = order[item / groups], g = item % groups;
+    const int2 ps = up[a];
+    const int chunk = g * blockDim.x + threadIdx.x;
+    const bool active = chunk * 16 < l_pad;
+    const size_t off = (size_t)chunk * 16;
+    uint4 ss = make_uint4(0, 0, 0, 0), se = ss;
+    if (active) {  // the sibling's DOWN interval does not depend on the wait
+        ss = ldg16(start, (size_t)ps.y * l_pad + off);
+        se = ldg16(end, (size_t)ps.y * l_pad + off);
+    }
+    uint32_t c = 0;
+    if (ps.x != 0) {
+        if (threadIdx.x == 0) {
+            const int* flag = ready + (size_t)ps.x * groups + g;
+            while (ld_acquire(flag) != epoch) __nanosleep(20);
+        }
+        __syncthreads();
+        if (active) {
+            uint4 us = ldcg16(ustart, (size_t)ps.x * l_pad + off), ue = ldcg16(uend, (size_t)ps.x * l_pad + off);
+            iv16 acc;
+            uint32_t os[8], oe[8];
+            widen(us, acc.s);
+            widen(ue, acc.e);
+            widen(ss, os);
+            widen(se, oe);
+            c = merge16(acc, os, oe);
+            ss = narrow(acc.s);
+            se = narrow(acc.e);
+        }
+    }
+    if (active) {
+        *reinterpret_cast<uint4*>(ustart + (size_t)a * l_pad + off) = ss;
+        *reinterpret_cast<uint4*>(uend + (size_t)a * l_pad + off) = se;
+    }
+    c = warp_sum(c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(upcost + a, (int32_t)c);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) st_release(ready + (size_t)a * groups + g, epoch);
+}
+
+// upscore[a] = sum over b = a, parent(a), ... (below the root's children) of upcost[b] + score[sibling(b)]:
+// one thread per listed node walks up; no level structure needed.
+__global__ void k_up_scores(const int32_t* __restrict__ order, int n_items, const int2* __restrict__ up,
+                            const int32_t* __restrict__ upcost, const int32_t* __restrict__ score,
+                            int32_t* __restrict__ upscore) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_items) return;
+    const int a = order[i];
+    int32_t tot = 0;
+    for (int b = a; b != 0;) {
+        int2 ps = up[b];
+        tot += score[ps.y] + (ps.x != 0 ? upcost[b] : 0);
+        b = ps.x;
+    }
+    upscore[a] = tot;
 }
 
 // Strict '<' with first-wins ties (src/copy_number.cxx:353-357): minimise (score, index) over the

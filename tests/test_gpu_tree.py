@@ -67,6 +67,9 @@ def test_neighbourhood_scores_and_choice(ctx, port, n_leaves, bins, alleles, gre
         assert score == want["score"] and tuple(moves[idx]) == want["move"]
     merges, nbytes = gt.last_nni_work()
     assert merges >= 2 * len(moves) and nbytes == (merges + len(moves)) * 2 * gt.L
+    cand_bytes, up_bytes = gt.last_nni_traffic()
+    root_moves = int((moves[:, 0] == 0).sum())
+    assert cand_bytes == (8 * len(moves) - 2 * root_moves) * gt.L and up_bytes % (6 * gt.L) == 0
     gt.free()
     prof.free()
 
@@ -141,3 +144,39 @@ def test_errors(ctx):
     assert t.nni_best(np.zeros((0, 4), np.int32))[0] == -1
     t.free()
     prof.free()
+
+
+def test_up_intervals_invariant_and_deep_trees(ctx, port):
+    """Caterpillar (maximally deep) and random trees: every candidate's 3-merge score equals the
+    reference's path re-scoring, before and after accepted moves (UP intervals rebuilt)."""
+    n_leaves, bins = 64, 300
+    prof = synth.make_profiles(n_leaves, bins, 2, seed=31)
+    bp = synth.bp_from_cn(prof["cn"], prof["seg"])
+    n = 2 * n_leaves - 1
+    # caterpillar: internal i has children (i+1, leaf), last internal has two leaves
+    c0 = np.full(n, -1, np.int32)
+    c1 = np.full(n, -1, np.int32)
+    for i in range(n_leaves - 1):
+        c0[i] = i + 1 if i < n_leaves - 2 else n_leaves - 1 + i
+        c1[i] = n_leaves - 1 + i + (1 if i == n_leaves - 2 else 0)
+    leaf_row = np.full(n, -1, np.int32)
+    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
+    leaf_bp = np.zeros((n, bp.shape[1]), np.int32)
+    leaf_bp[n_leaves - 1:] = bp
+    gp = Profiles(ctx, bp)
+    gt = Tree(ctx, gp, c0, c1, leaf_row)
+    pt = PortTree(port, c0, c1, leaf_bp)
+    assert gt.small_rectilinear() == pt.small_rectilinear()
+    for step in range(6):
+        eu, ev = pt.edges()
+        order = np.random.default_rng(step).permutation(len(eu)).astype(np.int32)
+        full = pt.greedy_nni(eu, ev, order)
+        moves = gt.enumerate_moves(eu, ev, order)
+        idx, score, allsc = gt.nni_best(moves, want_all=True)
+        assert np.array_equal(allsc, full["scores"])
+        assert idx == full["index"]
+        if idx < 0:
+            break
+        assert gt.apply_nni(*moves[idx]) == pt.apply_nni(*full["move"])
+    gt.free()
+    gp.free()
