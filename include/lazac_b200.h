@@ -120,9 +120,10 @@ int lzg_tree_ancestral(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t
 /* Work the REFERENCE's path algorithm does for the candidates of the last lzg_nni_best on this
  * tree: merges (= sum over candidates of depth(v)+1) and bytes read (= (merges + n_moves) * 2 * L). */
 int lzg_tree_last_nni_work(const lzg_tree* t, int64_t* merges, int64_t* bytes);
-/* Algorithmic bytes of the same call as executed here: candidates (8 L each: w, y, z and the UP
- * interval of u; 6 L when u is the root) and the UP pass it had to run first (6 L per internal
- * non-root node: read UP(parent) and DOWN(sibling), write UP; 0 when the UP intervals were valid). */
+/* Algorithmic bytes of the same call as executed here: candidates (10 L each: the intervals of w,
+ * y, z, u and the UP interval of u; 6 L when u is the root) and the UP pass it had to run first
+ * (4 L per internal non-root node: read DOWN(sibling), write UP; + 2 L per heavy path for the UP
+ * interval its head hangs off; 0 when the UP intervals were still valid). */
 int lzg_tree_last_nni_traffic(const lzg_tree* t, int64_t* cand_bytes, int64_t* up_bytes);
 
 #ifdef __cplusplus

@@ -10,6 +10,7 @@
 #include "lzg_tree.cuh"
 
 #include <algorithm>
+#include <cstring>
 
 namespace {
 
@@ -216,62 +217,56 @@ int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t) {
     return LZG_OK;
 }
 
-// UP intervals for every internal non-root node: one dependency-driven launch (see k_up_chain).
-int lzg_tree_up_pass(lzg_ctx* ctx, lzg_tree* t) {
+// Heavy-path decomposition of the internal non-root nodes, paths listed parents-first (a path's
+// head hangs off a node of an earlier path or off the root).  order[] = nodes path after path,
+// path_off[] = path boundaries.  Returns the number of paths.
+static int build_up_paths(const lzg_tree* t, int32_t* order, int32_t* path_off, int* n_order) {
     const int n = t->n_nodes;
-    const size_t nb = (size_t)n * t->l_pad;
-    int groups, threads = chunk_threads(t->l_pad, &groups);
-    if (!t->d_ustart) {
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ustart, nb));
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_uend, nb));
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_upscore, sizeof(int32_t) * n));
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_upcost, sizeof(int32_t) * n));
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ready, sizeof(int) * ((size_t)n * groups + 1)));
-        LZG_CUDA(ctx, cudaMemsetAsync(t->d_ready, 0, sizeof(int) * ((size_t)n * groups + 1), ctx->stream));
-        t->epoch = 0;
-    }
-    // parents-first order of the internal non-root nodes, staged in pinned memory (no sync needed:
-    // every public entry point ends with a synchronising read-back before the staging area is reused)
-    int rc = lzg_ensure_pinned(ctx, (size_t)n + 64);
-    if (rc != LZG_OK) return rc;
-    int32_t* order = ctx->h_pinned + 64;
-    int cnt = 0;
-    if (t->child0[0] >= 0) {
-        for (int c : {t->child0[0], t->child1[0]})
-            if (t->child0[c] >= 0) order[cnt++] = c;
-        for (int i = 0; i < cnt; i++) {
-            const int a = order[i];
-            for (int c : {t->child0[a], t->child1[a]})
-                if (t->child0[c] >= 0) order[cnt++] = c;
+    std::vector<int32_t> size(n, 0), pre;
+    pre.reserve(n);
+    pre.push_back(0);
+    for (size_t i = 0; i < pre.size(); i++) {  // BFS order: parents before children
+        int a = pre[i];
+        if (t->child0[a] >= 0) {
+            pre.push_back(t->child0[a]);
+            pre.push_back(t->child1[a]);
         }
     }
-    t->up_nodes = cnt;
-    if (cnt > 0) {
-        t->epoch++;
-        int* ticket = t->d_ready + (size_t)n * groups;
-        LZG_CUDA(ctx, cudaMemcpyAsync(t->d_order, order, sizeof(int32_t) * cnt, cudaMemcpyHostToDevice, ctx->stream));
-        LZG_CUDA(ctx, cudaMemsetAsync(t->d_upcost, 0, sizeof(int32_t) * n, ctx->stream));
-        LZG_CUDA(ctx, cudaMemsetAsync(ticket, 0, sizeof(int), ctx->stream));
-        k_up_chain<<<cnt * groups, threads, 0, ctx->stream>>>(t->d_order, groups, t->d_up, t->d_start, t->d_end, t->d_ustart, t->d_uend,
-                                                              t->d_upcost, t->d_ready, t->epoch, ticket, t->l_pad);
-        LZG_LAUNCH_CHECK(ctx);
-        k_up_scores<<<(cnt + 255) / 256, 256, 0, ctx->stream>>>(t->d_order, cnt, t->d_up, t->d_upcost, t->d_score, t->d_upscore);
-        LZG_LAUNCH_CHECK(ctx);
+    for (int i = n - 1; i >= 0; i--) {  // internal nodes below (and including) a
+        int a = pre[i];
+        if (t->child0[a] >= 0) size[a] = 1 + size[t->child0[a]] + size[t->child1[a]];
     }
-    t->up_valid = true;
-    return LZG_OK;
+    int cnt = 0, paths = 0;
+    std::vector<int32_t> heads;
+    if (t->child0[0] >= 0)
+        for (int c : {t->child0[0], t->child1[0]})
+            if (size[c] > 0) heads.push_back(c);
+    for (size_t h = 0; h < heads.size(); h++) {
+        path_off[paths++] = cnt;
+        for (int a = heads[h]; a >= 0;) {
+            order[cnt++] = a;
+            const int c0 = t->child0[a], c1 = t->child1[a];
+            const int heavy = size[c0] >= size[c1] ? c0 : c1, light = heavy == c0 ? c1 : c0;
+            if (size[light] > 0) heads.push_back(light);
+            a = size[heavy] > 0 ? heavy : -1;
+        }
+    }
+    path_off[paths] = cnt;
+    *n_order = cnt;
+    return paths;
 }
 
 static int ensure_cand_buffers(lzg_ctx* ctx, lzg_tree* t, int n_moves) {
-    if (n_moves <= t->cand_cap) return LZG_OK;
-    int cap = std::max(n_moves, 2 * t->n_nodes);
-    if (t->d_moves) cudaFree(t->d_moves);
-    if (t->d_cand_score) cudaFree(t->d_cand_score);
-    t->d_moves = nullptr;
-    t->d_cand_score = nullptr;
+    if (n_moves <= t->cand_cap && t->d_pass) return LZG_OK;
+    const int cap = std::max(n_moves, 2 * t->n_nodes);
+    lzg_dev_free(ctx, t->d_pass);
+    lzg_dev_free(ctx, t->d_cand);
+    t->d_pass = nullptr;
+    t->d_cand = nullptr;
     t->cand_cap = 0;
-    LZG_CUDA(ctx, cudaMalloc(&t->d_moves, sizeof(int32_t) * 4 * (size_t)cap));
-    LZG_CUDA(ctx, cudaMalloc(&t->d_cand_score, sizeof(int32_t) * (size_t)cap));
+    // d_pass: [path_off | order | moves] packed per call; d_cand: [ctl (16) | cand_score (cap)]
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_pass, sizeof(int32_t) * ((size_t)2 * t->n_nodes + 8 + 4 * (size_t)cap)));
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_cand, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)cap)));
     t->cand_cap = cap;
     return LZG_OK;
 }
@@ -285,6 +280,7 @@ static bool is_move(const lzg_tree* t, int u, int w, int v, int z) {
     return true;
 }
 
+// One neighbourhood pass: one staged H2D copy, one memset, one launch (k_nni_pass), one read-back.
 int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
                         int32_t* best_index, int32_t* best_score, int32_t* all_scores) {
     t->last_v.resize(n_moves);
@@ -301,34 +297,81 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         *best_score = t->root_score;
         return LZG_OK;
     }
+    const int n = t->n_nodes;
+    int groups, threads = chunk_threads(t->l_pad, &groups);
     int rc = ensure_cand_buffers(ctx, t, n_moves);
     if (rc != LZG_OK) return rc;
-    t->last_up_ran = !t->up_valid;
-    if (!t->up_valid) {
-        rc = lzg_tree_up_pass(ctx, t);
-        if (rc != LZG_OK) return rc;
+    if (!t->d_ustart) {
+        const size_t nb = (size_t)n * t->l_pad;
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ustart, nb));
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_uend, nb));
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ready, sizeof(int) * (size_t)n * groups));
+        LZG_CUDA(ctx, cudaMemsetAsync(t->d_ready, 0, sizeof(int) * (size_t)n * groups, ctx->stream));
+        t->epoch = 0;
+        t->up_valid = false;
     }
-    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_moves, moves, sizeof(int32_t) * 4 * (size_t)n_moves, cudaMemcpyHostToDevice, ctx->stream));
-    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand_score, 0, sizeof(int32_t) * (size_t)n_moves, ctx->stream));
-    int groups, threads = chunk_threads(t->l_pad, &groups);
-    k_nni_scores<<<dim3(n_moves, groups), threads, 0, ctx->stream>>>(t->d_moves, t->d_child0, t->d_child1, t->d_start, t->d_end, t->d_ustart,
-                                                                       t->d_uend, t->d_score, t->d_upscore, t->d_cand_score, t->l_pad);
+    // staging (pinned; every public entry point ends with a synchronising read-back, so the area is
+    // free again when the next call fills it): [result (16) | path_off | order | moves]
+    rc = lzg_ensure_pinned(ctx, 16 + (size_t)2 * n + 8 + 4 * (size_t)n_moves);
+    if (rc != LZG_OK) return rc;
+    int32_t* stage = ctx->h_pinned + 16;
+    int n_paths = 0, n_order = 0;
+    if (!t->up_valid) {
+        n_paths = build_up_paths(t, stage + n + 2, stage, &n_order);
+        // compact: path_off has n_paths + 1 entries; move order right behind it
+        memmove(stage + n_paths + 1, stage + n + 2, sizeof(int32_t) * n_order);
+        t->up_nodes = n_order;
+        t->up_paths = n_paths;
+        t->epoch++;
+        t->last_up_ran = true;
+    } else {
+        stage[0] = 0;
+    }
+    const size_t o_order = (size_t)n_paths + 1, o_moves = (o_order + n_order + 3) / 4 * 4;  // int4 loads of the moves
+    memcpy(stage + o_moves, moves, sizeof(int32_t) * 4 * (size_t)n_moves);
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass, stage, sizeof(int32_t) * (o_moves + 4 * (size_t)n_moves), cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)n_moves), ctx->stream));
+    lzg_pass_args A;
+    A.path_off = t->d_pass;
+    A.order = t->d_pass + o_order;
+    A.moves = t->d_pass + o_moves;
+    A.n_paths = n_paths;
+    A.n_cand = n_moves;
+    A.groups = groups;
+    A.l_pad = t->l_pad;
+    A.epoch = t->epoch;
+    A.greedy = greedy;
+    A.child0 = t->d_child0;
+    A.child1 = t->d_child1;
+    A.up = t->d_up;
+    A.start = t->d_start;
+    A.end = t->d_end;
+    A.ustart = t->d_ustart;
+    A.uend = t->d_uend;
+    A.score = t->d_score;
+    A.ready = t->d_ready;
+    A.ctl = t->d_cand;
+    A.cand_score = t->d_cand + LZG_CTL_INTS;
+    const long long items = ((long long)n_paths + n_moves) * groups;
+    k_nni_pass<<<(unsigned)items, threads, 0, ctx->stream>>>(A);
     LZG_LAUNCH_CHECK(ctx);
-    k_nni_argmin<<<1, 1024, 0, ctx->stream>>>(t->d_cand_score, n_moves, t->d_score, greedy, ctx->d_scratch);
-    LZG_LAUNCH_CHECK(ctx);
-    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, ctx->d_scratch, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    t->up_valid = true;
+    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_cand, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     if (all_scores)
-        LZG_CUDA(ctx, cudaMemcpyAsync(all_scores, t->d_cand_score, sizeof(int32_t) * (size_t)n_moves, cudaMemcpyDeviceToHost, ctx->stream));
+        LZG_CUDA(ctx, cudaMemcpyAsync(all_scores, t->d_cand + LZG_CTL_INTS, sizeof(int32_t) * (size_t)n_moves, cudaMemcpyDeviceToHost, ctx->stream));
     LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    *best_index = ctx->h_pinned[0];
-    *best_score = ctx->h_pinned[1];
+    *best_index = ctx->h_pinned[LZG_CTL_BEST];
+    *best_score = ctx->h_pinned[LZG_CTL_SCORE];
     return LZG_OK;
 }
 
+// Accept a move: one memset, one launch (k_apply_move), one read-back.
 int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     if (!is_move(t, u, w, v, z)) return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "not an NNI move of this topology");
+    const int y = t->child0[v] == z ? t->child1[v] : t->child0[v];
+    int depth = 0;
+    for (int a = v; a != 0; a = t->parent[a]) depth++;
     // host mirror
-    int y = t->child0[v] == z ? t->child1[v] : t->child0[v];
     t->child0[v] = std::min(w, y);
     t->child1[v] = std::max(w, y);
     t->child0[u] = std::min(v, z);
@@ -336,19 +379,14 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     t->parent[w] = v;
     t->parent[z] = u;
     t->up_valid = false;
-    int depth = 0;
-    for (int a = v; a != 0; a = t->parent[a]) depth++;
-    k_apply_topology<<<1, 1, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, u, w, v, z);
-    LZG_LAUNCH_CHECK(ctx);
-    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cost, 0, sizeof(int32_t) * (size_t)(depth + 1), ctx->stream));
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_ctl, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)depth + 1), ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
-    k_rescore_path<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_cost, v, t->l_pad);
+    k_apply_move<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_score, t->d_cost, t->d_ctl,
+                                                      u, w, v, z, y, t->l_pad);
     LZG_LAUNCH_CHECK(ctx);
-    k_path_scores<<<1, 1, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_cost, t->d_score, v);
-    LZG_LAUNCH_CHECK(ctx);
-    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_score, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_ctl, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    t->root_score = ctx->h_pinned[0];
+    t->root_score = ctx->h_pinned[LZG_CTL_SCORE];
     return LZG_OK;
 }
 

@@ -14,11 +14,11 @@ struct lzg_tree {
     int2* d_up = nullptr;       // (parent, sibling) per node, (-1,-1) for the root
     uint8_t *d_start = nullptr, *d_end = nullptr;
     int32_t* d_score = nullptr;  // cumulative subtree score (t[u].data.score)
-    int32_t* d_cost = nullptr;   // per-node merge cost / per-step path cost scratch [n_nodes]
+    int32_t* d_ctl = nullptr;    // 16 control ints (finished-CTA counter, results) right in front of d_cost
+    int32_t* d_cost = nullptr;   // = d_ctl + 16: per-node merge cost / per-step path cost scratch [n_nodes + 1]
     int32_t* d_order = nullptr;  // level-ordered node list scratch [n_nodes]
     // UP intervals (rest of the tree seen from the edge above a node), allocated on first use
     uint8_t *d_ustart = nullptr, *d_uend = nullptr;
-    int32_t *d_upscore = nullptr, *d_upcost = nullptr;
     int* d_ready = nullptr;      // per (node, chunk group) epoch flags of the dependency-driven passes, + 1 ticket counter
     int epoch = 0;
     bool up_valid = false;       // cleared by every topology / interval change
@@ -26,18 +26,18 @@ struct lzg_tree {
     int32_t root_score = 0;
     // candidate buffers, grown on demand
     int32_t cand_cap = 0;
-    int32_t* d_moves = nullptr;       // [cand_cap][4]
-    int32_t* d_cand_score = nullptr;  // [cand_cap]
+    int32_t* d_pass = nullptr;        // per-pass upload: [path_off | order | moves]
+    int32_t* d_cand = nullptr;        // [ctl (16) | cand_score (cand_cap)]
     std::vector<int32_t> last_v;      // v of every candidate of the last lzg_nni_best
     int32_t last_root_moves = 0;      // candidates of that call whose u is the root (two merges, no UP)
     bool last_up_ran = false;         // that call had to rebuild the UP intervals
     int32_t up_nodes = 0;             // internal non-root nodes (UP rows written by an UP pass)
+    int32_t up_paths = 0;             // heavy paths they form
 };
 
 int lzg_tree_upload_topology(lzg_ctx* ctx, lzg_tree* t);
 int lzg_tree_gather_leaves(lzg_ctx* ctx, lzg_tree* t, const lzg_profiles* p, const int32_t* leaf_row);
 int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t);
-int lzg_tree_up_pass(lzg_ctx* ctx, lzg_tree* t);
 int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
                         int32_t* best_index, int32_t* best_score, int32_t* all_scores);
 int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z);

@@ -12,14 +12,12 @@ static void tree_release(lzg_tree* t) {
     cudaFree(t->d_start);
     cudaFree(t->d_end);
     cudaFree(t->d_score);
-    cudaFree(t->d_cost);
+    cudaFree(t->d_ctl);
     cudaFree(t->d_order);
-    cudaFree(t->d_moves);
-    cudaFree(t->d_cand_score);
+    lzg_dev_free(t->ctx, t->d_pass);
+    lzg_dev_free(t->ctx, t->d_cand);
     lzg_dev_free(t->ctx, t->d_ustart);
     lzg_dev_free(t->ctx, t->d_uend);
-    lzg_dev_free(t->ctx, t->d_upscore);
-    lzg_dev_free(t->ctx, t->d_upcost);
     lzg_dev_free(t->ctx, t->d_ready);
     delete t;
 }
@@ -38,7 +36,8 @@ static int tree_alloc(lzg_ctx* ctx, int n_nodes, int L, int l_pad, lzg_tree** ou
     if (e == cudaSuccess) e = cudaMalloc(&t->d_start, nb);
     if (e == cudaSuccess) e = cudaMalloc(&t->d_end, nb);
     if (e == cudaSuccess) e = cudaMalloc(&t->d_score, sizeof(int32_t) * n_nodes);
-    if (e == cudaSuccess) e = cudaMalloc(&t->d_cost, sizeof(int32_t) * (n_nodes + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&t->d_ctl, sizeof(int32_t) * (16 + n_nodes + 1));
+    if (e == cudaSuccess) t->d_cost = t->d_ctl + 16;
     if (e == cudaSuccess) e = cudaMalloc(&t->d_order, sizeof(int32_t) * n_nodes);
     if (e == cudaSuccess) e = cudaMemsetAsync(t->d_score, 0, sizeof(int32_t) * n_nodes, ctx->stream);
     if (e != cudaSuccess) {
@@ -250,8 +249,8 @@ int lzg_tree_last_nni_work(const lzg_tree* t, int64_t* merges, int64_t* bytes) {
 int lzg_tree_last_nni_traffic(const lzg_tree* t, int64_t* cand_bytes, int64_t* up_bytes) {
     if (!t) return LZG_ERR_ARG;
     const int64_t c = (int64_t)t->last_v.size(), L = t->L;
-    if (cand_bytes) *cand_bytes = (c * 8 - (int64_t)t->last_root_moves * 2) * L;
-    if (up_bytes) *up_bytes = t->last_up_ran ? (int64_t)t->up_nodes * 6 * L : 0;
+    if (cand_bytes) *cand_bytes = (c * 10 - (int64_t)t->last_root_moves * 4) * L;
+    if (up_bytes) *up_bytes = t->last_up_ran ? ((int64_t)t->up_nodes * 4 + (int64_t)t->up_paths * 2) * L : 0;
     return LZG_OK;
 }
 

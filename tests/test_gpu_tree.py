@@ -69,7 +69,7 @@ def test_neighbourhood_scores_and_choice(ctx, port, n_leaves, bins, alleles, gre
     assert merges >= 2 * len(moves) and nbytes == (merges + len(moves)) * 2 * gt.L
     cand_bytes, up_bytes = gt.last_nni_traffic()
     root_moves = int((moves[:, 0] == 0).sum())
-    assert cand_bytes == (8 * len(moves) - 2 * root_moves) * gt.L and up_bytes % (6 * gt.L) == 0
+    assert cand_bytes == (10 * len(moves) - 4 * root_moves) * gt.L and up_bytes % (2 * gt.L) == 0
     gt.free()
     prof.free()
 
