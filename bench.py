@@ -41,6 +41,7 @@ WORKLOADS = {
 }
 NNI_WORKLOADS = {
     "cfg4": dict(cells=1000, bins=5000, alleles=1),
+    "cfg5": dict(cells=10000, bins=10000, alleles=2),
     "tiny": dict(cells=60, bins=300, alleles=1),
 }
 # VABSDIFF4.U8.ACC issue rate measured on this pool's B200 (tools/microbench.cu,
@@ -269,6 +270,77 @@ def nni_section(ctx, args, peaks, peaks_kind):
     return out
 
 
+def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
+    """cfg5 (N > 1): every rank holds the tree, scores its slice of the neighbourhood, and the ranks
+    min-all-reduce one 64-bit (score, index) key over NCCL; timed by wall clock between barriers
+    (max over ranks), one pass per step, UP intervals rebuilt every pass as after an accepted move."""
+    import torch
+    import torch.distributed as dist
+    from lazac_copy_number_b200 import nj, sharding, synth
+    from lazac_copy_number_b200.api import Profiles, Tree
+    name = "tiny" if args.workload == "tiny" else "cfg5"
+    w = NNI_WORKLOADS[name]
+    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0, want_tree=True)
+    bp = bp_int8_chunked(prof["cn"], prof["seg"])
+    n_leaves, L = bp.shape
+    n = 2 * n_leaves - 1
+    c0, c1 = synth.perturb_tree(prof["child0"], prof["child1"], n_leaves // 5, np.random.default_rng(1))
+    leaf_row = np.full(n, -1, np.int32)
+    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
+    gp = Profiles(ctx, bp)
+    t = Tree(ctx, gp, c0, c1, leaf_row)
+    root = t.small_rectilinear()
+    eu, ev = t.edges()
+    order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
+    moves = t.enumerate_moves(eu, ev, order)
+    C_ = len(moves)
+    lo, hi = sharding.candidate_slice(C_, rank, world)
+    mine = np.ascontiguousarray(moves[lo:hi])
+    dep = nj.depths(c0, c1)
+
+    def one_pass():
+        li, ls, _ = t.nni_best(mine)
+        return sharding.allreduce_best(li, ls, lo, device="cuda")
+
+    for _ in range(max(3, args.warmup)):
+        gi, gs = one_pass()
+    tot = 0.0
+    for _ in range(args.steps):
+        t.set_topology(c0, c1)          # stale UP intervals, as after an accepted move (untimed)
+        t.small_rectilinear()
+        ctx.flush_l2()
+        ctx.sync()
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        gi, gs = one_pass()
+        torch.cuda.synchronize()
+        tot += time.perf_counter() - t0
+    tt = torch.tensor([tot], dtype=torch.float64, device="cuda")
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    tot = float(tt[0])
+    cb, ub = t.last_nni_traffic()
+    bt = torch.tensor([float(cb + ub)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(bt, op=dist.ReduceOp.SUM)
+    merges, ref_bytes = t.last_nni_work()
+    out = {
+        "metric": "nni_candidates_scored_per_sec", "value": C_ * args.steps / tot, "unit": "candidates/s", "n_gpus": world,
+        "ms_per_step": 1e3 * tot / args.steps, "scaling": "strong",
+        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_,
+                   "seed_tree": "generating tree + %d random NNIs (NJ at this n is host-side O(n^3): SURVEY.md 8(f) rank 1)" % (n_leaves // 5),
+                   "pass": "per rank: UP pass (replicated) + its slice of the candidates + argmin; then one 8-byte NCCL min all-reduce",
+                   "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
+                   "root_score": int(root), "best_index": int(gi), "best_score": None if gs is None else int(gs),
+                   "timing": "wall clock between barrier + synchronize, max over ranks"},
+        "roofline": {"bound": "hbm", "achieved": float(bt[0]) / world / (tot / args.steps) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s per GPU",
+                     "frac": float(bt[0]) / world / (tot / args.steps) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
+                     "algorithmic_bytes_per_pass_all_ranks": int(bt[0])},
+    }
+    t.free()
+    gp.free()
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -282,6 +354,8 @@ def run_b200(args):
         sys.exit("no GPU: the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries one JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_bench_%h_%p.log")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     peaks, peaks_kind = measured_peaks()
 
@@ -313,6 +387,17 @@ def run_b200(args):
 
     for _ in range(max(3, args.warmup)):
         step_device()
+    n1_same = None
+    if world > 1 and rank == 0:
+        # the same matrix on ONE GPU (all shards on rank 0), for the strong-scaling denominator
+        ts = []
+        for _ in range(3):
+            ctx.flush_l2()
+            ctx.timer_start()
+            gp.distance_device_async(d_D.data_ptr(), 0, 1)
+            ts.append(ctx.timer_stop())
+        n1_same = {"ms_per_step": float(np.median(ts)), "value": P / (float(np.median(ts)) * 1e-3), "unit": "cell-pairs/s",
+                   "note": "this workload on one GPU of the same box, same kernel (measured before the timed region)"}
     barrier()
     launches0 = ctx.launch_count()
     clocks = ClockSampler(local)
@@ -392,6 +477,8 @@ def run_b200(args):
                                  "frac": hbm_bytes / world / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_kind": peaks_kind}},
             "wall_s_timed_region": wall,
         }
+        if n1_same:
+            line["n1_same_workload"] = n1_same
     if world == 1 and not args.no_cpu:
         n_sample = args.ref_cells or (160 if L <= 10000 else 110)
         v, kind, dt, pairs = cpu_distance_sample(bp, min(n, n_sample))
@@ -401,6 +488,10 @@ def run_b200(args):
     del d_D
     if world == 1 and not args.no_nni:
         line["nni"] = nni_section(ctx, args, peaks, peaks_kind)
+    if world > 1 and not args.no_nni:
+        nni = nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind)
+        if rank == 0:
+            line["nni"] = nni
     ctx.close()
     if rank == 0:
         print(json.dumps(line), flush=True)

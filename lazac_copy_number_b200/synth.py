@@ -126,3 +126,28 @@ def write_cn_csv(path, prof, both_alleles_columns=True):
                     if two:
                         row += ",%d" % cn[i, by_chrom[ch][1][0] + k]
                     f.write(row + "\n")
+
+
+def perturb_tree(child0, child1, n_moves, rng):
+    """n_moves random NNIs on a (child0, child1) tree with root 0: a cheap stand-in for a seed tree
+    that is close to, but not at, a local optimum.  Returns new arrays."""
+    c0, c1 = np.array(child0, np.int32), np.array(child1, np.int32)
+    n = len(c0)
+    parent = np.full(n, -1, np.int32)
+    for u in range(n):
+        if c0[u] >= 0:
+            parent[c0[u]] = u
+            parent[c1[u]] = u
+    internal = np.flatnonzero((c0 >= 0) & (np.arange(n) != 0))
+    if len(internal) == 0:
+        return c0, c1
+    for _ in range(n_moves):
+        v = int(internal[rng.integers(len(internal))])
+        u = int(parent[v])
+        w = int(c1[u] if c0[u] == v else c0[u])
+        z = int(c0[v] if rng.random() < 0.5 else c1[v])
+        y = int(c1[v] if c0[v] == z else c0[v])
+        c0[v], c1[v] = min(w, y), max(w, y)
+        c0[u], c1[u] = min(v, z), max(v, z)
+        parent[w], parent[z] = v, u
+    return c0, c1
