@@ -1,0 +1,470 @@
+// host/main.cpp -- the `lazac` command line of the reference (subcommands `distance` and `nni`,
+// same flags, same output files) over liblazac_b200.so.
+// Follows /root/reference/src/lazac.cxx: do_distance :97-132, do_nni :134-338, main :340-431.
+// Additive, not in the reference: `--device N` on both subcommands; the GPU-free helper
+// subcommands `nj` (seed tree from a PREFIX_dist_matrix.txt) and `bp` (breakpoint matrix of a CSV),
+// used by the CPU-side tests.
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <ctime>
+#include <fstream>
+#include <iostream>
+#include <map>
+#include <optional>
+#include <random>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "lazac_b200.h"
+#include "newick.hpp"
+#include "profiles.hpp"
+#include "search.hpp"
+#include "seed_tree.hpp"
+
+using namespace lazac_host;
+
+namespace {
+
+// "[2026-11-04 17:31:08.321] [lazac] [info] message" (the reference's spdlog default pattern)
+void log_info(const std::string& msg) {
+    using namespace std::chrono;
+    const auto now = system_clock::now();
+    const std::time_t tt = system_clock::to_time_t(now);
+    const int ms = (int)(duration_cast<milliseconds>(now.time_since_epoch()).count() % 1000);
+    std::tm tm_buf;
+    localtime_r(&tt, &tm_buf);
+    char stamp[64];
+    std::strftime(stamp, sizeof stamp, "%Y-%m-%d %H:%M:%S", &tm_buf);
+    std::printf("[%s.%03d] [lazac] [info] %s\n", stamp, ms, msg.c_str());
+    std::fflush(stdout);
+}
+
+struct Args {
+    std::string command, cn_profile, tree, output;
+    double aggression = 1.0;
+    int iterations = 100, seed = 0, device = 0;
+    bool greedy = false, have_output = false;
+};
+
+const char* USAGE =
+    "Usage: lazac distance cn_profile -o PREFIX [--device N]\n"
+    "       lazac nni cn_profile [-t TREE] -o PREFIX [-a AGGRESSION] [-i ITERATIONS] [-g] [-s SEED] [--device N]\n"
+    "\n"
+    "  -t, --tree        seed tree in Newick format. [default: \"\"]\n"
+    "  -o, --output      prefix of the output files [required]\n"
+    "  -a, --aggression  aggression of stochastic perturbation in (0, infinity) [default: 1]\n"
+    "  -i, --iterations  number of iterations to perform without improvement before stopping [default: 100]\n"
+    "  -g, --greedy      use greedy hill climbing strategy as opposed to full NNI neighborhood exploration\n"
+    "  -s, --seed        seed for random number generator [default: 0]\n"
+    "      --device      CUDA device index [default: 0]\n";
+
+Args parse_args(int argc, char** argv) {
+    Args a;
+    if (argc < 2) throw std::runtime_error("missing subcommand");
+    a.command = argv[1];
+    if (a.command != "distance" && a.command != "nni" && a.command != "nj" && a.command != "bp")
+        throw std::runtime_error("unknown subcommand: " + a.command);
+    bool have_positional = false;
+    for (int i = 2; i < argc; i++) {
+        const std::string s = argv[i];
+        auto value = [&]() -> std::string {
+            if (i + 1 >= argc) throw std::runtime_error(s + ": expected 1 argument(s). 0 provided.");
+            return argv[++i];
+        };
+        auto number = [&](const std::string& v, bool integer) -> double {
+            size_t used = 0;
+            double x = 0;
+            try {
+                x = integer ? (double)std::stoi(v, &used) : std::stod(v, &used);
+            } catch (const std::exception&) {
+                used = 0;
+            }
+            if (used != v.size() || v.empty()) throw std::runtime_error("pattern '" + v + "' not found");
+            return x;
+        };
+        if (s == "-o" || s == "--output") {
+            a.output = value();
+            a.have_output = true;
+        } else if (s == "-t" || s == "--tree") {
+            a.tree = value();
+        } else if (s == "-a" || s == "--aggression") {
+            a.aggression = number(value(), false);
+        } else if (s == "-i" || s == "--iterations") {
+            a.iterations = (int)number(value(), true);
+        } else if (s == "-s" || s == "--seed") {
+            a.seed = (int)number(value(), true);
+        } else if (s == "--device") {
+            a.device = (int)number(value(), true);
+        } else if (s == "-g" || s == "--greedy") {
+            a.greedy = true;
+        } else if (s == "-h" || s == "--help") {
+            std::cout << USAGE;
+            std::exit(0);
+        } else if (!s.empty() && s[0] == '-' && s.size() > 1 && !(s[1] >= '0' && s[1] <= '9')) {
+            throw std::runtime_error("Unknown argument: " + s);
+        } else if (!have_positional) {
+            a.cn_profile = s;
+            have_positional = true;
+        } else {
+            throw std::runtime_error("Maximum number of positional arguments exceeded");
+        }
+    }
+    if (!have_positional) throw std::runtime_error("cn_profile: 1 argument(s) expected. 0 provided.");
+    if (!a.have_output) throw std::runtime_error("-o: required.");
+    return a;
+}
+
+struct Gpu {
+    lzg_ctx* ctx = nullptr;
+    explicit Gpu(int device) {
+        int rc = lzg_init(device, &ctx);
+        if (rc != LZG_OK)  // no CPU fallback: the hot path exists on the GPU only
+            throw std::runtime_error(std::string("cannot open CUDA device: ") + lzg_status_string(rc) + ": " + lzg_last_error(nullptr));
+    }
+    ~Gpu() {
+        if (ctx) lzg_shutdown(ctx);
+    }
+    void check(int rc) const {
+        if (rc != LZG_OK) throw_lzg(ctx, rc);
+    }
+};
+
+// build_distance_matrix (src/lazac.cxx:63-95) through the C ABI; returns the device-resident profiles too.
+std::vector<int32_t> build_distance_matrix(const Gpu& gpu, const BreakpointSet& set, lzg_profiles** keep) {
+    const int n = (int)set.names.size();
+    lzg_profiles* p = nullptr;
+    gpu.check(lzg_profiles_upload(gpu.ctx, set.bp.data(), n, set.L, &p));
+    std::vector<int32_t> D((size_t)n * n);
+    log_info("Built 0 out of " + std::to_string(n) + " rows of distance matrix.");
+    gpu.check(lzg_distance_matrix(gpu.ctx, p, D.data()));
+    log_info("Finished building " + std::to_string(n) + " x " + std::to_string(n) + " distance matrix.");
+    if (keep) *keep = p;
+    else lzg_profiles_free(p);
+    return D;
+}
+
+// Integer rows formatted into one buffer per row (the reference streams value by value; bytes are identical).
+void write_matrix_txt(const std::string& path, const std::vector<std::string>& names, const std::vector<int32_t>& D) {
+    const size_t n = names.size();
+    std::ofstream out(path, std::ios::out);
+    out << n << "\n";
+    std::string line;
+    for (size_t i = 0; i < n; i++) {
+        line = names[i];
+        for (size_t j = 0; j < n; j++) {
+            line += ' ';
+            line += std::to_string(D[i * n + j]);
+        }
+        line += '\n';
+        out << line;
+    }
+}
+
+void write_matrix_csv(const std::string& path, const std::vector<std::string>& names, const std::vector<int32_t>& D) {
+    const size_t n = names.size();
+    std::ofstream out(path, std::ios::out);
+    std::string line;
+    for (size_t i = 0; i < n; i++) {
+        if (i != 0) line += ',';
+        line += names[i];
+    }
+    line += '\n';
+    out << line;
+    for (size_t i = 0; i < n; i++) {
+        line = names[i];
+        for (size_t j = 0; j < n; j++) {
+            line += ',';
+            line += std::to_string(D[i * n + j]);
+        }
+        line += '\n';
+        out << line;
+    }
+}
+
+void do_distance(const Args& a) {
+    const BreakpointSet set = to_breakpoint_set(read_cn_profiles(a.cn_profile));
+    Gpu gpu(a.device);
+    const std::vector<int32_t> D = build_distance_matrix(gpu, set, nullptr);
+    write_matrix_csv(a.output + "_dist_matrix.csv", set.names, D);
+    write_matrix_txt(a.output + "_dist_matrix.txt", set.names, D);
+}
+
+std::string slurp(const std::string& path) {
+    std::ifstream in(path);
+    std::stringstream buffer;
+    buffer << in.rdbuf();
+    return buffer.str();
+}
+
+// PREFIX_dist_matrix.txt -> names + integer matrix (helper subcommand `nj`)
+void read_matrix_txt(const std::string& path, std::vector<std::string>& names, std::vector<int32_t>& D) {
+    std::ifstream in(path);
+    if (!in) throw std::runtime_error("Cannot open file " + path);
+    size_t n = 0;
+    in >> n;
+    names.resize(n);
+    D.resize(n * n);
+    for (size_t i = 0; i < n; i++) {
+        in >> names[i];
+        for (size_t j = 0; j < n; j++) in >> D[i * n + j];
+    }
+    if (!in) throw std::runtime_error("Failed to parse distance matrix.");
+}
+
+struct Candidate {
+    GpuTree t;
+};
+
+std::string scores_text(const std::vector<int>& v) {  // pprint compact: [a, b, c]
+    std::string s = "[";
+    for (size_t i = 0; i < v.size(); i++) {
+        if (i) s += ", ";
+        s += std::to_string(v[i]);
+    }
+    return s + "]";
+}
+
+void do_nni(const Args& a) {
+    /* Load copy number profiles */
+    const BreakpointSet set = to_breakpoint_set(read_cn_profiles(a.cn_profile));
+    const int n_cells = (int)set.names.size();
+    Gpu gpu(a.device);
+    lzg_profiles* prof = nullptr;
+
+    /* Load/initialize seed tree */
+    NewickTree nt;
+    if (a.tree.empty()) {
+        log_info("No seed tree provided for NNI inference, building tree using neighbor joining.");
+        const std::vector<int32_t> D = build_distance_matrix(gpu, set, &prof);
+        write_matrix_txt(a.output + "_dist_matrix.txt", set.names, D);
+        const std::string output_tree = a.output + "_nj_tree.newick";
+        log_info("Building NJ tree from distance matrix using neighbor joining.");
+        for (const std::string& nm : set.names) {
+            // the reference's matrix parser takes a token that starts like a number for a distance
+            // (src/dmat.cxx:163-291) and then fails: keep that a clear error instead of a wrong tree
+            if (nm.empty() || (nm[0] >= '0' && nm[0] <= '9') || nm[0] == '.' || nm[0] == '+' || nm[0] == '-')
+                throw std::runtime_error("Failed to parse distance matrix.");
+        }
+        const SeedTree nj = neighbor_joining_clearcut(D, set.names, (uint32_t)a.seed);
+        log_info("Outputting NJ tree to file: " + output_tree);
+        {
+            std::ofstream out(output_tree, std::ios::out);
+            out << nj.newick();
+        }
+        nt = read_newick(slurp(output_tree));
+    } else {
+        log_info("Reading seed tree from file: " + a.tree);
+        nt = read_newick(slurp(a.tree));
+        gpu.check(lzg_profiles_upload(gpu.ctx, set.bp.data(), n_cells, set.L, &prof));
+    }
+
+    /* Creates rectilinear vertex data */
+    const int n = nt.size();
+    std::map<std::string, int> row_of;
+    for (int i = 0; i < n_cells; i++) row_of[set.names[i]] = i;
+    Topology topo;
+    topo.c0.assign(n, -1);
+    topo.c1.assign(n, -1);
+    std::vector<int32_t> leaf_row(n, -1);
+    for (int u = 0; u < n; u++) {
+        const auto& ch = nt.children[u];
+        if (ch.empty()) {
+            auto it = row_of.find(nt.name[u]);
+            if (it == row_of.end()) throw std::runtime_error("leaf '" + nt.name[u] + "' of the seed tree has no copy number profile");
+            leaf_row[u] = it->second;
+        } else if (ch.size() == 2) {
+            topo.set_children(u, ch[0], ch[1]);
+        } else {
+            throw std::logic_error("every child must have exactly two children");
+        }
+    }
+    topo.rebuild_parents();
+
+    lzg_tree* base = nullptr;
+    gpu.check(lzg_tree_create(gpu.ctx, prof, n, topo.c0.data(), topo.c1.data(), leaf_row.data(), &base));
+
+    std::ranlux48_base gen(a.seed);
+
+    /* Candidate tree set is obtained by randomly perturbing candidate trees. */
+    std::vector<Candidate> candidates;
+    const float aggressions[] = {0, 0.25, 0.50, 0.75, 1, 1.25, 1.5, 1.75};
+    for (float aggression : aggressions) {
+        Candidate c;
+        c.t.topo = stochastic_nni(topo, gen, aggression);
+        gpu.check(lzg_tree_clone(gpu.ctx, base, &c.t.h));
+        gpu.check(lzg_tree_set_topology(gpu.ctx, c.t.h, c.t.topo.c0.data(), c.t.topo.c1.data()));
+        candidates.push_back(c);
+    }
+    lzg_tree_free(base);
+
+    auto score_all = [&]() {
+        for (auto& c : candidates) {
+            int32_t s = 0;
+            gpu.check(lzg_tree_score(gpu.ctx, c.t.h, &s));
+            c.t.score = s;
+        }
+        std::sort(candidates.begin(), candidates.end(), [](const Candidate& x, const Candidate& y) { return x.t.score > y.t.score; });
+    };
+
+    std::string progress;  // nlohmann dump(): keys in alphabetical order, no spaces
+    bool any_progress = false;
+    ClimbStats stats;
+    int counter = 0, iteration = 0;
+    for (; counter < a.iterations; iteration++) {
+        score_all();
+        std::vector<int> scores;
+        for (auto& c : candidates) scores.push_back(c.t.score);
+
+        progress += any_progress ? "," : "[";
+        any_progress = true;
+        progress += "{\"iteration\":" + std::to_string(iteration) + ",\"scores\":[";
+        for (size_t i = 0; i < scores.size(); i++) progress += (i ? "," : "") + std::to_string(scores[i]);
+        progress += "]}";
+        log_info("Candidate tree scores @ iteration " + std::to_string(iteration) + ": " + scores_text(scores));
+
+        // Select and perturb candidate tree.
+        std::uniform_int_distribution<int> distrib(0, (int)candidates.size() - 1);
+        const int candidate_tree_idx = distrib(gen);
+
+        GpuTree work;
+        work.topo = candidates[candidate_tree_idx].t.topo;
+        work.score = candidates[candidate_tree_idx].t.score;
+        gpu.check(lzg_tree_clone(gpu.ctx, candidates[candidate_tree_idx].t.h, &work.h));
+        std::uniform_real_distribution<double> aggression_distrib(0, a.aggression);
+        // the reference perturbs a temporary and drops it (src/lazac.cxx:284): only the RNG draws matter
+        (void)stochastic_nni(work.topo, gen, (float)aggression_distrib(gen));
+
+        hill_climb(gpu.ctx, work, gen, a.greedy, &stats);
+        if (work.score < candidates[0].t.score) {
+            lzg_tree_free(candidates[0].t.h);
+            candidates[0].t = work;
+            log_info("Updated candidate tree set.");
+            counter = 0;
+            continue;
+        }
+        lzg_tree_free(work.h);
+        counter++;
+    }
+    score_all();
+    GpuTree& best = candidates.back().t;
+
+    /* ancestral_labeling (src/copy_number.cxx:187-225): labels on the GPU, pre-order renumbering here */
+    const int L = set.L;
+    std::vector<int32_t> labels((size_t)n * L), branch(n);
+    gpu.check(lzg_tree_ancestral(gpu.ctx, best.h, labels.data(), branch.data()));
+    std::vector<int> old_id, new_parent;
+    {
+        std::vector<std::pair<int, int>> st;  // (node, new id of its parent)
+        st.emplace_back(0, -1);
+        while (!st.empty()) {
+            const auto [u, p] = st.back();
+            st.pop_back();
+            const int k = (int)old_id.size();
+            old_id.push_back(u);
+            new_parent.push_back(p);
+            if (!best.topo.leaf(u)) {
+                st.emplace_back(best.topo.c0[u], k);
+                st.emplace_back(best.topo.c1[u], k);
+            }
+        }
+    }
+    std::vector<std::string> names(n);
+    std::vector<std::vector<int>> children(n);
+    std::vector<std::optional<int>> length(n);
+    for (int k = 0; k < n; k++) {
+        names[k] = nt.name[old_id[k]];
+        if (new_parent[k] >= 0) {
+            children[new_parent[k]].push_back(k);
+            length[k] = branch[old_id[k]];
+        }
+    }
+    for (auto& c : children) std::sort(c.begin(), c.end());
+
+    {
+        std::ofstream out(a.output + "_tree.newick", std::ios::out);
+        out << write_newick(names, children, length) << "\n";
+    }
+    {
+        std::ofstream out(a.output + "_info.json", std::ios::out);
+        out << (any_progress ? progress + "]" : std::string("null")) << "\n";
+    }
+    {
+        std::ofstream out(a.output + "_ancestral_cn_profile.csv", std::ios::out);
+        out << "node,chrom,allele,start,end,cn\n";
+        std::vector<int> bp(L), cn;
+        std::vector<GenomicBin> bins;
+        std::string block;
+        for (int k = 0; k < n; k++) {
+            const int32_t* row = labels.data() + (size_t)old_id[k] * L;
+            bp.assign(row, row + L);
+            copynumber_transform(bp, set.bins, cn, bins);
+            block.clear();
+            for (int i = 0; i < L; i++) {
+                block += names[k];
+                block += ',';
+                block += bins[i].chromosome;
+                block += ',';
+                block += bins[i].allele;
+                block += ',';
+                block += std::to_string(bins[i].start);
+                block += ',';
+                block += std::to_string(bins[i].end);
+                block += ',';
+                block += std::to_string(cn[i]);
+                block += '\n';
+            }
+            out << block;
+        }
+    }
+    log_info("search: " + std::to_string(stats.passes) + " neighbourhood passes, " + std::to_string(stats.candidates) +
+             " candidates scored, " + std::to_string(stats.moves) + " moves accepted");
+    for (auto& c : candidates) lzg_tree_free(c.t.h);
+    lzg_profiles_free(prof);
+}
+
+void do_nj(const Args& a) {  // helper: PREFIX_dist_matrix.txt -> Newick, no GPU
+    std::vector<std::string> names;
+    std::vector<int32_t> D;
+    read_matrix_txt(a.cn_profile, names, D);
+    std::ofstream out(a.output, std::ios::out);
+    out << neighbor_joining_clearcut(D, names, (uint32_t)a.seed).newick();
+}
+
+void do_bp(const Args& a) {  // helper: CSV -> names + breakpoint matrix (text), no GPU
+    const BreakpointSet set = to_breakpoint_set(read_cn_profiles(a.cn_profile));
+    std::ofstream out(a.output, std::ios::out);
+    out << set.names.size() << " " << set.L << "\n";
+    for (size_t i = 0; i < set.names.size(); i++) {
+        out << set.names[i];
+        for (int k = 0; k < set.L; k++) out << " " << set.bp[i * set.L + k];
+        out << "\n";
+    }
+    for (const auto& b : set.bins) out << b.chromosome << " " << b.allele << " " << b.start << " " << b.end << "\n";
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    Args a;
+    try {
+        a = parse_args(argc, argv);
+    } catch (const std::runtime_error& err) {
+        std::cerr << err.what() << std::endl << USAGE;
+        return 1;
+    }
+    try {
+        if (a.command == "nni") do_nni(a);
+        else if (a.command == "distance") do_distance(a);
+        else if (a.command == "nj") do_nj(a);
+        else do_bp(a);
+    } catch (const std::exception& e) {
+        // the reference lets these terminate the process (std::terminate); we report and exit non-zero
+        std::cerr << "lazac: " << e.what() << std::endl;
+        return 2;
+    }
+    return 0;
+}

@@ -1,0 +1,19 @@
+// host/seed_tree.hpp -- NJ seed tree (see seed_tree.cpp).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace lazac_host {
+
+struct SeedTree {
+    std::vector<int> left, right;        // -1 for leaves
+    std::vector<std::string> leaf_name;  // empty for internal nodes
+    int root = -1;
+    std::string newick() const;          // "(...);\n" exactly as the reference's PREFIX_nj_tree.newick
+};
+
+// D: n x n symmetric integer matrix, rows/columns in the order of `names`; seed = -s.
+SeedTree neighbor_joining_clearcut(const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed);
+
+}  // namespace lazac_host

@@ -107,6 +107,12 @@ int lzg_tree_score(lzg_ctx* ctx, lzg_tree* t, int32_t* root_score);
  * all_scores (optional, [n_moves]) receives every candidate's root score. */
 int lzg_nni_best(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int32_t greedy,
                  int32_t* best_index, int32_t* best_score, int32_t* all_scores);
+/* Score of the LAST candidate of the last lzg_nni_best on this tree (the tree's root score if it
+ * had no candidates).  The reference's greedy_nni leaves t[0].data.score at that value when a pass
+ * finds nothing (src/copy_number.cxx:351 sets it per candidate, :365-366 do not restore it), and
+ * hill_climb returns the tree like that, so do_nni's acceptance test (src/lazac.cxx:287) compares
+ * this number, not the tree's true score.  A host that wants the same search trajectory needs it. */
+int lzg_tree_last_candidate_score(const lzg_tree* t, int32_t* score);
 /* nni(t,u,w,v,z); unvisit(t,0,v); small_rectilinear(t,0) -- src/copy_number.cxx:397,408-409. */
 int lzg_tree_apply_nni(lzg_ctx* ctx, lzg_tree* t, int32_t u, int32_t w, int32_t v, int32_t z,
                        int32_t* root_score);

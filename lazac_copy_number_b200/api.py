@@ -253,3 +253,9 @@ class Tree:
         c, u = C.c_int64(0), C.c_int64(0)
         self.ctx.check(self.ctx.lib.lzg_tree_last_nni_traffic(self.h, C.byref(c), C.byref(u)))
         return c.value, u.value
+
+    def last_candidate_score(self):
+        """t[0].data.score as the reference's greedy_nni leaves it after a pass that finds nothing."""
+        s = C.c_int32(0)
+        self.ctx.check(self.ctx.lib.lzg_tree_last_candidate_score(self.h, C.byref(s)))
+        return s.value

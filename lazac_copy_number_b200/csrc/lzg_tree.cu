@@ -292,6 +292,7 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         t->last_v[i] = m[2];
         t->last_root_moves += m[0] == 0;
     }
+    t->last_cand_score = t->root_score;
     if (n_moves == 0) {
         *best_index = -1;
         *best_score = t->root_score;
@@ -362,6 +363,7 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     *best_index = ctx->h_pinned[LZG_CTL_BEST];
     *best_score = ctx->h_pinned[LZG_CTL_SCORE];
+    t->last_cand_score = ctx->h_pinned[LZG_CTL_LAST];
     return LZG_OK;
 }
 

@@ -29,6 +29,7 @@ struct lzg_tree {
     int32_t* d_pass = nullptr;        // per-pass upload: [path_off | order | moves]
     int32_t* d_cand = nullptr;        // [ctl (16) | cand_score (cand_cap)]
     std::vector<int32_t> last_v;      // v of every candidate of the last lzg_nni_best
+    int32_t last_cand_score = 0;      // score of the last candidate of that call (root score when it had none)
     int32_t last_root_moves = 0;      // candidates of that call whose u is the root (two merges, no UP)
     bool last_up_ran = false;         // that call had to rebuild the UP intervals
     int32_t up_nodes = 0;             // internal non-root nodes (UP rows written by an UP pass)

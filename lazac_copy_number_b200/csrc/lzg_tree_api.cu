@@ -246,6 +246,12 @@ int lzg_tree_last_nni_work(const lzg_tree* t, int64_t* merges, int64_t* bytes) {
     return LZG_OK;
 }
 
+int lzg_tree_last_candidate_score(const lzg_tree* t, int32_t* score) {
+    if (!t || !score) return LZG_ERR_ARG;
+    *score = t->last_cand_score;
+    return LZG_OK;
+}
+
 int lzg_tree_last_nni_traffic(const lzg_tree* t, int64_t* cand_bytes, int64_t* up_bytes) {
     if (!t) return LZG_ERR_ARG;
     const int64_t c = (int64_t)t->last_v.size(), L = t->L;

@@ -63,7 +63,7 @@ struct lzg_pass_args {
     int32_t* cand_score;  // [n_cand], zeroed
 };
 
-enum { LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_INTS = 16 };
+enum { LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_LAST = 4, LZG_CTL_INTS = 16 };
 
 __global__ void __launch_bounds__(256)
 k_nni_pass(const lzg_pass_args A) {
@@ -218,6 +218,7 @@ k_nni_pass(const lzg_pass_args A) {
     __syncthreads();
     if (tid == 0) {
         for (int k = 1; k < (blockDim.x + 31) / 32; k++) best = s_key[k] < best ? s_key[k] : best;
+        A.ctl[LZG_CTL_LAST] = __ldcg(A.cand_score + A.n_cand - 1);  // see lzg_tree_last_candidate_score
         if (best == ~0ull) {
             A.ctl[LZG_CTL_BEST] = -1;
             A.ctl[LZG_CTL_SCORE] = base;

@@ -158,6 +158,56 @@ def main():
                         bp=bp.astype(np.int8), D=D, child0=c0, child1=c1, score_before=np.int32(s0),
                         hc_seed=np.int32(7), hc_child0=h0, hc_child1=h1, hc_score=np.int32(s1),
                         gen_next_after=np.uint64(gen.next()))
+    # ---- CLI runs on a synthetic single-allele input (what the reference's loader reads) -------
+    cli2 = os.path.join(OUT, "synth_cli")
+    shutil.rmtree(cli2, ignore_errors=True)
+    os.makedirs(cli2)
+    prof = synth.make_profiles(30, 150, 1, seed=11)
+    src2 = os.path.join(cli2, "synth_cn_profile.csv")
+    synth.write_cn_csv(src2, prof)
+    shutil.copy(src, os.path.join(cli, "PTX008_cn_profile.csv"))   # inputs travel with the goldens
+    runs = {"full": ["-a", "1", "-i", "4", "-s", "3"], "greedy": ["-a", "1.5", "-i", "4", "-s", "5", "-g"]}
+    for tag, flags in runs.items():
+        run_ref_cli(["nni", src2] + flags + ["-o", os.path.join(cli2, tag)])
+    # a run from a given seed tree (-t): the NJ tree of the first run, other seed
+    run_ref_cli(["nni", src2, "-t", os.path.join(cli2, "full_nj_tree.newick"), "-a", "2", "-i", "3", "-s", "9",
+                 "-o", os.path.join(cli2, "fromtree")])
+    run_ref_cli(["distance", src2, "-o", os.path.join(cli2, "dist")])
+    with open(os.path.join(cli2, "COMMANDS.txt"), "w") as f:
+        f.write("lazac_ref nni synth_cn_profile.csv -a 1 -i 4 -s 3 -o full\n"
+                "lazac_ref nni synth_cn_profile.csv -a 1.5 -i 4 -s 5 -g -o greedy\n"
+                "lazac_ref nni synth_cn_profile.csv -t full_nj_tree.newick -a 2 -i 3 -s 9 -o fromtree\n"
+                "lazac_ref distance synth_cn_profile.csv -o dist\n"
+                "(ptx008_cli: lazac_ref distance / nni -a 2 -s 0 on PTX008_cn_profile.csv)\n")
+    # ---- CLI run on the leaves of one paper simulation (100 cells x 1000 loci): a long trajectory ----
+    cli3 = os.path.join(OUT, "sim_cli")
+    shutil.rmtree(cli3, ignore_errors=True)
+    os.makedirs(cli3)
+    import hashlib
+    leafset = set(leaves)
+    with tempfile.TemporaryDirectory() as tmp:
+        src3 = os.path.join(tmp, "sim.csv")
+        with gzip.open(sim + "_full_cn_profiles.csv.gz", "rt") as f, open(src3, "w") as o:
+            o.write("node,chrom,start,end,cn_a\n")
+            for r in csv.DictReader(f):
+                if r["node"] in leafset:  # leaves only; names must not look like numbers
+                    o.write("c%s,%s,%s,%s,%s\n" % (r["node"], r["chrom"], r["start"], r["end"], r["cn_a"]))
+        run_ref_cli(["nni", src3, "-a", "1", "-i", "2", "-s", "1", "-o", os.path.join(tmp, "sim")])
+        with open(src3, "rb") as f, gzip.GzipFile(os.path.join(cli3, "sim_cn_profile.csv.gz"), "wb", mtime=0) as o:
+            o.write(f.read())
+        hashes = {}
+        for fn in sorted(os.listdir(tmp)):
+            if fn == "sim.csv":
+                continue
+            with open(os.path.join(tmp, fn), "rb") as f:
+                data = f.read()
+            hashes[fn] = hashlib.sha256(data).hexdigest()
+            if len(data) < 100000:
+                shutil.copy(os.path.join(tmp, fn), os.path.join(cli3, fn))
+        with open(os.path.join(cli3, "SHA256.txt"), "w") as f:
+            f.write("# lazac_ref nni sim.csv -a 1 -i 2 -s 1 -o sim   (sim.csv = gunzip sim_cn_profile.csv.gz)\n")
+            for fn, h in hashes.items():
+                f.write("%s  %s\n" % (h, fn))
     total = sum(os.path.getsize(os.path.join(dp, f)) for dp, _, fs in os.walk(OUT) for f in fs)
     print("golden vectors written to %s (%.1f KiB)" % (OUT, total / 1024))
 

@@ -1,0 +1,56 @@
+"""CPU: the GPU-free parts of the C++ host (host/lazac): the Clearcut-exact NJ seed tree and the
+CSV -> breakpoint-vector ingest, against the reference CLI's own output files (tests/golden)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+LAZAC = os.path.join(ROOT, "host", "lazac")
+
+
+@pytest.fixture(scope="module")
+def lazac():
+    if not os.path.exists(LAZAC):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "lazac_copy_number_b200", "csrc"), "-j4"], check=True, stdout=subprocess.DEVNULL)
+        subprocess.run(["make", "-C", os.path.join(ROOT, "host")], check=True, stdout=subprocess.DEVNULL)
+    return LAZAC
+
+
+@pytest.mark.parametrize("matrix,seed,tree", [
+    ("ptx008_cli/PTX008_dist_matrix.txt", 0, "ptx008_cli/PTX008_nj_tree.newick"),
+    ("synth_cli/full_dist_matrix.txt", 3, "synth_cli/full_nj_tree.newick"),
+    ("synth_cli/greedy_dist_matrix.txt", 5, "synth_cli/greedy_nj_tree.newick"),
+])
+def test_nj_seed_tree_is_byte_identical(lazac, tmp_path, matrix, seed, tree):
+    out = tmp_path / "nj.newick"
+    subprocess.run([lazac, "nj", os.path.join(GOLD, matrix), "-s", str(seed), "-o", str(out)], check=True)
+    with open(os.path.join(GOLD, tree), "rb") as f:
+        assert out.read_bytes() == f.read()
+
+
+def test_breakpoint_ingest_matches_reference(lazac, tmp_path):
+    g = np.load(os.path.join(GOLD, "ptx008.npz"))
+    out = tmp_path / "bp.txt"
+    subprocess.run([lazac, "bp", os.path.join(GOLD, "ptx008_cli", "PTX008_cn_profile.csv"), "-o", str(out)], check=True)
+    lines = out.read_text().split("\n")
+    n, L = (int(x) for x in lines[0].split())
+    assert (n, L) == g["bp"].shape
+    for i in range(n):
+        tok = lines[1 + i].split()
+        assert tok[0] == str(g["names"][i])
+        assert [int(x) for x in tok[1:]] == list(g["bp"][i])
+    bins = [ln.split() for ln in lines[1 + n:1 + n + L]]
+    assert [[int(b[0]), int(b[2]), int(b[3])] for b in bins] == g["bins"].tolist()
+    assert all(b[1] == "cn_a" for b in bins)
+
+
+def test_usage_errors(lazac):
+    r = subprocess.run([lazac, "nni", "x.csv"], capture_output=True, text=True)
+    assert r.returncode == 1 and "-o: required." in r.stderr
+    r = subprocess.run([lazac, "frobnicate"], capture_output=True, text=True)
+    assert r.returncode == 1
+    r = subprocess.run([lazac, "bp", "/nonexistent.csv", "-o", "/dev/null"], capture_output=True, text=True)
+    assert r.returncode == 2 and "Cannot open" in r.stderr
