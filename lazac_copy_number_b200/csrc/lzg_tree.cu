@@ -10,6 +10,9 @@
 #include "lzg_tree.cuh"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace {
@@ -217,41 +220,66 @@ int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t) {
     return LZG_OK;
 }
 
-// Heavy-path decomposition of the internal non-root nodes, paths listed parents-first (a path's
-// head hangs off a node of an earlier path or off the root).  order[] = nodes path after path,
-// path_off[] = path boundaries.  Returns the number of paths.
-static int build_up_paths(const lzg_tree* t, int32_t* order, int32_t* path_off, int* n_order) {
+// Internal nodes in the subtree of every node (0 for leaves): the weight the heavy-path
+// decomposition uses.  Rebuilt from scratch after a topology replacement; an accepted NNI
+// (u, w, v, z) only changes the entry of v (lzg_tree_apply), so it is kept up to date in O(1).
+static void rebuild_isize(lzg_tree* t) {
     const int n = t->n_nodes;
-    std::vector<int32_t> size(n, 0), pre;
+    std::vector<int32_t>& pre = t->tmp_pre;
+    t->isize.assign(n, 0);
+    pre.clear();
     pre.reserve(n);
     pre.push_back(0);
     for (size_t i = 0; i < pre.size(); i++) {  // BFS order: parents before children
-        int a = pre[i];
+        const int a = pre[i];
         if (t->child0[a] >= 0) {
             pre.push_back(t->child0[a]);
             pre.push_back(t->child1[a]);
         }
     }
-    for (int i = n - 1; i >= 0; i--) {  // internal nodes below (and including) a
-        int a = pre[i];
-        if (t->child0[a] >= 0) size[a] = 1 + size[t->child0[a]] + size[t->child1[a]];
+    for (int i = n - 1; i >= 0; i--) {
+        const int a = pre[i];
+        if (t->child0[a] >= 0) t->isize[a] = 1 + t->isize[t->child0[a]] + t->isize[t->child1[a]];
     }
+    t->isize_valid = true;
+}
+
+// Heavy-path decomposition of the internal non-root nodes, paths listed parents-first (a path's
+// head hangs off a node of an earlier path or off the root).  order[] = {node, sibling} path
+// after path, rec[] = {first index into order, length, parent of the head, sibling of the head}.
+// Also fills t->up_rank (position of a node in order, -1 for the root and the leaves).
+static int build_up_paths(lzg_tree* t, int2* order, int4* rec, int* n_order) {
+    const int n = t->n_nodes;
+    if (!t->isize_valid) rebuild_isize(t);
+    const int32_t* size = t->isize.data();
+    const int32_t *c0a = t->child0.data(), *c1a = t->child1.data();
+    t->up_rank.assign(n, -1);
+    int32_t* rank = t->up_rank.data();
     int cnt = 0, paths = 0;
-    std::vector<int32_t> heads;
-    if (t->child0[0] >= 0)
-        for (int c : {t->child0[0], t->child1[0]})
-            if (size[c] > 0) heads.push_back(c);
-    for (size_t h = 0; h < heads.size(); h++) {
-        path_off[paths++] = cnt;
-        for (int a = heads[h]; a >= 0;) {
-            order[cnt++] = a;
-            const int c0 = t->child0[a], c1 = t->child1[a];
-            const int heavy = size[c0] >= size[c1] ? c0 : c1, light = heavy == c0 ? c1 : c0;
-            if (size[light] > 0) heads.push_back(light);
-            a = size[heavy] > 0 ? heavy : -1;
-        }
+    std::vector<int32_t>& heads = t->tmp_heads;  // (head, its parent, its sibling) triples, a queue
+    heads.clear();
+    heads.reserve(3 * (size_t)n / 2 + 6);
+    if (c0a[0] >= 0) {
+        const int a = c0a[0], b = c1a[0];
+        if (size[a] > 0) heads.insert(heads.end(), {a, 0, b});
+        if (size[b] > 0) heads.insert(heads.end(), {b, 0, a});
     }
-    path_off[paths] = cnt;
+    for (size_t h = 0; h < heads.size(); h += 3) {
+        const int first = cnt;
+        int a = heads[h], sib = heads[h + 2];
+        while (true) {
+            rank[a] = cnt;
+            order[cnt++] = make_int2(a, sib);
+            const int c0 = c0a[a], c1 = c1a[a];
+            const bool h0 = size[c0] >= size[c1];
+            const int heavy = h0 ? c0 : c1, light = h0 ? c1 : c0;
+            if (size[light] > 0) heads.insert(heads.end(), {light, a, heavy});
+            if (size[heavy] == 0) break;
+            a = heavy;
+            sib = light;
+        }
+        rec[paths++] = make_int4(first, cnt - first, heads[h + 1], heads[h + 2]);
+    }
     *n_order = cnt;
     return paths;
 }
@@ -264,8 +292,8 @@ static int ensure_cand_buffers(lzg_ctx* ctx, lzg_tree* t, int n_moves) {
     t->d_pass = nullptr;
     t->d_cand = nullptr;
     t->cand_cap = 0;
-    // d_pass: [path_off | order | moves] packed per call; d_cand: [ctl (16) | cand_score (cap)]
-    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_pass, sizeof(int32_t) * ((size_t)2 * t->n_nodes + 8 + 4 * (size_t)cap)));
+    // d_pass: [path records | order | items] packed per call; d_cand: [ctl (16) | cand_score (cap)]
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_pass, sizeof(int32_t) * ((size_t)6 * t->n_nodes + 12 + 8 * (size_t)cap)));
     LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_cand, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)cap)));
     t->cand_cap = cap;
     return LZG_OK;
@@ -280,19 +308,16 @@ static bool is_move(const lzg_tree* t, int u, int w, int v, int z) {
     return true;
 }
 
-// One neighbourhood pass: one staged H2D copy, one memset, one launch (k_nni_pass), one read-back.
+// One neighbourhood pass.  The UP pass is launched first (it needs the path tables only), so the
+// host's validation and packing of the move list run while the GPU builds the UP intervals; then
+// items, argmin and one 64-byte read-back.
 int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
                         int32_t* best_index, int32_t* best_score, int32_t* all_scores) {
-    t->last_v.resize(n_moves);
-    t->last_root_moves = 0;
+    const auto t_enter = std::chrono::steady_clock::now();
     t->last_up_ran = false;
-    for (int i = 0; i < n_moves; i++) {
-        const int32_t* m = moves + 4 * (size_t)i;
-        if (!is_move(t, m[0], m[1], m[2], m[3])) return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "candidate is not an NNI move of this topology");
-        t->last_v[i] = m[2];
-        t->last_root_moves += m[0] == 0;
-    }
     t->last_cand_score = t->root_score;
+    t->last_items = t->last_root_items = 0;
+    t->last_v.resize(n_moves);
     if (n_moves == 0) {
         *best_index = -1;
         *best_score = t->root_score;
@@ -312,39 +337,24 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         t->up_valid = false;
     }
     // staging (pinned; every public entry point ends with a synchronising read-back, so the area is
-    // free again when the next call fills it): [result (16) | path_off | order | moves]
-    rc = lzg_ensure_pinned(ctx, 16 + (size_t)2 * n + 8 + 4 * (size_t)n_moves);
+    // free again when the next call fills it): [result (16) | path records + order (6 n + 8) | items]
+    rc = lzg_ensure_pinned(ctx, 16 + (size_t)6 * n + 12 + 8 * (size_t)n_moves);
     if (rc != LZG_OK) return rc;
     int32_t* stage = ctx->h_pinned + 16;
-    int n_paths = 0, n_order = 0;
-    if (!t->up_valid) {
-        n_paths = build_up_paths(t, stage + n + 2, stage, &n_order);
-        // compact: path_off has n_paths + 1 entries; move order right behind it
-        memmove(stage + n_paths + 1, stage + n + 2, sizeof(int32_t) * n_order);
-        t->up_nodes = n_order;
-        t->up_paths = n_paths;
-        t->epoch++;
-        t->last_up_ran = true;
-    } else {
-        stage[0] = 0;
+    const size_t o_items = ((size_t)6 * n + 8 + 3) / 4 * 4;  // 16-byte aligned, fixed offset of the items in the staging area and in d_pass
+    const int dbg = getenv("LZG_PASS_DEBUG") ? atoi(getenv("LZG_PASS_DEBUG")) : 0;
+    const bool trace = (dbg & 4) != 0;  // LZG_PASS_DEBUG=4: host preparation / kernel time of every pass on stderr
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (trace) {
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaEventRecord(e0, ctx->stream);
     }
-    const size_t o_order = (size_t)n_paths + 1, o_moves = (o_order + n_order + 3) / 4 * 4;  // int4 loads of the moves
-    memcpy(stage + o_moves, moves, sizeof(int32_t) * 4 * (size_t)n_moves);
-    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass, stage, sizeof(int32_t) * (o_moves + 4 * (size_t)n_moves), cudaMemcpyHostToDevice, ctx->stream));
-    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)n_moves), ctx->stream));
-    lzg_pass_args A;
-    A.path_off = t->d_pass;
-    A.order = t->d_pass + o_order;
-    A.moves = t->d_pass + o_moves;
-    A.n_paths = n_paths;
+    lzg_pass_args A{};
     A.n_cand = n_moves;
     A.groups = groups;
     A.l_pad = t->l_pad;
-    A.epoch = t->epoch;
     A.greedy = greedy;
-    A.child0 = t->d_child0;
-    A.child1 = t->d_child1;
-    A.up = t->d_up;
     A.start = t->d_start;
     A.end = t->d_end;
     A.ustart = t->d_ustart;
@@ -353,10 +363,92 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     A.ready = t->d_ready;
     A.ctl = t->d_cand;
     A.cand_score = t->d_cand + LZG_CTL_INTS;
-    const long long items = ((long long)n_paths + n_moves) * groups;
-    k_nni_pass<<<(unsigned)items, threads, 0, ctx->stream>>>(A);
+    A.items = reinterpret_cast<const int4*>(t->d_pass + o_items);
+    A.n_items = 0;
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)n_moves), ctx->stream));
+    int n_paths = 0, n_order = 0;
+    if (!t->up_valid) {
+        // records are written at the front, the order behind the worst-case record area, then compacted
+        n_paths = build_up_paths(t, reinterpret_cast<int2*>(stage + 4 * (size_t)n), reinterpret_cast<int4*>(stage), &n_order);
+        memmove(stage + 4 * (size_t)n_paths, stage + 4 * (size_t)n, sizeof(int2) * n_order);
+        t->up_nodes = n_order;
+        t->up_paths = n_paths;
+        t->epoch++;
+        t->last_up_ran = true;
+        const size_t ints = 4 * (size_t)n_paths + 2 * (size_t)n_order;
+        if (n_paths > 0) {
+            LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass, stage, sizeof(int32_t) * ints, cudaMemcpyHostToDevice, ctx->stream));
+            A.path_rec = reinterpret_cast<const int4*>(t->d_pass);
+            A.order = reinterpret_cast<const int2*>(t->d_pass + 4 * (size_t)n_paths);
+            A.n_paths = n_paths;
+            A.epoch = t->epoch;
+            k_up_pass<<<n_paths * groups, threads, 0, ctx->stream>>>(A);
+            LZG_LAUNCH_CHECK(ctx);
+        }
+        t->up_valid = true;
+    }
+    const auto t_up = std::chrono::steady_clock::now();
+    // items: the two candidates of an edge (u, v) as one record, sorted by the walker rank of u so
+    // that neighbouring CTAs share rows (both items under one u read DOWN(u) and UP(u))
+    int n_items = 0;
+    {
+        std::vector<int32_t>& raw = t->tmp_items;
+        std::vector<int32_t>& cnt = t->tmp_count;
+        raw.resize(8 * (size_t)n_moves);
+        cnt.assign((size_t)t->up_nodes + 2, 0);
+        for (int i = 0; i < n_moves;) {
+            const int32_t* m = moves + 4 * (size_t)i;
+            const int u = m[0], w = m[1], v = m[2], z = m[3];
+            if (!is_move(t, u, w, v, z)) {
+                cudaStreamSynchronize(ctx->stream);
+                return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "candidate is not an NNI move of this topology");
+            }
+            t->last_v[i] = v;
+            const int a = t->child0[v], b = t->child1[v];
+            int ia = z == a ? i : -1, ib = z == b ? i : -1, used = 1;
+            if (i + 1 < n_moves && m[4] == u && m[5] == w && m[6] == v && m[7] != z && t->parent[m[7]] == v) {
+                (m[7] == a ? ia : ib) = i + 1;
+                t->last_v[i + 1] = v;
+                used = 2;
+            }
+            int32_t* r = raw.data() + 8 * (size_t)n_items++;
+            r[0] = u, r[1] = w, r[2] = v, r[3] = a, r[4] = b, r[5] = ia, r[6] = ib, r[7] = 0;
+            cnt[t->up_rank[u] + 2]++;
+            t->last_root_items += u == 0;
+            i += used;
+        }
+        for (size_t k = 1; k < cnt.size(); k++) cnt[k] += cnt[k - 1];
+        int32_t* dst = stage + o_items;
+        for (int k = 0; k < n_items; k++) {
+            const int32_t* r = raw.data() + 8 * (size_t)k;
+            memcpy(dst + 8 * (size_t)cnt[t->up_rank[r[0]] + 1]++, r, sizeof(int32_t) * 8);
+        }
+        t->last_items = n_items;
+    }
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass + o_items, stage + o_items, sizeof(int32_t) * 8 * (size_t)n_items, cudaMemcpyHostToDevice, ctx->stream));
+    A.n_items = n_items;
+    const auto t_launch = std::chrono::steady_clock::now();
+    if (dbg & 8) {  // 8 positions per thread, five CTAs per SM
+        const int gi = (t->l_pad + 256 * 8 - 1) / (256 * 8);
+        k_nni_items<8><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
+    } else {
+        const int gi = (t->l_pad + 256 * 16 - 1) / (256 * 16);
+        k_nni_items<16><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
+    }
     LZG_LAUNCH_CHECK(ctx);
-    t->up_valid = true;
+    k_nni_argmin<<<1, 1024, 0, ctx->stream>>>(A);
+    LZG_LAUNCH_CHECK(ctx);
+    if (trace) {
+        cudaEventRecord(e1, ctx->stream);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        fprintf(stderr, "[lzg pass] moves %d items %d paths %d: host %.1f us to the UP launch + %.1f us to the items launch, stream %.1f us\n", n_moves,
+                n_items, n_paths, std::chrono::duration<double, std::micro>(t_up - t_enter).count(),
+                std::chrono::duration<double, std::micro>(t_launch - t_up).count(), ms * 1e3);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+    }
     LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_cand, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     if (all_scores)
         LZG_CUDA(ctx, cudaMemcpyAsync(all_scores, t->d_cand + LZG_CTL_INTS, sizeof(int32_t) * (size_t)n_moves, cudaMemcpyDeviceToHost, ctx->stream));
@@ -381,6 +473,7 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     t->parent[w] = v;
     t->parent[z] = u;
     t->up_valid = false;
+    if (t->isize_valid) t->isize[v] = 1 + t->isize[w] + t->isize[y];  // u's subtree keeps its node set
     LZG_CUDA(ctx, cudaMemsetAsync(t->d_ctl, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)depth + 1), ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
     k_apply_move<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_score, t->d_cost, t->d_ctl,

@@ -30,10 +30,15 @@ struct lzg_tree {
     int32_t* d_cand = nullptr;        // [ctl (16) | cand_score (cand_cap)]
     std::vector<int32_t> last_v;      // v of every candidate of the last lzg_nni_best
     int32_t last_cand_score = 0;      // score of the last candidate of that call (root score when it had none)
-    int32_t last_root_moves = 0;      // candidates of that call whose u is the root (two merges, no UP)
+    int32_t last_items = 0;           // work items of that call (an item = the two candidates of one edge (u, v))
+    int32_t last_root_items = 0;      // items whose u is the root (no UP / DOWN(u) rows: 6 L instead of 10 L bytes)
     bool last_up_ran = false;         // that call had to rebuild the UP intervals
     int32_t up_nodes = 0;             // internal non-root nodes (UP rows written by an UP pass)
     int32_t up_paths = 0;             // heavy paths they form
+    std::vector<int32_t> up_rank;     // position of a node in the walker order (-1: root, leaves); valid while up_valid
+    std::vector<int32_t> isize;       // internal nodes in the subtree of every node (heavy-path weights)
+    bool isize_valid = false;         // cleared by lzg_tree_set_topology; kept current by lzg_tree_apply
+    std::vector<int32_t> tmp_pre, tmp_heads, tmp_items, tmp_count;  // per-pass host scratch, kept to avoid reallocation
 };
 
 int lzg_tree_upload_topology(lzg_ctx* ctx, lzg_tree* t);

@@ -169,6 +169,7 @@ int lzg_tree_set_topology(lzg_ctx* ctx, lzg_tree* t, const int32_t* child0, cons
     }
     t->scored = false;
     t->up_valid = false;
+    t->isize_valid = false;
     return lzg_tree_upload_topology(ctx, t);
 }
 
@@ -254,8 +255,8 @@ int lzg_tree_last_candidate_score(const lzg_tree* t, int32_t* score) {
 
 int lzg_tree_last_nni_traffic(const lzg_tree* t, int64_t* cand_bytes, int64_t* up_bytes) {
     if (!t) return LZG_ERR_ARG;
-    const int64_t c = (int64_t)t->last_v.size(), L = t->L;
-    if (cand_bytes) *cand_bytes = (c * 10 - (int64_t)t->last_root_moves * 4) * L;
+    const int64_t c = (int64_t)t->last_items, L = t->L;  // one item = both candidates of an edge (u, v)
+    if (cand_bytes) *cand_bytes = (c * 10 - (int64_t)t->last_root_items * 4) * L;
     if (up_bytes) *up_bytes = t->last_up_ran ? ((int64_t)t->up_nodes * 4 + (int64_t)t->up_paths * 2) * L : 0;
     return LZG_OK;
 }

@@ -1,0 +1,268 @@
+// lzg_tree_pass.cuh -- one NNI neighbourhood pass: k_up_pass (UP intervals, heavy-path walkers),
+// k_nni_items (both candidates of every edge (u, v) in one work item), k_nni_argmin (the
+// reference's choice).  Included by lzg_tree_nni.cuh inside its anonymous namespace.
+//
+// Measured on B200 (profiles/README.md, round 1): the scoring arithmetic is ~350 integer
+// instructions per 16 positions of an item, so the pass is bound by instruction issue and
+// round-trip latency rather than by HBM; a persistent producer/consumer ring fed by bulk async
+// copies (tried: one producer warp could not describe entries fast enough, and 148 walkers at a
+// time starved the dependency chains) lost to plain short-lived CTAs at high occupancy.  So:
+//  * k_up_pass: one CTA per (heavy path, chunk group), drawn from a ticket counter in
+//    parents-first order; the running UP interval stays in registers, sibling rows are
+//    prefetched two nodes ahead, every node's UP row is published with a per-(node, group) epoch
+//    flag (stores, bar.sync, st.release by one thread / ld.acquire by one thread, bar.sync, ld.cg).
+//    Cross-CTA hops are light edges only (<= log2 n on any root-leaf path).  A ticket is drawn
+//    by a running CTA and only waits for smaller tickets: no deadlock.
+//  * k_nni_items: one CTA per (item, chunk group) behind the kernel boundary -- no flags, no
+//    tickets: the item record, then all ten row loads at once, the arithmetic on u16x2 lanes,
+//    per-warp partial scores added to cand_score with fire-and-forget REDs.
+//  * k_nni_argmin: min (score, index) over the candidates below the current root score
+//    (greedy: min index) -- the reference's strict '<', first-wins rule (src/copy_number.cxx:353-362).
+#pragma once
+
+// even bytes / odd bytes of a word as u16x2 lanes (the merge is per position, so any fixed lane
+// assignment works; the even half is a full-rate LOP3, the odd half one PRMT)
+__device__ __forceinline__ void split2(uint32_t x, uint32_t (&o)[2]) {
+    o[0] = x & 0x00ff00ffu;
+    o[1] = __byte_perm(x, 0, 0x4341);
+}
+
+struct lzg_pass_args {
+    const int4* path_rec;  // [n_paths] {first index into order, nodes on the path, parent of the head, sibling of the head}
+    const int2* order;     // {node, its sibling}: internal non-root nodes, heavy paths back to back, parents-first
+    const int4* items;     // [n_items][2]: {u, w, v, a}, {b, index of the candidate z = a, index of the candidate z = b, 0}
+    int n_paths, n_items, n_cand, groups, l_pad, epoch, greedy;
+    const uint8_t *start, *end;
+    uint8_t *ustart, *uend;
+    const int32_t* score;
+    int* ready;           // [n_nodes][groups] epoch flags of the UP rows
+    int* ctl;             // [0] ticket, [2] best index, [3] best score, [4] last candidate's score
+    int32_t* cand_score;  // [n_cand], zeroed
+};
+
+enum { LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_LAST = 4, LZG_CTL_INTS = 16 };
+
+// One heavy path x one chunk group: UP(a) for every node a of the path, top-down, running
+// interval in registers; sibling intervals are prefetched two nodes ahead.
+__device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int tid) {
+    const int g = item % A.groups, p = item / A.groups;
+    const int chunk = g * blockDim.x + tid;
+    const bool active = chunk * 16 < A.l_pad;
+    const size_t off = (size_t)chunk * 16;
+    const int l_pad = A.l_pad;
+    const int4 pr = A.path_rec[p];
+    const int k0 = pr.x, k1 = pr.x + pr.y;
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    uint4 ss = z4, se = z4, n1s = z4, n1e = z4, n2s = z4, n2e = z4;
+    if (active) {
+        ss = ldg16(A.start, (size_t)pr.w * l_pad + off);
+        se = ldg16(A.end, (size_t)pr.w * l_pad + off);
+    }
+    int2 cur = A.order[k0];
+    int2 nx1 = k0 + 1 < k1 ? A.order[k0 + 1] : make_int2(0, 0);
+    int2 nx2 = k0 + 2 < k1 ? A.order[k0 + 2] : make_int2(0, 0);
+    if (active && k0 + 1 < k1) {
+        n1s = ldg16(A.start, (size_t)nx1.y * l_pad + off);
+        n1e = ldg16(A.end, (size_t)nx1.y * l_pad + off);
+    }
+    iv16 acc;
+    uint32_t os[8], oe[8];
+    if (pr.z != 0) {
+        if (tid == 0) {
+            const int* flag = A.ready + (size_t)pr.z * A.groups + g;
+            while (ld_acquire(flag) != A.epoch) __nanosleep(32);
+        }
+        __syncthreads();
+        if (active) {
+            widen(ldcg16(A.ustart, (size_t)pr.z * l_pad + off), acc.s);
+            widen(ldcg16(A.uend, (size_t)pr.z * l_pad + off), acc.e);
+            widen(ss, os);
+            widen(se, oe);
+            merge16(acc, os, oe);
+        }
+    } else if (active) {
+        widen(ss, acc.s);
+        widen(se, acc.e);
+    }
+    for (int k = k0;; k++) {
+        int2 nx3 = make_int2(0, 0);
+        if (k + 2 < k1) {
+            if (active) {
+                n2s = ldg16(A.start, (size_t)nx2.y * l_pad + off);
+                n2e = ldg16(A.end, (size_t)nx2.y * l_pad + off);
+            }
+            if (k + 3 < k1) nx3 = A.order[k + 3];
+        }
+        if (active) {
+            *reinterpret_cast<uint4*>(A.ustart + (size_t)cur.x * l_pad + off) = narrow(acc.s);
+            *reinterpret_cast<uint4*>(A.uend + (size_t)cur.x * l_pad + off) = narrow(acc.e);
+        }
+        __syncthreads();
+        if (tid == 0) st_release(A.ready + (size_t)cur.x * A.groups + g, A.epoch);
+        if (k + 1 >= k1) break;
+        if (active) {
+            widen(n1s, os);
+            widen(n1e, oe);
+            merge16(acc, os, oe);
+        }
+        cur = nx1;
+        nx1 = nx2;
+        nx2 = nx3;
+        n1s = n2s;
+        n1e = n2e;
+    }
+}
+
+
+__global__ void __launch_bounds__(256)
+k_up_pass(const lzg_pass_args A) {
+    __shared__ int s_item;
+    if (threadIdx.x == 0) s_item = atomicAdd(A.ctl + LZG_CTL_TICKET, 1);
+    __syncthreads();
+    walk_path(A, s_item, threadIdx.x);
+}
+
+// ---- items -------------------------------------------------------------------------------------------
+template <int CPT>
+struct lzg_vec {  // a thread's CPT positions of one row
+    uint32_t w[CPT / 4];
+};
+template <int CPT>
+__device__ __forceinline__ lzg_vec<CPT> ldg_vec(const uint8_t* p) {
+    lzg_vec<CPT> v;
+    if (CPT == 16) {
+        const uint4 x = __ldg(reinterpret_cast<const uint4*>(p));
+        v.w[0] = x.x, v.w[1] = x.y, v.w[CPT / 4 - 2] = x.z, v.w[CPT / 4 - 1] = x.w;
+    } else {
+        const uint2 x = __ldg(reinterpret_cast<const uint2*>(p));
+        v.w[0] = x.x, v.w[1] = x.y;
+    }
+    return v;
+}
+
+__device__ __forceinline__ int32_t warp_sum_i(int32_t v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Both candidates of an edge (u, v) on CPT positions: cost parts of z = a and z = b, each already
+// net of c0 (the current tree re-rooted above u).  rows: w, a, b[, DOWN(u), UP(u)] x {start, end}.
+template <int CPT, bool HAS_UP>
+__device__ __forceinline__ void score_pair(const lzg_pass_args& A, int u, int w, int a, int b, size_t off, int32_t& pA, int32_t& pB) {
+    const size_t lp = (size_t)A.l_pad;
+    lzg_vec<CPT> row[HAS_UP ? 10 : 6];
+    row[0] = ldg_vec<CPT>(A.start + w * lp + off), row[1] = ldg_vec<CPT>(A.end + w * lp + off);
+    row[2] = ldg_vec<CPT>(A.start + a * lp + off), row[3] = ldg_vec<CPT>(A.end + a * lp + off);
+    row[4] = ldg_vec<CPT>(A.start + b * lp + off), row[5] = ldg_vec<CPT>(A.end + b * lp + off);
+    if (HAS_UP) {
+        row[6] = ldg_vec<CPT>(A.start + u * lp + off), row[7] = ldg_vec<CPT>(A.end + u * lp + off);
+        row[8] = ldg_vec<CPT>(A.ustart + u * lp + off), row[9] = ldg_vec<CPT>(A.uend + u * lp + off);
+    }
+    uint32_t cA = 0, cB = 0, c0 = 0;
+#pragma unroll
+    for (int q = 0; q < CPT / 4; q++) {  // four positions (one word of every row) at a time: short live ranges
+        uint32_t ws[2], we[2], as[2], ae[2], bs[2], be[2], ds[2], de[2], us[2], ue[2];
+        split2(row[0].w[q], ws), split2(row[1].w[q], we);
+        split2(row[2].w[q], as), split2(row[3].w[q], ae);
+        split2(row[4].w[q], bs), split2(row[5].w[q], be);
+        if (HAS_UP) {
+            split2(row[6].w[q], ds), split2(row[7].w[q], de);
+            split2(row[8].w[q], us), split2(row[9].w[q], ue);
+        }
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            {   // z = a: v keeps b -- merge(w, b), then a, then UP(u)
+                const uint32_t lo1 = __vmaxu2(ws[h], bs[h]), hi1 = __vminu2(we[h], be[h]);
+                const uint32_t s1 = __vminu2(lo1, hi1), e1 = __vmaxu2(lo1, hi1);
+                const uint32_t lo2 = __vmaxu2(s1, as[h]), hi2 = __vminu2(e1, ae[h]);
+                const uint32_t s2 = __vminu2(lo2, hi2);
+                cA = cA + lo1 - s1;
+                cA = cA + lo2 - s2;
+                if (HAS_UP) {
+                    const uint32_t e2 = __vmaxu2(lo2, hi2);
+                    const uint32_t lo3 = __vmaxu2(s2, us[h]), hi3 = __vminu2(e2, ue[h]);
+                    cA = cA + lo3 - __vminu2(lo3, hi3);
+                }
+            }
+            {   // z = b: v keeps a
+                const uint32_t lo1 = __vmaxu2(ws[h], as[h]), hi1 = __vminu2(we[h], ae[h]);
+                const uint32_t s1 = __vminu2(lo1, hi1), e1 = __vmaxu2(lo1, hi1);
+                const uint32_t lo2 = __vmaxu2(s1, bs[h]), hi2 = __vminu2(e1, be[h]);
+                const uint32_t s2 = __vminu2(lo2, hi2);
+                cB = cB + lo1 - s1;
+                cB = cB + lo2 - s2;
+                if (HAS_UP) {
+                    const uint32_t e2 = __vmaxu2(lo2, hi2);
+                    const uint32_t lo3 = __vmaxu2(s2, us[h]), hi3 = __vminu2(e2, ue[h]);
+                    cB = cB + lo3 - __vminu2(lo3, hi3);
+                }
+            }
+            if (HAS_UP) {  // the current tree re-rooted above u
+                const uint32_t lo3 = __vmaxu2(ds[h], us[h]), hi3 = __vminu2(de[h], ue[h]);
+                c0 = c0 + lo3 - __vminu2(lo3, hi3);
+            }
+        }
+    }
+    // per u16 lane: <= 3 merges x 4 words x 254 -- no carry between the lanes
+    const int32_t z = (int32_t)((c0 & 0xffffu) + (c0 >> 16));
+    pA = (int32_t)((cA & 0xffffu) + (cA >> 16)) - z;
+    pB = (int32_t)((cB & 0xffffu) + (cB >> 16)) - z;
+}
+
+template <int CPT>
+__global__ void __launch_bounds__(256, CPT == 16 ? 3 : 5)
+k_nni_items(const lzg_pass_args A, int groups_i) {
+    const int tid = threadIdx.x;
+    const int it = blockIdx.x / groups_i, g = blockIdx.x % groups_i;
+    const int4 i0 = __ldg(A.items + 2 * it), i1 = __ldg(A.items + 2 * it + 1);
+    const int u = i0.x, w = i0.y, a = i0.w, b = i1.x, ia = i1.y, ib = i1.z;
+    const size_t off = ((size_t)g * 256 + tid) * CPT;
+    int32_t base = 0;
+    if (tid == 0 && g == 0) base = A.score[w] + A.score[a] + A.score[b] + (u ? A.score[0] - A.score[u] : 0);
+    int32_t pA = 0, pB = 0;
+    if (off < (size_t)A.l_pad) {
+        if (u) score_pair<CPT, true>(A, u, w, a, b, off, pA, pB);
+        else score_pair<CPT, false>(A, u, w, a, b, off, pA, pB);
+    }
+    pA = warp_sum_i(pA) + base;
+    pB = warp_sum_i(pB) + base;
+    if ((tid & 31) == 0) {
+        if (ia >= 0 && pA) atomicAdd(A.cand_score + ia, pA);
+        if (ib >= 0 && pB) atomicAdd(A.cand_score + ib, pB);
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+k_nni_argmin(const lzg_pass_args A) {
+    __shared__ unsigned long long s_key[32];
+    const int tid = threadIdx.x;
+    const int32_t root = A.score[0];
+    unsigned long long best = ~0ull;
+    for (int i = tid; i < A.n_cand; i += blockDim.x) {
+        const int32_t sc = A.cand_score[i];
+        if (sc < root) {
+            unsigned long long key = A.greedy ? (unsigned long long)i : (((unsigned long long)(uint32_t)sc) << 32) | (uint32_t)i;
+            best = key < best ? key : best;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other < best ? other : best;
+    }
+    if ((tid & 31) == 0) s_key[tid >> 5] = best;
+    __syncthreads();
+    if (tid == 0) {
+        for (int k = 1; k < 32; k++) best = s_key[k] < best ? s_key[k] : best;
+        A.ctl[LZG_CTL_LAST] = A.cand_score[A.n_cand - 1];  // see lzg_tree_last_candidate_score
+        if (best == ~0ull) {
+            A.ctl[LZG_CTL_BEST] = -1;
+            A.ctl[LZG_CTL_SCORE] = root;
+        } else {
+            const int idx = (int)(best & 0xffffffffu);
+            A.ctl[LZG_CTL_BEST] = idx;
+            A.ctl[LZG_CTL_SCORE] = A.cand_score[idx];
+        }
+    }
+}

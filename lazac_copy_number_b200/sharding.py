@@ -40,8 +40,12 @@ def shard_rows(n_cells, shard, n_shards, bm=128):
 
 
 def candidate_slice(n_candidates, rank, world):
-    """Contiguous slice [lo, hi) of the enumeration scored by `rank`."""
-    return n_candidates * rank // world, n_candidates * (rank + 1) // world
+    """Contiguous slice [lo, hi) of the enumeration scored by `rank`.  Boundaries are even: the
+    enumeration lists the two candidates of an edge back to back (src/copy_number.cxx:340-346)
+    and the GPU pass scores such a pair as one work item."""
+    pairs = (n_candidates + 1) // 2
+    lo, hi = 2 * (pairs * rank // world), 2 * (pairs * (rank + 1) // world)
+    return min(lo, n_candidates), min(hi, n_candidates)
 
 
 def pack_key(score, global_index, greedy=False):

@@ -68,8 +68,10 @@ def test_neighbourhood_scores_and_choice(ctx, port, n_leaves, bins, alleles, gre
     merges, nbytes = gt.last_nni_work()
     assert merges >= 2 * len(moves) and nbytes == (merges + len(moves)) * 2 * gt.L
     cand_bytes, up_bytes = gt.last_nni_traffic()
+    # the two candidates of an edge are one work item: 10 L bytes per pair, 6 L under the root
     root_moves = int((moves[:, 0] == 0).sum())
-    assert cand_bytes == (10 * len(moves) - 4 * root_moves) * gt.L and up_bytes % (2 * gt.L) == 0
+    assert len(moves) % 2 == 0 and root_moves % 2 == 0
+    assert cand_bytes == (10 * len(moves) // 2 - 4 * root_moves // 2) * gt.L and up_bytes % (2 * gt.L) == 0
     gt.free()
     prof.free()
 
@@ -143,6 +145,49 @@ def test_errors(ctx):
     assert e.value.status == 7
     assert t.nni_best(np.zeros((0, 4), np.int32))[0] == -1
     t.free()
+    prof.free()
+
+
+def test_arbitrary_move_lists(ctx, port):
+    """lzg_nni_best takes any list of moves: pairs broken apart by a shuffle, duplicates, odd
+    lengths, a single move -- scores and the first-wins choice still follow list order."""
+    bp, c0, c1, leaf_row, leaf_bp = make_case(50, 700, 2, seed=77)
+    prof = Profiles(ctx, bp)
+    gt = Tree(ctx, prof, c0, c1, leaf_row)
+    pt = PortTree(port, c0, c1, leaf_bp)
+    gt.small_rectilinear()
+    pt.small_rectilinear()
+    eu, ev = pt.edges()
+    order = np.arange(len(eu), dtype=np.int32)
+    full = pt.greedy_nni(eu, ev, order)
+    moves, scores = full["moves"], full["scores"]
+    rng = np.random.default_rng(5)
+    root = pt.score[0]
+    for trial in range(6):
+        if trial == 0:
+            sel = rng.permutation(len(moves))                      # pairs broken apart
+        elif trial == 1:
+            sel = np.concatenate([np.arange(len(moves)), rng.integers(0, len(moves), 17)])  # duplicates
+        elif trial == 2:
+            sel = np.arange(1, len(moves))                         # odd length, shifted pairing
+        elif trial == 3:
+            sel = np.array([int(np.argmin(scores))])               # one move
+        elif trial == 4:
+            sel = np.repeat(np.arange(0, len(moves), 2), 2)        # (z, z) twins: same edge, same z
+        else:
+            sel = np.arange(len(moves))[::-1]                      # reversed pairs
+        idx, score, allsc = gt.nni_best(moves[sel], want_all=True)
+        want_sc = scores[sel]
+        assert np.array_equal(allsc, want_sc), trial
+        better = np.flatnonzero(want_sc < root)
+        if len(better) == 0:
+            assert idx == -1 and score == root
+        else:
+            best = better[np.argmin(want_sc[better])]              # argmin returns the first minimum
+            assert idx == best and score == want_sc[best], trial
+        gidx, _, _ = gt.nni_best(moves[sel], greedy=True)
+        assert gidx == (better[0] if len(better) else -1)
+    gt.free()
     prof.free()
 
 

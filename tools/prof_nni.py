@@ -35,6 +35,21 @@ with Context(0) as ctx:
         idx, score, _ = t.nni_best(moves)
         times.append(ctx.timer_stop())
     cb, ub = t.last_nni_traffic()
+    up_only = []
+    for _ in range(reps):  # the UP pass alone (plus one item): its critical path
+        t.set_topology(c0, c1)
+        t.small_rectilinear()
+        ctx.flush_l2()
+        ctx.timer_start()
+        t.nni_best(moves[:2])
+        up_only.append(ctx.timer_stop())
+    hot = []
+    for _ in range(reps):  # UP intervals valid: scoring only
+        ctx.flush_l2()
+        ctx.timer_start()
+        t.nni_best(moves)
+        hot.append(ctx.timer_stop())
+    print("ms UP pass + 1 item:", ["%.3f" % x for x in up_only], " ms scoring only:", ["%.3f" % x for x in hot])
     print("nodes %d L %d candidates %d root %d best %d/%d mean depth %.1f" % (n, bp.shape[1], len(moves), root, idx, score, dep[moves[:, 2]].mean()))
     print("ms per pass:", ["%.3f" % x for x in times], "algorithmic bytes", cb + ub,
           "GB/s %.1f" % ((cb + ub) / (min(times) * 1e-3) / 1e9))
