@@ -10,8 +10,9 @@ Workloads (BASELINE.json `configs`); a step = one whole distan
   cfg3  20,000 cells x 10,000 bins x 2 alleles (L = 20,000)  default at --gpus > 1: tile rows of
         the ONE matrix are dealt to the ranks (strong scaling, no data-path collective; every
         rank ends with its own row/column strips)
-The NNI path (cfg4: 1,000 cells x 5,000 bins, NJ seed tree, one neighbourhood pass per step) is
-reported under "nni" in the same line at --gpus 1.
+The NNI path is reported in the same line at --gpus 1: "nni" = cfg4 (1,000 cells x 5,000 bins, NJ
+seed tree), "nni_large" = cfg5's shape (10,000 cells x 20,000 positions) on the one GPU; a step is
+one hill-climb iteration (accept a move + score the whole new neighbourhood).
 
 value   = cell pairs (n(n+1)/2, as the reference's loop counts them, src/lazac.cxx:81-91) per
           second with the packed profiles already resident in HBM; device time (CUDA events on
@@ -178,8 +179,94 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def nni_iterations(ctx, t, moves, order, steps, warmup):
+    """Times hill-climb iterations on tree t: accept a move (lzg_tree_apply_nni), then score the
+    whole new neighbourhood (lzg_nni_best).  The tree alternates between T0 and T1 = T0 + one
+    move (the inverse of nni(u, w, v, z) is nni(u, z, v, w)), so every step sees stale UP
+    intervals exactly as in hill_climb (src/copy_number.cxx:393-409).  Device time, CUDA events
+    on the library stream, L2 flushed before every step."""
+    m = tuple(int(x) for x in moves[len(moves) // 2])
+    inv = (m[0], m[3], m[2], m[1])
+    t.nni_best(moves)
+    t.apply_nni(*m)
+    eu1, ev1 = t.edges()
+    moves1 = t.enumerate_moves(eu1, ev1, order)
+    t.apply_nni(*inv)
+    lists = (moves1, moves)
+    for k in range(2 * max(2, (warmup + 1) // 2)):
+        t.apply_nni(*(m if k % 2 == 0 else inv))
+        t.nni_best(lists[k % 2])
+    n_it = steps + steps % 2                    # an even number of steps: the tree ends as T0
+    # (1) the pass on its own, as lzg_nni_best runs it on stale UP intervals: UP pass + items + argmin
+    os.environ["LZG_EAGER_UP"] = "0"
+    stale_ms = 0.0
+    cand = 0
+    cb = ub = 0
+    for k in range(n_it):
+        t.apply_nni(*(m if k % 2 == 0 else inv))   # untimed
+        ctx.flush_l2()
+        ctx.timer_start()
+        t.nni_best(lists[k % 2])
+        stale_ms += ctx.timer_stop()
+        cand += len(lists[k % 2])
+        c, u = t.last_nni_traffic()
+        cb, ub = cb + c, ub + u
+    del os.environ["LZG_EAGER_UP"]
+    # (2) whole iterations: the move application queues the UP pass behind itself
+    ap_ms = ps_ms = wall = 0.0
+    for k in range(n_it):
+        ctx.flush_l2()
+        ctx.sync()
+        t0 = time.perf_counter()
+        ctx.timer_start()
+        t.apply_nni(*(m if k % 2 == 0 else inv))
+        ap_ms += ctx.timer_stop()
+        ctx.timer_start()
+        t.nni_best(lists[k % 2])
+        ps_ms += ctx.timer_stop()
+        wall += time.perf_counter() - t0
+    hot = 0.0
+    for _ in range(n_it):                        # UP intervals still valid: scoring only
+        ctx.flush_l2()
+        ctx.timer_start()
+        idx, score, _ = t.nni_best(moves)
+        hot += ctx.timer_stop()
+    return {"iterations": n_it, "candidates": cand, "stale_pass_ms": stale_ms / n_it, "apply_ms": ap_ms / n_it, "pass_ms": ps_ms / n_it, "wall_s": wall,
+            "scoring_only_ms": hot / n_it, "cand_bytes": cb // n_it, "up_bytes": ub // n_it, "best_index": int(idx), "best_score": int(score),
+            "moves_bytes": int(moves.nbytes)}
+
+
+def nni_report(name, r, t, moves, dep, root, seed_tree, peaks, peaks_kind, n_leaves, L, note):
+    n = 2 * n_leaves - 1
+    C_ = len(moves)
+    it_ms = r["apply_ms"] + r["pass_ms"]
+    ps_ms = r["stale_pass_ms"]
+    nbytes = r["cand_bytes"] + r["up_bytes"]
+    merges, ref_bytes = t.last_nni_work()
+    return {
+        "metric": "nni_candidates_scored_per_sec", "value": C_ / (ps_ms * 1e-3), "unit": "candidates/s",
+        "ms_per_step": ps_ms,
+        "e2e": {"value": r["candidates"] / r["wall_s"], "unit": "candidates/s", "h2d_bytes_per_step": r["moves_bytes"] + 16, "d2h_bytes_per_step": 72,
+                "call": "whole hill-climb iterations, lzg_tree_apply_nni + lzg_nni_best with a host move list, wall clock"},
+        "iteration": {"value": C_ / (it_ms * 1e-3), "unit": "candidates/s", "ms_per_step": it_ms, "apply_ms": r["apply_ms"], "pass_ms": r["pass_ms"],
+                      "note": "accept a move (path re-scoring; the UP pass is queued behind it) + score the new neighbourhood, device time"},
+        "scoring_only": {"value": C_ / (r["scoring_only_ms"] * 1e-3), "unit": "candidates/s", "ms_per_step": r["scoring_only_ms"],
+                         "note": "UP intervals already valid (no move accepted since the last pass)"},
+        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_, "seed_tree": seed_tree,
+                   "step": "one neighbourhood pass as lzg_nni_best runs it after an accepted move: host packing of the move list, UP pass over "
+                           "the internal nodes, scoring of every candidate (the two candidates of an edge = one work item), argmin, read-back",
+                   "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
+                   "reference_algorithm_merges_per_pass": int(merges), "reference_algorithm_bytes_per_pass": int(ref_bytes),
+                   "root_score": int(root), "best_index": r["best_index"], "best_score": r["best_score"], "l2": "flushed between steps"},
+        "roofline": {"bound": "hbm", "achieved": nbytes / (ps_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": nbytes / (ps_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
+                     "algorithmic_bytes_per_pass": int(nbytes), "candidate_bytes": int(r["cand_bytes"]), "up_pass_bytes": int(r["up_bytes"]),
+                     "scoring_only_frac": r["cand_bytes"] / (r["scoring_only_ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], "note": note},
+    }
+
+
 def nni_section(ctx, args, peaks, peaks_kind):
-    """cfg4: one NNI neighbourhood pass per step on an NJ seed tree (1 GPU)."""
+    """cfg4: hill-climb iterations on an NJ seed tree (1 GPU)."""
     from lazac_copy_number_b200 import nj, synth
     from lazac_copy_number_b200.api import Profiles, Tree
     name = "tiny" if args.workload == "tiny" else "cfg4"
@@ -199,49 +286,11 @@ def nni_section(ctx, args, peaks, peaks_kind):
     order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
     moves = t.enumerate_moves(eu, ev, order)
     dep = nj.depths(c0, c1)
-    for _ in range(max(3, args.warmup)):
-        idx, score, _ = t.nni_best(moves)
-
-    def timed_pass(with_up):
-        """One neighbourhood pass as lzg_nni_best runs it: upload of the move list, (UP pass,) scorer,
-        argmin, 8-byte read-back.  with_up: the UP intervals are stale, as after every accepted move."""
-        dev_ms, wall, cb, ub = 0.0, 0.0, 0, 0
-        for _ in range(args.steps):
-            if with_up:
-                t.set_topology(c0, c1)      # invalidates everything (outside the timed region)
-                t.small_rectilinear()
-            ctx.flush_l2()
-            ctx.sync()
-            t0 = time.perf_counter()
-            ctx.timer_start()
-            t.nni_best(moves)
-            dev_ms += ctx.timer_stop()
-            wall += time.perf_counter() - t0
-            cb, ub = t.last_nni_traffic()
-        return dev_ms, wall, cb, ub
-
-    dev_ms, wall, cand_bytes, up_bytes = timed_pass(True)
-    dev_ms2, wall2, cand_bytes2, _ = timed_pass(False)
-    idx, score, _ = t.nni_best(moves)
-    merges, ref_bytes = t.last_nni_work()
+    r = nni_iterations(ctx, t, moves, order, args.steps, args.warmup)
+    out = nni_report(name, r, t, moves, dep, root, "NJ (numpy float64) of the GPU distance matrix", peaks, peaks_kind, n_leaves, L,
+                     "tree state (%.1f MB incl. UP intervals) fits the 126 MB L2 at this size: the step is launch/latency bound, not HBM bound"
+                     % (4 * n * L / 1e6))
     C_ = len(moves)
-    nbytes = cand_bytes + up_bytes
-    out = {
-        "metric": "nni_candidates_scored_per_sec", "value": C_ * args.steps / (dev_ms * 1e-3), "unit": "candidates/s",
-        "e2e": {"value": C_ * args.steps / wall, "unit": "candidates/s", "h2d_bytes_per_step": int(moves.nbytes), "d2h_bytes_per_step": 8},
-        "ms_per_step": dev_ms / args.steps,
-        "scoring_only": {"value": C_ * args.steps / (dev_ms2 * 1e-3), "unit": "candidates/s", "ms_per_step": dev_ms2 / args.steps,
-                         "note": "UP intervals already valid (no move accepted since the last pass)"},
-        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_, "seed_tree": "NJ (numpy float64) of the GPU distance matrix",
-                   "pass": "UP pass over the internal nodes + 3-merge scoring of every candidate + argmin (what one hill-climb iteration runs)",
-                   "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
-                   "reference_algorithm_merges_per_pass": int(merges), "reference_algorithm_bytes_per_pass": int(ref_bytes),
-                   "root_score": int(root), "best_index": int(idx), "best_score": int(score), "l2": "flushed between steps"},
-        "roofline": {"bound": "hbm", "achieved": nbytes / (dev_ms / args.steps * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": nbytes / (dev_ms / args.steps * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
-                     "algorithmic_bytes_per_pass": int(nbytes), "candidate_bytes": int(cand_bytes), "up_pass_bytes": int(up_bytes),
-                     "note": "tree state (%.1f MB incl. UP intervals) fits the 126 MB L2 at this size: the pass is launch/latency bound, not HBM bound" % (4 * n * L / 1e6)},
-    }
     if not args.no_cpu:
         # the reference's candidate loop (src/copy_number.cxx:347-366) on the same tree, 1 thread
         from oracle import Port, PortTree, have_ref
@@ -259,12 +308,41 @@ def nni_section(ctx, args, peaks, peaks_kind):
             pt = PortTree(Port(), c0, c1, leaf_bp)
             pt.small_rectilinear()
             t0 = time.perf_counter()
-            r = pt.greedy_nni(eu, ev, order)
+            rr = pt.greedy_nni(eu, ev, order)
             dt = time.perf_counter() - t0
-            sc, kind = r["scores"], "port"
+            sc, kind = rr["scores"], "port"
         _, _, allsc = t.nni_best(moves, want_all=True)
         out["cpu_baseline"] = {"value": C_ / dt, "unit": "candidates/s", "cores": 1, "kind": kind, "sample": "the same full pass (%d candidates)" % C_,
                                "scores_equal_gpu": bool(np.array_equal(sc, allsc))}
+    t.free()
+    gp.free()
+    return out
+
+
+def nni_section_large(ctx, args, peaks, peaks_kind):
+    """cfg5's shape on ONE GPU (tree state 0.8 GB + 0.8 GB of UP intervals: beyond L2, the regime the
+    HBM roofline describes)."""
+    from lazac_copy_number_b200 import nj, synth
+    from lazac_copy_number_b200.api import Profiles, Tree
+    w = NNI_WORKLOADS["cfg5"]
+    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0, want_tree=True)
+    bp = bp_int8_chunked(prof["cn"], prof["seg"])
+    n_leaves, L = bp.shape
+    n = 2 * n_leaves - 1
+    c0, c1 = synth.perturb_tree(prof["child0"], prof["child1"], n_leaves // 5, np.random.default_rng(1))
+    leaf_row = np.full(n, -1, np.int32)
+    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
+    gp = Profiles(ctx, bp)
+    t = Tree(ctx, gp, c0, c1, leaf_row)
+    root = t.small_rectilinear()
+    eu, ev = t.edges()
+    order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
+    moves = t.enumerate_moves(eu, ev, order)
+    dep = nj.depths(c0, c1)
+    r = nni_iterations(ctx, t, moves, order, min(args.steps, 10), args.warmup)
+    out = nni_report("cfg5 on 1 GPU", r, t, moves, dep, root,
+                     "generating tree + %d random NNIs (NJ at this n is host-side O(n^3): SURVEY.md 8(f) rank 1)" % (n_leaves // 5),
+                     peaks, peaks_kind, n_leaves, L, "tree state %.1f GB incl. UP intervals" % (4 * n * L / 1e9))
     t.free()
     gp.free()
     return out
@@ -488,6 +566,8 @@ def run_b200(args):
     del d_D
     if world == 1 and not args.no_nni:
         line["nni"] = nni_section(ctx, args, peaks, peaks_kind)
+        if args.workload != "tiny" and not args.no_nni_large:
+            line["nni_large"] = nni_section_large(ctx, args, peaks, peaks_kind)
     if world > 1 and not args.no_nni:
         nni = nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind)
         if rank == 0:
@@ -509,6 +589,7 @@ def main():
     ap.add_argument("--ref-cells", type=int, default=0, help="cells in the CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-nni", action="store_true", help="skip the NNI section")
+    ap.add_argument("--no-nni-large", action="store_true", help="skip the cfg5-shaped NNI section at --gpus 1")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

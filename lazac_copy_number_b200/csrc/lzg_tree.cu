@@ -220,13 +220,14 @@ int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t) {
     return LZG_OK;
 }
 
-// Internal nodes in the subtree of every node (0 for leaves): the weight the heavy-path
-// decomposition uses.  Rebuilt from scratch after a topology replacement; an accepted NNI
-// (u, w, v, z) only changes the entry of v (lzg_tree_apply), so it is kept up to date in O(1).
-static void rebuild_isize(lzg_tree* t) {
+// Packed host mirror for the heavy-path tables: {child0, child1, internal nodes in the subtree
+// (0 for leaves), parent} per node -- one cache line touch per visited node.  Rebuilt from
+// scratch after a topology replacement; an accepted NNI (u, w, v, z) rewrites four entries
+// (lzg_tree_apply), the subtree count changes for v only.
+static void rebuild_node4(lzg_tree* t) {
     const int n = t->n_nodes;
     std::vector<int32_t>& pre = t->tmp_pre;
-    t->isize.assign(n, 0);
+    t->node4.resize(n);
     pre.clear();
     pre.reserve(n);
     pre.push_back(0);
@@ -239,9 +240,10 @@ static void rebuild_isize(lzg_tree* t) {
     }
     for (int i = n - 1; i >= 0; i--) {
         const int a = pre[i];
-        if (t->child0[a] >= 0) t->isize[a] = 1 + t->isize[t->child0[a]] + t->isize[t->child1[a]];
+        const int c0 = t->child0[a], c1 = t->child1[a];
+        t->node4[a] = make_int4(c0, c1, c0 >= 0 ? 1 + t->node4[c0].z + t->node4[c1].z : 0, t->parent[a]);
     }
-    t->isize_valid = true;
+    t->node4_valid = true;
 }
 
 // Heavy-path decomposition of the internal non-root nodes, paths listed parents-first (a path's
@@ -250,33 +252,34 @@ static void rebuild_isize(lzg_tree* t) {
 // Also fills t->up_rank (position of a node in order, -1 for the root and the leaves).
 static int build_up_paths(lzg_tree* t, int2* order, int4* rec, int* n_order) {
     const int n = t->n_nodes;
-    if (!t->isize_valid) rebuild_isize(t);
-    const int32_t* size = t->isize.data();
-    const int32_t *c0a = t->child0.data(), *c1a = t->child1.data();
+    if (!t->node4_valid) rebuild_node4(t);
+    const int4* nd = t->node4.data();
     t->up_rank.assign(n, -1);
     int32_t* rank = t->up_rank.data();
     int cnt = 0, paths = 0;
-    std::vector<int32_t>& heads = t->tmp_heads;  // (head, its parent, its sibling) triples, a queue
-    heads.clear();
-    heads.reserve(3 * (size_t)n / 2 + 6);
-    if (c0a[0] >= 0) {
-        const int a = c0a[0], b = c1a[0];
-        if (size[a] > 0) heads.insert(heads.end(), {a, 0, b});
-        if (size[b] > 0) heads.insert(heads.end(), {b, 0, a});
+    t->tmp_heads.resize(3 * (size_t)n / 2 + 6);  // (head, its parent, its sibling) triples, a queue
+    int32_t* heads = t->tmp_heads.data();
+    size_t n_heads = 0;
+    if (nd[0].x >= 0) {
+        const int a = nd[0].x, b = nd[0].y;
+        if (nd[a].z > 0) heads[n_heads++] = a, heads[n_heads++] = 0, heads[n_heads++] = b;
+        if (nd[b].z > 0) heads[n_heads++] = b, heads[n_heads++] = 0, heads[n_heads++] = a;
     }
-    for (size_t h = 0; h < heads.size(); h += 3) {
+    for (size_t h = 0; h < n_heads; h += 3) {
         const int first = cnt;
         int a = heads[h], sib = heads[h + 2];
+        int4 na = nd[a];
         while (true) {
             rank[a] = cnt;
             order[cnt++] = make_int2(a, sib);
-            const int c0 = c0a[a], c1 = c1a[a];
-            const bool h0 = size[c0] >= size[c1];
-            const int heavy = h0 ? c0 : c1, light = h0 ? c1 : c0;
-            if (size[light] > 0) heads.insert(heads.end(), {light, a, heavy});
-            if (size[heavy] == 0) break;
+            const int4 n0 = nd[na.x], n1 = nd[na.y];
+            const bool h0 = n0.z >= n1.z;
+            const int heavy = h0 ? na.x : na.y, light = h0 ? na.y : na.x;
+            if ((h0 ? n1.z : n0.z) > 0) heads[n_heads++] = light, heads[n_heads++] = a, heads[n_heads++] = heavy;
+            if ((h0 ? n0.z : n1.z) == 0) break;
             a = heavy;
             sib = light;
+            na = h0 ? n0 : n1;
         }
         rec[paths++] = make_int4(first, cnt - first, heads[h + 1], heads[h + 2]);
     }
@@ -306,6 +309,54 @@ static bool is_move(const lzg_tree* t, int u, int w, int v, int z) {
     if (t->parent[v] != u || t->parent[w] != u || w == v) return false;
     if (t->parent[z] != v) return false;
     return true;
+}
+
+// Queues the UP pass of the current topology on the stream: heavy-path tables (host), one H2D
+// copy, k_up_pass.  Called by lzg_tree_nni_scores when the UP intervals are stale and by
+// lzg_tree_apply right behind the move, so that the GPU rebuilds them while the host
+// enumerates and packs the next neighbourhood.
+static int launch_up_pass(lzg_ctx* ctx, lzg_tree* t, int groups, int threads) {
+    const int n = t->n_nodes;
+    int rc = lzg_ensure_pinned(ctx, 16 + (size_t)6 * n + 12);
+    if (rc != LZG_OK) return rc;
+    int32_t* stage = ctx->h_pinned + 16;
+    int n_order = 0;
+    const bool trace = getenv("LZG_PASS_DEBUG") && (atoi(getenv("LZG_PASS_DEBUG")) & 4);
+    const auto t0 = std::chrono::steady_clock::now();
+    // records are written at the front, the order behind the worst-case record area, then compacted
+    const int n_paths = build_up_paths(t, reinterpret_cast<int2*>(stage + 4 * (size_t)n), reinterpret_cast<int4*>(stage), &n_order);
+    memmove(stage + 4 * (size_t)n_paths, stage + 4 * (size_t)n, sizeof(int2) * n_order);
+    const auto t1 = std::chrono::steady_clock::now();
+    t->up_nodes = n_order;
+    t->up_paths = n_paths;
+    t->epoch++;
+    t->up_ran = true;
+    if (n_paths > 0) {
+        LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand, 0, sizeof(int32_t) * LZG_CTL_INTS, ctx->stream));  // the ticket counter
+        LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass, stage, sizeof(int32_t) * (4 * (size_t)n_paths + 2 * (size_t)n_order), cudaMemcpyHostToDevice,
+                                      ctx->stream));
+        lzg_pass_args A{};
+        A.path_rec = reinterpret_cast<const int4*>(t->d_pass);
+        A.order = reinterpret_cast<const int2*>(t->d_pass + 4 * (size_t)n_paths);
+        A.n_paths = n_paths;
+        A.groups = groups;
+        A.l_pad = t->l_pad;
+        A.epoch = t->epoch;
+        A.start = t->d_start;
+        A.end = t->d_end;
+        A.ustart = t->d_ustart;
+        A.uend = t->d_uend;
+        A.ready = t->d_ready;
+        A.ctl = t->d_cand;
+        k_up_pass<<<n_paths * groups, threads, 0, ctx->stream>>>(A);
+        LZG_LAUNCH_CHECK(ctx);
+    }
+    if (trace)
+        fprintf(stderr, "[lzg up] paths %d nodes %d: tables %.1f us, queueing %.1f us\n", n_paths, n_order,
+                std::chrono::duration<double, std::micro>(t1 - t0).count(),
+                std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t1).count());
+    t->up_valid = true;
+    return LZG_OK;
 }
 
 // One neighbourhood pass.  The UP pass is launched first (it needs the path tables only), so the
@@ -365,28 +416,15 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     A.cand_score = t->d_cand + LZG_CTL_INTS;
     A.items = reinterpret_cast<const int4*>(t->d_pass + o_items);
     A.n_items = 0;
-    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)n_moves), ctx->stream));
-    int n_paths = 0, n_order = 0;
+    int n_paths = 0;
     if (!t->up_valid) {
-        // records are written at the front, the order behind the worst-case record area, then compacted
-        n_paths = build_up_paths(t, reinterpret_cast<int2*>(stage + 4 * (size_t)n), reinterpret_cast<int4*>(stage), &n_order);
-        memmove(stage + 4 * (size_t)n_paths, stage + 4 * (size_t)n, sizeof(int2) * n_order);
-        t->up_nodes = n_order;
-        t->up_paths = n_paths;
-        t->epoch++;
-        t->last_up_ran = true;
-        const size_t ints = 4 * (size_t)n_paths + 2 * (size_t)n_order;
-        if (n_paths > 0) {
-            LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass, stage, sizeof(int32_t) * ints, cudaMemcpyHostToDevice, ctx->stream));
-            A.path_rec = reinterpret_cast<const int4*>(t->d_pass);
-            A.order = reinterpret_cast<const int2*>(t->d_pass + 4 * (size_t)n_paths);
-            A.n_paths = n_paths;
-            A.epoch = t->epoch;
-            k_up_pass<<<n_paths * groups, threads, 0, ctx->stream>>>(A);
-            LZG_LAUNCH_CHECK(ctx);
-        }
-        t->up_valid = true;
+        rc = launch_up_pass(ctx, t, groups, threads);
+        if (rc != LZG_OK) return rc;
+        n_paths = t->up_paths;
     }
+    t->last_up_ran = t->up_ran;  // also when lzg_tree_apply already queued it behind the move
+    t->up_ran = false;
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)n_moves), ctx->stream));
     const auto t_up = std::chrono::steady_clock::now();
     // items: the two candidates of an edge (u, v) as one record, sorted by the walker rank of u so
     // that neighbouring CTAs share rows (both items under one u read DOWN(u) and UP(u))
@@ -473,14 +511,27 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     t->parent[w] = v;
     t->parent[z] = u;
     t->up_valid = false;
-    if (t->isize_valid) t->isize[v] = 1 + t->isize[w] + t->isize[y];  // u's subtree keeps its node set
+    if (t->node4_valid) {  // u's subtree keeps its node set: the count changes for v only
+        int4* nd = t->node4.data();
+        nd[v] = make_int4(t->child0[v], t->child1[v], 1 + nd[w].z + nd[y].z, u);
+        nd[u].x = t->child0[u], nd[u].y = t->child1[u];
+        nd[w].w = v;
+        nd[z].w = u;
+    }
     LZG_CUDA(ctx, cudaMemsetAsync(t->d_ctl, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)depth + 1), ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
     k_apply_move<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_score, t->d_cost, t->d_ctl,
                                                       u, w, v, z, y, t->l_pad);
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_ctl, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
-    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    LZG_CUDA(ctx, cudaEventRecord(ctx->ev_group, ctx->stream));
+    // a neighbourhood pass follows an accepted move (hill_climb, src/copy_number.cxx:393-409): queue its
+    // UP pass now, the caller only waits for the root score
+    if (t->d_ustart && t->d_pass && !(getenv("LZG_EAGER_UP") && atoi(getenv("LZG_EAGER_UP")) == 0)) {
+        int rc = launch_up_pass(ctx, t, groups, threads);
+        if (rc != LZG_OK) return rc;
+    }
+    LZG_CUDA(ctx, cudaEventSynchronize(ctx->ev_group));
     t->root_score = ctx->h_pinned[LZG_CTL_SCORE];
     return LZG_OK;
 }

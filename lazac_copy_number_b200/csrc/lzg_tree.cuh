@@ -32,12 +32,13 @@ struct lzg_tree {
     int32_t last_cand_score = 0;      // score of the last candidate of that call (root score when it had none)
     int32_t last_items = 0;           // work items of that call (an item = the two candidates of one edge (u, v))
     int32_t last_root_items = 0;      // items whose u is the root (no UP / DOWN(u) rows: 6 L instead of 10 L bytes)
-    bool last_up_ran = false;         // that call had to rebuild the UP intervals
+    bool last_up_ran = false;         // the UP intervals were rebuilt for that call (by it, or by the lzg_tree_apply before it)
+    bool up_ran = false;              // an UP pass was queued since the last lzg_nni_best
     int32_t up_nodes = 0;             // internal non-root nodes (UP rows written by an UP pass)
     int32_t up_paths = 0;             // heavy paths they form
     std::vector<int32_t> up_rank;     // position of a node in the walker order (-1: root, leaves); valid while up_valid
-    std::vector<int32_t> isize;       // internal nodes in the subtree of every node (heavy-path weights)
-    bool isize_valid = false;         // cleared by lzg_tree_set_topology; kept current by lzg_tree_apply
+    std::vector<int4> node4;          // {child0, child1, internal nodes in the subtree, parent}: packed mirror for the path tables
+    bool node4_valid = false;         // cleared by lzg_tree_set_topology; kept current by lzg_tree_apply
     std::vector<int32_t> tmp_pre, tmp_heads, tmp_items, tmp_count;  // per-pass host scratch, kept to avoid reallocation
 };
 

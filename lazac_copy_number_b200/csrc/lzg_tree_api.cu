@@ -169,7 +169,7 @@ int lzg_tree_set_topology(lzg_ctx* ctx, lzg_tree* t, const int32_t* child0, cons
     }
     t->scored = false;
     t->up_valid = false;
-    t->isize_valid = false;
+    t->node4_valid = false;
     return lzg_tree_upload_topology(ctx, t);
 }
 
