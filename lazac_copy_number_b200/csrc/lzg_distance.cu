@@ -118,20 +118,21 @@ __global__ void k_bias_rows_i8(uint8_t* __restrict__ d, int n, int L, int l_pad,
 }
 
 // ---- the pair kernel ---------------------------------------------------------------------------
-// Work is described by SEGMENTS built on the host (build_schedule below): a segment is one
+// Work is described by SEGMENTS built on the host (get_schedule below): a segment is one
 // BM x BN tile of cell pairs (rows of tile-row r against rows of tile-row c, c >= r) over the
-// k-iterations [k0, k1) of KC positions each.  The grid is persistent -- one CTA per resident
-// slot (2 per SM for 128 x 128 tiles) -- and CTA b executes segments seg_off[b] .. seg_off[b+1].
-// The host cuts the (tile, k) iteration space into equal-cost contiguous ranges (stream-K), so
-// every SM finishes together whatever the number of tiles; a tile cut across CTAs is
-// accumulated with integer atomics (exact, order-free) into cells zeroed by k_zero_tiles.
+// 16-byte position chunks [k0, k1).  The grid is persistent -- one CTA per SM -- and CTA b
+// executes segments seg_off[b] .. seg_off[b+1].  The host cuts the (tile, chunk) space into
+// contiguous ranges of equal cost (stream-K at chunk granularity, a fixed cost per segment for its
+// pipeline fill and epilogue), so every SM finishes together whatever the number of tiles; a
+// tile cut across CTAs is accumulated with integer atomics (exact, order-free) into cells zeroed
+// by k_zero_tiles.
 //
 // Diagonal tiles (r == c) skip their lower-left quadrant: thread (ty, tx) owns rows ty + TY*i and
 // columns tx + TX*j, so "row >= BM/2 and column < BN/2" is i >= 4 && j < 4 for every thread
 // alike -- a quarter of the SADs of those tiles, with no divergence; the quadrant is filled
 // from the mirror of the upper-right one.
 struct lzg_seg {
-    int32_t r, c, k0, k1;  // k1 < 0: accumulate with atomics into pre-zeroed cells, k-range [k0, -k1)
+    int32_t r, c, k0, k1;  // chunks [k0, k1); k1 < 0: accumulate with atomics into pre-zeroed cells, range [k0, -k1)
 };
 
 // One k-iteration (KC positions) of a thread's 8 x 8 pairs.  DIAG skips the lower-left quadrant.
@@ -163,6 +164,33 @@ __device__ __forceinline__ void tile_step(uint32_t (&acc)[8][8], const uint8_t* 
     }
 }
 
+// The last stage of a segment may hold fewer than eight chunks: same arithmetic, rolled loop.
+template <int BM, int BN, bool DIAG>
+__device__ __forceinline__ void tile_step_partial(uint32_t (&acc)[8][8], const uint8_t* sA, const uint8_t* sB, int tx, int ty, int nc) {
+    constexpr int TX = BN / 8, TY = BM / 8;
+    const int swa = ty & 7, swb = tx & 7;
+#pragma unroll 1
+    for (int c = 0; c < nc; c++) {
+        uint4 a[8], b[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            a[i] = *reinterpret_cast<const uint4*>(sA + (ty + TY * i) * KC + ((c ^ swa) << 4));
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            b[j] = *reinterpret_cast<const uint4*>(sB + (tx + TX * j) * KC + ((c ^ swb) << 4));
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                if (DIAG && i >= 4 && j < 4) continue;
+                acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]);
+                acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
+                acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]);
+                acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
+            }
+    }
+}
+
 template <int BM, int BN, int STAGES>
 __global__ void __launch_bounds__((BM / 8) * (BN / 8), 1)
 k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_seg* __restrict__ segs,
@@ -178,26 +206,29 @@ k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_se
     for (int s = s_begin; s < s_end; s++) {
         const lzg_seg sg = segs[s];
         const bool atomic = sg.k1 < 0;
-        const int k_begin = sg.k0, n_it = (atomic ? -sg.k1 : sg.k1) - sg.k0;
+        const int k_begin = sg.k0, n_chunks = (atomic ? -sg.k1 : sg.k1) - sg.k0, n_it = (n_chunks + 7) >> 3;
         const bool diag = sg.r == sg.c;
         const int row0 = sg.r * BM, col0 = sg.c * BN;
-        const uint8_t* gA = prof + (size_t)row0 * l_pad + (size_t)k_begin * KC;
-        const uint8_t* gB = prof + (size_t)col0 * l_pad + (size_t)k_begin * KC;
+        const uint8_t* gA = prof + (size_t)row0 * l_pad + (size_t)k_begin * 16;
+        const uint8_t* gB = prof + (size_t)col0 * l_pad + (size_t)k_begin * 16;
 
         auto load_stage = [&](int it, int slot) {
             uint8_t* sA = smem + slot * STAGE_BYTES;
             uint8_t* sB = sA + A_BYTES;
             const uint8_t* a = gA + (size_t)it * KC;
             const uint8_t* b = gB + (size_t)it * KC;
+            const int c = tid & 7;  // T is a multiple of 8: a thread always copies the same chunk column
+            if (it * 8 + c < n_chunks) {  // the last stage of a segment may be partial
 #pragma unroll
-            for (int q = tid; q < BM * 8; q += T) {
-                int r = q >> 3, c = q & 7;
-                cp_async16(sA + r * KC + ((c ^ (r & 7)) << 4), a + (size_t)r * l_pad + (c << 4));
-            }
+                for (int q = tid; q < BM * 8; q += T) {
+                    const int r = q >> 3;
+                    cp_async16(sA + r * KC + ((c ^ (r & 7)) << 4), a + (size_t)r * l_pad + (c << 4));
+                }
 #pragma unroll
-            for (int q = tid; q < BN * 8; q += T) {
-                int r = q >> 3, c = q & 7;
-                cp_async16(sB + r * KC + ((c ^ (r & 7)) << 4), b + (size_t)r * l_pad + (c << 4));
+                for (int q = tid; q < BN * 8; q += T) {
+                    const int r = q >> 3;
+                    cp_async16(sB + r * KC + ((c ^ (r & 7)) << 4), b + (size_t)r * l_pad + (c << 4));
+                }
             }
         };
 
@@ -223,8 +254,14 @@ k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_se
             }
             const uint8_t* sA = smem + (it % STAGES) * STAGE_BYTES;
             const uint8_t* sB = sA + A_BYTES;
-            if (!diag) tile_step<BM, BN, false>(acc, sA, sB, tx, ty);
-            else tile_step<BM, BN, true>(acc, sA, sB, tx, ty);
+            const int nc = n_chunks - it * 8;
+            if (nc >= 8) {
+                if (!diag) tile_step<BM, BN, false>(acc, sA, sB, tx, ty);
+                else tile_step<BM, BN, true>(acc, sA, sB, tx, ty);
+            } else {
+                if (!diag) tile_step_partial<BM, BN, false>(acc, sA, sB, tx, ty, nc);
+                else tile_step_partial<BM, BN, true>(acc, sA, sB, tx, ty, nc);
+            }
         }
         cp_async_wait<0>();
         __syncthreads();
@@ -298,15 +335,17 @@ constexpr int dist_smem_bytes() {
     return pipe > epi ? pipe : epi;
 }
 
-// Cuts the shard's (tile, k-iteration) space into n_ctas contiguous ranges of equal cost.
+// Cuts the shard's (tile, chunk) space into at most n_ctas contiguous ranges of equal cost.
 // Tile rows are dealt to shards in pairs (r, R-1-r): every pair has R+1 tiles, so every shard
-// gets the same triangle area.  Cost of one k-iteration: 4 units, 3 for a diagonal tile.
+// gets the same triangle area.  Cost of one 16-byte chunk of a tile: 4 units, 3 for a diagonal
+// tile; every segment adds LZG_SEG_COST units (pipeline fill + epilogue, about 0.8 of a 128-byte
+// stage measured on cfg2).  The smallest feasible per-CTA budget is found by bisection.
 const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slots_per_sm, int shard, int n_shards,
                                  int row_lo, int row_hi, int* status) {
     for (auto& sc : p->schedules)
         if (sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
     const int R = (p->n + bm - 1) / bm;
-    const int K = p->l_pad / KC;
+    const int K = p->l_pad / 16;  // chunks per row
     std::vector<int2> tiles;
     int64_t pairs = 0, units = 0;
     auto rows_in = [&](int r) { return (int64_t)(std::min(p->n, (r + 1) * bm) - r * bm); };
@@ -326,33 +365,60 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
     sc.row_lo = row_lo;
     sc.row_hi = row_hi;
     sc.pairs = pairs;
-    const int64_t iters = (int64_t)tiles.size() * K;
-    const int G = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * slots_per_sm, iters));
+    const int64_t seg_cost = getenv("LZG_SEG_COST") ? atoi(getenv("LZG_SEG_COST")) : 26;
+    const int min_take = 8;  // never cut a segment shorter than one stage (unless the tile ends)
+    const int G = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * slots_per_sm, (int64_t)tiles.size() * ((K + min_take - 1) / min_take)));
     std::vector<lzg_seg> segs;
-    std::vector<int32_t> seg_off(G + 1, 0);
-    std::vector<int2> split;
-    int cur = 0;
-    int64_t cum = 0;
-    auto boundary = [&](int b) { return units * (int64_t)(b + 1) / G; };
-    for (const int2& t : tiles) {
-        const int u = t.x == t.y ? 3 : 4;
-        const size_t first = segs.size();
-        int k = 0;
-        while (k < K) {
-            int64_t rem = boundary(cur) - cum;
-            int it = (int)std::min<int64_t>(K - k, std::max<int64_t>(1, (rem + u - 1) / u));
-            segs.push_back(lzg_seg{t.x, t.y, k, k + it});
-            cum += (int64_t)it * u;
-            k += it;
-            while (cur < G - 1 && cum >= boundary(cur)) seg_off[++cur] = (int32_t)segs.size();
+    std::vector<int32_t> seg_off;
+    // greedy fill with a per-CTA budget; returns the number of CTAs used (segments written when emit)
+    auto fill = [&](int64_t budget, bool emit) {
+        int ctas = 1;
+        int64_t load = 0;
+        if (emit) {
+            segs.clear();
+            seg_off.assign(1, 0);
         }
-        if (segs.size() - first > 1) {
-            for (size_t q = first; q < segs.size(); q++) segs[q].k1 = -segs[q].k1;
-            split.push_back(t);
+        for (const int2& t : tiles) {
+            const int u = t.x == t.y ? 3 : 4;
+            int k = 0;
+            while (k < K) {
+                const int want = std::min(K - k, min_take);
+                if (load > 0 && load + seg_cost + (int64_t)want * u > budget) {  // this CTA is full
+                    ctas++;
+                    load = 0;
+                    if (emit) seg_off.push_back((int32_t)segs.size());
+                }
+                int take = (int)std::min<int64_t>(K - k, std::max<int64_t>(want, (budget - load - seg_cost) / u));
+                if (K - k - take < min_take) take = K - k;  // no sliver at the end of a tile
+                if (emit) segs.push_back(lzg_seg{t.x, t.y, k, k + take});
+                load += seg_cost + (int64_t)take * u;
+                k += take;
+            }
         }
+        return ctas;
+    };
+    int64_t lo = (units + (int64_t)tiles.size() * seg_cost) / G, hi = units + (int64_t)tiles.size() * seg_cost + seg_cost;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) / 2;
+        if (fill(mid, false) <= G) hi = mid;
+        else lo = mid + 1;
     }
-    while (cur < G) seg_off[++cur] = (int32_t)segs.size();
-    sc.n_ctas = G;
+    const int used = tiles.empty() ? 0 : fill(lo, true);
+    if (!tiles.empty()) seg_off.push_back((int32_t)segs.size());
+    // tiles cut into several segments are accumulated with atomics
+    std::vector<int2> split;
+    for (size_t q = 0; q < segs.size();) {
+        size_t e = q + 1;
+        while (e < segs.size() && segs[e].r == segs[q].r && segs[e].c == segs[q].c) e++;
+        if (e - q > 1) {
+            for (size_t i = q; i < e; i++) segs[i].k1 = -segs[i].k1;
+            split.push_back(make_int2(segs[q].r, segs[q].c));
+        }
+        q = e;
+    }
+    const int Gu = std::max(used, 1);
+    if (seg_off.empty()) seg_off.assign(2, 0);
+    sc.n_ctas = Gu;
     sc.n_segs = (int)segs.size();
     sc.n_split = (int)split.size();
     if (sc.n_segs > 0) {

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Times the distance kernel (device-resident, CUDA events) for LZG_DIST_VARIANT values.
+"""Times the distance kernel (device-resident, CUDA events) for LZG_SEG_COST values (fixed cost of a stream-K segment in the schedule).
 usage: python tools/sweep_distance.py 0 1 2 12 4      (experiments; not part of the product)"""
 import json
 import os
@@ -36,6 +36,6 @@ print(json.dumps(out))
 ''' % ROOT
 
 for v in sys.argv[1:] or ["0"]:
-    env = dict(os.environ, LZG_DIST_VARIANT=v)
+    env = dict(os.environ, LZG_SEG_COST=v)
     r = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True)
-    print("variant", v, r.stdout.strip().splitlines()[-1] if r.returncode == 0 and r.stdout.strip() else "FAILED " + r.stderr[-400:], flush=True)
+    print("seg_cost", v, r.stdout.strip().splitlines()[-1] if r.returncode == 0 and r.stdout.strip() else "FAILED " + r.stderr[-400:], flush=True)
