@@ -501,8 +501,20 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
 int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     if (!is_move(t, u, w, v, z)) return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "not an NNI move of this topology");
     const int y = t->child0[v] == z ? t->child1[v] : t->child0[v];
+    // the path in the OLD topology: v, u, parent(u), ..., root; step k writes node[k] after merging other[k]
+    lzg_apply_args P;
     int depth = 0;
     for (int a = v; a != 0; a = t->parent[a]) depth++;
+    P.n_steps = depth + 1;
+    P.u = u, P.w = w, P.v = v, P.z = z, P.y = y;
+    P.node[0] = v, P.other[0] = y;
+    P.node[1] = u, P.other[1] = z;
+    for (int k = 2, b = u; k < std::min(P.n_steps, LZG_APPLY_LISTED); k++) {
+        const int pb = t->parent[b];
+        P.node[k] = pb;
+        P.other[k] = t->child0[pb] == b ? t->child1[pb] : t->child0[pb];
+        b = pb;
+    }
     // host mirror
     t->child0[v] = std::min(w, y);
     t->child1[v] = std::max(w, y);
@@ -521,7 +533,7 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     LZG_CUDA(ctx, cudaMemsetAsync(t->d_ctl, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)depth + 1), ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
     k_apply_move<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_score, t->d_cost, t->d_ctl,
-                                                      u, w, v, z, y, t->l_pad);
+                                                      P, t->l_pad);
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_ctl, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     LZG_CUDA(ctx, cudaEventRecord(ctx->ev_group, ctx->stream));

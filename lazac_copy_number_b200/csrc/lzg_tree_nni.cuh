@@ -46,66 +46,87 @@ __device__ __forceinline__ uint4 ldcg16(const uint8_t* base, size_t off) {
 // ---- accept a move = ONE launch ------------------------------------------------------------------------
 // nni(t,u,w,v,z); unvisit(t,0,v); small_rectilinear(t,0) (src/copy_number.cxx:397,408-409): rewrite
 // the intervals of v, u, parent(u), ..., root.  Every thread owns 16 positions and walks the path
-// with its running interval in registers.  The new children of v are (w, y) and the other child
-// of u is z; everything above u is read from the (parent, sibling) table, whose entries for u and
-// its ancestors the move does not touch, so thread 0 of CTA 0 can patch the topology arrays while
-// the others walk.  Step k's cost goes to path_cost[k]; the CTA that finishes last turns the
-// costs into cumulative scores (src/copy_number.cxx:264) and leaves the root score in ctl.
+// with its running interval in registers.  The host lists the path in the kernel arguments
+// (step k writes node[k] after merging other[k]: v <- (w, y), u <- (v, z), then the old
+// ancestors of u with their siblings), so the sibling rows are prefetched two steps ahead and
+// the final score update loads everything at once; a path longer than LZG_APPLY_LISTED continues
+// through the (parent, sibling) table, whose entries above u the move does not touch.  Step
+// k's cost goes to path_cost[k]; the CTA that finishes last turns the costs into cumulative
+// scores (src/copy_number.cxx:264), leaves the root score in ctl and patches the topology arrays.
+#define LZG_APPLY_LISTED 64
+struct lzg_apply_args {
+    int n_steps, u, w, v, z, y;
+    int node[LZG_APPLY_LISTED], other[LZG_APPLY_LISTED];
+};
+
 __global__ void __launch_bounds__(256)
 k_apply_move(int32_t* child0, int32_t* child1, int2* up, uint8_t* __restrict__ start, uint8_t* __restrict__ end,
-             int32_t* __restrict__ score, int32_t* __restrict__ path_cost, int* __restrict__ ctl, int u, int w, int v, int z,
-             int y, int l_pad) {
+             int32_t* __restrict__ score, int32_t* __restrict__ path_cost, int* __restrict__ ctl, const lzg_apply_args P, int l_pad) {
     const int chunk = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = chunk * 16 < l_pad;
     const size_t off = (size_t)chunk * 16;
+    const int n_listed = min(P.n_steps, LZG_APPLY_LISTED);
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
     iv16 acc;
     uint32_t os[8], oe[8];
+    uint4 s0 = z4, e0 = z4, s1 = z4, e1 = z4, s2 = z4, e2 = z4;
     if (active) {
-        widen(ldg16(start, (size_t)w * l_pad + off), acc.s);
-        widen(ldg16(end, (size_t)w * l_pad + off), acc.e);
-        widen(ldg16(start, (size_t)y * l_pad + off), os);
-        widen(ldg16(end, (size_t)y * l_pad + off), oe);
+        widen(ldg16(start, (size_t)P.w * l_pad + off), acc.s);
+        widen(ldg16(end, (size_t)P.w * l_pad + off), acc.e);
+        s0 = ldg16(start, (size_t)P.other[0] * l_pad + off), e0 = ldg16(end, (size_t)P.other[0] * l_pad + off);
+        if (n_listed > 1) s1 = ldg16(start, (size_t)P.other[1] * l_pad + off), e1 = ldg16(end, (size_t)P.other[1] * l_pad + off);
     }
-    int a = v, step = 0;
-    int2 ps = make_int2(u, z);  // (parent, sibling) of v after the move
-    while (true) {
+    int a = 0;
+    for (int k = 0; k < P.n_steps; k++) {
+        int oth_next2 = -1;
+        if (k + 2 < n_listed) oth_next2 = P.other[k + 2];
+        if (active && oth_next2 >= 0) s2 = ldg16(start, (size_t)oth_next2 * l_pad + off), e2 = ldg16(end, (size_t)oth_next2 * l_pad + off);
+        if (k < n_listed) {
+            a = P.node[k];
+        } else {  // beyond the listed part: follow the table (a is the node written last)
+            const int2 ps = up[a];
+            a = ps.x;
+            if (active) s0 = ldg16(start, (size_t)ps.y * l_pad + off), e0 = ldg16(end, (size_t)ps.y * l_pad + off);
+        }
         uint32_t c = 0;
         if (active) {
+            widen(s0, os);
+            widen(e0, oe);
             c = merge16(acc, os, oe);
             *reinterpret_cast<uint4*>(start + (size_t)a * l_pad + off) = narrow(acc.s);
             *reinterpret_cast<uint4*>(end + (size_t)a * l_pad + off) = narrow(acc.e);
         }
         c = warp_sum(c);
-        if ((threadIdx.x & 31) == 0 && c) atomicAdd(path_cost + step, (int32_t)c);
-        if (a == 0) break;
-        if (active) {
-            widen(ldg16(start, (size_t)ps.y * l_pad + off), os);
-            widen(ldg16(end, (size_t)ps.y * l_pad + off), oe);
-        }
-        a = ps.x;
-        if (a != 0) ps = up[a];
-        step++;
+        if ((threadIdx.x & 31) == 0 && c) atomicAdd(path_cost + k, (int32_t)c);
+        s0 = s1, e0 = e1;
+        s1 = s2, e1 = e2;
     }
     __shared__ int s_last;
+    __shared__ int32_t s_term[LZG_APPLY_LISTED];
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) s_last = atomicAdd(ctl + LZG_CTL_DONE, 1) == (int)gridDim.x - 1;
     __syncthreads();
-    if (!s_last || threadIdx.x != 0) return;
+    if (!s_last) return;
     __threadfence();
-    // cumulative scores along the path, then the topology patch (nni(), src/copy_number.cxx:279-284)
-    int32_t s = __ldcg(path_cost + 0) + score[w] + score[y];
-    score[v] = s;
-    s += __ldcg(path_cost + 1) + score[z];
-    score[u] = s;
-    step = 2;
-    for (int b = u; b != 0; step++) {
+    // cumulative scores along the path: score[node[k]] = cost[k] + score[other[k]] + score[node[k-1]] (w for k = 0)
+    for (int k = threadIdx.x; k < n_listed; k += blockDim.x) s_term[k] = __ldcg(path_cost + k) + score[P.other[k]];
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    int32_t s = score[P.w];
+    for (int k = 0; k < n_listed; k++) {
+        s += s_term[k];
+        score[P.node[k]] = s;
+    }
+    for (int k = n_listed, b = P.node[LZG_APPLY_LISTED - 1]; k < P.n_steps; k++) {
         const int2 q = up[b];
-        s += __ldcg(path_cost + step) + score[q.y];
+        s += __ldcg(path_cost + k) + score[q.y];
         score[q.x] = s;
         b = q.x;
     }
     ctl[LZG_CTL_SCORE] = s;
+    // the topology patch (nni(), src/copy_number.cxx:279-284)
+    const int u = P.u, w = P.w, v = P.v, z = P.z, y = P.y;
     child0[v] = min(w, y);
     child1[v] = max(w, y);
     child0[u] = min(v, z);
