@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstring>
 #include <ctime>
+#include <cstdlib>
 #include <fstream>
 #include <iostream>
 #include <map>
@@ -249,7 +250,10 @@ void do_nni(const Args& a) {
             if (nm.empty() || (nm[0] >= '0' && nm[0] <= '9') || nm[0] == '.' || nm[0] == '+' || nm[0] == '-')
                 throw std::runtime_error("Failed to parse distance matrix.");
         }
-        const SeedTree nj = neighbor_joining_clearcut(D, set.names, (uint32_t)a.seed);
+        // LAZAC_NJ=host: the Clearcut restatement on the CPU (what the parity tests compare the GPU with)
+        const char* nj_env = getenv("LAZAC_NJ");
+        const SeedTree nj = nj_env && std::string(nj_env) == "host" ? neighbor_joining_clearcut(D, set.names, (uint32_t)a.seed)
+                                                                   : neighbor_joining_gpu(gpu.ctx, D, set.names, (uint32_t)a.seed);
         log_info("Outputting NJ tree to file: " + output_tree);
         {
             std::ofstream out(output_tree, std::ios::out);
@@ -426,12 +430,18 @@ void do_nni(const Args& a) {
     lzg_profiles_free(prof);
 }
 
-void do_nj(const Args& a) {  // helper: PREFIX_dist_matrix.txt -> Newick, no GPU
+void do_nj(const Args& a) {  // helper: PREFIX_dist_matrix.txt -> Newick; on the CPU unless LAZAC_NJ=gpu
     std::vector<std::string> names;
     std::vector<int32_t> D;
     read_matrix_txt(a.cn_profile, names, D);
     std::ofstream out(a.output, std::ios::out);
-    out << neighbor_joining_clearcut(D, names, (uint32_t)a.seed).newick();
+    const char* nj_env = getenv("LAZAC_NJ");
+    if (nj_env && std::string(nj_env) == "gpu") {
+        Gpu gpu(0);
+        out << neighbor_joining_gpu(gpu.ctx, D, names, (uint32_t)a.seed).newick();
+    } else {
+        out << neighbor_joining_clearcut(D, names, (uint32_t)a.seed).newick();
+    }
 }
 
 void do_bp(const Args& a) {  // helper: CSV -> names + breakpoint matrix (text), no GPU

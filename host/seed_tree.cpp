@@ -56,13 +56,8 @@ struct Joiner {
 
 }  // namespace
 
-SeedTree neighbor_joining_clearcut(const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed) {
-    const long n = (long)names.size();
-    if ((size_t)n * n != D.size()) throw std::runtime_error("distance matrix size mismatch");
-    SeedTree out;
-    if (n == 0) throw std::runtime_error("Failed to parse distance matrix.");
-
-    // ---- shuffle (NJ_shuffle_distance_matrix): position i of the working matrix is taxon perm[i]
+// NJ_shuffle_distance_matrix: position i of the working matrix is taxon perm[i].
+static std::vector<long> clearcut_shuffle(long n, uint32_t seed) {
     std::mt19937 mt(seed);
     std::vector<long> perm(n);
     for (long i = 0; i < n; i++) perm[i] = i;
@@ -70,6 +65,33 @@ SeedTree neighbor_joining_clearcut(const std::vector<int32_t>& D, const std::vec
         long k = i + draw_below(mt, n - i);
         if (k != i) std::swap(perm[i], perm[k]);
     }
+    return perm;
+}
+
+SeedTree neighbor_joining_gpu(lzg_ctx* ctx, const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed) {
+    const long n = (long)names.size();
+    if ((size_t)n * n != D.size()) throw std::runtime_error("distance matrix size mismatch");
+    if (n == 0) throw std::runtime_error("Failed to parse distance matrix.");
+    const std::vector<long> perm = clearcut_shuffle(n, seed);
+    std::vector<int32_t> p32(perm.begin(), perm.end()), left(2 * n - 1), right(2 * n - 1);
+    const int rc = lzg_nj_seed_tree(ctx, D.data(), (int32_t)n, p32.data(), left.data(), right.data());
+    if (rc != LZG_OK) throw std::runtime_error(std::string("lzg_nj_seed_tree: ") + lzg_last_error(ctx));
+    SeedTree out;
+    out.left.assign(left.begin(), left.end());
+    out.right.assign(right.begin(), right.end());
+    out.leaf_name.resize(2 * n - 1);
+    for (long i = 0; i < n; i++) out.leaf_name[i] = names[perm[i]];
+    out.root = (int)(2 * n - 2);
+    return out;
+}
+
+SeedTree neighbor_joining_clearcut(const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed) {
+    const long n = (long)names.size();
+    if ((size_t)n * n != D.size()) throw std::runtime_error("distance matrix size mismatch");
+    SeedTree out;
+    if (n == 0) throw std::runtime_error("Failed to parse distance matrix.");
+
+    const std::vector<long> perm = clearcut_shuffle(n, seed);
 
     Joiner J;
     J.n0 = n;

@@ -4,6 +4,8 @@
 #include <string>
 #include <vector>
 
+#include "lazac_b200.h"
+
 namespace lazac_host {
 
 struct SeedTree {
@@ -15,5 +17,8 @@ struct SeedTree {
 
 // D: n x n symmetric integer matrix, rows/columns in the order of `names`; seed = -s.
 SeedTree neighbor_joining_clearcut(const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed);
+
+// The same tree from the GPU (lzg_nj_seed_tree): the O(n^3) minimum scans run as device reductions.
+SeedTree neighbor_joining_gpu(lzg_ctx* ctx, const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed);
 
 }  // namespace lazac_host

@@ -126,11 +126,23 @@ int lzg_tree_ancestral(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t
 /* Work the REFERENCE's path algorithm does for the candidates of the last lzg_nni_best on this
  * tree: merges (= sum over candidates of depth(v)+1) and bytes read (= (merges + n_moves) * 2 * L). */
 int lzg_tree_last_nni_work(const lzg_tree* t, int64_t* merges, int64_t* bytes);
-/* Algorithmic bytes of the same call as executed here: candidates (10 L each: the intervals of w,
- * y, z, u and the UP interval of u; 6 L when u is the root) and the UP pass it had to run first
+/* Algorithmic bytes of the same call as executed here: work items (the two candidates of an edge
+ * (u, v) listed back to back are ONE item of 10 L bytes: the intervals of w, both children of v, u
+ * and the UP interval of u; 6 L when u is the root) and the UP pass that was run for it
  * (4 L per internal non-root node: read DOWN(sibling), write UP; + 2 L per heavy path for the UP
  * interval its head hangs off; 0 when the UP intervals were still valid). */
 int lzg_tree_last_nni_traffic(const lzg_tree* t, int64_t* cand_bytes, int64_t* up_bytes);
+
+/* ---- NJ seed tree ---------------------------------------------------
+ * Replaces the file hop + Clearcut run of do_nni, /root/reference/src/lazac.cxx:155-200
+ * (NJ_neighbor_joining, src/clearcut.cxx:925): neighbour joining on the integer matrix D (host,
+ * N x N, values < 2^24), float32 operation order, tie rule and index bookkeeping as the reference.
+ * The caller supplies the taxon shuffle (NJ_shuffle_distance_matrix, src/clearcut.cxx:1644, is
+ * MT19937 host logic): position i of the working matrix is taxon perm[i].
+ * left/right: int32 [2N-1], -1 for nodes 0 .. N-1 (the leaves, = shuffled positions), internal
+ * nodes N .. 2N-2 in creation order, the root is node 2N-2. */
+int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, const int32_t* perm, int32_t* left,
+                     int32_t* right);
 
 #ifdef __cplusplus
 }

@@ -52,6 +52,7 @@ SYMBOLS = [
     ("lzg_tree_last_candidate_score", _i, [_vp, _i32p]),
     ("lzg_tree_last_nni_work", _i, [_vp, _i64p, _i64p]),
     ("lzg_tree_last_nni_traffic", _i, [_vp, _i64p, _i64p]),
+    ("lzg_nj_seed_tree", _i, [_vp, _vp, _i32, _vp, _vp, _vp]),
 ]
 
 

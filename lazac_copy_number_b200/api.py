@@ -69,6 +69,17 @@ class Context:
         buf = (C.c_uint8 * max(n, 1)).from_address(p.value)
         return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
+    def nj_seed_tree(self, D, perm):
+        """Clearcut-exact neighbour joining of the integer matrix D on the GPU (the seed tree of
+        do_nni, src/lazac.cxx:155-200); perm = the taxon shuffle (position i holds taxon perm[i]).
+        Returns (left, right): int32 [2N-1], -1 for the N leaves, root = 2N-2."""
+        D = i32(D)
+        n = D.shape[0]
+        perm = i32(perm)
+        left, right = np.zeros(2 * n - 1, np.int32), np.zeros(2 * n - 1, np.int32)
+        self.check(self.lib.lzg_nj_seed_tree(self.h, ptr(D), n, ptr(perm), ptr(left), ptr(right)))
+        return left, right
+
     # -- reference-named entry points -------------------------------------------------------------
     def upload_profiles(self, bp):
         return Profiles(self, bp)

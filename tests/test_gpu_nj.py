@@ -1,0 +1,89 @@
+"""GPU: lzg_nj_seed_tree (Clearcut-exact neighbour joining on the device) against the host
+restatement of the reference's NJ (`lazac nj`, itself byte-identical to the reference CLI's
+PREFIX_nj_tree.newick on the golden matrices -- tests/test_host_cpu.py).  Integer matrices with
+many ties and with row sums beyond 2^24, so both the tie rule and the float32 summation order
+are exercised."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+LAZAC = os.path.join(ROOT, "host", "lazac")
+if not os.path.exists(LAZAC):
+    subprocess.run(["make", "-C", os.path.join(ROOT, "host")], check=False, stdout=subprocess.DEVNULL)
+
+
+def write_matrix(path, D):
+    """PREFIX_dist_matrix.txt as write_matrix_txt / the reference writes it (src/lazac.cxx:118-131)."""
+    n = len(D)
+    with open(path, "w") as f:
+        f.write("%d\n" % n)
+        for i in range(n):
+            f.write("c%05d " % i + " ".join(str(int(x)) for x in D[i]) + "\n")
+
+
+def nj_both(tmp_path, D, seed):
+    src = tmp_path / "m.txt"
+    write_matrix(src, D)
+    outs = []
+    for mode in ("host", "gpu"):
+        out = tmp_path / ("nj_%s.newick" % mode)
+        subprocess.run([LAZAC, "nj", str(src), "-s", str(seed), "-o", str(out)], check=True, env=dict(os.environ, LAZAC_NJ=mode))
+        outs.append(out.read_bytes())
+    return outs
+
+
+def l1_matrix(n, L, lo, hi, seed):
+    rng = np.random.default_rng(seed)
+    x = rng.integers(lo, hi + 1, size=(n, L))
+    return np.abs(x[:, None, :] - x[None, :, :]).sum(axis=2)
+
+
+@pytest.mark.parametrize("n,L,hi,seed", [(2, 5, 3, 0), (3, 5, 3, 1), (4, 6, 1, 2), (17, 12, 1, 3), (150, 40, 2, 4), (600, 30, 1, 5)])
+def test_nj_gpu_equals_host_on_tie_heavy_matrices(tmp_path, n, L, hi, seed):
+    host, gpu = nj_both(tmp_path, l1_matrix(n, L, 0, hi, seed), seed)
+    assert host == gpu
+
+
+def test_nj_gpu_equals_host_with_large_row_sums(tmp_path):
+    """Row sums far beyond 2^24: every float32 addition rounds, so the summation order matters."""
+    rng = np.random.default_rng(9)
+    n = 700
+    D = rng.integers(1, 1 << 20, size=(n, n))
+    D = np.triu(D, 1)
+    D = D + D.T
+    host, gpu = nj_both(tmp_path, D, 11)
+    assert host == gpu
+
+
+@pytest.mark.parametrize("matrix,seed,tree", [
+    ("ptx008_cli/PTX008_dist_matrix.txt", 0, "ptx008_cli/PTX008_nj_tree.newick"),
+    ("synth_cli/full_dist_matrix.txt", 3, "synth_cli/full_nj_tree.newick"),
+    ("synth_cli/greedy_dist_matrix.txt", 5, "synth_cli/greedy_nj_tree.newick"),
+])
+def test_nj_gpu_reproduces_the_reference_cli_files(tmp_path, matrix, seed, tree):
+    out = tmp_path / "nj.newick"
+    subprocess.run([LAZAC, "nj", os.path.join(GOLD, matrix), "-s", str(seed), "-o", str(out)], check=True,
+                   env=dict(os.environ, LAZAC_NJ="gpu"))
+    with open(os.path.join(GOLD, tree), "rb") as f:
+        assert out.read_bytes() == f.read()
+
+
+def test_nj_api_shapes_and_errors(ctx):
+    from lazac_copy_number_b200._capi import LazacGpuError
+    D = l1_matrix(9, 10, 0, 2, 1)
+    left, right = ctx.nj_seed_tree(D, np.arange(9))
+    assert (left[:9] == -1).all() and (right[:9] == -1).all()
+    kids = np.concatenate([left[9:], right[9:]])
+    assert sorted(kids.tolist()) == list(range(16))          # every node but the root is a child exactly once
+    with pytest.raises(LazacGpuError):
+        ctx.nj_seed_tree(D, np.zeros(9, np.int32))              # not a permutation
+    big = D.copy()
+    big[0, 1] = big[1, 0] = 1 << 24
+    with pytest.raises(LazacGpuError):
+        ctx.nj_seed_tree(big, np.arange(9))                     # not exact in float32
