@@ -276,10 +276,13 @@ def nni_section(ctx, args, peaks, peaks_kind):
     n_leaves, L = bp.shape
     gp = Profiles(ctx, bp)
     D = gp.distance_matrix()
-    c0, c1 = nj.neighbor_joining(D)
+    # the seed tree of do_nni (src/lazac.cxx:155-200): Clearcut-exact NJ on the GPU, seed-0 shuffle replaced by a numpy one
+    perm = np.random.default_rng(0).permutation(n_leaves).astype(np.int32)
+    t0 = time.perf_counter()
+    left, right = ctx.nj_seed_tree(D, perm)
+    nj_s = time.perf_counter() - t0
+    c0, c1, leaf_row = nj.tree_from_seed(left, right, perm)
     n = 2 * n_leaves - 1
-    leaf_row = np.full(n, -1, np.int32)
-    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
     t = Tree(ctx, gp, c0, c1, leaf_row)
     root = t.small_rectilinear()
     eu, ev = t.edges()
@@ -287,7 +290,8 @@ def nni_section(ctx, args, peaks, peaks_kind):
     moves = t.enumerate_moves(eu, ev, order)
     dep = nj.depths(c0, c1)
     r = nni_iterations(ctx, t, moves, order, args.steps, args.warmup)
-    out = nni_report(name, r, t, moves, dep, root, "NJ (numpy float64) of the GPU distance matrix", peaks, peaks_kind, n_leaves, L,
+    out = nni_report(name, r, t, moves, dep, root, "lzg_nj_seed_tree (Clearcut-exact NJ on the GPU, %.1f ms) of the GPU distance matrix" % (1e3 * nj_s),
+                     peaks, peaks_kind, n_leaves, L,
                      "tree state (%.1f MB incl. UP intervals) fits the 126 MB L2 at this size: the step is launch/latency bound, not HBM bound"
                      % (4 * n * L / 1e6))
     C_ = len(moves)
@@ -295,7 +299,7 @@ def nni_section(ctx, args, peaks, peaks_kind):
         # the reference's candidate loop (src/copy_number.cxx:347-366) on the same tree, 1 thread
         from oracle import Port, PortTree, have_ref
         leaf_bp = np.zeros((n, L), np.int32)
-        leaf_bp[n_leaves - 1:] = bp
+        leaf_bp[n_leaves - 1:] = bp[perm]
         if have_ref():
             from oracle.ref import Ref
             rt = Ref().tree(c0, c1, leaf_bp)

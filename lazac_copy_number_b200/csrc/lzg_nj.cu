@@ -78,7 +78,7 @@ k_nj_argmin(const float* __restrict__ m, int n0, int base, int size, const float
 // One join: NJ_compute_r + NJ_collapse + the index-0-to-b relabelling, a single CTA (O(size) work).
 __global__ void __launch_bounds__(1024)
 k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node,
-          float* __restrict__ cv, unsigned long long* __restrict__ key, int32_t* __restrict__ left, int32_t* __restrict__ right, int joined) {
+          unsigned long long* __restrict__ key, int32_t* __restrict__ left, int32_t* __restrict__ right, int joined) {
     __shared__ int s_a, s_b;
     __shared__ float s_a2, s_b2;
     const int tid = threadIdx.x;
@@ -101,26 +101,38 @@ k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__
     const float denom = (float)(size - 3);
     float* row_a = m + (size_t)(a + base) * n0 + base;
     float* row_b = m + (size_t)(b + base) * n0 + base;
-    // every index but a: two subtractions (NJ_compute_r), the joined distance, one addition (NJ_collapse)
-    for (int i = tid; i < size; i += blockDim.x) {
-        if (i == a) continue;
-        const float da = row_a[i], db = row_b[i];  // d(b, b) = 0 at i == b, as the reference reads it
-        const float c = (float)((double)__fadd_rn(__fsub_rn(da, a2), __fsub_rn(db, b2)) / 2.0);
-        cv[i] = c;
-        row_a[i] = c;
-        m[(size_t)(i + base) * n0 + a + base] = c;
-        float ri = __fsub_rn(__fsub_rn(r[i + base], da), db);
-        ri = __fadd_rn(ri, c);
-        r[i + base] = ri;
-        r2[i + base] = __fdiv_rn(ri, denom);
+    // Every index but a: two subtractions (NJ_compute_r), the joined distance, one addition
+    // (NJ_collapse).  Indices are visited in the order the reference sums the joined row's r --
+    // i = a+1 .. size-1, then 0 .. a-1 -- in chunks of blockDim.x staged in shared memory, so
+    // that thread 0 adds chunk k one float32 at a time while the others already compute chunk k+1.
+    __shared__ float s_cv[2][1024];
+    float sum = 0.0f;
+    const int n_terms = size - 1;
+    for (int p0 = 0, buf = 0; p0 < n_terms; p0 += blockDim.x, buf ^= 1) {
+        const int p = p0 + tid;
+        if (p < n_terms) {
+            int i = a + 1 + p;
+            if (i >= size) i -= size;
+            const float da = row_a[i], db = row_b[i];  // d(b, b) = 0 at i == b, as the reference reads it
+            const float c = (float)((double)__fadd_rn(__fsub_rn(da, a2), __fsub_rn(db, b2)) / 2.0);
+            s_cv[buf][tid] = c;
+            row_a[i] = c;
+            m[(size_t)(i + base) * n0 + a + base] = c;
+            float ri = __fsub_rn(__fsub_rn(r[i + base], da), db);
+            ri = __fadd_rn(ri, c);
+            r[i + base] = ri;
+            r2[i + base] = __fdiv_rn(ri, denom);
+        }
+        __syncthreads();  // chunk staged; also: thread 0 has finished adding the previous chunk of this buffer's twin
+        if (tid == 0) {
+            const int cnt = min((int)blockDim.x, n_terms - p0);
+#pragma unroll 8
+            for (int q = 0; q < cnt; q++) sum = __fadd_rn(sum, s_cv[buf][q]);
+        }
     }
-    __syncthreads();
-    if (tid == 0) {  // r of the joined row: the reference's summation order, one float32 add at a time
-        float s = 0.0f;
-        for (int i = a + 1; i < size; i++) s = __fadd_rn(s, cv[i]);
-        for (int i = 0; i < a; i++) s = __fadd_rn(s, cv[i]);
-        r[a + base] = s;
-        r2[a + base] = __fdiv_rn(s, denom);
+    if (tid == 0) {
+        r[a + base] = sum;
+        r2[a + base] = __fdiv_rn(sum, denom);
         node[a + base] = joined;
     }
     __syncthreads();
@@ -165,7 +177,7 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     }
     int32_t *d_D = nullptr, *d_perm = nullptr, *d_left = nullptr, *d_right = nullptr;
     int* d_node = nullptr;
-    float *d_m = nullptr, *d_r = nullptr, *d_r2 = nullptr, *d_cv = nullptr;
+    float *d_m = nullptr, *d_r = nullptr, *d_r2 = nullptr;
     unsigned long long* d_key = nullptr;
     const size_t nn = (size_t)n * n;
     auto release = [&]() {
@@ -177,7 +189,6 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
         lzg_dev_free(ctx, d_m);
         lzg_dev_free(ctx, d_r);
         lzg_dev_free(ctx, d_r2);
-        lzg_dev_free(ctx, d_cv);
         lzg_dev_free(ctx, d_key);
     };
     cudaError_t e = lzg_dev_alloc(ctx, (void**)&d_D, sizeof(int32_t) * nn);
@@ -188,7 +199,6 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_node, sizeof(int) * n);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r, sizeof(float) * n);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r2, sizeof(float) * n);
-    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_cv, sizeof(float) * n);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_key, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_D, D_host, sizeof(int32_t) * nn, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_perm, perm, sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream);
@@ -205,7 +215,7 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     for (int size = n; size > 2; size--, base++, joined++) {
         const int grid = std::max(1, std::min(size - 1, ctx->sm_count * 8));
         k_nj_argmin<<<grid, 256, 0, ctx->stream>>>(d_m, n, base, size, d_r2, d_key);
-        k_nj_join<<<1, 1024, 0, ctx->stream>>>(d_m, n, base, size, d_r, d_r2, d_node, d_cv, d_key, d_left, d_right, joined);
+        k_nj_join<<<1, 1024, 0, ctx->stream>>>(d_m, n, base, size, d_r, d_r2, d_node, d_key, d_left, d_right, joined);
         ctx->launches += 2;
     }
     k_nj_finish<<<1, 1, 0, ctx->stream>>>(d_node, base, d_left, d_right, joined);

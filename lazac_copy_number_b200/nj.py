@@ -1,7 +1,8 @@
 """Host-side neighbour joining for seed trees of synthetic benchmarks (numpy, float64).
 
-This is NOT the byte-exact clearcut restatement (that lives in the C++ host, host/nj_clearcut.*);
-it only provides an NJ-shaped seed topology (deep, unbalanced, like the reference's
+This is NOT the byte-exact Clearcut restatement (that is lzg_nj_seed_tree on the GPU and
+host/seed_tree.cpp on the CPU; tree_from_seed below adapts the GPU's output); neighbor_joining
+only provides an NJ-shaped seed topology (deep, unbalanced, like the reference's
 /root/reference/src/clearcut.cxx:925 NJ_neighbor_joining produces) for bench.py and tests, where
 the GPU path and the oracle are both driven from the same topology arrays.
 """
@@ -53,6 +54,26 @@ def neighbor_joining(D):
     assert len(rest) == 2 and nxt == 0
     child0[0], child1[0] = min(rest), max(rest)
     return child0, child1
+
+
+def tree_from_seed(left, right, perm):
+    """(left, right) of lzg_nj_seed_tree (Context.nj_seed_tree: leaves 0 .. n-1 = shuffled positions,
+    internal nodes n .. 2n-2 in creation order, root last) -> (child0, child1, leaf_row) in the
+    layout lzg_tree_create takes: root = node 0, child0 < child1, leaf at node id (n-1) + position
+    with leaf_row = the taxon (profile row) at that position."""
+    total = len(left)
+    n = (total + 1) // 2
+    new_id = np.empty(total, np.int64)
+    new_id[:n] = n - 1 + np.arange(n)
+    new_id[n:] = total - 1 - np.arange(n, total)         # the root 2n-2 becomes 0
+    child0 = np.full(total, -1, np.int32)
+    child1 = np.full(total, -1, np.int32)
+    a, b = new_id[left[n:]], new_id[right[n:]]
+    child0[new_id[n:]] = np.minimum(a, b)
+    child1[new_id[n:]] = np.maximum(a, b)
+    leaf_row = np.full(total, -1, np.int32)
+    leaf_row[n - 1:] = np.asarray(perm, np.int32)
+    return child0, child1, leaf_row
 
 
 def depths(child0, child1):

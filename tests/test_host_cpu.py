@@ -54,3 +54,15 @@ def test_usage_errors(lazac):
     assert r.returncode == 1
     r = subprocess.run([lazac, "bp", "/nonexistent.csv", "-o", "/dev/null"], capture_output=True, text=True)
     assert r.returncode == 2 and "Cannot open" in r.stderr
+
+
+def test_tree_from_seed_layout():
+    """nj.tree_from_seed: lzg_nj_seed_tree's (left, right) -> lzg_tree_create's arrays."""
+    import numpy as np
+    from lazac_copy_number_b200 import nj
+    left = np.array([-1, -1, -1, 0, 3], np.int32)    # node 3 = (leaf 0, leaf 2), root 4 = (3, leaf 1)
+    right = np.array([-1, -1, -1, 2, 1], np.int32)
+    c0, c1, leaf_row = nj.tree_from_seed(left, right, [2, 0, 1])
+    assert c0.tolist() == [1, 2, -1, -1, -1] and c1.tolist() == [3, 4, -1, -1, -1]
+    assert leaf_row.tolist() == [-1, -1, 2, 0, 1]
+    assert nj.depths(c0, c1).tolist() == [0, 1, 2, 1, 2]
