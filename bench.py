@@ -265,6 +265,21 @@ def nni_report(name, r, t, moves, dep, root, seed_tree, peaks, peaks_kind, n_lea
     }
 
 
+def nj_seed(ctx, gp, n_leaves):
+    """The seed tree of do_nni (src/lazac.cxx:155-200) for the profiles gp: GPU distance matrix, then
+    Clearcut-exact NJ on the GPU (the MT19937 taxon shuffle replaced by a numpy one, same on every rank)."""
+    from lazac_copy_number_b200 import nj
+    t0 = time.perf_counter()
+    D = gp.distance_matrix()
+    t1 = time.perf_counter()
+    perm = np.random.default_rng(0).permutation(n_leaves).astype(np.int32)
+    left, right = ctx.nj_seed_tree(D, perm)
+    t2 = time.perf_counter()
+    c0, c1, leaf_row = nj.tree_from_seed(left, right, perm)
+    return c0, c1, leaf_row, "lzg_nj_seed_tree (Clearcut-exact NJ on the GPU, %.0f ms) of the GPU distance matrix (%.0f ms to the host)" % (
+        1e3 * (t2 - t1), 1e3 * (t1 - t0))
+
+
 def nni_section(ctx, args, peaks, peaks_kind):
     """cfg4: hill-climb iterations on an NJ seed tree (1 GPU)."""
     from lazac_copy_number_b200 import nj, synth
@@ -333,10 +348,8 @@ def nni_section_large(ctx, args, peaks, peaks_kind):
     bp = bp_int8_chunked(prof["cn"], prof["seg"])
     n_leaves, L = bp.shape
     n = 2 * n_leaves - 1
-    c0, c1 = synth.perturb_tree(prof["child0"], prof["child1"], n_leaves // 5, np.random.default_rng(1))
-    leaf_row = np.full(n, -1, np.int32)
-    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
     gp = Profiles(ctx, bp)
+    c0, c1, leaf_row, seed_note = nj_seed(ctx, gp, n_leaves)
     t = Tree(ctx, gp, c0, c1, leaf_row)
     root = t.small_rectilinear()
     eu, ev = t.edges()
@@ -344,8 +357,7 @@ def nni_section_large(ctx, args, peaks, peaks_kind):
     moves = t.enumerate_moves(eu, ev, order)
     dep = nj.depths(c0, c1)
     r = nni_iterations(ctx, t, moves, order, min(args.steps, 10), args.warmup)
-    out = nni_report("cfg5 on 1 GPU", r, t, moves, dep, root,
-                     "generating tree + %d random NNIs (NJ at this n is host-side O(n^3): SURVEY.md 8(f) rank 1)" % (n_leaves // 5),
+    out = nni_report("cfg5 on 1 GPU", r, t, moves, dep, root, seed_note,
                      peaks, peaks_kind, n_leaves, L, "tree state %.1f GB incl. UP intervals" % (4 * n * L / 1e9))
     t.free()
     gp.free()
@@ -366,10 +378,8 @@ def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
     bp = bp_int8_chunked(prof["cn"], prof["seg"])
     n_leaves, L = bp.shape
     n = 2 * n_leaves - 1
-    c0, c1 = synth.perturb_tree(prof["child0"], prof["child1"], n_leaves // 5, np.random.default_rng(1))
-    leaf_row = np.full(n, -1, np.int32)
-    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
     gp = Profiles(ctx, bp)
+    c0, c1, leaf_row, seed_note = nj_seed(ctx, gp, n_leaves)
     t = Tree(ctx, gp, c0, c1, leaf_row)
     root = t.small_rectilinear()
     eu, ev = t.edges()
@@ -409,7 +419,7 @@ def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
         "metric": "nni_candidates_scored_per_sec", "value": C_ * args.steps / tot, "unit": "candidates/s", "n_gpus": world,
         "ms_per_step": 1e3 * tot / args.steps, "scaling": "strong",
         "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_,
-                   "seed_tree": "generating tree + %d random NNIs (NJ at this n is host-side O(n^3): SURVEY.md 8(f) rank 1)" % (n_leaves // 5),
+                   "seed_tree": seed_note,
                    "pass": "per rank: UP pass (replicated) + its slice of the candidates + argmin; then one 8-byte NCCL min all-reduce",
                    "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
                    "root_score": int(root), "best_index": int(gi), "best_score": None if gs is None else int(gs),

@@ -115,6 +115,8 @@ int lzg_shutdown(lzg_ctx* ctx) {
     if (!ctx) return LZG_ERR_ARG;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    for (auto& sc : ctx->schedules) lzg_dev_free(ctx, sc.d_block);
+    cudaStreamSynchronize(ctx->stream);
     if (ctx->flush_buf) cudaFree(ctx->flush_buf);
     if (ctx->d_flag) cudaFree(ctx->d_flag);
     if (ctx->d_scratch) cudaFree(ctx->d_scratch);
@@ -254,7 +256,6 @@ int lzg_profiles_free(lzg_profiles* p) {
     lzg_ctx* ctx = p->ctx;
     cudaSetDevice(ctx->device);
     // stream-ordered frees: no synchronisation, the blocks go back to the pool
-    for (auto& sc : p->schedules) lzg_dev_free(ctx, sc.d_block);
     lzg_dev_free(ctx, p->d_D);
     lzg_dev_free(ctx, p->d);
     delete p;

@@ -10,6 +10,19 @@
 
 #define LZG_BIAS 128  // int8 value v is stored as the byte v + 128 (exact unsigned abs-diff / min / max)
 
+// Persistent-grid work schedule of the distance kernel for one (tile size, shard) (lzg_distance.cu).
+struct lzg_schedule {
+    int n = 0, l_pad = 0;           // the input shape it was built for (schedules are cached per context)
+    int bm = 0, shard = 0, n_shards = 0, row_lo = 0, row_hi = 0;
+    int n_ctas = 0, n_segs = 0, n_split = 0;
+    int64_t pairs = 0;
+    void* d_block = nullptr;        // one pooled allocation holding the three arrays below
+    size_t bytes = 0;
+    void* d_segs = nullptr;         // lzg_seg[n_segs]
+    int32_t* d_seg_off = nullptr;   // [n_ctas + 1]
+    int2* d_split = nullptr;        // tiles accumulated with atomics (zeroed first)
+};
+
 struct lzg_ctx {
     int device = 0;
     int sm_count = 148;
@@ -26,6 +39,7 @@ struct lzg_ctx {
     size_t d_scratch_ints = 0;
     cudaStream_t copy_stream = nullptr;  // D2H of finished row groups while later groups compute
     cudaEvent_t ev_group = nullptr;
+    std::vector<lzg_schedule> schedules;  // distance schedules by (shape, tile, shard); freed at shutdown
 };
 
 // Stream-ordered device allocation from the device's default memory pool, whose release threshold
@@ -38,18 +52,6 @@ inline void lzg_dev_free(lzg_ctx* ctx, void* p) {
     if (p) cudaFreeAsync(p, ctx->stream);
 }
 
-// Persistent-grid work schedule of the distance kernel for one (tile size, shard) (lzg_distance.cu).
-struct lzg_schedule {
-    int bm = 0, shard = 0, n_shards = 0, row_lo = 0, row_hi = 0;
-    int n_ctas = 0, n_segs = 0, n_split = 0;
-    int64_t pairs = 0;
-    void* d_block = nullptr;        // one pooled allocation holding the three arrays below
-    size_t bytes = 0;
-    void* d_segs = nullptr;         // lzg_seg[n_segs]
-    int32_t* d_seg_off = nullptr;   // [n_ctas + 1]
-    int2* d_split = nullptr;        // tiles accumulated with atomics (zeroed first)
-};
-
 struct lzg_profiles {
     lzg_ctx* ctx = nullptr;
     int32_t n = 0, L = 0;
@@ -57,7 +59,6 @@ struct lzg_profiles {
     uint8_t* d = nullptr;          // [n_pad][l_pad]
     size_t d_bytes = 0;
     int32_t* d_D = nullptr;        // lazily allocated N x N result used by the host-output entry points
-    std::vector<lzg_schedule> schedules;
 };
 
 int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuccess);

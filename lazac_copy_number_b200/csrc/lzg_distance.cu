@@ -342,8 +342,8 @@ constexpr int dist_smem_bytes() {
 // stage measured on cfg2).  The smallest feasible per-CTA budget is found by bisection.
 const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slots_per_sm, int shard, int n_shards,
                                  int row_lo, int row_hi, int* status) {
-    for (auto& sc : p->schedules)
-        if (sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
+    for (auto& sc : ctx->schedules)
+        if (sc.n == p->n && sc.l_pad == p->l_pad && sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
     const int R = (p->n + bm - 1) / bm;
     const int K = p->l_pad / 16;  // chunks per row
     std::vector<int2> tiles;
@@ -359,6 +359,8 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
         }
     }
     lzg_schedule sc;
+    sc.n = p->n;
+    sc.l_pad = p->l_pad;
     sc.bm = bm;
     sc.shard = shard;
     sc.n_shards = n_shards;
@@ -442,8 +444,12 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
         sc.d_seg_off = reinterpret_cast<int32_t*>((uint8_t*)sc.d_block + o_off);
         sc.d_split = reinterpret_cast<int2*>((uint8_t*)sc.d_block + o_split);
     }
-    p->schedules.push_back(sc);
-    return &p->schedules.back();
+    if (ctx->schedules.size() >= 64) {  // a small cache: same-shape matrices reuse their schedule
+        lzg_dev_free(ctx, ctx->schedules.front().d_block);
+        ctx->schedules.erase(ctx->schedules.begin());
+    }
+    ctx->schedules.push_back(sc);
+    return &ctx->schedules.back();
 }
 
 template <int BM, int BN, int STAGES>

@@ -9,7 +9,7 @@ timeout 600 python bench.py --steps 20 --warmup 3 > gpurun_out/bench_cfg2.json 2
 timeout 600 python bench.py --workload cfg3 --steps 5 --warmup 3 --no-nni --no-cpu > gpurun_out/bench_cfg3_1gpu.json 2> gpurun_out/bench_cfg3.err; echo "bench cfg3 rc=$?"
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "ref rc=$?"
 timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 &&
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/ncu_launches.log 2>&1
 echo "ncu rc=$?"
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log | tail -2; cat gpurun_out/bench_cfg2.json; cat gpurun_out/bench_cfg3_1gpu.json; cat gpurun_out/bench_reference.json
