@@ -186,8 +186,21 @@ void write_matrix_csv(const std::string& path, const std::vector<std::string>& n
     }
 }
 
+// CSV -> breakpoint set; LAZAC_TIMING=1 logs how long the two steps took.
+BreakpointSet ingest(const std::string& path) {
+    const auto t0 = std::chrono::steady_clock::now();
+    const std::map<std::string, CellProfile> cells = read_cn_profiles(path);
+    const auto t1 = std::chrono::steady_clock::now();
+    BreakpointSet set = to_breakpoint_set(cells);
+    const auto t2 = std::chrono::steady_clock::now();
+    if (getenv("LAZAC_TIMING"))
+        fprintf(stderr, "[lazac timing] read_cn_profiles %.0f ms, to_breakpoint_set %.0f ms\n", std::chrono::duration<double, std::milli>(t1 - t0).count(),
+                std::chrono::duration<double, std::milli>(t2 - t1).count());
+    return set;
+}
+
 void do_distance(const Args& a) {
-    const BreakpointSet set = to_breakpoint_set(read_cn_profiles(a.cn_profile));
+    const BreakpointSet set = ingest(a.cn_profile);
     Gpu gpu(a.device);
     const std::vector<int32_t> D = build_distance_matrix(gpu, set, nullptr);
     write_matrix_csv(a.output + "_dist_matrix.csv", set.names, D);
@@ -231,7 +244,7 @@ std::string scores_text(const std::vector<int>& v) {  // pprint compact: [a, b, 
 
 void do_nni(const Args& a) {
     /* Load copy number profiles */
-    const BreakpointSet set = to_breakpoint_set(read_cn_profiles(a.cn_profile));
+    const BreakpointSet set = ingest(a.cn_profile);
     const int n_cells = (int)set.names.size();
     Gpu gpu(a.device);
     lzg_profiles* prof = nullptr;
@@ -399,29 +412,29 @@ void do_nni(const Args& a) {
     {
         std::ofstream out(a.output + "_ancestral_cn_profile.csv", std::ios::out);
         out << "node,chrom,allele,start,end,cn\n";
+        // every node is labelled over the same positions: one segment order, one ",chrom,allele,start,end," per output row
+        const SegmentOrder order = make_segment_order(set.bins);
+        std::vector<std::string> mid(L);
+        for (int i = 0; i < L; i++) {
+            const GenomicBin& b = set.bins[order.perm[i]];
+            mid[i] = "," + b.chromosome + "," + b.allele + "," + std::to_string(b.start) + "," + std::to_string(b.end) + ",";
+        }
         std::vector<int> bp(L), cn;
-        std::vector<GenomicBin> bins;
         std::string block;
+        char num[16];
         for (int k = 0; k < n; k++) {
             const int32_t* row = labels.data() + (size_t)old_id[k] * L;
             bp.assign(row, row + L);
-            copynumber_transform(bp, set.bins, cn, bins);
+            copynumber_transform(bp, set.bins, order, cn, nullptr);
             block.clear();
             for (int i = 0; i < L; i++) {
                 block += names[k];
-                block += ',';
-                block += bins[i].chromosome;
-                block += ',';
-                block += bins[i].allele;
-                block += ',';
-                block += std::to_string(bins[i].start);
-                block += ',';
-                block += std::to_string(bins[i].end);
-                block += ',';
-                block += std::to_string(cn[i]);
+                block += mid[i];
+                const int len = snprintf(num, sizeof num, "%d", cn[i]);
+                block.append(num, (size_t)len);
                 block += '\n';
             }
-            out << block;
+            out.write(block.data(), (std::streamsize)block.size());
         }
     }
     log_info("search: " + std::to_string(stats.passes) + " neighbourhood passes, " + std::to_string(stats.candidates) +
@@ -445,7 +458,7 @@ void do_nj(const Args& a) {  // helper: PREFIX_dist_matrix.txt -> Newick; on the
 }
 
 void do_bp(const Args& a) {  // helper: CSV -> names + breakpoint matrix (text), no GPU
-    const BreakpointSet set = to_breakpoint_set(read_cn_profiles(a.cn_profile));
+    const BreakpointSet set = ingest(a.cn_profile);
     std::ofstream out(a.output, std::ios::out);
     out << set.names.size() << " " << set.L << "\n";
     for (size_t i = 0; i < set.names.size(); i++) {

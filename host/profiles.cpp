@@ -3,7 +3,9 @@
 
 #include <algorithm>
 #include <fstream>
+#include <cstring>
 #include <numeric>
+#include <sstream>
 #include <stdexcept>
 
 namespace lazac_host {
@@ -81,9 +83,8 @@ void segment_order(const std::vector<GenomicBin>& bins, std::vector<size_t>& per
 
 }  // namespace
 
-std::map<std::string, CellProfile> read_cn_profiles(const std::string& path) {
-    std::ifstream in(path, std::ios::binary);
-    if (!in) throw std::runtime_error("Cannot open file " + path);
+// The general reader: any RFC 4180 file, one character at a time.
+static std::map<std::string, CellProfile> read_cn_profiles_stream(std::istream& in, const std::string& path) {
     std::vector<std::string> rec;
     if (!next_record(in, rec)) throw std::runtime_error("empty CSV: " + path);
     auto column = [&](const char* name) {
@@ -110,13 +111,125 @@ std::map<std::string, CellProfile> read_cn_profiles(const std::string& path) {
     return cells;
 }
 
-void breakpoint_transform(const CellProfile& in, std::vector<int>& bp, std::vector<GenomicBin>& bins) {
-    std::vector<size_t> perm, seg_end;
-    segment_order(in.bins, perm, seg_end);
+// Plain decimal integer in [p, e): the common case of std::stoi; anything else goes through to_int.
+static int fast_int(const char* p, const char* e, const char* column) {
+    const char* q = p;
+    bool neg = false;
+    if (q < e && (*q == '-' || *q == '+')) neg = *q++ == '-';
+    long v = 0;
+    const char* digits = q;
+    while (q < e && *q >= '0' && *q <= '9' && q - digits < 9) v = v * 10 + (*q++ - '0');
+    if (q == e && q > digits) return (int)(neg ? -v : v);
+    return to_int(std::string(p, e), column);
+}
+
+std::map<std::string, CellProfile> read_cn_profiles(const std::string& path) {
+    std::ifstream in(path, std::ios::binary);
+    if (!in) throw std::runtime_error("Cannot open file " + path);
+    std::string buf;
+    in.seekg(0, std::ios::end);
+    const std::streamoff size = in.tellg();
+    in.seekg(0, std::ios::beg);
+    if (size > 0) {
+        buf.resize((size_t)size);
+        in.read(&buf[0], size);
+        buf.resize((size_t)in.gcount());
+    }
+    // Quotes (or a bare CR) are rare in these files: they take the general reader.  Everything else is
+    // split in place -- one pass, no per-field strings, the cell looked up only when the node changes.
+    bool plain = buf.find('"') == std::string::npos;
+    for (size_t q = buf.find('\r'); plain && q != std::string::npos; q = buf.find('\r', q + 1))
+        if (q + 1 >= buf.size() || buf[q + 1] != '\n') plain = false;
+    if (!plain) {
+        std::istringstream ss(buf);
+        return read_cn_profiles_stream(ss, path);
+    }
+    const char* p = buf.data();
+    const char* const end = p + buf.size();
+    auto next_line = [&](const char*& lo, const char*& hi) {  // [lo, hi) without the line terminator
+        if (p >= end) return false;
+        lo = p;
+        const char* nl = (const char*)memchr(p, '\n', (size_t)(end - p));
+        hi = nl ? nl : end;
+        p = nl ? nl + 1 : end;
+        if (hi > lo && hi[-1] == '\r') hi--;
+        return true;
+    };
+    const char *lo, *hi;
+    if (!next_line(lo, hi)) throw std::runtime_error("empty CSV: " + path);
+    std::vector<std::string> header;
+    for (const char* f = lo;;) {
+        const char* c = (const char*)memchr(f, ',', (size_t)(hi - f));
+        header.emplace_back(f, c ? c : hi);
+        if (!c) break;
+        f = c + 1;
+    }
+    auto column = [&](const char* name) {
+        auto it = std::find(header.begin(), header.end(), name);
+        if (it == header.end()) throw std::runtime_error(std::string("Can't find a column named ") + name);
+        return (size_t)(it - header.begin());
+    };
+    const size_t c_node = column("node"), c_chrom = column("chrom"), c_start = column("start"), c_end = column("end"),
+                 c_cn = column("cn_a");
+    const size_t width = header.size();
+    std::map<std::string, CellProfile> cells;
+    std::string last_name;
+    CellProfile* cell = nullptr;
+    std::vector<std::pair<const char*, const char*>> f(width);
+    const std::string allele = "cn_a";
+    size_t rows_per_cell = 0;
+    while (p < end) {
+        // one scan of the line: field boundaries and the terminator together (lines are ~25 bytes)
+        size_t nf = 0;
+        const char* s0 = p;
+        const char* q = p;
+        for (; q < end && *q != '\n'; q++) {
+            if (*q == ',') {
+                if (nf < width) f[nf] = {s0, q};
+                nf++;
+                s0 = q + 1;
+            }
+        }
+        const char* hi2 = q;
+        p = q < end ? q + 1 : end;
+        if (hi2 > s0 && hi2[-1] == '\r') hi2--;
+        if (nf == 0 && hi2 == s0) continue;  // blank line
+        if (nf < width) f[nf] = {s0, hi2};
+        nf++;
+        if (nf < width) throw std::runtime_error("short CSV row in " + path);
+        const size_t name_len = (size_t)(f[c_node].second - f[c_node].first);
+        if (!cell || name_len != last_name.size() || memcmp(f[c_node].first, last_name.data(), name_len) != 0) {
+            if (cell) rows_per_cell = std::max(rows_per_cell, cell->cn.size());
+            last_name.assign(f[c_node].first, name_len);
+            cell = &cells[last_name];
+            if (cell->cn.empty() && rows_per_cell) {  // the cells of a file have the same number of bins
+                cell->cn.reserve(rows_per_cell);
+                cell->bins.reserve(rows_per_cell);
+            }
+        }
+        cell->bins.emplace_back();
+        GenomicBin& b = cell->bins.back();
+        b.chromosome.assign(f[c_chrom].first, f[c_chrom].second);
+        b.allele = allele;
+        b.start = fast_int(f[c_start].first, f[c_start].second, "start");
+        b.end = fast_int(f[c_end].first, f[c_end].second, "end");
+        cell->cn.push_back(fast_int(f[c_cn].first, f[c_cn].second, "cn_a"));
+    }
+    return cells;
+}
+
+SegmentOrder make_segment_order(const std::vector<GenomicBin>& bins) {
+    SegmentOrder o;
+    segment_order(bins, o.perm, o.seg_end);
+    return o;
+}
+
+void breakpoint_transform(const CellProfile& in, const SegmentOrder& o, std::vector<int>& bp, std::vector<GenomicBin>& bins) {
+    const std::vector<size_t>& perm = o.perm;
     bp.resize(perm.size());
     bins.resize(perm.size());
     size_t lo = 0;
-    for (size_t hi : seg_end) {
+    for (size_t hi : o.seg_end) {
         for (size_t k = lo; k < hi; k++) {
             const int v = in.cn[perm[k]];
             if (k == lo) bp[k] = v - 2;
@@ -128,30 +241,53 @@ void breakpoint_transform(const CellProfile& in, std::vector<int>& bp, std::vect
     }
 }
 
-void copynumber_transform(const std::vector<int>& bp, const std::vector<GenomicBin>& bins, std::vector<int>& cn,
-                          std::vector<GenomicBin>& out_bins) {
-    std::vector<size_t> perm, seg_end;
-    segment_order(bins, perm, seg_end);
+void breakpoint_transform(const CellProfile& in, std::vector<int>& bp, std::vector<GenomicBin>& bins) {
+    breakpoint_transform(in, make_segment_order(in.bins), bp, bins);
+}
+
+void copynumber_transform(const std::vector<int>& bp, const std::vector<GenomicBin>& bins, const SegmentOrder& o, std::vector<int>& cn,
+                          std::vector<GenomicBin>* out_bins) {
+    const std::vector<size_t>& perm = o.perm;
     cn.resize(perm.size());
-    out_bins.resize(perm.size());
+    if (out_bins) out_bins->resize(perm.size());
     size_t lo = 0;
-    for (size_t hi : seg_end) {
+    for (size_t hi : o.seg_end) {
         for (size_t k = lo; k < hi; k++) {
             const int v = bp[perm[k]];
             if (k == lo) cn[k] = v + 2;
             else if (k == hi - 1) cn[k] = 2 - v;
             else cn[k] = v + cn[k - 1];
-            out_bins[k] = bins[perm[k]];
+            if (out_bins) (*out_bins)[k] = bins[perm[k]];
         }
         lo = hi;
     }
 }
 
+void copynumber_transform(const std::vector<int>& bp, const std::vector<GenomicBin>& bins, std::vector<int>& cn,
+                          std::vector<GenomicBin>& out_bins) {
+    copynumber_transform(bp, bins, make_segment_order(bins), cn, &out_bins);
+}
+
+static bool same_bins(const std::vector<GenomicBin>& a, const std::vector<GenomicBin>& b) {
+    if (a.size() != b.size()) return false;
+    for (size_t i = 0; i < a.size(); i++)
+        if (a[i].start != b[i].start || a[i].end != b[i].end || a[i].chromosome != b[i].chromosome || a[i].allele != b[i].allele) return false;
+    return true;
+}
+
 BreakpointSet to_breakpoint_set(const std::map<std::string, CellProfile>& cells) {
     BreakpointSet out;
     std::vector<int> bp;
+    // cells normally list the same bins in the same order: the segment order (a map + stable sorts on
+    // strings) is then computed once and reused
+    const CellProfile* order_of = nullptr;
+    SegmentOrder order;
     for (const auto& kv : cells) {
-        breakpoint_transform(kv.second, bp, out.bins);
+        if (!order_of || !same_bins(order_of->bins, kv.second.bins)) {
+            order = make_segment_order(kv.second.bins);
+            order_of = &kv.second;
+        }
+        breakpoint_transform(kv.second, order, bp, out.bins);
         if (out.names.empty()) out.L = (int)bp.size();
         if ((int)bp.size() != out.L)
             throw std::runtime_error("cell '" + kv.first + "' has " + std::to_string(bp.size()) + " bins, expected " +

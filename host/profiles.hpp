@@ -35,10 +35,23 @@ struct BreakpointSet {
 // convert_to_breakpoint_profile(cn, 2) for every cell.
 BreakpointSet to_breakpoint_set(const std::map<std::string, CellProfile>& cells);
 
+// Position order of convert_to_breakpoint_profile / convert_to_copynumber_profile: positions grouped
+// by (chromosome, allele) in std::map order, each group stable-sorted by bin (src/copy_number.cxx:28-41).
+struct SegmentOrder {
+    std::vector<size_t> perm;      // output position -> input position
+    std::vector<size_t> seg_end;   // end of every segment in output positions
+};
+SegmentOrder make_segment_order(const std::vector<GenomicBin>& bins);
+
 // Per (chromosome, allele) segment: bp[0] = cn[0] - 2, bp[i] = cn[i] - cn[i-1], bp[last] = 2 - cn[last].
 void breakpoint_transform(const CellProfile& in, std::vector<int>& bp, std::vector<GenomicBin>& bins);
 // Inverse with the same first/last rules, for one labelled vector over `bins`.
 void copynumber_transform(const std::vector<int>& bp, const std::vector<GenomicBin>& bins, std::vector<int>& cn,
                           std::vector<GenomicBin>& out_bins);
+
+// The same two with a precomputed order (one order serves every cell / node over the same bins).
+void breakpoint_transform(const CellProfile& in, const SegmentOrder& order, std::vector<int>& bp, std::vector<GenomicBin>& bins);
+void copynumber_transform(const std::vector<int>& bp, const std::vector<GenomicBin>& bins, const SegmentOrder& order, std::vector<int>& cn,
+                          std::vector<GenomicBin>* out_bins);
 
 }  // namespace lazac_host

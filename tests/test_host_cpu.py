@@ -66,3 +66,38 @@ def test_tree_from_seed_layout():
     assert c0.tolist() == [1, 2, -1, -1, -1] and c1.tolist() == [3, 4, -1, -1, -1]
     assert leaf_row.tolist() == [-1, -1, 2, 0, 1]
     assert nj.depths(c0, c1).tolist() == [0, 1, 2, 1, 2]
+
+
+def test_csv_fast_path_equals_general_reader(lazac, tmp_path):
+    """The in-place CSV splitter (plain files) and the RFC 4180 reader (quotes, stray CR) give the
+    same breakpoint vectors; CRLF, blank lines, a missing final newline, extra columns, cells whose
+    rows are interleaved and bins listed in different orders per cell are all covered."""
+    rows = [("b2", "2", 10, 20, 3), ("a1", "1", 0, 10, 2), ("a1", "1", 10, 20, 4), ("b2", "1", 0, 10, 1),
+            ("a1", "2", 10, 20, 2), ("b2", "1", 10, 20, 2), ("a1", "2", 0, 10, 5), ("b2", "2", 0, 10, 0),
+            ("c3", "10", 0, 5, 7), ("c3", "1", 0, 10, 2), ("c3", "1", 10, 20, 2), ("c3", "2", 0, 10, 2), ("c3", "2", 10, 20, 1)]
+    # c3 has one more bin: give the others that bin too (all cells must cover the same bins)
+    rows += [("a1", "10", 0, 5, 2), ("b2", "10", 0, 5, 3)]
+
+    def text(nl, quote, final_nl=True, blank=False):
+        q = (lambda s: '"%s"' % s) if quote else (lambda s: s)
+        lines = ["node,chrom,start,end,cn_a,cn_b,extra"]
+        for k, (node, chrom, s, e, cn) in enumerate(rows):
+            lines.append("%s,%s,%d,%d,%d,1,x" % (q(node), q(chrom), s, e, cn))
+            if blank and k == 3:
+                lines.append("")
+        return nl.join(lines) + (nl if final_nl else "")
+
+    outs = []
+    for name, body in [("plain", text("\n", False)), ("crlf", text("\r\n", False)), ("quoted", text("\n", True)),
+                       ("nofinal", text("\n", False, final_nl=False)), ("blank", text("\n", False, blank=True)),
+                       ("quoted_crlf", text("\r\n", True))]:
+        src = tmp_path / (name + ".csv")
+        src.write_bytes(body.encode())
+        out = tmp_path / (name + ".txt")
+        subprocess.run([lazac, "bp", str(src), "-o", str(out)], check=True)
+        outs.append(out.read_text())
+    assert all(o == outs[0] for o in outs)
+    first = outs[0].splitlines()
+    assert first[0] == "3 5" and first[1].split()[0] == "a1"
+    # a1: chrom "1": cn 2,4 -> [0, -2]; chrom "10": cn 2 -> single bin = first rule [0]; chrom "2": 5,2 -> [3, 0]
+    assert [int(x) for x in first[1].split()[1:]] == [0, -2, 0, 3, 0]
