@@ -365,71 +365,67 @@ def nni_section_large(ctx, args, peaks, peaks_kind):
 
 
 def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
-    """cfg5 (N > 1): every rank holds the tree, scores its slice of the neighbourhood, and the ranks
-    min-all-reduce one 64-bit (score, index) key over NCCL; timed by wall clock between barriers
-    (max over ranks), one pass per step, UP intervals rebuilt every pass as after an accepted move."""
+    """cfg5 (N > 1), positions sharded: every rank holds the same topology over its column slice of
+    the profiles, runs the whole pass (UP pass + all candidates) on 1/N of the bytes, and the ranks
+    sum-all-reduce the int32 vector {root score, candidate scores} over NCCL before the arg-min.
+    Timed by wall clock between barriers (max over ranks), one pass per step, UP intervals rebuilt
+    every pass as after an accepted move."""
     import torch
     import torch.distributed as dist
     from lazac_copy_number_b200 import nj, sharding, synth
-    from lazac_copy_number_b200.api import Profiles, Tree
+    from lazac_copy_number_b200.api import Profiles
     name = "tiny" if args.workload == "tiny" else "cfg5"
     w = NNI_WORKLOADS[name]
     prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0, want_tree=True)
     bp = bp_int8_chunked(prof["cn"], prof["seg"])
     n_leaves, L = bp.shape
     n = 2 * n_leaves - 1
-    gp = Profiles(ctx, bp)
+    gp = Profiles(ctx, bp)                      # whole rows once, for the seed tree (the same on every rank)
     c0, c1, leaf_row, seed_note = nj_seed(ctx, gp, n_leaves)
-    t = Tree(ctx, gp, c0, c1, leaf_row)
-    root = t.small_rectilinear()
-    eu, ev = t.edges()
+    gp.free()
+    st = sharding.PositionShardedTree(ctx, bp, c0, c1, leaf_row, rank, world)
+    root = st.small_rectilinear()
+    eu, ev = st.edges()
     order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
-    moves = t.enumerate_moves(eu, ev, order)
+    moves = st.enumerate_moves(eu, ev, order)
     C_ = len(moves)
-    lo, hi = sharding.candidate_slice(C_, rank, world)
-    mine = np.ascontiguousarray(moves[lo:hi])
     dep = nj.depths(c0, c1)
-
-    def one_pass():
-        li, ls, _ = t.nni_best(mine)
-        return sharding.allreduce_best(li, ls, lo, device="cuda")
-
     for _ in range(max(3, args.warmup)):
-        gi, gs = one_pass()
+        st.tree.set_topology(c0, c1)
+        st.tree.small_rectilinear()
+        gi, gs, _ = st.nni_best(moves)
     tot = 0.0
     for _ in range(args.steps):
-        t.set_topology(c0, c1)          # stale UP intervals, as after an accepted move (untimed)
-        t.small_rectilinear()
+        st.tree.set_topology(c0, c1)          # stale UP intervals, as after an accepted move (untimed)
+        st.tree.small_rectilinear()
         ctx.flush_l2()
         ctx.sync()
         torch.cuda.synchronize()
         dist.barrier()
         t0 = time.perf_counter()
-        gi, gs = one_pass()
+        gi, gs, _ = st.nni_best(moves)
         torch.cuda.synchronize()
         tot += time.perf_counter() - t0
     tt = torch.tensor([tot], dtype=torch.float64, device="cuda")
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     tot = float(tt[0])
-    cb, ub = t.last_nni_traffic()
+    cb, ub = st.last_nni_traffic()
     bt = torch.tensor([float(cb + ub)], dtype=torch.float64, device="cuda")
     dist.all_reduce(bt, op=dist.ReduceOp.SUM)
-    merges, ref_bytes = t.last_nni_work()
     out = {
         "metric": "nni_candidates_scored_per_sec", "value": C_ * args.steps / tot, "unit": "candidates/s", "n_gpus": world,
         "ms_per_step": 1e3 * tot / args.steps, "scaling": "strong",
         "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_,
-                   "seed_tree": seed_note,
-                   "pass": "per rank: UP pass (replicated) + its slice of the candidates + argmin; then one 8-byte NCCL min all-reduce",
+                   "seed_tree": seed_note, "positions_per_rank": st.hi - st.lo,
+                   "pass": "per rank: UP pass + all candidates over its column slice; one NCCL sum all-reduce of %d int32; argmin" % (C_ + 1),
                    "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
-                   "root_score": int(root), "best_index": int(gi), "best_score": None if gs is None else int(gs),
+                   "root_score": int(root), "best_index": int(gi), "best_score": int(gs),
                    "timing": "wall clock between barrier + synchronize, max over ranks"},
         "roofline": {"bound": "hbm", "achieved": float(bt[0]) / world / (tot / args.steps) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s per GPU",
                      "frac": float(bt[0]) / world / (tot / args.steps) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
                      "algorithmic_bytes_per_pass_all_ranks": int(bt[0])},
     }
-    t.free()
-    gp.free()
+    st.free()
     return out
 
 

@@ -53,6 +53,8 @@ int lzg_launch_count(const lzg_ctx* ctx, int64_t* out);
 int lzg_timer_start(lzg_ctx* ctx);
 int lzg_timer_stop(lzg_ctx* ctx, float* ms);
 int lzg_sync(lzg_ctx* ctx);
+/* The CUDA stream (cudaStream_t) every call on this context is ordered on. */
+int lzg_stream(lzg_ctx* ctx, void** stream);
 /* Writes a scratch buffer larger than L2 (timing hygiene between timed iterations). */
 int lzg_flush_l2(lzg_ctx* ctx);
 /* Pinned host memory for callers that want asynchronous copies to overlap. */
@@ -107,6 +109,17 @@ int lzg_tree_score(lzg_ctx* ctx, lzg_tree* t, int32_t* root_score);
  * all_scores (optional, [n_moves]) receives every candidate's root score. */
 int lzg_nni_best(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int32_t greedy,
                  int32_t* best_index, int32_t* best_score, int32_t* all_scores);
+/* The same pass in two halves, for trees whose POSITIONS are sharded over GPUs (every quantity of
+ * the pass is a sum over positions; each rank holds a column slice of the profiles and the same
+ * topology): _launch queues the UP pass and the candidate scores of this rank's columns and
+ * returns, without waiting, the DEVICE vector d_exchange = {root score, score of candidate 0, ...}
+ * (n_exchange = n_moves + 1 ints; NULL / 0 for an empty move list); the caller sum-reduces it in
+ * place over the ranks on lzg_stream(ctx) (NCCL all-reduce); _finish runs the arg-min of
+ * lzg_nni_best on the reduced vector.  lzg_nni_best == _launch + _finish with nothing between. */
+int lzg_nni_scores_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves,
+                          int32_t** d_exchange, int32_t* n_exchange);
+int lzg_nni_scores_finish(lzg_ctx* ctx, lzg_tree* t, int32_t greedy, int32_t* best_index,
+                          int32_t* best_score, int32_t* all_scores);
 /* Score of the LAST candidate of the last lzg_nni_best on this tree (the tree's root score if it
  * had no candidates).  The reference's greedy_nni leaves t[0].data.score at that value when a pass
  * finds nothing (src/copy_number.cxx:351 sets it per candidate, :365-366 do not restore it), and

@@ -28,6 +28,7 @@ SYMBOLS = [
     ("lzg_timer_start", _i, [_vp]),
     ("lzg_timer_stop", _i, [_vp, C.POINTER(C.c_float)]),
     ("lzg_sync", _i, [_vp]),
+    ("lzg_stream", _i, [_vp, _vpp]),
     ("lzg_flush_l2", _i, [_vp]),
     ("lzg_host_alloc", _i, [_vp, C.c_uint64, _vpp]),
     ("lzg_host_free", _i, [_vp, _vp]),
@@ -46,6 +47,8 @@ SYMBOLS = [
     ("lzg_tree_get_topology", _i, [_vp, _vp, _vp]),
     ("lzg_tree_score", _i, [_vp, _vp, _i32p]),
     ("lzg_nni_best", _i, [_vp, _vp, _i32, _vp, _i32, _i32p, _i32p, _vp]),
+    ("lzg_nni_scores_launch", _i, [_vp, _vp, _i32, _vp, _vpp, _i32p]),
+    ("lzg_nni_scores_finish", _i, [_vp, _vp, _i32, _i32p, _i32p, _vp]),
     ("lzg_tree_apply_nni", _i, [_vp, _vp, _i32, _i32, _i32, _i32, _i32p]),
     ("lzg_tree_get_intervals", _i, [_vp, _vp, _vp, _vp, _vp]),
     ("lzg_tree_ancestral", _i, [_vp, _vp, _vp, _vp]),

@@ -57,6 +57,12 @@ class Context:
     def sync(self):
         self.check(self.lib.lzg_sync(self.h))
 
+    def stream(self):
+        """cudaStream_t (as an int) every call on this context is ordered on."""
+        out = C.c_void_p()
+        self.check(self.lib.lzg_stream(self.h, C.byref(out)))
+        return out.value or 0
+
     def flush_l2(self):
         self.check(self.lib.lzg_flush_l2(self.h))
 
@@ -212,6 +218,22 @@ class Tree:
         allsc = np.zeros(len(moves), np.int32) if want_all else None
         self.ctx.check(self.ctx.lib.lzg_nni_best(self.ctx.h, self.h, len(moves), ptr(moves), int(greedy),
                                                  C.byref(bi), C.byref(bs), ptr(allsc)))
+        return bi.value, bs.value, allsc
+
+    def nni_scores_launch(self, moves):
+        """First half of nni_best for position-sharded trees (lzg_nni_scores_launch): queues the
+        pass and returns (device address, length) of {root score, candidate scores}; the caller
+        sum-reduces that vector over the ranks on ctx.stream(), then calls nni_scores_finish."""
+        moves = i32(moves).reshape(-1, 4)
+        d, n = C.c_void_p(), C.c_int32(0)
+        self.ctx.check(self.ctx.lib.lzg_nni_scores_launch(self.ctx.h, self.h, len(moves), ptr(moves), C.byref(d), C.byref(n)))
+        self._pending_moves = len(moves)
+        return d.value or 0, n.value
+
+    def nni_scores_finish(self, greedy=False, want_all=False):
+        bi, bs = C.c_int32(0), C.c_int32(0)
+        allsc = np.zeros(self._pending_moves, np.int32) if want_all else None
+        self.ctx.check(self.ctx.lib.lzg_nni_scores_finish(self.ctx.h, self.h, int(greedy), C.byref(bi), C.byref(bs), ptr(allsc)))
         return bi.value, bs.value, allsc
 
     def greedy_nni(self, eu, ev, order, greedy=False):

@@ -156,6 +156,12 @@ int lzg_sync(lzg_ctx* ctx) {
     return LZG_OK;
 }
 
+int lzg_stream(lzg_ctx* ctx, void** stream) {
+    if (!ctx || !stream) return LZG_ERR_ARG;
+    *stream = (void*)ctx->stream;
+    return LZG_OK;
+}
+
 int lzg_flush_l2(lzg_ctx* ctx) {
     if (!ctx) return LZG_ERR_ARG;
     if (!ctx->flush_buf) {

@@ -362,16 +362,19 @@ static int launch_up_pass(lzg_ctx* ctx, lzg_tree* t, int groups, int threads) {
 // One neighbourhood pass.  The UP pass is launched first (it needs the path tables only), so the
 // host's validation and packing of the move list run while the GPU builds the UP intervals; then
 // items, argmin and one 64-byte read-back.
-int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
-                        int32_t* best_index, int32_t* best_score, int32_t* all_scores) {
+//
+// Two halves: lzg_tree_nni_launch queues everything up to the candidate scores (no read-back),
+// lzg_tree_nni_finish the arg-min and the read-back.  lzg_nni_best runs them back to back; with the
+// positions sharded over ranks the caller sum-reduces {root score, scores} between the two.
+int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves) {
     const auto t_enter = std::chrono::steady_clock::now();
     t->last_up_ran = false;
     t->last_cand_score = t->root_score;
     t->last_items = t->last_root_items = 0;
     t->last_v.resize(n_moves);
+    t->pass_pending = false;
     if (n_moves == 0) {
-        *best_index = -1;
-        *best_score = t->root_score;
+        t->pass_pending = true;
         return LZG_OK;
     }
     const int n = t->n_nodes;
@@ -405,7 +408,6 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     A.n_cand = n_moves;
     A.groups = groups;
     A.l_pad = t->l_pad;
-    A.greedy = greedy;
     A.start = t->d_start;
     A.end = t->d_end;
     A.ustart = t->d_ustart;
@@ -474,8 +476,6 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         k_nni_items<16><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
     }
     LZG_LAUNCH_CHECK(ctx);
-    k_nni_argmin<<<1, 1024, 0, ctx->stream>>>(A);
-    LZG_LAUNCH_CHECK(ctx);
     if (trace) {
         cudaEventRecord(e1, ctx->stream);
         cudaEventSynchronize(e1);
@@ -487,6 +487,26 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
     }
+    t->pass_pending = true;
+    return LZG_OK;
+}
+
+int lzg_tree_nni_finish(lzg_ctx* ctx, lzg_tree* t, int greedy, int32_t* best_index, int32_t* best_score, int32_t* all_scores) {
+    if (!t->pass_pending) return lzg_fail(ctx, LZG_ERR_STATE, "no neighbourhood pass is pending on this tree");
+    t->pass_pending = false;
+    const int n_moves = (int)t->last_v.size();
+    if (n_moves == 0) {
+        *best_index = -1;
+        *best_score = t->root_score;
+        return LZG_OK;
+    }
+    lzg_pass_args A{};
+    A.n_cand = n_moves;
+    A.greedy = greedy;
+    A.ctl = t->d_cand;
+    A.cand_score = t->d_cand + LZG_CTL_INTS;
+    k_nni_argmin<<<1, 1024, 0, ctx->stream>>>(A);
+    LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_cand, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     if (all_scores)
         LZG_CUDA(ctx, cudaMemcpyAsync(all_scores, t->d_cand + LZG_CTL_INTS, sizeof(int32_t) * (size_t)n_moves, cudaMemcpyDeviceToHost, ctx->stream));
@@ -495,6 +515,15 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     *best_score = ctx->h_pinned[LZG_CTL_SCORE];
     t->last_cand_score = ctx->h_pinned[LZG_CTL_LAST];
     return LZG_OK;
+}
+
+int32_t* lzg_tree_exchange_vector(lzg_tree* t) { return t->d_cand + LZG_CTL_ROOT; }
+
+int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
+                        int32_t* best_index, int32_t* best_score, int32_t* all_scores) {
+    const int rc = lzg_tree_nni_launch(ctx, t, n_moves, moves);
+    if (rc != LZG_OK) return rc;
+    return lzg_tree_nni_finish(ctx, t, greedy, best_index, best_score, all_scores);
 }
 
 // Accept a move: one memset, one launch (k_apply_move), one read-back.

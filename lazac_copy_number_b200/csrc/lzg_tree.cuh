@@ -38,6 +38,7 @@ struct lzg_tree {
     int32_t up_paths = 0;             // heavy paths they form
     std::vector<int32_t> up_rank;     // position of a node in the walker order (-1: root, leaves); valid while up_valid
     std::vector<int4> node4;          // {child0, child1, internal nodes in the subtree, parent}: packed mirror for the path tables
+    bool pass_pending = false;        // lzg_tree_nni_launch queued a pass whose scores lzg_tree_nni_finish has not reduced yet
     bool node4_valid = false;         // cleared by lzg_tree_set_topology; kept current by lzg_tree_apply
     std::vector<int32_t> tmp_pre, tmp_heads, tmp_items, tmp_count;  // per-pass host scratch, kept to avoid reallocation
 };
@@ -45,6 +46,9 @@ struct lzg_tree {
 int lzg_tree_upload_topology(lzg_ctx* ctx, lzg_tree* t);
 int lzg_tree_gather_leaves(lzg_ctx* ctx, lzg_tree* t, const lzg_profiles* p, const int32_t* leaf_row);
 int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t);
+int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves);
+int32_t* lzg_tree_exchange_vector(lzg_tree* t);  // {root score, candidate scores} of the pending pass (device)
+int lzg_tree_nni_finish(lzg_ctx* ctx, lzg_tree* t, int greedy, int32_t* best_index, int32_t* best_score, int32_t* all_scores);
 int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int greedy,
                         int32_t* best_index, int32_t* best_score, int32_t* all_scores);
 int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z);

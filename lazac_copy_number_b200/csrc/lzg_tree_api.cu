@@ -200,6 +200,27 @@ int lzg_nni_best(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* move
     return lzg_tree_nni_scores(ctx, t, n_moves, moves, greedy, best_index, best_score, all_scores);
 }
 
+int lzg_nni_scores_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_t* moves, int32_t** d_exchange,
+                          int32_t* n_exchange) {
+    if (!ctx || !t || t->ctx != ctx || n_moves < 0 || (n_moves > 0 && !moves) || !d_exchange || !n_exchange)
+        return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nni_scores_launch: bad argument");
+    if (!t->scored) return lzg_fail(ctx, LZG_ERR_STATE, "tree must be scored (lzg_tree_score) before lzg_nni_scores_launch");
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int rc = lzg_tree_nni_launch(ctx, t, n_moves, moves);
+    if (rc != LZG_OK) return rc;
+    *d_exchange = n_moves ? lzg_tree_exchange_vector(t) : nullptr;
+    *n_exchange = n_moves ? n_moves + 1 : 0;
+    return LZG_OK;
+}
+
+int lzg_nni_scores_finish(lzg_ctx* ctx, lzg_tree* t, int32_t greedy, int32_t* best_index, int32_t* best_score,
+                          int32_t* all_scores) {
+    if (!ctx || !t || t->ctx != ctx || !best_index || !best_score)
+        return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nni_scores_finish: bad argument");
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    return lzg_tree_nni_finish(ctx, t, greedy, best_index, best_score, all_scores);
+}
+
 int lzg_tree_apply_nni(lzg_ctx* ctx, lzg_tree* t, int32_t u, int32_t w, int32_t v, int32_t z, int32_t* root_score) {
     if (!ctx || !t || t->ctx != ctx) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_tree_apply_nni: bad argument");
     if (!t->scored) return lzg_fail(ctx, LZG_ERR_STATE, "tree must be scored before lzg_tree_apply_nni");

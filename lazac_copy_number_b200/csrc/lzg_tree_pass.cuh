@@ -36,11 +36,13 @@ struct lzg_pass_args {
     uint8_t *ustart, *uend;
     const int32_t* score;
     int* ready;           // [n_nodes][groups] epoch flags of the UP rows
-    int* ctl;             // [0] ticket, [2] best index, [3] best score, [4] last candidate's score
+    int* ctl;             // [0] ticket, [2] best index, [3] best score, [4] last candidate's score, [15] root score
     int32_t* cand_score;  // [n_cand], zeroed
 };
 
-enum { LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_LAST = 4, LZG_CTL_INTS = 16 };
+// ctl[LZG_CTL_ROOT] sits directly below cand_score: {root score, candidate scores} is ONE vector of
+// n_cand + 1 ints, every entry a sum over positions -- what position-sharded ranks sum-reduce.
+enum { LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_LAST = 4, LZG_CTL_ROOT = 15, LZG_CTL_INTS = 16 };
 
 // One heavy path x one chunk group: UP(a) for every node a of the path, top-down, running
 // interval in registers; sibling intervals are prefetched two nodes ahead.
@@ -220,6 +222,7 @@ k_nni_items(const lzg_pass_args A, int groups_i) {
     const size_t off = ((size_t)g * 256 + tid) * CPT;
     int32_t base = 0;
     if (tid == 0 && g == 0) base = A.score[w] + A.score[a] + A.score[b] + (u ? A.score[0] - A.score[u] : 0);
+    if (tid == 0 && blockIdx.x == 0) A.ctl[LZG_CTL_ROOT] = A.score[0];
     int32_t pA = 0, pB = 0;
     if (off < (size_t)A.l_pad) {
         if (u) score_pair<CPT, true>(A, u, w, a, b, off, pA, pB);
@@ -237,7 +240,7 @@ __global__ void __launch_bounds__(1024)
 k_nni_argmin(const lzg_pass_args A) {
     __shared__ unsigned long long s_key[32];
     const int tid = threadIdx.x;
-    const int32_t root = A.score[0];
+    const int32_t root = A.ctl[LZG_CTL_ROOT];  // written by k_nni_items; summed over the ranks when positions are sharded
     unsigned long long best = ~0ull;
     for (int i = tid; i < A.n_cand; i += blockDim.x) {
         const int32_t sc = A.cand_score[i];

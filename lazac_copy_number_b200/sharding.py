@@ -5,7 +5,14 @@ tiles, so every rank gets the same triangle area -- and no collective runs until
 (the C side, lzg_distance_shard in csrc/lzg_api.cu, applies the same rule; this mirror is what
 tests and bench.py use to predict which rows a rank owns).
 
-NNI: every rank holds the whole tree, scores a contiguous slice of the host's candidate
+NNI, positions sharded (PositionShardedTree, the one that scales): every quantity of a
+neighbourhood pass is a sum over positions (src/copy_number.cxx:227-277 merges position by
+position), so every rank keeps the same topology over its own column slice of the profiles, runs
+the whole pass on 1/world of the bytes, and the ranks sum-all-reduce ONE int32 vector
+{root score, candidate scores} (NCCL over NVLink, ordered on the context's stream -- no host wait)
+before the arg-min.  Moves are applied by every rank; nothing else is exchanged.
+
+NNI, candidates sharded (the first cut, kept for comparison): every rank holds the whole tree, scores a contiguous slice of the host's candidate
 enumeration and the ranks min-all-reduce one 64-bit key (score << 32 | global index), which
 reproduces the reference's "strictly smaller, first in enumeration order" rule
 (/root/reference/src/copy_number.cxx:353-357) across ranks; greedy mode reduces the index alone.
@@ -75,3 +82,95 @@ def allreduce_best(local_index, local_score, lo, greedy=False, device="cpu"):
     t = torch.tensor([key], dtype=torch.int64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     return unpack_key(int(t.item()), greedy)
+
+
+def position_slice(n_pos, rank, world, align=16):
+    """Columns [lo, hi) of the breakpoint profiles held by `rank`; boundaries are multiples of
+    `align` (the device rows are padded to 16-byte chunks) except the last one."""
+    units = (n_pos + align - 1) // align
+    lo, hi = align * (units * rank // world), align * (units * (rank + 1) // world)
+    return min(lo, n_pos), min(hi, n_pos)
+
+
+class _DeviceVector:
+    """int32 device memory owned by the C library, seen through __cuda_array_interface__."""
+
+    def __init__(self, address, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (address, False), "version": 2}
+
+
+def device_vector(address, n, device):
+    """torch view (no copy) of n int32 at a device address."""
+    import torch
+    return torch.as_tensor(_DeviceVector(address, n), device="cuda:%d" % device)
+
+
+class PositionShardedTree:
+    """This rank's part of a tree whose positions are dealt over the ranks of a torch.distributed
+    group.  Same calls as api.Tree; scores are global (summed over the ranks)."""
+
+    def __init__(self, ctx, bp, child0, child1, leaf_row, rank=None, world=None, group=None):
+        import torch
+        import torch.distributed as dist
+        from .api import Profiles, Tree
+        self.ctx, self.group = ctx, group
+        self.rank = dist.get_rank(group) if rank is None else rank
+        self.world = dist.get_world_size(group) if world is None else world
+        self.lo, self.hi = position_slice(bp.shape[1], self.rank, self.world)
+        if self.hi <= self.lo:
+            raise ValueError("more ranks than 16-position chunks")
+        self.profiles = Profiles(ctx, np.ascontiguousarray(bp[:, self.lo:self.hi]))
+        self.tree = Tree(ctx, self.profiles, child0, child1, leaf_row)
+        self._stream = torch.cuda.ExternalStream(ctx.stream(), device=ctx.device)
+        self.root = None
+
+    def free(self):
+        self.tree.free()
+        self.profiles.free()
+
+    def _sum(self, tensor):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
+            with torch.cuda.stream(self._stream):
+                dist.all_reduce(tensor, op=dist.ReduceOp.SUM, group=self.group)
+
+    def small_rectilinear(self):
+        import torch
+        part = self.tree.small_rectilinear()
+        t = torch.tensor([part], dtype=torch.int32, device="cuda:%d" % self.ctx.device)
+        self._stream.wait_stream(torch.cuda.current_stream(self.ctx.device))
+        self._sum(t)
+        self._stream.synchronize()
+        self.root = int(t.item())
+        return self.root
+
+    def edges(self):
+        return self.tree.edges()
+
+    def enumerate_moves(self, eu, ev, order):
+        return self.tree.enumerate_moves(eu, ev, order)
+
+    def nni_best(self, moves, greedy=False, want_all=False):
+        address, n = self.tree.nni_scores_launch(moves)
+        if n:
+            self._sum(device_vector(address, n, self.ctx.device))
+            return self.tree.nni_scores_finish(greedy, want_all)
+        return -1, self.root, (np.zeros(0, np.int32) if want_all else None)
+
+    def apply_nni(self, u, w, v, z, new_root=None):
+        """Every rank applies the move to its columns.  The new global root score is the accepted
+        candidate's score (pass it as new_root to skip the all-reduce of one int)."""
+        part = self.tree.apply_nni(u, w, v, z)
+        if new_root is None:
+            import torch
+            t = torch.tensor([part], dtype=torch.int32, device="cuda:%d" % self.ctx.device)
+            self._stream.wait_stream(torch.cuda.current_stream(self.ctx.device))
+            self._sum(t)
+            self._stream.synchronize()
+            new_root = int(t.item())
+        self.root = new_root
+        return new_root
+
+    def last_nni_traffic(self):
+        return self.tree.last_nni_traffic()

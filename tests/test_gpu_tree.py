@@ -225,3 +225,59 @@ def test_up_intervals_invariant_and_deep_trees(ctx, port):
         assert gt.apply_nni(*moves[idx]) == pt.apply_nni(*full["move"])
     gt.free()
     gp.free()
+
+
+@pytest.mark.parametrize("n_leaves,bins,alleles,parts,greedy", [(40, 300, 2, 2, False), (90, 700, 1, 3, False), (90, 700, 1, 2, True),
+                                                                (12, 16, 1, 1, False)])
+def test_position_sharded_pass(ctx, port, n_leaves, bins, alleles, parts, greedy):
+    """lzg_nni_scores_launch / _finish: column slices of the profiles as separate trees (what the
+    ranks of a multi-GPU run hold), their {root, scores} vectors summed on the context's stream (the
+    NCCL all-reduce of sharding.PositionShardedTree), arg-min on the sum -- the oracle's choice on the
+    whole profiles, along a hill climb."""
+    import torch
+    from lazac_copy_number_b200 import sharding
+    bp, c0, c1, leaf_row, leaf_bp = make_case(n_leaves, bins, alleles, seed=7 * n_leaves)
+    L = bp.shape[1]
+    cuts = [sharding.position_slice(L, r, parts) for r in range(parts)]
+    assert cuts[0][0] == 0 and cuts[-1][1] == L and all(cuts[r][1] == cuts[r + 1][0] for r in range(parts - 1))
+    profs = [Profiles(ctx, np.ascontiguousarray(bp[:, lo:hi])) for lo, hi in cuts]
+    trees = [Tree(ctx, p, c0, c1, leaf_row) for p in profs]
+    pt = PortTree(port, c0, c1, leaf_bp)
+    root = pt.small_rectilinear()
+    assert sum(t.small_rectilinear() for t in trees) == root
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=ctx.device)
+    for it in range(6):
+        eu, ev = pt.edges()
+        order = np.random.default_rng(it).permutation(len(eu)).astype(np.int32)
+        full = pt.greedy_nni(eu, ev, order, greedy=False)
+        want = pt.greedy_nni(eu, ev, order, greedy=greedy, want_all=False)
+        moves = full["moves"]
+        vecs = []
+        for t in trees:
+            address, n = t.nni_scores_launch(moves)
+            assert n == len(moves) + 1
+            vecs.append(sharding.device_vector(address, n, ctx.device))
+        with torch.cuda.stream(stream):
+            total = torch.stack(vecs).sum(0, dtype=torch.int32)
+            for v in vecs:
+                v.copy_(total)
+        for t in trees:
+            bi, bs, allsc = t.nni_scores_finish(greedy, want_all=True)
+            assert np.array_equal(allsc, full["scores"])
+            assert bi == want["index"]
+            if bi >= 0:
+                assert bs == full["scores"][bi]
+            else:
+                assert bs == root
+            assert t.last_candidate_score() == full["scores"][-1]
+        if want["index"] < 0:
+            break
+        m = [int(x) for x in moves[want["index"]]]
+        root = pt.apply_nni(*m)
+        assert sum(t.apply_nni(*m) for t in trees) == root
+    with pytest.raises(LazacGpuError):
+        trees[0].nni_scores_finish()          # nothing pending
+    for t in trees:
+        t.free()
+    for p in profs:
+        p.free()

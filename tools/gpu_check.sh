@@ -1,5 +1,7 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, smoke, bench (cfg2 + NNI), cfg3 on one GPU, ncu launch list.
+# One gpurun call: GPU parity tests, smoke, bench (cfg2 + NNI), cfg3 on one GPU, ncu launch list
+# (every kernel but the NJ seed tree's ~22000 k_nj_* launches, which would fill the window;
+# profiles/r01_launches_bench_cfg2_v4_with_nj.txt holds a capture that includes them).
 # Usage (from the repo root, on the GPU box): bash tools/gpu_check.sh
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,driver_version,clocks.max.sm,clocks.max.mem,memory.total --format=csv > gpurun_out/gpu.csv
@@ -10,6 +12,7 @@ timeout 600 python bench.py --workload cfg3 --steps 5 --warmup 3 --no-nni --no-c
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "ref rc=$?"
 timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches.csv \
+    -k 'regex:^k_(zcnt|zero|fill|bias|nni|up_|apply|merge|level|gather|label|unpack)' \
     python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/ncu_launches.log 2>&1
 echo "ncu rc=$?"
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log | tail -2; cat gpurun_out/bench_cfg2.json; cat gpurun_out/bench_cfg3_1gpu.json; cat gpurun_out/bench_reference.json

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list per kernel (ns).
-usage: python tools/summarize_launches.py gpurun_out/launches.csv [> profiles/rNN_launches.txt]"""
+usage: python tools/summarize_launches.py gpurun_out/launches.csv [--by-name] [> profiles/rNN_launches.txt]
+--by-name merges the launch shapes of a kernel (NJ's scan shrinks its grid every join)."""
 import collections
 import csv
 import sys
@@ -15,7 +16,8 @@ for r in rows[1:]:
     except ValueError:
         continue
     name = r[ki].split("(")[0].replace("<unnamed>::", "").replace("void ", "")
-    agg.setdefault((name, r[gi], r[bi]), []).append(v)
+    key = (name, "*", r[bi]) if "--by-name" in sys.argv else (name, r[gi], r[bi])
+    agg.setdefault(key, []).append(v)
 tot = sum(sum(v) for v in agg.values())
 print("%-46s %-16s %-14s %5s %12s %10s %10s %10s %6s" % ("kernel", "grid", "block", "n", "total_ns", "mean_ns", "min_ns", "max_ns", "share"))
 for (name, g, b), v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
