@@ -179,22 +179,25 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def nni_iterations(ctx, t, moves, order, steps, warmup):
+def nni_iterations(ctx, t, moves, order, steps, warmup, apply=None, align=None):
     """Times hill-climb iterations on tree t: accept a move (lzg_tree_apply_nni), then score the
     whole new neighbourhood (lzg_nni_best).  The tree alternates between T0 and T1 = T0 + one
     move (the inverse of nni(u, w, v, z) is nni(u, z, v, w)), so every step sees stale UP
     intervals exactly as in hill_climb (src/copy_number.cxx:393-409).  Device time, CUDA events
-    on the library stream, L2 flushed before every step."""
+    on the library stream, L2 flushed before every step.  `apply` replaces t.apply_nni and `align`
+    (a rank barrier) runs before every timed region when t is one rank's part of a sharded tree."""
+    apply = apply or t.apply_nni
+    align = align or ctx.sync      # the L2 flush has drained before the clock starts: host preparation is not hidden behind it
     m = tuple(int(x) for x in moves[len(moves) // 2])
     inv = (m[0], m[3], m[2], m[1])
     t.nni_best(moves)
-    t.apply_nni(*m)
+    apply(*m)
     eu1, ev1 = t.edges()
     moves1 = t.enumerate_moves(eu1, ev1, order)
-    t.apply_nni(*inv)
+    apply(*inv)
     lists = (moves1, moves)
     for k in range(2 * max(2, (warmup + 1) // 2)):
-        t.apply_nni(*(m if k % 2 == 0 else inv))
+        apply(*(m if k % 2 == 0 else inv))
         t.nni_best(lists[k % 2])
     n_it = steps + steps % 2                    # an even number of steps: the tree ends as T0
     # (1) the pass on its own, as lzg_nni_best runs it on stale UP intervals: UP pass + items + argmin
@@ -203,8 +206,9 @@ def nni_iterations(ctx, t, moves, order, steps, warmup):
     cand = 0
     cb = ub = 0
     for k in range(n_it):
-        t.apply_nni(*(m if k % 2 == 0 else inv))   # untimed
+        apply(*(m if k % 2 == 0 else inv))   # untimed
         ctx.flush_l2()
+        align()
         ctx.timer_start()
         t.nni_best(lists[k % 2])
         stale_ms += ctx.timer_stop()
@@ -212,26 +216,27 @@ def nni_iterations(ctx, t, moves, order, steps, warmup):
         c, u = t.last_nni_traffic()
         cb, ub = cb + c, ub + u
     del os.environ["LZG_EAGER_UP"]
-    # (2) whole iterations: the move application queues the UP pass behind itself
-    ap_ms = ps_ms = wall = 0.0
+    # (2) whole iterations: the move application queues the UP pass behind itself; ONE timer over both
+    # calls (a stop between them would wait for the queued UP pass and expose the host's packing)
+    it_ms = wall = 0.0
     for k in range(n_it):
         ctx.flush_l2()
         ctx.sync()
+        align()
         t0 = time.perf_counter()
         ctx.timer_start()
-        t.apply_nni(*(m if k % 2 == 0 else inv))
-        ap_ms += ctx.timer_stop()
-        ctx.timer_start()
+        apply(*(m if k % 2 == 0 else inv))
         t.nni_best(lists[k % 2])
-        ps_ms += ctx.timer_stop()
+        it_ms += ctx.timer_stop()
         wall += time.perf_counter() - t0
     hot = 0.0
     for _ in range(n_it):                        # UP intervals still valid: scoring only
         ctx.flush_l2()
+        align()
         ctx.timer_start()
         idx, score, _ = t.nni_best(moves)
         hot += ctx.timer_stop()
-    return {"iterations": n_it, "candidates": cand, "stale_pass_ms": stale_ms / n_it, "apply_ms": ap_ms / n_it, "pass_ms": ps_ms / n_it, "wall_s": wall,
+    return {"iterations": n_it, "candidates": cand, "stale_pass_ms": stale_ms / n_it, "iteration_ms": it_ms / n_it, "wall_s": wall,
             "scoring_only_ms": hot / n_it, "cand_bytes": cb // n_it, "up_bytes": ub // n_it, "best_index": int(idx), "best_score": int(score),
             "moves_bytes": int(moves.nbytes)}
 
@@ -239,7 +244,7 @@ def nni_iterations(ctx, t, moves, order, steps, warmup):
 def nni_report(name, r, t, moves, dep, root, seed_tree, peaks, peaks_kind, n_leaves, L, note):
     n = 2 * n_leaves - 1
     C_ = len(moves)
-    it_ms = r["apply_ms"] + r["pass_ms"]
+    it_ms = r["iteration_ms"]
     ps_ms = r["stale_pass_ms"]
     nbytes = r["cand_bytes"] + r["up_bytes"]
     merges, ref_bytes = t.last_nni_work()
@@ -248,8 +253,8 @@ def nni_report(name, r, t, moves, dep, root, seed_tree, peaks, peaks_kind, n_lea
         "ms_per_step": ps_ms,
         "e2e": {"value": r["candidates"] / r["wall_s"], "unit": "candidates/s", "h2d_bytes_per_step": r["moves_bytes"] + 16, "d2h_bytes_per_step": 72,
                 "call": "whole hill-climb iterations, lzg_tree_apply_nni + lzg_nni_best with a host move list, wall clock"},
-        "iteration": {"value": C_ / (it_ms * 1e-3), "unit": "candidates/s", "ms_per_step": it_ms, "apply_ms": r["apply_ms"], "pass_ms": r["pass_ms"],
-                      "note": "accept a move (path re-scoring; the UP pass is queued behind it) + score the new neighbourhood, device time"},
+        "iteration": {"value": C_ / (it_ms * 1e-3), "unit": "candidates/s", "ms_per_step": it_ms,
+                      "note": "accept a move (path re-scoring; the UP pass is queued behind it) + score the new neighbourhood, device time, one timer over both calls"},
         "scoring_only": {"value": C_ / (r["scoring_only_ms"] * 1e-3), "unit": "candidates/s", "ms_per_step": r["scoring_only_ms"],
                          "note": "UP intervals already valid (no move accepted since the last pass)"},
         "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_, "seed_tree": seed_tree,
@@ -368,8 +373,8 @@ def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
     """cfg5 (N > 1), positions sharded: every rank holds the same topology over its column slice of
     the profiles, runs the whole pass (UP pass + all candidates) on 1/N of the bytes, and the ranks
     sum-all-reduce the int32 vector {root score, candidate scores} over NCCL before the arg-min.
-    Timed by wall clock between barriers (max over ranks), one pass per step, UP intervals rebuilt
-    every pass as after an accepted move."""
+    Same steps as the one-GPU sections (nni_iterations): the pass after an accepted move, whole
+    iterations, scoring only."""
     import torch
     import torch.distributed as dist
     from lazac_copy_number_b200 import nj, sharding, synth
@@ -390,39 +395,38 @@ def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
     moves = st.enumerate_moves(eu, ev, order)
     C_ = len(moves)
     dep = nj.depths(c0, c1)
-    for _ in range(max(3, args.warmup)):
-        st.tree.set_topology(c0, c1)
-        st.tree.small_rectilinear()
-        gi, gs, _ = st.nni_best(moves)
-    tot = 0.0
-    for _ in range(args.steps):
-        st.tree.set_topology(c0, c1)          # stale UP intervals, as after an accepted move (untimed)
-        st.tree.small_rectilinear()
-        ctx.flush_l2()
+
+    def align():
         ctx.sync()
         torch.cuda.synchronize()
         dist.barrier()
-        t0 = time.perf_counter()
-        gi, gs, _ = st.nni_best(moves)
-        torch.cuda.synchronize()
-        tot += time.perf_counter() - t0
-    tt = torch.tensor([tot], dtype=torch.float64, device="cuda")
+
+    # the new global root score of an accepted move is the winner's score: no collective in the move application
+    r = nni_iterations(ctx, st, moves, order, args.steps, args.warmup, apply=lambda *m: st.apply_nni(*m, new_root=0), align=align)
+    keys = ("stale_pass_ms", "iteration_ms", "scoring_only_ms", "wall_s")
+    tt = torch.tensor([r[k] for k in keys], dtype=torch.float64, device="cuda")
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    tot = float(tt[0])
-    cb, ub = st.last_nni_traffic()
-    bt = torch.tensor([float(cb + ub)], dtype=torch.float64, device="cuda")
+    r.update({k: float(v) for k, v in zip(keys, tt)})
+    bt = torch.tensor([float(r["cand_bytes"] + r["up_bytes"])], dtype=torch.float64, device="cuda")
     dist.all_reduce(bt, op=dist.ReduceOp.SUM)
+    ps_ms, it_ms = r["stale_pass_ms"], r["iteration_ms"]
     out = {
-        "metric": "nni_candidates_scored_per_sec", "value": C_ * args.steps / tot, "unit": "candidates/s", "n_gpus": world,
-        "ms_per_step": 1e3 * tot / args.steps, "scaling": "strong",
+        "metric": "nni_candidates_scored_per_sec", "value": C_ / (ps_ms * 1e-3), "unit": "candidates/s", "n_gpus": world,
+        "ms_per_step": ps_ms, "scaling": "strong",
+        "e2e": {"value": r["candidates"] / r["wall_s"], "unit": "candidates/s", "h2d_bytes_per_step": r["moves_bytes"] + 16, "d2h_bytes_per_step": 72,
+                "call": "whole hill-climb iterations on every rank (apply + launch + all-reduce + finish), wall clock, max over ranks"},
+        "iteration": {"value": C_ / (it_ms * 1e-3), "unit": "candidates/s", "ms_per_step": it_ms},
+        "scoring_only": {"value": C_ / (r["scoring_only_ms"] * 1e-3), "unit": "candidates/s", "ms_per_step": r["scoring_only_ms"]},
         "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_,
                    "seed_tree": seed_note, "positions_per_rank": st.hi - st.lo,
-                   "pass": "per rank: UP pass + all candidates over its column slice; one NCCL sum all-reduce of %d int32; argmin" % (C_ + 1),
+                   "step": "per rank, after an accepted move: UP pass + all candidates over its column slice; one NCCL sum all-reduce of %d int32 "
+                           "on the library stream; argmin; read-back" % (C_ + 1),
                    "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
-                   "root_score": int(root), "best_index": int(gi), "best_score": int(gs),
-                   "timing": "wall clock between barrier + synchronize, max over ranks"},
-        "roofline": {"bound": "hbm", "achieved": float(bt[0]) / world / (tot / args.steps) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s per GPU",
-                     "frac": float(bt[0]) / world / (tot / args.steps) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
+                   "root_score": int(root), "best_index": r["best_index"], "best_score": r["best_score"],
+                   "timing": "CUDA events on the library stream (the all-reduce is ordered on it), ranks aligned by a barrier before every step, max over ranks",
+                   "l2": "flushed between steps"},
+        "roofline": {"bound": "hbm", "achieved": float(bt[0]) / world / (ps_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s per GPU",
+                     "frac": float(bt[0]) / world / (ps_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
                      "algorithmic_bytes_per_pass_all_ranks": int(bt[0])},
     }
     st.free()

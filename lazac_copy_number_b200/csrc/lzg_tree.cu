@@ -275,7 +275,10 @@ static int build_up_paths(lzg_tree* t, int2* order, int4* rec, int* n_order) {
             const int4 n0 = nd[na.x], n1 = nd[na.y];
             const bool h0 = n0.z >= n1.z;
             const int heavy = h0 ? na.x : na.y, light = h0 ? na.y : na.x;
-            if ((h0 ? n1.z : n0.z) > 0) heads[n_heads++] = light, heads[n_heads++] = a, heads[n_heads++] = heavy;
+            if ((h0 ? n1.z : n0.z) > 0) {
+                heads[n_heads++] = light, heads[n_heads++] = a, heads[n_heads++] = heavy;
+                order[cnt - 1].y |= LZG_ORDER_PUBLISH;  // the light child's path will wait for UP(a)
+            }
             if ((h0 ? n0.z : n1.z) == 0) break;
             a = heavy;
             sib = light;
@@ -385,8 +388,9 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         const size_t nb = (size_t)n * t->l_pad;
         LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ustart, nb));
         LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_uend, nb));
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ready, sizeof(int) * (size_t)n * groups));
-        LZG_CUDA(ctx, cudaMemsetAsync(t->d_ready, 0, sizeof(int) * (size_t)n * groups, ctx->stream));
+        const size_t n_flags = (size_t)n * groups;  // per (node, chunk group)
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ready, sizeof(int) * n_flags));
+        LZG_CUDA(ctx, cudaMemsetAsync(t->d_ready, 0, sizeof(int) * n_flags, ctx->stream));
         t->epoch = 0;
         t->up_valid = false;
     }

@@ -10,9 +10,14 @@
 //  * k_up_pass: one CTA per (heavy path, chunk group), drawn from a ticket counter in
 //    parents-first order; the running UP interval stays in registers, sibling rows are
 //    prefetched two nodes ahead, every node's UP row is published with a per-(node, group) epoch
-//    flag (stores, bar.sync, st.release by one thread / ld.acquire by one thread, bar.sync, ld.cg).
-//    Cross-CTA hops are light edges only (<= log2 n on any root-leaf path).  A ticket is drawn
-//    by a running CTA and only waits for smaller tickets: no deadlock.
+//    flag (stores, bar.sync, st.release by one thread / ld.acquire by one thread, bar.sync, ld.cg) --
+//    only where another path's head hangs off the node (one node in three at cfg5): the release
+//    fence costs a store round trip (200 -> 185 us at cfg5).  Cross-CTA hops are light edges only
+//    (<= log2 n on any root-leaf path).  A ticket is drawn by a running CTA and only waits for
+//    smaller tickets: no deadlock.  At cfg5 the kernel moves 0.88 GB of DRAM traffic (0.51 read,
+//    0.37 written) in 185 us = 4.8 TB/s, 0.73 of the measured copy peak.  (Tried: persistent warp
+//    walkers -- one warp per (path, 512-position slice), static item order, no ticket and no CTA
+//    barrier: 212 us, eight times the fences.)
 //  * k_nni_items: one CTA per (item, chunk group) behind the kernel boundary -- no flags, no
 //    tickets: the item record, then all ten row loads at once, the arithmetic on u16x2 lanes,
 //    per-warp partial scores added to cand_score with fire-and-forget REDs.
@@ -29,7 +34,7 @@ __device__ __forceinline__ void split2(uint32_t x, uint32_t (&o)[2]) {
 
 struct lzg_pass_args {
     const int4* path_rec;  // [n_paths] {first index into order, nodes on the path, parent of the head, sibling of the head}
-    const int2* order;     // {node, its sibling}: internal non-root nodes, heavy paths back to back, parents-first
+    const int2* order;     // {node, its sibling | LZG_ORDER_PUBLISH}: internal non-root nodes, heavy paths back to back, parents-first
     const int4* items;     // [n_items][2]: {u, w, v, a}, {b, index of the candidate z = a, index of the candidate z = b, 0}
     int n_paths, n_items, n_cand, groups, l_pad, epoch, greedy;
     const uint8_t *start, *end;
@@ -43,6 +48,10 @@ struct lzg_pass_args {
 // ctl[LZG_CTL_ROOT] sits directly below cand_score: {root score, candidate scores} is ONE vector of
 // n_cand + 1 ints, every entry a sum over positions -- what position-sharded ranks sum-reduce.
 enum { LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_LAST = 4, LZG_CTL_ROOT = 15, LZG_CTL_INTS = 16 };
+
+// order[].y: the sibling, and LZG_ORDER_PUBLISH if another path's head hangs off the node -- only
+// those UP rows are waited for across walkers, only they pay the release fence.
+enum { LZG_ORDER_PUBLISH = 1 << 30, LZG_ORDER_NODE = LZG_ORDER_PUBLISH - 1 };
 
 // One heavy path x one chunk group: UP(a) for every node a of the path, top-down, running
 // interval in registers; sibling intervals are prefetched two nodes ahead.
@@ -64,8 +73,8 @@ __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int 
     int2 nx1 = k0 + 1 < k1 ? A.order[k0 + 1] : make_int2(0, 0);
     int2 nx2 = k0 + 2 < k1 ? A.order[k0 + 2] : make_int2(0, 0);
     if (active && k0 + 1 < k1) {
-        n1s = ldg16(A.start, (size_t)nx1.y * l_pad + off);
-        n1e = ldg16(A.end, (size_t)nx1.y * l_pad + off);
+        n1s = ldg16(A.start, (size_t)(nx1.y & LZG_ORDER_NODE) * l_pad + off);
+        n1e = ldg16(A.end, (size_t)(nx1.y & LZG_ORDER_NODE) * l_pad + off);
     }
     iv16 acc;
     uint32_t os[8], oe[8];
@@ -90,8 +99,8 @@ __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int 
         int2 nx3 = make_int2(0, 0);
         if (k + 2 < k1) {
             if (active) {
-                n2s = ldg16(A.start, (size_t)nx2.y * l_pad + off);
-                n2e = ldg16(A.end, (size_t)nx2.y * l_pad + off);
+                n2s = ldg16(A.start, (size_t)(nx2.y & LZG_ORDER_NODE) * l_pad + off);
+                n2e = ldg16(A.end, (size_t)(nx2.y & LZG_ORDER_NODE) * l_pad + off);
             }
             if (k + 3 < k1) nx3 = A.order[k + 3];
         }
@@ -99,8 +108,10 @@ __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int 
             *reinterpret_cast<uint4*>(A.ustart + (size_t)cur.x * l_pad + off) = narrow(acc.s);
             *reinterpret_cast<uint4*>(A.uend + (size_t)cur.x * l_pad + off) = narrow(acc.e);
         }
-        __syncthreads();
-        if (tid == 0) st_release(A.ready + (size_t)cur.x * A.groups + g, A.epoch);
+        if (cur.y & LZG_ORDER_PUBLISH) {  // a path head hangs off this node (uniform over the CTA)
+            __syncthreads();
+            if (tid == 0) st_release(A.ready + (size_t)cur.x * A.groups + g, A.epoch);
+        }
         if (k + 1 >= k1) break;
         if (active) {
             widen(n1s, os);
@@ -242,12 +253,24 @@ k_nni_argmin(const lzg_pass_args A) {
     const int tid = threadIdx.x;
     const int32_t root = A.ctl[LZG_CTL_ROOT];  // written by k_nni_items; summed over the ranks when positions are sharded
     unsigned long long best = ~0ull;
-    for (int i = tid; i < A.n_cand; i += blockDim.x) {
-        const int32_t sc = A.cand_score[i];
-        if (sc < root) {
-            unsigned long long key = A.greedy ? (unsigned long long)i : (((unsigned long long)(uint32_t)sc) << 32) | (uint32_t)i;
-            best = key < best ? key : best;
+    // cand_score is 64-byte aligned (d_cand + LZG_CTL_INTS): four candidates per load, all loads of a
+    // thread independent
+    const int n4 = A.n_cand >> 2;
+    const int4* sc4 = reinterpret_cast<const int4*>(A.cand_score);
+    for (int q = tid; q < n4; q += blockDim.x) {
+        const int4 v = __ldcg(sc4 + q);
+        const int32_t sc[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int i = 4 * q + e;
+            const unsigned long long key = A.greedy ? (unsigned long long)i : (((unsigned long long)(uint32_t)sc[e]) << 32) | (uint32_t)i;
+            best = (sc[e] < root && key < best) ? key : best;
         }
+    }
+    for (int i = 4 * n4 + tid; i < A.n_cand; i += blockDim.x) {
+        const int32_t sc = A.cand_score[i];
+        const unsigned long long key = A.greedy ? (unsigned long long)i : (((unsigned long long)(uint32_t)sc) << 32) | (uint32_t)i;
+        best = (sc < root && key < best) ? key : best;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

@@ -123,6 +123,7 @@ class PositionShardedTree:
         self.tree = Tree(ctx, self.profiles, child0, child1, leaf_row)
         self._stream = torch.cuda.ExternalStream(ctx.stream(), device=ctx.device)
         self.root = None
+        self._vec, self._vec_key = None, None    # torch view of the exchange vector (same address while the move count is)
 
     def free(self):
         self.tree.free()
@@ -152,10 +153,22 @@ class PositionShardedTree:
         return self.tree.enumerate_moves(eu, ev, order)
 
     def nni_best(self, moves, greedy=False, want_all=False):
+        import os
+        import time
+        trace = os.environ.get("LZG_SHARD_TRACE")
+        t0 = time.perf_counter()
         address, n = self.tree.nni_scores_launch(moves)
+        t1 = time.perf_counter()
         if n:
-            self._sum(device_vector(address, n, self.ctx.device))
-            return self.tree.nni_scores_finish(greedy, want_all)
+            if self._vec is None or self._vec_key != (address, n):
+                self._vec, self._vec_key = device_vector(address, n, self.ctx.device), (address, n)
+            self._sum(self._vec)
+            t2 = time.perf_counter()
+            out = self.tree.nni_scores_finish(greedy, want_all)
+            if trace:
+                t3 = time.perf_counter()
+                print("[shard %d] launch %.0f us, all-reduce call %.0f us, finish %.0f us" % (self.rank, 1e6 * (t1 - t0), 1e6 * (t2 - t1), 1e6 * (t3 - t2)), flush=True)
+            return out
         return -1, self.root, (np.zeros(0, np.int32) if want_all else None)
 
     def apply_nni(self, u, w, v, z, new_root=None):
