@@ -241,6 +241,48 @@ def nni_iterations(ctx, t, moves, order, steps, warmup, apply=None, align=None):
             "moves_bytes": int(moves.nbytes)}
 
 
+def nni_trajectory(ctx, t, order, max_steps, apply=None, align=None):
+    """A real hill climb from the tree's current topology (hill_climb, src/copy_number.cxx:375-417:
+    one fixed shuffle of the edge indices, every pass scores the whole neighbourhood, the best
+    strictly improving move is accepted, until none is left or max_steps).  Every iteration
+    (accept the previous winner + pass) is timed on the device; the host's re-enumeration of the
+    move list in Python between iterations is not part of the library and is left out."""
+    apply = apply or t.apply_nni
+    align = align or ctx.sync
+    eu, ev = t.edges()
+    moves = t.enumerate_moves(eu, ev, order)
+    idx, score, _ = t.nni_best(moves)           # first pass: untimed (UP intervals of the starting tree)
+    first = score
+    ms, cand, accepted = [], 0, 0
+    while idx >= 0 and accepted < max_steps:
+        m = tuple(int(x) for x in moves[idx])
+        # the move list of the tree AFTER the move has to exist before the clock starts
+        # (hill_climb patches four entries of its edge index in place, src/copy_number.cxx:401-406):
+        # apply on the host's copy of the topology by applying for real, enumerating, undoing
+        apply(*m)
+        eu, ev = t.edges()
+        nxt = t.enumerate_moves(eu, ev, order)
+        apply(m[0], m[3], m[2], m[1])
+        t.nni_best(moves)                       # back in the state right after the last pass
+        ctx.flush_l2()
+        align()
+        ctx.timer_start()
+        apply(*m)
+        idx, score, _ = t.nni_best(nxt)
+        ms.append(ctx.timer_stop())
+        cand += len(nxt)
+        moves = nxt
+        accepted += 1
+    if not ms:
+        return {"iterations": 0}
+    ms_sorted = sorted(ms)
+    return {"iterations": accepted, "median_ms": ms_sorted[len(ms) // 2], "mean_ms": sum(ms) / len(ms), "max_ms": ms_sorted[-1],
+            "value": cand / (sum(ms) * 1e-3), "unit": "candidates/s", "first_accepted_score": int(first), "last_score": int(score),
+            "ended": "no improving move left" if idx < 0 else "step limit",
+            "note": "real hill climb from the seed tree: every iteration = accept the previous winner (lzg_tree_apply_nni) + score the whole new "
+                    "neighbourhood (lzg_nni_best), device time, L2 flushed before each"}
+
+
 def nni_report(name, r, t, moves, dep, root, seed_tree, peaks, peaks_kind, n_leaves, L, note):
     n = 2 * n_leaves - 1
     C_ = len(moves)
@@ -338,6 +380,7 @@ def nni_section(ctx, args, peaks, peaks_kind):
         _, _, allsc = t.nni_best(moves, want_all=True)
         out["cpu_baseline"] = {"value": C_ / dt, "unit": "candidates/s", "cores": 1, "kind": kind, "sample": "the same full pass (%d candidates)" % C_,
                                "scores_equal_gpu": bool(np.array_equal(sc, allsc))}
+    out["trajectory"] = nni_trajectory(ctx, t, order, max(20, args.steps))
     t.free()
     gp.free()
     return out
@@ -364,6 +407,7 @@ def nni_section_large(ctx, args, peaks, peaks_kind):
     r = nni_iterations(ctx, t, moves, order, min(args.steps, 10), args.warmup)
     out = nni_report("cfg5 on 1 GPU", r, t, moves, dep, root, seed_note,
                      peaks, peaks_kind, n_leaves, L, "tree state %.1f GB incl. UP intervals" % (4 * n * L / 1e9))
+    out["trajectory"] = nni_trajectory(ctx, t, order, 20)
     t.free()
     gp.free()
     return out
@@ -429,6 +473,7 @@ def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
                      "frac": float(bt[0]) / world / (ps_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
                      "algorithmic_bytes_per_pass_all_ranks": int(bt[0])},
     }
+    out["trajectory"] = nni_trajectory(ctx, st, order, 20, apply=lambda *m: st.apply_nni(*m, new_root=0), align=align)
     st.free()
     return out
 

@@ -88,6 +88,8 @@ int lzg_init(int device, lzg_ctx** out) {
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_group, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_stage, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_items, cudaEventDisableTiming);
     if (e == cudaSuccess) {
         // keep freed blocks in the device's default pool (see lzg_dev_alloc)
         cudaMemPool_t pool;
@@ -123,6 +125,8 @@ int lzg_shutdown(lzg_ctx* ctx) {
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->ev_group) cudaEventDestroy(ctx->ev_group);
+    if (ctx->ev_stage) cudaEventDestroy(ctx->ev_stage);
+    if (ctx->ev_items) cudaEventDestroy(ctx->ev_items);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);

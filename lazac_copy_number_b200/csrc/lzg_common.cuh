@@ -39,6 +39,8 @@ struct lzg_ctx {
     size_t d_scratch_ints = 0;
     cudaStream_t copy_stream = nullptr;  // D2H of finished row groups while later groups compute
     cudaEvent_t ev_group = nullptr;
+    cudaEvent_t ev_items = nullptr;  // the last k_nni_items launch (reader of the item records) / the item copy on copy_stream
+    cudaEvent_t ev_stage = nullptr;  // the last asynchronous copy OUT of the pinned staging area that no synchronising call has waited for
     std::vector<lzg_schedule> schedules;  // distance schedules by (shape, tile, shard); freed at shutdown
 };
 

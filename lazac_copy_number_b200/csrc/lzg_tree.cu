@@ -326,6 +326,9 @@ static int launch_up_pass(lzg_ctx* ctx, lzg_tree* t, int groups, int threads) {
     int n_order = 0;
     const bool trace = getenv("LZG_PASS_DEBUG") && (atoi(getenv("LZG_PASS_DEBUG")) & 4);
     const auto t0 = std::chrono::steady_clock::now();
+    // lzg_tree_apply returns without waiting for the table copy it queued: a second move right
+    // behind the first must not rewrite the staging area under it
+    LZG_CUDA(ctx, cudaEventSynchronize(ctx->ev_stage));
     // records are written at the front, the order behind the worst-case record area, then compacted
     const int n_paths = build_up_paths(t, reinterpret_cast<int2*>(stage + 4 * (size_t)n), reinterpret_cast<int4*>(stage), &n_order);
     memmove(stage + 4 * (size_t)n_paths, stage + 4 * (size_t)n, sizeof(int2) * n_order);
@@ -338,6 +341,7 @@ static int launch_up_pass(lzg_ctx* ctx, lzg_tree* t, int groups, int threads) {
         LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand, 0, sizeof(int32_t) * LZG_CTL_INTS, ctx->stream));  // the ticket counter
         LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass, stage, sizeof(int32_t) * (4 * (size_t)n_paths + 2 * (size_t)n_order), cudaMemcpyHostToDevice,
                                       ctx->stream));
+        LZG_CUDA(ctx, cudaEventRecord(ctx->ev_stage, ctx->stream));
         lzg_pass_args A{};
         A.path_rec = reinterpret_cast<const int4*>(t->d_pass);
         A.order = reinterpret_cast<const int2*>(t->d_pass + 4 * (size_t)n_paths);
@@ -361,6 +365,8 @@ static int launch_up_pass(lzg_ctx* ctx, lzg_tree* t, int groups, int threads) {
     t->up_valid = true;
     return LZG_OK;
 }
+
+static cudaEvent_t g_apply_tl[3] = {nullptr, nullptr, nullptr};  // LZG_PASS_DEBUG=16: before / behind k_apply_move, behind the queued UP pass
 
 // One neighbourhood pass.  The UP pass is launched first (it needs the path tables only), so the
 // host's validation and packing of the move list run while the GPU builds the UP intervals; then
@@ -469,7 +475,19 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         }
         t->last_items = n_items;
     }
-    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass + o_items, stage + o_items, sizeof(int32_t) * 8 * (size_t)n_items, cudaMemcpyHostToDevice, ctx->stream));
+    static cudaEvent_t tl[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // LZG_PASS_DEBUG=16: stream timeline of the pass, no host waits
+    if (dbg & 16) {
+        for (auto& e : tl)
+            if (!e) cudaEventCreate(&e);
+        cudaEventRecord(tl[0], ctx->stream);  // behind the UP pass (and whatever was queued before this call)
+    }
+    // the item records go up on the copy stream, beside the UP kernel (not behind it); the copy only has
+    // to wait for the previous reader of the record area
+    LZG_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_items, 0));
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_pass + o_items, stage + o_items, sizeof(int32_t) * 8 * (size_t)n_items, cudaMemcpyHostToDevice, ctx->copy_stream));
+    LZG_CUDA(ctx, cudaEventRecord(ctx->ev_items, ctx->copy_stream));
+    LZG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_items, 0));
+    if (dbg & 16) cudaEventRecord(tl[1], ctx->stream);
     A.n_items = n_items;
     const auto t_launch = std::chrono::steady_clock::now();
     if (dbg & 8) {  // 8 positions per thread, five CTAs per SM
@@ -480,6 +498,24 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         k_nni_items<16><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
     }
     LZG_LAUNCH_CHECK(ctx);
+    LZG_CUDA(ctx, cudaEventRecord(ctx->ev_items, ctx->stream));
+    if (dbg & 16) {
+        cudaEventRecord(tl[2], ctx->stream);
+        cudaEventSynchronize(tl[2]);
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, tl[0], tl[1]);
+        cudaEventElapsedTime(&b, tl[1], tl[2]);
+        fprintf(stderr, "[lzg timeline] host: %.1f us from entry to the items launch; stream: wait for the item records %.1f us, k_nni_items %.1f us\n",
+                std::chrono::duration<double, std::micro>(t_launch - t_enter).count(), a * 1e3, b * 1e3);
+        if (g_apply_tl[2] && t->last_up_ran && n_paths == 0) {  // the move before this pass queued the UP pass
+            float c = 0, d = 0, e = 0;
+            cudaEventElapsedTime(&c, g_apply_tl[0], g_apply_tl[1]);
+            cudaEventElapsedTime(&d, g_apply_tl[1], g_apply_tl[2]);
+            cudaEventElapsedTime(&e, g_apply_tl[2], tl[0]);
+            fprintf(stderr, "[lzg timeline]   before it: k_apply_move + read-back %.1f us, then idle + tables H2D + k_up_pass %.1f us, then %.1f us to this pass\n",
+                    c * 1e3, d * 1e3, e * 1e3);
+        }
+    }
     if (trace) {
         cudaEventRecord(e1, ctx->stream);
         cudaEventSynchronize(e1);
@@ -563,6 +599,12 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
         nd[w].w = v;
         nd[z].w = u;
     }
+    const bool timeline = getenv("LZG_PASS_DEBUG") && (atoi(getenv("LZG_PASS_DEBUG")) & 16);
+    if (timeline) {
+        for (auto& e : g_apply_tl)
+            if (!e) cudaEventCreate(&e);
+        cudaEventRecord(g_apply_tl[0], ctx->stream);
+    }
     LZG_CUDA(ctx, cudaMemsetAsync(t->d_ctl, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)depth + 1), ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
     k_apply_move<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_score, t->d_cost, t->d_ctl,
@@ -570,12 +612,14 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_ctl, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     LZG_CUDA(ctx, cudaEventRecord(ctx->ev_group, ctx->stream));
+    if (timeline) cudaEventRecord(g_apply_tl[1], ctx->stream);
     // a neighbourhood pass follows an accepted move (hill_climb, src/copy_number.cxx:393-409): queue its
     // UP pass now, the caller only waits for the root score
     if (t->d_ustart && t->d_pass && !(getenv("LZG_EAGER_UP") && atoi(getenv("LZG_EAGER_UP")) == 0)) {
         int rc = launch_up_pass(ctx, t, groups, threads);
         if (rc != LZG_OK) return rc;
     }
+    if (timeline) cudaEventRecord(g_apply_tl[2], ctx->stream);
     LZG_CUDA(ctx, cudaEventSynchronize(ctx->ev_group));
     t->root_score = ctx->h_pinned[LZG_CTL_SCORE];
     return LZG_OK;
