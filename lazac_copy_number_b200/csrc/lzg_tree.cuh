@@ -37,7 +37,7 @@ struct lzg_tree {
     int32_t up_nodes = 0;             // internal non-root nodes (UP rows written by an UP pass)
     int32_t up_paths = 0;             // heavy paths they form
     std::vector<int32_t> up_rank;     // position of a node in the walker order (-1: root, leaves); valid while up_valid
-    std::vector<int4> node4;          // {child0, child1, internal nodes in the subtree, parent}: packed mirror for the path tables
+    std::vector<int4> node4;          // {heavy child, light child, internal nodes in the subtree << 2 | flags, parent}: packed mirror for the path tables (make_node4)
     bool pass_pending = false;        // lzg_tree_nni_launch queued a pass whose scores lzg_tree_nni_finish has not reduced yet
     bool node4_valid = false;         // cleared by lzg_tree_set_topology; kept current by lzg_tree_apply
     std::vector<int32_t> tmp_pre, tmp_heads, tmp_items, tmp_count;  // per-pass host scratch, kept to avoid reallocation
