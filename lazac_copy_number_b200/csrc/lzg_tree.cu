@@ -499,10 +499,7 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     if (dbg & 16) cudaEventRecord(tl[1], ctx->stream);
     A.n_items = n_items;
     const auto t_launch = std::chrono::steady_clock::now();
-    if (dbg & 8) {  // 8 positions per thread, five CTAs per SM
-        const int gi = (t->l_pad + 256 * 8 - 1) / (256 * 8);
-        k_nni_items<8><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
-    } else {
+    {
         const int gi = (t->l_pad + 256 * 16 - 1) / (256 * 16);
         k_nni_items<16><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
     }

@@ -185,46 +185,49 @@ __device__ __forceinline__ void score_pair(const lzg_pass_args& A, int u, int w,
         }
 #pragma unroll
         for (int h = 0; h < 2; h++) {
+            // Integer min/max issues at half rate (VIMNMX and the three-input VIMNMX3 alike, 63 lanes/clk/SM
+            // measured), IADD3 at full rate, so: end = lo + hi - start instead of max(lo, hi), and the
+            // cost of a merge whose interval is not needed, max(0, s - ue, us - e) (both intervals are
+            // proper: s <= e), as ONE VIMNMX3 over differences biased by 256 per lane (no borrow between the
+            // u16 lanes; each of cA, cB, c0 takes exactly one biased term per word, so the bias cancels in
+            // cA - c0 and cB - c0).
+            const uint32_t K = 0x01000100u;
             {   // z = a: v keeps b -- merge(w, b), then a, then UP(u)
                 const uint32_t lo1 = __vmaxu2(ws[h], bs[h]), hi1 = __vminu2(we[h], be[h]);
-                const uint32_t s1 = __vminu2(lo1, hi1), e1 = __vmaxu2(lo1, hi1);
+                const uint32_t s1 = __vminu2(lo1, hi1), e1 = lo1 + hi1 - s1;
                 const uint32_t lo2 = __vmaxu2(s1, as[h]), hi2 = __vminu2(e1, ae[h]);
                 const uint32_t s2 = __vminu2(lo2, hi2);
                 cA = cA + lo1 - s1;
                 cA = cA + lo2 - s2;
                 if (HAS_UP) {
-                    const uint32_t e2 = __vmaxu2(lo2, hi2);
-                    const uint32_t lo3 = __vmaxu2(s2, us[h]), hi3 = __vminu2(e2, ue[h]);
-                    cA = cA + lo3 - __vminu2(lo3, hi3);
+                    const uint32_t e2 = lo2 + hi2 - s2;
+                    cA += __vimax3_u16x2(s2 + K - ue[h], us[h] + K - e2, K);
                 }
             }
             {   // z = b: v keeps a
                 const uint32_t lo1 = __vmaxu2(ws[h], as[h]), hi1 = __vminu2(we[h], ae[h]);
-                const uint32_t s1 = __vminu2(lo1, hi1), e1 = __vmaxu2(lo1, hi1);
+                const uint32_t s1 = __vminu2(lo1, hi1), e1 = lo1 + hi1 - s1;
                 const uint32_t lo2 = __vmaxu2(s1, bs[h]), hi2 = __vminu2(e1, be[h]);
                 const uint32_t s2 = __vminu2(lo2, hi2);
                 cB = cB + lo1 - s1;
                 cB = cB + lo2 - s2;
                 if (HAS_UP) {
-                    const uint32_t e2 = __vmaxu2(lo2, hi2);
-                    const uint32_t lo3 = __vmaxu2(s2, us[h]), hi3 = __vminu2(e2, ue[h]);
-                    cB = cB + lo3 - __vminu2(lo3, hi3);
+                    const uint32_t e2 = lo2 + hi2 - s2;
+                    cB += __vimax3_u16x2(s2 + K - ue[h], us[h] + K - e2, K);
                 }
             }
-            if (HAS_UP) {  // the current tree re-rooted above u
-                const uint32_t lo3 = __vmaxu2(ds[h], us[h]), hi3 = __vminu2(de[h], ue[h]);
-                c0 = c0 + lo3 - __vminu2(lo3, hi3);
-            }
+            if (HAS_UP)  // the current tree re-rooted above u
+                c0 += __vimax3_u16x2(ds[h] + K - ue[h], us[h] + K - de[h], K);
         }
     }
-    // per u16 lane: <= 3 merges x 4 words x 254 -- no carry between the lanes
+    // per u16 lane: <= 4 words x (2 x 255 + 511) -- no carry between the lanes
     const int32_t z = (int32_t)((c0 & 0xffffu) + (c0 >> 16));
     pA = (int32_t)((cA & 0xffffu) + (cA >> 16)) - z;
     pB = (int32_t)((cB & 0xffffu) + (cB >> 16)) - z;
 }
 
 template <int CPT>
-__global__ void __launch_bounds__(256, CPT == 16 ? 3 : 5)
+__global__ void __launch_bounds__(256, 4)  // 64 registers: four CTAs per SM (three at 72-80 registers were 10 % slower, five spill)
 k_nni_items(const lzg_pass_args A, int groups_i) {
     const int tid = threadIdx.x;
     const int it = blockIdx.x / groups_i, g = blockIdx.x % groups_i;

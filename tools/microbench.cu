@@ -21,6 +21,9 @@ __global__ void k(uint32_t* out, int iters, uint32_t seed) {
             if (OP == 2) a[i] = __byte_perm(a[i], x, 0x4140 + i);
             if (OP == 3) a[i] = a[i] + x + i;                       // IADD3
             if (OP == 4) a[i] = a[i] * x + y;                       // IMAD
+            if (OP == 6) a[i] = __vimax3_u16x2(a[i], x + i, y);      // VIMNMX3.U16x2
+            if (OP == 7) a[i] = __vimin3_u16x2(__vmaxu2(a[i], x + i), y, x);  // VIMNMX + VIMNMX3 chain
+            if (OP == 8) a[i] = (a[i] & (x + i)) ^ y;                // LOP3
             if (OP == 5) { a[i] = sad4(x, y + i, a[i]); x = x * 5 + a[i]; }  // SAD + IMAD mix
         }
     }
@@ -45,7 +48,7 @@ void run(const char* name, int sms, double mhz_hint) {
         cudaEventRecord(e1); cudaEventSynchronize(e1);
         float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
     }
-    double lane_instr = (double)blocks * threads * iters * ILP * (OP == 5 ? 2 : 1);
+    double lane_instr = (double)blocks * threads * iters * ILP * (OP == 5 || OP == 7 ? 2 : 1);
     double per_s = lane_instr / (best * 1e-3);
     printf("{\"op\": \"%s\", \"ms\": %.4f, \"lane_instr_per_s\": %.4e, \"lane_instr_per_clk_per_sm_at_%.0fMHz\": %.2f}\n",
            name, best, per_s, mhz_hint, per_s / (mhz_hint * 1e6) / sms);
@@ -62,5 +65,8 @@ int main() {
     run<3>("IADD3", sms, mhz);
     run<4>("IMAD", sms, mhz);
     run<5>("VABSDIFF4+IMAD", sms, mhz);
+    run<6>("VIMNMX3.U16x2", sms, mhz);
+    run<7>("VIMNMX.U16x2+VIMNMX3.U16x2", sms, mhz);
+    run<8>("LOP3", sms, mhz);
     return 0;
 }
