@@ -122,7 +122,11 @@ Args parse_args(int argc, char** argv) {
 struct Gpu {
     lzg_ctx* ctx = nullptr;
     explicit Gpu(int device) {
+        const auto t0 = std::chrono::steady_clock::now();
         int rc = lzg_init(device, &ctx);
+        if (getenv("LAZAC_TIMING"))
+            std::cerr << "[lazac timing] lzg_init (CUDA context) " << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count()
+                      << " ms" << std::endl;
         if (rc != LZG_OK)  // no CPU fallback: the hot path exists on the GPU only
             throw std::runtime_error(std::string("cannot open CUDA device: ") + lzg_status_string(rc) + ": " + lzg_last_error(nullptr));
     }
@@ -305,6 +309,11 @@ void do_nni(const Args& a) {
     gpu.check(lzg_tree_create(gpu.ctx, prof, n, topo.c0.data(), topo.c1.data(), leaf_row.data(), &base));
 
     std::ranlux48_base gen(a.seed);
+    const bool timing = getenv("LAZAC_TIMING") != nullptr;
+    using clk = std::chrono::steady_clock;
+    auto ms_since = [](clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); };
+    double t_init = 0, t_score = 0, t_clone = 0, t_draws = 0, t_climb = 0;
+    auto t_mark = clk::now();
 
     /* Candidate tree set is obtained by randomly perturbing candidate trees. */
     std::vector<Candidate> candidates;
@@ -317,14 +326,17 @@ void do_nni(const Args& a) {
         candidates.push_back(c);
     }
     lzg_tree_free(base);
+    t_init = ms_since(t_mark);
 
     auto score_all = [&]() {
+        const auto t0 = clk::now();
         for (auto& c : candidates) {
             int32_t s = 0;
             gpu.check(lzg_tree_score(gpu.ctx, c.t.h, &s));
             c.t.score = s;
         }
         std::sort(candidates.begin(), candidates.end(), [](const Candidate& x, const Candidate& y) { return x.t.score > y.t.score; });
+        t_score += ms_since(t0);
     };
 
     std::string progress;  // nlohmann dump(): keys in alphabetical order, no spaces
@@ -348,14 +360,20 @@ void do_nni(const Args& a) {
         const int candidate_tree_idx = distrib(gen);
 
         GpuTree work;
+        t_mark = clk::now();
         work.topo = candidates[candidate_tree_idx].t.topo;
         work.score = candidates[candidate_tree_idx].t.score;
         gpu.check(lzg_tree_clone(gpu.ctx, candidates[candidate_tree_idx].t.h, &work.h));
+        t_clone += ms_since(t_mark);
+        t_mark = clk::now();
         std::uniform_real_distribution<double> aggression_distrib(0, a.aggression);
         // the reference perturbs a temporary and drops it (src/lazac.cxx:284): only the RNG draws matter
-        (void)stochastic_nni(work.topo, gen, (float)aggression_distrib(gen));
+        stochastic_nni_draws(work.topo, gen, (float)aggression_distrib(gen));
+        t_draws += ms_since(t_mark);
 
+        t_mark = clk::now();
         hill_climb(gpu.ctx, work, gen, a.greedy, &stats);
+        t_climb += ms_since(t_mark);
         if (work.score < candidates[0].t.score) {
             lzg_tree_free(candidates[0].t.h);
             candidates[0].t = work;
@@ -367,6 +385,9 @@ void do_nni(const Args& a) {
         counter++;
     }
     score_all();
+    if (timing)
+        std::cerr << "[lazac timing] search: candidate set " << t_init << " ms, scoring the set " << t_score << " ms, clones " << t_clone
+                  << " ms, perturbation draws " << t_draws << " ms, hill climbs " << t_climb << " ms (" << stats.passes << " passes)" << std::endl;
     GpuTree& best = candidates.back().t;
 
     /* ancestral_labeling (src/copy_number.cxx:187-225): labels on the GPU, pre-order renumbering here */
@@ -420,22 +441,43 @@ void do_nni(const Args& a) {
             mid[i] = "," + b.chromosome + "," + b.allele + "," + std::to_string(b.start) + "," + std::to_string(b.end) + ",";
         }
         std::vector<int> bp(L), cn;
-        std::string block;
-        char num[16];
+        size_t mid_bytes = 0;
+        for (const auto& m : mid) mid_bytes += m.size();
+        std::vector<char> block;
+        const auto t_out = std::chrono::steady_clock::now();
         for (int k = 0; k < n; k++) {
             const int32_t* row = labels.data() + (size_t)old_id[k] * L;
             bp.assign(row, row + L);
             copynumber_transform(bp, set.bins, order, cn, nullptr);
-            block.clear();
+            // one buffer per node, rows laid down with memcpy and a hand-rolled integer formatter
+            // (snprintf per row was most of the 2.5 s this file took at cfg4's size)
+            const std::string& name = names[k];
+            block.resize(mid_bytes + (size_t)L * (name.size() + 13));
+            char* p = block.data();
             for (int i = 0; i < L; i++) {
-                block += names[k];
-                block += mid[i];
-                const int len = snprintf(num, sizeof num, "%d", cn[i]);
-                block.append(num, (size_t)len);
-                block += '\n';
+                memcpy(p, name.data(), name.size());
+                p += name.size();
+                memcpy(p, mid[i].data(), mid[i].size());
+                p += mid[i].size();
+                long long v = cn[i];
+                if (v < 0) {
+                    *p++ = '-';
+                    v = -v;
+                }
+                char digits[12];
+                int nd = 0;
+                do {
+                    digits[nd++] = (char)('0' + v % 10);
+                    v /= 10;
+                } while (v);
+                while (nd) *p++ = digits[--nd];
+                *p++ = '\n';
             }
-            out.write(block.data(), (std::streamsize)block.size());
+            out.write(block.data(), (std::streamsize)(p - block.data()));
         }
+        if (timing)
+            std::cerr << "[lazac timing] ancestral CSV " << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_out).count()
+                      << " ms" << std::endl;
     }
     log_info("search: " + std::to_string(stats.passes) + " neighbourhood passes, " + std::to_string(stats.candidates) +
              " candidates scored, " + std::to_string(stats.moves) + " moves accepted");
@@ -472,6 +514,18 @@ void do_bp(const Args& a) {  // helper: CSV -> names + breakpoint matrix (text),
 }  // namespace
 
 int main(int argc, char** argv) {
+    if (argc >= 2 && std::string(argv[1]) == "selftest") {  // host-only checks, no GPU (tests/test_host_cpu.py)
+        int bad = 0;
+        for (int leaves : {2, 3, 4, 5, 8, 33, 200, 1000})
+            for (unsigned seed : {1u, 2u, 3u})
+                for (float aggression : {0.0f, 0.3f, 1.0f, 1.75f})
+                    if (!stochastic_nni_selftest(leaves, seed, aggression)) {
+                        std::cerr << "stochastic_nni mismatch: leaves " << leaves << " seed " << seed << " aggression " << aggression << std::endl;
+                        bad++;
+                    }
+        std::cout << (bad ? "selftest FAILED" : "selftest ok") << std::endl;
+        return bad ? 3 : 0;
+    }
     Args a;
     try {
         a = parse_args(argc, argv);

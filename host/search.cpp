@@ -49,31 +49,124 @@ int rand_int(std::ranlux48_base& gen, int a, int b) {
     return distrib(gen);
 }
 
-// internal edges (u, v with v internal) in edges() order
-void internal_edges(const Topology& t, std::vector<std::pair<int, int>>& out) {
-    out.clear();
-    for (int u = 0; u < t.size(); u++) {
-        if (t.c0[u] < 0) continue;
-        if (!t.leaf(t.c0[u])) out.emplace_back(u, t.c0[u]);
-        if (!t.leaf(t.c1[u])) out.emplace_back(u, t.c1[u]);
+// Order statistics over "internal edges (u, v with v internal) in edges() order" = by u, child0
+// before child1: a Fenwick tree over u of the number of internal children.  The reference
+// rebuilds the whole edge list before every draw (src/copy_number.cxx:425-440, O(n log n) per
+// step, O(n^2 log n) per call -- SURVEY.md 8(f) rank 4); the k-th entry of that list is all a
+// step needs, and an NNI changes the count of u and v only.
+struct InternalEdgeIndex {
+    std::vector<int> fen;  // 1-based
+    int n = 0, total = 0, top = 1;
+    static int weight(const Topology& t, int u) { return t.c0[u] < 0 ? 0 : (int)!t.leaf(t.c0[u]) + (int)!t.leaf(t.c1[u]); }
+    explicit InternalEdgeIndex(const Topology& t) : fen(t.size() + 1, 0), n(t.size()) {
+        for (int u = 0; u < n; u++) {
+            const int w = weight(t, u);
+            fen[u + 1] += w;
+            total += w;
+            const int up = (u + 1) + ((u + 1) & -(u + 1));
+            if (up <= n) fen[up] += fen[u + 1];
+        }
+        while (top * 2 <= n) top *= 2;
     }
-}
+    void add(int u, int delta) {
+        for (int i = u + 1; i <= n; i += i & -i) fen[i] += delta;
+    }
+    // the k-th (0-based) internal edge
+    std::pair<int, int> kth(const Topology& t, int k) const {
+        int pos = 0, rem = k;
+        for (int step = top; step > 0; step >>= 1)
+            if (pos + step <= n && fen[pos + step] <= rem) {
+                pos += step;
+                rem -= fen[pos];
+            }
+        const int u = pos;  // 0-based node: prefix(u) <= k < prefix(u + 1)
+        if (!t.leaf(t.c0[u]) && rem == 0) return {u, t.c0[u]};
+        return {u, t.c1[u]};
+    }
+};
 }  // namespace
 
 Topology stochastic_nni(const Topology& t, std::ranlux48_base& gen, float aggression) {
     Topology p = t;
-    std::vector<std::pair<int, int>> ie;
-    internal_edges(p, ie);
-    const int num_perturbations = ie.size() * aggression;  // size_t * float -> float -> int, as the reference
+    InternalEdgeIndex index(p);
+    const size_t n_edges = (size_t)index.total;
+    const int num_perturbations = n_edges * aggression;  // size_t * float -> float -> int, as the reference
     for (int i = 0; i < num_perturbations; i++) {
-        internal_edges(p, ie);
-        const auto [u, v] = ie[rand_int(gen, 0, (int)ie.size() - 1)];
+        const auto [u, v] = index.kth(p, rand_int(gen, 0, (int)n_edges - 1));  // an NNI keeps the number of internal edges
         const int w_only = p.c0[u] == v ? p.c1[u] : p.c0[u];
         const int w = (rand_int(gen, 0, 0), w_only);          // one child of u besides v: a draw from {0}
+        const int z = rand_int(gen, 0, 1) == 0 ? p.c0[v] : p.c1[v];
+        const int wu = InternalEdgeIndex::weight(p, u), wv = InternalEdgeIndex::weight(p, v);
+        p.nni(u, w, v, z);
+        index.add(u, InternalEdgeIndex::weight(p, u) - wu);
+        index.add(v, InternalEdgeIndex::weight(p, v) - wv);
+    }
+    return p;
+}
+
+// The reference's procedure word for word (edge list rebuilt before every draw): what the indexed
+// version above must reproduce.  Only the self-test calls it.
+static Topology stochastic_nni_rebuild(const Topology& t, std::ranlux48_base& gen, float aggression) {
+    Topology p = t;
+    std::vector<std::pair<int, int>> ie;
+    auto list = [&]() {
+        ie.clear();
+        for (int u = 0; u < p.size(); u++) {
+            if (p.c0[u] < 0) continue;
+            if (!p.leaf(p.c0[u])) ie.emplace_back(u, p.c0[u]);
+            if (!p.leaf(p.c1[u])) ie.emplace_back(u, p.c1[u]);
+        }
+    };
+    list();
+    const int num_perturbations = ie.size() * aggression;
+    for (int i = 0; i < num_perturbations; i++) {
+        list();
+        const auto [u, v] = ie[rand_int(gen, 0, (int)ie.size() - 1)];
+        const int w_only = p.c0[u] == v ? p.c1[u] : p.c0[u];
+        const int w = (rand_int(gen, 0, 0), w_only);
         const int z = rand_int(gen, 0, 1) == 0 ? p.c0[v] : p.c1[v];
         p.nni(u, w, v, z);
     }
     return p;
+}
+
+bool stochastic_nni_selftest(int n_leaves, unsigned seed, float aggression) {
+    // random topology by coalescence; internal ids 0 .. n_leaves-2 (root 0), leaves behind them
+    const int n = 2 * n_leaves - 1;
+    Topology t;
+    t.c0.assign(n, -1);
+    t.c1.assign(n, -1);
+    std::ranlux48_base build(seed * 7919u + 1);
+    std::vector<int> active;
+    for (int i = 0; i < n_leaves; i++) active.push_back(n_leaves - 1 + i);
+    int next = n_leaves - 2;
+    while (active.size() > 1) {
+        const int i = rand_int(build, 0, (int)active.size() - 1);
+        const int a = active[i];
+        active[i] = active.back();
+        active.pop_back();
+        const int j = rand_int(build, 0, (int)active.size() - 1);
+        const int b = active[j];
+        t.set_children(next, a, b);
+        active[j] = next--;
+    }
+    t.rebuild_parents();
+    std::ranlux48_base g1(seed), g2(seed), g3(seed);
+    const Topology a = stochastic_nni(t, g1, aggression), b = stochastic_nni_rebuild(t, g2, aggression);
+    stochastic_nni_draws(t, g3, aggression);
+    const auto x1 = g1(), x2 = g2(), x3 = g3();  // the generators must be left in the same state
+    return a.c0 == b.c0 && a.c1 == b.c1 && a.parent == b.parent && x1 == x2 && x1 == x3;
+}
+
+void stochastic_nni_draws(const Topology& t, std::ranlux48_base& gen, float aggression) {
+    size_t n_edges = 0;
+    for (int u = 0; u < t.size(); u++) n_edges += (size_t)InternalEdgeIndex::weight(t, u);
+    const int num_perturbations = n_edges * aggression;
+    for (int i = 0; i < num_perturbations; i++) {
+        (void)rand_int(gen, 0, (int)n_edges - 1);
+        (void)rand_int(gen, 0, 0);
+        (void)rand_int(gen, 0, 1);
+    }
 }
 
 int hill_climb(lzg_ctx* ctx, GpuTree& t, std::ranlux48_base& gen, bool greedy, ClimbStats* stats) {

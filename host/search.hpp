@@ -28,6 +28,13 @@ struct Topology {
 // stochastic_nni (src/copy_number.cxx:419-462): floor(#internal edges * aggression) random NNIs,
 // three uniform_int_distribution draws each; the float product is the reference's.
 Topology stochastic_nni(const Topology& t, std::ranlux48_base& gen, float aggression);
+// The same RNG draws without the tree: do_nni perturbs a temporary and drops it
+// (src/lazac.cxx:284); the draws do not depend on the topology (an NNI keeps the number of
+// internal edges, the other two ranges are constants).
+void stochastic_nni_draws(const Topology& t, std::ranlux48_base& gen, float aggression);
+// `lazac selftest`: the indexed stochastic_nni against the reference's list-rebuilding procedure
+// on a random tree (same result, same generator state afterwards; also for the draws-only variant).
+bool stochastic_nni_selftest(int n_leaves, unsigned seed, float aggression);
 
 struct GpuTree {
     lzg_tree* h = nullptr;

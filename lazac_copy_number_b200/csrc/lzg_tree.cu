@@ -311,6 +311,8 @@ static int ensure_cand_buffers(lzg_ctx* ctx, lzg_tree* t, int n_moves) {
     LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_pass, sizeof(int32_t) * ((size_t)6 * t->n_nodes + 12 + 8 * (size_t)cap)));
     LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_cand, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)cap)));
     t->cand_cap = cap;
+    // the item records are written on the copy stream: order it behind this allocation point
+    LZG_CUDA(ctx, cudaEventRecord(ctx->ev_items, ctx->stream));
     return LZG_OK;
 }
 
