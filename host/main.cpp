@@ -8,6 +8,8 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <future>
+#include <memory>
 #include <ctime>
 #include <cstdlib>
 #include <fstream>
@@ -203,9 +205,17 @@ BreakpointSet ingest(const std::string& path) {
     return set;
 }
 
+// The CUDA context of a fresh process takes seconds (2.4 s measured on a B200 box): open it on a
+// second thread while this one parses the CSV.
+std::future<std::unique_ptr<Gpu>> open_gpu_async(int device) {
+    return std::async(std::launch::async, [device]() { return std::make_unique<Gpu>(device); });
+}
+
 void do_distance(const Args& a) {
+    auto gpu_opening = open_gpu_async(a.device);
     const BreakpointSet set = ingest(a.cn_profile);
-    Gpu gpu(a.device);
+    const std::unique_ptr<Gpu> gpu_owner = gpu_opening.get();
+    Gpu& gpu = *gpu_owner;
     const std::vector<int32_t> D = build_distance_matrix(gpu, set, nullptr);
     write_matrix_csv(a.output + "_dist_matrix.csv", set.names, D);
     write_matrix_txt(a.output + "_dist_matrix.txt", set.names, D);
@@ -247,10 +257,21 @@ std::string scores_text(const std::vector<int>& v) {  // pprint compact: [a, b, 
 }
 
 void do_nni(const Args& a) {
+    const auto t_start = std::chrono::steady_clock::now();
+    struct Total {  // LAZAC_TIMING: wall time of the whole command, printed when do_nni returns
+        std::chrono::steady_clock::time_point t0;
+        ~Total() {
+            if (getenv("LAZAC_TIMING"))
+                std::cerr << "[lazac timing] do_nni total " << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count()
+                          << " ms" << std::endl;
+        }
+    } total{t_start};
     /* Load copy number profiles */
+    auto gpu_opening = open_gpu_async(a.device);
     const BreakpointSet set = ingest(a.cn_profile);
     const int n_cells = (int)set.names.size();
-    Gpu gpu(a.device);
+    const std::unique_ptr<Gpu> gpu_owner = gpu_opening.get();
+    Gpu& gpu = *gpu_owner;
     lzg_profiles* prof = nullptr;
 
     /* Load/initialize seed tree */
@@ -393,7 +414,9 @@ void do_nni(const Args& a) {
     /* ancestral_labeling (src/copy_number.cxx:187-225): labels on the GPU, pre-order renumbering here */
     const int L = set.L;
     std::vector<int32_t> labels((size_t)n * L), branch(n);
+    t_mark = clk::now();
     gpu.check(lzg_tree_ancestral(gpu.ctx, best.h, labels.data(), branch.data()));
+    if (timing) std::cerr << "[lazac timing] ancestral labels (GPU + read-back of " << (size_t)n * L * 4 / 1000000 << " MB) " << ms_since(t_mark) << " ms" << std::endl;
     std::vector<int> old_id, new_parent;
     {
         std::vector<std::pair<int, int>> st;  // (node, new id of its parent)
