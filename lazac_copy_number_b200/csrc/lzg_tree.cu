@@ -638,7 +638,7 @@ static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, i
     const size_t max_ints = (size_t)16 << 20;
     int block_rows = (int)std::max<size_t>(1, std::min<size_t>(rows, max_ints / std::max(1, L)));
     int32_t* d_tmp = nullptr;
-    LZG_CUDA(ctx, cudaMalloc(&d_tmp, sizeof(int32_t) * (size_t)block_rows * L));
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&d_tmp, sizeof(int32_t) * (size_t)block_rows * L));
     for (int r0 = 0; r0 < rows; r0 += block_rows) {
         int nr = std::min(block_rows, rows - r0);
         dim3 grid(std::max(1, std::min(64, (L + 255) / 256)), nr);
@@ -648,11 +648,11 @@ static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, i
         if (e == cudaSuccess) e = cudaMemcpyAsync(h_dst + (size_t)r0 * L, d_tmp, sizeof(int32_t) * (size_t)nr * L, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) {
-            cudaFree(d_tmp);
+            lzg_dev_free(ctx, d_tmp);
             return lzg_fail(ctx, LZG_ERR_CUDA, "interval download", e);
         }
     }
-    cudaFree(d_tmp);
+    lzg_dev_free(ctx, d_tmp);
     return LZG_OK;
 }
 
@@ -689,8 +689,8 @@ int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* br
     }
     uint8_t* d_label = nullptr;
     int32_t* d_branch = nullptr;
-    LZG_CUDA(ctx, cudaMalloc(&d_label, (size_t)n * t->l_pad));
-    cudaError_t e = cudaMalloc(&d_branch, sizeof(int32_t) * n);
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&d_label, (size_t)n * t->l_pad));
+    cudaError_t e = lzg_dev_alloc(ctx, (void**)&d_branch, sizeof(int32_t) * n);
     if (e == cudaSuccess) e = cudaMemsetAsync(d_branch, 0, sizeof(int32_t) * n, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(t->d_order, order.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream);
     int rc = LZG_OK;
@@ -717,7 +717,7 @@ int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* br
         else branch[0] = -1;
     }
     cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_label);
-    cudaFree(d_branch);
+    lzg_dev_free(ctx, d_label);
+    lzg_dev_free(ctx, d_branch);
     return rc;
 }
