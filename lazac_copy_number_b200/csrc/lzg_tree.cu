@@ -457,17 +457,29 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
         std::vector<int32_t>& cnt = t->tmp_count;
         raw.resize(8 * (size_t)n_moves);
         cnt.assign((size_t)t->up_nodes + 2, 0);
+        // validity (is_move) and the children of v from the packed node mirror: three 16-byte records per
+        // candidate instead of seven scattered ints (the mirror is current here: the UP pass of this
+        // topology was listed from it)
+        if (!t->node4_valid) rebuild_node4(t);
+        const int4* nd = t->node4.data();
+        const unsigned un = (unsigned)n;
         for (int i = 0; i < n_moves;) {
             const int32_t* m = moves + 4 * (size_t)i;
             const int u = m[0], w = m[1], v = m[2], z = m[3];
-            if (!is_move(t, u, w, v, z)) {
+            bool ok = (unsigned)u < un && (unsigned)w < un && (unsigned)v < un && (unsigned)z < un && w != v;
+            int4 nv = make_int4(-1, -1, 0, -1);
+            if (ok) {
+                nv = nd[v];
+                ok = nv.x >= 0 && nv.w == u && nd[w].w == u && nd[z].w == v;
+            }
+            if (!ok) {
                 cudaStreamSynchronize(ctx->stream);
                 return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "candidate is not an NNI move of this topology");
             }
             t->last_v[i] = v;
-            const int a = t->child0[v], b = t->child1[v];
+            const int a = nv.x, b = nv.y;  // the children of v (z is one of them: its parent is v)
             int ia = z == a ? i : -1, ib = z == b ? i : -1, used = 1;
-            if (i + 1 < n_moves && m[4] == u && m[5] == w && m[6] == v && m[7] != z && t->parent[m[7]] == v) {
+            if (i + 1 < n_moves && m[4] == u && m[5] == w && m[6] == v && m[7] != z && (m[7] == a || m[7] == b)) {
                 (m[7] == a ? ia : ib) = i + 1;
                 t->last_v[i + 1] = v;
                 used = 2;
@@ -478,6 +490,7 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
             t->last_root_items += u == 0;
             i += used;
         }
+        const auto t_p1 = std::chrono::steady_clock::now();
         for (size_t k = 1; k < cnt.size(); k++) cnt[k] += cnt[k - 1];
         int32_t* dst = stage + o_items;
         for (int k = 0; k < n_items; k++) {
@@ -485,6 +498,9 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
             memcpy(dst + 8 * (size_t)cnt[t->up_rank[r[0]] + 1]++, r, sizeof(int32_t) * 8);
         }
         t->last_items = n_items;
+        if (trace)
+            fprintf(stderr, "[lzg pack] records %.1f us, sort into the staging area %.1f us\n", std::chrono::duration<double, std::micro>(t_p1 - t_up).count(),
+                    std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_p1).count());
     }
     static cudaEvent_t tl[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // LZG_PASS_DEBUG=16: stream timeline of the pass, no host waits
     if (dbg & 16) {
