@@ -272,10 +272,17 @@ static int build_up_paths(lzg_tree* t, int2* order, int4* rec, int* n_order) {
     t->tmp_heads.resize(3 * (size_t)n / 2 + 12);  // (head, its parent, its sibling) triples, a queue (+ one speculative triple)
     int32_t* heads = t->tmp_heads.data();
     size_t n_heads = 0;
+    // item_start[u]: first slot of the work items (u, v) of node u, in an array
+    // sorted by the walker rank of u (the root's items first); an item per internal child, heavy first
+    t->item_start.resize((size_t)n);
+    int32_t* item_start = t->item_start.data();  // indexed by node id (the root's items start at 0)
+    item_start[0] = 0;
+    int slots = 0;
     {
         const int4 r = nd[0];
         if (r.z & 1) heads[n_heads++] = r.x, heads[n_heads++] = 0, heads[n_heads++] = r.y;
         if (r.z & 2) heads[n_heads++] = r.y, heads[n_heads++] = 0, heads[n_heads++] = r.x;
+        slots = (r.z & 1) + ((r.z >> 1) & 1);
     }
     for (size_t h = 0; h < n_heads; h += 3) {
         const int first = cnt;
@@ -286,6 +293,8 @@ static int build_up_paths(lzg_tree* t, int2* order, int4* rec, int* n_order) {
             // the light child's triple is always written, the queue only grows if it is internal;
             // its path will wait for UP(a): that node publishes
             const int light_internal = (na.z >> 1) & 1;
+            item_start[a] = slots;
+            slots += (na.z & 1) + light_internal;
             heads[n_heads] = na.y, heads[n_heads + 1] = a, heads[n_heads + 2] = na.x;
             n_heads += 3 * (size_t)light_internal;
             order[cnt++] = make_int2(a, sib | (light_internal ? LZG_ORDER_PUBLISH : 0));
@@ -453,54 +462,108 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     // that neighbouring CTAs share rows (both items under one u read DOWN(u) and UP(u))
     int n_items = 0;
     {
-        std::vector<int32_t>& raw = t->tmp_items;
-        std::vector<int32_t>& cnt = t->tmp_count;
-        raw.resize(8 * (size_t)n_moves);
-        cnt.assign((size_t)t->up_nodes + 2, 0);
-        // validity (is_move) and the children of v from the packed node mirror: three 16-byte records per
-        // candidate instead of seven scattered ints (the mirror is current here: the UP pass of this
-        // topology was listed from it)
         if (!t->node4_valid) rebuild_node4(t);
         const int4* nd = t->node4.data();
         const unsigned un = (unsigned)n;
-        for (int i = 0; i < n_moves;) {
-            const int32_t* m = moves + 4 * (size_t)i;
-            const int u = m[0], w = m[1], v = m[2], z = m[3];
-            bool ok = (unsigned)u < un && (unsigned)w < un && (unsigned)v < un && (unsigned)z < un && w != v;
-            int4 nv = make_int4(-1, -1, 0, -1);
-            if (ok) {
-                nv = nd[v];
-                ok = nv.x >= 0 && nv.w == u && nd[w].w == u && nd[z].w == v;
-            }
-            if (!ok) {
-                cudaStreamSynchronize(ctx->stream);
-                return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "candidate is not an NNI move of this topology");
-            }
-            t->last_v[i] = v;
-            const int a = nv.x, b = nv.y;  // the children of v (z is one of them: its parent is v)
-            int ia = z == a ? i : -1, ib = z == b ? i : -1, used = 1;
-            if (i + 1 < n_moves && m[4] == u && m[5] == w && m[6] == v && m[7] != z && (m[7] == a || m[7] == b)) {
-                (m[7] == a ? ia : ib) = i + 1;
-                t->last_v[i + 1] = v;
-                used = 2;
-            }
-            int32_t* r = raw.data() + 8 * (size_t)n_items++;
-            r[0] = u, r[1] = w, r[2] = v, r[3] = a, r[4] = b, r[5] = ia, r[6] = ib, r[7] = 0;
-            cnt[t->up_rank[u] + 2]++;
-            t->last_root_items += u == 0;
-            i += used;
-        }
-        const auto t_p1 = std::chrono::steady_clock::now();
-        for (size_t k = 1; k < cnt.size(); k++) cnt[k] += cnt[k - 1];
         int32_t* dst = stage + o_items;
-        for (int k = 0; k < n_items; k++) {
-            const int32_t* r = raw.data() + 8 * (size_t)k;
-            memcpy(dst + 8 * (size_t)cnt[t->up_rank[r[0]] + 1]++, r, sizeof(int32_t) * 8);
+        // One candidate pair -> one record.  Validity (is_move) and the children of v come from the packed
+        // node mirror (current here: the UP pass of this topology was listed from it).
+        // direct = true: the list is expected to be a whole neighbourhood (one item per internal
+        // non-root v, what greedy_nni enumerates): every record goes straight to its slot in the
+        // rank-of-u order (item_start, laid out with the path tables), no sort.  Returns 2 if the
+        // list turns out not to be one (an item missing or listed twice): the caller then runs the
+        // general form, a counting sort by the rank of u.
+        // The whole-neighbourhood form: candidates 2k and 2k + 1 are the two moves of one edge, fixed
+        // stride -- no iteration waits for the records the one before it loaded.
+        auto pack_direct = [&]() -> int {
+            std::vector<uint64_t>& seen = t->tmp_seen;  // one bit per item slot
+            seen.assign(((size_t)t->up_nodes + 64) / 64, 0);
+            const int32_t* item_start = t->item_start.data();
+            const int pairs = n_moves / 2;
+            int bad = 0, again = 0, roots = 0;
+            for (int k = 0; k < pairs; k++) {
+                const int32_t* m = moves + 8 * (size_t)k;
+                const int u = m[0], w = m[1], v = m[2], z0 = m[3], z1 = m[7];
+                if (!((unsigned)u < un && (unsigned)w < un && (unsigned)v < un && (unsigned)z0 < un && (unsigned)z1 < un)) return 1;
+                if (m[4] != u || m[5] != w || m[6] != v) return 2;  // not a pair: the general form decides
+                const int4 nv = nd[v], nu = nd[u];
+                // v internal, {v, w} = the children of u, {z0, z1} = the children of v
+                const bool vw = (nu.x == v && nu.y == w) || (nu.x == w && nu.y == v);
+                const bool zz = (nv.x == z0 && nv.y == z1) || (nv.x == z1 && nv.y == z0);
+                bad |= !(nv.x >= 0 && vw && v != w);
+                again |= !zz;
+                if (nu.x < 0) return 2;  // u is a leaf: no item slots of its own
+                const int slot = item_start[u] + (nu.x == v ? 0 : (nu.z & 1));
+                if ((unsigned)slot >= (unsigned)t->up_nodes) return 2;
+                const uint64_t bit = 1ull << (slot & 63);
+                again |= (seen[slot >> 6] & bit) != 0;
+                seen[slot >> 6] |= bit;
+                roots += u == 0;
+                int32_t* r = dst + 8 * (size_t)slot;
+                r[0] = u, r[1] = w, r[2] = v, r[3] = nv.x, r[4] = nv.y;
+                r[5] = nv.x == z0 ? 2 * k : 2 * k + 1, r[6] = nv.x == z0 ? 2 * k + 1 : 2 * k, r[7] = 0;
+            }
+            if (bad || again) return 2;  // the general form tells a malformed list from an unusual one
+            n_items = pairs;
+            t->last_root_items = roots;
+            t->last_whole = true;  // the v of the candidates = every internal non-root node, twice (lzg_tree_last_nni_work)
+            return 0;
+        };
+        // The general form: any list of moves; adjacent candidates of one edge share a record; counting sort
+        // by the walker rank of u.
+        auto pack_general = [&]() -> int {
+            std::vector<int32_t>& raw = t->tmp_items;
+            std::vector<int32_t>& cnt = t->tmp_count;
+            raw.resize(8 * (size_t)n_moves);
+            cnt.assign((size_t)t->up_nodes + 2, 0);
+            n_items = 0;
+            t->last_root_items = 0;
+            t->last_whole = false;
+            for (int i = 0; i < n_moves;) {
+                const int32_t* m = moves + 4 * (size_t)i;
+                const int u = m[0], w = m[1], v = m[2], z = m[3];
+                bool ok = (unsigned)u < un && (unsigned)w < un && (unsigned)v < un && (unsigned)z < un;
+                int4 nv = make_int4(-1, -1, 0, -1);
+                if (ok) {
+                    nv = nd[v];
+                    const int4 nu = nd[u];
+                    // v internal, {v, w} = the children of u, z a child of v
+                    ok = nv.x >= 0 && ((nu.x == v && nu.y == w) || (nu.x == w && nu.y == v)) && v != w && nd[z].w == v;
+                }
+                if (!ok) return 1;
+                t->last_v[i] = v;
+                const int a = nv.x, b = nv.y;  // the children of v
+                int ia = z == a ? i : -1, ib = z == b ? i : -1, used = 1;
+                if (i + 1 < n_moves && m[4] == u && m[5] == w && m[6] == v && m[7] != z && (m[7] == a || m[7] == b)) {
+                    (m[7] == a ? ia : ib) = i + 1;
+                    t->last_v[i + 1] = v;
+                    used = 2;
+                }
+                int32_t* r = raw.data() + 8 * (size_t)n_items++;
+                r[0] = u, r[1] = w, r[2] = v, r[3] = a, r[4] = b, r[5] = ia, r[6] = ib, r[7] = 0;
+                cnt[t->up_rank[u] + 2]++;
+                t->last_root_items += u == 0;
+                i += used;
+            }
+            for (size_t k = 1; k < cnt.size(); k++) cnt[k] += cnt[k - 1];
+            for (int k = 0; k < n_items; k++) {
+                const int32_t* r = raw.data() + 8 * (size_t)k;
+                memcpy(dst + 8 * (size_t)cnt[t->up_rank[r[0]] + 1]++, r, sizeof(int32_t) * 8);
+            }
+            return 0;
+        };
+        // a whole neighbourhood has two candidates per internal non-root node
+        int st = n_moves == 2 * t->up_nodes ? pack_direct() : 2;
+        const bool direct_ok = st == 0;
+        if (st == 2) st = pack_general();
+        if (st != 0) {
+            cudaStreamSynchronize(ctx->stream);
+            return lzg_fail(ctx, LZG_ERR_NOT_A_MOVE, "candidate is not an NNI move of this topology");
         }
         t->last_items = n_items;
         if (trace)
-            fprintf(stderr, "[lzg pack] records %.1f us, sort into the staging area %.1f us\n", std::chrono::duration<double, std::micro>(t_p1 - t_up).count(),
-                    std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_p1).count());
+            fprintf(stderr, "[lzg pack] %d records in %.1f us (%s)\n", n_items, std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_up).count(),
+                    direct_ok ? "placed directly" : "counting sort");
     }
     static cudaEvent_t tl[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // LZG_PASS_DEBUG=16: stream timeline of the pass, no host waits
     if (dbg & 16) {

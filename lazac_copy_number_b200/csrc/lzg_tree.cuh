@@ -38,6 +38,9 @@ struct lzg_tree {
     int32_t up_paths = 0;             // heavy paths they form
     std::vector<int32_t> up_rank;     // position of a node in the walker order (-1: root, leaves); valid while up_valid
     std::vector<int4> node4;          // {heavy child, light child, internal nodes in the subtree << 2 | flags, parent}: packed mirror for the path tables (make_node4)
+    std::vector<int32_t> item_start;  // per node: first item slot of its internal children (build_up_paths)
+    std::vector<uint64_t> tmp_seen;   // one bit per item slot (direct placement of a whole neighbourhood)
+    bool last_whole = false;          // the last pass scored a whole neighbourhood: last_v is not filled, v = every internal non-root node twice
     bool pass_pending = false;        // lzg_tree_nni_launch queued a pass whose scores lzg_tree_nni_finish has not reduced yet
     bool node4_valid = false;         // cleared by lzg_tree_set_topology; kept current by lzg_tree_apply
     std::vector<int32_t> tmp_pre, tmp_heads, tmp_items, tmp_count;  // per-pass host scratch, kept to avoid reallocation

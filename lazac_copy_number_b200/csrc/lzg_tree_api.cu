@@ -250,7 +250,11 @@ int lzg_tree_last_nni_work(const lzg_tree* t, int64_t* merges, int64_t* bytes) {
     std::vector<int32_t> depth(t->n_nodes, -1);
     depth[0] = 0;
     int64_t m = 0;
-    for (int v : t->last_v) {
+    std::vector<int32_t> whole;
+    if (t->last_whole)
+        for (int v = 1; v < t->n_nodes; v++)
+            if (t->child0[v] >= 0) whole.push_back(v), whole.push_back(v);
+    for (int v : (t->last_whole ? whole : t->last_v)) {
         // depth by walking up with memoisation
         int a = v, steps = 0;
         while (depth[a] < 0) {
