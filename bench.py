@@ -50,6 +50,13 @@ NNI_WORKLOADS = {
 SAD4_PEAK_LANE_INSTR_PER_S = 1.8304e13
 
 
+# DRAM traffic per launch / per pass from the committed ncu --set full captures (bytes); None elsewhere
+NCU_DRAM_BYTES = {
+    ("distance", "cfg2"): 14432768,                                   # k_zcnt_distance: 14.43 MB read, 0 written (14.0 MB algorithmic)
+    ("nni", "cfg5 on 1 GPU"): 513864000 + 364247296 + 1283499000 + 4908800,  # k_up_pass (r + w) + k_nni_items (r + w); 2.93 GB algorithmic
+}
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -306,7 +313,9 @@ def nni_report(name, r, t, moves, dep, root, seed_tree, peaks, peaks_kind, n_lea
                    "reference_algorithm_merges_per_pass": int(merges), "reference_algorithm_bytes_per_pass": int(ref_bytes),
                    "root_score": int(root), "best_index": r["best_index"], "best_score": r["best_score"], "l2": "flushed between steps"},
         "roofline": {"bound": "hbm", "achieved": nbytes / (ps_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": nbytes / (ps_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
+                     "frac": nbytes / (ps_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": NCU_DRAM_BYTES.get(("nni", name)), "peak_kind": peaks_kind,
+                     "traffic_source": "k_up_pass + k_nni_items, dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full on a random tree of this "
+                                       "shape (profiles/r01_ncu_nni_v5_cfg5.txt)" if ("nni", name) in NCU_DRAM_BYTES else None,
                      "algorithmic_bytes_per_pass": int(nbytes), "candidate_bytes": int(r["cand_bytes"]), "up_pass_bytes": int(r["up_bytes"]),
                      "scoring_only_frac": r["cand_bytes"] / (r["scoring_only_ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], "note": note},
     }
@@ -609,7 +618,9 @@ def run_b200(args):
             "roofline": {"bound": "int_alu", "kernel": "k_zcnt_distance", "achieved": achieved / 1e9, "peak": SAD4_PEAK_LANE_INSTR_PER_S / 1e9,
                          "unit": "G lane-instr/s (VABSDIFF4.U8.ACC, 4 positions each) per GPU", "frac": achieved / SAD4_PEAK_LANE_INSTR_PER_S,
                          "peak_kind": "measured (tools/microbench.cu on this pool, profiles/r01_microbench_int_pipes.jsonl)",
-                         "traffic": None,
+                         "traffic": NCU_DRAM_BYTES.get(("distance", name)),
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r01_ncu_dist_cfg2.txt)"
+                                           if ("distance", name) in NCU_DRAM_BYTES else None,
                          "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / world / (ms_step * 1e-3) / 1e9, "peak_gbs": peaks["hbm_gbs"],
                                  "frac": hbm_bytes / world / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_kind": peaks_kind}},
             "wall_s_timed_region": wall,
