@@ -120,6 +120,16 @@ int lzg_nni_scores_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int3
                           int32_t** d_exchange, int32_t* n_exchange);
 int lzg_nni_scores_finish(lzg_ctx* ctx, lzg_tree* t, int32_t greedy, int32_t* best_index,
                           int32_t* best_score, int32_t* all_scores);
+/* The three steps in one call, the all-reduce inside the library: ncclAllReduce(sum, int32) on
+ * lzg_stream(ctx) through the process's libnccl.so.2 (loaded with dlopen on first use; the library
+ * has no link-time dependency on NCCL).  lzg_comm_init is collective over the ranks: unique_id =
+ * the 128 bytes of one ncclGetUniqueId() call, the same on every rank (world == 1: may be NULL,
+ * no NCCL).  One communicator serves every tree of the context. */
+typedef struct lzg_comm lzg_comm;
+int lzg_comm_init(lzg_ctx* ctx, int32_t rank, int32_t world, const void* unique_id, lzg_comm** out);
+int lzg_comm_free(lzg_comm* comm);
+int lzg_nni_best_sharded(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_moves, const int32_t* moves,
+                         int32_t greedy, int32_t* best_index, int32_t* best_score, int32_t* all_scores);
 /* Score of the LAST candidate of the last lzg_nni_best on this tree (the tree's root score if it
  * had no candidates).  The reference's greedy_nni leaves t[0].data.score at that value when a pass
  * finds nothing (src/copy_number.cxx:351 sets it per candidate, :365-366 do not restore it), and

@@ -49,6 +49,9 @@ SYMBOLS = [
     ("lzg_nni_best", _i, [_vp, _vp, _i32, _vp, _i32, _i32p, _i32p, _vp]),
     ("lzg_nni_scores_launch", _i, [_vp, _vp, _i32, _vp, _vpp, _i32p]),
     ("lzg_nni_scores_finish", _i, [_vp, _vp, _i32, _i32p, _i32p, _vp]),
+    ("lzg_comm_init", _i, [_vp, _i32, _i32, _vp, _vpp]),
+    ("lzg_comm_free", _i, [_vp]),
+    ("lzg_nni_best_sharded", _i, [_vp, _vp, _vp, _i32, _vp, _i32, _i32p, _i32p, _vp]),
     ("lzg_tree_apply_nni", _i, [_vp, _vp, _i32, _i32, _i32, _i32, _i32p]),
     ("lzg_tree_get_intervals", _i, [_vp, _vp, _vp, _vp, _vp]),
     ("lzg_tree_ancestral", _i, [_vp, _vp, _vp, _vp]),

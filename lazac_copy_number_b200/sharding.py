@@ -17,6 +17,9 @@ enumeration and the ranks min-all-reduce one 64-bit key (score << 32 | global in
 reproduces the reference's "strictly smaller, first in enumeration order" rule
 (/root/reference/src/copy_number.cxx:353-357) across ranks; greedy mode reduces the index alone.
 """
+import ctypes as C
+import os
+
 import numpy as np
 
 NO_MOVE = (1 << 63) - 1  # int64 max: "no improving candidate on this rank"
@@ -123,9 +126,29 @@ class PositionShardedTree:
         self.tree = Tree(ctx, self.profiles, child0, child1, leaf_row)
         self._stream = torch.cuda.ExternalStream(ctx.stream(), device=ctx.device)
         self.root = None
+        # The all-reduce inside the library (lzg_nni_best_sharded: launch, ncclAllReduce and arg-min queued
+        # back to back by one C call).  The ranks agree on an NCCL unique id through the process group;
+        # LZG_SHARD_NCCL=0, or a libnccl the library cannot open, leaves the exchange to torch.distributed.
+        self.comm = None
+        if os.environ.get("LZG_SHARD_NCCL", "1") != "0":
+            ident = [torch.cuda.nccl.unique_id() if self.rank == 0 else None]
+            if self.world > 1:
+                dist.broadcast_object_list(ident, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            handle = C.c_void_p()
+            rc = ctx.lib.lzg_comm_init(ctx.h, self.rank, self.world, ident[0], C.byref(handle))
+            ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device="cuda:%d" % ctx.device)
+            if self.world > 1:
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)   # every rank or none
+            if int(ok.item()) == 1:
+                self.comm = handle
+            elif rc == 0:
+                ctx.lib.lzg_comm_free(handle)
         self._vec, self._vec_key = None, None    # torch view of the exchange vector (same address while the move count is)
 
     def free(self):
+        if self.comm is not None:
+            self.ctx.lib.lzg_comm_free(self.comm)
+            self.comm = None
         self.tree.free()
         self.profiles.free()
 
@@ -153,8 +176,17 @@ class PositionShardedTree:
         return self.tree.enumerate_moves(eu, ev, order)
 
     def nni_best(self, moves, greedy=False, want_all=False):
-        import os
         import time
+        if self.comm is not None:
+            moves = np.ascontiguousarray(moves, np.int32).reshape(-1, 4)
+            if len(moves) == 0:
+                return -1, self.root, (np.zeros(0, np.int32) if want_all else None)
+            bi, bs = C.c_int32(0), C.c_int32(0)
+            allsc = np.zeros(len(moves), np.int32) if want_all else None
+            self.ctx.check(self.ctx.lib.lzg_nni_best_sharded(self.ctx.h, self.comm, self.tree.h, len(moves), moves.ctypes.data_as(C.c_void_p),
+                                                             int(greedy), C.byref(bi), C.byref(bs),
+                                                             allsc.ctypes.data_as(C.c_void_p) if want_all else None))
+            return bi.value, bs.value, allsc
         trace = os.environ.get("LZG_SHARD_TRACE")
         t0 = time.perf_counter()
         address, n = self.tree.nni_scores_launch(moves)

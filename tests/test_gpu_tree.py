@@ -281,3 +281,30 @@ def test_position_sharded_pass(ctx, port, n_leaves, bins, alleles, parts, greedy
         t.free()
     for p in profs:
         p.free()
+
+
+def test_sharded_entry_point_with_one_rank(ctx, port):
+    """lzg_comm_init(world = 1) + lzg_nni_best_sharded: the three-step call without an exchange is
+    lzg_nni_best (the N > 1 exchange itself is exercised by bench.py --gpus N, same trajectory and scores)."""
+    import ctypes as C
+    bp, c0, c1, leaf_row, leaf_bp = make_case(70, 400, 2, seed=77)
+    prof = Profiles(ctx, bp)
+    gt = Tree(ctx, prof, c0, c1, leaf_row)
+    pt = PortTree(port, c0, c1, leaf_bp)
+    assert gt.small_rectilinear() == pt.small_rectilinear()
+    comm = C.c_void_p()
+    ctx.check(ctx.lib.lzg_comm_init(ctx.h, 0, 1, None, C.byref(comm)))
+    eu, ev = pt.edges()
+    order = np.random.default_rng(5).permutation(len(eu)).astype(np.int32)
+    full = pt.greedy_nni(eu, ev, order)
+    moves = np.ascontiguousarray(full["moves"], np.int32)
+    bi, bs = C.c_int32(0), C.c_int32(0)
+    allsc = np.zeros(len(moves), np.int32)
+    ctx.check(ctx.lib.lzg_nni_best_sharded(ctx.h, comm, gt.h, len(moves), moves.ctypes.data_as(C.c_void_p), 0, C.byref(bi), C.byref(bs),
+                                           allsc.ctypes.data_as(C.c_void_p)))
+    assert np.array_equal(allsc, full["scores"]) and bi.value == full["index"]
+    with pytest.raises(LazacGpuError):
+        ctx.check(ctx.lib.lzg_comm_init(ctx.h, 3, 2, None, C.byref(C.c_void_p())))   # rank out of range / no id
+    ctx.check(ctx.lib.lzg_comm_free(comm))
+    gt.free()
+    prof.free()
