@@ -1,15 +1,18 @@
 #!/usr/bin/env python
 """bench.py -- ZCNT hot-path throughput on B200 (contract: one JSON line on stdout from rank 0).
 
-    python bench.py --gpus 1 --steps K --warmup W            # 1 GPU: BASELINE.json configs[1]
+    python bench.py --gpus 1 --steps K --warmup W            # 1 GPU
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference ...                     # the reference's own CPU code
 
 Workloads (BASELINE.json `configs`); a step = one whole distance matrix:
-  cfg2  1,000 cells x 5,000 bins x 2 alleles (L = 10,000)   default at --gpus 1
-  cfg3  20,000 cells x 10,000 bins x 2 alleles (L = 20,000)  default at --gpus > 1: tile rows of
-        the ONE matrix are dealt to the ranks (strong scaling, no data-path collective; every
-        rank ends with its own row/column strips)
+  cfg3  20,000 cells x 10,000 bins x 2 alleles (L = 20,000)  the headline at EVERY --gpus N: the
+        matrix BASELINE.json's scaling target is quoted on; it fits one GPU (0.4 GB in, 1.6 GB
+        out), so N = 1 runs the same matrix and the 1/2/4/8 series is one strong-scaling series
+        (tile rows of the ONE matrix dealt to the ranks, no data-path collective; every rank
+        ends with its own row/column strips)
+  cfg2  1,000 cells x 5,000 bins x 2 alleles (L = 10,000)   configs[1]; reported in the same
+        line at --gpus 1 as "cfg2" (same calls, same keys), or alone with --workload cfg2
 The NNI path is reported in the same line at --gpus 1: "nni" = cfg4 (1,000 cells x 5,000 bins, NJ
 seed tree), "nni_large" = cfg5's shape (10,000 cells x 20,000 positions) on the one GPU; a step is
 one hill-climb iteration (accept a move + score the whole new neighbourhood).
@@ -156,7 +159,7 @@ def run_reference(args):
     rank, local, world = dist_env()
     if rank != 0:
         return
-    name = args.workload or ("cfg2" if args.gpus == 1 else "cfg3")
+    name = args.workload or "cfg3"
     w = WORKLOADS[name]
     from lazac_copy_number_b200 import synth
     # the sample only needs the first cells: generate a smaller tree of the same shape per cell
@@ -175,7 +178,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": "zcnt_cell_pairs_per_sec", "value": value, "unit": "cell-pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps),
-        "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "int32", "data": "synthetic",
         "config": {"workload": name, "cells": w["cells"], "bins": w["bins"], "alleles": w["alleles"],
                    "positions": bp.shape[1], "sample": sample},
@@ -504,8 +507,35 @@ def run_b200(args):
         os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_bench_%h_%p.log")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     peaks, peaks_kind = measured_peaks()
+    ctx = Context(local)
 
-    name = args.workload or ("cfg2" if world == 1 else "cfg3")
+    name = args.workload or "cfg3"
+    line = distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
+    if world == 1 and name == "cfg3" and not args.no_cfg2:
+        # BASELINE.json configs[1] beside the headline: same kernel, same calls, a matrix of 36 tiles
+        line["cfg2"] = distance_section(ctx, args, "cfg2", rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
+    if world == 1 and not args.no_nni:
+        line["nni"] = nni_section(ctx, args, peaks, peaks_kind)
+        if args.workload != "tiny" and not args.no_nni_large:
+            line["nni_large"] = nni_section_large(ctx, args, peaks, peaks_kind)
+    if world > 1 and not args.no_nni:
+        nni = nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind)
+        if rank == 0:
+            line["nni"] = nni
+    ctx.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu):
+    """One distance workload: device-resident steps (value, roofline), then the host-buffer calls
+    (e2e), then the reference's pair loop on a bounded sample (rank 0, one GPU only)."""
+    import torch
+    import torch.distributed as dist
+    from lazac_copy_number_b200.api import Profiles
+
     w = WORKLOADS[name]
     from lazac_copy_number_b200 import synth
     prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)   # same seed on every rank
@@ -514,7 +544,6 @@ def run_b200(args):
     n, L = bp.shape
     P = n * (n + 1) // 2
 
-    ctx = Context(local)
     gp = Profiles(ctx, bp)
     d_D = torch.empty((n, n), dtype=torch.int32, device="cuda")
     shard, n_shards = rank, world
@@ -604,7 +633,7 @@ def run_b200(args):
         line = {
             "metric": "zcnt_cell_pairs_per_sec", "value": value, "unit": "cell-pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u8 (int8 + 128 bias), int32 accumulate",
+            "scaling": "strong", "vs_baseline": None, "dtype": "u8 (int8 + 128 bias), int32 accumulate",
             "data": "synthetic",
             "config": {"workload": name, "cells": n, "bins": w["bins"], "alleles": w["alleles"], "positions": L, "pairs": P,
                        "position_ops_per_step": P * L, "sharding": "tile rows dealt in pairs (r, R-1-r) to %d rank(s)" % world,
@@ -627,26 +656,14 @@ def run_b200(args):
         }
         if n1_same:
             line["n1_same_workload"] = n1_same
-    if world == 1 and not args.no_cpu:
+    if world == 1 and cpu:
         n_sample = args.ref_cells or (160 if L <= 10000 else 110)
         v, kind, dt, pairs = cpu_distance_sample(bp, min(n, n_sample))
         line["cpu_baseline"] = {"value": v, "unit": "cell-pairs/s", "cores": 1, "kind": kind,
                                 "sample": "first %d cells of the same input (%d pairs, %.1f s)" % (min(n, n_sample), pairs, dt)}
     gp.free()
-    del d_D
-    if world == 1 and not args.no_nni:
-        line["nni"] = nni_section(ctx, args, peaks, peaks_kind)
-        if args.workload != "tiny" and not args.no_nni_large:
-            line["nni_large"] = nni_section_large(ctx, args, peaks, peaks_kind)
-    if world > 1 and not args.no_nni:
-        nni = nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind)
-        if rank == 0:
-            line["nni"] = nni
-    ctx.close()
-    if rank == 0:
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    del d_D, h_bp, h_D
+    return line
 
 
 def main():
@@ -658,6 +675,7 @@ def main():
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--ref-cells", type=int, default=0, help="cells in the CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cfg2", action="store_true", help="skip the cfg2 section beside the cfg3 headline at --gpus 1")
     ap.add_argument("--no-nni", action="store_true", help="skip the NNI section")
     ap.add_argument("--no-nni-large", action="store_true", help="skip the cfg5-shaped NNI section at --gpus 1")
     args = ap.parse_args()

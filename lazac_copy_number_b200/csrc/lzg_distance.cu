@@ -370,17 +370,48 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
     const int64_t seg_cost = getenv("LZG_SEG_COST") ? atoi(getenv("LZG_SEG_COST")) : 26;
     const int min_take = 8;  // never cut a segment shorter than one stage (unless the tile ends)
     const int G = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * slots_per_sm, (int64_t)tiles.size() * ((K + min_take - 1) / min_take)));
+    // Large matrices: the CTAs run side by side at the same speed, so what CTA b does as its s-th
+    // tile decides what is in L2 together.  In row-major order the 148 CTAs sit in 148 different
+    // tile rows and every operand strip comes from DRAM (cfg3: 54.8 GB read for 0.4 GB of
+    // profiles, profiles/r01_ncu_dist_cfg3.txt).  Here the off-diagonal tiles are listed by
+    // SB x SB super-blocks (rows by their rank among the shard's rows) and, once the cuts are
+    // known, dealt so that step s of all CTAs is one run of that list: one super-block's 2 SB
+    // strips at a time.  Diagonal tiles (cheaper, so they would shift the cuts) go last.  Off-
+    // diagonal tiles all cost the same, so the permutation leaves the cuts where they were.
+    const int SB = getenv("LZG_DIST_SB") ? atoi(getenv("LZG_DIST_SB")) : 12;
+    size_t n_off = 0;
+    for (const int2& t : tiles) n_off += t.x != t.y;
+    const bool reorder = SB > 0 && n_off >= (size_t)2 * G;
+    if (reorder) {
+        std::vector<int> rank_of(R, 0);
+        for (int r = 0, k = 0; r < R; r++) {
+            int pr = std::min(r, R - 1 - r);
+            if (pr % n_shards != shard || r < row_lo || r >= row_hi) continue;
+            rank_of[r] = k++;
+        }
+        std::vector<int2> off, diag;
+        for (const int2& t : tiles) (t.x == t.y ? diag : off).push_back(t);
+        std::stable_sort(off.begin(), off.end(), [&](const int2& a, const int2& b) {
+            const int ba = rank_of[a.x] / SB, bb = rank_of[b.x] / SB;
+            if (ba != bb) return ba < bb;
+            return a.y / SB < b.y / SB;  // inside a super-block: row-major, as listed
+        });
+        tiles = off;
+        tiles.insert(tiles.end(), diag.begin(), diag.end());
+    }
     std::vector<lzg_seg> segs;
-    std::vector<int32_t> seg_off;
+    std::vector<int32_t> seg_off, seg_tile;
     // greedy fill with a per-CTA budget; returns the number of CTAs used (segments written when emit)
     auto fill = [&](int64_t budget, bool emit) {
         int ctas = 1;
         int64_t load = 0;
         if (emit) {
             segs.clear();
+            seg_tile.clear();
             seg_off.assign(1, 0);
         }
-        for (const int2& t : tiles) {
+        for (size_t ti = 0; ti < tiles.size(); ti++) {
+            const int2 t = tiles[ti];
             const int u = t.x == t.y ? 3 : 4;
             int k = 0;
             while (k < K) {
@@ -392,7 +423,10 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
                 }
                 int take = (int)std::min<int64_t>(K - k, std::max<int64_t>(want, (budget - load - seg_cost) / u));
                 if (K - k - take < min_take) take = K - k;  // no sliver at the end of a tile
-                if (emit) segs.push_back(lzg_seg{t.x, t.y, k, k + take});
+                if (emit) {
+                    segs.push_back(lzg_seg{t.x, t.y, k, k + take});
+                    seg_tile.push_back((int32_t)ti);
+                }
                 load += seg_cost + (int64_t)take * u;
                 k += take;
             }
@@ -405,7 +439,35 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
         if (fill(mid, false) <= G) hi = mid;
         else lo = mid + 1;
     }
-    const int used = tiles.empty() ? 0 : fill(lo, true);
+    int used = tiles.empty() ? 0 : fill(lo, true);
+    if (reorder) {
+        // x0[b] = list position of the tile CTA b starts in; CTAs 0 .. g_off-1 start among the off-diagonal tiles
+        std::vector<int64_t> x0;
+        for (int b = 0; b < used; b++) x0.push_back(seg_tile[seg_off[b]]);
+        int g_off = 0;
+        while (g_off < used && x0[g_off] < (int64_t)n_off) g_off++;
+        std::vector<int2> ord(tiles.begin(), tiles.begin() + n_off), out(n_off, make_int2(-1, -1));
+        std::vector<char> taken(n_off, 0);
+        for (int b = 0; b < g_off; b++) {
+            const int64_t x1 = b + 1 < used ? std::min<int64_t>(x0[b + 1], (int64_t)n_off) : (int64_t)n_off;
+            for (int64_t pos = x0[b]; pos < x1; pos++) {
+                const int64_t idx = (pos - x0[b]) * g_off + b;
+                if (idx < (int64_t)n_off && !taken[idx]) {
+                    out[pos] = ord[idx];
+                    taken[idx] = 1;
+                }
+            }
+        }
+        size_t next = 0;
+        for (size_t pos = 0; pos < n_off; pos++) {
+            if (out[pos].x >= 0) continue;
+            while (taken[next]) next++;
+            out[pos] = ord[next];
+            taken[next++] = 1;
+        }
+        std::copy(out.begin(), out.end(), tiles.begin());
+        used = fill(lo, true);
+    }
     if (!tiles.empty()) seg_off.push_back((int32_t)segs.size());
     // tiles cut into several segments are accumulated with atomics
     std::vector<int2> split;

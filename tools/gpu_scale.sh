@@ -3,7 +3,7 @@
 # usage (gpurun --gpus 8): bash tools/gpu_scale.sh [steps]
 steps=${1:-10}
 mkdir -p gpurun_out
-timeout 600 python bench.py --gpus 1 --steps $steps --warmup 3 --workload cfg3 --no-nni-large > gpurun_out/scale_n1.json 2> gpurun_out/scale_n1.err; echo "N=1 rc=$?"
+timeout 600 python bench.py --gpus 1 --steps $steps --warmup 3 --no-nni-large > gpurun_out/scale_n1.json 2> gpurun_out/scale_n1.err; echo "N=1 rc=$?"
 for N in 2 4 8; do
     timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29600 + N)) \
         bench.py --gpus $N --steps $steps --warmup 3 > gpurun_out/scale_n$N.json 2> gpurun_out/scale_n$N.err; echo "N=$N rc=$?"
