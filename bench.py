@@ -56,8 +56,12 @@ SAD4_PEAK_LANE_INSTR_PER_S = 1.8304e13
 # DRAM traffic per launch / per pass from the committed ncu --set full captures (bytes); None elsewhere
 NCU_DRAM_BYTES = {
     ("distance", "cfg2"): 14432768,                                   # k_zcnt_distance: 14.43 MB read, 0 written (14.0 MB algorithmic)
+    ("distance", "cfg3"): 12706586000 + 1601038000,                   # 12.7 GB read + 1.6 GB written (2.0 GB algorithmic); 54.75 + 1.60 GB before the super-block tile order
     ("nni", "cfg5 on 1 GPU"): 513864000 + 364247296 + 1283499000 + 4908800,  # k_up_pass (r + w) + k_nni_items (r + w); 2.93 GB algorithmic
 }
+
+
+NCU_DIST_FILES = {"cfg2": "r01_ncu_dist_cfg2.txt", "cfg3": "r01_ncu_dist_cfg3_v2.txt"}
 
 
 def measured_peaks():
@@ -648,7 +652,7 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
                          "unit": "G lane-instr/s (VABSDIFF4.U8.ACC, 4 positions each) per GPU", "frac": achieved / SAD4_PEAK_LANE_INSTR_PER_S,
                          "peak_kind": "measured (tools/microbench.cu on this pool, profiles/r01_microbench_int_pipes.jsonl)",
                          "traffic": NCU_DRAM_BYTES.get(("distance", name)),
-                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r01_ncu_dist_cfg2.txt)"
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/%s)" % NCU_DIST_FILES.get(name)
                                            if ("distance", name) in NCU_DRAM_BYTES else None,
                          "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / world / (ms_step * 1e-3) / 1e9, "peak_gbs": peaks["hbm_gbs"],
                                  "frac": hbm_bytes / world / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_kind": peaks_kind}},

@@ -376,12 +376,15 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
     // profiles, profiles/r01_ncu_dist_cfg3.txt).  Here the off-diagonal tiles are listed by
     // SB x SB super-blocks (rows by their rank among the shard's rows) and, once the cuts are
     // known, dealt so that step s of all CTAs is one run of that list: one super-block's 2 SB
-    // strips at a time.  Diagonal tiles (cheaper, so they would shift the cuts) go last.  Off-
-    // diagonal tiles all cost the same, so the permutation leaves the cuts where they were.
+    // strips at a time.  Only off-diagonal tiles change places, and they all cost the same, so
+    // the cuts stay where the row-major list put them; the diagonal tiles keep their positions
+    // (spread over the CTAs: their cost is the least certain, and a CTA holding only diagonal
+    // tiles finished 1.6 ms late at cfg3).
     const int SB = getenv("LZG_DIST_SB") ? atoi(getenv("LZG_DIST_SB")) : 12;
     size_t n_off = 0;
     for (const int2& t : tiles) n_off += t.x != t.y;
     const bool reorder = SB > 0 && n_off >= (size_t)2 * G;
+    std::vector<int2> ord;
     if (reorder) {
         std::vector<int> rank_of(R, 0);
         for (int r = 0, k = 0; r < R; r++) {
@@ -389,15 +392,27 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
             if (pr % n_shards != shard || r < row_lo || r >= row_hi) continue;
             rank_of[r] = k++;
         }
-        std::vector<int2> off, diag;
-        for (const int2& t : tiles) (t.x == t.y ? diag : off).push_back(t);
-        std::stable_sort(off.begin(), off.end(), [&](const int2& a, const int2& b) {
+        for (const int2& t : tiles)
+            if (t.x != t.y) ord.push_back(t);
+        std::stable_sort(ord.begin(), ord.end(), [&](const int2& a, const int2& b) {
             const int ba = rank_of[a.x] / SB, bb = rank_of[b.x] / SB;
             if (ba != bb) return ba < bb;
             return a.y / SB < b.y / SB;  // inside a super-block: row-major, as listed
         });
-        tiles = off;
-        tiles.insert(tiles.end(), diag.begin(), diag.end());
+    }
+    // Phase-aligned form (LZG_DIST_ALIGN, default on): every CTA first runs m = n_off / G WHOLE
+    // off-diagonal tiles -- CTA b's s-th is ord[s * G + b], so all CTAs start every tile together
+    // and the CTAs sharing a strip want the same chunk at the same time -- and only the rest
+    // (fewer than G off-diagonal tiles plus the diagonal ones) is cut into G equal-cost tails.
+    const bool aligned = reorder && !(getenv("LZG_DIST_ALIGN") && atoi(getenv("LZG_DIST_ALIGN")) == 0);
+    const size_t m_whole = aligned ? n_off / (size_t)G : 0;
+    if (aligned) {
+        std::vector<int2> rest(ord.begin() + m_whole * G, ord.end());
+        for (const int2& t : tiles)
+            if (t.x == t.y) rest.push_back(t);
+        tiles.swap(rest);
+        units = 0;
+        for (const int2& t : tiles) units += (int64_t)K * (t.x == t.y ? 3 : 4);
     }
     std::vector<lzg_seg> segs;
     std::vector<int32_t> seg_off, seg_tile;
@@ -440,32 +455,33 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
         else lo = mid + 1;
     }
     int used = tiles.empty() ? 0 : fill(lo, true);
-    if (reorder) {
-        // x0[b] = list position of the tile CTA b starts in; CTAs 0 .. g_off-1 start among the off-diagonal tiles
+    if (reorder && !aligned) {
+        // x0[b] = list position of the tile CTA b starts in; its s-th off-diagonal tile becomes ord[s * used + b]
         std::vector<int64_t> x0;
         for (int b = 0; b < used; b++) x0.push_back(seg_tile[seg_off[b]]);
-        int g_off = 0;
-        while (g_off < used && x0[g_off] < (int64_t)n_off) g_off++;
-        std::vector<int2> ord(tiles.begin(), tiles.begin() + n_off), out(n_off, make_int2(-1, -1));
-        std::vector<char> taken(n_off, 0);
-        for (int b = 0; b < g_off; b++) {
-            const int64_t x1 = b + 1 < used ? std::min<int64_t>(x0[b + 1], (int64_t)n_off) : (int64_t)n_off;
-            for (int64_t pos = x0[b]; pos < x1; pos++) {
-                const int64_t idx = (pos - x0[b]) * g_off + b;
+        x0.push_back((int64_t)tiles.size());
+        std::vector<char> taken(n_off, 0), placed(tiles.size(), 0);
+        for (int b = 0; b < used; b++) {
+            int64_t step = 0;
+            for (int64_t pos = x0[b]; pos < x0[b + 1]; pos++) {
+                if (tiles[pos].x == tiles[pos].y) {
+                    placed[pos] = 1;
+                    continue;
+                }
+                const int64_t idx = step++ * used + b;
                 if (idx < (int64_t)n_off && !taken[idx]) {
-                    out[pos] = ord[idx];
-                    taken[idx] = 1;
+                    tiles[pos] = ord[idx];
+                    taken[idx] = placed[pos] = 1;
                 }
             }
         }
         size_t next = 0;
-        for (size_t pos = 0; pos < n_off; pos++) {
-            if (out[pos].x >= 0) continue;
+        for (size_t pos = 0; pos < tiles.size(); pos++) {
+            if (placed[pos]) continue;
             while (taken[next]) next++;
-            out[pos] = ord[next];
+            tiles[pos] = ord[next];
             taken[next++] = 1;
         }
-        std::copy(out.begin(), out.end(), tiles.begin());
         used = fill(lo, true);
     }
     if (!tiles.empty()) seg_off.push_back((int32_t)segs.size());
@@ -479,6 +495,22 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
             split.push_back(make_int2(segs[q].r, segs[q].c));
         }
         q = e;
+    }
+    if (aligned) {  // CTA b: its whole tiles, then its tail
+        std::vector<lzg_seg> all;
+        std::vector<int32_t> all_off;
+        for (int b = 0; b < G; b++) {
+            all_off.push_back((int32_t)all.size());
+            for (size_t st = 0; st < m_whole; st++) {
+                const int2 t = ord[st * G + b];
+                all.push_back(lzg_seg{t.x, t.y, 0, K});
+            }
+            if (b < used) all.insert(all.end(), segs.begin() + seg_off[b], segs.begin() + seg_off[b + 1]);
+        }
+        all_off.push_back((int32_t)all.size());
+        segs.swap(all);
+        seg_off.swap(all_off);
+        used = G;
     }
     const int Gu = std::max(used, 1);
     if (seg_off.empty()) seg_off.assign(2, 0);

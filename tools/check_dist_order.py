@@ -20,8 +20,9 @@ for r0 in range(0, cells, 2000):
 del prof
 
 
-def run(sb, n_shards):
+def run(sb, n_shards, align=1):
     os.environ["LZG_DIST_SB"] = str(sb)
+    os.environ["LZG_DIST_ALIGN"] = str(align)
     with Context(0) as ctx:   # a fresh context: schedules are cached per context
         gp = Profiles(ctx, bp)
         d = torch.zeros((cells, cells), dtype=torch.int32, device="cuda")
@@ -41,9 +42,9 @@ def run(sb, n_shards):
 
 ref, t0 = run(0, 1)
 print("row-major      1 shard : %.3f ms" % t0, flush=True)
-for sb in (12, 8, 16):
-    d, t = run(sb, 1)
-    print("super-block %2d 1 shard : %.3f ms  equal=%s" % (sb, t, bool(torch.equal(d, ref))), flush=True)
+for sb, al in ((12, 0), (12, 1), (8, 1), (16, 1)):
+    d, t = run(sb, 1, al)
+    print("super-block %2d align %d 1 shard : %.3f ms  equal=%s" % (sb, al, t, bool(torch.equal(d, ref))), flush=True)
     del d
 d, t = run(0, 8)
 print("row-major      8 shards: %.3f ms (sum)  equal=%s" % (t, bool(torch.equal(d, ref))), flush=True)

@@ -3,6 +3,7 @@
 # and an ncu --set full capture of k_zcnt_distance at cfg3 (device-resident, one launch per matrix).
 # Usage (on the GPU box, from the repo root): bash tools/gpu_final.sh
 mkdir -p gpurun_out
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -2 gpurun_out/pytest_gpu.log
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "ref rc=$?"
 timeout 600 python bench.py > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench rc=$?"
 timeout 300 python tools/prof_distance.py 20000 10000 2 2 device > gpurun_out/prof_dist_cfg3_plain.log 2>&1 &&
