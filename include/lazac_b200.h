@@ -88,6 +88,18 @@ int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard, int32
 int lzg_distance_shard_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard,
                                     int32_t n_shards, int32_t* d_D, int64_t* pairs_done);
 
+/* Host only -- no GPU, no context: the work plan lzg_distance_* launches for an n x L input on a
+ * device of sm_count SMs (one persistent CTA per SM).  segs receives four ints per
+ * segment {tile row, tile column, k0, k1}: 16-byte position chunks [k0, |k1|) of that tile, k1 < 0
+ * where the tile is cut across CTAs and accumulated with atomics; CTA b runs segments
+ * seg_off[b] .. seg_off[b+1].  info = {CTAs, segments, tile edge, chunks per row} is always filled;
+ * LZG_ERR_ARG when cap_segs / cap_ctas are too small (call again with info's sizes).  row_lo/row_hi
+ * restrict the tile rows (0, INT32_MAX for all).  The CPU tests check with it that every chunk of
+ * every tile of the reference's i <= j loop (src/lazac.cxx:81-91) is covered exactly once. */
+int lzg_distance_plan(int32_t n, int32_t L, int32_t sm_count, int32_t shard, int32_t n_shards,
+                      int32_t row_lo, int32_t row_hi, int32_t* segs, int64_t cap_segs,
+                      int32_t* seg_off, int32_t cap_ctas, int32_t* info);
+
 /* ---- small parsimony on a resident tree: replaces digraph<rectilinear_vertex_data>
  *      (include/copy_number.hpp:98-105) and the functions that walk it. -------------------- */
 /* leaf_row[u] = profile row of leaf u, -1 for internal nodes (src/lazac.cxx:212-235). */

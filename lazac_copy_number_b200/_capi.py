@@ -16,6 +16,7 @@ STATUS = {0: "LZG_OK", 1: "LZG_ERR_ARG", 2: "LZG_ERR_NOT_BINARY", 3: "LZG_ERR_RA
 
 # every symbol include/lazac_b200.h declares: (name, restype, argtypes)
 _vp, _i, _i32, _i64p = C.c_void_p, C.c_int, C.c_int32, C.POINTER(C.c_int64)
+_i64 = C.c_int64
 _i32p = C.POINTER(C.c_int32)
 _vpp = C.POINTER(C.c_void_p)
 SYMBOLS = [
@@ -40,6 +41,7 @@ SYMBOLS = [
     ("lzg_distance_matrix_device_async", _i, [_vp, _vp, _vp]),
     ("lzg_distance_shard", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
     ("lzg_distance_shard_device_async", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
+    ("lzg_distance_plan", _i, [_i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _i32, _vp]),
     ("lzg_tree_create", _i, [_vp, _vp, _i32, _vp, _vp, _vp, _vpp]),
     ("lzg_tree_clone", _i, [_vp, _vp, _vpp]),
     ("lzg_tree_free", _i, [_vp]),

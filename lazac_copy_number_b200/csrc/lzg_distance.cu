@@ -340,15 +340,22 @@ constexpr int dist_smem_bytes() {
 // gets the same triangle area.  Cost of one 16-byte chunk of a tile: 4 units, 3 for a diagonal
 // tile; every segment adds LZG_SEG_COST units (pipeline fill + epilogue, about 0.8 of a 128-byte
 // stage measured on cfg2).  The smallest feasible per-CTA budget is found by bisection.
-const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slots_per_sm, int shard, int n_shards,
-                                 int row_lo, int row_hi, int* status) {
-    for (auto& sc : ctx->schedules)
-        if (sc.n == p->n && sc.l_pad == p->l_pad && sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
-    const int R = (p->n + bm - 1) / bm;
-    const int K = p->l_pad / 16;  // chunks per row
+struct lzg_plan {
+    std::vector<lzg_seg> segs;
+    std::vector<int32_t> seg_off;  // [n_ctas + 1]
+    std::vector<int2> split;       // tiles accumulated with atomics
+    int64_t pairs = 0;
+    int n_ctas = 0;
+};
+
+// Host only (no CUDA call): lzg_distance_plan exports it so the CPU tests can check coverage and balance.
+void plan_schedule(int n, int l_pad, int bm, int sm_count, int slots_per_sm, int shard, int n_shards, int row_lo, int row_hi,
+                   lzg_plan& out) {
+    const int R = (n + bm - 1) / bm;
+    const int K = l_pad / 16;  // chunks per row
     std::vector<int2> tiles;
     int64_t pairs = 0, units = 0;
-    auto rows_in = [&](int r) { return (int64_t)(std::min(p->n, (r + 1) * bm) - r * bm); };
+    auto rows_in = [&](int r) { return (int64_t)(std::min(n, (r + 1) * bm) - r * bm); };
     for (int r = 0; r < R; r++) {
         int pr = std::min(r, R - 1 - r);
         if (pr % n_shards != shard || r < row_lo || r >= row_hi) continue;
@@ -358,18 +365,9 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
             units += (int64_t)K * (c == r ? 3 : 4);
         }
     }
-    lzg_schedule sc;
-    sc.n = p->n;
-    sc.l_pad = p->l_pad;
-    sc.bm = bm;
-    sc.shard = shard;
-    sc.n_shards = n_shards;
-    sc.row_lo = row_lo;
-    sc.row_hi = row_hi;
-    sc.pairs = pairs;
     const int64_t seg_cost = getenv("LZG_SEG_COST") ? atoi(getenv("LZG_SEG_COST")) : 26;
     const int min_take = 8;  // never cut a segment shorter than one stage (unless the tile ends)
-    const int G = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * slots_per_sm, (int64_t)tiles.size() * ((K + min_take - 1) / min_take)));
+    const int G = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count * slots_per_sm, (int64_t)tiles.size() * ((K + min_take - 1) / min_take)));
     // Large matrices: the CTAs run side by side at the same speed, so what CTA b does as its s-th
     // tile decides what is in L2 together.  In row-major order the 148 CTAs sit in 148 different
     // tile rows and every operand strip comes from DRAM (cfg3: 54.8 GB read for 0.4 GB of
@@ -512,9 +510,33 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
         seg_off.swap(all_off);
         used = G;
     }
-    const int Gu = std::max(used, 1);
     if (seg_off.empty()) seg_off.assign(2, 0);
-    sc.n_ctas = Gu;
+    out.segs.swap(segs);
+    out.seg_off.swap(seg_off);
+    out.split.swap(split);
+    out.pairs = pairs;
+    out.n_ctas = std::max(used, 1);
+}
+
+const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slots_per_sm, int shard, int n_shards,
+                                 int row_lo, int row_hi, int* status) {
+    for (auto& sc : ctx->schedules)
+        if (sc.n == p->n && sc.l_pad == p->l_pad && sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
+    lzg_plan plan;
+    plan_schedule(p->n, p->l_pad, bm, ctx->sm_count, slots_per_sm, shard, n_shards, row_lo, row_hi, plan);
+    std::vector<lzg_seg>& segs = plan.segs;
+    std::vector<int32_t>& seg_off = plan.seg_off;
+    std::vector<int2>& split = plan.split;
+    lzg_schedule sc;
+    sc.n = p->n;
+    sc.l_pad = p->l_pad;
+    sc.bm = bm;
+    sc.shard = shard;
+    sc.n_shards = n_shards;
+    sc.row_lo = row_lo;
+    sc.row_hi = row_hi;
+    sc.pairs = plan.pairs;
+    sc.n_ctas = plan.n_ctas;
     sc.n_segs = (int)segs.size();
     sc.n_split = (int)split.size();
     if (sc.n_segs > 0) {
@@ -608,4 +630,27 @@ int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int
     if (pairs_done) *pairs_done = sc->pairs;
     if (sc->n_segs == 0) return LZG_OK;
     return bm == 64 ? launch_distance<64, 64, 4>(ctx, p, sc, d_D) : launch_distance<128, 128, 3>(ctx, p, sc, d_D);
+}
+
+// Host-only view of the work plan (no GPU, no context): see include/lazac_b200.h.
+int lzg_distance_plan(int32_t n, int32_t L, int32_t sm_count, int32_t shard, int32_t n_shards, int32_t row_lo, int32_t row_hi,
+                      int32_t* segs, int64_t cap_segs, int32_t* seg_off, int32_t cap_ctas, int32_t* info) {
+    if (n < 1 || L < 1 || sm_count < 1 || n_shards < 1 || shard < 0 || shard >= n_shards || !info) return LZG_ERR_ARG;
+    const int l_pad = std::max(128, (L + 127) / 128 * 128);  // as lzg_profiles_upload pads
+    const int bm = n <= 64 ? 64 : 128;                       // lzg_distance_tile
+    lzg_plan plan;
+    plan_schedule(n, l_pad, bm, sm_count, bm == 64 ? 3 : 1, shard, n_shards, row_lo, row_hi, plan);
+    info[0] = plan.n_ctas;
+    info[1] = (int32_t)plan.segs.size();
+    info[2] = bm;
+    info[3] = l_pad / 16;
+    if ((int64_t)plan.segs.size() > cap_segs || plan.n_ctas > cap_ctas || (plan.segs.size() && (!segs || !seg_off))) return LZG_ERR_ARG;
+    for (size_t i = 0; i < plan.segs.size(); i++) {
+        segs[4 * i] = plan.segs[i].r;
+        segs[4 * i + 1] = plan.segs[i].c;
+        segs[4 * i + 2] = plan.segs[i].k0;
+        segs[4 * i + 3] = plan.segs[i].k1;
+    }
+    for (int b = 0; b <= plan.n_ctas; b++) seg_off[b] = plan.seg_off[b];
+    return LZG_OK;
 }
