@@ -56,12 +56,12 @@ SAD4_PEAK_LANE_INSTR_PER_S = 1.8304e13
 # DRAM traffic per launch / per pass from the committed ncu --set full captures (bytes); None elsewhere
 NCU_DRAM_BYTES = {
     ("distance", "cfg2"): 14432768,                                   # k_zcnt_distance: 14.43 MB read, 0 written (14.0 MB algorithmic)
-    ("distance", "cfg3"): 12706586000 + 1601038000,                   # 12.7 GB read + 1.6 GB written (2.0 GB algorithmic); 54.75 + 1.60 GB before the super-block tile order
+    ("distance", "cfg3"): 7686961408 + 1603739392,                    # 7.7 GB read + 1.6 GB written (2.0 GB algorithmic); 54.75 + 1.60 GB with the row-major tile list
     ("nni", "cfg5 on 1 GPU"): 513864000 + 364247296 + 1283499000 + 4908800,  # k_up_pass (r + w) + k_nni_items (r + w); 2.93 GB algorithmic
 }
 
 
-NCU_DIST_FILES = {"cfg2": "r01_ncu_dist_cfg2.txt", "cfg3": "r01_ncu_dist_cfg3_v2.txt"}
+NCU_DIST_FILES = {"cfg2": "r01_ncu_dist_cfg2.txt", "cfg3": "r01_ncu_dist_cfg3_v3.txt"}
 
 
 def measured_peaks():
