@@ -56,7 +56,7 @@ SAD4_PEAK_LANE_INSTR_PER_S = 1.8304e13
 # DRAM traffic per launch / per pass from the committed ncu --set full captures (bytes); None elsewhere
 NCU_DRAM_BYTES = {
     ("distance", "cfg2"): 14432768,                                   # k_zcnt_distance: 14.43 MB read, 0 written (14.0 MB algorithmic)
-    ("distance", "cfg3"): 7686961408 + 1603739392,                    # 7.7 GB read + 1.6 GB written (2.0 GB algorithmic); 54.75 + 1.60 GB with the row-major tile list
+    ("distance", "cfg3"): 7726542000 + 1607675000,                    # 7.7 GB read + 1.6 GB written (2.0 GB algorithmic); 54.75 + 1.60 GB with the row-major tile list
     ("nni", "cfg5 on 1 GPU"): 513864000 + 364247296 + 1283499000 + 4908800,  # k_up_pass (r + w) + k_nni_items (r + w); 2.93 GB algorithmic
 }
 
