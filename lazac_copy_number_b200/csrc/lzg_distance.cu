@@ -122,10 +122,12 @@ __global__ void k_bias_rows_i8(uint8_t* __restrict__ d, int n, int L, int l_pad,
 // BM x BN tile of cell pairs (rows of tile-row r against rows of tile-row c, c >= r) over the
 // 16-byte position chunks [k0, k1).  The grid is persistent -- one CTA per SM -- and CTA b
 // executes segments seg_off[b] .. seg_off[b+1].  The host cuts the (tile, chunk) space into
-// contiguous ranges of equal cost (stream-K at chunk granularity, a fixed cost per segment for its
+// ranges of equal cost (stream-K at chunk granularity, a fixed cost per segment for its
 // pipeline fill and epilogue), so every SM finishes together whatever the number of tiles; a
 // tile cut across CTAs is accumulated with integer atomics (exact, order-free) into cells zeroed
-// by k_zero_tiles.
+// by k_zero_tiles.  For large matrices the plan also decides which tiles run side by side (whole
+// tiles in lock step, one super-block of tiles at a time) so that operand strips are shared
+// through the L2 -- plan_schedule below.
 //
 // Diagonal tiles (r == c) skip their lower-left quadrant: thread (ty, tx) owns rows ty + TY*i and
 // columns tx + TX*j, so "row >= BM/2 and column < BN/2" is i >= 4 && j < 4 for every thread
