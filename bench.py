@@ -661,7 +661,7 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
         if n1_same:
             line["n1_same_workload"] = n1_same
     if world == 1 and cpu:
-        n_sample = args.ref_cells or (160 if L <= 10000 else 110)
+        n_sample = args.ref_cells or (500 if L <= 10000 else 360)   # about 10 s of the reference's pair loop
         v, kind, dt, pairs = cpu_distance_sample(bp, min(n, n_sample))
         line["cpu_baseline"] = {"value": v, "unit": "cell-pairs/s", "cores": 1, "kind": kind,
                                 "sample": "first %d cells of the same input (%d pairs, %.1f s)" % (min(n, n_sample), pairs, dt)}
