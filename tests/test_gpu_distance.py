@@ -108,3 +108,21 @@ def test_int8_minus_128_is_out_of_range(ctx):
     with pytest.raises(LazacGpuError) as e:
         Profiles(ctx, bp)
     assert e.value.status == 3
+
+
+def test_tile_orders_give_the_same_matrix(port, monkeypatch):
+    """The plan's tile order (row-major list, super-blocks, phase-aligned whole tiles)
+    only decides which CTA computes what and when: 26 tile rows = 325 off-diagonal tiles is enough
+    to switch the re-ordering on, and every order must give the oracle's matrix bit for bit."""
+    from lazac_copy_number_b200.api import Context
+    n, L = 3300, 200
+    bp = synth.random_bp(n, L, seed=21, density=0.3)
+    want = port.distance_matrix(bp)
+    for sb, aligned in (("0", "0"), ("12", "0"), ("12", "1"), ("5", "1")):
+        monkeypatch.setenv("LZG_DIST_SB", sb)
+        monkeypatch.setenv("LZG_DIST_ALIGN", aligned)
+        with Context(0) as own:          # schedules are cached per context
+            prof = Profiles(own, bp)
+            got = prof.distance_matrix()
+            prof.free()
+        assert np.array_equal(got, want), (sb, aligned)
