@@ -154,6 +154,9 @@ int lzg_tree_apply_nni(lzg_ctx* ctx, lzg_tree* t, int32_t u, int32_t w, int32_t 
 /* start/end: int32 [n_nodes][L]; score: int32 [n_nodes] (any may be NULL). */
 int lzg_tree_get_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end,
                            int32_t* score);
+/* The same for the listed nodes only: start/end int32 [n_ids][L] (either may be NULL). */
+int lzg_tree_get_node_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t n_ids, const int32_t* ids,
+                                int32_t* start, int32_t* end);
 /* ancestral_labeling's per-position math, src/copy_number.cxx:165-225: labels int32
  * [n_nodes][L] and in_branch_len int32 [n_nodes] (-1 for the root), indexed by THIS tree's node
  * ids; the pre-order renumbering of :215 is host logic. */

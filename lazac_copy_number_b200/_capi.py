@@ -56,6 +56,7 @@ SYMBOLS = [
     ("lzg_nni_best_sharded", _i, [_vp, _vp, _vp, _i32, _vp, _i32, _i32p, _i32p, _vp]),
     ("lzg_tree_apply_nni", _i, [_vp, _vp, _i32, _i32, _i32, _i32, _i32p]),
     ("lzg_tree_get_intervals", _i, [_vp, _vp, _vp, _vp, _vp]),
+    ("lzg_tree_get_node_intervals", _i, [_vp, _vp, _i32, _vp, _vp, _vp]),
     ("lzg_tree_ancestral", _i, [_vp, _vp, _vp, _vp]),
     ("lzg_tree_last_candidate_score", _i, [_vp, _i32p]),
     ("lzg_tree_last_nni_work", _i, [_vp, _i64p, _i64p]),

@@ -256,6 +256,19 @@ class Tree:
         self.ctx.check(self.ctx.lib.lzg_tree_get_intervals(self.ctx.h, self.h, ptr(S), ptr(E), ptr(sc)))
         return S, E, sc
 
+    def node_intervals(self, ids):
+        """(start, end) int32 [len(ids)][L] of the listed nodes; scores() has the cumulative scores."""
+        ids = i32(ids)
+        S = np.zeros((len(ids), self.L), np.int32)
+        E = np.zeros((len(ids), self.L), np.int32)
+        self.ctx.check(self.ctx.lib.lzg_tree_get_node_intervals(self.ctx.h, self.h, len(ids), ptr(ids), ptr(S), ptr(E)))
+        return S, E
+
+    def scores(self):
+        sc = np.zeros(self.n, np.int32)
+        self.ctx.check(self.ctx.lib.lzg_tree_get_intervals(self.ctx.h, self.h, None, None, ptr(sc)))
+        return sc
+
     def ancestral_labeling(self):
         """ancestral_labeling(t, 0, bins), src/copy_number.cxx:187-225, including the pre-order
         renumbering (children pushed ascending, so the larger id is numbered first).

@@ -746,6 +746,18 @@ int lzg_tree_download(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* 
     return rc;
 }
 
+// start/end rows of the listed nodes only ([n_ids][L] each): trees beyond a few GB are inspected node by node.
+int lzg_tree_download_rows(lzg_ctx* ctx, const lzg_tree* t, int n_ids, const int32_t* ids, int32_t* start, int32_t* end) {
+    for (int k = 0; k < n_ids; k++) {
+        if (ids[k] < 0 || ids[k] >= t->n_nodes) return lzg_fail(ctx, LZG_ERR_ARG, "node id out of range");
+        int rc = LZG_OK;
+        if (start) rc = download_bytes_as_i32(ctx, t->d_start + (size_t)ids[k] * t->l_pad, 1, t->L, t->l_pad, start + (size_t)k * t->L);
+        if (rc == LZG_OK && end) rc = download_bytes_as_i32(ctx, t->d_end + (size_t)ids[k] * t->l_pad, 1, t->L, t->l_pad, end + (size_t)k * t->L);
+        if (rc != LZG_OK) return rc;
+    }
+    return LZG_OK;
+}
+
 // Depth-level schedule, root first.
 int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* branch) {
     const int n = t->n_nodes;

@@ -57,3 +57,4 @@ int lzg_tree_nni_scores(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
 int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z);
 int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* branch);
 int lzg_tree_download(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end, int32_t* score);
+int lzg_tree_download_rows(lzg_ctx* ctx, const lzg_tree* t, int n_ids, const int32_t* ids, int32_t* start, int32_t* end);

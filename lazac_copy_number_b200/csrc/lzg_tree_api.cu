@@ -238,6 +238,12 @@ int lzg_tree_get_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int3
     return lzg_tree_download(ctx, t, start, end, score);
 }
 
+int lzg_tree_get_node_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t n_ids, const int32_t* ids, int32_t* start, int32_t* end) {
+    if (!ctx || !t || t->ctx != ctx || n_ids < 0 || (n_ids > 0 && !ids)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_tree_get_node_intervals: bad argument");
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    return lzg_tree_download_rows(ctx, t, n_ids, ids, start, end);
+}
+
 int lzg_tree_ancestral(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* in_branch_len) {
     if (!ctx || !t || t->ctx != ctx) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_tree_ancestral: bad argument");
     if (!t->scored) return lzg_fail(ctx, LZG_ERR_STATE, "tree must be scored before lzg_tree_ancestral");

@@ -56,6 +56,8 @@ class Port:
         lib.zo_cn_from_bp.argtypes = [C.c_int, _i32p, _i32p, _i32p]
         lib.zo_distance_matrix.argtypes = [C.c_int, C.c_int, _i32p, _i32p]
         lib.zo_distance_rows.argtypes = [C.c_int, C.c_int, _i32p, C.c_int, C.c_int, _i32p]
+        lib.zo_distance_rows_i8.argtypes = [C.c_int, C.c_int, np.ctypeslib.ndpointer(dtype=np.int8, flags="C_CONTIGUOUS"),
+                                            C.c_int, _i32p, _i32p]
         lib.zo_merge.argtypes = [C.c_int] + [_i32p] * 6
         lib.zo_merge.restype = C.c_int32
         lib.zo_small_rectilinear.argtypes = [C.c_int, C.c_int] + [_i32p] * 6
@@ -89,6 +91,15 @@ class Port:
         n, L = bp.shape
         D = np.zeros((r1 - r0, n), np.int32)
         self.lib.zo_distance_rows(n, L, bp, r0, r1, D)
+        return D
+
+    def distance_rows_i8(self, bp, rows):
+        """Rows `rows` of the matrix (against every cell) from an int8 matrix: int32 [len(rows)][n]."""
+        bp = np.ascontiguousarray(bp, dtype=np.int8)
+        rows = _i32(rows)
+        n, L = bp.shape
+        D = np.zeros((len(rows), n), np.int32)
+        self.lib.zo_distance_rows_i8(n, L, bp, len(rows), rows, D)
         return D
 
     def merge(self, us, ue, vs, ve):

@@ -98,10 +98,49 @@ def tree_case(ref, n_leaves, bins, alleles, seed):
     return out
 
 
+def sim_cli_case(sim_name, out_dir, flags, keep_small=True):
+    """Leaves of one paper simulation through the reference CLI: the input travels gzipped, the
+    outputs as SHA-256 (plus the small files themselves)."""
+    import hashlib
+    sim = os.path.join(REFROOT, "data", "simulations", sim_name)
+    with open(sim + "_edgelist.csv") as f:
+        edges = [(r["src"], r["dst"]) for r in csv.DictReader(f)]
+    srcs = {a for a, _ in edges}
+    leafset = {b for _, b in edges if b not in srcs}
+    shutil.rmtree(out_dir, ignore_errors=True)
+    os.makedirs(out_dir)
+    with tempfile.TemporaryDirectory() as tmp:
+        src3 = os.path.join(tmp, "sim.csv")
+        with gzip.open(sim + "_full_cn_profiles.csv.gz", "rt") as f, open(src3, "w") as o:
+            o.write("node,chrom,start,end,cn_a\n")
+            for r in csv.DictReader(f):
+                if r["node"] in leafset:  # leaves only; names must not look like numbers (SURVEY.md F13)
+                    o.write("c%s,%s,%s,%s,%s\n" % (r["node"], r["chrom"], r["start"], r["end"], r["cn_a"]))
+        run_ref_cli(["nni", src3] + flags + ["-o", os.path.join(tmp, "sim")], timeout=3600)
+        with open(src3, "rb") as f, gzip.GzipFile(os.path.join(out_dir, "sim_cn_profile.csv.gz"), "wb", mtime=0) as o:
+            o.write(f.read())
+        hashes = {}
+        for fn in sorted(os.listdir(tmp)):
+            if fn == "sim.csv":
+                continue
+            with open(os.path.join(tmp, fn), "rb") as f:
+                data = f.read()
+            hashes[fn] = hashlib.sha256(data).hexdigest()
+            if keep_small and len(data) < 100000:
+                shutil.copy(os.path.join(tmp, fn), os.path.join(out_dir, fn))
+        with open(os.path.join(out_dir, "SHA256.txt"), "w") as f:
+            f.write("# %s leaves: lazac_ref nni sim.csv %s -o sim   (sim.csv = gunzip sim_cn_profile.csv.gz)\n" % (sim_name, " ".join(flags)))
+            for fn, h in hashes.items():
+                f.write("%s  %s\n" % (h, fn))
+
+
 def main():
     build()
     if not (have_ref() and have_ref_bin()):
         sys.exit("the reference is not built (needs /root/reference)")
+    if "--n600" in sys.argv:   # the 600-cell paper simulation alone (about three minutes of the reference CLI)
+        sim_cli_case("n600_l1000_s0", os.path.join(OUT, "sim600_cli"), ["-a", "1", "-i", "1", "-s", "1"], keep_small=True)
+        return
     ref = Ref()
     os.makedirs(OUT, exist_ok=True)
 

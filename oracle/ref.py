@@ -20,6 +20,11 @@ class Ref:
         lib.ref_distance_matrix.argtypes = [ci, ci, _i32p, _i32p]
         lib.ref_tree_new.argtypes = [ci, ci, _i32p, _i32p, _i32p]
         lib.ref_tree_new.restype = vp
+        _i8p = np.ctypeslib.ndpointer(dtype=np.int8, flags="C_CONTIGUOUS")
+        lib.ref_tree_new_i8.argtypes = [ci, ci, _i32p, _i32p, _i32p, _i8p]
+        lib.ref_tree_new_i8.restype = vp
+        lib.ref_distance_rows_i8.argtypes = [ci, ci, _i8p, ci, _i32p, _i32p]
+        lib.ref_get_scores.argtypes = [vp, _i32p]
         lib.ref_tree_clone.argtypes = [vp]
         lib.ref_tree_clone.restype = vp
         lib.ref_tree_free.argtypes = [vp]
@@ -60,8 +65,24 @@ class Ref:
         self.lib.ref_distance_matrix(n, L, bp, D)
         return D
 
+    def distance_rows_i8(self, bp, rows):
+        """The reference's pair arithmetic (operator- + breakpoint_magnitude) for the given rows
+        against every cell; bp is int8 [n][L].  Returns int32 [len(rows)][n]."""
+        bp = np.ascontiguousarray(bp, dtype=np.int8)
+        rows = _i32(rows)
+        n, L = bp.shape
+        D = np.zeros((len(rows), n), np.int32)
+        self.lib.ref_distance_rows_i8(n, L, bp, len(rows), rows, D)
+        return D
+
     def gen(self, seed):
         return RefGen(self, seed)
+
+    def tree_i8(self, child0, child1, leaf_row, bp):
+        """Tree whose leaves take their profiles from rows of a compact int8 matrix."""
+        bp = np.ascontiguousarray(bp, dtype=np.int8)
+        h = self.lib.ref_tree_new_i8(len(child0), bp.shape[1], _i32(child0), _i32(child1), _i32(leaf_row), bp)
+        return RefTree(self, handle=h, n=len(child0), L=bp.shape[1])
 
     def tree(self, child0, child1, leaf_bp):
         return RefTree(self, child0, child1, leaf_bp)
@@ -125,6 +146,11 @@ class RefTree:
                 S[u], E[u] = s, e
             sc[u] = k
         return S, E, sc
+
+    def scores(self):
+        sc = np.zeros(self.n, np.int32)
+        self.ref.lib.ref_get_scores(self.h, sc)
+        return sc
 
     def topology(self):
         c0, c1 = np.zeros(self.n, np.int32), np.zeros(self.n, np.int32)

@@ -109,6 +109,26 @@ int ref_distance_matrix(int N, int L, const int32_t* bp, int32_t* D) {
     return 0;
 }
 
+// Rows rows[0..n_rows) of the same pair loop against every cell, from a compact int8 matrix
+// (the large configurations: cfg3 is 400 MB as int8).  D_out is [n_rows][N].
+int ref_distance_rows_i8(int N, int L, const int8_t* bp, int n_rows, const int32_t* rows, int32_t* D_out) {
+    breakpoint_profile a, b;
+    a.bins.resize(L);
+    b.bins.resize(L);
+    a.profile.resize(L);
+    b.profile.resize(L);
+    for (int r = 0; r < n_rows; r++) {
+        const int8_t* ra = bp + (size_t)rows[r] * L;
+        for (int k = 0; k < L; k++) a.profile[k] = ra[k];
+        for (int j = 0; j < N; j++) {
+            const int8_t* rb = bp + (size_t)j * L;
+            for (int k = 0; k < L; k++) b.profile[k] = rb[k];
+            D_out[(size_t)r * N + j] = breakpoint_magnitude(a - b);
+        }
+    }
+    return 0;
+}
+
 // ---- trees -------------------------------------------------------------------------------
 // Nodes are 0..n_nodes-1, root = 0.  child0/child1 = -1 for leaves.  leaf_bp is
 // [n_nodes][L]; rows of internal nodes are ignored.
@@ -122,6 +142,30 @@ ref_tree* ref_tree_new(int n_nodes, int L, const int32_t* child0, const int32_t*
         r.name = std::to_string(u);
         if (child0[u] < 0 && child1[u] < 0) {
             std::vector<int> p(leaf_bp + (size_t)u * L, leaf_bp + (size_t)(u + 1) * L);
+            r.start = p;
+            r.end = p;
+        }
+        h->t.add_vertex(r);
+    }
+    for (int u = 0; u < n_nodes; u++) {
+        if (child0[u] >= 0) h->t.add_edge(u, child0[u]);
+        if (child1[u] >= 0) h->t.add_edge(u, child1[u]);
+    }
+    return h;
+}
+
+// Same, leaves taken from a compact int8 matrix: leaf_row[u] = row of bp for leaf u (-1 internal).
+ref_tree* ref_tree_new_i8(int n_nodes, int L, const int32_t* child0, const int32_t* child1,
+                          const int32_t* leaf_row, const int8_t* bp) {
+    ref_tree* h = new ref_tree();
+    h->n_nodes = n_nodes;
+    h->L = L;
+    for (int u = 0; u < n_nodes; u++) {
+        rectilinear_vertex_data r;
+        r.name = std::to_string(u);
+        if (child0[u] < 0 && child1[u] < 0) {
+            const int8_t* row = bp + (size_t)leaf_row[u] * L;
+            std::vector<int> p(row, row + L);
             r.start = p;
             r.end = p;
         }
@@ -159,6 +203,11 @@ int ref_get_node(const ref_tree* h, int u, int32_t* start, int32_t* end, int32_t
     if (start) std::memcpy(start, d.start->data(), sizeof(int32_t) * h->L);
     if (end) std::memcpy(end, d.end->data(), sizeof(int32_t) * h->L);
     return 0;
+}
+
+// score of every node
+void ref_get_scores(const ref_tree* h, int32_t* score) {
+    for (int u = 0; u < h->n_nodes; u++) score[u] = h->t[u].data.score;
 }
 
 // Children in ascending id order (std::set order), -1 for leaves.

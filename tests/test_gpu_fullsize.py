@@ -12,18 +12,12 @@ size-independent properties of the path:
 import numpy as np
 import pytest
 
+from _inputs import config_bp
 from lazac_copy_number_b200 import sharding, synth
 from lazac_copy_number_b200.api import Profiles, Tree
 from oracle import PortTree
 
 pytestmark = pytest.mark.gpu
-
-
-def bp_int8(cn, seg, rows=2000):
-    out = np.empty(cn.shape, np.int8)
-    for r0 in range(0, cn.shape[0], rows):
-        out[r0:r0 + rows] = synth.bp_from_cn(cn[r0:r0 + rows], seg).astype(np.int8)
-    return out
 
 
 def tree_arrays(n_leaves, seed):
@@ -68,9 +62,7 @@ def test_cfg5_shape_properties(ctx):
     19,996 candidates, 0.8 GB of intervals + 0.8 GB of UP intervals)."""
     import torch
     n_leaves = 10000
-    prof = synth.make_profiles(n_leaves, 10000, 2, seed=0)
-    bp = bp_int8(prof["cn"], prof["seg"])
-    del prof
+    bp = config_bp(n_leaves, 10000, 2)
     L = bp.shape[1]
     c0, c1, leaf_row = tree_arrays(n_leaves, 1)
     gp = Profiles(ctx, bp)
@@ -124,9 +116,7 @@ def test_cfg5_shape_properties(ctx):
 def test_cfg3_shape_distance_properties(ctx):
     """BASELINE.json configs[2]'s input on one GPU: 20,000 cells x 20,000 positions, 2.0e8 pairs."""
     n = 20000
-    prof = synth.make_profiles(n, 10000, 2, seed=0)
-    bp = bp_int8(prof["cn"], prof["seg"])
-    del prof
+    bp = config_bp(n, 10000, 2)
     gp = Profiles(ctx, bp)
     D = ctx.pinned((n, n), np.int32)
     gp.distance_matrix(D)

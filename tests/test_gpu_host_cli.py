@@ -74,22 +74,32 @@ def test_no_gpu_flag_errors_cleanly(tmp_path):
     assert r.returncode == 2 and "cannot open CUDA device" in r.stderr
 
 
-def test_simulation_nni_long_trajectory(tmp_path):
-    """Leaves of the paper simulation n100_l1000_s0: hundreds of neighbourhood passes; every output
-    file must hash to what the reference CLI wrote."""
+def hashed_simulation_case(tmp_path, case_dir, flags, n_files):
     import gzip
     import hashlib
-    d = os.path.join(GOLD, "sim_cli")
+    d = os.path.join(GOLD, case_dir)
     src = tmp_path / "sim.csv"
     with gzip.open(os.path.join(d, "sim_cn_profile.csv.gz"), "rb") as f:
         src.write_bytes(f.read())
-    run(["nni", str(src), "-a", "1", "-i", "2", "-s", "1", "-o", str(tmp_path / "sim")])
+    run(["nni", str(src)] + flags + ["-o", str(tmp_path / "sim")])
     want = {}
     with open(os.path.join(d, "SHA256.txt")) as f:
         for line in f:
             if not line.startswith("#"):
                 h, fn = line.split()
                 want[fn] = h
-    assert len(want) == 5
+    assert len(want) == n_files
     for fn, h in want.items():
         assert hashlib.sha256((tmp_path / fn).read_bytes()).hexdigest() == h, fn
+
+
+def test_simulation_nni_long_trajectory(tmp_path):
+    """Leaves of the paper simulation n100_l1000_s0: hundreds of neighbourhood passes; every output
+    file must hash to what the reference CLI wrote."""
+    hashed_simulation_case(tmp_path, "sim_cli", ["-a", "1", "-i", "2", "-s", "1"], 5)
+
+
+def test_simulation_n600_hash_only(tmp_path):
+    """Leaves of n600_l1000_s0 (1,467 neighbourhood passes, 1.75 M candidates, 170 s
+    of the reference CLI on one core): `nni -a 1 -i 1 -s 1`, every output file by SHA-256."""
+    hashed_simulation_case(tmp_path, "sim600_cli", ["-a", "1", "-i", "1", "-s", "1"], 5)
