@@ -2,6 +2,8 @@
 #include "search.hpp"
 
 #include <algorithm>
+#include <climits>
+#include <cstdlib>
 #include <numeric>
 #include <stdexcept>
 
@@ -170,17 +172,46 @@ void stochastic_nni_draws(const Topology& t, std::ranlux48_base& gen, float aggr
 }
 
 int hill_climb(lzg_ctx* ctx, GpuTree& t, std::ranlux48_base& gen, bool greedy, ClimbStats* stats) {
+    // The shuffle is the host's (the generator is): random_indices over the edges() order of the
+    // current topology, src/copy_number.cxx:381-388.  Everything after it -- greedy_nni over the whole
+    // neighbourhood, accepting the winner, re-scoring its path, the in-place edge-index patch of
+    // :401-406 (an edge index stays with its child end) and the stopping rule -- runs on the device
+    // inside ONE call (lzg_hill_climb).  LAZAC_STEPWISE=1 keeps the older call-per-pass loop.
+    const int n_edges = t.topo.size() - 1;
+    std::vector<int> random_indices((size_t)std::max(0, n_edges));
+    for (int i = 0; i < n_edges; i++) random_indices[i] = i;
+    std::shuffle(random_indices.begin(), random_indices.end(), gen);
+    static const bool stepwise = getenv("LAZAC_STEPWISE") && atoi(getenv("LAZAC_STEPWISE")) != 0;
+    if (stepwise) return hill_climb_stepwise(ctx, t, random_indices, greedy, stats);
+    lzg_climb_result res{};
+    int rc = lzg_hill_climb(ctx, t.h, n_edges, random_indices.data(), greedy ? 1 : 0, INT32_MAX, 0, nullptr, &res);
+    if (rc != LZG_OK) throw_lzg(ctx, rc);
+    if (res.n_moves > 0) {
+        std::vector<int32_t> c0(t.topo.size()), c1(t.topo.size());
+        rc = lzg_tree_get_topology(t.h, c0.data(), c1.data());
+        if (rc != LZG_OK) throw_lzg(ctx, rc);
+        t.topo.c0.assign(c0.begin(), c0.end());
+        t.topo.c1.assign(c1.begin(), c1.end());
+        t.topo.rebuild_parents();
+    }
+    // the reference returns the tree with t[0].score left at the LAST candidate's score of the final,
+    // fruitless pass (greedy_nni does not restore it), and do_nni's acceptance test reads that number
+    t.score = res.returned_score;
+    if (stats) {
+        stats->passes += res.n_passes;
+        stats->candidates += (long)res.candidates;
+        stats->moves += res.n_moves;
+    }
+    return t.score;
+}
+
+int hill_climb_stepwise(lzg_ctx* ctx, GpuTree& t, const std::vector<int>& random_indices, bool greedy, ClimbStats* stats) {
     // edge index == index of the edge's child end in the initial edges() order: an NNI re-hangs
     // w and z but keeps their indices (src/copy_number.cxx:401-406), so the enumeration only needs
     // "child of edge idx" plus the current topology
     const std::vector<std::pair<int, int>> e0 = t.topo.edges();
     std::vector<int> child_of(e0.size());
-    std::vector<int> random_indices(e0.size());
-    for (size_t i = 0; i < e0.size(); i++) {
-        child_of[i] = e0[i].second;
-        random_indices[i] = (int)i;
-    }
-    std::shuffle(random_indices.begin(), random_indices.end(), gen);
+    for (size_t i = 0; i < e0.size(); i++) child_of[i] = e0[i].second;
 
     int current = t.score;
     std::vector<int32_t> moves;

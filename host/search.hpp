@@ -50,6 +50,9 @@ struct ClimbStats {
 // tree reports as t[0].data.score: the score of the last candidate probed by the final, fruitless
 // pass (see lzg_tree_last_candidate_score) -- that is what do_nni's acceptance test compares.
 int hill_climb(lzg_ctx* ctx, GpuTree& t, std::ranlux48_base& gen, bool greedy, ClimbStats* stats);
+// The same climb with one library call per pass and per accepted move (lzg_nni_best + lzg_tree_apply_nni),
+// the host enumerating the neighbourhood in between; kept as the cross-check of the device-side loop.
+int hill_climb_stepwise(lzg_ctx* ctx, GpuTree& t, const std::vector<int>& random_indices, bool greedy, ClimbStats* stats);
 
 [[noreturn]] void throw_lzg(lzg_ctx* ctx, int rc);
 

@@ -151,6 +151,39 @@ int lzg_tree_last_candidate_score(const lzg_tree* t, int32_t* score);
 /* nni(t,u,w,v,z); unvisit(t,0,v); small_rectilinear(t,0) -- src/copy_number.cxx:397,408-409. */
 int lzg_tree_apply_nni(lzg_ctx* ctx, lzg_tree* t, int32_t u, int32_t w, int32_t v, int32_t z,
                        int32_t* root_score);
+/* hill_climb(t, gen, greedy), src/copy_number.cxx:375-417, with the host out of the loop: every
+ * iteration (greedy_nni over the whole neighbourhood, accept the winner, re-score its path) runs on the
+ * device from device-resident state; on one GPU the whole climb is ONE CUDA graph launch (a WHILE
+ * node repeats the iteration until a pass finds no improving candidate).
+ *   edge_order = random_indices of :381-388: a permutation of 0 .. n_edges-1 (n_edges = n_nodes - 1),
+ *   index i = the i-th edge of t.edges() (by parent id, then child id) of the tree's CURRENT topology;
+ *   the shuffle itself (std::shuffle with the caller's generator) is host logic.  An edge index stays
+ *   with its child end while moves are accepted (:401-406), which the library reproduces.
+ *   greedy != 0: a pass accepts the first improving candidate in enumeration order (:358-362).
+ *   max_moves: stop after that many accepted moves (INT32_MAX: until no candidate improves).
+ *   moves (optional): the first moves_cap accepted moves, int32 [moves_cap][5] = (u, w, v, z, score after).
+ * The tree ends with the final topology, intervals and scores; lzg_tree_get_topology returns it. */
+typedef struct lzg_climb_result {
+    int32_t n_moves;         /* accepted moves                                                       */
+    int32_t n_passes;        /* neighbourhood passes (= greedy_nni calls)                            */
+    int32_t reason;          /* 1 no improving candidate, 2 accepted move did not improve (:412),
+                                3 max_moves reached                                                  */
+    int32_t true_score;      /* small-parsimony score of the final tree                              */
+    int32_t returned_score;  /* t[0].data.score as the reference's hill_climb returns it: the score of
+                                the LAST candidate of the final, fruitless pass (see
+                                lzg_tree_last_candidate_score); equals true_score unless reason == 1 */
+    int64_t candidates;      /* candidates scored                                                    */
+} lzg_climb_result;
+int lzg_hill_climb(lzg_ctx* ctx, lzg_tree* t, int32_t n_edges, const int32_t* edge_order, int32_t greedy,
+                   int32_t max_moves, int32_t moves_cap, int32_t* moves, lzg_climb_result* out);
+/* The same climb on a tree whose positions are sharded over the ranks of comm: every rank runs the
+ * iteration on its columns, {root score, candidate scores} is sum-reduced with ncclAllReduce on the
+ * context's stream between the scoring and the arg-min, and every rank takes the same decisions. */
+int lzg_hill_climb_sharded(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, const int32_t* edge_order,
+                           int32_t greedy, int32_t max_moves, int32_t moves_cap, int32_t* moves, lzg_climb_result* out);
+/* Device time stamps (ns, %globaltimer) at the end of every pass of the last climb on this tree:
+ * stamps[k] - stamps[k-1] = one iteration (accept + UP pass + all candidates + arg-min). */
+int lzg_tree_last_climb_stamps(const lzg_tree* t, int32_t cap, uint64_t* stamps, int32_t* n);
 /* start/end: int32 [n_nodes][L]; score: int32 [n_nodes] (any may be NULL). */
 int lzg_tree_get_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end,
                            int32_t* score);

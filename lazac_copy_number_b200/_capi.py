@@ -55,6 +55,9 @@ SYMBOLS = [
     ("lzg_comm_free", _i, [_vp]),
     ("lzg_nni_best_sharded", _i, [_vp, _vp, _vp, _i32, _vp, _i32, _i32p, _i32p, _vp]),
     ("lzg_tree_apply_nni", _i, [_vp, _vp, _i32, _i32, _i32, _i32, _i32p]),
+    ("lzg_hill_climb", _i, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp]),
+    ("lzg_hill_climb_sharded", _i, [_vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp]),
+    ("lzg_tree_last_climb_stamps", _i, [_vp, _i32, _vp, _i32p]),
     ("lzg_tree_get_intervals", _i, [_vp, _vp, _vp, _vp, _vp]),
     ("lzg_tree_get_node_intervals", _i, [_vp, _vp, _i32, _vp, _vp, _vp]),
     ("lzg_tree_ancestral", _i, [_vp, _vp, _vp, _vp]),
@@ -63,6 +66,12 @@ SYMBOLS = [
     ("lzg_tree_last_nni_traffic", _i, [_vp, _i64p, _i64p]),
     ("lzg_nj_seed_tree", _i, [_vp, _vp, _i32, _vp, _vp, _vp]),
 ]
+
+
+class ClimbResult(C.Structure):
+    """lzg_climb_result (include/lazac_b200.h)."""
+    _fields_ = [("n_moves", C.c_int32), ("n_passes", C.c_int32), ("reason", C.c_int32), ("true_score", C.c_int32),
+                ("returned_score", C.c_int32), ("candidates", C.c_int64)]
 
 
 class LazacGpuError(RuntimeError):

@@ -249,6 +249,34 @@ class Tree:
         self.ctx.check(self.ctx.lib.lzg_tree_apply_nni(self.ctx.h, self.h, u, w, v, z, C.byref(s)))
         return s.value
 
+    def hill_climb(self, edge_order, greedy=False, max_moves=2 ** 31 - 1, want_moves=True, comm=None):
+        """hill_climb(t, gen, greedy), src/copy_number.cxx:375-417, with the shuffle done by the caller:
+        edge_order = random_indices (a permutation of the indices of edges() of the CURRENT topology).
+        The whole climb runs on the device (lzg_hill_climb).  Returns a dict: moves [k][5] =
+        (u, w, v, z, score after), n_moves, n_passes, reason, true_score, returned_score, candidates."""
+        order = i32(edge_order)
+        res = _capi.ClimbResult()
+        cap = min(int(max_moves), 1 << 20) if want_moves else 0
+        moves = np.zeros((cap, 5), np.int32) if cap else None
+        if comm is None:
+            rc = self.ctx.lib.lzg_hill_climb(self.ctx.h, self.h, len(order), ptr(order), int(greedy), int(max_moves), cap, ptr(moves), C.byref(res))
+        else:
+            rc = self.ctx.lib.lzg_hill_climb_sharded(self.ctx.h, comm, self.h, len(order), ptr(order), int(greedy), int(max_moves), cap, ptr(moves),
+                                                     C.byref(res))
+        self.ctx.check(rc)
+        out = {k: getattr(res, k) for k, _ in _capi.ClimbResult._fields_}
+        out["moves"] = moves[:min(cap, res.n_moves)] if cap else None
+        return out
+
+    def climb_stamps(self):
+        """Device time stamps (ns) at the end of every pass of the last hill_climb on this tree."""
+        n = C.c_int32(0)
+        self.ctx.check(self.ctx.lib.lzg_tree_last_climb_stamps(self.h, 0, None, C.byref(n)))
+        st = np.zeros(n.value, np.uint64)
+        if n.value:
+            self.ctx.check(self.ctx.lib.lzg_tree_last_climb_stamps(self.h, n.value, ptr(st), C.byref(n)))
+        return st
+
     def intervals(self):
         S = np.zeros((self.n, self.L), np.int32)
         E = np.zeros((self.n, self.L), np.int32)

@@ -58,6 +58,18 @@ struct lzg_comm {
     int rank = 0, world = 1;
 };
 
+int lzg_comm_world(const lzg_comm* c) { return c ? c->world : 1; }
+
+int lzg_comm_allreduce_sum(lzg_ctx* ctx, lzg_comm* c, int32_t* d_vec, size_t n) {
+    if (!c || !c->comm) return LZG_OK;
+    const int nrc = nccl_api()->all_reduce(d_vec, d_vec, n, LZG_NCCL_INT32, LZG_NCCL_SUM, c->comm, ctx->stream);
+    if (nrc != 0) {
+        cudaStreamSynchronize(ctx->stream);
+        return lzg_fail(ctx, LZG_ERR_STATE, nccl_api()->get_error_string ? nccl_api()->get_error_string(nrc) : "ncclAllReduce failed");
+    }
+    return LZG_OK;
+}
+
 extern "C" {
 
 int lzg_comm_init(lzg_ctx* ctx, int32_t rank, int32_t world, const void* unique_id, lzg_comm** out) {
@@ -115,6 +127,15 @@ int lzg_nni_best_sharded(lzg_ctx* ctx, lzg_comm* c, lzg_tree* t, int32_t n_moves
         }
     }
     return lzg_tree_nni_finish(ctx, t, greedy, best_index, best_score, all_scores);
+}
+
+int lzg_hill_climb_sharded(lzg_ctx* ctx, lzg_comm* c, lzg_tree* t, int32_t n_edges, const int32_t* edge_order, int32_t greedy,
+                           int32_t max_moves, int32_t moves_cap, int32_t* moves, lzg_climb_result* out) {
+    if (!ctx || !c || c->ctx != ctx || !t || t->ctx != ctx || n_edges < 0 || (n_edges > 0 && !edge_order) || moves_cap < 0 || (moves_cap > 0 && !moves))
+        return lzg_fail(ctx, LZG_ERR_ARG, "lzg_hill_climb_sharded: bad argument");
+    if (!t->scored) return lzg_fail(ctx, LZG_ERR_STATE, "tree must be scored (lzg_tree_score) before lzg_hill_climb_sharded");
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    return lzg_tree_climb(ctx, c, t, n_edges, edge_order, greedy, max_moves, moves_cap, moves, out);
 }
 
 }  // extern "C"

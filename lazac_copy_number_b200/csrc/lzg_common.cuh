@@ -42,6 +42,14 @@ struct lzg_ctx {
     cudaEvent_t ev_items = nullptr;  // the last k_nni_items launch (reader of the item records) / the item copy on copy_stream
     cudaEvent_t ev_stage = nullptr;  // the last asynchronous copy OUT of the pinned staging area that no synchronising call has waited for
     std::vector<lzg_schedule> schedules;  // distance schedules by (shape, tile, shard); freed at shutdown
+    struct climb_graph {                  // one WHILE graph per launch geometry of the climb (lzg_tree.cu)
+        int n_items = 0, gi = 0, groups = 0, threads = 0, up_grid = 0, n_cand = 0;
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        cudaGraphConditionalHandle handle = 0;
+    };
+    std::vector<climb_graph> climb_graphs;
+    int climb_graph_broken = 0;           // conditional nodes refused by this driver: batches of queued iterations instead
 };
 
 // Stream-ordered device allocation from the device's default memory pool, whose release threshold

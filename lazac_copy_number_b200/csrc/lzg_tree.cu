@@ -325,6 +325,39 @@ static int ensure_cand_buffers(lzg_ctx* ctx, lzg_tree* t, int n_moves) {
     return LZG_OK;
 }
 
+// UP intervals + the epoch flags of the table-driven UP pass, allocated on first use
+static int ensure_up_buffers(lzg_ctx* ctx, lzg_tree* t, int groups) {
+    if (t->d_ustart) return LZG_OK;
+    const int n = t->n_nodes;
+    const size_t nb = (size_t)n * t->l_pad;
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ustart, nb));
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_uend, nb));
+    const size_t n_flags = (size_t)n * groups;  // per (node, chunk group)
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ready, sizeof(int) * n_flags));
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_ready, 0, sizeof(int) * n_flags, ctx->stream));
+    t->epoch = 0;
+    t->up_valid = false;
+    return LZG_OK;
+}
+
+// The host mirror's share of an accepted move (topology, parents, the packed node records).
+static void host_apply_move(lzg_tree* t, int u, int w, int v, int z) {
+    const int y = t->child0[v] == z ? t->child1[v] : t->child0[v];
+    t->child0[v] = std::min(w, y);
+    t->child1[v] = std::max(w, y);
+    t->child0[u] = std::min(v, z);
+    t->child1[u] = std::max(v, z);
+    t->parent[w] = v;
+    t->parent[z] = u;
+    if (t->node4_valid) {  // u's subtree keeps its node set: the count changes for v only, the heavy / light roles for v and u
+        int4* nd = t->node4.data();
+        nd[w].w = v;
+        nd[z].w = u;
+        nd[v] = make_node4(nd, t->child0[v], t->child1[v], u);
+        nd[u] = make_node4(nd, t->child0[u], t->child1[u], nd[u].w);
+    }
+}
+
 static bool is_move(const lzg_tree* t, int u, int w, int v, int z) {
     const int n = t->n_nodes;
     if (u < 0 || u >= n || v < 0 || v >= n || w < 0 || w >= n || z < 0 || z >= n) return false;
@@ -410,16 +443,8 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     int groups, threads = chunk_threads(t->l_pad, &groups);
     int rc = ensure_cand_buffers(ctx, t, n_moves);
     if (rc != LZG_OK) return rc;
-    if (!t->d_ustart) {
-        const size_t nb = (size_t)n * t->l_pad;
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ustart, nb));
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_uend, nb));
-        const size_t n_flags = (size_t)n * groups;  // per (node, chunk group)
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_ready, sizeof(int) * n_flags));
-        LZG_CUDA(ctx, cudaMemsetAsync(t->d_ready, 0, sizeof(int) * n_flags, ctx->stream));
-        t->epoch = 0;
-        t->up_valid = false;
-    }
+    rc = ensure_up_buffers(ctx, t, groups);
+    if (rc != LZG_OK) return rc;
     // staging (pinned; every public entry point ends with a synchronising read-back, so the area is
     // free again when the next call fills it): [result (16) | path records + order (6 n + 8) | items]
     rc = lzg_ensure_pinned(ctx, 16 + (size_t)6 * n + 12 + 8 * (size_t)n_moves);
@@ -582,7 +607,7 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     const auto t_launch = std::chrono::steady_clock::now();
     {
         const int gi = (t->l_pad + 256 * 16 - 1) / (256 * 16);
-        k_nni_items<16><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
+        k_nni_items<16, false><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
     }
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaEventRecord(ctx->ev_items, ctx->stream));
@@ -632,7 +657,7 @@ int lzg_tree_nni_finish(lzg_ctx* ctx, lzg_tree* t, int greedy, int32_t* best_ind
     A.greedy = greedy;
     A.ctl = t->d_cand;
     A.cand_score = t->d_cand + LZG_CTL_INTS;
-    k_nni_argmin<<<1, 1024, 0, ctx->stream>>>(A);
+    k_nni_argmin<false><<<1, 1024, 0, ctx->stream>>>(A);
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_cand, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     if (all_scores)
@@ -671,21 +696,9 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
         P.other[k] = t->child0[pb] == b ? t->child1[pb] : t->child0[pb];
         b = pb;
     }
-    // host mirror
-    t->child0[v] = std::min(w, y);
-    t->child1[v] = std::max(w, y);
-    t->child0[u] = std::min(v, z);
-    t->child1[u] = std::max(v, z);
-    t->parent[w] = v;
-    t->parent[z] = u;
+    host_apply_move(t, u, w, v, z);
     t->up_valid = false;
-    if (t->node4_valid) {  // u's subtree keeps its node set: the count changes for v only, the heavy / light roles for v and u
-        int4* nd = t->node4.data();
-        nd[w].w = v;
-        nd[z].w = u;
-        nd[v] = make_node4(nd, t->child0[v], t->child1[v], u);
-        nd[u] = make_node4(nd, t->child0[u], t->child1[u], nd[u].w);
-    }
+    t->d_node4_valid = false;  // k_apply_move does not maintain the device twin
     const bool timeline = getenv("LZG_PASS_DEBUG") && (atoi(getenv("LZG_PASS_DEBUG")) & 16);
     if (timeline) {
         for (auto& e : g_apply_tl)
@@ -811,4 +824,349 @@ int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* br
     lzg_dev_free(ctx, d_label);
     lzg_dev_free(ctx, d_branch);
     return rc;
+}
+
+// ---- hill_climb on the device (kernels: lzg_tree_climb.cuh) ----------------------------------------------
+// Host side of lzg_hill_climb: lays the static work items out once per climb, uploads them with the
+// candidate numbering of the caller's shuffled edge order, launches the climb (one WHILE graph, or
+// batches of queued iterations where a collective sits inside the iteration), reads back one move
+// log and replays it on the host mirror.
+namespace {
+
+constexpr int LZG_CLIMB_LOG = 4096;  // accepted moves logged on the device before the host drains the log
+
+struct climb_layout {  // offsets (bytes) into t->d_climb
+    size_t items, slot_of, cbase, pair_v, upload_bytes, pcost, tail, mlog, queue, tlog, total;
+};
+
+climb_layout climb_offsets(int n_nodes, int n_items, int groups) {
+    climb_layout o;
+    auto up16 = [](size_t x) { return (x + 15) / 16 * 16; };
+    size_t p = 0;
+    o.items = p, p = up16(p + sizeof(int4) * 2 * (size_t)std::max(1, n_items));
+    o.slot_of = p, p = up16(p + sizeof(int32_t) * (size_t)n_nodes);
+    o.cbase = p, p = up16(p + sizeof(int32_t) * (size_t)n_nodes);
+    o.pair_v = p, p = up16(p + sizeof(int32_t) * (size_t)std::max(1, n_items));
+    o.upload_bytes = p;  // everything above is rewritten by the host at the start of a climb
+    o.pcost = p, p = up16(p + sizeof(int32_t) * (size_t)n_nodes);
+    o.tail = p, p = up16(p + sizeof(int32_t) * (size_t)std::max(4, groups));
+    o.mlog = p, p = up16(p + sizeof(int32_t) * 5 * (size_t)LZG_CLIMB_LOG);
+    o.queue = p, p = up16(p + sizeof(unsigned long long) * (size_t)groups * ((size_t)n_items + 1));
+    o.tlog = p, p = up16(p + sizeof(unsigned long long) * ((size_t)LZG_CLIMB_LOG + 2));
+    o.total = p;
+    return o;
+}
+
+int ensure_climb_buffers(lzg_ctx* ctx, lzg_tree* t, int n_items, int groups) {
+    const climb_layout o = climb_offsets(t->n_nodes, n_items, groups);
+    if (t->d_climb && t->climb_items == n_items && t->climb_bytes == o.total) return LZG_OK;
+    lzg_dev_free(ctx, t->d_climb);
+    t->d_climb = nullptr;
+    LZG_CUDA(ctx, lzg_dev_alloc(ctx, &t->d_climb, o.total));
+    // cost cells, queue tails and queue entries start at zero (epochs start at 1); the upload area is written per climb
+    LZG_CUDA(ctx, cudaMemsetAsync((uint8_t*)t->d_climb + o.pcost, 0, o.total - o.pcost, ctx->stream));
+    t->climb_bytes = o.total;
+    t->climb_items = n_items;
+    t->df_epoch = 1;
+    if (!t->d_node4) {
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&t->d_node4, sizeof(int4) * (size_t)t->n_nodes));
+        t->d_node4_valid = false;
+    }
+    return LZG_OK;
+}
+
+struct climb_geometry {
+    int n_items, n_cand, gi, groups, threads, up_grid;
+};
+
+void* climb_kernel(int which) {
+    switch (which) {
+        case 0: return (void*)k_up_df<true>;
+        case 1: return (void*)k_nni_items<16, true>;
+        case 2: return (void*)k_nni_argmin<true>;
+        default: return (void*)k_apply2<true>;
+    }
+}
+
+// One iteration = {apply, up, items, argmin}; pass 0 has no move to apply.  Plain stream launches.
+int climb_enqueue_pass(lzg_ctx* ctx, const climb_geometry& G, bool with_apply, lzg_comm* comm, lzg_tree* t) {
+    const lzg_pass_args dummy{};
+    if (with_apply) {
+        k_apply2<true><<<G.groups, G.threads, 0, ctx->stream>>>(dummy, lzg_move{0, 0, 0, 0});
+        LZG_LAUNCH_CHECK(ctx);
+    }
+    k_up_df<true><<<G.up_grid, G.threads, 0, ctx->stream>>>(dummy);
+    LZG_LAUNCH_CHECK(ctx);
+    k_nni_items<16, true><<<G.n_items * G.gi, 256, 0, ctx->stream>>>(dummy, G.gi);
+    LZG_LAUNCH_CHECK(ctx);
+    if (comm && lzg_comm_world(comm) > 1) {
+        const int rc = lzg_comm_allreduce_sum(ctx, comm, t->d_cand + LZG_CTL_ROOT, (size_t)G.n_cand + 1);
+        if (rc != LZG_OK) return rc;
+    }
+    k_nni_argmin<true><<<1, 1024, 0, ctx->stream>>>(dummy);
+    LZG_LAUNCH_CHECK(ctx);
+    return LZG_OK;
+}
+
+// The climb as one graph: pass 0, then a WHILE node whose body is one iteration; the arg-min kernel sets
+// the loop condition.  Kernel arguments are dummies -- the kernels read c_pass -- so one graph serves
+// every tree of this launch geometry.
+lzg_ctx::climb_graph* climb_graph_for(lzg_ctx* ctx, const climb_geometry& G) {
+    for (auto& g : ctx->climb_graphs)
+        if (g.n_items == G.n_items && g.gi == G.gi && g.groups == G.groups && g.threads == G.threads && g.up_grid == G.up_grid && g.n_cand == G.n_cand) return &g;
+    if (ctx->climb_graph_broken) return nullptr;
+    lzg_ctx::climb_graph cg;
+    cg.n_items = G.n_items, cg.gi = G.gi, cg.groups = G.groups, cg.threads = G.threads, cg.up_grid = G.up_grid, cg.n_cand = G.n_cand;
+    static lzg_pass_args dummy{};
+    static lzg_move no_move{0, 0, 0, 0};
+    static int gi_arg;
+    gi_arg = G.gi;
+    auto add_kernel = [&](cudaGraph_t graph, cudaGraphNode_t* dep, int which, cudaGraphNode_t* out) -> cudaError_t {
+        cudaKernelNodeParams kp{};
+        void* args_up[] = {(void*)&dummy};
+        void* args_items[] = {(void*)&dummy, (void*)&gi_arg};
+        void* args_apply[] = {(void*)&dummy, (void*)&no_move};
+        kp.func = climb_kernel(which);
+        kp.sharedMemBytes = 0;
+        kp.extra = nullptr;
+        switch (which) {
+            case 0: kp.gridDim = dim3(G.up_grid), kp.blockDim = dim3(G.threads), kp.kernelParams = args_up; break;
+            case 1: kp.gridDim = dim3(G.n_items * G.gi), kp.blockDim = dim3(256), kp.kernelParams = args_items; break;
+            case 2: kp.gridDim = dim3(1), kp.blockDim = dim3(1024), kp.kernelParams = args_up; break;
+            default: kp.gridDim = dim3(G.groups), kp.blockDim = dim3(G.threads), kp.kernelParams = args_apply; break;
+        }
+        return cudaGraphAddKernelNode(out, graph, dep, dep ? 1 : 0, &kp);
+    };
+    cudaError_t e = cudaGraphCreate(&cg.graph, 0);
+    cudaGraphNode_t n0 = nullptr, n1 = nullptr, n2 = nullptr, nw = nullptr;
+    if (e == cudaSuccess) e = cudaGraphConditionalHandleCreate(&cg.handle, cg.graph, 1, cudaGraphCondAssignDefault);
+    if (e == cudaSuccess) e = add_kernel(cg.graph, nullptr, 0, &n0);
+    if (e == cudaSuccess) e = add_kernel(cg.graph, &n0, 1, &n1);
+    if (e == cudaSuccess) e = add_kernel(cg.graph, &n1, 2, &n2);
+    if (e == cudaSuccess) {
+        cudaGraphNodeParams cp{};
+        cp.type = cudaGraphNodeTypeConditional;
+        cp.conditional.handle = cg.handle;
+        cp.conditional.type = cudaGraphCondTypeWhile;
+        cp.conditional.size = 1;
+        e = cudaGraphAddNode(&nw, cg.graph, &n2, 1, &cp);
+        if (e == cudaSuccess) {
+            cudaGraph_t body = cp.conditional.phGraph_out[0];
+            cudaGraphNode_t b0 = nullptr, b1 = nullptr, b2 = nullptr, b3 = nullptr;
+            e = add_kernel(body, nullptr, 3, &b0);
+            if (e == cudaSuccess) e = add_kernel(body, &b0, 0, &b1);
+            if (e == cudaSuccess) e = add_kernel(body, &b1, 1, &b2);
+            if (e == cudaSuccess) e = add_kernel(body, &b2, 2, &b3);
+        }
+    }
+    if (e == cudaSuccess) e = cudaGraphInstantiate(&cg.exec, cg.graph, 0);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        if (cg.graph) cudaGraphDestroy(cg.graph);
+        ctx->climb_graph_broken = 1;
+        if (getenv("LZG_CLIMB_DEBUG")) fprintf(stderr, "[lzg climb] WHILE graph unavailable (%s): queued batches instead\n", cudaGetErrorString(e));
+        return nullptr;
+    }
+    ctx->climb_graphs.push_back(cg);
+    return &ctx->climb_graphs.back();
+}
+
+}  // namespace
+
+int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, const int32_t* edge_order, int32_t greedy, int32_t max_moves,
+                   int32_t moves_cap, int32_t* moves, lzg_climb_result* out) {
+    const int n = t->n_nodes;
+    const bool sharded = comm && lzg_comm_world(comm) > 1;
+    lzg_climb_result R{};
+    R.true_score = R.returned_score = t->root_score;
+    R.reason = 1;
+    t->climb_stamps.clear();
+    if (n_edges != n - 1) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_hill_climb: n_edges must be n_nodes - 1");
+    // child end of every edge index (t.edges(): by parent id, then child id) and the candidate numbering
+    std::vector<int32_t>& child_of = t->tmp_pre;
+    child_of.clear();
+    for (int u = 0; u < n; u++)
+        if (t->child0[u] >= 0) child_of.push_back(t->child0[u]), child_of.push_back(t->child1[u]);
+    if ((int)child_of.size() != n_edges) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_hill_climb: topology mirror is inconsistent");
+    std::vector<int32_t> cbase(n, -1), pair_v;
+    {
+        std::vector<char> seen(n_edges, 0);
+        for (int q = 0; q < n_edges; q++) {
+            const int e = edge_order[q];
+            if (e < 0 || e >= n_edges || seen[e]) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_hill_climb: edge_order is not a permutation");
+            seen[e] = 1;
+            const int v = child_of[e];
+            if (t->child0[v] < 0) continue;  // greedy_nni skips edges into leaves (:334)
+            cbase[v] = 2 * (int)pair_v.size();
+            pair_v.push_back(v);
+        }
+    }
+    const int n_items = (int)pair_v.size(), n_cand = 2 * n_items;
+    R.n_passes = 0;
+    if (n_items == 0 || max_moves <= 0) {  // nothing to enumerate: greedy_nni returns no move, the tree is untouched
+        R.n_passes = n_items == 0 ? 1 : 0;
+        R.reason = n_items == 0 ? 1 : 3;
+        if (out) *out = R;
+        return LZG_OK;
+    }
+    int groups, threads = chunk_threads(t->l_pad, &groups);
+    int rc = ensure_cand_buffers(ctx, t, n_cand);
+    if (rc == LZG_OK) rc = ensure_up_buffers(ctx, t, groups);
+    if (rc == LZG_OK) rc = ensure_climb_buffers(ctx, t, n_items, groups);
+    if (rc != LZG_OK) return rc;
+    const climb_layout o = climb_offsets(n, n_items, groups);
+    // ---- layout: item slots in the walker order of the starting topology (neighbours share rows in L2) ----
+    rc = lzg_ensure_pinned(ctx, 16 + (size_t)6 * n + 12 + o.upload_bytes / 4 + 64 + 5 * (size_t)LZG_CLIMB_LOG);
+    if (rc != LZG_OK) return rc;
+    LZG_CUDA(ctx, cudaEventSynchronize(ctx->ev_stage));
+    int32_t* scratch = ctx->h_pinned + 16;                                   // path tables of build_up_paths (not uploaded here)
+    uint8_t* blob = reinterpret_cast<uint8_t*>(ctx->h_pinned + 16 + (size_t)6 * n + 12 + 4);
+    blob = reinterpret_cast<uint8_t*>(((uintptr_t)blob + 15) / 16 * 16);
+    int n_order = 0;
+    const int n_paths = build_up_paths(t, reinterpret_cast<int2*>(scratch + 4 * (size_t)n), reinterpret_cast<int4*>(scratch), &n_order);
+    if (n_order != n_items) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_hill_climb: internal node count mismatch");
+    {
+        const int4* nd = t->node4.data();
+        int32_t* slot_of = reinterpret_cast<int32_t*>(blob + o.slot_of);
+        int32_t* h_cbase = reinterpret_cast<int32_t*>(blob + o.cbase);
+        int32_t* h_pair = reinterpret_cast<int32_t*>(blob + o.pair_v);
+        int4* items = reinterpret_cast<int4*>(blob + o.items);
+        memcpy(h_cbase, cbase.data(), sizeof(int32_t) * n);
+        memcpy(h_pair, pair_v.data(), sizeof(int32_t) * n_items);
+        for (int x = 0; x < n; x++) slot_of[x] = -1;
+        for (int k = 0; k < n_items; k++) {
+            const int v = pair_v[k], u = nd[v].w;
+            const int4 nu = nd[u];
+            const int slot = t->item_start[u] + (nu.x == v ? 0 : (nu.z & 1));
+            if (slot < 0 || slot >= n_items) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_hill_climb: item slot out of range");
+            slot_of[v] = slot;
+            const int w = nu.x == v ? nu.y : nu.x;
+            items[2 * slot] = make_int4(u, w, v, t->child0[v]);
+            items[2 * slot + 1] = make_int4(t->child1[v], cbase[v], cbase[v] + 1, 0);
+        }
+    }
+    uint8_t* dc = (uint8_t*)t->d_climb;
+    LZG_CUDA(ctx, cudaMemcpyAsync(dc, blob, o.upload_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (!t->d_node4_valid) {
+        LZG_CUDA(ctx, cudaMemcpyAsync(t->d_node4, t->node4.data(), sizeof(int4) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+        t->d_node4_valid = true;
+    }
+    // ---- the descriptor (constant memory) and the control block ----
+    climb_geometry G;
+    G.n_items = n_items, G.n_cand = n_cand, G.groups = groups, G.threads = threads;
+    G.gi = (t->l_pad + 256 * 16 - 1) / (256 * 16);
+    G.up_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * std::max(1, 1024 / threads)));  // persistent; a function of the data set only (graph cache)
+    const bool want_graph = !sharded && !(getenv("LZG_CLIMB_GRAPH") && atoi(getenv("LZG_CLIMB_GRAPH")) == 0);
+    lzg_ctx::climb_graph* cg = want_graph ? climb_graph_for(ctx, G) : nullptr;
+    lzg_pass_args A{};
+    A.n_items = n_items, A.n_cand = n_cand, A.groups = groups, A.l_pad = t->l_pad, A.greedy = greedy;
+    A.start = t->d_start, A.end = t->d_end, A.wstart = t->d_start, A.wend = t->d_end;
+    A.ustart = t->d_ustart, A.uend = t->d_uend;
+    A.score = t->d_score, A.wscore = t->d_score;
+    A.ctl = t->d_cand, A.cand_score = t->d_cand + LZG_CTL_INTS;
+    A.node4 = t->d_node4, A.child0 = t->d_child0, A.child1 = t->d_child1, A.up = t->d_up;
+    A.items = reinterpret_cast<const int4*>(dc + o.items), A.witems = reinterpret_cast<int4*>(dc + o.items);
+    A.slot_of = reinterpret_cast<const int32_t*>(dc + o.slot_of);
+    A.cbase = reinterpret_cast<const int32_t*>(dc + o.cbase);
+    A.pair_v = reinterpret_cast<const int32_t*>(dc + o.pair_v);
+    A.pcost = reinterpret_cast<int32_t*>(dc + o.pcost);
+    A.tail = reinterpret_cast<int*>(dc + o.tail);
+    A.mlog = reinterpret_cast<int32_t*>(dc + o.mlog);
+    A.queue = reinterpret_cast<unsigned long long*>(dc + o.queue);
+    A.tlog = reinterpret_cast<unsigned long long*>(dc + o.tlog);
+    A.qcap = n_items + 1, A.sharded = sharded ? 1 : 0;
+    A.log_cap = getenv("LZG_CLIMB_LOGCAP") ? std::max(1, std::min(LZG_CLIMB_LOG, atoi(getenv("LZG_CLIMB_LOGCAP")))) : LZG_CLIMB_LOG;  // tests shrink it to exercise the drain-and-continue path
+    A.use_cond = cg ? 1 : 0, A.cond_handle = cg ? (unsigned long long)cg->handle : 0ull;
+    LZG_CUDA(ctx, cudaMemcpyToSymbolAsync(c_pass, &A, sizeof(A), 0, cudaMemcpyHostToDevice, ctx->stream));
+    int32_t* h_ctl = ctx->h_pinned;  // 16 ints: the control block goes up and comes back through the head of the staging area
+    for (int q = 0; q < LZG_CTL_INTS; q++) h_ctl[q] = 0;
+    h_ctl[LZG_CTL_BEST] = -1;
+    h_ctl[LZG_CTL_NPATHS] = n_paths;
+    h_ctl[LZG_CTL_MAXMOVES] = max_moves;
+    h_ctl[LZG_CTL_EPOCH] = t->df_epoch;
+    h_ctl[LZG_CTL_CURRENT] = h_ctl[LZG_CTL_PARTROOT] = t->root_score;
+    LZG_CUDA(ctx, cudaMemcpyAsync(t->d_cand, h_ctl, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand + LZG_CTL_INTS, 0, sizeof(int32_t) * (size_t)n_cand, ctx->stream));
+    LZG_CUDA(ctx, cudaEventRecord(ctx->ev_stage, ctx->stream));
+    // ---- run ----
+    int32_t* h_log = reinterpret_cast<int32_t*>(blob + ((o.upload_bytes + 63) / 64 * 64));  // behind the upload area (read by the H2D above only)
+    const bool debug = getenv("LZG_CLIMB_DEBUG") != nullptr;
+    int total_moves = 0, stop = 0, passes = 0;
+    long long replayed = 0;
+    bool first = true;
+    t->up_valid = false;
+    while (true) {
+        if (cg) {
+            LZG_CUDA(ctx, cudaGraphLaunch(cg->exec, ctx->stream));
+            ctx->launches += 3;  // pass 0; the iterations of the WHILE body are counted from the pass counter below
+        } else {
+            rc = climb_enqueue_pass(ctx, G, false, comm, t);
+            int batch = 2;
+            while (rc == LZG_OK) {
+                for (int q = 0; q < batch && rc == LZG_OK; q++) rc = climb_enqueue_pass(ctx, G, true, comm, t);
+                if (rc != LZG_OK) break;
+                LZG_CUDA(ctx, cudaMemcpyAsync(h_ctl, t->d_cand, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
+                LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                if (h_ctl[LZG_CTL_STOP]) break;
+                batch = std::min(2 * batch, 64);
+            }
+            if (rc != LZG_OK) {
+                cudaStreamSynchronize(ctx->stream);
+                return rc;
+            }
+        }
+        LZG_CUDA(ctx, cudaMemcpyAsync(h_ctl, t->d_cand, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
+        LZG_CUDA(ctx, cudaMemcpyAsync(h_log, A.mlog, sizeof(int32_t) * 5 * (size_t)LZG_CLIMB_LOG, cudaMemcpyDeviceToHost, ctx->stream));
+        LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        stop = h_ctl[LZG_CTL_STOP];
+        const int logged = h_ctl[LZG_CTL_NLOGGED];
+        if (cg) ctx->launches += 4 * (int64_t)(h_ctl[LZG_CTL_PASSES] - passes - (first ? 1 : 0));
+        passes = h_ctl[LZG_CTL_PASSES];
+        total_moves = h_ctl[LZG_CTL_NMOVES];
+        if (debug) fprintf(stderr, "[lzg climb] %s: stop %d, moves %d (logged %d), passes %d, current %d, paths %d\n", cg ? "graph" : "batches", stop, total_moves, logged, passes, h_ctl[LZG_CTL_CURRENT], h_ctl[LZG_CTL_NPATHS]);
+        for (int k = 0; k < logged; k++) {
+            const int32_t* r = h_log + 5 * (size_t)k;
+            if (!is_move(t, r[0], r[1], r[2], r[3])) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_hill_climb: the device logged a move the host mirror cannot apply");
+            host_apply_move(t, r[0], r[1], r[2], r[3]);
+            if (moves && replayed < moves_cap) memcpy(moves + 5 * replayed, r, sizeof(int32_t) * 5);
+            replayed++;
+        }
+        first = false;
+        if (stop == 3 && total_moves < max_moves) {  // only the log was full: drain it and go on
+            LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand + LZG_CTL_STOP, 0, sizeof(int32_t), ctx->stream));
+            LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand + LZG_CTL_NLOGGED, 0, sizeof(int32_t), ctx->stream));
+            continue;
+        }
+        break;
+    }
+    t->df_epoch = h_ctl[LZG_CTL_EPOCH];
+    if (stop == 4 || stop == 0) return lzg_fail(ctx, LZG_ERR_STATE, stop == 4 ? "lzg_hill_climb: the UP pass waited for a path that was never queued" : "lzg_hill_climb: the climb did not terminate");
+    if (replayed != total_moves) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_hill_climb: move log incomplete");
+    {   // the path count the device maintained incrementally must match the final topology
+        int heads = 0;
+        const int4* nd = t->node4.data();
+        for (int p = 0; p < n; p++)
+            if (nd[p].x >= 0) heads += p == 0 ? (nd[p].z & 1) + ((nd[p].z >> 1) & 1) : ((nd[p].z & 3) == 3);
+        if (heads != h_ctl[LZG_CTL_NPATHS]) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_hill_climb: path count diverged from the topology");
+    }
+    // time stamps of the passes
+    {
+        const int n_st = std::min(passes, A.log_cap + 1);
+        t->climb_stamps.resize(n_st);
+        if (n_st > 0) {
+            LZG_CUDA(ctx, cudaMemcpyAsync(t->climb_stamps.data(), A.tlog, sizeof(uint64_t) * n_st, cudaMemcpyDeviceToHost, ctx->stream));
+            LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+    }
+    if (total_moves > 0) t->root_score = h_ctl[LZG_CTL_PARTROOT];
+    t->last_cand_score = h_ctl[LZG_CTL_LAST];
+    t->up_valid = false;  // the UP rows are current only if the climb ended on a fruitless pass; the table-driven pass keeps its own books
+    R.n_moves = total_moves;
+    R.n_passes = passes;
+    R.reason = stop;
+    R.true_score = h_ctl[LZG_CTL_CURRENT];
+    R.returned_score = stop == 1 ? h_ctl[LZG_CTL_LAST] : h_ctl[LZG_CTL_CURRENT];
+    R.candidates = (int64_t)passes * n_cand;
+    if (out) *out = R;
+    return LZG_OK;
 }

@@ -44,7 +44,23 @@ struct lzg_tree {
     bool pass_pending = false;        // lzg_tree_nni_launch queued a pass whose scores lzg_tree_nni_finish has not reduced yet
     bool node4_valid = false;         // cleared by lzg_tree_set_topology; kept current by lzg_tree_apply
     std::vector<int32_t> tmp_pre, tmp_heads, tmp_items, tmp_count;  // per-pass host scratch, kept to avoid reallocation
+    // ---- device-driven climb (lzg_tree_climb.cuh) ----
+    int4* d_node4 = nullptr;          // device twin of node4, kept current by k_apply2
+    bool d_node4_valid = false;
+    void* d_climb = nullptr;          // one block: [items | slot_of | cbase | pair_v | pcost | tail | mlog | queue | tlog]
+    size_t climb_bytes = 0;
+    int32_t climb_items = 0;          // internal non-root nodes the block was sized for
+    int32_t df_epoch = 1;             // epoch of the dataflow UP pass's queue entries (monotonic per tree)
+    std::vector<uint64_t> climb_stamps;  // %globaltimer at the end of every pass of the last climb
 };
+
+struct lzg_comm;
+struct lzg_climb_result;
+int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, const int32_t* edge_order, int32_t greedy, int32_t max_moves,
+                   int32_t moves_cap, int32_t* moves, lzg_climb_result* out);
+// the all-reduce of the position-sharded pass (lzg_comm.cu): sums vec[0 .. n) over the ranks on ctx->stream; 0 = ok
+int lzg_comm_allreduce_sum(lzg_ctx* ctx, lzg_comm* comm, int32_t* d_vec, size_t n);
+int lzg_comm_world(const lzg_comm* comm);
 
 int lzg_tree_upload_topology(lzg_ctx* ctx, lzg_tree* t);
 int lzg_tree_gather_leaves(lzg_ctx* ctx, lzg_tree* t, const lzg_profiles* p, const int32_t* leaf_row);

@@ -21,6 +21,8 @@ static void tree_release(lzg_tree* t) {
     lzg_dev_free(t->ctx, t->d_ustart);
     lzg_dev_free(t->ctx, t->d_uend);
     lzg_dev_free(t->ctx, t->d_ready);
+    lzg_dev_free(t->ctx, t->d_node4);
+    lzg_dev_free(t->ctx, t->d_climb);
     delete t;
 }
 
@@ -132,6 +134,10 @@ int lzg_tree_clone(lzg_ctx* ctx, const lzg_tree* s, lzg_tree** out) {
     t->parent = s->parent;
     t->scored = s->scored;
     t->root_score = s->root_score;
+    if (s->node4_valid) {  // the packed node records of the topology: a clone is usually climbed right away
+        t->node4 = s->node4;
+        t->node4_valid = true;
+    }
     const int n = s->n_nodes;
     const size_t nb = (size_t)n * s->l_pad;
     cudaError_t e = cudaMemcpyAsync(t->d_child0, s->d_child0, sizeof(int32_t) * n, cudaMemcpyDeviceToDevice, ctx->stream);
@@ -172,6 +178,7 @@ int lzg_tree_set_topology(lzg_ctx* ctx, lzg_tree* t, const int32_t* child0, cons
     t->scored = false;
     t->up_valid = false;
     t->node4_valid = false;
+    t->d_node4_valid = false;
     return lzg_tree_upload_topology(ctx, t);
 }
 
@@ -230,6 +237,22 @@ int lzg_tree_apply_nni(lzg_ctx* ctx, lzg_tree* t, int32_t u, int32_t w, int32_t 
     int rc = lzg_tree_apply(ctx, t, u, w, v, z);
     if (rc == LZG_OK && root_score) *root_score = t->root_score;
     return rc;
+}
+
+int lzg_hill_climb(lzg_ctx* ctx, lzg_tree* t, int32_t n_edges, const int32_t* edge_order, int32_t greedy, int32_t max_moves,
+                   int32_t moves_cap, int32_t* moves, lzg_climb_result* out) {
+    if (!ctx || !t || t->ctx != ctx || n_edges < 0 || (n_edges > 0 && !edge_order) || moves_cap < 0 || (moves_cap > 0 && !moves))
+        return lzg_fail(ctx, LZG_ERR_ARG, "lzg_hill_climb: bad argument");
+    if (!t->scored) return lzg_fail(ctx, LZG_ERR_STATE, "tree must be scored (lzg_tree_score) before lzg_hill_climb");
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    return lzg_tree_climb(ctx, nullptr, t, n_edges, edge_order, greedy, max_moves, moves_cap, moves, out);
+}
+
+int lzg_tree_last_climb_stamps(const lzg_tree* t, int32_t cap, uint64_t* stamps, int32_t* n) {
+    if (!t || !n || cap < 0 || (cap > 0 && !stamps)) return LZG_ERR_ARG;
+    *n = (int32_t)t->climb_stamps.size();
+    for (int k = 0; k < cap && k < *n; k++) stamps[k] = t->climb_stamps[k];
+    return LZG_OK;
 }
 
 int lzg_tree_get_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end, int32_t* score) {

@@ -172,6 +172,8 @@ __global__ void k_label_level(const int32_t* __restrict__ order, const int2* __r
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(branch + u, (int32_t)c);
 }
 
+#include "lzg_tree_climb.cuh"
+
 // biased bytes [rows][l_pad] -> int32 [rows][L]
 __global__ void k_unpack_i32(const uint8_t* __restrict__ src, int32_t* __restrict__ dst, int L, int l_pad) {
     int r = blockIdx.y;

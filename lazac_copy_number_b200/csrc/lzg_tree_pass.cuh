@@ -43,11 +43,40 @@ struct lzg_pass_args {
     int* ready;           // [n_nodes][groups] epoch flags of the UP rows
     int* ctl;             // [0] ticket, [2] best index, [3] best score, [4] last candidate's score, [15] root score
     int32_t* cand_score;  // [n_cand], zeroed
+    // ---- the device-driven hill climb (lzg_tree_climb.cuh): everything a whole climb needs, so that its
+    //      kernels take no per-tree launch arguments (they read this struct from constant memory) ----
+    int4* node4;          // [n_nodes] {heavy child, light child, internal nodes below << 2 | flags, parent}
+    int32_t *child0, *child1;
+    int2* up;             // (parent, sibling)
+    uint8_t *wstart, *wend;  // the DOWN intervals, writable (== start / end)
+    int32_t* wscore;
+    int32_t* pcost;       // [n_nodes] per-node merge cost of the move being applied; all zero between launches
+    int4* witems;         // == items, writable: five records change per accepted move
+    const int32_t* slot_of;  // [n_nodes] item slot of an internal non-root node
+    const int32_t* cbase;    // [n_nodes] index of the node's first candidate in the host's enumeration (2 x rank among the internal edges)
+    const int32_t* pair_v;   // [n_items] v of the candidates 2k, 2k + 1
+    unsigned long long* queue;  // [groups][qcap] ready path heads of the dataflow UP pass: epoch << 32 | node
+    int* tail;            // [groups] heads pushed so far
+    int32_t* mlog;        // [log_cap][5] accepted moves (u, w, v, z, new score)
+    unsigned long long* tlog;  // [log_cap + 2] %globaltimer at the end of every pass
+    int qcap, log_cap, sharded, use_cond;
+    unsigned long long cond_handle;  // cudaGraphConditionalHandle of the WHILE node the climb runs in
 };
+
+// The climb's copy of the arguments (cudaMemcpyToSymbolAsync before the climb is launched): a CUDA graph
+// freezes kernel arguments, and one graph serves every tree of a shape.
+__constant__ lzg_pass_args c_pass;
 
 // ctl[LZG_CTL_ROOT] sits directly below cand_score: {root score, candidate scores} is ONE vector of
 // n_cand + 1 ints, every entry a sum over positions -- what position-sharded ranks sum-reduce.
-enum { LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_LAST = 4, LZG_CTL_ROOT = 15, LZG_CTL_INTS = 16 };
+enum {
+    LZG_CTL_TICKET = 0, LZG_CTL_DONE = 1, LZG_CTL_BEST = 2, LZG_CTL_SCORE = 3, LZG_CTL_LAST = 4,
+    // the climb's own state (lzg_tree_climb.cuh)
+    LZG_CTL_STOP = 5,      // 0 running, 1 no improving move, 2 the accepted move did not improve, 3 move budget used up, 4 protocol error
+    LZG_CTL_NMOVES = 6, LZG_CTL_CURRENT = 7, LZG_CTL_NPATHS = 8, LZG_CTL_PASSES = 9, LZG_CTL_MAXMOVES = 10,
+    LZG_CTL_EPOCH = 11, LZG_CTL_UPDONE = 12, LZG_CTL_PARTROOT = 13, LZG_CTL_NLOGGED = 14,
+    LZG_CTL_ROOT = 15, LZG_CTL_INTS = 16
+};
 
 // order[].y: the sibling, and LZG_ORDER_PUBLISH if another path's head hangs off the node -- only
 // those UP rows are waited for across walkers, only they pay the release fence.
@@ -226,12 +255,16 @@ __device__ __forceinline__ void score_pair(const lzg_pass_args& A, int u, int w,
     pB = (int32_t)((cB & 0xffffu) + (cB >> 16)) - z;
 }
 
-template <int CPT>
+// DESC: the arguments come from constant memory (c_pass) and the launch is one step of a device-driven
+// climb: nothing to do once the climb has stopped.
+template <int CPT, bool DESC>
 __global__ void __launch_bounds__(256, 4)  // 64 registers: four CTAs per SM (three at 72-80 registers were 10 % slower, five spill)
-k_nni_items(const lzg_pass_args A, int groups_i) {
+k_nni_items(const lzg_pass_args A_, int groups_i) {
+    const lzg_pass_args& A = DESC ? c_pass : A_;
     const int tid = threadIdx.x;
     const int it = blockIdx.x / groups_i, g = blockIdx.x % groups_i;
     const int4 i0 = __ldg(A.items + 2 * it), i1 = __ldg(A.items + 2 * it + 1);
+    if (DESC && __ldcg(A.ctl + LZG_CTL_STOP)) return;
     const int u = i0.x, w = i0.y, a = i0.w, b = i1.x, ia = i1.y, ib = i1.z;
     const size_t off = ((size_t)g * 256 + tid) * CPT;
     int32_t base = 0;
@@ -250,30 +283,49 @@ k_nni_items(const lzg_pass_args A, int groups_i) {
     }
 }
 
+// CLIMB: one step of a device-driven climb (arguments from c_pass).  The scores are zeroed as they are read
+// (the next pass accumulates into them again), the pass is counted and time-stamped, a pass that finds
+// nothing stops the climb, and inside the WHILE graph the loop condition is set here -- the last kernel
+// of every iteration.
+template <bool CLIMB>
 __global__ void __launch_bounds__(1024)
-k_nni_argmin(const lzg_pass_args A) {
+k_nni_argmin(const lzg_pass_args A_) {
+    const lzg_pass_args& A = CLIMB ? c_pass : A_;
     __shared__ unsigned long long s_key[32];
+    __shared__ int32_t s_last_score;
     const int tid = threadIdx.x;
-    const int32_t root = A.ctl[LZG_CTL_ROOT];  // written by k_nni_items; summed over the ranks when positions are sharded
+    if (CLIMB && __ldcg(A.ctl + LZG_CTL_STOP)) {
+        if (A.use_cond && tid == 0) cudaGraphSetConditional(A.cond_handle, 0);
+        return;
+    }
+    const int32_t root = __ldcg(A.ctl + LZG_CTL_ROOT);  // written by k_nni_items; summed over the ranks when positions are sharded
     unsigned long long best = ~0ull;
+    // non-greedy: min (score, index); greedy: min (index) with the score riding in the low half
+    auto key_of = [&](int32_t sc, int i) -> unsigned long long {
+        return A.greedy ? (((unsigned long long)(uint32_t)i) << 32) | (uint32_t)sc : (((unsigned long long)(uint32_t)sc) << 32) | (uint32_t)i;
+    };
     // cand_score is 64-byte aligned (d_cand + LZG_CTL_INTS): four candidates per load, all loads of a
     // thread independent
     const int n4 = A.n_cand >> 2;
-    const int4* sc4 = reinterpret_cast<const int4*>(A.cand_score);
+    int4* sc4 = reinterpret_cast<int4*>(A.cand_score);
     for (int q = tid; q < n4; q += blockDim.x) {
         const int4 v = __ldcg(sc4 + q);
+        if (CLIMB) sc4[q] = make_int4(0, 0, 0, 0);
         const int32_t sc[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int e = 0; e < 4; e++) {
             const int i = 4 * q + e;
-            const unsigned long long key = A.greedy ? (unsigned long long)i : (((unsigned long long)(uint32_t)sc[e]) << 32) | (uint32_t)i;
+            const unsigned long long key = key_of(sc[e], i);
             best = (sc[e] < root && key < best) ? key : best;
+            if (i == A.n_cand - 1) s_last_score = sc[e];
         }
     }
     for (int i = 4 * n4 + tid; i < A.n_cand; i += blockDim.x) {
-        const int32_t sc = A.cand_score[i];
-        const unsigned long long key = A.greedy ? (unsigned long long)i : (((unsigned long long)(uint32_t)sc) << 32) | (uint32_t)i;
+        const int32_t sc = __ldcg(A.cand_score + i);
+        if (CLIMB) A.cand_score[i] = 0;
+        const unsigned long long key = key_of(sc, i);
         best = (sc < root && key < best) ? key : best;
+        if (i == A.n_cand - 1) s_last_score = sc;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -284,14 +336,25 @@ k_nni_argmin(const lzg_pass_args A) {
     __syncthreads();
     if (tid == 0) {
         for (int k = 1; k < 32; k++) best = s_key[k] < best ? s_key[k] : best;
-        A.ctl[LZG_CTL_LAST] = A.cand_score[A.n_cand - 1];  // see lzg_tree_last_candidate_score
+        A.ctl[LZG_CTL_LAST] = s_last_score;  // see lzg_tree_last_candidate_score
         if (best == ~0ull) {
             A.ctl[LZG_CTL_BEST] = -1;
             A.ctl[LZG_CTL_SCORE] = root;
         } else {
-            const int idx = (int)(best & 0xffffffffu);
-            A.ctl[LZG_CTL_BEST] = idx;
-            A.ctl[LZG_CTL_SCORE] = A.cand_score[idx];
+            A.ctl[LZG_CTL_BEST] = A.greedy ? (int)(best >> 32) : (int)(best & 0xffffffffu);
+            A.ctl[LZG_CTL_SCORE] = A.greedy ? (int)(best & 0xffffffffu) : (int)(best >> 32);
+        }
+        if (CLIMB) {
+            const int pass = A.ctl[LZG_CTL_PASSES];
+            if (pass == 0) A.ctl[LZG_CTL_CURRENT] = root;  // hill_climb's current_score = t[0].data.score (src/copy_number.cxx:390)
+            A.ctl[LZG_CTL_PASSES] = pass + 1;
+            if (pass <= A.log_cap) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                A.tlog[pass] = now;
+            }
+            if (best == ~0ull) A.ctl[LZG_CTL_STOP] = 1;  // greedy_nni found no move: hill_climb breaks (:394)
+            if (A.use_cond) cudaGraphSetConditional(A.cond_handle, best == ~0ull ? 0u : 1u);
         }
     }
 }

@@ -203,6 +203,16 @@ class PositionShardedTree:
             return out
         return -1, self.root, (np.zeros(0, np.int32) if want_all else None)
 
+    def hill_climb(self, edge_order, greedy=False, max_moves=2 ** 31 - 1, want_moves=True):
+        """The whole climb with the ranks in lock step (lzg_hill_climb_sharded): per iteration one NCCL
+        sum all-reduce of {root score, candidate scores} on the library stream, nothing else exchanged,
+        no host decision -- every rank derives the same winner from the same reduced vector."""
+        if self.comm is None:
+            raise RuntimeError("the sharded climb needs the in-library NCCL communicator (LZG_SHARD_NCCL=1)")
+        out = self.tree.hill_climb(edge_order, greedy, max_moves, want_moves, comm=self.comm)
+        self.root = out["true_score"]
+        return out
+
     def apply_nni(self, u, w, v, z, new_root=None):
         """Every rank applies the move to its columns.  The new global root score is the accepted
         candidate's score (pass it as new_root to skip the all-reduce of one int)."""
