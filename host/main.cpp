@@ -50,12 +50,13 @@ struct Args {
     std::string command, cn_profile, tree, output;
     double aggression = 1.0;
     int iterations = 100, seed = 0, device = 0;
+    std::vector<int> devices;  // --devices: several GPUs of the box for the distance matrix (trees run on the first)
     bool greedy = false, have_output = false;
 };
 
 const char* USAGE =
-    "Usage: lazac distance cn_profile -o PREFIX [--device N]\n"
-    "       lazac nni cn_profile [-t TREE] -o PREFIX [-a AGGRESSION] [-i ITERATIONS] [-g] [-s SEED] [--device N]\n"
+    "Usage: lazac distance cn_profile -o PREFIX [--device N | --devices LIST]\n"
+    "       lazac nni cn_profile [-t TREE] -o PREFIX [-a AGGRESSION] [-i ITERATIONS] [-g] [-s SEED] [--device N | --devices LIST]\n"
     "\n"
     "  -t, --tree        seed tree in Newick format. [default: \"\"]\n"
     "  -o, --output      prefix of the output files [required]\n"
@@ -63,7 +64,8 @@ const char* USAGE =
     "  -i, --iterations  number of iterations to perform without improvement before stopping [default: 100]\n"
     "  -g, --greedy      use greedy hill climbing strategy as opposed to full NNI neighborhood exploration\n"
     "  -s, --seed        seed for random number generator [default: 0]\n"
-    "      --device      CUDA device index [default: 0]\n";
+    "      --device      CUDA device index [default: 0]\n"
+    "      --devices     GPUs for the distance matrix, e.g. 0-7 or 0,2,3 (the search runs on the first)\n";
 
 Args parse_args(int argc, char** argv) {
     Args a;
@@ -102,6 +104,21 @@ Args parse_args(int argc, char** argv) {
             a.seed = (int)number(value(), true);
         } else if (s == "--device") {
             a.device = (int)number(value(), true);
+        } else if (s == "--devices") {  // "0-7", "0,2,3", "1"
+            const std::string v = value();
+            size_t pos = 0;
+            while (pos <= v.size()) {
+                const size_t comma = std::min(v.find(',', pos), v.size());
+                const std::string part = v.substr(pos, comma - pos);
+                const size_t dash = part.find('-');
+                const int lo = (int)number(dash == std::string::npos ? part : part.substr(0, dash), true);
+                const int hi = dash == std::string::npos ? lo : (int)number(part.substr(dash + 1), true);
+                if (lo < 0 || hi < lo || hi - lo > 1023) throw std::runtime_error("pattern '" + v + "' not found");
+                for (int d = lo; d <= hi; d++) a.devices.push_back(d);
+                pos = comma + 1;
+            }
+            if (a.devices.empty()) throw std::runtime_error("--devices: expected at least one device");
+            a.device = a.devices[0];
         } else if (s == "-g" || s == "--greedy") {
             a.greedy = true;
         } else if (s == "-h" || s == "--help") {
@@ -123,6 +140,14 @@ Args parse_args(int argc, char** argv) {
 
 struct Gpu {
     lzg_ctx* ctx = nullptr;
+    lzg_multi* multi = nullptr;  // --devices: one context per GPU; ctx = the first one's
+    explicit Gpu(const std::vector<int>& devices) {
+        std::vector<int32_t> d(devices.begin(), devices.end());
+        int rc = lzg_multi_init(d.data(), (int32_t)d.size(), &multi);
+        if (rc == LZG_OK) rc = lzg_multi_context(multi, 0, &ctx);
+        if (rc != LZG_OK)
+            throw std::runtime_error(std::string("cannot open CUDA devices: ") + lzg_status_string(rc) + ": " + lzg_last_error(nullptr));
+    }
     explicit Gpu(int device) {
         const auto t0 = std::chrono::steady_clock::now();
         int rc = lzg_init(device, &ctx);
@@ -133,7 +158,8 @@ struct Gpu {
             throw std::runtime_error(std::string("cannot open CUDA device: ") + lzg_status_string(rc) + ": " + lzg_last_error(nullptr));
     }
     ~Gpu() {
-        if (ctx) lzg_shutdown(ctx);
+        if (multi) lzg_multi_shutdown(multi);
+        else if (ctx) lzg_shutdown(ctx);
     }
     void check(int rc) const {
         if (rc != LZG_OK) throw_lzg(ctx, rc);
@@ -144,13 +170,20 @@ struct Gpu {
 std::vector<int32_t> build_distance_matrix(const Gpu& gpu, const BreakpointSet& set, lzg_profiles** keep) {
     const int n = (int)set.names.size();
     lzg_profiles* p = nullptr;
-    gpu.check(lzg_profiles_upload(gpu.ctx, set.bp.data(), n, set.L, &p));
     std::vector<int32_t> D((size_t)n * n);
     log_info("Built 0 out of " + std::to_string(n) + " rows of distance matrix.");
-    gpu.check(lzg_distance_matrix(gpu.ctx, p, D.data()));
+    if (gpu.multi && lzg_multi_size(gpu.multi) > 1) {
+        // several GPUs: row blocks uploaded per GPU, tile rows dealt to them, the matrix gathered here
+        const int rc = lzg_distance_matrix_multi(gpu.multi, set.bp.data(), n, set.L, D.data(), nullptr);
+        if (rc != LZG_OK) throw std::runtime_error(std::string(lzg_status_string(rc)) + ": " + lzg_multi_last_error(gpu.multi));
+        if (keep) gpu.check(lzg_profiles_upload(gpu.ctx, set.bp.data(), n, set.L, &p));  // the trees of the search live on the first GPU
+    } else {
+        gpu.check(lzg_profiles_upload(gpu.ctx, set.bp.data(), n, set.L, &p));
+        gpu.check(lzg_distance_matrix(gpu.ctx, p, D.data()));
+    }
     log_info("Finished building " + std::to_string(n) + " x " + std::to_string(n) + " distance matrix.");
     if (keep) *keep = p;
-    else lzg_profiles_free(p);
+    else if (p) lzg_profiles_free(p);
     return D;
 }
 
@@ -207,12 +240,14 @@ BreakpointSet ingest(const std::string& path) {
 
 // The CUDA context of a fresh process takes seconds (2.4 s measured on a B200 box): open it on a
 // second thread while this one parses the CSV.
-std::future<std::unique_ptr<Gpu>> open_gpu_async(int device) {
-    return std::async(std::launch::async, [device]() { return std::make_unique<Gpu>(device); });
+std::future<std::unique_ptr<Gpu>> open_gpu_async(const Args& a) {
+    const int device = a.device;
+    const std::vector<int> devices = a.devices;
+    return std::async(std::launch::async, [device, devices]() { return devices.empty() ? std::make_unique<Gpu>(device) : std::make_unique<Gpu>(devices); });
 }
 
 void do_distance(const Args& a) {
-    auto gpu_opening = open_gpu_async(a.device);
+    auto gpu_opening = open_gpu_async(a);
     const BreakpointSet set = ingest(a.cn_profile);
     const std::unique_ptr<Gpu> gpu_owner = gpu_opening.get();
     Gpu& gpu = *gpu_owner;
@@ -267,7 +302,7 @@ void do_nni(const Args& a) {
         }
     } total{t_start};
     /* Load copy number profiles */
-    auto gpu_opening = open_gpu_async(a.device);
+    auto gpu_opening = open_gpu_async(a);
     const BreakpointSet set = ingest(a.cn_profile);
     const int n_cells = (int)set.names.size();
     const std::unique_ptr<Gpu> gpu_owner = gpu_opening.get();

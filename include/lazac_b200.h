@@ -88,6 +88,25 @@ int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard, int32
 int lzg_distance_shard_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard,
                                     int32_t n_shards, int32_t* d_D, int64_t* pairs_done);
 
+/* ---- several GPUs of one box, one process: build_distance_matrix ends with the WHOLE matrix in the
+ *      caller's buffer (src/lazac.cxx:63-95 returns one matrix; do_nni feeds it to NJ, :153-200).
+ * lzg_multi_init opens one context per listed device and enables peer access between them (NVLink /
+ * NVSwitch).  lzg_distance_matrix_multi: every GPU uploads 1/G of the profile rows over its own
+ * PCIe link and pushes them to its peers, computes its tile rows (dealt in pairs (r, R-1-r)), writes
+ * the mirror of every tile straight into the owner's memory, and copies the output rows it owns into
+ * D_host -- all GPUs at once.  Pinned host buffers (lzg_host_alloc) make the copies asynchronous. */
+typedef struct lzg_multi lzg_multi;
+int lzg_multi_init(const int32_t* devices, int32_t n_devices, lzg_multi** out);
+int lzg_multi_shutdown(lzg_multi* m);
+int lzg_multi_size(const lzg_multi* m);
+/* The i-th device's context, for the single-GPU entry points (trees, NJ); owned by m. */
+int lzg_multi_context(lzg_multi* m, int32_t i, lzg_ctx** ctx);
+const char* lzg_multi_last_error(const lzg_multi* m);
+int lzg_distance_matrix_multi(lzg_multi* m, const int32_t* bp, int32_t n_cells, int32_t n_pos, int32_t* D_host,
+                              int64_t* pairs_done);
+int lzg_distance_matrix_multi_i8(lzg_multi* m, const int8_t* bp, int32_t n_cells, int32_t n_pos, int32_t* D_host,
+                                 int64_t* pairs_done);
+
 /* Host only -- no GPU, no context: the work plan lzg_distance_* launches for an n x L input on a
  * device of sm_count SMs (one persistent CTA per SM).  segs receives four ints per
  * segment {tile row, tile column, k0, k1}: 16-byte position chunks [k0, |k1|) of that tile, k1 < 0

@@ -41,6 +41,13 @@ SYMBOLS = [
     ("lzg_distance_matrix_device_async", _i, [_vp, _vp, _vp]),
     ("lzg_distance_shard", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
     ("lzg_distance_shard_device_async", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
+    ("lzg_multi_init", _i, [_vp, _i32, _vpp]),
+    ("lzg_multi_shutdown", _i, [_vp]),
+    ("lzg_multi_size", _i, [_vp]),
+    ("lzg_multi_context", _i, [_vp, _i32, _vpp]),
+    ("lzg_multi_last_error", C.c_char_p, [_vp]),
+    ("lzg_distance_matrix_multi", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
+    ("lzg_distance_matrix_multi_i8", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
     ("lzg_distance_plan", _i, [_i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _i32, _vp]),
     ("lzg_tree_create", _i, [_vp, _vp, _i32, _vp, _vp, _vp, _vpp]),
     ("lzg_tree_clone", _i, [_vp, _vp, _vpp]),

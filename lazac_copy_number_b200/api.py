@@ -105,6 +105,47 @@ class Context:
             prof.free()
 
 
+class MultiContext:
+    """Several GPUs of one box driven from this process (lzg_multi_*): build_distance_matrix with the
+    whole matrix gathered into one host buffer."""
+
+    def __init__(self, devices):
+        self.lib = _capi.load()
+        dev = i32(list(devices))
+        h = C.c_void_p()
+        rc = self.lib.lzg_multi_init(ptr(dev), len(dev), C.byref(h))
+        if rc != 0:
+            raise LazacGpuError(rc, self.lib.lzg_last_error(None).decode())
+        self.h, self.devices = h, [int(d) for d in dev]
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lzg_multi_shutdown(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def distance_matrix(self, bp, out=None):
+        """bp: int8 or int32 [n][L] (pinned buffers make the copies asynchronous).  Returns (D, pairs)."""
+        bp = np.asarray(bp)
+        n, L = bp.shape
+        D = np.empty((n, n), np.int32) if out is None else out
+        pairs = C.c_int64(0)
+        if bp.dtype == np.int8:
+            bp = np.ascontiguousarray(bp)
+            rc = self.lib.lzg_distance_matrix_multi_i8(self.h, ptr(bp), n, L, ptr(D), C.byref(pairs))
+        else:
+            bp = i32(bp)
+            rc = self.lib.lzg_distance_matrix_multi(self.h, ptr(bp), n, L, ptr(D), C.byref(pairs))
+        if rc != 0:
+            raise LazacGpuError(rc, self.lib.lzg_multi_last_error(self.h).decode())
+        return D, pairs.value
+
+
 class Profiles:
     """Breakpoint vectors of N cells resident in HBM (int8 + 128 bias)."""
 

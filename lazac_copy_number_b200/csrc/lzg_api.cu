@@ -8,10 +8,6 @@
 #include "lzg_common.cuh"
 #include "lzg_tree.cuh"
 
-int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
-int lzg_pack_rows_i8(lzg_ctx* ctx, const int8_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
-int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v);
-int lzg_bias_rows_i8(lzg_ctx* ctx, uint8_t* d, int n, int n_pad, int L, int l_pad);
 
 static thread_local std::string g_init_error;
 
@@ -177,7 +173,7 @@ int lzg_flush_l2(lzg_ctx* ctx) {
 
 int lzg_host_alloc(lzg_ctx* ctx, uint64_t bytes, void** out) {
     if (!ctx || !out) return LZG_ERR_ARG;
-    LZG_CUDA(ctx, cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    LZG_CUDA(ctx, cudaHostAlloc(out, bytes, cudaHostAllocPortable));  // pinned for every GPU of the process (lzg_multi)
     return LZG_OK;
 }
 

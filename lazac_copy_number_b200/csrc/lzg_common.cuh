@@ -43,7 +43,7 @@ struct lzg_ctx {
     cudaEvent_t ev_stage = nullptr;  // the last asynchronous copy OUT of the pinned staging area that no synchronising call has waited for
     std::vector<lzg_schedule> schedules;  // distance schedules by (shape, tile, shard); freed at shutdown
     struct climb_graph {                  // one WHILE graph per launch geometry of the climb (lzg_tree.cu)
-        int n_items = 0, gi = 0, groups = 0, threads = 0, up_grid = 0, n_cand = 0;
+        int n_items = 0, groups = 0, threads = 0, up_grid = 0, n_cand = 0;
         cudaGraph_t graph = nullptr;
         cudaGraphExec_t exec = nullptr;
         cudaGraphConditionalHandle handle = 0;
@@ -87,8 +87,13 @@ int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuc
     } while (0)
 
 // distance module (lzg_distance.cu)
+// d_row_base (optional, device array of one pointer per tile row): where the output rows of each tile row live
+// instead of the one N x N matrix d_D (the row blocks of several GPUs, lzg_multi.cu)
 int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int row_lo, int row_hi,
-                     int32_t* d_D, int64_t* pairs_done);
+                     int32_t* d_D, int64_t* pairs_done, int32_t* const* d_row_base = nullptr);
+int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
+int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v);
+int lzg_bias_rows_i8(lzg_ctx* ctx, uint8_t* d, int n, int n_pad, int L, int l_pad);
 // tile edge of the pair kernel for this input: one 64 x 64 tile when n <= 64, else 128 x 128
 inline int lzg_distance_tile(const lzg_profiles* p) { return p->n <= 64 ? 64 : 128; }
 // pinned / scratch helpers (lzg_api.cu)

@@ -59,21 +59,6 @@ __global__ void k_pack_i32(const int32_t* __restrict__ src, uint8_t* __restrict_
     if (bad) atomicOr(flag, 1);
 }
 
-// int8 [rows][L] -> biased bytes [rows][l_pad]; -128 is out of range (keeps |a-b| <= 254).
-__global__ void k_pack_i8(const int8_t* __restrict__ src, uint8_t* __restrict__ dst, int rows, int L,
-                          int l_pad, int* flag) {
-    int r = blockIdx.y;
-    const int8_t* s = src + (size_t)r * L;
-    uint8_t* d = dst + (size_t)r * l_pad;
-    int bad = 0;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < l_pad; k += gridDim.x * blockDim.x) {
-        int v = k < L ? s[k] : 0;
-        bad |= (v == -128);
-        d[k] = (uint8_t)(v + LZG_BIAS);
-    }
-    if (bad) atomicOr(flag, 1);
-}
-
 __global__ void k_fill_bytes(uint8_t* dst, size_t n, uint8_t v) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         dst[i] = v;
@@ -196,7 +181,7 @@ __device__ __forceinline__ void tile_step_partial(uint32_t (&acc)[8][8], const u
 template <int BM, int BN, int STAGES>
 __global__ void __launch_bounds__((BM / 8) * (BN / 8), 1)
 k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_seg* __restrict__ segs,
-                const int32_t* __restrict__ seg_off, int32_t* __restrict__ D) {
+                const int32_t* __restrict__ seg_off, int32_t* __restrict__ D, int32_t* const* __restrict__ row_base) {
     constexpr int TX = BN / 8, TY = BM / 8, T = TX * TY;
     constexpr int A_BYTES = BM * KC, B_BYTES = BN * KC, STAGE_BYTES = A_BYTES + B_BYTES;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -211,6 +196,10 @@ k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_se
         const int k_begin = sg.k0, n_chunks = (atomic ? -sg.k1 : sg.k1) - sg.k0, n_it = (n_chunks + 7) >> 3;
         const bool diag = sg.r == sg.c;
         const int row0 = sg.r * BM, col0 = sg.c * BN;
+        // where the output rows of tile row r live: one N x N matrix, or (several GPUs, lzg_multi.cu) the
+        // owner's row block -- the mirror of a tile then goes straight into a peer's memory over NVLink
+        int32_t* const out_r = row_base ? row_base[sg.r] : D + (size_t)row0 * n;
+        int32_t* const out_c = row_base ? row_base[sg.c] : D + (size_t)col0 * n;
         const uint8_t* gA = prof + (size_t)row0 * l_pad + (size_t)k_begin * 16;
         const uint8_t* gB = prof + (size_t)col0 * l_pad + (size_t)k_begin * 16;
 
@@ -282,7 +271,7 @@ k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_se
             const int c = tid % BN, rmax = min(BM, n - row0);
             const bool col_ok = col0 + c < n;
             const int32_t* src = tbuf + (tid / BN) * LD + c;
-            int32_t* dst = D + (size_t)(row0 + tid / BN) * n + col0 + c;
+            int32_t* dst = out_r + (size_t)(tid / BN) * n + col0 + c;
             const int r_skip = (diag && c < BN / 2) ? BM / 2 : BM;  // lower-left quadrant of a diagonal tile
             const int r_end = col_ok ? min(rmax, r_skip) : 0;
             if (atomic) {
@@ -301,7 +290,7 @@ k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_se
             int c = tid / BM;
             if (diag) c += BN / 2;  // only the upper-right quadrant of a diagonal tile is mirrored
             const int32_t* src = tbuf + r * LD + c;
-            int32_t* dst = D + (size_t)(col0 + c) * n + row0 + r;
+            int32_t* dst = out_c + (size_t)c * n + row0 + r;
             const int c_end = row_ok ? cmax : 0;
             if (atomic) {
 #pragma unroll 4
@@ -317,15 +306,17 @@ k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_se
 
 // Zeroes the cells (tile and mirror) of the tiles that are accumulated with atomics.
 template <int BM, int BN>
-__global__ void k_zero_tiles(const int2* __restrict__ tiles, int n, int32_t* __restrict__ D) {
+__global__ void k_zero_tiles(const int2* __restrict__ tiles, int n, int32_t* __restrict__ D, int32_t* const* __restrict__ row_base) {
     const int2 t = tiles[blockIdx.x];
     const int row0 = t.x * BM, col0 = t.y * BN;
+    int32_t* const out_r = row_base ? row_base[t.x] : D + (size_t)row0 * n;
+    int32_t* const out_c = row_base ? row_base[t.y] : D + (size_t)col0 * n;
     for (int q = blockIdx.y * blockDim.x + threadIdx.x; q < BM * BN; q += gridDim.y * blockDim.x) {
         int r = q / BN, c = q % BN;
         int gi = row0 + r, gj = col0 + c;
         if (gi < n && gj < n) {
-            D[(size_t)gi * n + gj] = 0;
-            D[(size_t)gj * n + gi] = 0;
+            out_r[(size_t)r * n + gj] = 0;
+            out_c[(size_t)c * n + gi] = 0;
         }
     }
 }
@@ -571,17 +562,17 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
 }
 
 template <int BM, int BN, int STAGES>
-int launch_distance(lzg_ctx* ctx, const lzg_profiles* p, const lzg_schedule* sc, int32_t* d_D) {
+int launch_distance(lzg_ctx* ctx, const lzg_profiles* p, const lzg_schedule* sc, int32_t* d_D, int32_t* const* d_row_base) {
     constexpr int smem = dist_smem_bytes<BM, BN, STAGES>();
     constexpr int T = (BM / 8) * (BN / 8);
     if (sc->n_split > 0) {
-        k_zero_tiles<BM, BN><<<dim3(sc->n_split, 16), 256, 0, ctx->stream>>>(sc->d_split, p->n, d_D);
+        k_zero_tiles<BM, BN><<<dim3(sc->n_split, 16), 256, 0, ctx->stream>>>(sc->d_split, p->n, d_D, d_row_base);
         LZG_LAUNCH_CHECK(ctx);
     }
     auto kern = k_zcnt_distance<BM, BN, STAGES>;
     LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    kern<<<sc->n_ctas, T, smem, ctx->stream>>>(p->d, p->l_pad, p->n, (const lzg_seg*)sc->d_segs, sc->d_seg_off, d_D);
+    kern<<<sc->n_ctas, T, smem, ctx->stream>>>(p->d, p->l_pad, p->n, (const lzg_seg*)sc->d_segs, sc->d_seg_off, d_D, d_row_base);
     LZG_LAUNCH_CHECK(ctx);
     return LZG_OK;
 }
@@ -591,13 +582,6 @@ int launch_distance(lzg_ctx* ctx, const lzg_profiles* p, const lzg_schedule* sc,
 int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad) {
     dim3 grid(std::max(1, std::min(64, (l_pad / 4 + 255) / 256)), rows);
     k_pack_i32<<<grid, 256, 0, ctx->stream>>>(d_src, d_dst, rows, L, l_pad, ctx->d_flag);
-    LZG_LAUNCH_CHECK(ctx);
-    return LZG_OK;
-}
-
-int lzg_pack_rows_i8(lzg_ctx* ctx, const int8_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad) {
-    dim3 grid(std::max(1, std::min(64, (l_pad + 255) / 256)), rows);
-    k_pack_i8<<<grid, 256, 0, ctx->stream>>>(d_src, d_dst, rows, L, l_pad, ctx->d_flag);
     LZG_LAUNCH_CHECK(ctx);
     return LZG_OK;
 }
@@ -620,7 +604,7 @@ int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v) {
 // Computes the shard's tiles of tile rows [row_lo, row_hi) into the full N x N device matrix d_D
 // (asynchronous on ctx->stream).
 int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int row_lo, int row_hi, int32_t* d_D,
-                     int64_t* pairs_done) {
+                     int64_t* pairs_done, int32_t* const* d_row_base) {
     if (pairs_done) *pairs_done = 0;
     if (p->n == 0) return LZG_OK;
     int status = LZG_OK;
@@ -631,7 +615,7 @@ int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int
     if (!sc) return status;
     if (pairs_done) *pairs_done = sc->pairs;
     if (sc->n_segs == 0) return LZG_OK;
-    return bm == 64 ? launch_distance<64, 64, 4>(ctx, p, sc, d_D) : launch_distance<128, 128, 3>(ctx, p, sc, d_D);
+    return bm == 64 ? launch_distance<64, 64, 4>(ctx, p, sc, d_D, d_row_base) : launch_distance<128, 128, 3>(ctx, p, sc, d_D, d_row_base);
 }
 
 // Host-only view of the work plan (no GPU, no context): see include/lazac_b200.h.

@@ -607,7 +607,7 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     const auto t_launch = std::chrono::steady_clock::now();
     {
         const int gi = (t->l_pad + 256 * 16 - 1) / (256 * 16);
-        k_nni_items<16, false><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
+        k_nni_items<16><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
     }
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaEventRecord(ctx->ev_items, ctx->stream));
@@ -833,25 +833,42 @@ int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* br
 // log and replays it on the host mirror.
 namespace {
 
-constexpr int LZG_CLIMB_LOG = 4096;  // accepted moves logged on the device before the host drains the log
+constexpr int LZG_CLIMB_LOG = 4096;    // accepted moves logged on the device before the host drains the log
+constexpr int LZG_UQ_SLACK = 4096;     // queue entries beyond one per (node, chunk group): tickets drawn by idle CTAs
 
 struct climb_layout {  // offsets (bytes) into t->d_climb
-    size_t items, slot_of, cbase, pair_v, upload_bytes, pcost, tail, mlog, queue, tlog, total;
+    size_t items, slot_of, cbase, pair_v, upload_bytes, pcost, tail, xctl, dn_stamp, up_stamp, rec_stamp, part, uq_flag, wl, deep_chg, zero_end,
+        mlog, uq, deep_path, queue, tlog, total;
+    int ucap;
 };
 
 climb_layout climb_offsets(int n_nodes, int n_items, int groups) {
     climb_layout o;
     auto up16 = [](size_t x) { return (x + 15) / 16 * 16; };
+    const size_t ni = (size_t)std::max(1, n_items), G = (size_t)groups, nn = (size_t)n_nodes;
+    o.ucap = (int)std::min<size_t>(ni * G + LZG_UQ_SLACK, (size_t)1 << 30);
     size_t p = 0;
-    o.items = p, p = up16(p + sizeof(int4) * 2 * (size_t)std::max(1, n_items));
-    o.slot_of = p, p = up16(p + sizeof(int32_t) * (size_t)n_nodes);
-    o.cbase = p, p = up16(p + sizeof(int32_t) * (size_t)n_nodes);
-    o.pair_v = p, p = up16(p + sizeof(int32_t) * (size_t)std::max(1, n_items));
+    o.items = p, p = up16(p + sizeof(int4) * 2 * ni);
+    o.slot_of = p, p = up16(p + sizeof(int32_t) * nn);
+    o.cbase = p, p = up16(p + sizeof(int32_t) * nn);
+    o.pair_v = p, p = up16(p + sizeof(int32_t) * ni);
     o.upload_bytes = p;  // everything above is rewritten by the host at the start of a climb
-    o.pcost = p, p = up16(p + sizeof(int32_t) * (size_t)n_nodes);
-    o.tail = p, p = up16(p + sizeof(int32_t) * (size_t)std::max(4, groups));
+    // zero at allocation and kept consistent by the kernels
+    o.pcost = p, p = up16(p + sizeof(int32_t) * nn);
+    o.tail = p, p = up16(p + sizeof(int32_t) * std::max<size_t>(4, G));
+    o.xctl = p, p = up16(p + sizeof(int32_t) * LZG_X_INTS);
+    o.dn_stamp = p, p = up16(p + sizeof(int32_t) * nn * G);
+    o.up_stamp = p, p = up16(p + sizeof(int32_t) * nn * G);
+    o.rec_stamp = p, p = up16(p + sizeof(int32_t) * ni);
+    o.part = p, p = up16(p + sizeof(int32_t) * 2 * ni * G);
+    o.uq_flag = p, p = up16(p + sizeof(int32_t) * (size_t)o.ucap);
+    o.wl = p, p = up16(p + sizeof(int32_t) * ni * G);
+    o.deep_chg = p, p = up16(p + sizeof(int32_t) * nn * G);
+    o.queue = p, p = up16(p + sizeof(unsigned long long) * G * (ni + 1));
+    o.zero_end = p;
     o.mlog = p, p = up16(p + sizeof(int32_t) * 5 * (size_t)LZG_CLIMB_LOG);
-    o.queue = p, p = up16(p + sizeof(unsigned long long) * (size_t)groups * ((size_t)n_items + 1));
+    o.uq = p, p = up16(p + sizeof(int4) * (size_t)o.ucap);
+    o.deep_path = p, p = up16(p + sizeof(int2) * nn * G);
     o.tlog = p, p = up16(p + sizeof(unsigned long long) * ((size_t)LZG_CLIMB_LOG + 2));
     o.total = p;
     return o;
@@ -863,8 +880,8 @@ int ensure_climb_buffers(lzg_ctx* ctx, lzg_tree* t, int n_items, int groups) {
     lzg_dev_free(ctx, t->d_climb);
     t->d_climb = nullptr;
     LZG_CUDA(ctx, lzg_dev_alloc(ctx, &t->d_climb, o.total));
-    // cost cells, queue tails and queue entries start at zero (epochs start at 1); the upload area is written per climb
-    LZG_CUDA(ctx, cudaMemsetAsync((uint8_t*)t->d_climb + o.pcost, 0, o.total - o.pcost, ctx->stream));
+    // cost cells, counters, stamps, queue flags start at zero (stamps and epochs start at 1); the upload area is written per climb
+    LZG_CUDA(ctx, cudaMemsetAsync((uint8_t*)t->d_climb + o.pcost, 0, o.zero_end - o.pcost, ctx->stream));
     t->climb_bytes = o.total;
     t->climb_items = n_items;
     t->df_epoch = 1;
@@ -876,87 +893,92 @@ int ensure_climb_buffers(lzg_ctx* ctx, lzg_tree* t, int n_items, int groups) {
 }
 
 struct climb_geometry {
-    int n_items, n_cand, gi, groups, threads, up_grid;
+    int n_items, n_cand, groups, threads, up_grid, delta_grid, wl_grid, scan_grid;
 };
 
-void* climb_kernel(int which) {
+enum { K_UP_FULL = 0, K_DIRTY, K_ITEMS, K_ASSEMBLE, K_ARGMIN, K_APPLY, K_UP_DELTA };
+
+struct climb_launch {
+    void* fn;
+    dim3 grid, block;
+    bool has_arg;  // k_nni_argmin takes a (dummy) lzg_pass_args by value; the others take nothing
+};
+
+climb_launch climb_kernel(int which, const climb_geometry& G) {
     switch (which) {
-        case 0: return (void*)k_up_df<true>;
-        case 1: return (void*)k_nni_items<16, true>;
-        case 2: return (void*)k_nni_argmin<true>;
-        default: return (void*)k_apply2<true>;
+        case K_UP_FULL: return {(void*)k_up_df, dim3(G.up_grid), dim3(G.threads), false};
+        case K_DIRTY: return {(void*)k_dirty_scan, dim3(G.scan_grid), dim3(256), false};
+        case K_ITEMS: return {(void*)k_items_wl, dim3(G.wl_grid), dim3(G.threads), false};
+        case K_ASSEMBLE: return {(void*)k_cand_assemble, dim3(G.scan_grid), dim3(256), false};
+        case K_ARGMIN: return {(void*)k_nni_argmin<true>, dim3(1), dim3(1024), true};
+        case K_APPLY: return {(void*)k_apply2, dim3(G.groups), dim3(G.threads), false};
+        default: return {(void*)k_up_delta, dim3(G.delta_grid), dim3(G.threads), false};
     }
 }
 
-// One iteration = {apply, up, items, argmin}; pass 0 has no move to apply.  Plain stream launches.
-int climb_enqueue_pass(lzg_ctx* ctx, const climb_geometry& G, bool with_apply, lzg_comm* comm, lzg_tree* t) {
-    const lzg_pass_args dummy{};
-    if (with_apply) {
-        k_apply2<true><<<G.groups, G.threads, 0, ctx->stream>>>(dummy, lzg_move{0, 0, 0, 0});
-        LZG_LAUNCH_CHECK(ctx);
+const int PASS0[] = {K_UP_FULL, K_DIRTY, K_ITEMS, K_ASSEMBLE, K_ARGMIN};
+const int ITERATION[] = {K_APPLY, K_UP_DELTA, K_DIRTY, K_ITEMS, K_ASSEMBLE, K_ARGMIN};
+
+// One pass as plain stream launches; the all-reduce of the position-sharded climb sits between the
+// assembled scores and the arg-min.
+int climb_enqueue(lzg_ctx* ctx, const climb_geometry& G, const int* seq, int n_seq, lzg_comm* comm, lzg_tree* t) {
+    static lzg_pass_args dummy{};
+    for (int q = 0; q < n_seq; q++) {
+        if (seq[q] == K_ARGMIN && comm && lzg_comm_world(comm) > 1) {
+            const int rc = lzg_comm_allreduce_sum(ctx, comm, t->d_cand + LZG_CTL_ROOT, (size_t)G.n_cand + 1);
+            if (rc != LZG_OK) return rc;
+        }
+        const climb_launch L = climb_kernel(seq[q], G);
+        void* args[] = {(void*)&dummy};
+        LZG_CUDA(ctx, cudaLaunchKernel(L.fn, L.grid, L.block, L.has_arg ? args : nullptr, 0, ctx->stream));
+        ctx->launches++;
     }
-    k_up_df<true><<<G.up_grid, G.threads, 0, ctx->stream>>>(dummy);
-    LZG_LAUNCH_CHECK(ctx);
-    k_nni_items<16, true><<<G.n_items * G.gi, 256, 0, ctx->stream>>>(dummy, G.gi);
-    LZG_LAUNCH_CHECK(ctx);
-    if (comm && lzg_comm_world(comm) > 1) {
-        const int rc = lzg_comm_allreduce_sum(ctx, comm, t->d_cand + LZG_CTL_ROOT, (size_t)G.n_cand + 1);
-        if (rc != LZG_OK) return rc;
-    }
-    k_nni_argmin<true><<<1, 1024, 0, ctx->stream>>>(dummy);
-    LZG_LAUNCH_CHECK(ctx);
     return LZG_OK;
 }
 
 // The climb as one graph: pass 0, then a WHILE node whose body is one iteration; the arg-min kernel sets
-// the loop condition.  Kernel arguments are dummies -- the kernels read c_pass -- so one graph serves
-// every tree of this launch geometry.
+// the loop condition.  The kernels read c_pass, so one graph serves every tree of this launch geometry.
 lzg_ctx::climb_graph* climb_graph_for(lzg_ctx* ctx, const climb_geometry& G) {
     for (auto& g : ctx->climb_graphs)
-        if (g.n_items == G.n_items && g.gi == G.gi && g.groups == G.groups && g.threads == G.threads && g.up_grid == G.up_grid && g.n_cand == G.n_cand) return &g;
+        if (g.n_items == G.n_items && g.groups == G.groups && g.threads == G.threads && g.up_grid == G.up_grid && g.n_cand == G.n_cand) return &g;
     if (ctx->climb_graph_broken) return nullptr;
     lzg_ctx::climb_graph cg;
-    cg.n_items = G.n_items, cg.gi = G.gi, cg.groups = G.groups, cg.threads = G.threads, cg.up_grid = G.up_grid, cg.n_cand = G.n_cand;
+    cg.n_items = G.n_items, cg.groups = G.groups, cg.threads = G.threads, cg.up_grid = G.up_grid, cg.n_cand = G.n_cand;
     static lzg_pass_args dummy{};
-    static lzg_move no_move{0, 0, 0, 0};
-    static int gi_arg;
-    gi_arg = G.gi;
-    auto add_kernel = [&](cudaGraph_t graph, cudaGraphNode_t* dep, int which, cudaGraphNode_t* out) -> cudaError_t {
-        cudaKernelNodeParams kp{};
-        void* args_up[] = {(void*)&dummy};
-        void* args_items[] = {(void*)&dummy, (void*)&gi_arg};
-        void* args_apply[] = {(void*)&dummy, (void*)&no_move};
-        kp.func = climb_kernel(which);
-        kp.sharedMemBytes = 0;
-        kp.extra = nullptr;
-        switch (which) {
-            case 0: kp.gridDim = dim3(G.up_grid), kp.blockDim = dim3(G.threads), kp.kernelParams = args_up; break;
-            case 1: kp.gridDim = dim3(G.n_items * G.gi), kp.blockDim = dim3(256), kp.kernelParams = args_items; break;
-            case 2: kp.gridDim = dim3(1), kp.blockDim = dim3(1024), kp.kernelParams = args_up; break;
-            default: kp.gridDim = dim3(G.groups), kp.blockDim = dim3(G.threads), kp.kernelParams = args_apply; break;
+    auto add_chain = [&](cudaGraph_t graph, const int* seq, int n_seq, cudaGraphNode_t* last) -> cudaError_t {
+        cudaGraphNode_t prev = nullptr;
+        for (int q = 0; q < n_seq; q++) {
+            const climb_launch L = climb_kernel(seq[q], G);
+            cudaKernelNodeParams kp{};
+            void* args[] = {(void*)&dummy};
+            kp.func = L.fn;
+            kp.gridDim = L.grid;
+            kp.blockDim = L.block;
+            kp.sharedMemBytes = 0;
+            kp.kernelParams = L.has_arg ? args : nullptr;
+            kp.extra = nullptr;
+            cudaGraphNode_t node = nullptr;
+            const cudaError_t e = cudaGraphAddKernelNode(&node, graph, prev ? &prev : nullptr, prev ? 1 : 0, &kp);
+            if (e != cudaSuccess) return e;
+            prev = node;
         }
-        return cudaGraphAddKernelNode(out, graph, dep, dep ? 1 : 0, &kp);
+        *last = prev;
+        return cudaSuccess;
     };
     cudaError_t e = cudaGraphCreate(&cg.graph, 0);
-    cudaGraphNode_t n0 = nullptr, n1 = nullptr, n2 = nullptr, nw = nullptr;
+    cudaGraphNode_t tail0 = nullptr, nw = nullptr;
     if (e == cudaSuccess) e = cudaGraphConditionalHandleCreate(&cg.handle, cg.graph, 1, cudaGraphCondAssignDefault);
-    if (e == cudaSuccess) e = add_kernel(cg.graph, nullptr, 0, &n0);
-    if (e == cudaSuccess) e = add_kernel(cg.graph, &n0, 1, &n1);
-    if (e == cudaSuccess) e = add_kernel(cg.graph, &n1, 2, &n2);
+    if (e == cudaSuccess) e = add_chain(cg.graph, PASS0, 5, &tail0);
     if (e == cudaSuccess) {
         cudaGraphNodeParams cp{};
         cp.type = cudaGraphNodeTypeConditional;
         cp.conditional.handle = cg.handle;
         cp.conditional.type = cudaGraphCondTypeWhile;
         cp.conditional.size = 1;
-        e = cudaGraphAddNode(&nw, cg.graph, &n2, 1, &cp);
+        e = cudaGraphAddNode(&nw, cg.graph, &tail0, 1, &cp);
         if (e == cudaSuccess) {
-            cudaGraph_t body = cp.conditional.phGraph_out[0];
-            cudaGraphNode_t b0 = nullptr, b1 = nullptr, b2 = nullptr, b3 = nullptr;
-            e = add_kernel(body, nullptr, 3, &b0);
-            if (e == cudaSuccess) e = add_kernel(body, &b0, 0, &b1);
-            if (e == cudaSuccess) e = add_kernel(body, &b1, 1, &b2);
-            if (e == cudaSuccess) e = add_kernel(body, &b2, 2, &b3);
+            cudaGraphNode_t tail1 = nullptr;
+            e = add_chain(cp.conditional.phGraph_out[0], ITERATION, 6, &tail1);
         }
     }
     if (e == cudaSuccess) e = cudaGraphInstantiate(&cg.exec, cg.graph, 0);
@@ -1054,12 +1076,17 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     // ---- the descriptor (constant memory) and the control block ----
     climb_geometry G;
     G.n_items = n_items, G.n_cand = n_cand, G.groups = groups, G.threads = threads;
-    G.gi = (t->l_pad + 256 * 16 - 1) / (256 * 16);
-    G.up_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * std::max(1, 1024 / threads)));  // persistent; a function of the data set only (graph cache)
+    const int per_sm = std::max(1, 1024 / threads);
+    // persistent grids; functions of the data set only (one graph per data set)
+    G.up_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * per_sm));
+    G.delta_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * 2));
+    G.wl_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * per_sm));
+    G.scan_grid = (n_items + 255) / 256;
     const bool want_graph = !sharded && !(getenv("LZG_CLIMB_GRAPH") && atoi(getenv("LZG_CLIMB_GRAPH")) == 0);
     lzg_ctx::climb_graph* cg = want_graph ? climb_graph_for(ctx, G) : nullptr;
     lzg_pass_args A{};
     A.n_items = n_items, A.n_cand = n_cand, A.groups = groups, A.l_pad = t->l_pad, A.greedy = greedy;
+    A.n_nodes = n, A.threads = threads, A.ucap = o.ucap;
     A.start = t->d_start, A.end = t->d_end, A.wstart = t->d_start, A.wend = t->d_end;
     A.ustart = t->d_ustart, A.uend = t->d_uend;
     A.score = t->d_score, A.wscore = t->d_score;
@@ -1071,6 +1098,16 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     A.pair_v = reinterpret_cast<const int32_t*>(dc + o.pair_v);
     A.pcost = reinterpret_cast<int32_t*>(dc + o.pcost);
     A.tail = reinterpret_cast<int*>(dc + o.tail);
+    A.xctl = reinterpret_cast<int*>(dc + o.xctl);
+    A.dn_stamp = reinterpret_cast<int32_t*>(dc + o.dn_stamp);
+    A.up_stamp = reinterpret_cast<int32_t*>(dc + o.up_stamp);
+    A.rec_stamp = reinterpret_cast<int32_t*>(dc + o.rec_stamp);
+    A.part = reinterpret_cast<int32_t*>(dc + o.part);
+    A.uq = reinterpret_cast<int4*>(dc + o.uq);
+    A.uq_flag = reinterpret_cast<int32_t*>(dc + o.uq_flag);
+    A.wl = reinterpret_cast<int32_t*>(dc + o.wl);
+    A.deep_path = reinterpret_cast<int2*>(dc + o.deep_path);
+    A.deep_chg = reinterpret_cast<int32_t*>(dc + o.deep_chg);
     A.mlog = reinterpret_cast<int32_t*>(dc + o.mlog);
     A.queue = reinterpret_cast<unsigned long long*>(dc + o.queue);
     A.tlog = reinterpret_cast<unsigned long long*>(dc + o.tlog);
@@ -1078,7 +1115,7 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     A.log_cap = getenv("LZG_CLIMB_LOGCAP") ? std::max(1, std::min(LZG_CLIMB_LOG, atoi(getenv("LZG_CLIMB_LOGCAP")))) : LZG_CLIMB_LOG;  // tests shrink it to exercise the drain-and-continue path
     A.use_cond = cg ? 1 : 0, A.cond_handle = cg ? (unsigned long long)cg->handle : 0ull;
     LZG_CUDA(ctx, cudaMemcpyToSymbolAsync(c_pass, &A, sizeof(A), 0, cudaMemcpyHostToDevice, ctx->stream));
-    int32_t* h_ctl = ctx->h_pinned;  // 16 ints: the control block goes up and comes back through the head of the staging area
+    int32_t* h_ctl = ctx->h_pinned;  // the control block goes up and comes back through the head of the staging area
     for (int q = 0; q < LZG_CTL_INTS; q++) h_ctl[q] = 0;
     h_ctl[LZG_CTL_BEST] = -1;
     h_ctl[LZG_CTL_NPATHS] = n_paths;
@@ -1086,24 +1123,25 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     h_ctl[LZG_CTL_EPOCH] = t->df_epoch;
     h_ctl[LZG_CTL_CURRENT] = h_ctl[LZG_CTL_PARTROOT] = t->root_score;
     LZG_CUDA(ctx, cudaMemcpyAsync(t->d_cand, h_ctl, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyHostToDevice, ctx->stream));
-    LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand + LZG_CTL_INTS, 0, sizeof(int32_t) * (size_t)n_cand, ctx->stream));
     LZG_CUDA(ctx, cudaEventRecord(ctx->ev_stage, ctx->stream));
     // ---- run ----
     int32_t* h_log = reinterpret_cast<int32_t*>(blob + ((o.upload_bytes + 63) / 64 * 64));  // behind the upload area (read by the H2D above only)
     const bool debug = getenv("LZG_CLIMB_DEBUG") != nullptr;
     int total_moves = 0, stop = 0, passes = 0;
     long long replayed = 0;
-    bool first = true;
     t->up_valid = false;
     while (true) {
+        // every (re)start scores the whole neighbourhood once: queues empty, everything dirty
+        static const int32_t x_init[LZG_X_INTS] = {0, 0, 0, 0, 0, 1, 0, 0};
+        LZG_CUDA(ctx, cudaMemcpyAsync(A.xctl, x_init, sizeof(x_init), cudaMemcpyHostToDevice, ctx->stream));
+        const int passes_before = passes;
         if (cg) {
             LZG_CUDA(ctx, cudaGraphLaunch(cg->exec, ctx->stream));
-            ctx->launches += 3;  // pass 0; the iterations of the WHILE body are counted from the pass counter below
         } else {
-            rc = climb_enqueue_pass(ctx, G, false, comm, t);
+            rc = climb_enqueue(ctx, G, PASS0, 5, comm, t);
             int batch = 2;
             while (rc == LZG_OK) {
-                for (int q = 0; q < batch && rc == LZG_OK; q++) rc = climb_enqueue_pass(ctx, G, true, comm, t);
+                for (int q = 0; q < batch && rc == LZG_OK; q++) rc = climb_enqueue(ctx, G, ITERATION, 6, comm, t);
                 if (rc != LZG_OK) break;
                 LZG_CUDA(ctx, cudaMemcpyAsync(h_ctl, t->d_cand, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
                 LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1120,8 +1158,8 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
         LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         stop = h_ctl[LZG_CTL_STOP];
         const int logged = h_ctl[LZG_CTL_NLOGGED];
-        if (cg) ctx->launches += 4 * (int64_t)(h_ctl[LZG_CTL_PASSES] - passes - (first ? 1 : 0));
         passes = h_ctl[LZG_CTL_PASSES];
+        if (cg) ctx->launches += 5 + 6 * (int64_t)std::max(0, passes - passes_before - 1);  // kernels the graph ran: pass 0 + the iterations
         total_moves = h_ctl[LZG_CTL_NMOVES];
         if (debug) fprintf(stderr, "[lzg climb] %s: stop %d, moves %d (logged %d), passes %d, current %d, paths %d\n", cg ? "graph" : "batches", stop, total_moves, logged, passes, h_ctl[LZG_CTL_CURRENT], h_ctl[LZG_CTL_NPATHS]);
         for (int k = 0; k < logged; k++) {
@@ -1131,7 +1169,6 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
             if (moves && replayed < moves_cap) memcpy(moves + 5 * replayed, r, sizeof(int32_t) * 5);
             replayed++;
         }
-        first = false;
         if (stop == 3 && total_moves < max_moves) {  // only the log was full: drain it and go on
             LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand + LZG_CTL_STOP, 0, sizeof(int32_t), ctx->stream));
             LZG_CUDA(ctx, cudaMemsetAsync(t->d_cand + LZG_CTL_NLOGGED, 0, sizeof(int32_t), ctx->stream));
@@ -1139,8 +1176,8 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
         }
         break;
     }
-    t->df_epoch = h_ctl[LZG_CTL_EPOCH];
-    if (stop == 4 || stop == 0) return lzg_fail(ctx, LZG_ERR_STATE, stop == 4 ? "lzg_hill_climb: the UP pass waited for a path that was never queued" : "lzg_hill_climb: the climb did not terminate");
+    t->df_epoch = h_ctl[LZG_CTL_EPOCH] + 1;
+    if (stop == 4 || stop == 0) return lzg_fail(ctx, LZG_ERR_STATE, stop == 4 ? "lzg_hill_climb: a work queue waited for an entry that was never pushed" : "lzg_hill_climb: the climb did not terminate");
     if (replayed != total_moves) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_hill_climb: move log incomplete");
     {   // the path count the device maintained incrementally must match the final topology
         int heads = 0;
@@ -1160,7 +1197,7 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     }
     if (total_moves > 0) t->root_score = h_ctl[LZG_CTL_PARTROOT];
     t->last_cand_score = h_ctl[LZG_CTL_LAST];
-    t->up_valid = false;  // the UP rows are current only if the climb ended on a fruitless pass; the table-driven pass keeps its own books
+    t->up_valid = false;  // the table-driven pass of the stepwise calls keeps its own books
     R.n_moves = total_moves;
     R.n_passes = passes;
     R.reason = stop;

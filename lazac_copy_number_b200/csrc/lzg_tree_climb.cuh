@@ -1,32 +1,44 @@
 // lzg_tree_climb.cuh -- hill_climb (/root/reference/src/copy_number.cxx:375-417) with the host out of
-// the loop.  Included by lzg_tree.cu inside its anonymous namespace, after lzg_tree_nni.cuh.
+// the loop and with INCREMENTAL passes.  Included by lzg_tree.cu inside its anonymous namespace, after
+// lzg_tree_nni.cuh.
 //
 // One iteration of the reference's loop is greedy_nni (score the whole neighbourhood, pick) ->
-// nni + unvisit + small_rectilinear (accept).  Here that is four kernels that read their operands from
-// device memory only, so the host can queue iterations blindly -- or not at all: the whole climb
-// runs as ONE CUDA graph whose WHILE node repeats {k_apply2, k_up_df, k_nni_items, k_nni_argmin} until
-// the arg-min finds no improving candidate (cudaGraphSetConditional from the last kernel).
+// nni + unvisit + small_rectilinear (accept).  Here every kernel of an iteration reads its operands
+// from device memory only, so the whole climb runs as ONE CUDA graph whose WHILE node repeats the
+// iteration until the arg-min finds no improving candidate (cudaGraphSetConditional from the last
+// kernel); where a collective sits inside the iteration (positions sharded over GPUs) the host
+// queues the same kernels in batches.
 //
-// What makes it possible: inside one hill_climb the shuffled
+// (1) Static work items.  Inside one hill_climb the shuffled
 // edge order is fixed and an edge index stays with its child end (src/copy_number.cxx:381-388,
 // 401-406), and an NNI never changes which nodes are internal.  So the candidates of the internal
 // non-root node v are ALWAYS number cbase[v] (z = the child of v with the smaller id, the std::set
 // order of :340-346) and cbase[v] + 1: the work items never move, an accepted move rewrites five of
-// them (those of u, v, w, z and y) and nothing is packed or validated on the host between passes.
+// them (those of u, v, w, z and y), nothing is packed or validated on the host between passes.
 //
-//  * k_up_df   UP intervals by heavy-path walkers, DATAFLOW scheduled: a path's head is pushed to a
-//              per-chunk-group ready queue by the walker that publishes the UP row it hangs off
-//              (atomicAdd on the tail, st.release of epoch << 32 | node); persistent CTAs draw tickets
-//              (slot, group) and wait for queue entry `slot`.  An entry is always pushed while a
-//              smaller ticket is processed, and tickets are drawn by running CTAs in order, so the
-//              waits cannot deadlock.  The walk follows the node4 records (heavy child first) two
-//              nodes ahead; there are no host-built path tables, so an accepted move only has to
-//              patch two node4 records and the path count.
-//  * k_apply2  accepts the winner that k_nni_argmin left in ctl[BEST] (or an explicit move): derives
-//              (u, w, v, z) from the topology arrays, rewrites the intervals along v .. root following
-//              the (parent, sibling) table two steps ahead, and its last CTA turns the per-node
-//              costs into cumulative scores, patches topology, node4 records, path count, the five
-//              item records, logs the move and applies hill_climb's stopping rule (:411-412).
+// (2) Incremental passes.  An accepted move changes very little: the DOWN intervals of some nodes on
+// the path v .. root, and through them the UP intervals of a few subtrees hanging off that path
+// (measured on cfg4/cfg5-like inputs: ~1 % of the UP rows and 2-4 % of the work items change per
+// move).  Every candidate score is a sum over positions of terms that depend on five rows only, so:
+//  * k_apply2 compares every row it rewrites with the old one and stamps the chunk groups that
+//    really changed (dn_stamp), and seeds the UP queue: the sibling of every changed path node, plus
+//    v and z whose place in the tree changed (UP of the path nodes themselves cannot change: their
+//    inputs are outside the path);
+//  * k_up_delta recomputes exactly the queued UP rows, top-down: a row that comes out different is
+//    stamped (up_stamp) and its internal children are queued -- the heavy child continues in
+//    registers, the light one goes through the queue; a row that comes out equal ends the wave;
+//  * k_dirty_scan lists the (item, chunk group) pairs that read a stamped row or a rewritten record,
+//    k_items_wl re-scores only those and keeps their position sums in `part`;
+//  * k_cand_assemble adds the cumulative-score terms (they change along the whole path) to the
+//    position sums of EVERY item -- one thread per item -- and k_nni_argmin picks as before.
+// The first pass of a climb runs the full UP pass (k_up_df) and marks everything dirty.  Scores are
+// identical to a full pass by construction: an item is re-scored whenever one of its inputs changed.
+//
+//  * k_up_df   the full UP pass: heavy-path walkers, DATAFLOW scheduled -- a path's head is pushed to a
+//              per-chunk-group ready queue by the walker that publishes the UP row it hangs off;
+//              persistent CTAs draw tickets (slot, group) and wait for queue entry `slot`.  An entry
+//              is always pushed while a smaller ticket is processed, and tickets are drawn by
+//              running CTAs in order, so the waits cannot deadlock.  No host-built path tables.
 #pragma once
 
 __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
@@ -50,8 +62,11 @@ __device__ __forceinline__ int4 make_node4_dev(const int4* nd, int c0, int c1, i
 __device__ __forceinline__ int heads_below(int p, const int4& rec) {
     return p == 0 ? (rec.z & 1) + ((rec.z >> 1) & 1) : ((rec.z & 3) == 3 ? 1 : 0);
 }
+__device__ __forceinline__ bool differs(const uint4& a, const uint4& b) {
+    return ((a.x ^ b.x) | (a.y ^ b.y) | (a.z ^ b.z) | (a.w ^ b.w)) != 0;
+}
 
-// ---- UP pass, dataflow -----------------------------------------------------------------------------
+// ---- full UP pass, dataflow --------------------------------------------------------------------------
 // One heavy path x one chunk group.  head = first node of the path; its parent's UP row is published.
 __device__ __forceinline__ void up_walk_df(const lzg_pass_args& A, int head, int g, int tid, int epoch) {
     const int chunk = g * blockDim.x + tid;
@@ -115,17 +130,15 @@ __device__ __forceinline__ void up_walk_df(const lzg_pass_args& A, int head, int
     }
 }
 
-// Persistent CTAs.  Self-resetting: the last CTA to leave zeroes the ticket and the tails and advances
-// the epoch, so the next pass needs no memset.  A wait that lasts implausibly long (a path count that
-// does not match the node4 records would leave a ticket without a producer) raises STOP = 4 instead of
-// hanging the GPU.
-template <bool DESC>
+// Persistent CTAs.  Self-resetting: the last CTA to leave zeroes the ticket and the tails, so the next
+// full pass needs no memset.  A wait that lasts implausibly long (a path count that does not match the
+// node4 records would leave a ticket without a producer) raises STOP = 4 instead of hanging the GPU.
 __global__ void __launch_bounds__(256)
-k_up_df(const lzg_pass_args A_) {
-    const lzg_pass_args& A = DESC ? c_pass : A_;
+k_up_df() {
+    const lzg_pass_args& A = c_pass;
     __shared__ int s_ticket, s_head;
     const int tid = threadIdx.x;
-    if (DESC && __ldcg(A.ctl + LZG_CTL_STOP)) return;
+    if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
     const int epoch = __ldcg(A.ctl + LZG_CTL_EPOCH);
     const int total = __ldcg(A.ctl + LZG_CTL_NPATHS) * A.groups;
     const int4 r0 = __ldg(A.node4);
@@ -167,89 +180,138 @@ k_up_df(const lzg_pass_args A_) {
             A.ctl[LZG_CTL_TICKET] = 0;
             A.ctl[LZG_CTL_UPDONE] = 0;
             for (int g = 0; g < A.groups; g++) A.tail[g] = 0;
-            A.ctl[LZG_CTL_EPOCH] = epoch + 1;
         }
     }
 }
 
+// ---- the queue of UP rows to recompute (incremental pass) -------------------------------------------------
+// Pushed by k_apply2 (before k_up_delta starts) and by the walkers of k_up_delta (while it runs: payload,
+// fence, flag).
+__device__ __forceinline__ void uq_push(const lzg_pass_args& A, int stamp, int node_and_flags, int g, int parent, int sib) {
+    const int pos = atomicAdd(A.xctl + LZG_X_UQ_PUSHED, 1);
+    if (pos < A.ucap) {
+        A.uq[pos] = make_int4(node_and_flags, g, parent, sib);
+        __threadfence();
+        st_release(A.uq_flag + pos, stamp);
+    }
+}
+
 // ---- accept a move -----------------------------------------------------------------------------------
-#define LZG_PATH_CAP 1024  // steps of the path kept in shared memory for the parallel score update; longer paths finish sequentially
+#define LZG_PATH_CAP 1024  // steps of the path kept in shared memory; longer paths continue in global scratch
 
-struct lzg_move {
-    int u, w, v, z;
-};
-
-// CLIMB: the move is the winner k_nni_argmin left in ctl[BEST]; otherwise `m` (validated by the host).
-template <bool CLIMB>
+// The move is the winner k_nni_argmin left in ctl[BEST].  One CTA per chunk group.
 __global__ void __launch_bounds__(256)
-k_apply2(const lzg_pass_args A_, const lzg_move m) {
-    const lzg_pass_args& A = CLIMB ? c_pass : A_;
+k_apply2() {
+    const lzg_pass_args& A = c_pass;
     __shared__ int2 s_path[LZG_PATH_CAP];  // (node written, sibling merged) per step
     __shared__ int32_t s_term[LZG_PATH_CAP];
+    __shared__ int32_t s_chg[LZG_PATH_CAP];
     __shared__ int s_is_last;
-    const int tid = threadIdx.x;
-    int u, w, v, z, y;
-    if (CLIMB) {
-        if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
-        const int best = __ldcg(A.ctl + LZG_CTL_BEST);
-        v = __ldg(A.pair_v + (best >> 1));
-        const int a0 = A.child0[v], a1 = A.child1[v];
-        z = (best & 1) ? a1 : a0;  // candidate cbase[v] swaps the child with the smaller id, cbase[v] + 1 the other
-        y = (best & 1) ? a0 : a1;
-        const int2 e = A.up[v];
-        u = e.x;
-        w = e.y;
-    } else {
-        u = m.u, w = m.w, v = m.v, z = m.z;
-        y = A.child0[v] == z ? A.child1[v] : A.child0[v];
-    }
-    const int chunk = blockIdx.x * blockDim.x + tid;
+    const int tid = threadIdx.x, g = blockIdx.x;
+    if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
+    const int stamp = __ldcg(A.ctl + LZG_CTL_EPOCH);
+    const int best = __ldcg(A.ctl + LZG_CTL_BEST);
+    const int v = __ldg(A.pair_v + (best >> 1));
+    const int a0 = A.child0[v], a1 = A.child1[v];
+    const int z = (best & 1) ? a1 : a0;  // candidate cbase[v] swaps the child with the smaller id, cbase[v] + 1 the other
+    const int y = (best & 1) ? a0 : a1;
+    const int2 uw = A.up[v];
+    const int u = uw.x, w = uw.y;
+    const int chunk = g * blockDim.x + tid;
     const bool active = chunk * 16 < A.l_pad;
     const size_t off = (size_t)chunk * 16, lp = (size_t)A.l_pad;
     const uint4 z4 = make_uint4(0, 0, 0, 0);
+    int2* const deep_path = A.deep_path + (size_t)g * A.n_nodes;
+    int32_t* const deep_chg = A.deep_chg + (size_t)g * A.n_nodes;
     iv16 acc;
     uint32_t os[8], oe[8];
     // (parent, sibling) two steps ahead of the merge; the entries from u upwards are not touched by the move
     int2 e1 = A.up[u];
     int2 e2 = e1.x >= 0 ? A.up[e1.x] : make_int2(-1, -1);
     uint4 ys = z4, ye = z4, zs = z4, ze = z4, q1s = z4, q1e = z4, q2s = z4, q2e = z4;
+    uint4 ovs = z4, ove = z4, ous = z4, oue = z4, o1s = z4, o1e = z4, o2s = z4, o2e = z4;  // the rows about to be overwritten
     if (active) {
         widen(ldg16(A.start, w * lp + off), acc.s);
         widen(ldg16(A.end, w * lp + off), acc.e);
         ys = ldg16(A.start, y * lp + off), ye = ldg16(A.end, y * lp + off);
         zs = ldg16(A.start, z * lp + off), ze = ldg16(A.end, z * lp + off);
-        if (e1.x >= 0) q1s = ldg16(A.start, e1.y * lp + off), q1e = ldg16(A.end, e1.y * lp + off);
+        ovs = ldg16(A.start, v * lp + off), ove = ldg16(A.end, v * lp + off);
+        ous = ldg16(A.start, u * lp + off), oue = ldg16(A.end, u * lp + off);
+        if (e1.x >= 0) {
+            q1s = ldg16(A.start, e1.y * lp + off), q1e = ldg16(A.end, e1.y * lp + off);
+            o1s = ldg16(A.start, e1.x * lp + off), o1e = ldg16(A.end, e1.x * lp + off);
+        }
     }
+    for (int q = tid; q < LZG_PATH_CAP; q += blockDim.x) s_term[q] = 0, s_chg[q] = 0;
+    __syncthreads();
     int k = 0;
-    auto step = [&](int node, int other, const uint4& rs, const uint4& re) {
+    // step k: node = merge(running interval, other); costs and "changed" flags are fire-and-forget
+    // shared-memory reductions (no shuffle chain in the walk), read back once the walk is over
+    auto step = [&](int node, int other, const uint4& rs, const uint4& re, const uint4& olds, const uint4& olde) {
         uint32_t c = 0;
+        bool chg = false;
         if (active) {
             widen(rs, os);
             widen(re, oe);
             c = merge16(acc, os, oe);
-            *reinterpret_cast<uint4*>(A.wstart + node * lp + off) = narrow(acc.s);
-            *reinterpret_cast<uint4*>(A.wend + node * lp + off) = narrow(acc.e);
+            const uint4 ns = narrow(acc.s), ne = narrow(acc.e);
+            chg = differs(ns, olds) || differs(ne, olde);
+            *reinterpret_cast<uint4*>(A.wstart + node * lp + off) = ns;
+            *reinterpret_cast<uint4*>(A.wend + node * lp + off) = ne;
         }
-        c = warp_sum(c);
-        if ((tid & 31) == 0 && c) atomicAdd(A.pcost + node, (int32_t)c);
-        if (tid == 0 && k < LZG_PATH_CAP) s_path[k] = make_int2(node, other);
+        if (k < LZG_PATH_CAP) {
+            if (c) atomicAdd(&s_term[k], (int32_t)c);
+            if (chg) s_chg[k] = 1;
+            if (tid == 0) s_path[k] = make_int2(node, other);
+        } else {
+            c = warp_sum(c);
+            if ((tid & 31) == 0 && c) atomicAdd(A.pcost + node, (int32_t)c);
+            if (chg) deep_chg[k] = 1;
+            if (tid == 0) deep_path[k] = make_int2(node, other);
+        }
         k++;
     };
-    step(v, y, ys, ye);  // the new v = merge(w, y)
-    step(u, z, zs, ze);  // the new u = merge(v, z)
+    step(v, y, ys, ye, ovs, ove);  // the new v = merge(w, y)
+    step(u, z, zs, ze, ous, oue);  // the new u = merge(v, z)
     while (e1.x >= 0) {
         int2 e3 = make_int2(-1, -1);
         if (e2.x >= 0) {
             e3 = A.up[e2.x];
-            if (active) q2s = ldg16(A.start, e2.y * lp + off), q2e = ldg16(A.end, e2.y * lp + off);
+            if (active) {
+                q2s = ldg16(A.start, e2.y * lp + off), q2e = ldg16(A.end, e2.y * lp + off);
+                o2s = ldg16(A.start, e2.x * lp + off), o2e = ldg16(A.end, e2.x * lp + off);
+            }
         }
-        step(e1.x, e1.y, q1s, q1e);
+        step(e1.x, e1.y, q1s, q1e, o1s, o1e);
         e1 = e2;
         e2 = e3;
-        q1s = q2s;
-        q1e = q2e;
+        q1s = q2s, q1e = q2e;
+        o1s = o2s, o1e = o2e;
     }
     const int n_steps = k;
+    __threadfence();  // the deep-path records of this CTA, read back below by other threads of it
+    __syncthreads();
+    auto path_at = [&](int q) -> int2 { return q < LZG_PATH_CAP ? s_path[q] : deep_path[q]; };
+    // this chunk group's share: costs, stamps of the rows that changed, UP rows to recompute
+    for (int q = tid; q < n_steps; q += blockDim.x) {
+        const bool chg = q < LZG_PATH_CAP ? s_chg[q] != 0 : __ldcg(deep_chg + q) != 0;
+        if (q >= LZG_PATH_CAP) deep_chg[q] = 0;
+        if (q < LZG_PATH_CAP && s_term[q]) atomicAdd(A.pcost + s_path[q].x, s_term[q]);
+        if (!chg) continue;
+        const int2 pq = path_at(q);
+        A.dn_stamp[(size_t)pq.x * A.groups + g] = stamp;
+        // DOWN(node_q) is an input of UP(sibling of node_q) = UP(other_(q+1)); node_0 = v: its sibling z is queued anyway
+        if (q >= 1 && q + 1 < n_steps) {
+            const int2 nx = path_at(q + 1);
+            if (__ldg(A.node4 + nx.y).x >= 0) uq_push(A, stamp, nx.y, g, nx.x, pq.x);
+        }
+    }
+    if (tid == 0) {
+        // v hangs under u beside z now, and its children w, y got a new parent / sibling: their UP rows are
+        // recomputed whether or not UP(v) comes out different
+        uq_push(A, stamp, v | LZG_UQ_FORCE, g, u, z);
+        if (__ldg(A.node4 + z).x >= 0) uq_push(A, stamp, z, g, u, v);
+    }
     __threadfence();
     __syncthreads();
     if (tid == 0) s_is_last = atomicAdd(A.ctl + LZG_CTL_DONE, 1) == (int)gridDim.x - 1;
@@ -270,12 +332,11 @@ k_apply2(const lzg_pass_args A_, const lzg_move m) {
         s += s_term[q];
         A.wscore[s_path[q].x] = s;
     }
-    for (int q = n_listed, b = s_path[LZG_PATH_CAP - 1].x; q < n_steps; q++) {  // beyond the shared list: follow the table
-        const int2 ps = A.up[b];
-        s += __ldcg(A.pcost + ps.x) + A.wscore[ps.y];
-        A.pcost[ps.x] = 0;
-        A.wscore[ps.x] = s;
-        b = ps.x;
+    for (int q = n_listed; q < n_steps; q++) {  // beyond the shared list
+        const int2 pq = deep_path[q];
+        s += __ldcg(A.pcost + pq.x) + A.wscore[pq.y];
+        A.pcost[pq.x] = 0;
+        A.wscore[pq.x] = s;
     }
     // nni(t, u, w, v, z), src/copy_number.cxx:279-284
     A.child0[v] = min(w, y), A.child1[v] = max(w, y);
@@ -284,7 +345,7 @@ k_apply2(const lzg_pass_args A_, const lzg_move m) {
     A.up[y] = make_int2(v, w);
     A.up[v] = make_int2(u, z);
     A.up[z] = make_int2(u, v);
-    if (A.node4) {
+    {
         // heavy / light roles: only the subtree count of v changes (u keeps its node set)
         const int4 nu = A.node4[u], nv = A.node4[v];
         const int before = heads_below(u, nu) + heads_below(v, nv);
@@ -296,7 +357,7 @@ k_apply2(const lzg_pass_args A_, const lzg_move m) {
         A.node4[u] = nu2;
         A.ctl[LZG_CTL_NPATHS] += heads_below(u, nu2) + heads_below(v, nv2) - before;
     }
-    if (A.witems) {  // the items of v, w, z, y (parent, sibling or children changed) and of u (children changed)
+    {   // the items of v, w, z, y (parent, sibling or children changed) and of u (children changed)
         const int xs[5] = {v, w, z, y, u};
 #pragma unroll
         for (int q = 0; q < 5; q++) {
@@ -306,27 +367,206 @@ k_apply2(const lzg_pass_args A_, const lzg_move m) {
             const int2 ps = A.up[x];
             A.witems[2 * slot] = make_int4(ps.x, ps.y, x, A.child0[x]);
             A.witems[2 * slot + 1] = make_int4(A.child1[x], cb, cb + 1, 0);
+            A.rec_stamp[slot] = stamp;
         }
     }
     A.ctl[LZG_CTL_DONE] = 0;
     A.ctl[LZG_CTL_PARTROOT] = s;
-    if (CLIMB) {
-        // under position sharding s is this rank's part; the new global score is the winner's reduced score
-        const int32_t new_score = A.sharded ? A.ctl[LZG_CTL_SCORE] : s;
-        const int nm = A.ctl[LZG_CTL_NMOVES];
-        const int slot = A.ctl[LZG_CTL_NLOGGED];
-        if (slot < A.log_cap) {
-            int32_t* r = A.mlog + 5 * (size_t)slot;
-            r[0] = u, r[1] = w, r[2] = v, r[3] = z, r[4] = new_score;
-            A.ctl[LZG_CTL_NLOGGED] = slot + 1;
-        }
-        A.ctl[LZG_CTL_NMOVES] = nm + 1;
-        int stop = 0;
-        if (A.ctl[LZG_CTL_CURRENT] <= new_score) stop = 2;  // hill_climb :412
-        else A.ctl[LZG_CTL_CURRENT] = new_score;
-        if (!stop && (nm + 1 >= A.ctl[LZG_CTL_MAXMOVES] || slot + 1 >= A.log_cap)) stop = 3;
-        if (stop) A.ctl[LZG_CTL_STOP] = stop;
-    } else {
-        A.ctl[LZG_CTL_SCORE] = s;
+    // under position sharding s is this rank's part; the new global score is the winner's reduced score
+    const int32_t new_score = A.sharded ? A.ctl[LZG_CTL_SCORE] : s;
+    const int nm = A.ctl[LZG_CTL_NMOVES];
+    const int slot = A.ctl[LZG_CTL_NLOGGED];
+    if (slot < A.log_cap) {
+        int32_t* r = A.mlog + 5 * (size_t)slot;
+        r[0] = u, r[1] = w, r[2] = v, r[3] = z, r[4] = new_score;
+        A.ctl[LZG_CTL_NLOGGED] = slot + 1;
     }
+    A.ctl[LZG_CTL_NMOVES] = nm + 1;
+    int stop = 0;
+    if (A.ctl[LZG_CTL_CURRENT] <= new_score) stop = 2;  // hill_climb :412
+    else A.ctl[LZG_CTL_CURRENT] = new_score;
+    if (!stop && (nm + 1 >= A.ctl[LZG_CTL_MAXMOVES] || slot + 1 >= A.log_cap)) stop = 3;
+    if (stop) A.ctl[LZG_CTL_STOP] = stop;
+}
+
+// ---- incremental UP pass ---------------------------------------------------------------------------------
+// Persistent CTAs drain the queue.  A unit = recompute UP(x) for one chunk group from UP(parent) and
+// DOWN(sibling); if the row comes out different (or the unit is forced) its internal children follow: the
+// heavy one in registers, the light one through the queue.  A CTA leaves when every pushed unit is done
+// (done is read before pushed: pushed only grows and done <= pushed, so equality means nothing is in flight).
+__global__ void __launch_bounds__(256)
+k_up_delta() {
+    const lzg_pass_args& A = c_pass;
+    __shared__ int s_unit;
+    const int tid = threadIdx.x;
+    if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
+    const int stamp = __ldcg(A.ctl + LZG_CTL_EPOCH);
+    const size_t lp = (size_t)A.l_pad;
+    for (;;) {
+        if (tid == 0) {
+            const int t = atomicAdd(A.xctl + LZG_X_UQ_TICKET, 1);
+            int got = -1;
+            long long spins = 0;
+            for (;;) {
+                if (t < A.ucap && ld_acquire(A.uq_flag + t) == stamp) {
+                    got = t;
+                    break;
+                }
+                const int done = __ldcg(A.xctl + LZG_X_UQ_DONE);
+                const int pushed = __ldcg(A.xctl + LZG_X_UQ_PUSHED);
+                if (done == pushed && t >= pushed) break;
+                if (++spins > (1ll << 24)) {
+                    A.ctl[LZG_CTL_STOP] = 4;
+                    break;
+                }
+                __nanosleep(20);
+            }
+            s_unit = got;
+        }
+        __syncthreads();
+        const int unit = s_unit;
+        if (unit < 0) break;
+        const int4 e = __ldcg(A.uq + unit);
+        int x = e.x & ~LZG_UQ_FORCE;
+        bool force = (e.x & LZG_UQ_FORCE) != 0;
+        const int g = e.y, p = e.z, sib = e.w;
+        const int chunk = g * blockDim.x + tid;
+        const bool active = chunk * 16 < A.l_pad;
+        const size_t off = (size_t)chunk * 16;
+        iv16 acc;
+        uint32_t os[8], oe[8];
+        if (active) {
+            const uint4 ss = ldg16(A.start, sib * lp + off), se = ldg16(A.end, sib * lp + off);
+            if (p != 0) {
+                widen(ldcg16(A.ustart, p * lp + off), acc.s);
+                widen(ldcg16(A.uend, p * lp + off), acc.e);
+                widen(ss, os);
+                widen(se, oe);
+                merge16(acc, os, oe);
+            } else {
+                widen(ss, acc.s);
+                widen(se, acc.e);
+            }
+        }
+        for (;;) {
+            const int4 nx = __ldg(A.node4 + x);
+            bool chg = false;
+            uint4 ns = make_uint4(0, 0, 0, 0), ne = ns;
+            if (active) {
+                ns = narrow(acc.s), ne = narrow(acc.e);
+                chg = differs(ns, ldcg16(A.ustart, x * lp + off)) || differs(ne, ldcg16(A.uend, x * lp + off));
+            }
+            const int any = __syncthreads_or(chg);
+            if (any) {
+                if (active) {
+                    *reinterpret_cast<uint4*>(A.ustart + x * lp + off) = ns;
+                    *reinterpret_cast<uint4*>(A.uend + x * lp + off) = ne;
+                }
+                if (tid == 0) A.up_stamp[(size_t)x * A.groups + g] = stamp;
+            }
+            if (!any && !force) break;
+            if (nx.z & 2) {  // light child internal: queue it (it reads UP(x) from memory)
+                __syncthreads();
+                if (tid == 0) uq_push(A, stamp, nx.y, g, x, nx.x);
+            }
+            if (!(nx.z & 1)) break;
+            if (active) {  // continue with the heavy child: UP(heavy) = merge(UP(x), DOWN(light))
+                widen(ldg16(A.start, nx.y * lp + off), os);
+                widen(ldg16(A.end, nx.y * lp + off), oe);
+                merge16(acc, os, oe);
+            }
+            x = nx.x;
+            force = false;  // a forced unit (v) recomputes BOTH children whatever came out for v; below them the wave decides
+        }
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            atomicAdd(A.xctl + LZG_X_UQ_DONE, 1);
+        }
+    }
+}
+
+// ---- which items read something that changed ------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_dirty_scan() {
+    const lzg_pass_args& A = c_pass;
+    if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
+    const int stamp = __ldcg(A.ctl + LZG_CTL_EPOCH);
+    const bool all = __ldcg(A.xctl + LZG_X_FULL) != 0;  // first pass of a climb: everything
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot == 0) A.xctl[LZG_X_UQ_PUSHED] = 0, A.xctl[LZG_X_UQ_DONE] = 0, A.xctl[LZG_X_UQ_TICKET] = 0;  // k_up_delta is done
+    if (slot >= A.n_items) return;
+    const int4 i0 = __ldg(A.items + 2 * slot), i1 = __ldg(A.items + 2 * slot + 1);
+    const int u = i0.x, w = i0.y, a = i0.w, b = i1.x;
+    const bool rec = __ldcg(A.rec_stamp + slot) == stamp;
+    const int G = A.groups;
+    for (int g = 0; g < G; g++) {
+        bool d = all || rec || __ldcg(A.dn_stamp + (size_t)w * G + g) == stamp || __ldcg(A.dn_stamp + (size_t)a * G + g) == stamp ||
+                 __ldcg(A.dn_stamp + (size_t)b * G + g) == stamp;
+        if (!d && u) d = __ldcg(A.dn_stamp + (size_t)u * G + g) == stamp || __ldcg(A.up_stamp + (size_t)u * G + g) == stamp;
+        if (d) {
+            reinterpret_cast<int2*>(A.part)[(size_t)slot * G + g] = make_int2(0, 0);
+            A.wl[atomicAdd(A.xctl + LZG_X_WL_COUNT, 1)] = slot * G + g;
+        }
+    }
+}
+
+// ---- re-score the listed (item, chunk group) pairs ----------------------------------------------------------------
+// Persistent CTAs of `threads` threads (the chunk-group width of the UP / apply kernels).  Position sums
+// only: the cumulative-score terms are added per pass by k_cand_assemble.
+__global__ void __launch_bounds__(256, 4)
+k_items_wl() {
+    const lzg_pass_args& A = c_pass;
+    __shared__ int s_unit;
+    const int tid = threadIdx.x;
+    if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
+    const int count = __ldcg(A.xctl + LZG_X_WL_COUNT);
+    for (;;) {
+        if (tid == 0) s_unit = atomicAdd(A.xctl + LZG_X_WL_TICKET, 1);
+        __syncthreads();
+        const int t = s_unit;
+        if (t >= count) break;
+        const int e = __ldcg(A.wl + t);
+        const int slot = e / A.groups, g = e % A.groups;
+        const int4 i0 = __ldg(A.items + 2 * slot), i1 = __ldg(A.items + 2 * slot + 1);
+        const int u = i0.x, w = i0.y, a = i0.w, b = i1.x;
+        const size_t off = ((size_t)g * blockDim.x + tid) * 16;
+        int32_t pA = 0, pB = 0;
+        if (off < (size_t)A.l_pad) {
+            if (u) score_pair<16, true>(A, u, w, a, b, off, pA, pB);
+            else score_pair<16, false>(A, u, w, a, b, off, pA, pB);
+        }
+        pA = warp_sum_i(pA);
+        pB = warp_sum_i(pB);
+        if ((tid & 31) == 0) {
+            int32_t* cell = A.part + 2 * ((size_t)slot * A.groups + g);
+            if (pA) atomicAdd(cell, pA);
+            if (pB) atomicAdd(cell + 1, pB);
+        }
+        __syncthreads();  // s_unit is rewritten by the next round
+    }
+}
+
+// ---- every candidate's score = its position sums + the cumulative-score terms -------------------------------------
+__global__ void __launch_bounds__(256)
+k_cand_assemble() {
+    const lzg_pass_args& A = c_pass;
+    if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot == 0) {
+        A.ctl[LZG_CTL_ROOT] = A.score[0];
+        A.xctl[LZG_X_WL_COUNT] = 0, A.xctl[LZG_X_WL_TICKET] = 0, A.xctl[LZG_X_FULL] = 0;  // k_items_wl is done
+    }
+    if (slot >= A.n_items) return;
+    const int4 i0 = __ldg(A.items + 2 * slot), i1 = __ldg(A.items + 2 * slot + 1);
+    const int u = i0.x, w = i0.y, a = i0.w, b = i1.x, ia = i1.y, ib = i1.z;
+    int32_t pA = 0, pB = 0;
+    const int2* cell = reinterpret_cast<const int2*>(A.part) + (size_t)slot * A.groups;
+    for (int g = 0; g < A.groups; g++) {
+        const int2 c = __ldcg(cell + g);
+        pA += c.x, pB += c.y;
+    }
+    const int32_t base = A.score[w] + A.score[a] + A.score[b] + (u ? A.score[0] - A.score[u] : 0);
+    A.cand_score[ia] = pA + base;
+    A.cand_score[ib] = pB + base;
 }

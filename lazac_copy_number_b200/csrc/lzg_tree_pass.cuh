@@ -59,6 +59,16 @@ struct lzg_pass_args {
     int* tail;            // [groups] heads pushed so far
     int32_t* mlog;        // [log_cap][5] accepted moves (u, w, v, z, new score)
     unsigned long long* tlog;  // [log_cap + 2] %globaltimer at the end of every pass
+    int* xctl;            // counters of the incremental pass (LZG_X_*)
+    int32_t *dn_stamp, *up_stamp;  // [n_nodes][groups] iteration in which a chunk group of a DOWN / UP row last changed value
+    int32_t* rec_stamp;   // [n_items] iteration in which an item record was rewritten
+    int32_t* part;        // [n_items][groups][2] position sums (candidate z = a, z = b; net of c0) of one chunk group of an item
+    int4* uq;             // [ucap] UP rows to recompute: {node | LZG_UQ_FORCE, chunk group, parent, sibling}
+    int32_t* uq_flag;     // [ucap] stamp of the iteration the entry belongs to
+    int32_t* wl;          // [n_items * groups] dirty (item slot, chunk group) pairs: slot * groups + group
+    int2* deep_path;      // [groups][n_nodes] (node, sibling) per step of a path longer than LZG_PATH_CAP
+    int32_t* deep_chg;    // [groups][n_nodes] "row changed" per such step; all zero between launches
+    int n_nodes, ucap, threads;
     int qcap, log_cap, sharded, use_cond;
     unsigned long long cond_handle;  // cudaGraphConditionalHandle of the WHILE node the climb runs in
 };
@@ -77,6 +87,9 @@ enum {
     LZG_CTL_EPOCH = 11, LZG_CTL_UPDONE = 12, LZG_CTL_PARTROOT = 13, LZG_CTL_NLOGGED = 14,
     LZG_CTL_ROOT = 15, LZG_CTL_INTS = 16
 };
+// xctl: the work queues of the incremental pass
+enum { LZG_X_UQ_PUSHED = 0, LZG_X_UQ_DONE = 1, LZG_X_UQ_TICKET = 2, LZG_X_WL_COUNT = 3, LZG_X_WL_TICKET = 4, LZG_X_FULL = 5, LZG_X_INTS = 8 };
+enum { LZG_UQ_FORCE = 1 << 30 };
 
 // order[].y: the sibling, and LZG_ORDER_PUBLISH if another path's head hangs off the node -- only
 // those UP rows are waited for across walkers, only they pay the release fence.
@@ -255,16 +268,12 @@ __device__ __forceinline__ void score_pair(const lzg_pass_args& A, int u, int w,
     pB = (int32_t)((cB & 0xffffu) + (cB >> 16)) - z;
 }
 
-// DESC: the arguments come from constant memory (c_pass) and the launch is one step of a device-driven
-// climb: nothing to do once the climb has stopped.
-template <int CPT, bool DESC>
+template <int CPT>
 __global__ void __launch_bounds__(256, 4)  // 64 registers: four CTAs per SM (three at 72-80 registers were 10 % slower, five spill)
-k_nni_items(const lzg_pass_args A_, int groups_i) {
-    const lzg_pass_args& A = DESC ? c_pass : A_;
+k_nni_items(const lzg_pass_args A, int groups_i) {
     const int tid = threadIdx.x;
     const int it = blockIdx.x / groups_i, g = blockIdx.x % groups_i;
     const int4 i0 = __ldg(A.items + 2 * it), i1 = __ldg(A.items + 2 * it + 1);
-    if (DESC && __ldcg(A.ctl + LZG_CTL_STOP)) return;
     const int u = i0.x, w = i0.y, a = i0.w, b = i1.x, ia = i1.y, ib = i1.z;
     const size_t off = ((size_t)g * 256 + tid) * CPT;
     int32_t base = 0;
@@ -283,21 +292,11 @@ k_nni_items(const lzg_pass_args A_, int groups_i) {
     }
 }
 
-// CLIMB: one step of a device-driven climb (arguments from c_pass).  The scores are zeroed as they are read
-// (the next pass accumulates into them again), the pass is counted and time-stamped, a pass that finds
-// nothing stops the climb, and inside the WHILE graph the loop condition is set here -- the last kernel
-// of every iteration.
 template <bool CLIMB>
-__global__ void __launch_bounds__(1024)
-k_nni_argmin(const lzg_pass_args A_) {
-    const lzg_pass_args& A = CLIMB ? c_pass : A_;
+__device__ __forceinline__ void argmin_body(const lzg_pass_args& A) {
     __shared__ unsigned long long s_key[32];
     __shared__ int32_t s_last_score;
     const int tid = threadIdx.x;
-    if (CLIMB && __ldcg(A.ctl + LZG_CTL_STOP)) {
-        if (A.use_cond && tid == 0) cudaGraphSetConditional(A.cond_handle, 0);
-        return;
-    }
     const int32_t root = __ldcg(A.ctl + LZG_CTL_ROOT);  // written by k_nni_items; summed over the ranks when positions are sharded
     unsigned long long best = ~0ull;
     // non-greedy: min (score, index); greedy: min (index) with the score riding in the low half
@@ -307,10 +306,9 @@ k_nni_argmin(const lzg_pass_args A_) {
     // cand_score is 64-byte aligned (d_cand + LZG_CTL_INTS): four candidates per load, all loads of a
     // thread independent
     const int n4 = A.n_cand >> 2;
-    int4* sc4 = reinterpret_cast<int4*>(A.cand_score);
+    const int4* sc4 = reinterpret_cast<const int4*>(A.cand_score);
     for (int q = tid; q < n4; q += blockDim.x) {
         const int4 v = __ldcg(sc4 + q);
-        if (CLIMB) sc4[q] = make_int4(0, 0, 0, 0);
         const int32_t sc[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int e = 0; e < 4; e++) {
@@ -322,7 +320,6 @@ k_nni_argmin(const lzg_pass_args A_) {
     }
     for (int i = 4 * n4 + tid; i < A.n_cand; i += blockDim.x) {
         const int32_t sc = __ldcg(A.cand_score + i);
-        if (CLIMB) A.cand_score[i] = 0;
         const unsigned long long key = key_of(sc, i);
         best = (sc < root && key < best) ? key : best;
         if (i == A.n_cand - 1) s_last_score = sc;
@@ -335,7 +332,7 @@ k_nni_argmin(const lzg_pass_args A_) {
     if ((tid & 31) == 0) s_key[tid >> 5] = best;
     __syncthreads();
     if (tid == 0) {
-        for (int k = 1; k < 32; k++) best = s_key[k] < best ? s_key[k] : best;
+        for (int k = 1; k < (int)(blockDim.x >> 5); k++) best = s_key[k] < best ? s_key[k] : best;
         A.ctl[LZG_CTL_LAST] = s_last_score;  // see lzg_tree_last_candidate_score
         if (best == ~0ull) {
             A.ctl[LZG_CTL_BEST] = -1;
@@ -348,6 +345,7 @@ k_nni_argmin(const lzg_pass_args A_) {
             const int pass = A.ctl[LZG_CTL_PASSES];
             if (pass == 0) A.ctl[LZG_CTL_CURRENT] = root;  // hill_climb's current_score = t[0].data.score (src/copy_number.cxx:390)
             A.ctl[LZG_CTL_PASSES] = pass + 1;
+            A.ctl[LZG_CTL_EPOCH] += 1;  // the stamp of the next iteration's changes (lzg_tree_climb.cuh)
             if (pass <= A.log_cap) {
                 unsigned long long now;
                 asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
@@ -357,4 +355,15 @@ k_nni_argmin(const lzg_pass_args A_) {
             if (A.use_cond) cudaGraphSetConditional(A.cond_handle, best == ~0ull ? 0u : 1u);
         }
     }
+}
+
+template <bool CLIMB>
+__global__ void __launch_bounds__(1024)
+k_nni_argmin(const lzg_pass_args A_) {
+    const lzg_pass_args& A = CLIMB ? c_pass : A_;
+    if (CLIMB && __ldcg(A.ctl + LZG_CTL_STOP)) {
+        if (A.use_cond && threadIdx.x == 0) cudaGraphSetConditional(A.cond_handle, 0);
+        return;
+    }
+    argmin_body<CLIMB>(A);
 }

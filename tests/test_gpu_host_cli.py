@@ -68,6 +68,19 @@ def test_synthetic_distance(tmp_path):
         assert same(tmp_path / ("dist" + f), os.path.join(GOLD, "synth_cli", "dist" + f)), f
 
 
+def test_devices_flag(tmp_path):
+    """--devices: the distance matrix on every GPU of the box (one GPU: the same single-device path), same bytes."""
+    import torch
+    g = torch.cuda.device_count()
+    src = os.path.join(GOLD, "synth_cli", "synth_cn_profile.csv")
+    run(["distance", src, "-o", str(tmp_path / "dist"), "--devices", "0-%d" % (g - 1)])
+    for f in ("_dist_matrix.csv", "_dist_matrix.txt"):
+        assert same(tmp_path / ("dist" + f), os.path.join(GOLD, "synth_cli", "dist" + f)), f
+    run(["nni", src, "-a", "1", "-i", "4", "-s", "3", "-o", str(tmp_path / "full"), "--devices", ",".join(str(d) for d in range(g))])
+    for f in ("_dist_matrix.txt", "_nj_tree.newick", "_tree.newick", "_info.json", "_ancestral_cn_profile.csv"):
+        assert same(tmp_path / ("full" + f), os.path.join(GOLD, "synth_cli", "full" + f)), f
+
+
 def test_no_gpu_flag_errors_cleanly(tmp_path):
     src = os.path.join(GOLD, "synth_cli", "synth_cn_profile.csv")
     r = subprocess.run([LAZAC, "distance", src, "-o", str(tmp_path / "x"), "--device", "99"], capture_output=True, text=True)
