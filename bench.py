@@ -5,28 +5,35 @@
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference ...                     # the reference's own CPU code
 
-Workloads (BASELINE.json `configs`, SURVEY.md §8(d)); a step = one whole distance matrix:
+Workloads (BASELINE.json `configs`, SURVEY.md 8(d)); a step = one whole distance matrix:
   cfg3  20,000 cells x 10,000 bins x 2 alleles (L = 20,000)  the headline at EVERY --gpus N: the
         matrix BASELINE.json's scaling target is quoted on; it fits one GPU (0.4 GB in, 1.6 GB
         out), so N = 1 runs the same matrix and the 1/2/4/8 series is one strong-scaling series
-        (tile rows of the ONE matrix dealt to the ranks, no data-path collective; every rank
-        ends with its own row/column strips)
   cfg2  1,000 cells x 5,000 bins x 2 alleles (L = 10,000)   configs[1]; reported in the same
         line at --gpus 1 as "cfg2" (same calls, same keys), or alone with --workload cfg2
-The NNI path is reported in the same line at --gpus 1: "nni" = cfg4 (1,000 cells x 5,000 bins, NJ
-seed tree), "nni_large" = cfg5's shape (10,000 cells x 20,000 positions) on the one GPU; a step is
-one hill-climb iteration (accept a move + score the whole new neighbourhood).
+The NNI path is reported in the same line: "nni" = cfg4 (1,000 cells x 5,000 bins, NJ seed tree),
+"nni_large" = cfg5's shape on the one GPU; at --gpus N > 1 "nni" = cfg5 with the positions sharded
+over the ranks.  A step is one hill-climb iteration of lzg_hill_climb (accept the previous
+winner + score the neighbourhood of the new tree), timed on the device by the kernels' own stamps.
 
 value   = cell pairs (n(n+1)/2, as the reference's loop counts them, src/lazac.cxx:81-91) per
           second with the packed profiles already resident in HBM; device time (CUDA events on
           the library's stream), summed over the K steps, max over ranks; L2 flushed between steps.
-e2e     = the same through the host-buffer C-ABI calls a caller of build_distance_matrix would
-          make (lzg_profiles_upload_i8 + lzg_distance_matrix / lzg_distance_shard), pinned host
-          buffers, H2D and D2H inside the timed region.
+e2e     = the same through the host-buffer C-ABI calls a caller of build_distance_matrix makes:
+          pinned host profiles in, the WHOLE matrix in one pinned host buffer out.  N = 1:
+          lzg_profiles_upload_i8 + lzg_distance_matrix; N > 1: rank 0 drives all N GPUs from one
+          process (lzg_distance_matrix_multi: per-GPU upload of a row block, NVLink all-gather,
+          mirrors written into the owners' memory, per-GPU copy-out), the other ranks idle.
+Every roofline denominator and DRAM byte count is PARSED from a file under profiles/ that the JSON
+line names (integer-pipe microbenchmark, ncu --set full summaries); MEASURED_PEAKS.json gives the
+HBM peak.
 """
 import argparse
+import glob
+import hashlib
 import json
 import os
+import re
 import subprocess
 import sys
 import threading
@@ -37,6 +44,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+PROFILES = os.path.join(ROOT, "profiles")
 
 WORKLOADS = {
     "cfg2": dict(cells=1000, bins=5000, alleles=2),
@@ -48,28 +56,77 @@ NNI_WORKLOADS = {
     "cfg5": dict(cells=10000, bins=10000, alleles=2),
     "tiny": dict(cells=60, bins=300, alleles=1),
 }
-# VABSDIFF4.U8.ACC issue rate measured on this pool's B200 (tools/microbench.cu,
-# profiles/r01_microbench_int_pipes.jsonl): 62.94 lane-instr/clk/SM x 148 SMs x 1.965 GHz.
-SAD4_PEAK_LANE_INSTR_PER_S = 1.8304e13
+PERTURB = 0.25      # the climbs start from the NJ seed tree after floor(0.25 x internal edges) random NNIs -- do_nni's candidate
+                    # set is the seed tree perturbed with aggressions 0 .. 1.75 (src/lazac.cxx:243-248)
 
 
-# DRAM traffic per launch / per pass from the committed ncu --set full captures (bytes); None elsewhere
-NCU_DRAM_BYTES = {
-    ("distance", "cfg2"): 14432768,                                   # k_zcnt_distance: 14.43 MB read, 0 written (14.0 MB algorithmic)
-    ("distance", "cfg3"): 7726542000 + 1607675000,                    # 7.7 GB read + 1.6 GB written (2.0 GB algorithmic); 54.75 + 1.60 GB with the row-major tile list
-    ("nni", "cfg5 on 1 GPU"): 513864000 + 364247296 + 1283499000 + 4908800,  # k_up_pass (r + w) + k_nni_items (r + w); 2.93 GB algorithmic
-}
+# ---- roofline inputs: parsed from profiles/, never pasted ---------------------------------------------
+def latest(pattern):
+    """Newest round's file matching profiles/<pattern> (rNN_ prefix sorts by round)."""
+    hits = sorted(glob.glob(os.path.join(PROFILES, pattern)))
+    return hits[-1] if hits else None
 
 
-NCU_DIST_FILES = {"cfg2": "r01_ncu_dist_cfg2.txt", "cfg3": "r01_ncu_dist_cfg3_v3.txt"}
+def microbench_rate(op_prefix):
+    """lane-instructions / s of one instruction from the committed run of tools/microbench.cu."""
+    path = latest("r*_microbench_int_pipes.jsonl")
+    if path:
+        with open(path) as f:
+            for line in f:
+                try:
+                    row = json.loads(line)
+                except ValueError:
+                    continue
+                if str(row.get("op", "")).startswith(op_prefix) and "lane_instr_per_s" in row:
+                    return float(row["lane_instr_per_s"]), os.path.relpath(path, ROOT), row
+    return None, None, None
+
+
+_UNITS = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+
+
+def ncu_value(path, metric, kernel_substr=None):
+    """One metric of a tools/ncu_summary.py text file: value of the first launch whose kernel name contains
+    kernel_substr (files with several launches list them side by side).  Byte units are converted to bytes."""
+    if not path or not os.path.exists(path):
+        return None
+    kernels, col = None, 0
+    with open(path) as f:
+        lines = f.read().splitlines()
+    for ln in lines:
+        if ln.startswith("kernels:"):
+            kernels = [k.strip() for k in ln[len("kernels:"):].split("|")]
+    if kernel_substr and kernels:
+        hits = [i for i, k in enumerate(kernels) if kernel_substr in k]
+        if not hits:
+            return None
+        col = hits[0]
+    for ln in lines:
+        parts = ln.split()
+        if parts and parts[0] == metric:
+            rest = parts[1:]
+            unit = None
+            if rest and not re.match(r"^-?[0-9.,eE+]+$", rest[0]):
+                unit, rest = rest[0], rest[1:]
+            try:
+                v = float(rest[col].replace(",", ""))
+            except (IndexError, ValueError):
+                return None
+            return v * _UNITS.get(unit, 1.0)
+    return None
+
+
+def ncu_dram_bytes(path, kernel_substr=None):
+    r, w = ncu_value(path, "dram__bytes_read.sum", kernel_substr), ncu_value(path, "dram__bytes_write.sum", kernel_substr)
+    return None if r is None or w is None else r + w
 
 
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return json.load(f), "measured"
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
     except Exception:
-        return {"hbm_gbs": 6650.0}, "fallback"
+        return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -123,14 +180,6 @@ def dist_env():
     return rank, local, world
 
 
-def make_workload(name):
-    from lazac_copy_number_b200 import synth
-    w = WORKLOADS[name]
-    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)
-    bp = synth.bp_from_cn(prof["cn"], prof["seg"]).astype(np.int8)  # |bp| <= 8: int8 exact
-    return bp
-
-
 def bp_int8_chunked(cn, seg, rows=2000):
     from lazac_copy_number_b200 import synth
     out = np.empty(cn.shape, np.int8)
@@ -139,6 +188,13 @@ def bp_int8_chunked(cn, seg, rows=2000):
     return out
 
 
+def workload_bp(w):
+    from lazac_copy_number_b200 import synth
+    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)   # same seed on every rank
+    return bp_int8_chunked(prof["cn"], prof["seg"])
+
+
+# ---- the reference's CPU code (cpu_baseline legs and --impl reference) -------------------------------------
 def cpu_distance_sample(bp, n_sample):
     """The reference's pair loop on the first n_sample cells, single-threaded (the reference has
     no threads).  Uses oracle/_ref (the unmodified reference functions) when it was built, else
@@ -157,9 +213,57 @@ def cpu_distance_sample(bp, n_sample):
     return pairs / dt, kind, dt, pairs
 
 
+def seed_tree_arrays(bp, D=None):
+    """The seed tree of the NNI sections, identical in both arms: Clearcut-exact NJ of the distance matrix with
+    the taxon order of NJ_shuffle_distance_matrix for seed 0 (src/lazac.cxx:171-187).  On the CPU (liblazac_host.so,
+    the code `lazac` links) when no GPU matrix is given -- the reference arm."""
+    from lazac_copy_number_b200 import nj, search
+    n = bp.shape[0]
+    perm = search.clearcut_shuffle(n, 0)
+    if D is None:
+        from oracle import Port
+        D = Port().distance_matrix(bp.astype(np.int32))
+    left, right = search.nj_seed_tree_cpu(D, perm)
+    return nj.tree_from_seed(left, right, perm), perm
+
+
+def perturbed(c0, c1):
+    """The starting tree of the measured climbs: floor(PERTURB x internal edges) random NNIs on the seed tree."""
+    from lazac_copy_number_b200 import synth
+    n_internal_edges = int(((c0 >= 0) & (np.arange(len(c0)) != 0)).sum())
+    return synth.perturb_tree(c0, c1, int(PERTURB * n_internal_edges), np.random.default_rng(1))
+
+
+def cpu_candidate_loop(bp, c0, c1, leaf_row, order, max_edges=None):
+    """The reference's candidate loop (src/copy_number.cxx:347-366: nni, unvisit, small_rectilinear, undo per
+    candidate) on one thread over the first max_edges entries of the shuffled edge order.  Returns
+    (candidates/s, kind, seconds, candidates, scores, moves)."""
+    from oracle import Port, PortTree, have_ref
+    sub = order if max_edges is None else order[:max_edges]
+    if have_ref():
+        from oracle.ref import Ref
+        rt = Ref().tree_i8(c0, c1, leaf_row, bp)
+        rt.small_rectilinear()
+        eu, ev = rt.edges()
+        t0 = time.perf_counter()
+        mv, sc = rt.candidate_scores(eu, ev, sub)
+        dt = time.perf_counter() - t0
+        return len(sc) / dt, "reference", dt, len(sc), sc, mv
+    n = len(c0)
+    leaf_bp = np.zeros((n, bp.shape[1]), np.int32)
+    leaf_bp[leaf_row >= 0] = bp[leaf_row[leaf_row >= 0]]
+    pt = PortTree(Port(), c0, c1, leaf_bp)
+    pt.small_rectilinear()
+    eu, ev = pt.edges()
+    t0 = time.perf_counter()
+    rr = pt.greedy_nni(eu, ev, sub)
+    dt = time.perf_counter() - t0
+    return len(rr["scores"]) / dt, "port", dt, len(rr["scores"]), rr["scores"], rr["moves"]
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path on this box's host
-    cores (1 thread: the reference is single-threaded), each step a bounded sample."""
+    """--impl reference: the reference's CPU implementation of both paths on this box's host cores
+    (1 thread: the reference is single-threaded), each step a bounded sample."""
     rank, local, world = dist_env()
     if rank != 0:
         return
@@ -185,366 +289,303 @@ def run_reference(args):
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "int32", "data": "synthetic",
         "config": {"workload": name, "cells": w["cells"], "bins": w["bins"], "alleles": w["alleles"],
-                   "positions": bp.shape[1], "sample": sample},
+                   "positions": bp.shape[1], "sample": sample,
+                   "note": "a per-pair rate at the workload's row length on a sub-sample of its cells: the whole cfg3 matrix is ~14 h of this loop"},
         "cpu_baseline": {"value": value, "unit": "cell-pairs/s", "cores": 1, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "cell-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if not args.no_nni:
+        # NNI candidates scored / s: the reference's candidate loop over whole neighbourhoods of cfg4's tree (the
+        # same seed tree, perturbation and edge order as the B200 arm's "nni" section)
+        nw = NNI_WORKLOADS["tiny" if name == "tiny" else "cfg4"]
+        prof = synth.make_profiles(nw["cells"], nw["bins"], nw["alleles"], seed=0)
+        nbp = bp_int8_chunked(prof["cn"], prof["seg"])
+        (c0, c1, leaf_row), _ = seed_tree_arrays(nbp)
+        c0, c1 = perturbed(c0, c1)
+        order = np.random.default_rng(0).permutation(len(c0) - 1).astype(np.int32)
+        tot_c, tot_t = 0, 0.0
+        for _ in range(max(1, min(args.steps, 5))):
+            v, kind, dt, cnt, _, _ = cpu_candidate_loop(nbp, c0, c1, leaf_row, order)
+            tot_c += cnt
+            tot_t += dt
+        line["nni"] = {"metric": "nni_candidates_scored_per_sec", "value": tot_c / tot_t, "unit": "candidates/s", "ms_per_step": 1e3 * tot_t / max(1, min(args.steps, 5)),
+                       "config": {"workload": "cfg4", "cells": nw["cells"], "positions": nbp.shape[1], "candidates": cnt,
+                                  "seed_tree": "Clearcut-exact NJ (CPU, liblazac_host.so) of the C port's distance matrix, %g x internal edges random NNIs" % PERTURB,
+                                  "step": "one whole neighbourhood through the reference's candidate loop (nni, unvisit, small_rectilinear, undo per candidate)"},
+                       "cpu_baseline": {"value": tot_c / tot_t, "unit": "candidates/s", "cores": 1, "kind": kind, "sample": "whole neighbourhoods of cfg4's tree"}}
     print(json.dumps(line), flush=True)
 
 
-def nni_iterations(ctx, t, moves, order, steps, warmup, apply=None, align=None):
-    """Times hill-climb iterations on tree t: accept a move (lzg_tree_apply_nni), then score the
-    whole new neighbourhood (lzg_nni_best).  The tree alternates between T0 and T1 = T0 + one
-    move (the inverse of nni(u, w, v, z) is nni(u, z, v, w)), so every step sees stale UP
-    intervals exactly as in hill_climb (src/copy_number.cxx:393-409).  Device time, CUDA events
-    on the library stream, L2 flushed before every step.  `apply` replaces t.apply_nni and `align`
-    (a rank barrier) runs before every timed region when t is one rank's part of a sharded tree."""
-    apply = apply or t.apply_nni
-    align = align or ctx.sync      # the L2 flush has drained before the clock starts: host preparation is not hidden behind it
-    m = tuple(int(x) for x in moves[len(moves) // 2])
-    inv = (m[0], m[3], m[2], m[1])
-    t.nni_best(moves)
-    apply(*m)
-    eu1, ev1 = t.edges()
-    moves1 = t.enumerate_moves(eu1, ev1, order)
-    apply(*inv)
-    lists = (moves1, moves)
-    for k in range(2 * max(2, (warmup + 1) // 2)):
-        apply(*(m if k % 2 == 0 else inv))
-        t.nni_best(lists[k % 2])
-    n_it = steps + steps % 2                    # an even number of steps: the tree ends as T0
-    # (1) the pass on its own, as lzg_nni_best runs it on stale UP intervals: UP pass + items + argmin
-    os.environ["LZG_EAGER_UP"] = "0"
-    stale_ms = 0.0
-    cand = 0
-    cb = ub = 0
-    for k in range(n_it):
-        apply(*(m if k % 2 == 0 else inv))   # untimed
-        ctx.flush_l2()
-        align()
-        ctx.timer_start()
-        t.nni_best(lists[k % 2])
-        stale_ms += ctx.timer_stop()
-        cand += len(lists[k % 2])
-        c, u = t.last_nni_traffic()
-        cb, ub = cb + c, ub + u
-    del os.environ["LZG_EAGER_UP"]
-    # (2) whole iterations: the move application queues the UP pass behind itself; ONE timer over both
-    # calls (a stop between them would wait for the queued UP pass and expose the host's packing)
-    it_ms = wall = 0.0
-    for k in range(n_it):
+# ---- NNI: the device-side hill climb ------------------------------------------------------------------------
+def iteration_stats(stamps_list):
+    """Per-iteration device times (us) from the %globaltimer stamps of one or more climbs."""
+    it = np.concatenate([np.diff(s.astype(np.int64)) / 1e3 for s in stamps_list if len(s) > 1]) if stamps_list else np.zeros(0)
+    if not len(it):
+        return None
+    return {"iterations": int(len(it)), "median_us": float(np.median(it)), "mean_us": float(it.mean()), "min_us": float(it.min()),
+            "p90_us": float(np.percentile(it, 90)), "max_us": float(it.max())}
+
+
+def climb_section(ctx, name, bp, c0, c1, leaf_row, seed_note, reps, max_moves, peaks, peaks_kind, cpu_edges, want_cpu):
+    """One NNI workload on one GPU: real climbs (lzg_hill_climb) from the perturbed seed tree."""
+    from lazac_copy_number_b200 import nj
+    from lazac_copy_number_b200.api import Profiles, Tree
+    n_leaves, L = bp.shape
+    n = 2 * n_leaves - 1
+    gp = Profiles(ctx, bp)
+    p0, p1 = perturbed(c0, c1)
+    base = Tree(ctx, gp, p0, p1, leaf_row)
+    root = base.small_rectilinear()
+    order = np.random.default_rng(0).permutation(n - 1).astype(np.int32)
+    n_cand = 2 * int(((p0 >= 0) & (np.arange(n) != 0)).sum())
+    dep = nj.depths(p0, p1)
+    internal = np.flatnonzero((p0 >= 0) & (np.arange(n) != 0))
+    # warm-up climb (graph instantiation, pools), then the measured ones; every climb starts from a fresh clone
+    w = base.clone()
+    w.hill_climb(order, max_moves=3, want_moves=False)
+    w.free()
+    stamps, walls, results = [], [], []
+    for _ in range(reps):
+        w = base.clone()
         ctx.flush_l2()
         ctx.sync()
-        align()
         t0 = time.perf_counter()
-        ctx.timer_start()
-        apply(*(m if k % 2 == 0 else inv))
-        t.nni_best(lists[k % 2])
-        it_ms += ctx.timer_stop()
-        wall += time.perf_counter() - t0
-    hot = 0.0
-    for _ in range(n_it):                        # UP intervals still valid: scoring only
+        r = w.hill_climb(order, max_moves=max_moves, want_moves=True)
+        walls.append(time.perf_counter() - t0)
+        stamps.append(w.climb_stamps())
+        results.append(r)
+        w.free()
+    r = results[-1]
+    st = iteration_stats(stamps)
+    # the first (full) pass kernel by kernel: one climb as queued launches with events between the kernels
+    os.environ["LZG_CLIMB_GRAPH"] = "0"
+    w = base.clone()
+    ctx.flush_l2()
+    ctx.sync()
+    w.hill_climb(order, max_moves=1, want_moves=False)
+    pass0 = w.climb_pass0_ms()
+    w.free()
+    del os.environ["LZG_CLIMB_GRAPH"]
+    # one iteration per call with the L2 flushed before each (max_moves = 1: first pass + accept), CUDA events around the call
+    flushed = []
+    w = base.clone()
+    for _ in range(6):
         ctx.flush_l2()
-        align()
+        ctx.sync()
         ctx.timer_start()
-        idx, score, _ = t.nni_best(moves)
-        hot += ctx.timer_stop()
-    return {"iterations": n_it, "candidates": cand, "stale_pass_ms": stale_ms / n_it, "iteration_ms": it_ms / n_it, "wall_s": wall,
-            "scoring_only_ms": hot / n_it, "cand_bytes": cb // n_it, "up_bytes": ub // n_it, "best_index": int(idx), "best_score": int(score),
-            "moves_bytes": int(moves.nbytes)}
-
-
-def nni_trajectory(ctx, t, order, max_steps, apply=None, align=None):
-    """A real hill climb from the tree's current topology (hill_climb, src/copy_number.cxx:375-417:
-    one fixed shuffle of the edge indices, every pass scores the whole neighbourhood, the best
-    strictly improving move is accepted, until none is left or max_steps).  Every iteration
-    (accept the previous winner + pass) is timed on the device; the host's re-enumeration of the
-    move list in Python between iterations is not part of the library and is left out."""
-    apply = apply or t.apply_nni
-    align = align or ctx.sync
-    eu, ev = t.edges()
-    moves = t.enumerate_moves(eu, ev, order)
-    idx, score, _ = t.nni_best(moves)           # first pass: untimed (UP intervals of the starting tree)
-    first = score
-    ms, cand, accepted = [], 0, 0
-    while idx >= 0 and accepted < max_steps:
+        rr = w.hill_climb(order, max_moves=1, want_moves=False)
+        flushed.append(ctx.timer_stop())
+        if rr["reason"] == 1:
+            break
+    w.free()
+    # the older call-per-pass form for comparison (lzg_nni_best + lzg_tree_apply_nni, host enumeration between them)
+    w = base.clone()
+    eu, ev = w.edges()
+    moves = w.enumerate_moves(eu, ev, order)
+    idx, _, _ = w.nni_best(moves)
+    step_ms = None
+    if idx >= 0:
         m = tuple(int(x) for x in moves[idx])
-        # the move list of the tree AFTER the move has to exist before the clock starts
-        # (hill_climb patches four entries of its edge index in place, src/copy_number.cxx:401-406):
-        # apply on the host's copy of the topology by applying for real, enumerating, undoing
-        apply(*m)
-        eu, ev = t.edges()
-        nxt = t.enumerate_moves(eu, ev, order)
-        apply(m[0], m[3], m[2], m[1])
-        t.nni_best(moves)                       # back in the state right after the last pass
+        w.apply_nni(*m)
+        eu1, ev1 = w.edges()
+        # edge indices stay with their child ends: re-enumerate from the unchanged child list of the first topology
+        moves1 = w.enumerate_moves(eu1, ev1, order)
+        w.apply_nni(m[0], m[3], m[2], m[1])
+        w.nni_best(moves)
         ctx.flush_l2()
-        align()
+        ctx.sync()
         ctx.timer_start()
-        apply(*m)
-        idx, score, _ = t.nni_best(nxt)
-        ms.append(ctx.timer_stop())
-        cand += len(nxt)
-        moves = nxt
-        accepted += 1
-    if not ms:
-        return {"iterations": 0}
-    ms_sorted = sorted(ms)
-    return {"iterations": accepted, "median_ms": ms_sorted[len(ms) // 2], "mean_ms": sum(ms) / len(ms), "max_ms": ms_sorted[-1],
-            "value": cand / (sum(ms) * 1e-3), "unit": "candidates/s", "first_accepted_score": int(first), "last_score": int(score),
-            "ended": "no improving move left" if idx < 0 else "step limit",
-            "note": "real hill climb from the seed tree: every iteration = accept the previous winner (lzg_tree_apply_nni) + score the whole new "
-                    "neighbourhood (lzg_nni_best), device time, L2 flushed before each"}
-
-
-def nni_report(name, r, t, moves, dep, root, seed_tree, peaks, peaks_kind, n_leaves, L, note):
-    n = 2 * n_leaves - 1
-    C_ = len(moves)
-    it_ms = r["iteration_ms"]
-    ps_ms = r["stale_pass_ms"]
-    nbytes = r["cand_bytes"] + r["up_bytes"]
-    merges, ref_bytes = t.last_nni_work()
-    return {
-        "metric": "nni_candidates_scored_per_sec", "value": C_ / (ps_ms * 1e-3), "unit": "candidates/s",
-        "ms_per_step": ps_ms,
-        "e2e": {"value": r["candidates"] / r["wall_s"], "unit": "candidates/s", "h2d_bytes_per_step": r["moves_bytes"] + 16, "d2h_bytes_per_step": 72,
-                "call": "whole hill-climb iterations, lzg_tree_apply_nni + lzg_nni_best with a host move list, wall clock"},
-        "iteration": {"value": C_ / (it_ms * 1e-3), "unit": "candidates/s", "ms_per_step": it_ms,
-                      "note": "accept a move (path re-scoring; the UP pass is queued behind it) + score the new neighbourhood, device time, one timer over both calls"},
-        "scoring_only": {"value": C_ / (r["scoring_only_ms"] * 1e-3), "unit": "candidates/s", "ms_per_step": r["scoring_only_ms"],
-                         "note": "UP intervals already valid (no move accepted since the last pass)"},
-        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_, "seed_tree": seed_tree,
-                   "step": "one neighbourhood pass as lzg_nni_best runs it after an accepted move: host packing of the move list, UP pass over "
-                           "the internal nodes, scoring of every candidate (the two candidates of an edge = one work item), argmin, read-back",
-                   "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
-                   "reference_algorithm_merges_per_pass": int(merges), "reference_algorithm_bytes_per_pass": int(ref_bytes),
-                   "root_score": int(root), "best_index": r["best_index"], "best_score": r["best_score"], "l2": "flushed between steps"},
-        "roofline": {"bound": "hbm", "achieved": nbytes / (ps_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": nbytes / (ps_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": NCU_DRAM_BYTES.get(("nni", name)), "peak_kind": peaks_kind,
-                     "traffic_source": "k_up_pass + k_nni_items, dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full on a random tree of this "
-                                       "shape (profiles/r01_ncu_nni_v5_cfg5.txt)" if ("nni", name) in NCU_DRAM_BYTES else None,
-                     "algorithmic_bytes_per_pass": int(nbytes), "candidate_bytes": int(r["cand_bytes"]), "up_pass_bytes": int(r["up_bytes"]),
-                     "scoring_only_frac": r["cand_bytes"] / (r["scoring_only_ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], "note": note},
+        w.apply_nni(*m)
+        w.nni_best(moves1)
+        step_ms = ctx.timer_stop()
+    w.free()
+    per_unit_bytes = 10 * L / max(1, r["units_per_full_pass"] // max(1, n_cand // 2))   # 10 rows of one chunk group
+    median_us = st["median_us"] if st else None
+    iters = sum(len(s) - 1 for s in stamps if len(s) > 1)
+    inc_units = (sum(x["item_units"] for x in results) - reps * r["units_per_full_pass"]) / max(1, iters)
+    up_units = sum(x["up_units"] for x in results) / max(1, iters)
+    items_full_bytes = (10 * (n_cand // 2) - 4 * int((p0[0] >= 0) * sum(1 for c in (p0[0], p1[0]) if p0[c] >= 0))) * L
+    up_full_bytes = (4 * len(internal)) * L
+    out = {
+        "metric": "nni_candidates_scored_per_sec", "value": n_cand / (median_us * 1e-6) if median_us else None, "unit": "candidates/s",
+        "ms_per_step": median_us / 1e3 if median_us else None,
+        "iteration": st,
+        "e2e": {"value": sum(x["candidates"] for x in results) / sum(walls), "unit": "candidates/s",
+                "h2d_bytes_per_step": int(4 * (n - 1) + 44 * (n_cand // 2) + 8 * n) // max(1, r["n_passes"]), "d2h_bytes_per_step": int(64 + 20 * r["n_moves"]) // max(1, r["n_passes"]),
+                "ms_per_climb": 1e3 * float(np.mean(walls)), "passes_per_climb": r["n_passes"],
+                "call": "lzg_hill_climb per climb, wall clock: host layout of the work items, their upload with the caller's edge order, ONE graph launch (WHILE node), "
+                        "read-back of the move log; candidates = passes x neighbourhood size"},
+        "climb": {"moves": r["n_moves"], "passes": r["n_passes"], "reason": r["reason"], "start_score": int(root), "end_score": r["true_score"],
+                  "returned_score": r["returned_score"], "max_moves": max_moves,
+                  "moves_sha1": hashlib.sha1(np.ascontiguousarray(r["moves"]).tobytes()).hexdigest()[:16]},
+        "incremental": {"item_units_per_iteration": float(inc_units), "units_per_full_pass": int(r["units_per_full_pass"]),
+                        "fraction_rescored": float(inc_units / max(1, r["units_per_full_pass"])), "up_units_per_iteration": float(up_units),
+                        "note": "an iteration re-scores only the (work item, chunk group) pairs that read a row the accepted move changed, and recomputes only "
+                                "the UP rows whose inputs changed; every candidate's score is still produced every pass and is identical to a full pass "
+                                "(tests/test_gpu_climb.py: whole trajectories against the oracle)"},
+        "full_pass": None if not pass0 else {
+            "ms": float(sum(pass0)), "value": n_cand / (sum(pass0) * 1e-3), "unit": "candidates/s",
+            "kernels_ms": dict(zip(("k_up_df", "k_dirty_scan", "k_items_wl", "k_cand_assemble", "k_nni_argmin"), pass0)),
+            "note": "the first pass of a climb: full UP pass + every work item, L2 flushed, CUDA events between the queued kernels"},
+        "flushed_iteration_call_ms": [float(x) for x in flushed],
+        "stepwise_iteration_ms": step_ms,
+        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": n_cand, "seed_tree": seed_note,
+                   "start": "%g x internal edges random NNIs on the seed tree (do_nni climbs from perturbed candidates, src/lazac.cxx:243-286)" % PERTURB,
+                   "step": "one iteration of hill_climb on the device: accept the winner (k_apply2), incremental UP pass (k_up_delta), dirty scan, re-scoring of "
+                           "the dirty work items (k_items_wl), score assembly for all candidates, arg-min; median over real climbs",
+                   "timing": "%globaltimer stamps written by the arg-min kernel of every pass (the loop runs inside one CUDA graph: no host in it)",
+                   "l2": "tree state %.0f MB incl. UP rows vs 126 MB of L2: %s; flushed_iteration_call_ms / full_pass are measured behind an L2 flush"
+                         % (4 * n * L / 1e6, "far beyond L2" if 4 * n * L > 3e8 else "resident in L2 across iterations, as in the product's loop"),
+                   "mean_depth_v": float(dep[internal].mean()), "max_depth_v": int(dep[internal].max())},
     }
-
-
-def nj_seed(ctx, gp, n_leaves):
-    """The seed tree of do_nni (src/lazac.cxx:155-200) for the profiles gp: GPU distance matrix, then
-    Clearcut-exact NJ on the GPU (the MT19937 taxon shuffle replaced by a numpy one, same on every rank)."""
-    from lazac_copy_number_b200 import nj
-    t0 = time.perf_counter()
-    D = gp.distance_matrix()
-    t1 = time.perf_counter()
-    perm = np.random.default_rng(0).permutation(n_leaves).astype(np.int32)
-    left, right = ctx.nj_seed_tree(D, perm)
-    t2 = time.perf_counter()
-    c0, c1, leaf_row = nj.tree_from_seed(left, right, perm)
-    return c0, c1, leaf_row, "lzg_nj_seed_tree (Clearcut-exact NJ on the GPU, %.0f ms) of the GPU distance matrix (%.0f ms to the host)" % (
-        1e3 * (t2 - t1), 1e3 * (t1 - t0))
-
-
-def nni_section(ctx, args, peaks, peaks_kind):
-    """cfg4: hill-climb iterations on an NJ seed tree (1 GPU)."""
-    from lazac_copy_number_b200 import nj, synth
-    from lazac_copy_number_b200.api import Profiles, Tree
-    name = "tiny" if args.workload == "tiny" else "cfg4"
-    w = NNI_WORKLOADS[name]
-    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)
-    bp = bp_int8_chunked(prof["cn"], prof["seg"])
-    n_leaves, L = bp.shape
-    gp = Profiles(ctx, bp)
-    D = gp.distance_matrix()
-    # the seed tree of do_nni (src/lazac.cxx:155-200): Clearcut-exact NJ on the GPU, seed-0 shuffle replaced by a numpy one
-    perm = np.random.default_rng(0).permutation(n_leaves).astype(np.int32)
-    t0 = time.perf_counter()
-    left, right = ctx.nj_seed_tree(D, perm)
-    nj_s = time.perf_counter() - t0
-    c0, c1, leaf_row = nj.tree_from_seed(left, right, perm)
-    n = 2 * n_leaves - 1
-    t = Tree(ctx, gp, c0, c1, leaf_row)
-    root = t.small_rectilinear()
-    eu, ev = t.edges()
-    order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
-    moves = t.enumerate_moves(eu, ev, order)
-    dep = nj.depths(c0, c1)
-    r = nni_iterations(ctx, t, moves, order, args.steps, args.warmup)
-    out = nni_report(name, r, t, moves, dep, root, "lzg_nj_seed_tree (Clearcut-exact NJ on the GPU, %.1f ms) of the GPU distance matrix" % (1e3 * nj_s),
-                     peaks, peaks_kind, n_leaves, L,
-                     "tree state (%.1f MB incl. UP intervals) fits the 126 MB L2 at this size: the step is launch/latency bound, not HBM bound"
-                     % (4 * n * L / 1e6))
-    C_ = len(moves)
-    if not args.no_cpu:
-        # the reference's candidate loop (src/copy_number.cxx:347-366) on the same tree, 1 thread
-        from oracle import Port, PortTree, have_ref
-        leaf_bp = np.zeros((n, L), np.int32)
-        leaf_bp[n_leaves - 1:] = bp[perm]
-        if have_ref():
-            from oracle.ref import Ref
-            rt = Ref().tree(c0, c1, leaf_bp)
-            rt.small_rectilinear()
-            t0 = time.perf_counter()
-            mv, sc = rt.candidate_scores(eu, ev, order)
-            dt = time.perf_counter() - t0
-            kind = "reference"
-        else:
-            pt = PortTree(Port(), c0, c1, leaf_bp)
-            pt.small_rectilinear()
-            t0 = time.perf_counter()
-            rr = pt.greedy_nni(eu, ev, order)
-            dt = time.perf_counter() - t0
-            sc, kind = rr["scores"], "port"
-        _, _, allsc = t.nni_best(moves, want_all=True)
-        out["cpu_baseline"] = {"value": C_ / dt, "unit": "candidates/s", "cores": 1, "kind": kind, "sample": "the same full pass (%d candidates)" % C_,
-                               "scores_equal_gpu": bool(np.array_equal(sc, allsc))}
-    out["trajectory"] = nni_trajectory(ctx, t, order, max(20, args.steps))
-    t.free()
+    # rooflines: the full pass's dominant kernel (k_items_wl over every item) against the HBM peak on algorithmic bytes and, from the
+    # committed ncu capture, against the integer ALU pipe; the incremental iteration is a latency chain, which neither describes
+    ncu_file = latest("r*_ncu_climb_%s.txt" % ("cfg5" if n_leaves >= 5000 else "cfg4"))
+    alu_pct = ncu_value(ncu_file, "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "k_items_wl")
+    traffic = ncu_dram_bytes(ncu_file, "k_items_wl")
+    if pass0:
+        t_items = pass0[2] * 1e-3
+        out["roofline"] = {
+            "kernel": "k_items_wl (first pass: every work item)", "bound": "int_alu" if (alu_pct or 0) > 60 else "hbm",
+            "achieved": items_full_bytes / t_items / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": items_full_bytes / t_items / 1e9 / peaks["hbm_gbs"],
+            "peak_kind": peaks_kind, "algorithmic_bytes": int(items_full_bytes), "traffic": traffic,
+            "alu_pipe_pct_of_peak": alu_pct, "source": os.path.relpath(ncu_file, ROOT) if ncu_file else None,
+            "note": "frac = algorithmic bytes (10 L per work item = per pair of candidates) / kernel time / HBM peak; alu_pipe_pct_of_peak is the integer ALU pipe "
+                    "utilisation ncu measured for the same launch shape (the kernel is issue bound where it exceeds the HBM fraction)",
+            "up_pass": {"kernel": "k_up_df", "achieved": up_full_bytes / (pass0[0] * 1e-3) / 1e9, "frac": up_full_bytes / (pass0[0] * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                        "algorithmic_bytes": int(up_full_bytes)},
+            "iteration": {"bound": "latency", "algorithmic_bytes": float(inc_units * per_unit_bytes + up_units * 6 * per_unit_bytes / 10),
+                          "note": "six dependent kernels on a few hundred rows: the accept walk (depth x row latency) dominates; see profiles/ launch lists"}}
+    if want_cpu:
+        v, kind, dt, cnt, sc, mv = cpu_candidate_loop(bp, p0, p1, leaf_row, order, cpu_edges)
+        # the same candidates on the GPU (stepwise call with all scores) must give the same numbers
+        w = base.clone()
+        eu, ev = w.edges()
+        moves = w.enumerate_moves(eu, ev, order if cpu_edges is None else order[:cpu_edges])
+        _, _, allsc = w.nni_best(moves, want_all=True)
+        w.free()
+        out["cpu_baseline"] = {"value": v, "unit": "candidates/s", "cores": 1, "kind": kind,
+                               "sample": "%d candidates of the same neighbourhood (%.1f s of the reference's candidate loop)" % (cnt, dt),
+                               "scores_equal_gpu": bool(np.array_equal(sc, allsc) and np.array_equal(mv, moves))}
+    base.free()
     gp.free()
     return out
 
 
-def nni_section_large(ctx, args, peaks, peaks_kind):
-    """cfg5's shape on ONE GPU (tree state 0.8 GB + 0.8 GB of UP intervals: beyond L2, the regime the
-    HBM roofline describes)."""
-    from lazac_copy_number_b200 import nj, synth
-    from lazac_copy_number_b200.api import Profiles, Tree
-    w = NNI_WORKLOADS["cfg5"]
-    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0, want_tree=True)
-    bp = bp_int8_chunked(prof["cn"], prof["seg"])
-    n_leaves, L = bp.shape
-    n = 2 * n_leaves - 1
-    gp = Profiles(ctx, bp)
-    c0, c1, leaf_row, seed_note = nj_seed(ctx, gp, n_leaves)
-    t = Tree(ctx, gp, c0, c1, leaf_row)
-    root = t.small_rectilinear()
-    eu, ev = t.edges()
-    order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
-    moves = t.enumerate_moves(eu, ev, order)
-    dep = nj.depths(c0, c1)
-    r = nni_iterations(ctx, t, moves, order, min(args.steps, 10), args.warmup)
-    out = nni_report("cfg5 on 1 GPU", r, t, moves, dep, root, seed_note,
-                     peaks, peaks_kind, n_leaves, L, "tree state %.1f GB incl. UP intervals" % (4 * n * L / 1e9))
-    out["trajectory"] = nni_trajectory(ctx, t, order, 20)
-    t.free()
-    gp.free()
-    return out
+def nni_sections(ctx, args, line, peaks, peaks_kind):
+    from lazac_copy_number_b200 import nj, search, synth
+    from lazac_copy_number_b200.api import Profiles
+    for key, name, reps, cap, cpu_edges in (("nni", "tiny" if args.workload == "tiny" else "cfg4", 4, 400, None), ("nni_large", "cfg5", 2, 80, 2500)):
+        if key == "nni_large" and (args.workload == "tiny" or args.no_nni_large):
+            continue
+        w = NNI_WORKLOADS[name]
+        bp = workload_bp(w)
+        gp = Profiles(ctx, bp)
+        t0 = time.perf_counter()
+        D = gp.distance_matrix()
+        t1 = time.perf_counter()
+        perm = search.clearcut_shuffle(bp.shape[0], 0)
+        left, right = ctx.nj_seed_tree(D, perm)
+        t2 = time.perf_counter()
+        gp.free()
+        c0, c1, leaf_row = nj.tree_from_seed(left, right, perm)
+        note = "lzg_nj_seed_tree (Clearcut-exact NJ on the GPU, %.0f ms; taxon order of seed 0) of the GPU distance matrix (%.0f ms to the host)" % (
+            1e3 * (t2 - t1), 1e3 * (t1 - t0))
+        if name != "cfg5" and not args.no_cpu:   # the CPU twin the reference arm uses must give the same tree
+            cl, cr = search.nj_seed_tree_cpu(D, perm)
+            assert np.array_equal(cl, left) and np.array_equal(cr, right), "GPU and CPU NJ seed trees differ"
+        line[key] = climb_section(ctx, name if name != "cfg5" else "cfg5 on 1 GPU", bp, c0, c1, leaf_row, note, reps, cap, peaks, peaks_kind,
+                                  cpu_edges, not args.no_cpu)
 
 
 def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
-    """cfg5 (N > 1), positions sharded: every rank holds the same topology over its column slice of
-    the profiles, runs the whole pass (UP pass + all candidates) on 1/N of the bytes, and the ranks
-    sum-all-reduce the int32 vector {root score, candidate scores} over NCCL before the arg-min.
-    Same steps as the one-GPU sections (nni_iterations): the pass after an accepted move, whole
-    iterations, scoring only."""
+    """cfg5 (N > 1), positions sharded: every rank holds the same topology over its column slice, runs every
+    iteration on 1/N of the bytes, and the ranks sum-all-reduce {root score, candidate scores} (NCCL, on the
+    library stream) between the score assembly and the arg-min -- lzg_hill_climb_sharded.  Rank 0 also runs the
+    same climb unsharded and the results must be identical."""
     import torch
     import torch.distributed as dist
-    from lazac_copy_number_b200 import nj, sharding, synth
-    from lazac_copy_number_b200.api import Profiles
+    from lazac_copy_number_b200 import nj, search, sharding
+    from lazac_copy_number_b200.api import Profiles, Tree
     name = "tiny" if args.workload == "tiny" else "cfg5"
     w = NNI_WORKLOADS[name]
-    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0, want_tree=True)
-    bp = bp_int8_chunked(prof["cn"], prof["seg"])
+    bp = workload_bp(w)
     n_leaves, L = bp.shape
     n = 2 * n_leaves - 1
     gp = Profiles(ctx, bp)                      # whole rows once, for the seed tree (the same on every rank)
-    c0, c1, leaf_row, seed_note = nj_seed(ctx, gp, n_leaves)
+    D = gp.distance_matrix()
+    perm = search.clearcut_shuffle(n_leaves, 0)
+    left, right = ctx.nj_seed_tree(D, perm)
+    c0, c1, leaf_row = nj.tree_from_seed(left, right, perm)
+    p0, p1 = perturbed(c0, c1)
+    order = np.random.default_rng(0).permutation(n - 1).astype(np.int32)
+    cap = 80
+    one = None
+    if rank == 0:                               # the 1-rank answer
+        t1 = Tree(ctx, gp, p0, p1, leaf_row)
+        t1.small_rectilinear()
+        one = t1.hill_climb(order, max_moves=cap)
+        t1.free()
     gp.free()
-    st = sharding.PositionShardedTree(ctx, bp, c0, c1, leaf_row, rank, world)
+    st = sharding.PositionShardedTree(ctx, bp, p0, p1, leaf_row, rank, world)
     root = st.small_rectilinear()
-    eu, ev = st.edges()
-    order = np.random.default_rng(0).permutation(len(eu)).astype(np.int32)
-    moves = st.enumerate_moves(eu, ev, order)
-    C_ = len(moves)
-    dep = nj.depths(c0, c1)
-
-    def align():
+    n_cand = 2 * int(((p0 >= 0) & (np.arange(n) != 0)).sum())
+    c0g, c1g = st.tree.topology()
+    stamps, walls, res = [], [], None
+    for rep in range(3):
+        st.tree.set_topology(p0, p1)
+        st.small_rectilinear()
+        ctx.flush_l2()
         ctx.sync()
         torch.cuda.synchronize()
         dist.barrier()
-
-    # the new global root score of an accepted move is the winner's score: no collective in the move application
-    r = nni_iterations(ctx, st, moves, order, args.steps, args.warmup, apply=lambda *m: st.apply_nni(*m, new_root=0), align=align)
-    keys = ("stale_pass_ms", "iteration_ms", "scoring_only_ms", "wall_s")
-    tt = torch.tensor([r[k] for k in keys], dtype=torch.float64, device="cuda")
+        t0 = time.perf_counter()
+        res = st.hill_climb(order, max_moves=cap)
+        walls.append(time.perf_counter() - t0)
+        if rep > 0:
+            stamps.append(st.tree.climb_stamps())
+    s = iteration_stats(stamps)
+    tt = torch.tensor([s["median_us"], s["mean_us"], s["max_us"], float(np.mean(walls[1:]))], dtype=torch.float64, device="cuda")
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    r.update({k: float(v) for k, v in zip(keys, tt)})
-    bt = torch.tensor([float(r["cand_bytes"] + r["up_bytes"])], dtype=torch.float64, device="cuda")
-    dist.all_reduce(bt, op=dist.ReduceOp.SUM)
-    ps_ms, it_ms = r["stale_pass_ms"], r["iteration_ms"]
+    med, mean, mx, wall = (float(x) for x in tt)
+    same = None
+    if rank == 0:
+        same = bool(one["n_moves"] == res["n_moves"] and one["true_score"] == res["true_score"] and one["returned_score"] == res["returned_score"]
+                    and np.array_equal(one["moves"], res["moves"]))
+        assert same, ("the sharded climb differs from the 1-rank climb", one["n_moves"], res["n_moves"], one["true_score"], res["true_score"])
+    pass0 = st.tree.climb_pass0_ms()
     out = {
-        "metric": "nni_candidates_scored_per_sec", "value": C_ / (ps_ms * 1e-3), "unit": "candidates/s", "n_gpus": world,
-        "ms_per_step": ps_ms, "scaling": "strong",
-        "e2e": {"value": r["candidates"] / r["wall_s"], "unit": "candidates/s", "h2d_bytes_per_step": r["moves_bytes"] + 16, "d2h_bytes_per_step": 72,
-                "call": "whole hill-climb iterations on every rank (apply + launch + all-reduce + finish), wall clock, max over ranks"},
-        "iteration": {"value": C_ / (it_ms * 1e-3), "unit": "candidates/s", "ms_per_step": it_ms},
-        "scoring_only": {"value": C_ / (r["scoring_only_ms"] * 1e-3), "unit": "candidates/s", "ms_per_step": r["scoring_only_ms"]},
-        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": C_,
-                   "seed_tree": seed_note, "positions_per_rank": st.hi - st.lo,
-                   "step": "per rank, after an accepted move: UP pass + all candidates over its column slice; one NCCL sum all-reduce of %d int32 "
-                           "on the library stream; argmin; read-back" % (C_ + 1),
-                   "mean_depth_v": float(dep[moves[:, 2]].mean()), "max_depth_v": int(dep[moves[:, 2]].max()),
-                   "root_score": int(root), "best_index": r["best_index"], "best_score": r["best_score"],
-                   "timing": "CUDA events on the library stream (the all-reduce is ordered on it), ranks aligned by a barrier before every step, max over ranks",
-                   "l2": "flushed between steps"},
-        "roofline": {"bound": "hbm", "achieved": float(bt[0]) / world / (ps_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s per GPU",
-                     "frac": float(bt[0]) / world / (ps_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_kind": peaks_kind,
-                     "algorithmic_bytes_per_pass_all_ranks": int(bt[0])},
+        "metric": "nni_candidates_scored_per_sec", "value": n_cand / (med * 1e-6), "unit": "candidates/s", "n_gpus": world,
+        "ms_per_step": med / 1e3, "scaling": "strong",
+        "iteration": {"median_us": med, "mean_us": mean, "max_us": mx, "iterations": s["iterations"], "note": "max over ranks of each rank's statistic"},
+        "e2e": {"value": res["candidates"] / wall, "unit": "candidates/s", "ms_per_climb": 1e3 * wall, "passes_per_climb": res["n_passes"],
+                "h2d_bytes_per_step": int(4 * (n - 1) + 44 * (n_cand // 2) + 8 * n) // max(1, res["n_passes"]), "d2h_bytes_per_step": int(64 + 20 * res["n_moves"]) // max(1, res["n_passes"]),
+                "call": "lzg_hill_climb_sharded on every rank, wall clock, max over ranks"},
+        "climb": {"moves": res["n_moves"], "passes": res["n_passes"], "reason": res["reason"], "start_score": int(root), "end_score": res["true_score"],
+                  "returned_score": res["returned_score"], "max_moves": cap, "equal_to_1_rank_climb": same,
+                  "moves_sha1": hashlib.sha1(np.ascontiguousarray(res["moves"]).tobytes()).hexdigest()[:16]},
+        "full_pass": None if not pass0 else {"ms": float(sum(pass0)), "kernels_ms": dict(zip(("k_up_df", "k_dirty_scan", "k_items_wl", "k_cand_assemble", "k_nni_argmin"), pass0))},
+        "config": {"workload": name, "cells": n_leaves, "positions": L, "nodes": n, "candidates": n_cand, "positions_per_rank": st.hi - st.lo,
+                   "step": "per rank and iteration: accept, incremental UP pass, dirty scan, dirty items over its column slice, score assembly; one NCCL sum "
+                           "all-reduce of %d int32 on the library stream; arg-min.  The kernels are queued in batches by every rank's host (a collective cannot "
+                           "sit inside the WHILE graph); no host decision between them" % (n_cand + 1),
+                   "timing": "%globaltimer stamps of every pass on each rank, median per rank, max over ranks", "l2": "tree state far beyond L2"},
     }
-    out["trajectory"] = nni_trajectory(ctx, st, order, 20, apply=lambda *m: st.apply_nni(*m, new_root=0), align=align)
     st.free()
     return out
 
 
-def run_b200(args):
-    import torch
-    import torch.distributed as dist
-    from lazac_copy_number_b200.api import Context, Profiles
-
-    rank, local, world = dist_env()
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d" % (args.gpus, args.gpus))
-    if not torch.cuda.is_available():
-        sys.exit("no GPU: the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries one JSON line only
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_bench_%h_%p.log")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    peaks, peaks_kind = measured_peaks()
-    ctx = Context(local)
-
-    name = args.workload or "cfg3"
-    line = distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
-    if world == 1 and name == "cfg3" and not args.no_cfg2:
-        # BASELINE.json configs[1] beside the headline: same kernel, same calls, a matrix of 36 tiles
-        line["cfg2"] = distance_section(ctx, args, "cfg2", rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
-    if world == 1 and not args.no_nni:
-        line["nni"] = nni_section(ctx, args, peaks, peaks_kind)
-        if args.workload != "tiny" and not args.no_nni_large:
-            line["nni_large"] = nni_section_large(ctx, args, peaks, peaks_kind)
-    if world > 1 and not args.no_nni:
-        nni = nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind)
-        if rank == 0:
-            line["nni"] = nni
-    ctx.close()
-    if rank == 0:
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
-
-
+# ---- distance ---------------------------------------------------------------------------------------------------------
 def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu):
     """One distance workload: device-resident steps (value, roofline), then the host-buffer calls
     (e2e), then the reference's pair loop on a bounded sample (rank 0, one GPU only)."""
     import torch
     import torch.distributed as dist
-    from lazac_copy_number_b200.api import Profiles
+    from lazac_copy_number_b200.api import MultiContext, Profiles
 
     w = WORKLOADS[name]
-    from lazac_copy_number_b200 import synth
-    prof = synth.make_profiles(w["cells"], w["bins"], w["alleles"], seed=0)   # same seed on every rank
-    bp = bp_int8_chunked(prof["cn"], prof["seg"])
-    del prof
+    bp = workload_bp(w)
     n, L = bp.shape
     P = n * (n + 1) // 2
 
@@ -602,31 +643,51 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
         dev_ms_max, pairs_total = dev_ms, my_pairs
     assert pairs_total == P, (pairs_total, P)
     value = P * args.steps / (dev_ms_max * 1e-3)
+    del d_D
 
-    # ---- e2e: host buffers through the C ABI (upload + compute + download), pinned memory ----
+    # ---- e2e: host buffers through the C ABI, the WHOLE matrix in one pinned host buffer at the end of every step ----
     h_bp = ctx.pinned(bp.shape, np.int8)
     h_bp[...] = bp
     h_D = ctx.pinned((n, n), np.int32)
-    def step_e2e():
-        p = Profiles(ctx, h_bp)
-        if world == 1:
+    e2e_extra = {}
+    if world == 1:
+        def step_e2e():
+            p = Profiles(ctx, h_bp)
             p.distance_matrix(h_D)
-        else:
-            p.distance_shard(shard, n_shards, h_D)
-        p.free()
-    for _ in range(3):
-        step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_e2e()
-    barrier()
-    e2e_s = time.perf_counter() - t0
+            p.free()
+        for _ in range(3):
+            step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_e2e()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        call = "lzg_profiles_upload_i8 + lzg_distance_matrix + lzg_profiles_free, pinned host buffers"
+    else:
+        # rank 0 drives all N GPUs from one process; the other ranks wait (their contexts stay open, idle)
+        e2e_s = 0.0
+        if rank == 0:
+            gp.distance_matrix(h_D)                                    # the 1-GPU bytes
+            want = hashlib.sha1(h_D.tobytes()).hexdigest()
+            with MultiContext(list(range(world))) as m:
+                h_D[...] = -1
+                for _ in range(3):
+                    m.distance_matrix(h_bp, out=h_D)
+                got = hashlib.sha1(h_D.tobytes()).hexdigest()
+                assert got == want, "the %d-GPU matrix differs from the 1-GPU matrix" % world
+                t0 = time.perf_counter()
+                for _ in range(args.steps):
+                    m.distance_matrix(h_bp, out=h_D)
+                e2e_s = time.perf_counter() - t0
+            e2e_extra = {"matrix_equal_to_1gpu": True, "sha1": got[:16]}
+        barrier()
+        call = ("lzg_distance_matrix_multi_i8 from rank 0's process over all %d GPUs (row block per GPU over its own PCIe link, NVLink all-gather, mirrors "
+                "written into the owners' memory, per-GPU copy-out into the one pinned host matrix); the other ranks idle" % world)
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te[0])
-    d2h = 4 * n * n if world == 1 else None
 
     line = None
     if rank == 0:
@@ -634,26 +695,26 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
         lane_instr = P * (L / 4.0)                       # one VABSDIFF4.ACC per 4 positions of a pair
         achieved = lane_instr / world / (ms_step * 1e-3)  # per GPU
         hbm_bytes = n * L + 4 * n * n
+        sad_peak, sad_file, sad_row = microbench_rate("VABSDIFF4")
+        ncu_file = latest("r*_ncu_dist_%s*.txt" % name)
+        traffic = ncu_dram_bytes(ncu_file)
         line = {
             "metric": "zcnt_cell_pairs_per_sec", "value": value, "unit": "cell-pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "u8 (int8 + 128 bias), int32 accumulate",
             "data": "synthetic",
             "config": {"workload": name, "cells": n, "bins": w["bins"], "alleles": w["alleles"], "positions": L, "pairs": P,
-                       "position_ops_per_step": P * L, "sharding": "tile rows dealt in pairs (r, R-1-r) to %d rank(s)" % world,
+                       "position_ops_per_step": P * L, "sharding": "tile rows dealt in pairs (r, R-1-r) to %d GPU(s)" % world,
                        "l2": "flushed between timed steps (256 MiB write)", "timing": "CUDA events on the library stream, summed over steps, max over ranks"},
-            "e2e": {"value": P * args.steps / e2e_s, "unit": "cell-pairs/s", "h2d_bytes_per_step": int(n * L),
-                    "d2h_bytes_per_step": int(d2h) if d2h is not None else int(4 * n * n // world),
-                    "ms_per_step": 1e3 * e2e_s / args.steps,
-                    "call": "lzg_profiles_upload_i8 + %s + lzg_profiles_free, pinned host buffers" % ("lzg_distance_matrix" if world == 1 else "lzg_distance_shard (every rank keeps its strips)")},
+            "e2e": dict({"value": P * args.steps / e2e_s, "unit": "cell-pairs/s", "h2d_bytes_per_step": int(n * L),
+                         "d2h_bytes_per_step": int(4 * n * n), "ms_per_step": 1e3 * e2e_s / args.steps, "call": call}, **e2e_extra),
             "gpu_launches": int(launches),
             "clocks": clk,
-            "roofline": {"bound": "int_alu", "kernel": "k_zcnt_distance", "achieved": achieved / 1e9, "peak": SAD4_PEAK_LANE_INSTR_PER_S / 1e9,
-                         "unit": "G lane-instr/s (VABSDIFF4.U8.ACC, 4 positions each) per GPU", "frac": achieved / SAD4_PEAK_LANE_INSTR_PER_S,
-                         "peak_kind": "measured (tools/microbench.cu on this pool, profiles/r01_microbench_int_pipes.jsonl)",
-                         "traffic": NCU_DRAM_BYTES.get(("distance", name)),
-                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/%s)" % NCU_DIST_FILES.get(name)
-                                           if ("distance", name) in NCU_DRAM_BYTES else None,
+            "roofline": {"bound": "int_alu", "kernel": "k_zcnt_distance", "achieved": achieved / 1e9, "peak": (sad_peak or 0) / 1e9,
+                         "unit": "G lane-instr/s (VABSDIFF4.U8.ACC, 4 positions each) per GPU", "frac": achieved / sad_peak if sad_peak else None,
+                         "peak_kind": "measured: tools/microbench.cu on this pool", "peak_source": sad_file,
+                         "peak_lanes_per_clk_per_sm": sad_row.get("lane_instr_per_clk_per_sm") if sad_row else None,
+                         "traffic": traffic, "traffic_source": os.path.relpath(ncu_file, ROOT) if ncu_file else None,
                          "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / world / (ms_step * 1e-3) / 1e9, "peak_gbs": peaks["hbm_gbs"],
                                  "frac": hbm_bytes / world / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_kind": peaks_kind}},
             "wall_s_timed_region": wall,
@@ -666,8 +727,45 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
         line["cpu_baseline"] = {"value": v, "unit": "cell-pairs/s", "cores": 1, "kind": kind,
                                 "sample": "first %d cells of the same input (%d pairs, %.1f s)" % (min(n, n_sample), pairs, dt)}
     gp.free()
-    del d_D, h_bp, h_D
+    del h_bp, h_D
     return line
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from lazac_copy_number_b200.api import Context
+
+    rank, local, world = dist_env()
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d" % (args.gpus, args.gpus))
+    if not torch.cuda.is_available():
+        sys.exit("no GPU: the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries one JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_bench_%h_%p.log")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    peaks, peaks_kind = measured_peaks()
+    ctx = Context(local)
+
+    name = args.workload or "cfg3"
+    line = distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
+    if world == 1 and name == "cfg3" and not args.no_cfg2:
+        # BASELINE.json configs[1] beside the headline: same kernel, same calls, a matrix of 36 tiles
+        line["cfg2"] = distance_section(ctx, args, "cfg2", rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
+    if world == 1 and not args.no_nni:
+        nni_sections(ctx, args, line, peaks, peaks_kind)
+    if world > 1 and not args.no_nni:
+        nni = nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind)
+        if rank == 0:
+            line["nni"] = nni
+    ctx.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def main():
@@ -678,9 +776,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--ref-cells", type=int, default=0, help="cells in the CPU sample")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
     ap.add_argument("--no-cfg2", action="store_true", help="skip the cfg2 section beside the cfg3 headline at --gpus 1")
-    ap.add_argument("--no-nni", action="store_true", help="skip the NNI section")
+    ap.add_argument("--no-nni", action="store_true", help="skip the NNI sections")
     ap.add_argument("--no-nni-large", action="store_true", help="skip the cfg5-shaped NNI section at --gpus 1")
     args = ap.parse_args()
     if args.impl == "reference":

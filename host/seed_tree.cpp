@@ -85,13 +85,17 @@ SeedTree neighbor_joining_gpu(lzg_ctx* ctx, const std::vector<int32_t>& D, const
     return out;
 }
 
+std::vector<long> clearcut_taxon_shuffle(long n, uint32_t seed) { return clearcut_shuffle(n, seed); }
+
 SeedTree neighbor_joining_clearcut(const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed) {
+    return neighbor_joining_perm(D, names, clearcut_shuffle((long)names.size(), seed));
+}
+
+SeedTree neighbor_joining_perm(const std::vector<int32_t>& D, const std::vector<std::string>& names, const std::vector<long>& perm) {
     const long n = (long)names.size();
-    if ((size_t)n * n != D.size()) throw std::runtime_error("distance matrix size mismatch");
+    if ((size_t)n * n != D.size() || (long)perm.size() != n) throw std::runtime_error("distance matrix size mismatch");
     SeedTree out;
     if (n == 0) throw std::runtime_error("Failed to parse distance matrix.");
-
-    const std::vector<long> perm = clearcut_shuffle(n, seed);
 
     Joiner J;
     J.n0 = n;

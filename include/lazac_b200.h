@@ -191,7 +191,12 @@ typedef struct lzg_climb_result {
     int32_t returned_score;  /* t[0].data.score as the reference's hill_climb returns it: the score of
                                 the LAST candidate of the final, fruitless pass (see
                                 lzg_tree_last_candidate_score); equals true_score unless reason == 1 */
-    int64_t candidates;      /* candidates scored                                                    */
+    int64_t candidates;      /* candidates scored (every pass yields the score of every candidate)   */
+    int64_t item_units;      /* (work item, chunk group) pairs whose position sums were re-computed: the
+                                first pass computes all of them, later passes only those that read a
+                                row an accepted move changed                                         */
+    int64_t up_units;        /* (node, chunk group) UP rows recomputed by the incremental passes     */
+    int64_t units_per_full_pass; /* work items x chunk groups                                        */
 } lzg_climb_result;
 int lzg_hill_climb(lzg_ctx* ctx, lzg_tree* t, int32_t n_edges, const int32_t* edge_order, int32_t greedy,
                    int32_t max_moves, int32_t moves_cap, int32_t* moves, lzg_climb_result* out);
@@ -203,6 +208,10 @@ int lzg_hill_climb_sharded(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_
 /* Device time stamps (ns, %globaltimer) at the end of every pass of the last climb on this tree:
  * stamps[k] - stamps[k-1] = one iteration (accept + UP pass + all candidates + arg-min). */
 int lzg_tree_last_climb_stamps(const lzg_tree* t, int32_t cap, uint64_t* stamps, int32_t* n);
+/* Device time (ms) of the five kernels of the last climb's FIRST pass -- the full one: UP pass, dirty scan,
+ * all work items, score assembly, arg-min -- measured with CUDA events when the climb ran as queued launches
+ * (LZG_CLIMB_GRAPH=0 or a sharded climb); LZG_ERR_STATE when it ran as a graph. */
+int lzg_tree_last_climb_pass0_ms(const lzg_tree* t, float* ms5);
 /* start/end: int32 [n_nodes][L]; score: int32 [n_nodes] (any may be NULL). */
 int lzg_tree_get_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end,
                            int32_t* score);

@@ -65,6 +65,7 @@ SYMBOLS = [
     ("lzg_hill_climb", _i, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp]),
     ("lzg_hill_climb_sharded", _i, [_vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp]),
     ("lzg_tree_last_climb_stamps", _i, [_vp, _i32, _vp, _i32p]),
+    ("lzg_tree_last_climb_pass0_ms", _i, [_vp, _vp]),
     ("lzg_tree_get_intervals", _i, [_vp, _vp, _vp, _vp, _vp]),
     ("lzg_tree_get_node_intervals", _i, [_vp, _vp, _i32, _vp, _vp, _vp]),
     ("lzg_tree_ancestral", _i, [_vp, _vp, _vp, _vp]),
@@ -78,7 +79,8 @@ SYMBOLS = [
 class ClimbResult(C.Structure):
     """lzg_climb_result (include/lazac_b200.h)."""
     _fields_ = [("n_moves", C.c_int32), ("n_passes", C.c_int32), ("reason", C.c_int32), ("true_score", C.c_int32),
-                ("returned_score", C.c_int32), ("candidates", C.c_int64)]
+                ("returned_score", C.c_int32), ("candidates", C.c_int64), ("item_units", C.c_int64), ("up_units", C.c_int64),
+                ("units_per_full_pass", C.c_int64)]
 
 
 class LazacGpuError(RuntimeError):

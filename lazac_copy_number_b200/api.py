@@ -318,6 +318,12 @@ class Tree:
             self.ctx.check(self.ctx.lib.lzg_tree_last_climb_stamps(self.h, n.value, ptr(st), C.byref(n)))
         return st
 
+    def climb_pass0_ms(self):
+        """Device ms of the five kernels of the last climb's first (full) pass, or None when it ran as a graph."""
+        ms = np.zeros(5, np.float32)
+        rc = self.ctx.lib.lzg_tree_last_climb_pass0_ms(self.h, ptr(ms))
+        return None if rc != 0 else [float(x) for x in ms]
+
     def intervals(self):
         S = np.zeros((self.n, self.L), np.int32)
         E = np.zeros((self.n, self.L), np.int32)

@@ -893,7 +893,7 @@ int ensure_climb_buffers(lzg_ctx* ctx, lzg_tree* t, int n_items, int groups) {
 }
 
 struct climb_geometry {
-    int n_items, n_cand, groups, threads, up_grid, delta_grid, wl_grid, scan_grid;
+    int n_items, n_cand, groups, threads, up_grid, delta_grid, wl_grid, scan_grid, item_grid;
 };
 
 enum { K_UP_FULL = 0, K_DIRTY, K_ITEMS, K_ASSEMBLE, K_ARGMIN, K_APPLY, K_UP_DELTA };
@@ -909,7 +909,7 @@ climb_launch climb_kernel(int which, const climb_geometry& G) {
         case K_UP_FULL: return {(void*)k_up_df, dim3(G.up_grid), dim3(G.threads), false};
         case K_DIRTY: return {(void*)k_dirty_scan, dim3(G.scan_grid), dim3(256), false};
         case K_ITEMS: return {(void*)k_items_wl, dim3(G.wl_grid), dim3(G.threads), false};
-        case K_ASSEMBLE: return {(void*)k_cand_assemble, dim3(G.scan_grid), dim3(256), false};
+        case K_ASSEMBLE: return {(void*)k_cand_assemble, dim3(G.item_grid), dim3(256), false};
         case K_ARGMIN: return {(void*)k_nni_argmin<true>, dim3(1), dim3(1024), true};
         case K_APPLY: return {(void*)k_apply2, dim3(G.groups), dim3(G.threads), false};
         default: return {(void*)k_up_delta, dim3(G.delta_grid), dim3(G.threads), false};
@@ -921,9 +921,10 @@ const int ITERATION[] = {K_APPLY, K_UP_DELTA, K_DIRTY, K_ITEMS, K_ASSEMBLE, K_AR
 
 // One pass as plain stream launches; the all-reduce of the position-sharded climb sits between the
 // assembled scores and the arg-min.
-int climb_enqueue(lzg_ctx* ctx, const climb_geometry& G, const int* seq, int n_seq, lzg_comm* comm, lzg_tree* t) {
+int climb_enqueue(lzg_ctx* ctx, const climb_geometry& G, const int* seq, int n_seq, lzg_comm* comm, lzg_tree* t, cudaEvent_t* marks = nullptr) {
     static lzg_pass_args dummy{};
     for (int q = 0; q < n_seq; q++) {
+        if (marks) cudaEventRecord(marks[q], ctx->stream);
         if (seq[q] == K_ARGMIN && comm && lzg_comm_world(comm) > 1) {
             const int rc = lzg_comm_allreduce_sum(ctx, comm, t->d_cand + LZG_CTL_ROOT, (size_t)G.n_cand + 1);
             if (rc != LZG_OK) return rc;
@@ -933,6 +934,7 @@ int climb_enqueue(lzg_ctx* ctx, const climb_geometry& G, const int* seq, int n_s
         LZG_CUDA(ctx, cudaLaunchKernel(L.fn, L.grid, L.block, L.has_arg ? args : nullptr, 0, ctx->stream));
         ctx->launches++;
     }
+    if (marks) cudaEventRecord(marks[n_seq], ctx->stream);
     return LZG_OK;
 }
 
@@ -1003,6 +1005,7 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     R.true_score = R.returned_score = t->root_score;
     R.reason = 1;
     t->climb_stamps.clear();
+    t->pass0_timed = false;
     if (n_edges != n - 1) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_hill_climb: n_edges must be n_nodes - 1");
     // child end of every edge index (t.edges(): by parent id, then child id) and the candidate numbering
     std::vector<int32_t>& child_of = t->tmp_pre;
@@ -1081,7 +1084,8 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     G.up_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * per_sm));
     G.delta_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * 2));
     G.wl_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * per_sm));
-    G.scan_grid = (n_items + 255) / 256;
+    G.scan_grid = (int)(((long long)n_items * groups + 255) / 256);
+    G.item_grid = (n_items + 255) / 256;
     const bool want_graph = !sharded && !(getenv("LZG_CLIMB_GRAPH") && atoi(getenv("LZG_CLIMB_GRAPH")) == 0);
     lzg_ctx::climb_graph* cg = want_graph ? climb_graph_for(ctx, G) : nullptr;
     lzg_pass_args A{};
@@ -1128,17 +1132,35 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     int32_t* h_log = reinterpret_cast<int32_t*>(blob + ((o.upload_bytes + 63) / 64 * 64));  // behind the upload area (read by the H2D above only)
     const bool debug = getenv("LZG_CLIMB_DEBUG") != nullptr;
     int total_moves = 0, stop = 0, passes = 0;
-    long long replayed = 0;
+    long long replayed = 0, item_units_before = 0, up_units_before = 0;
     t->up_valid = false;
     while (true) {
         // every (re)start scores the whole neighbourhood once: queues empty, everything dirty
         static const int32_t x_init[LZG_X_INTS] = {0, 0, 0, 0, 0, 1, 0, 0};
+        if (passes > 0) {  // a restart after a drained log: keep the work counters
+            int32_t h_x[LZG_X_INTS];
+            LZG_CUDA(ctx, cudaMemcpyAsync(h_x, A.xctl, sizeof(h_x), cudaMemcpyDeviceToHost, ctx->stream));
+            LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            item_units_before += h_x[LZG_X_WL_TOTAL], up_units_before += h_x[LZG_X_UQ_TOTAL];
+        }
         LZG_CUDA(ctx, cudaMemcpyAsync(A.xctl, x_init, sizeof(x_init), cudaMemcpyHostToDevice, ctx->stream));
         const int passes_before = passes;
         if (cg) {
             LZG_CUDA(ctx, cudaGraphLaunch(cg->exec, ctx->stream));
         } else {
-            rc = climb_enqueue(ctx, G, PASS0, 5, comm, t);
+            // queued mode also times the kernels of the first (full) pass one by one: the bench's per-kernel rooflines
+            cudaEvent_t marks[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+            const bool timed = passes == 0;
+            if (timed)
+                for (auto& m : marks) cudaEventCreate(&m);
+            rc = climb_enqueue(ctx, G, PASS0, 5, comm, t, timed ? marks : nullptr);
+            if (timed && rc == LZG_OK) {
+                cudaEventSynchronize(marks[5]);
+                for (int q = 0; q < 5; q++) cudaEventElapsedTime(&t->pass0_ms[q], marks[q], marks[q + 1]);
+                t->pass0_timed = true;
+            }
+            if (timed)
+                for (auto& m : marks) cudaEventDestroy(m);
             int batch = 2;
             while (rc == LZG_OK) {
                 for (int q = 0; q < batch && rc == LZG_OK; q++) rc = climb_enqueue(ctx, G, ITERATION, 6, comm, t);
@@ -1204,6 +1226,14 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     R.true_score = h_ctl[LZG_CTL_CURRENT];
     R.returned_score = stop == 1 ? h_ctl[LZG_CTL_LAST] : h_ctl[LZG_CTL_CURRENT];
     R.candidates = (int64_t)passes * n_cand;
+    {   // how much of the neighbourhood was really re-scored / how many UP rows were recomputed (chunk-group units)
+        int32_t h_x[LZG_X_INTS];
+        LZG_CUDA(ctx, cudaMemcpyAsync(h_x, A.xctl, sizeof(h_x), cudaMemcpyDeviceToHost, ctx->stream));
+        LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        R.item_units = h_x[LZG_X_WL_TOTAL] + item_units_before;
+        R.up_units = h_x[LZG_X_UQ_TOTAL] + up_units_before;
+        R.units_per_full_pass = (int64_t)n_items * groups;
+    }
     if (out) *out = R;
     return LZG_OK;
 }

@@ -52,6 +52,8 @@ struct lzg_tree {
     int32_t climb_items = 0;          // internal non-root nodes the block was sized for
     int32_t df_epoch = 1;             // epoch of the dataflow UP pass's queue entries (monotonic per tree)
     std::vector<uint64_t> climb_stamps;  // %globaltimer at the end of every pass of the last climb
+    float pass0_ms[5] = {0, 0, 0, 0, 0};  // device time of the kernels of the last climb's first pass (queued mode only): UP, dirty scan, items, assemble, arg-min
+    bool pass0_timed = false;
 };
 
 struct lzg_comm;

@@ -255,6 +255,13 @@ int lzg_tree_last_climb_stamps(const lzg_tree* t, int32_t cap, uint64_t* stamps,
     return LZG_OK;
 }
 
+int lzg_tree_last_climb_pass0_ms(const lzg_tree* t, float* ms5) {
+    if (!t || !ms5) return LZG_ERR_ARG;
+    if (!t->pass0_timed) return LZG_ERR_STATE;
+    for (int q = 0; q < 5; q++) ms5[q] = t->pass0_ms[q];
+    return LZG_OK;
+}
+
 int lzg_tree_get_intervals(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end, int32_t* score) {
     if (!ctx || !t || t->ctx != ctx) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_tree_get_intervals: bad argument");
     LZG_CUDA(ctx, cudaSetDevice(ctx->device));

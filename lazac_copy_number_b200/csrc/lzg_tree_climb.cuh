@@ -260,7 +260,8 @@ k_apply2() {
             *reinterpret_cast<uint4*>(A.wend + node * lp + off) = ne;
         }
         if (k < LZG_PATH_CAP) {
-            if (c) atomicAdd(&s_term[k], (int32_t)c);
+            c = __reduce_add_sync(0xffffffffu, c);  // one REDUX per warp: 256 same-address shared atomics would serialise
+            if ((tid & 31) == 0 && c) atomicAdd(&s_term[k], (int32_t)c);
             if (chg) s_chg[k] = 1;
             if (tid == 0) s_path[k] = make_int2(node, other);
         } else {
@@ -493,21 +494,23 @@ k_dirty_scan() {
     if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
     const int stamp = __ldcg(A.ctl + LZG_CTL_EPOCH);
     const bool all = __ldcg(A.xctl + LZG_X_FULL) != 0;  // first pass of a climb: everything
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot == 0) A.xctl[LZG_X_UQ_PUSHED] = 0, A.xctl[LZG_X_UQ_DONE] = 0, A.xctl[LZG_X_UQ_TICKET] = 0;  // k_up_delta is done
-    if (slot >= A.n_items) return;
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;  // one thread per (item slot, chunk group)
+    if (q == 0) {  // k_up_delta is done
+        A.xctl[LZG_X_UQ_TOTAL] += A.xctl[LZG_X_UQ_PUSHED];
+        A.xctl[LZG_X_UQ_PUSHED] = 0, A.xctl[LZG_X_UQ_DONE] = 0, A.xctl[LZG_X_UQ_TICKET] = 0;
+    }
+    const int G = A.groups;
+    if (q >= A.n_items * G) return;
+    const int slot = q / G, g = q % G;
     const int4 i0 = __ldg(A.items + 2 * slot), i1 = __ldg(A.items + 2 * slot + 1);
     const int u = i0.x, w = i0.y, a = i0.w, b = i1.x;
-    const bool rec = __ldcg(A.rec_stamp + slot) == stamp;
-    const int G = A.groups;
-    for (int g = 0; g < G; g++) {
-        bool d = all || rec || __ldcg(A.dn_stamp + (size_t)w * G + g) == stamp || __ldcg(A.dn_stamp + (size_t)a * G + g) == stamp ||
-                 __ldcg(A.dn_stamp + (size_t)b * G + g) == stamp;
-        if (!d && u) d = __ldcg(A.dn_stamp + (size_t)u * G + g) == stamp || __ldcg(A.up_stamp + (size_t)u * G + g) == stamp;
-        if (d) {
-            reinterpret_cast<int2*>(A.part)[(size_t)slot * G + g] = make_int2(0, 0);
-            A.wl[atomicAdd(A.xctl + LZG_X_WL_COUNT, 1)] = slot * G + g;
-        }
+    // all six stamps at once (independent loads): the record, DOWN(w), DOWN(a), DOWN(b), DOWN(u), UP(u)
+    const int s0 = __ldcg(A.rec_stamp + slot), s1 = __ldcg(A.dn_stamp + (size_t)w * G + g), s2 = __ldcg(A.dn_stamp + (size_t)a * G + g),
+              s3 = __ldcg(A.dn_stamp + (size_t)b * G + g), s4 = __ldcg(A.dn_stamp + (size_t)u * G + g), s5 = __ldcg(A.up_stamp + (size_t)u * G + g);
+    const bool d = all | (s0 == stamp) | (s1 == stamp) | (s2 == stamp) | (s3 == stamp) | ((u != 0) & ((s4 == stamp) | (s5 == stamp)));
+    if (d) {
+        reinterpret_cast<int2*>(A.part)[q] = make_int2(0, 0);
+        A.wl[atomicAdd(A.xctl + LZG_X_WL_COUNT, 1)] = q;
     }
 }
 
@@ -555,6 +558,7 @@ k_cand_assemble() {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot == 0) {
         A.ctl[LZG_CTL_ROOT] = A.score[0];
+        A.xctl[LZG_X_WL_TOTAL] += A.xctl[LZG_X_WL_COUNT];
         A.xctl[LZG_X_WL_COUNT] = 0, A.xctl[LZG_X_WL_TICKET] = 0, A.xctl[LZG_X_FULL] = 0;  // k_items_wl is done
     }
     if (slot >= A.n_items) return;

@@ -88,7 +88,8 @@ enum {
     LZG_CTL_ROOT = 15, LZG_CTL_INTS = 16
 };
 // xctl: the work queues of the incremental pass
-enum { LZG_X_UQ_PUSHED = 0, LZG_X_UQ_DONE = 1, LZG_X_UQ_TICKET = 2, LZG_X_WL_COUNT = 3, LZG_X_WL_TICKET = 4, LZG_X_FULL = 5, LZG_X_INTS = 8 };
+enum { LZG_X_UQ_PUSHED = 0, LZG_X_UQ_DONE = 1, LZG_X_UQ_TICKET = 2, LZG_X_WL_COUNT = 3, LZG_X_WL_TICKET = 4, LZG_X_FULL = 5,
+       LZG_X_WL_TOTAL = 6, LZG_X_UQ_TOTAL = 7, LZG_X_INTS = 8 };  // the totals: units processed since the climb started
 enum { LZG_UQ_FORCE = 1 << 30 };
 
 // order[].y: the sibling, and LZG_ORDER_PUBLISH if another path's head hangs off the node -- only

@@ -4,7 +4,7 @@ import functools
 
 import numpy as np
 
-from lazac_copy_number_b200 import nj, synth
+from lazac_copy_number_b200 import nj, search, synth
 
 
 def bp_int8(cn, seg, rows=2000):
@@ -24,10 +24,11 @@ def config_bp(cells, bins, alleles, seed=0):
 
 
 def nj_seed_tree(ctx, gp, n_leaves):
-    """The seed tree bench.py measures on: the GPU distance matrix of the profiles, Clearcut-exact NJ
-    on the GPU (lzg_nj_seed_tree) with a numpy taxon shuffle.  Returns (child0, child1, leaf_row, D)."""
+    """The seed tree bench.py's NNI sections start from: the GPU distance matrix of the profiles, Clearcut-exact NJ
+    on the GPU (lzg_nj_seed_tree) with the taxon order of NJ_shuffle_distance_matrix for seed 0.
+    Returns (child0, child1, leaf_row, D)."""
     D = gp.distance_matrix()
-    perm = np.random.default_rng(0).permutation(n_leaves).astype(np.int32)
+    perm = search.clearcut_shuffle(n_leaves, 0)
     left, right = ctx.nj_seed_tree(D, perm)
     c0, c1, leaf_row = nj.tree_from_seed(left, right, perm)
     return c0, c1, leaf_row, D

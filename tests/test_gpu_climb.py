@@ -154,3 +154,47 @@ def test_climb_rejects_a_bad_order(ctx):
         gt.hill_climb(np.arange(5, dtype=np.int32))          # wrong length
     gt.free()
     prof.free()
+
+
+def test_library_hill_climb_equals_reference_hill_climb(ctx, ref):
+    """search.hill_climb (host/search.cpp behind liblazac_host.so: std::shuffle with std::ranlux48_base, then
+    lzg_hill_climb) against the reference's own hill_climb with the same seed: same final topology, same
+    returned t[0].score (the stale last-candidate value included), same generator state afterwards -- on
+    the leaves of the paper simulation n100_l1000_s0 (golden: hill_climb(ranlux48_base(7))) and on seeded cases."""
+    import os
+    from lazac_copy_number_b200 import search
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sim_n100_l1000_s0.npz"))
+    bp, c0, c1 = gold["bp"].astype(np.int32), gold["child0"], gold["child1"]
+    n_leaves = bp.shape[0]
+    leaf_row = np.full(2 * n_leaves - 1, -1, np.int32)
+    leaf_row[n_leaves - 1:] = np.arange(n_leaves)
+    prof = Profiles(ctx, bp)
+    gt = Tree(ctx, prof, c0, c1, leaf_row)
+    assert gt.small_rectilinear() == int(gold["score_before"])
+    g = search.Generator(int(gold["hc_seed"]))
+    out = search.hill_climb(ctx, gt, g, greedy=False)
+    assert np.array_equal(out["child0"], gold["hc_child0"]) and np.array_equal(out["child1"], gold["hc_child1"])
+    assert g.next() == int(gold["gen_next_after"])
+    t0, t1 = gt.topology()
+    assert np.array_equal(t0, gold["hc_child0"]) and np.array_equal(t1, gold["hc_child1"])
+    gt.set_topology(t0, t1)
+    assert gt.small_rectilinear() == int(gold["hc_score"])
+    gt.free()
+    prof.free()
+    for n_leaves, seed, greedy in ((30, 11, False), (30, 12, True), (90, 13, False)):
+        bp, c0, c1, leaf_row = random_case(n_leaves, 400, 2, seed)
+        leaf_bp = np.zeros((2 * n_leaves - 1, bp.shape[1]), np.int32)
+        leaf_bp[n_leaves - 1:] = bp
+        prof = Profiles(ctx, bp)
+        gt = Tree(ctx, prof, c0, c1, leaf_row)
+        rt = ref.tree(c0, c1, leaf_bp)
+        assert gt.small_rectilinear() == rt.small_rectilinear()
+        g, rg = search.Generator(seed), ref.gen(seed)
+        out = search.hill_climb(ctx, gt, g, greedy=greedy)
+        rt.hill_climb(rg, greedy)
+        r0, r1 = rt.topology()
+        assert np.array_equal(out["child0"], r0) and np.array_equal(out["child1"], r1)
+        assert out["score"] == rt.node(0)[2]                      # t[0].data.score as the reference's hill_climb leaves it
+        assert g.next() == rg.next()
+        gt.free()
+        prof.free()

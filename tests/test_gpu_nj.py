@@ -87,3 +87,16 @@ def test_nj_api_shapes_and_errors(ctx):
     big[0, 1] = big[1, 0] = 1 << 24
     with pytest.raises(LazacGpuError):
         ctx.nj_seed_tree(big, np.arange(9))                     # not exact in float32
+
+
+def test_nj_gpu_equals_host_library(ctx):
+    """lzg_nj_seed_tree against liblazac_host.so's CPU neighbour joining (the code `lazac` links) with the same taxon order."""
+    from lazac_copy_number_b200 import search
+    for n, seed in ((2, 1), (3, 2), (17, 3), (300, 4)):
+        rng = np.random.default_rng(seed)
+        D = rng.integers(1, 400, (n, n)).astype(np.int32)
+        D = np.triu(D, 1) + np.triu(D, 1).T
+        perm = search.clearcut_shuffle(n, seed)
+        left, right = ctx.nj_seed_tree(D, perm)
+        cl, cr = search.nj_seed_tree_cpu(D, perm)
+        assert np.array_equal(left, cl) and np.array_equal(right, cr), n

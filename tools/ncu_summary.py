@@ -12,6 +12,7 @@ lts__t_sector_hit_rate.pct lts__throughput.avg.pct_of_peak_sustained_elapsed l1t
 sm__throughput.avg.pct_of_peak_sustained_elapsed sm__warps_active.avg.pct_of_peak_sustained_active smsp__inst_executed.sum
 smsp__issue_active.avg.pct_of_peak_sustained_active sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active
 sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_elapsed sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active
+sm__inst_executed_pipe_alu.sum sm__inst_executed_pipe_fma.sum sm__inst_executed.sum
 sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed
 l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed
 smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio
@@ -28,6 +29,7 @@ hdr, units, data = rows[0], rows[1], rows[2:]
 print("# %s  (ncu --set full --clock-control none; %d launch(es) captured)" % (rep.split("/")[-1], len(data)))
 ki = hdr.index("Kernel Name")
 print("kernel: " + data[0][ki][:100])
+print("kernels: " + " | ".join(r[ki].split("(")[0].replace("<unnamed>::", "").replace("void ", "")[:60] for r in data))
 for k in KEYS:
     if k in hdr:
         i = hdr.index(k)
