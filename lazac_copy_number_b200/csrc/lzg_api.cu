@@ -2,6 +2,7 @@
 #include <algorithm>
 #include <climits>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -55,7 +56,7 @@ const char* lzg_status_string(int s) {
         case LZG_OK: return "ok";
         case LZG_ERR_ARG: return "bad argument";
         case LZG_ERR_NOT_BINARY: return "every child must have exactly two children";
-        case LZG_ERR_RANGE: return "breakpoint value outside the int8 device format";
+        case LZG_ERR_RANGE: return "breakpoint value outside the device formats (|v| <= 32767)";
         case LZG_ERR_CUDA: return "CUDA error";
         case LZG_ERR_NO_DEVICE: return "no usable GPU (there is no CPU fallback)";
         case LZG_ERR_STATE: return "invalid state";
@@ -184,12 +185,14 @@ int lzg_host_free(lzg_ctx* ctx, void* p) {
 }
 
 // ---- profiles ----------------------------------------------------------------------------------
+// Two device formats: one byte per position (v + 128) when every |v| <= 127 -- all named
+// configurations -- else 16 bits (v + 32768) up to |v| <= 32767; beyond that LZG_ERR_RANGE.  The 8-bit form is
+// tried first; the range flag of its packing kernel decides.
 // int8 input: rows are copied straight into the padded device layout (one pitched H2D copy) and
 // biased in place.  int32 input: staged through a bounded device buffer (<= 256 MiB) and packed.
-static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32_t n, int32_t L, lzg_profiles** out) {
-    if (!ctx || !out || n < 0 || L < 0 || ((n > 0 && L > 0) && !host)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_profiles_upload: bad argument");
+static int profiles_upload_width(lzg_ctx* ctx, const void* host, bool is_i8, int32_t n, int32_t L, int width, lzg_profiles** out, bool* out_of_range) {
     *out = nullptr;
-    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    *out_of_range = false;
     lzg_profiles* p = new (std::nothrow) lzg_profiles();
     if (!p) return LZG_ERR_ARG;
     p->ctx = ctx;
@@ -197,7 +200,9 @@ static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32
     p->L = L;
     p->n_pad = std::max(128, (n + 127) / 128 * 128);
     p->l_pad = std::max(128, (L + 127) / 128 * 128);
-    p->d_bytes = (size_t)p->n_pad * p->l_pad;
+    p->width = width;
+    p->pitch = p->l_pad * width;
+    p->d_bytes = (size_t)p->n_pad * p->pitch;
     cudaError_t e = lzg_dev_alloc(ctx, (void**)&p->d, p->d_bytes);
     if (e != cudaSuccess) {
         delete p;
@@ -207,16 +212,16 @@ static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32
     e = cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), ctx->stream);
     if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "flag reset", e);
     void* d_stage = nullptr;
-    if (rc == LZG_OK && is_i8) {
+    if (rc == LZG_OK && is_i8 && width == 1) {
         if (n > 0 && L > 0) {
-            e = cudaMemcpy2DAsync(p->d, p->l_pad, host, L, L, n, cudaMemcpyHostToDevice, ctx->stream);
+            e = cudaMemcpy2DAsync(p->d, p->pitch, host, L, L, n, cudaMemcpyHostToDevice, ctx->stream);
             if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles H2D", e);
         }
         if (rc == LZG_OK) rc = lzg_bias_rows_i8(ctx, p->d, L > 0 ? n : 0, p->n_pad, L, p->l_pad);
     } else if (rc == LZG_OK) {
-        rc = lzg_fill_bytes(ctx, p->d + (size_t)n * p->l_pad, p->d_bytes - (size_t)n * p->l_pad, LZG_BIAS);
+        rc = lzg_fill_pad(ctx, p->d + (size_t)n * p->pitch, p->d_bytes - (size_t)n * p->pitch, width);
         if (rc == LZG_OK && n > 0 && L > 0) {
-            const size_t row_bytes = (size_t)L * 4;
+            const size_t row_bytes = (size_t)L * (is_i8 ? 1 : 4);
             int block_rows = (int)std::max<size_t>(1, std::min<size_t>(n, ((size_t)256 << 20) / row_bytes));
             e = lzg_dev_alloc(ctx, &d_stage, (size_t)block_rows * row_bytes);
             if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "staging allocation", e);
@@ -227,26 +232,41 @@ static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32
                     rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles H2D", e);
                     break;
                 }
-                rc = lzg_pack_rows_i32(ctx, (const int32_t*)d_stage, p->d + (size_t)r0 * p->l_pad, nr, L, p->l_pad);
+                if (is_i8) rc = lzg_pack_rows_i8_w2(ctx, (const int8_t*)d_stage, p->d + (size_t)r0 * p->pitch, nr, L, p->l_pad);
+                else rc = lzg_pack_rows_i32(ctx, (const int32_t*)d_stage, p->d + (size_t)r0 * p->pitch, nr, L, p->l_pad, width);
             }
         } else if (rc == LZG_OK && n > 0) {
-            rc = lzg_fill_bytes(ctx, p->d, (size_t)n * p->l_pad, LZG_BIAS);
+            rc = lzg_fill_pad(ctx, p->d, (size_t)n * p->pitch, width);
         }
     }
     if (rc == LZG_OK) {
         e = cudaMemcpyAsync(ctx->h_pinned, ctx->d_flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // the host buffer is not retained past this call
         if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "profiles pack", e);
-        else if (n > 0 && L > 0 && ctx->h_pinned[0]) rc = lzg_fail(ctx, LZG_ERR_RANGE, "breakpoint value outside [-127, 127]");
+        else if (n > 0 && L > 0 && ctx->h_pinned[0]) *out_of_range = true;
     }
     lzg_dev_free(ctx, d_stage);
-    if (rc != LZG_OK) {
+    if (rc != LZG_OK || *out_of_range) {
         lzg_dev_free(ctx, p->d);
         delete p;
         return rc;
     }
     *out = p;
     return LZG_OK;
+}
+
+static int profiles_upload_any(lzg_ctx* ctx, const void* host, bool is_i8, int32_t n, int32_t L, lzg_profiles** out) {
+    if (!ctx || !out || n < 0 || L < 0 || ((n > 0 && L > 0) && !host)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_profiles_upload: bad argument");
+    *out = nullptr;
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int forced = getenv("LZG_FORCE_WIDTH") ? atoi(getenv("LZG_FORCE_WIDTH")) : 0;  // tests: the 16-bit kernels on small values
+    for (int width = forced == 2 ? 2 : 1; width <= 2; width++) {
+        bool out_of_range = false;
+        const int rc = profiles_upload_width(ctx, host, is_i8, n, L, width, out, &out_of_range);
+        if (rc != LZG_OK) return rc;
+        if (!out_of_range) return LZG_OK;
+    }
+    return lzg_fail(ctx, LZG_ERR_RANGE, "breakpoint value outside [-32767, 32767]");
 }
 
 int lzg_profiles_upload(lzg_ctx* ctx, const int32_t* bp, int32_t n, int32_t L, lzg_profiles** out) {

@@ -8,7 +8,8 @@
 
 #include "lazac_b200.h"
 
-#define LZG_BIAS 128  // int8 value v is stored as the byte v + 128 (exact unsigned abs-diff / min / max)
+#define LZG_BIAS 128     // int8 value v is stored as the byte v + 128 (exact unsigned abs-diff / min / max)
+#define LZG_BIAS16 32768  // wider values (|v| <= 32767) as the 16-bit word v + 32768: the second device format
 
 // Persistent-grid work schedule of the distance kernel for one (tile size, shard) (lzg_distance.cu).
 struct lzg_schedule {
@@ -43,7 +44,7 @@ struct lzg_ctx {
     cudaEvent_t ev_stage = nullptr;  // the last asynchronous copy OUT of the pinned staging area that no synchronising call has waited for
     std::vector<lzg_schedule> schedules;  // distance schedules by (shape, tile, shard); freed at shutdown
     struct climb_graph {                  // one WHILE graph per launch geometry of the climb (lzg_tree.cu)
-        int n_items = 0, groups = 0, threads = 0, up_grid = 0, n_cand = 0;
+        int n_items = 0, groups = 0, threads = 0, up_grid = 0, n_cand = 0, width = 1;
         cudaGraph_t graph = nullptr;
         cudaGraphExec_t exec = nullptr;
         cudaGraphConditionalHandle handle = 0;
@@ -65,8 +66,10 @@ inline void lzg_dev_free(lzg_ctx* ctx, void* p) {
 struct lzg_profiles {
     lzg_ctx* ctx = nullptr;
     int32_t n = 0, L = 0;
-    int32_t n_pad = 0, l_pad = 0;  // rows padded to 128, positions padded to 128 (pad byte = LZG_BIAS)
-    uint8_t* d = nullptr;          // [n_pad][l_pad]
+    int32_t n_pad = 0, l_pad = 0;  // rows padded to 128, positions padded to 128 (pad value = the bias)
+    int32_t width = 1;             // bytes per position: 1 (|v| <= 127, every named configuration) or 2 (|v| <= 32767)
+    int32_t pitch = 0;             // bytes per row = l_pad * width
+    uint8_t* d = nullptr;          // [n_pad][pitch]
     size_t d_bytes = 0;
     int32_t* d_D = nullptr;        // lazily allocated N x N result used by the host-output entry points
 };
@@ -91,8 +94,10 @@ int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuc
 // instead of the one N x N matrix d_D (the row blocks of several GPUs, lzg_multi.cu)
 int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int row_lo, int row_hi,
                      int32_t* d_D, int64_t* pairs_done, int32_t* const* d_row_base = nullptr);
-int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);
+int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad, int width = 1);
 int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v);
+int lzg_fill_pad(lzg_ctx* ctx, uint8_t* d, size_t n_bytes, int width);
+int lzg_pack_rows_i8_w2(lzg_ctx* ctx, const int8_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad);  // the padding value of the format (bias) over whole rows
 int lzg_bias_rows_i8(lzg_ctx* ctx, uint8_t* d, int n, int n_pad, int L, int l_pad);
 // tile edge of the pair kernel for this input: one 64 x 64 tile when n <= 64, else 128 x 128
 inline int lzg_distance_tile(const lzg_profiles* p) { return p->n <= 64 ? 64 : 128; }

@@ -59,6 +59,34 @@ __global__ void k_pack_i32(const int32_t* __restrict__ src, uint8_t* __restrict_
     if (bad) atomicOr(flag, 1);
 }
 
+// int32 [rows][L] -> biased 16-bit words [rows][l_pad]; flags values outside [-32767, 32767].
+__global__ void k_pack_i32_w2(const int32_t* __restrict__ src, uint8_t* __restrict__ dst, int rows, int L, int l_pad, int* flag) {
+    int r = blockIdx.y;
+    const int32_t* s = src + (size_t)r * L;
+    uint32_t* d = reinterpret_cast<uint32_t*>(dst + (size_t)r * l_pad * 2);
+    int bad = 0;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < l_pad / 2; w += gridDim.x * blockDim.x) {
+        uint32_t out = 0;
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            int k = w * 2 + b;
+            int v = k < L ? s[k] : 0;
+            bad |= (v < -32767) | (v > 32767);
+            out |= (uint32_t)((v + LZG_BIAS16) & 0xffff) << (16 * b);
+        }
+        d[w] = out;
+    }
+    if (bad) atomicOr(flag, 1);
+}
+
+// int8 [rows][L] -> biased 16-bit words [rows][l_pad] (an int8 matrix that holds -128: the one value the 8-bit format lacks)
+__global__ void k_pack_i8_w2(const int8_t* __restrict__ src, uint8_t* __restrict__ dst, int rows, int L, int l_pad) {
+    int r = blockIdx.y;
+    const int8_t* s = src + (size_t)r * L;
+    uint16_t* d = reinterpret_cast<uint16_t*>(dst + (size_t)r * l_pad * 2);
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < l_pad; k += gridDim.x * blockDim.x) d[k] = (uint16_t)((k < L ? (int)s[k] : 0) + LZG_BIAS16);
+}
+
 __global__ void k_fill_bytes(uint8_t* dst, size_t n, uint8_t v) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         dst[i] = v;
@@ -125,7 +153,23 @@ struct lzg_seg {
 // One k-iteration (KC positions) of a thread's 8 x 8 pairs.  DIAG skips the lower-left quadrant.
 // (Measured on B200: reordering the SADs, streaming the row operands, or 8-byte operands with
 // two CTAs per SM are all within +-2 % or slower -- the loop is VABSDIFF4-issue bound.)
-template <int BM, int BN, bool DIAG>
+// 16-bit positions: one VABSDIFF.U32 per position of a pair (there is no packed 2 x 16 SAD on sm_100a: vabsdiff2 is
+// emulated), the halves of a word extracted once per row / column and reused over the 8 x 8 pairs.
+__device__ __forceinline__ void sad_w2(uint32_t (&acc)[8][8], const uint32_t (&a)[8], const uint32_t (&b)[8], bool diag) {
+    uint32_t alo[8], ahi[8], blo[8], bhi[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) alo[i] = a[i] & 0xffffu, ahi[i] = a[i] >> 16, blo[i] = b[i] & 0xffffu, bhi[i] = b[i] >> 16;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (diag && i >= 4 && j < 4) continue;
+            acc[i][j] = __usad(alo[i], blo[j], acc[i][j]);
+            acc[i][j] = __usad(ahi[i], bhi[j], acc[i][j]);
+        }
+}
+
+template <int BM, int BN, bool DIAG, int W>
 __device__ __forceinline__ void tile_step(uint32_t (&acc)[8][8], const uint8_t* sA, const uint8_t* sB, int tx, int ty) {
     constexpr int TX = BN / 8, TY = BM / 8;
     const int swa = ty & 7, swb = tx & 7;  // (row & 7) of every row this thread reads
@@ -138,21 +182,33 @@ __device__ __forceinline__ void tile_step(uint32_t (&acc)[8][8], const uint8_t* 
 #pragma unroll
         for (int j = 0; j < 8; j++)
             b[j] = *reinterpret_cast<const uint4*>(sB + (tx + TX * j) * KC + ((c ^ swb) << 4));
+        if (W == 2) {
+            uint32_t aw[8], bw[8];
 #pragma unroll
-        for (int i = 0; i < 8; i++)
+            for (int q = 0; q < 4; q++) {
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                if (DIAG && i >= 4 && j < 4) continue;  // lower-left quadrant: taken from the mirror
-                acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]);
-                acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
-                acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]);
-                acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
+                for (int i = 0; i < 8; i++) aw[i] = q == 0 ? a[i].x : q == 1 ? a[i].y : q == 2 ? a[i].z : a[i].w;
+#pragma unroll
+                for (int j = 0; j < 8; j++) bw[j] = q == 0 ? b[j].x : q == 1 ? b[j].y : q == 2 ? b[j].z : b[j].w;
+                sad_w2(acc, aw, bw, DIAG);
             }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (DIAG && i >= 4 && j < 4) continue;  // lower-left quadrant: taken from the mirror
+                    acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]);
+                    acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
+                    acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]);
+                    acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
+                }
+        }
     }
 }
 
 // The last stage of a segment may hold fewer than eight chunks: same arithmetic, rolled loop.
-template <int BM, int BN, bool DIAG>
+template <int BM, int BN, bool DIAG, int W>
 __device__ __forceinline__ void tile_step_partial(uint32_t (&acc)[8][8], const uint8_t* sA, const uint8_t* sB, int tx, int ty, int nc) {
     constexpr int TX = BN / 8, TY = BM / 8;
     const int swa = ty & 7, swb = tx & 7;
@@ -165,20 +221,33 @@ __device__ __forceinline__ void tile_step_partial(uint32_t (&acc)[8][8], const u
 #pragma unroll
         for (int j = 0; j < 8; j++)
             b[j] = *reinterpret_cast<const uint4*>(sB + (tx + TX * j) * KC + ((c ^ swb) << 4));
+        if (W == 2) {
+            uint32_t aw[8], bw[8];
 #pragma unroll
-        for (int i = 0; i < 8; i++)
+            for (int q = 0; q < 4; q++) {
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                if (DIAG && i >= 4 && j < 4) continue;
-                acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]);
-                acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
-                acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]);
-                acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
+                for (int i = 0; i < 8; i++) aw[i] = q == 0 ? a[i].x : q == 1 ? a[i].y : q == 2 ? a[i].z : a[i].w;
+#pragma unroll
+                for (int j = 0; j < 8; j++) bw[j] = q == 0 ? b[j].x : q == 1 ? b[j].y : q == 2 ? b[j].z : b[j].w;
+                sad_w2(acc, aw, bw, DIAG);
             }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (DIAG && i >= 4 && j < 4) continue;
+                    acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]);
+                    acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
+                    acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]);
+                    acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
+                }
+        }
     }
 }
 
-template <int BM, int BN, int STAGES>
+// l_pad = bytes per profile row (positions x bytes per position); W = bytes per position.
+template <int BM, int BN, int STAGES, int W>
 __global__ void __launch_bounds__((BM / 8) * (BN / 8), 1)
 k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_seg* __restrict__ segs,
                 const int32_t* __restrict__ seg_off, int32_t* __restrict__ D, int32_t* const* __restrict__ row_base) {
@@ -247,11 +316,11 @@ k_zcnt_distance(const uint8_t* __restrict__ prof, int l_pad, int n, const lzg_se
             const uint8_t* sB = sA + A_BYTES;
             const int nc = n_chunks - it * 8;
             if (nc >= 8) {
-                if (!diag) tile_step<BM, BN, false>(acc, sA, sB, tx, ty);
-                else tile_step<BM, BN, true>(acc, sA, sB, tx, ty);
+                if (!diag) tile_step<BM, BN, false, W>(acc, sA, sB, tx, ty);
+                else tile_step<BM, BN, true, W>(acc, sA, sB, tx, ty);
             } else {
-                if (!diag) tile_step_partial<BM, BN, false>(acc, sA, sB, tx, ty, nc);
-                else tile_step_partial<BM, BN, true>(acc, sA, sB, tx, ty, nc);
+                if (!diag) tile_step_partial<BM, BN, false, W>(acc, sA, sB, tx, ty, nc);
+                else tile_step_partial<BM, BN, true, W>(acc, sA, sB, tx, ty, nc);
             }
         }
         cp_async_wait<0>();
@@ -514,15 +583,15 @@ void plan_schedule(int n, int l_pad, int bm, int sm_count, int slots_per_sm, int
 const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slots_per_sm, int shard, int n_shards,
                                  int row_lo, int row_hi, int* status) {
     for (auto& sc : ctx->schedules)
-        if (sc.n == p->n && sc.l_pad == p->l_pad && sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
+        if (sc.n == p->n && sc.l_pad == p->pitch && sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
     lzg_plan plan;
-    plan_schedule(p->n, p->l_pad, bm, ctx->sm_count, slots_per_sm, shard, n_shards, row_lo, row_hi, plan);
+    plan_schedule(p->n, p->pitch, bm, ctx->sm_count, slots_per_sm, shard, n_shards, row_lo, row_hi, plan);
     std::vector<lzg_seg>& segs = plan.segs;
     std::vector<int32_t>& seg_off = plan.seg_off;
     std::vector<int2>& split = plan.split;
     lzg_schedule sc;
     sc.n = p->n;
-    sc.l_pad = p->l_pad;
+    sc.l_pad = p->pitch;  // the plan is cut in 16-byte chunks of a row
     sc.bm = bm;
     sc.shard = shard;
     sc.n_shards = n_shards;
@@ -561,7 +630,7 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
     return &ctx->schedules.back();
 }
 
-template <int BM, int BN, int STAGES>
+template <int BM, int BN, int STAGES, int W>
 int launch_distance(lzg_ctx* ctx, const lzg_profiles* p, const lzg_schedule* sc, int32_t* d_D, int32_t* const* d_row_base) {
     constexpr int smem = dist_smem_bytes<BM, BN, STAGES>();
     constexpr int T = (BM / 8) * (BN / 8);
@@ -569,19 +638,27 @@ int launch_distance(lzg_ctx* ctx, const lzg_profiles* p, const lzg_schedule* sc,
         k_zero_tiles<BM, BN><<<dim3(sc->n_split, 16), 256, 0, ctx->stream>>>(sc->d_split, p->n, d_D, d_row_base);
         LZG_LAUNCH_CHECK(ctx);
     }
-    auto kern = k_zcnt_distance<BM, BN, STAGES>;
+    auto kern = k_zcnt_distance<BM, BN, STAGES, W>;
     LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     LZG_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    kern<<<sc->n_ctas, T, smem, ctx->stream>>>(p->d, p->l_pad, p->n, (const lzg_seg*)sc->d_segs, sc->d_seg_off, d_D, d_row_base);
+    kern<<<sc->n_ctas, T, smem, ctx->stream>>>(p->d, p->pitch, p->n, (const lzg_seg*)sc->d_segs, sc->d_seg_off, d_D, d_row_base);
     LZG_LAUNCH_CHECK(ctx);
     return LZG_OK;
 }
 
 }  // namespace
 
-int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad) {
+int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad, int width) {
     dim3 grid(std::max(1, std::min(64, (l_pad / 4 + 255) / 256)), rows);
-    k_pack_i32<<<grid, 256, 0, ctx->stream>>>(d_src, d_dst, rows, L, l_pad, ctx->d_flag);
+    if (width == 2) k_pack_i32_w2<<<grid, 256, 0, ctx->stream>>>(d_src, d_dst, rows, L, l_pad, ctx->d_flag);
+    else k_pack_i32<<<grid, 256, 0, ctx->stream>>>(d_src, d_dst, rows, L, l_pad, ctx->d_flag);
+    LZG_LAUNCH_CHECK(ctx);
+    return LZG_OK;
+}
+
+int lzg_pack_rows_i8_w2(lzg_ctx* ctx, const int8_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad) {
+    dim3 grid(std::max(1, std::min(64, (l_pad + 255) / 256)), rows);
+    k_pack_i8_w2<<<grid, 256, 0, ctx->stream>>>(d_src, d_dst, rows, L, l_pad);
     LZG_LAUNCH_CHECK(ctx);
     return LZG_OK;
 }
@@ -589,6 +666,20 @@ int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int ro
 int lzg_bias_rows_i8(lzg_ctx* ctx, uint8_t* d, int n, int n_pad, int L, int l_pad) {
     dim3 grid(std::max(1, std::min(16, (l_pad / 16 + 255) / 256)), n_pad);
     k_bias_rows_i8<<<grid, 256, 0, ctx->stream>>>(d, n, L, l_pad, ctx->d_flag);
+    LZG_LAUNCH_CHECK(ctx);
+    return LZG_OK;
+}
+
+// whole padding rows of a format: bytes 0x80 (width 1), little-endian words 0x8000 (width 2: bytes 0x00, 0x80 alternating)
+__global__ void k_fill_pad16(uint32_t* dst, size_t n_words) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x) dst[i] = 0x80008000u;
+}
+
+int lzg_fill_pad(lzg_ctx* ctx, uint8_t* d, size_t n_bytes, int width) {
+    if (width == 1) return lzg_fill_bytes(ctx, d, n_bytes, LZG_BIAS);
+    if (n_bytes == 0) return LZG_OK;
+    const size_t words = n_bytes / 4;
+    k_fill_pad16<<<(int)std::min<size_t>(4096, (words + 255) / 256), 256, 0, ctx->stream>>>(reinterpret_cast<uint32_t*>(d), words);
     LZG_LAUNCH_CHECK(ctx);
     return LZG_OK;
 }
@@ -615,14 +706,15 @@ int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int
     if (!sc) return status;
     if (pairs_done) *pairs_done = sc->pairs;
     if (sc->n_segs == 0) return LZG_OK;
-    return bm == 64 ? launch_distance<64, 64, 4>(ctx, p, sc, d_D, d_row_base) : launch_distance<128, 128, 3>(ctx, p, sc, d_D, d_row_base);
+    if (p->width == 2) return bm == 64 ? launch_distance<64, 64, 4, 2>(ctx, p, sc, d_D, d_row_base) : launch_distance<128, 128, 3, 2>(ctx, p, sc, d_D, d_row_base);
+    return bm == 64 ? launch_distance<64, 64, 4, 1>(ctx, p, sc, d_D, d_row_base) : launch_distance<128, 128, 3, 1>(ctx, p, sc, d_D, d_row_base);
 }
 
 // Host-only view of the work plan (no GPU, no context): see include/lazac_b200.h.
 int lzg_distance_plan(int32_t n, int32_t L, int32_t sm_count, int32_t shard, int32_t n_shards, int32_t row_lo, int32_t row_hi,
                       int32_t* segs, int64_t cap_segs, int32_t* seg_off, int32_t cap_ctas, int32_t* info) {
     if (n < 1 || L < 1 || sm_count < 1 || n_shards < 1 || shard < 0 || shard >= n_shards || !info) return LZG_ERR_ARG;
-    const int l_pad = std::max(128, (L + 127) / 128 * 128);  // as lzg_profiles_upload pads
+    const int l_pad = std::max(128, (L + 127) / 128 * 128);  // as lzg_profiles_upload pads (the 8-bit format: one byte per position)
     const int bm = n <= 64 ? 64 : 128;                       // lzg_distance_tile
     lzg_plan plan;
     plan_schedule(n, l_pad, bm, sm_count, bm == 64 ? 3 : 1, shard, n_shards, row_lo, row_hi, plan);

@@ -156,14 +156,15 @@ int lzg_multi_context(lzg_multi* m, int32_t i, lzg_ctx** ctx) {
 
 const char* lzg_multi_last_error(const lzg_multi* m) { return m ? m->err.c_str() : ""; }
 
-static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n, int32_t L, int32_t* D_host, int64_t* pairs_out) {
-    if (!m || n < 0 || L < 0 || (n > 0 && L > 0 && !host) || (n > 0 && !D_host)) return multi_fail(m, LZG_ERR_ARG, "lzg_distance_matrix_multi: bad argument");
-    if (pairs_out) *pairs_out = 0;
-    if (n == 0) return LZG_OK;
+// One attempt in one device format (width = bytes per position); *out_of_range tells the caller to try the wider one.
+static int distance_multi_width(lzg_multi* m, const void* host, bool is_i8, int32_t n, int32_t L, int32_t* D_host, int64_t* pairs_out, int width,
+                                bool* out_of_range_) {
+    *out_of_range_ = false;
     const int G = (int)m->ctx.size();
     const int n_pad = std::max(128, (n + 127) / 128 * 128), l_pad = std::max(128, (L + 127) / 128 * 128);
+    const int pitch = l_pad * width;
     lzg_profiles shape;  // for lzg_distance_tile / the schedule cache
-    shape.n = n, shape.L = L, shape.n_pad = n_pad, shape.l_pad = l_pad;
+    shape.n = n, shape.L = L, shape.n_pad = n_pad, shape.l_pad = l_pad, shape.width = width, shape.pitch = pitch;
     const int bm = lzg_distance_tile(&shape), R = (n + bm - 1) / bm;
     auto owner = [&](int r) { return std::min(r, R - 1 - r) % G; };
     // output rows: slot of every tile row inside its owner's block
@@ -172,7 +173,7 @@ static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n,
     const size_t tile_row_ints = (size_t)bm * n;
     for (int g = 0; g < G; g++) {
         LZM_CUDA(m, cudaSetDevice(m->ctx[g]->device));
-        int rc = grow(m, &m->d_prof[g], &m->prof_cap[g], (size_t)n_pad * l_pad);
+        int rc = grow(m, &m->d_prof[g], &m->prof_cap[g], (size_t)n_pad * pitch);
         if (rc == LZG_OK) rc = grow(m, &m->d_rows[g], &m->rows_cap[g], sizeof(int32_t) * tile_row_ints * std::max(1, owned[g]));
         if (rc == LZG_OK) rc = grow(m, &m->d_table[g], &m->table_cap[g], sizeof(int32_t*) * (size_t)R);
         if (rc != LZG_OK) return rc;
@@ -189,25 +190,26 @@ static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n,
         LZM_CUDA(m, cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
         const int r0 = std::min(n_pad, g * blk), r1 = std::min(n_pad, r0 + blk), rows = r1 - r0;
         const int valid = std::max(0, std::min(n, r1) - r0);
-        uint8_t* dst = m->d_prof[g] + (size_t)r0 * l_pad;
+        uint8_t* dst = m->d_prof[g] + (size_t)r0 * pitch;
         if (rows > 0) {
-            if (is_i8) {
+            if (is_i8 && width == 1) {
                 if (valid > 0 && L > 0)
                     LZM_CUDA(m, cudaMemcpy2DAsync(dst, l_pad, (const int8_t*)host + (size_t)r0 * L, L, L, valid, cudaMemcpyHostToDevice, c->stream));
                 rc = lzg_bias_rows_i8(c, dst, L > 0 ? valid : 0, rows, L, l_pad);
             } else {
-                rc = lzg_fill_bytes(c, dst + (size_t)valid * l_pad, (size_t)(rows - valid) * l_pad, LZG_BIAS);
+                rc = lzg_fill_pad(c, dst + (size_t)valid * pitch, (size_t)(rows - valid) * pitch, width);
                 if (rc == LZG_OK && valid > 0 && L > 0) {
-                    const size_t row_bytes = (size_t)L * 4;
+                    const size_t row_bytes = (size_t)L * (is_i8 ? 1 : 4);
                     const int step = (int)std::max<size_t>(1, std::min<size_t>(valid, ((size_t)128 << 20) / row_bytes));
                     rc = grow(m, &m->d_stage[g], &m->stage_cap[g], (size_t)step * row_bytes);
                     for (int q = 0; rc == LZG_OK && q < valid; q += step) {
                         const int nr = std::min(step, valid - q);
                         LZM_CUDA(m, cudaMemcpyAsync(m->d_stage[g], (const uint8_t*)host + (size_t)(r0 + q) * row_bytes, (size_t)nr * row_bytes, cudaMemcpyHostToDevice, c->stream));
-                        rc = lzg_pack_rows_i32(c, (const int32_t*)m->d_stage[g], dst + (size_t)q * l_pad, nr, L, l_pad);
+                        if (is_i8) rc = lzg_pack_rows_i8_w2(c, (const int8_t*)m->d_stage[g], dst + (size_t)q * pitch, nr, L, l_pad);
+                        else rc = lzg_pack_rows_i32(c, (const int32_t*)m->d_stage[g], dst + (size_t)q * pitch, nr, L, l_pad, width);
                     }
                 } else if (rc == LZG_OK && valid > 0) {
-                    rc = lzg_fill_bytes(c, dst, (size_t)valid * l_pad, LZG_BIAS);
+                    rc = lzg_fill_pad(c, dst, (size_t)valid * pitch, width);
                 }
             }
             if (rc != LZG_OK) {
@@ -216,7 +218,7 @@ static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n,
             }
             for (int h = 0; h < G; h++) {
                 if (h == g) continue;
-                LZM_CUDA(m, cudaMemcpyPeerAsync(m->d_prof[h] + (size_t)r0 * l_pad, m->ctx[h]->device, dst, c->device, (size_t)rows * l_pad, c->stream));
+                LZM_CUDA(m, cudaMemcpyPeerAsync(m->d_prof[h] + (size_t)r0 * pitch, m->ctx[h]->device, dst, c->device, (size_t)rows * pitch, c->stream));
             }
         }
         LZM_CUDA(m, cudaEventRecord(m->ev_up[g], c->stream));
@@ -231,7 +233,7 @@ static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n,
         lzg_profiles p = shape;
         p.ctx = c;
         p.d = m->d_prof[g];
-        p.d_bytes = (size_t)n_pad * l_pad;
+        p.d_bytes = (size_t)n_pad * pitch;
         int64_t mine = 0;
         rc = lzg_distance_run(c, &p, g, G, 0, INT32_MAX, nullptr, &mine, m->d_table[g]);
         if (rc != LZG_OK) m->err = c->err;
@@ -258,9 +260,23 @@ static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n,
         if (rc == LZG_OK && (e1 != cudaSuccess || e2 != cudaSuccess)) rc = multi_fail(m, LZG_ERR_CUDA, "lzg_distance_matrix_multi", e1 != cudaSuccess ? e1 : e2);
         if (rc == LZG_OK && L > 0 && c->h_pinned[0]) out_of_range = true;
     }
-    if (rc == LZG_OK && out_of_range) rc = multi_fail(m, LZG_ERR_RANGE, "breakpoint value outside [-127, 127]");
+    if (rc == LZG_OK && out_of_range) *out_of_range_ = true;
     if (pairs_out) *pairs_out = pairs;
     return rc;
+}
+
+static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n, int32_t L, int32_t* D_host, int64_t* pairs_out) {
+    if (!m || n < 0 || L < 0 || (n > 0 && L > 0 && !host) || (n > 0 && !D_host)) return multi_fail(m, LZG_ERR_ARG, "lzg_distance_matrix_multi: bad argument");
+    if (pairs_out) *pairs_out = 0;
+    if (n == 0) return LZG_OK;
+    for (int width = 1; width <= 2; width++) {  // the 8-bit format first; its range flag sends wider data through the 16-bit one
+        bool out_of_range = false;
+        const int rc = distance_multi_width(m, host, is_i8, n, L, D_host, pairs_out, width, &out_of_range);
+        if (rc != LZG_OK) return rc;
+        if (!out_of_range) return LZG_OK;
+    }
+    if (pairs_out) *pairs_out = 0;
+    return multi_fail(m, LZG_ERR_RANGE, "breakpoint value outside [-32767, 32767]");
 }
 
 int lzg_distance_matrix_multi(lzg_multi* m, const int32_t* bp, int32_t n_cells, int32_t n_pos, int32_t* D_host, int64_t* pairs) {

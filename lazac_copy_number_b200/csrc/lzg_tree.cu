@@ -60,6 +60,41 @@ __device__ __forceinline__ uint32_t merge16(iv16& acc, const uint32_t* os, const
     return (c & 0xffffu) + (c >> 16);  // each lane <= 8 * 254
 }
 
+// ---- the two device formats behind one set of kernels (template parameter W = bytes per position) ----------------
+// A thread always owns one 16-byte chunk of a row: 16 positions widened to eight u16x2 words (W = 1), or 8 positions that
+// already ARE four u16x2 words (W = 2, values biased by 32768).  Row offsets and pitches are in bytes either way.
+template <int W>
+__device__ __forceinline__ void widen_w(const uint4& v, uint32_t* o) {
+    if (W == 1) {
+        widen(v, o);
+    } else {
+        o[0] = v.x, o[1] = v.y, o[2] = v.z, o[3] = v.w;
+    }
+}
+template <int W>
+__device__ __forceinline__ uint4 narrow_w(const uint32_t* o) {
+    if (W == 1) return narrow(o);
+    return make_uint4(o[0], o[1], o[2], o[3]);
+}
+// acc := merge(acc, other); returns the cost of the chunk.  16-bit lanes hold differences up to 65535, so their costs are
+// folded into 32 bits word by word; 8-bit data can add eight words per lane first (<= 8 * 254).
+template <int W>
+__device__ __forceinline__ uint32_t merge_w(iv16& acc, const uint32_t* os, const uint32_t* oe) {
+    if (W == 1) return merge16(acc, os, oe);
+    uint32_t c = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint32_t lo = __vmaxu2(acc.s[k], os[k]);
+        uint32_t hi = __vminu2(acc.e[k], oe[k]);
+        uint32_t st = __vminu2(lo, hi);
+        acc.e[k] = __vmaxu2(lo, hi);
+        acc.s[k] = st;
+        const uint32_t d = lo - st;  // per-lane lo >= st: no borrow between the lanes
+        c += (d & 0xffffu) + (d >> 16);
+    }
+    return c;
+}
+
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -68,18 +103,19 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 
 // ---- leaves ------------------------------------------------------------------------------------
 __global__ void k_gather_leaves(const uint8_t* __restrict__ prof, int prof_lpad, const int32_t* __restrict__ leaf_row,
-                                uint8_t* __restrict__ start, uint8_t* __restrict__ end, int l_pad) {
+                                uint8_t* __restrict__ start, uint8_t* __restrict__ end, int l_pad, uint32_t pad_word) {
     int u = blockIdx.y;
     int row = leaf_row[u];
     int chunk = blockIdx.x * blockDim.x + threadIdx.x;
     if (chunk * 16 >= l_pad) return;
     uint4 v = row >= 0 ? ldg16(prof, (size_t)row * prof_lpad + chunk * 16)
-                       : make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
+                       : make_uint4(pad_word, pad_word, pad_word, pad_word);
     *reinterpret_cast<uint4*>(start + (size_t)u * l_pad + chunk * 16) = v;
     *reinterpret_cast<uint4*>(end + (size_t)u * l_pad + chunk * 16) = v;
 }
 
 // ---- bottom-up, one launch per level (small_rectilinear, src/copy_number.cxx:227-277) -------------
+template <int W>
 __global__ void k_merge_level(const int32_t* __restrict__ order, const int32_t* __restrict__ child0,
                               const int32_t* __restrict__ child1, uint8_t* __restrict__ start,
                               uint8_t* __restrict__ end, int32_t* __restrict__ cost, int l_pad) {
@@ -92,14 +128,14 @@ __global__ void k_merge_level(const int32_t* __restrict__ order, const int32_t* 
         uint4 s0 = ldg16(start, o0), e0 = ldg16(end, o0), s1 = ldg16(start, o1), e1 = ldg16(end, o1);
         iv16 acc;
         uint32_t os[8], oe[8];
-        widen(s0, acc.s);
-        widen(e0, acc.e);
-        widen(s1, os);
-        widen(e1, oe);
-        c = merge16(acc, os, oe);
+        widen_w<W>(s0, acc.s);
+        widen_w<W>(e0, acc.e);
+        widen_w<W>(s1, os);
+        widen_w<W>(e1, oe);
+        c = merge_w<W>(acc, os, oe);
         size_t ou = (size_t)u * l_pad + chunk * 16;
-        *reinterpret_cast<uint4*>(start + ou) = narrow(acc.s);
-        *reinterpret_cast<uint4*>(end + ou) = narrow(acc.e);
+        *reinterpret_cast<uint4*>(start + ou) = narrow_w<W>(acc.s);
+        *reinterpret_cast<uint4*>(end + ou) = narrow_w<W>(acc.e);
     }
     c = warp_sum(c);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(cost + u, (int32_t)c);
@@ -123,6 +159,18 @@ __global__ void k_level_scores(const int32_t* __restrict__ order, const int32_t*
 }  // namespace
 
 #include "lzg_tree_nni.cuh"
+
+// launches a kernel template for the tree's device format
+#define LZG_BY_WIDTH(width_, ...)      \
+    do {                               \
+        if ((width_) == 2) {           \
+            constexpr int W = 2;       \
+            __VA_ARGS__;               \
+        } else {                       \
+            constexpr int W = 1;       \
+            __VA_ARGS__;               \
+        }                              \
+    } while (0)
 
 static inline int chunk_threads(int l_pad, int* groups) {
     int chunks = l_pad / 16;
@@ -157,7 +205,7 @@ int lzg_tree_upload_topology(lzg_ctx* ctx, lzg_tree* t) {
 int lzg_tree_gather_leaves(lzg_ctx* ctx, lzg_tree* t, const lzg_profiles* p, const int32_t* leaf_row) {
     LZG_CUDA(ctx, cudaMemcpyAsync(t->d_order, leaf_row, sizeof(int32_t) * t->n_nodes, cudaMemcpyHostToDevice, ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
-    k_gather_leaves<<<dim3(groups, t->n_nodes), threads, 0, ctx->stream>>>(p->d, p->l_pad, t->d_order, t->d_start, t->d_end, t->l_pad);
+    k_gather_leaves<<<dim3(groups, t->n_nodes), threads, 0, ctx->stream>>>(p->d, p->pitch, t->d_order, t->d_start, t->d_end, t->l_pad, t->width == 2 ? 0x80008000u : 0x80808080u);
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return LZG_OK;
@@ -205,8 +253,8 @@ int lzg_tree_full_score(lzg_ctx* ctx, lzg_tree* t) {
         int cnt = level_off[h + 1] - level_off[h];
         for (int done = 0; done < cnt; done += 65535) {  // gridDim.y limit
             int part = std::min(65535, cnt - done);
-            k_merge_level<<<dim3(groups, part), threads, 0, ctx->stream>>>(t->d_order + level_off[h] + done, t->d_child0, t->d_child1,
-                                                                           t->d_start, t->d_end, t->d_cost, t->l_pad);
+            LZG_BY_WIDTH(t->width, k_merge_level<W><<<dim3(groups, part), threads, 0, ctx->stream>>>(t->d_order + level_off[h] + done, t->d_child0, t->d_child1,
+                                                                                                    t->d_start, t->d_end, t->d_cost, t->l_pad));
             LZG_LAUNCH_CHECK(ctx);
         }
     }
@@ -408,7 +456,7 @@ static int launch_up_pass(lzg_ctx* ctx, lzg_tree* t, int groups, int threads) {
         A.uend = t->d_uend;
         A.ready = t->d_ready;
         A.ctl = t->d_cand;
-        k_up_pass<<<n_paths * groups, threads, 0, ctx->stream>>>(A);
+        LZG_BY_WIDTH(t->width, k_up_pass<W><<<n_paths * groups, threads, 0, ctx->stream>>>(A));
         LZG_LAUNCH_CHECK(ctx);
     }
     if (trace)
@@ -607,7 +655,7 @@ int lzg_tree_nni_launch(lzg_ctx* ctx, lzg_tree* t, int32_t n_moves, const int32_
     const auto t_launch = std::chrono::steady_clock::now();
     {
         const int gi = (t->l_pad + 256 * 16 - 1) / (256 * 16);
-        k_nni_items<16><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi);
+        LZG_BY_WIDTH(t->width, k_nni_items<16, W><<<n_items * gi, 256, 0, ctx->stream>>>(A, gi));
     }
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaEventRecord(ctx->ev_items, ctx->stream));
@@ -707,8 +755,8 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     }
     LZG_CUDA(ctx, cudaMemsetAsync(t->d_ctl, 0, sizeof(int32_t) * (LZG_CTL_INTS + (size_t)depth + 1), ctx->stream));
     int groups, threads = chunk_threads(t->l_pad, &groups);
-    k_apply_move<<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_score, t->d_cost, t->d_ctl,
-                                                      P, t->l_pad);
+    LZG_BY_WIDTH(t->width, k_apply_move<W><<<groups, threads, 0, ctx->stream>>>(t->d_child0, t->d_child1, t->d_up, t->d_start, t->d_end, t->d_score, t->d_cost,
+                                                                               t->d_ctl, P, t->l_pad));
     LZG_LAUNCH_CHECK(ctx);
     LZG_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, t->d_ctl, sizeof(int32_t) * LZG_CTL_INTS, cudaMemcpyDeviceToHost, ctx->stream));
     LZG_CUDA(ctx, cudaEventRecord(ctx->ev_group, ctx->stream));
@@ -725,7 +773,7 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     return LZG_OK;
 }
 
-static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, int L, int l_pad, int32_t* h_dst) {
+static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, int L, int l_pad, int32_t* h_dst, int width) {
     // convert on the device in row blocks of <= 64 MiB of int32, then copy out
     const size_t max_ints = (size_t)16 << 20;
     int block_rows = (int)std::max<size_t>(1, std::min<size_t>(rows, max_ints / std::max(1, L)));
@@ -734,7 +782,7 @@ static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, i
     for (int r0 = 0; r0 < rows; r0 += block_rows) {
         int nr = std::min(block_rows, rows - r0);
         dim3 grid(std::max(1, std::min(64, (L + 255) / 256)), nr);
-        k_unpack_i32<<<grid, 256, 0, ctx->stream>>>(d_src + (size_t)r0 * l_pad, d_tmp, L, l_pad);
+        LZG_BY_WIDTH(width, k_unpack_i32<W><<<grid, 256, 0, ctx->stream>>>(d_src + (size_t)r0 * l_pad, d_tmp, L, l_pad));
         ctx->launches++;
         cudaError_t e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaMemcpyAsync(h_dst + (size_t)r0 * L, d_tmp, sizeof(int32_t) * (size_t)nr * L, cudaMemcpyDeviceToHost, ctx->stream);
@@ -750,8 +798,8 @@ static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, i
 
 int lzg_tree_download(lzg_ctx* ctx, const lzg_tree* t, int32_t* start, int32_t* end, int32_t* score) {
     int rc = LZG_OK;
-    if (start) rc = download_bytes_as_i32(ctx, t->d_start, t->n_nodes, t->L, t->l_pad, start);
-    if (rc == LZG_OK && end) rc = download_bytes_as_i32(ctx, t->d_end, t->n_nodes, t->L, t->l_pad, end);
+    if (start) rc = download_bytes_as_i32(ctx, t->d_start, t->n_nodes, t->L, t->l_pad, start, t->width);
+    if (rc == LZG_OK && end) rc = download_bytes_as_i32(ctx, t->d_end, t->n_nodes, t->L, t->l_pad, end, t->width);
     if (rc == LZG_OK && score) {
         LZG_CUDA(ctx, cudaMemcpyAsync(score, t->d_score, sizeof(int32_t) * t->n_nodes, cudaMemcpyDeviceToHost, ctx->stream));
         LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -764,8 +812,8 @@ int lzg_tree_download_rows(lzg_ctx* ctx, const lzg_tree* t, int n_ids, const int
     for (int k = 0; k < n_ids; k++) {
         if (ids[k] < 0 || ids[k] >= t->n_nodes) return lzg_fail(ctx, LZG_ERR_ARG, "node id out of range");
         int rc = LZG_OK;
-        if (start) rc = download_bytes_as_i32(ctx, t->d_start + (size_t)ids[k] * t->l_pad, 1, t->L, t->l_pad, start + (size_t)k * t->L);
-        if (rc == LZG_OK && end) rc = download_bytes_as_i32(ctx, t->d_end + (size_t)ids[k] * t->l_pad, 1, t->L, t->l_pad, end + (size_t)k * t->L);
+        if (start) rc = download_bytes_as_i32(ctx, t->d_start + (size_t)ids[k] * t->l_pad, 1, t->L, t->l_pad, start + (size_t)k * t->L, t->width);
+        if (rc == LZG_OK && end) rc = download_bytes_as_i32(ctx, t->d_end + (size_t)ids[k] * t->l_pad, 1, t->L, t->l_pad, end + (size_t)k * t->L, t->width);
         if (rc != LZG_OK) return rc;
     }
     return LZG_OK;
@@ -804,8 +852,8 @@ int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* br
         int cnt = level_off[lv + 1] - level_off[lv];
         for (int done = 0; done < cnt; done += 65535) {
             int part = std::min(65535, cnt - done);
-            k_label_level<<<dim3(groups, part), threads, 0, ctx->stream>>>(t->d_order + level_off[lv] + done, t->d_up, t->d_start, t->d_end,
-                                                                           d_label, d_branch, t->l_pad);
+            LZG_BY_WIDTH(t->width, k_label_level<W><<<dim3(groups, part), threads, 0, ctx->stream>>>(t->d_order + level_off[lv] + done, t->d_up, t->d_start, t->d_end,
+                                                                                                    d_label, d_branch, t->l_pad));
             ctx->launches++;
         }
     }
@@ -813,7 +861,7 @@ int lzg_tree_label(lzg_ctx* ctx, const lzg_tree* t, int32_t* labels, int32_t* br
         e = cudaGetLastError();
         if (e != cudaSuccess) rc = lzg_fail(ctx, LZG_ERR_CUDA, "labeling launch", e);
     }
-    if (rc == LZG_OK && labels) rc = download_bytes_as_i32(ctx, d_label, n, t->L, t->l_pad, labels);
+    if (rc == LZG_OK && labels) rc = download_bytes_as_i32(ctx, d_label, n, t->L, t->l_pad, labels, t->width);
     if (rc == LZG_OK && branch) {
         e = cudaMemcpyAsync(branch, d_branch, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -893,7 +941,7 @@ int ensure_climb_buffers(lzg_ctx* ctx, lzg_tree* t, int n_items, int groups) {
 }
 
 struct climb_geometry {
-    int n_items, n_cand, groups, threads, up_grid, delta_grid, wl_grid, scan_grid, item_grid;
+    int n_items, n_cand, groups, threads, up_grid, delta_grid, wl_grid, scan_grid, item_grid, width;
 };
 
 enum { K_UP_FULL = 0, K_DIRTY, K_ITEMS, K_ASSEMBLE, K_ARGMIN, K_APPLY, K_UP_DELTA };
@@ -906,13 +954,13 @@ struct climb_launch {
 
 climb_launch climb_kernel(int which, const climb_geometry& G) {
     switch (which) {
-        case K_UP_FULL: return {(void*)k_up_df, dim3(G.up_grid), dim3(G.threads), false};
+        case K_UP_FULL: return {G.width == 2 ? (void*)k_up_df<2> : (void*)k_up_df<1>, dim3(G.up_grid), dim3(G.threads), false};
         case K_DIRTY: return {(void*)k_dirty_scan, dim3(G.scan_grid), dim3(256), false};
-        case K_ITEMS: return {(void*)k_items_wl, dim3(G.wl_grid), dim3(G.threads), false};
+        case K_ITEMS: return {G.width == 2 ? (void*)k_items_wl<2> : (void*)k_items_wl<1>, dim3(G.wl_grid), dim3(G.threads), false};
         case K_ASSEMBLE: return {(void*)k_cand_assemble, dim3(G.item_grid), dim3(256), false};
         case K_ARGMIN: return {(void*)k_nni_argmin<true>, dim3(1), dim3(1024), true};
-        case K_APPLY: return {(void*)k_apply2, dim3(G.groups), dim3(G.threads), false};
-        default: return {(void*)k_up_delta, dim3(G.delta_grid), dim3(G.threads), false};
+        case K_APPLY: return {G.width == 2 ? (void*)k_apply2<2> : (void*)k_apply2<1>, dim3(G.groups), dim3(G.threads), false};
+        default: return {G.width == 2 ? (void*)k_up_delta<2> : (void*)k_up_delta<1>, dim3(G.delta_grid), dim3(G.threads), false};
     }
 }
 
@@ -942,10 +990,10 @@ int climb_enqueue(lzg_ctx* ctx, const climb_geometry& G, const int* seq, int n_s
 // the loop condition.  The kernels read c_pass, so one graph serves every tree of this launch geometry.
 lzg_ctx::climb_graph* climb_graph_for(lzg_ctx* ctx, const climb_geometry& G) {
     for (auto& g : ctx->climb_graphs)
-        if (g.n_items == G.n_items && g.groups == G.groups && g.threads == G.threads && g.up_grid == G.up_grid && g.n_cand == G.n_cand) return &g;
+        if (g.n_items == G.n_items && g.groups == G.groups && g.threads == G.threads && g.up_grid == G.up_grid && g.n_cand == G.n_cand && g.width == G.width) return &g;
     if (ctx->climb_graph_broken) return nullptr;
     lzg_ctx::climb_graph cg;
-    cg.n_items = G.n_items, cg.groups = G.groups, cg.threads = G.threads, cg.up_grid = G.up_grid, cg.n_cand = G.n_cand;
+    cg.n_items = G.n_items, cg.groups = G.groups, cg.threads = G.threads, cg.up_grid = G.up_grid, cg.n_cand = G.n_cand, cg.width = G.width;
     static lzg_pass_args dummy{};
     auto add_chain = [&](cudaGraph_t graph, const int* seq, int n_seq, cudaGraphNode_t* last) -> cudaError_t {
         cudaGraphNode_t prev = nullptr;
@@ -1078,7 +1126,7 @@ int lzg_tree_climb(lzg_ctx* ctx, lzg_comm* comm, lzg_tree* t, int32_t n_edges, c
     }
     // ---- the descriptor (constant memory) and the control block ----
     climb_geometry G;
-    G.n_items = n_items, G.n_cand = n_cand, G.groups = groups, G.threads = threads;
+    G.n_items = n_items, G.n_cand = n_cand, G.groups = groups, G.threads = threads, G.width = t->width;
     const int per_sm = std::max(1, 1024 / threads);
     // persistent grids; functions of the data set only (one graph per data set)
     G.up_grid = std::max(1, std::min(n_items * groups, ctx->sm_count * per_sm));

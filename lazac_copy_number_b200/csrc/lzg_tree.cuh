@@ -8,7 +8,9 @@
 // subtree scores as int32.
 struct lzg_tree {
     lzg_ctx* ctx = nullptr;
-    int32_t n_nodes = 0, L = 0, l_pad = 0;
+    int32_t n_nodes = 0, L = 0;
+    int32_t l_pad = 0;   // BYTES per interval row (padded positions x bytes per position); a thread owns one 16-byte chunk of it
+    int32_t width = 1;   // bytes per position: the profiles' device format (lzg_profiles::width)
     std::vector<int32_t> child0, child1, parent;  // host mirror (child0 < child1, -1 for leaves)
     int32_t *d_child0 = nullptr, *d_child1 = nullptr;
     int2* d_up = nullptr;       // (parent, sibling) per node, (-1,-1) for the root

@@ -26,13 +26,14 @@ static void tree_release(lzg_tree* t) {
     delete t;
 }
 
-static int tree_alloc(lzg_ctx* ctx, int n_nodes, int L, int l_pad, lzg_tree** out) {
+static int tree_alloc(lzg_ctx* ctx, int n_nodes, int L, int l_pad, int width, lzg_tree** out) {
     lzg_tree* t = new (std::nothrow) lzg_tree();
     if (!t) return LZG_ERR_ARG;
     t->ctx = ctx;
     t->n_nodes = n_nodes;
     t->L = L;
     t->l_pad = l_pad;
+    t->width = width;
     const size_t nb = (size_t)n_nodes * l_pad;
     cudaError_t e = lzg_dev_alloc(ctx, (void**)&t->d_child0, sizeof(int32_t) * n_nodes);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&t->d_child1, sizeof(int32_t) * n_nodes);
@@ -105,7 +106,7 @@ int lzg_tree_create(lzg_ctx* ctx, const lzg_profiles* p, int32_t n_nodes, const 
             return lzg_fail(ctx, LZG_ERR_ARG, "leaf without a profile row");  // bad_optional_access in the reference
     }
     lzg_tree* t = nullptr;
-    int rc = tree_alloc(ctx, n_nodes, p->L, p->l_pad, &t);
+    int rc = tree_alloc(ctx, n_nodes, p->L, p->pitch, p->width, &t);
     if (rc != LZG_OK) return rc;
     rc = set_topology_host(ctx, t, child0, child1);
     if (rc == LZG_OK) rc = lzg_tree_upload_topology(ctx, t);
@@ -127,7 +128,7 @@ int lzg_tree_clone(lzg_ctx* ctx, const lzg_tree* s, lzg_tree** out) {
     *out = nullptr;
     LZG_CUDA(ctx, cudaSetDevice(ctx->device));
     lzg_tree* t = nullptr;
-    int rc = tree_alloc(ctx, s->n_nodes, s->L, s->l_pad, &t);
+    int rc = tree_alloc(ctx, s->n_nodes, s->L, s->l_pad, s->width, &t);
     if (rc != LZG_OK) return rc;
     t->child0 = s->child0;
     t->child1 = s->child1;

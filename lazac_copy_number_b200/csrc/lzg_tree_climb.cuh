@@ -68,6 +68,7 @@ __device__ __forceinline__ bool differs(const uint4& a, const uint4& b) {
 
 // ---- full UP pass, dataflow --------------------------------------------------------------------------
 // One heavy path x one chunk group.  head = first node of the path; its parent's UP row is published.
+template <int W>
 __device__ __forceinline__ void up_walk_df(const lzg_pass_args& A, int head, int g, int tid, int epoch) {
     const int chunk = g * blockDim.x + tid;
     const bool active = chunk * 16 < A.l_pad;
@@ -88,14 +89,14 @@ __device__ __forceinline__ void up_walk_df(const lzg_pass_args& A, int head, int
     if (active) {
         const uint4 ss = ldg16(A.start, sib * lp + off), se = ldg16(A.end, sib * lp + off);
         if (p != 0) {
-            widen(ldcg16(A.ustart, p * lp + off), acc.s);
-            widen(ldcg16(A.uend, p * lp + off), acc.e);
-            widen(ss, os);
-            widen(se, oe);
-            merge16(acc, os, oe);
+            widen_w<W>(ldcg16(A.ustart, p * lp + off), acc.s);
+            widen_w<W>(ldcg16(A.uend, p * lp + off), acc.e);
+            widen_w<W>(ss, os);
+            widen_w<W>(se, oe);
+            merge_w<W>(acc, os, oe);
         } else {
-            widen(ss, acc.s);
-            widen(se, acc.e);
+            widen_w<W>(ss, acc.s);
+            widen_w<W>(se, acc.e);
         }
     }
     int a = head;
@@ -106,8 +107,8 @@ __device__ __forceinline__ void up_walk_df(const lzg_pass_args& A, int head, int
             if (active) l2s = ldg16(A.start, nb.y * lp + off), l2e = ldg16(A.end, nb.y * lp + off);
         }
         if (active) {
-            *reinterpret_cast<uint4*>(A.ustart + a * lp + off) = narrow(acc.s);
-            *reinterpret_cast<uint4*>(A.uend + a * lp + off) = narrow(acc.e);
+            *reinterpret_cast<uint4*>(A.ustart + a * lp + off) = narrow_w<W>(acc.s);
+            *reinterpret_cast<uint4*>(A.uend + a * lp + off) = narrow_w<W>(acc.e);
         }
         if (na.z & 2) {  // the light child is internal: its path may start (uniform over the CTA)
             __syncthreads();
@@ -118,9 +119,9 @@ __device__ __forceinline__ void up_walk_df(const lzg_pass_args& A, int head, int
         }
         if (!(na.z & 1)) break;  // the heavy child is a leaf: end of the path
         if (active) {
-            widen(l1s, os);
-            widen(l1e, oe);
-            merge16(acc, os, oe);
+            widen_w<W>(l1s, os);
+            widen_w<W>(l1e, oe);
+            merge_w<W>(acc, os, oe);
         }
         a = na.x;
         na = nb;
@@ -133,6 +134,7 @@ __device__ __forceinline__ void up_walk_df(const lzg_pass_args& A, int head, int
 // Persistent CTAs.  Self-resetting: the last CTA to leave zeroes the ticket and the tails, so the next
 // full pass needs no memset.  A wait that lasts implausibly long (a path count that does not match the
 // node4 records would leave a ticket without a producer) raises STOP = 4 instead of hanging the GPU.
+template <int W>
 __global__ void __launch_bounds__(256)
 k_up_df() {
     const lzg_pass_args& A = c_pass;
@@ -171,7 +173,7 @@ k_up_df() {
             __syncthreads();
             head = s_head;
         }
-        if (head >= 0) up_walk_df(A, head, g, tid, epoch);
+        if (head >= 0) up_walk_df<W>(A, head, g, tid, epoch);
         __syncthreads();  // s_ticket / s_head are rewritten by the next round
     }
     if (tid == 0) {
@@ -200,13 +202,14 @@ __device__ __forceinline__ void uq_push(const lzg_pass_args& A, int stamp, int n
 #define LZG_PATH_CAP 1024  // steps of the path kept in shared memory; longer paths continue in global scratch
 
 // The move is the winner k_nni_argmin left in ctl[BEST].  One CTA per chunk group.
+template <int W>
 __global__ void __launch_bounds__(256)
 k_apply2() {
     const lzg_pass_args& A = c_pass;
     __shared__ int2 s_path[LZG_PATH_CAP];  // (node written, sibling merged) per step
     __shared__ int32_t s_term[LZG_PATH_CAP];
     __shared__ int32_t s_chg[LZG_PATH_CAP];
-    __shared__ int s_is_last;
+    __shared__ int s_is_last, s_steps;
     const int tid = threadIdx.x, g = blockIdx.x;
     if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
     const int stamp = __ldcg(A.ctl + LZG_CTL_EPOCH);
@@ -225,74 +228,84 @@ k_apply2() {
     int32_t* const deep_chg = A.deep_chg + (size_t)g * A.n_nodes;
     iv16 acc;
     uint32_t os[8], oe[8];
-    // (parent, sibling) two steps ahead of the merge; the entries from u upwards are not touched by the move
-    int2 e1 = A.up[u];
-    int2 e2 = e1.x >= 0 ? A.up[e1.x] : make_int2(-1, -1);
-    uint4 ys = z4, ye = z4, zs = z4, ze = z4, q1s = z4, q1e = z4, q2s = z4, q2e = z4;
-    uint4 ovs = z4, ove = z4, ous = z4, oue = z4, o1s = z4, o1e = z4, o2s = z4, o2e = z4;  // the rows about to be overwritten
-    if (active) {
-        widen(ldg16(A.start, w * lp + off), acc.s);
-        widen(ldg16(A.end, w * lp + off), acc.e);
-        ys = ldg16(A.start, y * lp + off), ye = ldg16(A.end, y * lp + off);
-        zs = ldg16(A.start, z * lp + off), ze = ldg16(A.end, z * lp + off);
-        ovs = ldg16(A.start, v * lp + off), ove = ldg16(A.end, v * lp + off);
-        ous = ldg16(A.start, u * lp + off), oue = ldg16(A.end, u * lp + off);
-        if (e1.x >= 0) {
-            q1s = ldg16(A.start, e1.y * lp + off), q1e = ldg16(A.end, e1.y * lp + off);
-            o1s = ldg16(A.start, e1.x * lp + off), o1e = ldg16(A.end, e1.x * lp + off);
+    for (int q = tid; q < LZG_PATH_CAP; q += blockDim.x) s_term[q] = 0, s_chg[q] = 0;
+    // Phase 1: the path v, u, parent(u), .. root with the sibling merged at every step, listed by following the
+    // (parent, sibling) table -- one dependent L2 load per step, nothing else waits on it.  The entries from u
+    // upwards are not touched by the move.  Every row the walk will touch is then requested into L2 at once
+    // (one prefetch per 128-byte line), so the walk itself runs on L2 hits instead of paying a DRAM round trip
+    // per step (36 us -> the L2 latency x depth at cfg5's size).
+    int n_steps = 2;
+    if (tid == 0) {
+        s_path[0] = make_int2(v, y);
+        s_path[1] = make_int2(u, z);
+        int a = u;
+        for (;;) {
+            const int2 e = A.up[a];
+            if (e.x < 0) break;
+            if (n_steps < LZG_PATH_CAP) s_path[n_steps] = e;
+            else deep_path[n_steps] = e;
+            n_steps++;
+            a = e.x;
+        }
+        s_steps = n_steps;
+    }
+    __syncthreads();
+    n_steps = s_steps;
+    auto path_at = [&](int q) -> int2 { return q < LZG_PATH_CAP ? s_path[q] : __ldcg(deep_path + q); };
+    if (active && (tid & 7) == 0) {
+        for (int q = 0; q < n_steps; q++) {
+            const int2 pq = path_at(q);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.start + pq.x * lp + off));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.end + pq.x * lp + off));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.start + pq.y * lp + off));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.end + pq.y * lp + off));
         }
     }
-    for (int q = tid; q < LZG_PATH_CAP; q += blockDim.x) s_term[q] = 0, s_chg[q] = 0;
-    __syncthreads();
-    int k = 0;
-    // step k: node = merge(running interval, other); costs and "changed" flags are fire-and-forget
-    // shared-memory reductions (no shuffle chain in the walk), read back once the walk is over
-    auto step = [&](int node, int other, const uint4& rs, const uint4& re, const uint4& olds, const uint4& olde) {
+    // Phase 2: the walk.  Rows of step k + 2 are requested while step k merges.
+    uint4 r0s = z4, r0e = z4, o0s = z4, o0e = z4, r1s = z4, r1e = z4, o1s = z4, o1e = z4, r2s = z4, r2e = z4, o2s = z4, o2e = z4;
+    auto load_step = [&](int q, uint4& rs, uint4& re, uint4& os_, uint4& oe_) {
+        if (q < n_steps && active) {
+            const int2 pq = path_at(q);
+            rs = ldg16(A.start, pq.y * lp + off), re = ldg16(A.end, pq.y * lp + off);        // the sibling merged in
+            os_ = ldg16(A.start, pq.x * lp + off), oe_ = ldg16(A.end, pq.x * lp + off);      // the row about to be overwritten
+        }
+    };
+    if (active) {
+        widen_w<W>(ldg16(A.start, w * lp + off), acc.s);
+        widen_w<W>(ldg16(A.end, w * lp + off), acc.e);
+    }
+    load_step(0, r0s, r0e, o0s, o0e);
+    load_step(1, r1s, r1e, o1s, o1e);
+    for (int k = 0; k < n_steps; k++) {
+        load_step(k + 2, r2s, r2e, o2s, o2e);
+        const int2 pq = path_at(k);
+        // step k: node = merge(running interval, sibling); costs and "changed" flags are fire-and-forget
+        // shared-memory reductions (no shuffle chain in the walk), read back once the walk is over
         uint32_t c = 0;
         bool chg = false;
         if (active) {
-            widen(rs, os);
-            widen(re, oe);
-            c = merge16(acc, os, oe);
-            const uint4 ns = narrow(acc.s), ne = narrow(acc.e);
-            chg = differs(ns, olds) || differs(ne, olde);
-            *reinterpret_cast<uint4*>(A.wstart + node * lp + off) = ns;
-            *reinterpret_cast<uint4*>(A.wend + node * lp + off) = ne;
+            widen_w<W>(r0s, os);
+            widen_w<W>(r0e, oe);
+            c = merge_w<W>(acc, os, oe);
+            const uint4 ns = narrow_w<W>(acc.s), ne = narrow_w<W>(acc.e);
+            chg = differs(ns, o0s) || differs(ne, o0e);
+            *reinterpret_cast<uint4*>(A.wstart + pq.x * lp + off) = ns;
+            *reinterpret_cast<uint4*>(A.wend + pq.x * lp + off) = ne;
         }
         if (k < LZG_PATH_CAP) {
             c = __reduce_add_sync(0xffffffffu, c);  // one REDUX per warp: 256 same-address shared atomics would serialise
             if ((tid & 31) == 0 && c) atomicAdd(&s_term[k], (int32_t)c);
             if (chg) s_chg[k] = 1;
-            if (tid == 0) s_path[k] = make_int2(node, other);
         } else {
             c = warp_sum(c);
-            if ((tid & 31) == 0 && c) atomicAdd(A.pcost + node, (int32_t)c);
+            if ((tid & 31) == 0 && c) atomicAdd(A.pcost + pq.x, (int32_t)c);
             if (chg) deep_chg[k] = 1;
-            if (tid == 0) deep_path[k] = make_int2(node, other);
         }
-        k++;
-    };
-    step(v, y, ys, ye, ovs, ove);  // the new v = merge(w, y)
-    step(u, z, zs, ze, ous, oue);  // the new u = merge(v, z)
-    while (e1.x >= 0) {
-        int2 e3 = make_int2(-1, -1);
-        if (e2.x >= 0) {
-            e3 = A.up[e2.x];
-            if (active) {
-                q2s = ldg16(A.start, e2.y * lp + off), q2e = ldg16(A.end, e2.y * lp + off);
-                o2s = ldg16(A.start, e2.x * lp + off), o2e = ldg16(A.end, e2.x * lp + off);
-            }
-        }
-        step(e1.x, e1.y, q1s, q1e, o1s, o1e);
-        e1 = e2;
-        e2 = e3;
-        q1s = q2s, q1e = q2e;
-        o1s = o2s, o1e = o2e;
+        r0s = r1s, r0e = r1e, o0s = o1s, o0e = o1e;
+        r1s = r2s, r1e = r2e, o1s = o2s, o1e = o2e;
     }
-    const int n_steps = k;
-    __threadfence();  // the deep-path records of this CTA, read back below by other threads of it
+    __threadfence();  // the deep-path flags of this CTA, read back below by other threads of it
     __syncthreads();
-    auto path_at = [&](int q) -> int2 { return q < LZG_PATH_CAP ? s_path[q] : deep_path[q]; };
     // this chunk group's share: costs, stamps of the rows that changed, UP rows to recompute
     for (int q = tid; q < n_steps; q += blockDim.x) {
         const bool chg = q < LZG_PATH_CAP ? s_chg[q] != 0 : __ldcg(deep_chg + q) != 0;
@@ -395,6 +408,7 @@ k_apply2() {
 // DOWN(sibling); if the row comes out different (or the unit is forced) its internal children follow: the
 // heavy one in registers, the light one through the queue.  A CTA leaves when every pushed unit is done
 // (done is read before pushed: pushed only grows and done <= pushed, so equality means nothing is in flight).
+template <int W>
 __global__ void __launch_bounds__(256)
 k_up_delta() {
     const lzg_pass_args& A = c_pass;
@@ -439,14 +453,14 @@ k_up_delta() {
         if (active) {
             const uint4 ss = ldg16(A.start, sib * lp + off), se = ldg16(A.end, sib * lp + off);
             if (p != 0) {
-                widen(ldcg16(A.ustart, p * lp + off), acc.s);
-                widen(ldcg16(A.uend, p * lp + off), acc.e);
-                widen(ss, os);
-                widen(se, oe);
-                merge16(acc, os, oe);
+                widen_w<W>(ldcg16(A.ustart, p * lp + off), acc.s);
+                widen_w<W>(ldcg16(A.uend, p * lp + off), acc.e);
+                widen_w<W>(ss, os);
+                widen_w<W>(se, oe);
+                merge_w<W>(acc, os, oe);
             } else {
-                widen(ss, acc.s);
-                widen(se, acc.e);
+                widen_w<W>(ss, acc.s);
+                widen_w<W>(se, acc.e);
             }
         }
         for (;;) {
@@ -454,7 +468,7 @@ k_up_delta() {
             bool chg = false;
             uint4 ns = make_uint4(0, 0, 0, 0), ne = ns;
             if (active) {
-                ns = narrow(acc.s), ne = narrow(acc.e);
+                ns = narrow_w<W>(acc.s), ne = narrow_w<W>(acc.e);
                 chg = differs(ns, ldcg16(A.ustart, x * lp + off)) || differs(ne, ldcg16(A.uend, x * lp + off));
             }
             const int any = __syncthreads_or(chg);
@@ -472,9 +486,9 @@ k_up_delta() {
             }
             if (!(nx.z & 1)) break;
             if (active) {  // continue with the heavy child: UP(heavy) = merge(UP(x), DOWN(light))
-                widen(ldg16(A.start, nx.y * lp + off), os);
-                widen(ldg16(A.end, nx.y * lp + off), oe);
-                merge16(acc, os, oe);
+                widen_w<W>(ldg16(A.start, nx.y * lp + off), os);
+                widen_w<W>(ldg16(A.end, nx.y * lp + off), oe);
+                merge_w<W>(acc, os, oe);
             }
             x = nx.x;
             force = false;  // a forced unit (v) recomputes BOTH children whatever came out for v; below them the wave decides
@@ -517,6 +531,7 @@ k_dirty_scan() {
 // ---- re-score the listed (item, chunk group) pairs ----------------------------------------------------------------
 // Persistent CTAs of `threads` threads (the chunk-group width of the UP / apply kernels).  Position sums
 // only: the cumulative-score terms are added per pass by k_cand_assemble.
+template <int W>
 __global__ void __launch_bounds__(256, 4)
 k_items_wl() {
     const lzg_pass_args& A = c_pass;
@@ -536,8 +551,13 @@ k_items_wl() {
         const size_t off = ((size_t)g * blockDim.x + tid) * 16;
         int32_t pA = 0, pB = 0;
         if (off < (size_t)A.l_pad) {
-            if (u) score_pair<16, true>(A, u, w, a, b, off, pA, pB);
-            else score_pair<16, false>(A, u, w, a, b, off, pA, pB);
+            if (W == 1) {
+                if (u) score_pair<16, true>(A, u, w, a, b, off, pA, pB);
+                else score_pair<16, false>(A, u, w, a, b, off, pA, pB);
+            } else {
+                if (u) score_pair_w2<true>(A, u, w, a, b, off, pA, pB);
+                else score_pair_w2<false>(A, u, w, a, b, off, pA, pB);
+            }
         }
         pA = warp_sum_i(pA);
         pB = warp_sum_i(pB);

@@ -59,6 +59,7 @@ struct lzg_apply_args {
     int node[LZG_APPLY_LISTED], other[LZG_APPLY_LISTED];
 };
 
+template <int W>
 __global__ void __launch_bounds__(256)
 k_apply_move(int32_t* child0, int32_t* child1, int2* up, uint8_t* __restrict__ start, uint8_t* __restrict__ end,
              int32_t* __restrict__ score, int32_t* __restrict__ path_cost, int* __restrict__ ctl, const lzg_apply_args P, int l_pad) {
@@ -71,8 +72,8 @@ k_apply_move(int32_t* child0, int32_t* child1, int2* up, uint8_t* __restrict__ s
     uint32_t os[8], oe[8];
     uint4 s0 = z4, e0 = z4, s1 = z4, e1 = z4, s2 = z4, e2 = z4;
     if (active) {
-        widen(ldg16(start, (size_t)P.w * l_pad + off), acc.s);
-        widen(ldg16(end, (size_t)P.w * l_pad + off), acc.e);
+        widen_w<W>(ldg16(start, (size_t)P.w * l_pad + off), acc.s);
+        widen_w<W>(ldg16(end, (size_t)P.w * l_pad + off), acc.e);
         s0 = ldg16(start, (size_t)P.other[0] * l_pad + off), e0 = ldg16(end, (size_t)P.other[0] * l_pad + off);
         if (n_listed > 1) s1 = ldg16(start, (size_t)P.other[1] * l_pad + off), e1 = ldg16(end, (size_t)P.other[1] * l_pad + off);
     }
@@ -90,11 +91,11 @@ k_apply_move(int32_t* child0, int32_t* child1, int2* up, uint8_t* __restrict__ s
         }
         uint32_t c = 0;
         if (active) {
-            widen(s0, os);
-            widen(e0, oe);
-            c = merge16(acc, os, oe);
-            *reinterpret_cast<uint4*>(start + (size_t)a * l_pad + off) = narrow(acc.s);
-            *reinterpret_cast<uint4*>(end + (size_t)a * l_pad + off) = narrow(acc.e);
+            widen_w<W>(s0, os);
+            widen_w<W>(e0, oe);
+            c = merge_w<W>(acc, os, oe);
+            *reinterpret_cast<uint4*>(start + (size_t)a * l_pad + off) = narrow_w<W>(acc.s);
+            *reinterpret_cast<uint4*>(end + (size_t)a * l_pad + off) = narrow_w<W>(acc.e);
         }
         c = warp_sum(c);
         if ((threadIdx.x & 31) == 0 && c) atomicAdd(path_cost + k, (int32_t)c);
@@ -140,6 +141,7 @@ k_apply_move(int32_t* child0, int32_t* child1, int2* up, uint8_t* __restrict__ s
 // ---- top-down labeling (local_labeling / ancestral_labeling, src/copy_number.cxx:165-225) ---------
 // label[root] = start[root]; label[c] = clamp(label[parent], start[c], end[c]);
 // branch[c] = sum |label[c] - label[parent]|.  One launch per depth level, root first.
+template <int W>
 __global__ void k_label_level(const int32_t* __restrict__ order, const int2* __restrict__ up, const uint8_t* __restrict__ start,
                               const uint8_t* __restrict__ end, uint8_t* __restrict__ label, int32_t* __restrict__ branch, int l_pad) {
     int u = order[blockIdx.y];
@@ -155,17 +157,18 @@ __global__ void k_label_level(const int32_t* __restrict__ order, const int2* __r
             uint4 e4 = ldg16(end, ou);
             uint4 p4 = *reinterpret_cast<const uint4*>(label + (size_t)p * l_pad + chunk * 16);
             uint32_t s[8], e[8], pl[8], out[8];
-            widen(s4, s);
-            widen(e4, e);
-            widen(p4, pl);
+            widen_w<W>(s4, s);
+            widen_w<W>(e4, e);
+            widen_w<W>(p4, pl);
 #pragma unroll
-            for (int k = 0; k < 8; k++) {
+            for (int k = 0; k < (W == 1 ? 8 : 4); k++) {
                 uint32_t x = __vminu2(__vmaxu2(pl[k], s[k]), e[k]);
                 out[k] = x;
-                c += __vmaxu2(x, pl[k]) - __vminu2(x, pl[k]);
+                const uint32_t d = __vmaxu2(x, pl[k]) - __vminu2(x, pl[k]);
+                c += W == 1 ? d : (d & 0xffffu) + (d >> 16);  // 16-bit lanes: fold every word (differences up to 65535)
             }
-            c = (c & 0xffffu) + (c >> 16);
-            *reinterpret_cast<uint4*>(label + ou) = narrow(out);
+            if (W == 1) c = (c & 0xffffu) + (c >> 16);
+            *reinterpret_cast<uint4*>(label + ou) = narrow_w<W>(out);
         }
     }
     c = warp_sum(c);
@@ -174,11 +177,14 @@ __global__ void k_label_level(const int32_t* __restrict__ order, const int2* __r
 
 #include "lzg_tree_climb.cuh"
 
-// biased bytes [rows][l_pad] -> int32 [rows][L]
+// biased bytes / 16-bit words [rows][l_pad bytes] -> int32 [rows][L]
+template <int W>
 __global__ void k_unpack_i32(const uint8_t* __restrict__ src, int32_t* __restrict__ dst, int L, int l_pad) {
     int r = blockIdx.y;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < L; k += gridDim.x * blockDim.x)
-        dst[(size_t)r * L + k] = (int32_t)src[(size_t)r * l_pad + k] - LZG_BIAS;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < L; k += gridDim.x * blockDim.x) {
+        if (W == 1) dst[(size_t)r * L + k] = (int32_t)src[(size_t)r * l_pad + k] - LZG_BIAS;
+        else dst[(size_t)r * L + k] = (int32_t)reinterpret_cast<const uint16_t*>(src + (size_t)r * l_pad)[k] - LZG_BIAS16;
+    }
 }
 
 }  // namespace

@@ -98,6 +98,7 @@ enum { LZG_ORDER_PUBLISH = 1 << 30, LZG_ORDER_NODE = LZG_ORDER_PUBLISH - 1 };
 
 // One heavy path x one chunk group: UP(a) for every node a of the path, top-down, running
 // interval in registers; sibling intervals are prefetched two nodes ahead.
+template <int W>
 __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int tid) {
     const int g = item % A.groups, p = item / A.groups;
     const int chunk = g * blockDim.x + tid;
@@ -128,15 +129,15 @@ __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int 
         }
         __syncthreads();
         if (active) {
-            widen(ldcg16(A.ustart, (size_t)pr.z * l_pad + off), acc.s);
-            widen(ldcg16(A.uend, (size_t)pr.z * l_pad + off), acc.e);
-            widen(ss, os);
-            widen(se, oe);
-            merge16(acc, os, oe);
+            widen_w<W>(ldcg16(A.ustart, (size_t)pr.z * l_pad + off), acc.s);
+            widen_w<W>(ldcg16(A.uend, (size_t)pr.z * l_pad + off), acc.e);
+            widen_w<W>(ss, os);
+            widen_w<W>(se, oe);
+            merge_w<W>(acc, os, oe);
         }
     } else if (active) {
-        widen(ss, acc.s);
-        widen(se, acc.e);
+        widen_w<W>(ss, acc.s);
+        widen_w<W>(se, acc.e);
     }
     for (int k = k0;; k++) {
         int2 nx3 = make_int2(0, 0);
@@ -148,8 +149,8 @@ __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int 
             if (k + 3 < k1) nx3 = A.order[k + 3];
         }
         if (active) {
-            *reinterpret_cast<uint4*>(A.ustart + (size_t)cur.x * l_pad + off) = narrow(acc.s);
-            *reinterpret_cast<uint4*>(A.uend + (size_t)cur.x * l_pad + off) = narrow(acc.e);
+            *reinterpret_cast<uint4*>(A.ustart + (size_t)cur.x * l_pad + off) = narrow_w<W>(acc.s);
+            *reinterpret_cast<uint4*>(A.uend + (size_t)cur.x * l_pad + off) = narrow_w<W>(acc.e);
         }
         if (cur.y & LZG_ORDER_PUBLISH) {  // a path head hangs off this node (uniform over the CTA)
             __syncthreads();
@@ -157,9 +158,9 @@ __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int 
         }
         if (k + 1 >= k1) break;
         if (active) {
-            widen(n1s, os);
-            widen(n1e, oe);
-            merge16(acc, os, oe);
+            widen_w<W>(n1s, os);
+            widen_w<W>(n1e, oe);
+            merge_w<W>(acc, os, oe);
         }
         cur = nx1;
         nx1 = nx2;
@@ -170,12 +171,13 @@ __device__ __forceinline__ void walk_path(const lzg_pass_args& A, int item, int 
 }
 
 
+template <int W>
 __global__ void __launch_bounds__(256)
 k_up_pass(const lzg_pass_args A) {
     __shared__ int s_item;
     if (threadIdx.x == 0) s_item = atomicAdd(A.ctl + LZG_CTL_TICKET, 1);
     __syncthreads();
-    walk_path(A, s_item, threadIdx.x);
+    walk_path<W>(A, s_item, threadIdx.x);
 }
 
 // ---- items -------------------------------------------------------------------------------------------
@@ -269,7 +271,55 @@ __device__ __forceinline__ void score_pair(const lzg_pass_args& A, int u, int w,
     pB = (int32_t)((cB & 0xffffu) + (cB >> 16)) - z;
 }
 
-template <int CPT>
+// The same on 16-bit positions (W = 2): a 16-byte chunk holds 8 positions that already are four u16x2 words, so nothing
+// is widened; lanes reach 65535, so an interval end is max(lo, hi) (lo + hi would overflow the lane), the distance to
+// UP(u) is (max(s, ue) - ue) + (max(us, e) - e) (at most one term is positive) and every word's costs are folded into
+// 32 bits at once.  The plain form: the path exists for value ranges no named configuration has.
+__device__ __forceinline__ uint32_t fold16(uint32_t d) { return (d & 0xffffu) + (d >> 16); }
+
+template <bool HAS_UP>
+__device__ __forceinline__ void score_pair_w2(const lzg_pass_args& A, int u, int w, int a, int b, size_t off, int32_t& pA, int32_t& pB) {
+    const size_t lp = (size_t)A.l_pad;
+    lzg_vec<16> row[HAS_UP ? 10 : 6];
+    row[0] = ldg_vec<16>(A.start + w * lp + off), row[1] = ldg_vec<16>(A.end + w * lp + off);
+    row[2] = ldg_vec<16>(A.start + a * lp + off), row[3] = ldg_vec<16>(A.end + a * lp + off);
+    row[4] = ldg_vec<16>(A.start + b * lp + off), row[5] = ldg_vec<16>(A.end + b * lp + off);
+    if (HAS_UP) {
+        row[6] = ldg_vec<16>(A.start + u * lp + off), row[7] = ldg_vec<16>(A.end + u * lp + off);
+        row[8] = ldg_vec<16>(A.ustart + u * lp + off), row[9] = ldg_vec<16>(A.uend + u * lp + off);
+    }
+    uint32_t cA = 0, cB = 0, c0 = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const uint32_t ws = row[0].w[q], we = row[1].w[q], as = row[2].w[q], ae = row[3].w[q], bs = row[4].w[q], be = row[5].w[q];
+        uint32_t ds = 0, de = 0, us = 0, ue = 0;
+        if (HAS_UP) ds = row[6].w[q], de = row[7].w[q], us = row[8].w[q], ue = row[9].w[q];
+        auto gap = [&](uint32_t s, uint32_t e) {  // distance between [s, e] and UP(u) = [us, ue]
+            return fold16(__vmaxu2(s, ue) - ue) + fold16(__vmaxu2(us, e) - e);
+        };
+        {   // z = a: v keeps b -- merge(w, b), then a, then UP(u)
+            const uint32_t lo1 = __vmaxu2(ws, bs), hi1 = __vminu2(we, be);
+            const uint32_t s1 = __vminu2(lo1, hi1), e1 = __vmaxu2(lo1, hi1);
+            const uint32_t lo2 = __vmaxu2(s1, as), hi2 = __vminu2(e1, ae);
+            const uint32_t s2 = __vminu2(lo2, hi2), e2 = __vmaxu2(lo2, hi2);
+            cA += fold16(lo1 - s1) + fold16(lo2 - s2);
+            if (HAS_UP) cA += gap(s2, e2);
+        }
+        {   // z = b: v keeps a
+            const uint32_t lo1 = __vmaxu2(ws, as), hi1 = __vminu2(we, ae);
+            const uint32_t s1 = __vminu2(lo1, hi1), e1 = __vmaxu2(lo1, hi1);
+            const uint32_t lo2 = __vmaxu2(s1, bs), hi2 = __vminu2(e1, be);
+            const uint32_t s2 = __vminu2(lo2, hi2), e2 = __vmaxu2(lo2, hi2);
+            cB += fold16(lo1 - s1) + fold16(lo2 - s2);
+            if (HAS_UP) cB += gap(s2, e2);
+        }
+        if (HAS_UP) c0 += gap(ds, de);  // the current tree re-rooted above u
+    }
+    pA = (int32_t)cA - (int32_t)c0;
+    pB = (int32_t)cB - (int32_t)c0;
+}
+
+template <int CPT, int W>
 __global__ void __launch_bounds__(256, 4)  // 64 registers: four CTAs per SM (three at 72-80 registers were 10 % slower, five spill)
 k_nni_items(const lzg_pass_args A, int groups_i) {
     const int tid = threadIdx.x;
@@ -282,8 +332,13 @@ k_nni_items(const lzg_pass_args A, int groups_i) {
     if (tid == 0 && blockIdx.x == 0) A.ctl[LZG_CTL_ROOT] = A.score[0];
     int32_t pA = 0, pB = 0;
     if (off < (size_t)A.l_pad) {
-        if (u) score_pair<CPT, true>(A, u, w, a, b, off, pA, pB);
-        else score_pair<CPT, false>(A, u, w, a, b, off, pA, pB);
+        if (W == 1) {
+            if (u) score_pair<CPT, true>(A, u, w, a, b, off, pA, pB);
+            else score_pair<CPT, false>(A, u, w, a, b, off, pA, pB);
+        } else {
+            if (u) score_pair_w2<true>(A, u, w, a, b, off, pA, pB);
+            else score_pair_w2<false>(A, u, w, a, b, off, pA, pB);
+        }
     }
     pA = warp_sum_i(pA) + base;
     pB = warp_sum_i(pB) + base;

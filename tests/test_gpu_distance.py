@@ -36,8 +36,9 @@ def test_distance_int8_upload(ctx, port):
 
 
 def test_range_error(ctx):
+    """Values beyond the 16-bit device format (tests/test_gpu_int16.py covers everything up to it)."""
     bp = np.zeros((4, 10), np.int32)
-    bp[2, 3] = 128
+    bp[2, 3] = 32768
     with pytest.raises(LazacGpuError) as e:
         Profiles(ctx, bp)
     assert e.value.status == 3
@@ -102,12 +103,13 @@ def test_repeated_upload_free_cycles(ctx, port):
         prof.free()
 
 
-def test_int8_minus_128_is_out_of_range(ctx):
+def test_int8_minus_128_uses_the_wide_format(ctx):
     bp = np.zeros((3, 40), np.int8)
     bp[1, 39] = -128
-    with pytest.raises(LazacGpuError) as e:
-        Profiles(ctx, bp)
-    assert e.value.status == 3
+    prof = Profiles(ctx, bp)
+    D = prof.distance_matrix()
+    prof.free()
+    assert D[1, 0] == 128 and D[0, 2] == 0
 
 
 def test_tile_orders_give_the_same_matrix(port, monkeypatch):

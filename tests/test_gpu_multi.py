@@ -31,7 +31,7 @@ def test_one_device_row_table_path(port, n, L, dtype):
 def test_range_and_empty(port):
     with MultiContext([0]) as m:
         bad = np.zeros((5, 40), np.int32)
-        bad[3, 7] = 200
+        bad[3, 7] = 40000
         with pytest.raises(LazacGpuError) as e:
             m.distance_matrix(bad)
         assert e.value.status == 3
