@@ -314,7 +314,7 @@ def run_reference(args):
                                   "seed_tree": "Clearcut-exact NJ (CPU, liblazac_host.so) of the C port's distance matrix, %g x internal edges random NNIs" % PERTURB,
                                   "step": "one whole neighbourhood through the reference's candidate loop (nni, unvisit, small_rectilinear, undo per candidate)"},
                        "cpu_baseline": {"value": tot_c / tot_t, "unit": "candidates/s", "cores": 1, "kind": kind, "sample": "whole neighbourhoods of cfg4's tree"}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---- NNI: the device-side hill climb ------------------------------------------------------------------------
@@ -577,7 +577,7 @@ def nni_section_sharded(ctx, args, rank, world, peaks, peaks_kind):
 
 
 # ---- distance ---------------------------------------------------------------------------------------------------------
-def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu):
+def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu, host_pg=None):
     """One distance workload: device-resident steps (value, roofline), then the host-buffer calls
     (e2e), then the reference's pair loop on a bounded sample (rank 0, one GPU only)."""
     import torch
@@ -665,8 +665,10 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
         e2e_s = time.perf_counter() - t0
         call = "lzg_profiles_upload_i8 + lzg_distance_matrix + lzg_profiles_free, pinned host buffers"
     else:
-        # rank 0 drives all N GPUs from one process; the other ranks wait (their contexts stay open, idle)
+        # rank 0 drives all N GPUs from one process; the other ranks wait ON THE HOST (a gloo barrier: an NCCL barrier would
+        # keep a spinning kernel on the very GPUs rank 0 is about to use)
         e2e_s = 0.0
+        barrier()
         if rank == 0:
             gp.distance_matrix(h_D)                                    # the 1-GPU bytes
             want = hashlib.sha1(h_D.tobytes()).hexdigest()
@@ -681,7 +683,8 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
                     m.distance_matrix(h_bp, out=h_D)
                 e2e_s = time.perf_counter() - t0
             e2e_extra = {"matrix_equal_to_1gpu": True, "sha1": got[:16]}
-        barrier()
+        torch.cuda.set_device(local)
+        dist.barrier(group=host_pg)
         call = ("lzg_distance_matrix_multi_i8 from rank 0's process over all %d GPUs (row block per GPU over its own PCIe link, NVLink all-gather, mirrors "
                 "written into the owners' memory, per-GPU copy-out into the one pinned host matrix); the other ranks idle" % world)
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
@@ -731,12 +734,35 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
     return line
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries ONE JSON line: file descriptor 1 is pointed at stderr for everything else in the process
+    (NCCL prints a version banner on fd 1 from C; libraries may print warnings), the line itself goes to the saved fd."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, data)
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from lazac_copy_number_b200.api import Context
 
     rank, local, world = dist_env()
+    host_pg = None
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d" % (args.gpus, args.gpus))
@@ -747,11 +773,12 @@ def run_b200(args):
         # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries one JSON line only
         os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_bench_%h_%p.log")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        host_pg = dist.new_group(backend="gloo")   # host-side waits (ranks that must leave their GPU idle)
     peaks, peaks_kind = measured_peaks()
     ctx = Context(local)
 
     name = args.workload or "cfg3"
-    line = distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
+    line = distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu, host_pg=host_pg if world > 1 else None)
     if world == 1 and name == "cfg3" and not args.no_cfg2:
         # BASELINE.json configs[1] beside the headline: same kernel, same calls, a matrix of 36 tiles
         line["cfg2"] = distance_section(ctx, args, "cfg2", rank, local, world, peaks, peaks_kind, cpu=not args.no_cpu)
@@ -763,7 +790,7 @@ def run_b200(args):
             line["nni"] = nni
     ctx.close()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -781,6 +808,7 @@ def main():
     ap.add_argument("--no-nni", action="store_true", help="skip the NNI sections")
     ap.add_argument("--no-nni-large", action="store_true", help="skip the cfg5-shaped NNI section at --gpus 1")
     args = ap.parse_args()
+    claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:

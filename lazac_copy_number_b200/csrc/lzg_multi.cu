@@ -38,6 +38,13 @@ struct lzg_multi {
 
 namespace {
 
+// the entry points visit every GPU; the caller's current device is put back when they return
+struct device_guard {
+    int dev = -1;
+    device_guard() { if (cudaGetDevice(&dev) != cudaSuccess) dev = -1; }
+    ~device_guard() { if (dev >= 0) cudaSetDevice(dev); }
+};
+
 int multi_fail(lzg_multi* m, int status, const char* what, cudaError_t e = cudaSuccess) {
     std::string msg = what ? what : "";
     if (e != cudaSuccess) {
@@ -73,6 +80,7 @@ extern "C" {
 int lzg_multi_init(const int32_t* devices, int32_t n_devices, lzg_multi** out) {
     if (!out || n_devices < 1 || !devices) return LZG_ERR_ARG;
     *out = nullptr;
+    device_guard restore;
     lzg_multi* m = new (std::nothrow) lzg_multi();
     if (!m) return LZG_ERR_ARG;
     for (int g = 0; g < n_devices; g++) {
@@ -130,6 +138,7 @@ int lzg_multi_init(const int32_t* devices, int32_t n_devices, lzg_multi** out) {
 
 int lzg_multi_shutdown(lzg_multi* m) {
     if (!m) return LZG_ERR_ARG;
+    device_guard restore;
     for (size_t g = 0; g < m->ctx.size(); g++) {
         cudaSetDevice(m->ctx[g]->device);
         cudaStreamSynchronize(m->ctx[g]->stream);
@@ -269,6 +278,7 @@ static int distance_multi(lzg_multi* m, const void* host, bool is_i8, int32_t n,
     if (!m || n < 0 || L < 0 || (n > 0 && L > 0 && !host) || (n > 0 && !D_host)) return multi_fail(m, LZG_ERR_ARG, "lzg_distance_matrix_multi: bad argument");
     if (pairs_out) *pairs_out = 0;
     if (n == 0) return LZG_OK;
+    device_guard restore;
     for (int width = 1; width <= 2; width++) {  // the 8-bit format first; its range flag sends wider data through the 16-bit one
         bool out_of_range = false;
         const int rc = distance_multi_width(m, host, is_i8, n, L, D_host, pairs_out, width, &out_of_range);

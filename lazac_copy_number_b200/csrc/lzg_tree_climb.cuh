@@ -189,12 +189,19 @@ k_up_df() {
 // ---- the queue of UP rows to recompute (incremental pass) -------------------------------------------------
 // Pushed by k_apply2 (before k_up_delta starts) and by the walkers of k_up_delta (while it runs: payload,
 // fence, flag).
+// LIVE = consumers may be running (k_up_delta's own pushes): the payload is fenced before the flag.  k_apply2's seeds are
+// read by the next kernel only: plain stores.
+template <bool LIVE>
 __device__ __forceinline__ void uq_push(const lzg_pass_args& A, int stamp, int node_and_flags, int g, int parent, int sib) {
     const int pos = atomicAdd(A.xctl + LZG_X_UQ_PUSHED, 1);
     if (pos < A.ucap) {
         A.uq[pos] = make_int4(node_and_flags, g, parent, sib);
-        __threadfence();
-        st_release(A.uq_flag + pos, stamp);
+        if (LIVE) {
+            __threadfence();
+            st_release(A.uq_flag + pos, stamp);
+        } else {
+            A.uq_flag[pos] = stamp;
+        }
     }
 }
 
@@ -209,7 +216,7 @@ k_apply2() {
     __shared__ int2 s_path[LZG_PATH_CAP];  // (node written, sibling merged) per step
     __shared__ int32_t s_term[LZG_PATH_CAP];
     __shared__ int32_t s_chg[LZG_PATH_CAP];
-    __shared__ int s_is_last, s_steps;
+    __shared__ int s_is_last;
     const int tid = threadIdx.x, g = blockIdx.x;
     if (__ldcg(A.ctl + LZG_CTL_STOP)) return;
     const int stamp = __ldcg(A.ctl + LZG_CTL_EPOCH);
@@ -228,84 +235,74 @@ k_apply2() {
     int32_t* const deep_chg = A.deep_chg + (size_t)g * A.n_nodes;
     iv16 acc;
     uint32_t os[8], oe[8];
-    for (int q = tid; q < LZG_PATH_CAP; q += blockDim.x) s_term[q] = 0, s_chg[q] = 0;
-    // Phase 1: the path v, u, parent(u), .. root with the sibling merged at every step, listed by following the
-    // (parent, sibling) table -- one dependent L2 load per step, nothing else waits on it.  The entries from u
-    // upwards are not touched by the move.  Every row the walk will touch is then requested into L2 at once
-    // (one prefetch per 128-byte line), so the walk itself runs on L2 hits instead of paying a DRAM round trip
-    // per step (36 us -> the L2 latency x depth at cfg5's size).
-    int n_steps = 2;
-    if (tid == 0) {
-        s_path[0] = make_int2(v, y);
-        s_path[1] = make_int2(u, z);
-        int a = u;
-        for (;;) {
-            const int2 e = A.up[a];
-            if (e.x < 0) break;
-            if (n_steps < LZG_PATH_CAP) s_path[n_steps] = e;
-            else deep_path[n_steps] = e;
-            n_steps++;
-            a = e.x;
-        }
-        s_steps = n_steps;
-    }
-    __syncthreads();
-    n_steps = s_steps;
-    auto path_at = [&](int q) -> int2 { return q < LZG_PATH_CAP ? s_path[q] : __ldcg(deep_path + q); };
-    if (active && (tid & 7) == 0) {
-        for (int q = 0; q < n_steps; q++) {
-            const int2 pq = path_at(q);
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.start + pq.x * lp + off));
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.end + pq.x * lp + off));
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.start + pq.y * lp + off));
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(A.end + pq.y * lp + off));
-        }
-    }
-    // Phase 2: the walk.  Rows of step k + 2 are requested while step k merges.
-    uint4 r0s = z4, r0e = z4, o0s = z4, o0e = z4, r1s = z4, r1e = z4, o1s = z4, o1e = z4, r2s = z4, r2e = z4, o2s = z4, o2e = z4;
-    auto load_step = [&](int q, uint4& rs, uint4& re, uint4& os_, uint4& oe_) {
-        if (q < n_steps && active) {
-            const int2 pq = path_at(q);
-            rs = ldg16(A.start, pq.y * lp + off), re = ldg16(A.end, pq.y * lp + off);        // the sibling merged in
-            os_ = ldg16(A.start, pq.x * lp + off), oe_ = ldg16(A.end, pq.x * lp + off);      // the row about to be overwritten
-        }
-    };
+    // (parent, sibling) two steps ahead of the merge; the entries from u upwards are not touched by the move
+    int2 e1 = A.up[u];
+    int2 e2 = e1.x >= 0 ? A.up[e1.x] : make_int2(-1, -1);
+    uint4 ys = z4, ye = z4, zs = z4, ze = z4, q1s = z4, q1e = z4, q2s = z4, q2e = z4;
+    uint4 ovs = z4, ove = z4, ous = z4, oue = z4, o1s = z4, o1e = z4, o2s = z4, o2e = z4;  // the rows about to be overwritten
     if (active) {
         widen_w<W>(ldg16(A.start, w * lp + off), acc.s);
         widen_w<W>(ldg16(A.end, w * lp + off), acc.e);
+        ys = ldg16(A.start, y * lp + off), ye = ldg16(A.end, y * lp + off);
+        zs = ldg16(A.start, z * lp + off), ze = ldg16(A.end, z * lp + off);
+        ovs = ldg16(A.start, v * lp + off), ove = ldg16(A.end, v * lp + off);
+        ous = ldg16(A.start, u * lp + off), oue = ldg16(A.end, u * lp + off);
+        if (e1.x >= 0) {
+            q1s = ldg16(A.start, e1.y * lp + off), q1e = ldg16(A.end, e1.y * lp + off);
+            o1s = ldg16(A.start, e1.x * lp + off), o1e = ldg16(A.end, e1.x * lp + off);
+        }
     }
-    load_step(0, r0s, r0e, o0s, o0e);
-    load_step(1, r1s, r1e, o1s, o1e);
-    for (int k = 0; k < n_steps; k++) {
-        load_step(k + 2, r2s, r2e, o2s, o2e);
-        const int2 pq = path_at(k);
-        // step k: node = merge(running interval, sibling); costs and "changed" flags are fire-and-forget
-        // shared-memory reductions (no shuffle chain in the walk), read back once the walk is over
+    for (int q = tid; q < LZG_PATH_CAP; q += blockDim.x) s_term[q] = 0, s_chg[q] = 0;
+    __syncthreads();
+    int k = 0;
+    // step k: node = merge(running interval, other); costs and "changed" flags are fire-and-forget
+    // shared-memory reductions (no shuffle chain in the walk), read back once the walk is over
+    auto step = [&](int node, int other, const uint4& rs, const uint4& re, const uint4& olds, const uint4& olde) {
         uint32_t c = 0;
         bool chg = false;
         if (active) {
-            widen_w<W>(r0s, os);
-            widen_w<W>(r0e, oe);
+            widen_w<W>(rs, os);
+            widen_w<W>(re, oe);
             c = merge_w<W>(acc, os, oe);
             const uint4 ns = narrow_w<W>(acc.s), ne = narrow_w<W>(acc.e);
-            chg = differs(ns, o0s) || differs(ne, o0e);
-            *reinterpret_cast<uint4*>(A.wstart + pq.x * lp + off) = ns;
-            *reinterpret_cast<uint4*>(A.wend + pq.x * lp + off) = ne;
+            chg = differs(ns, olds) || differs(ne, olde);
+            *reinterpret_cast<uint4*>(A.wstart + node * lp + off) = ns;
+            *reinterpret_cast<uint4*>(A.wend + node * lp + off) = ne;
         }
         if (k < LZG_PATH_CAP) {
             c = __reduce_add_sync(0xffffffffu, c);  // one REDUX per warp: 256 same-address shared atomics would serialise
             if ((tid & 31) == 0 && c) atomicAdd(&s_term[k], (int32_t)c);
             if (chg) s_chg[k] = 1;
+            if (tid == 0) s_path[k] = make_int2(node, other);
         } else {
             c = warp_sum(c);
-            if ((tid & 31) == 0 && c) atomicAdd(A.pcost + pq.x, (int32_t)c);
+            if ((tid & 31) == 0 && c) atomicAdd(A.pcost + node, (int32_t)c);
             if (chg) deep_chg[k] = 1;
+            if (tid == 0) deep_path[k] = make_int2(node, other);
         }
-        r0s = r1s, r0e = r1e, o0s = o1s, o0e = o1e;
-        r1s = r2s, r1e = r2e, o1s = o2s, o1e = o2e;
+        k++;
+    };
+    step(v, y, ys, ye, ovs, ove);  // the new v = merge(w, y)
+    step(u, z, zs, ze, ous, oue);  // the new u = merge(v, z)
+    while (e1.x >= 0) {
+        int2 e3 = make_int2(-1, -1);
+        if (e2.x >= 0) {
+            e3 = A.up[e2.x];
+            if (active) {
+                q2s = ldg16(A.start, e2.y * lp + off), q2e = ldg16(A.end, e2.y * lp + off);
+                o2s = ldg16(A.start, e2.x * lp + off), o2e = ldg16(A.end, e2.x * lp + off);
+            }
+        }
+        step(e1.x, e1.y, q1s, q1e, o1s, o1e);
+        e1 = e2;
+        e2 = e3;
+        q1s = q2s, q1e = q2e;
+        o1s = o2s, o1e = o2e;
     }
-    __threadfence();  // the deep-path flags of this CTA, read back below by other threads of it
+    const int n_steps = k;
+    __threadfence();  // the deep-path records of this CTA, read back below by other threads of it
     __syncthreads();
+    auto path_at = [&](int q) -> int2 { return q < LZG_PATH_CAP ? s_path[q] : deep_path[q]; };
     // this chunk group's share: costs, stamps of the rows that changed, UP rows to recompute
     for (int q = tid; q < n_steps; q += blockDim.x) {
         const bool chg = q < LZG_PATH_CAP ? s_chg[q] != 0 : __ldcg(deep_chg + q) != 0;
@@ -317,14 +314,14 @@ k_apply2() {
         // DOWN(node_q) is an input of UP(sibling of node_q) = UP(other_(q+1)); node_0 = v: its sibling z is queued anyway
         if (q >= 1 && q + 1 < n_steps) {
             const int2 nx = path_at(q + 1);
-            if (__ldg(A.node4 + nx.y).x >= 0) uq_push(A, stamp, nx.y, g, nx.x, pq.x);
+            if (__ldg(A.node4 + nx.y).x >= 0) uq_push<false>(A, stamp, nx.y, g, nx.x, pq.x);
         }
     }
     if (tid == 0) {
         // v hangs under u beside z now, and its children w, y got a new parent / sibling: their UP rows are
         // recomputed whether or not UP(v) comes out different
-        uq_push(A, stamp, v | LZG_UQ_FORCE, g, u, z);
-        if (__ldg(A.node4 + z).x >= 0) uq_push(A, stamp, z, g, u, v);
+        uq_push<false>(A, stamp, v | LZG_UQ_FORCE, g, u, z);
+        if (__ldg(A.node4 + z).x >= 0) uq_push<false>(A, stamp, z, g, u, v);
     }
     __threadfence();
     __syncthreads();
@@ -482,7 +479,7 @@ k_up_delta() {
             if (!any && !force) break;
             if (nx.z & 2) {  // light child internal: queue it (it reads UP(x) from memory)
                 __syncthreads();
-                if (tid == 0) uq_push(A, stamp, nx.y, g, x, nx.x);
+                if (tid == 0) uq_push<true>(A, stamp, nx.y, g, x, nx.x);
             }
             if (!(nx.z & 1)) break;
             if (active) {  // continue with the heavy child: UP(heavy) = merge(UP(x), DOWN(light))
