@@ -52,6 +52,7 @@ struct Args {
     int iterations = 100, seed = 0, device = 0;
     std::vector<int> devices;  // --devices: several GPUs of the box for the distance matrix (trees run on the first)
     bool greedy = false, have_output = false;
+    bool cache = false;  // --cache: keep / use the binary profile cache next to the CSV
 };
 
 const char* USAGE =
@@ -65,13 +66,14 @@ const char* USAGE =
     "  -g, --greedy      use greedy hill climbing strategy as opposed to full NNI neighborhood exploration\n"
     "  -s, --seed        seed for random number generator [default: 0]\n"
     "      --device      CUDA device index [default: 0]\n"
-    "      --devices     GPUs for the distance matrix, e.g. 0-7 or 0,2,3 (the search runs on the first)\n";
+    "      --devices     GPUs for the distance matrix, e.g. 0-7 or 0,2,3 (the search runs on the first)\n"
+    "      --cache       read the breakpoint profiles from CSV.lzbp when it matches the CSV, write it otherwise\n";
 
 Args parse_args(int argc, char** argv) {
     Args a;
     if (argc < 2) throw std::runtime_error("missing subcommand");
     a.command = argv[1];
-    if (a.command != "distance" && a.command != "nni" && a.command != "nj" && a.command != "bp")
+    if (a.command != "distance" && a.command != "nni" && a.command != "nj" && a.command != "bp" && a.command != "writebench")
         throw std::runtime_error("unknown subcommand: " + a.command);
     bool have_positional = false;
     for (int i = 2; i < argc; i++) {
@@ -119,6 +121,8 @@ Args parse_args(int argc, char** argv) {
             }
             if (a.devices.empty()) throw std::runtime_error("--devices: expected at least one device");
             a.device = a.devices[0];
+        } else if (s == "--cache") {
+            a.cache = true;
         } else if (s == "-g" || s == "--greedy") {
             a.greedy = true;
         } else if (s == "-h" || s == "--help") {
@@ -187,47 +191,83 @@ std::vector<int32_t> build_distance_matrix(const Gpu& gpu, const BreakpointSet& 
     return D;
 }
 
-// Integer rows formatted into one buffer per row (the reference streams value by value; bytes are identical).
-void write_matrix_txt(const std::string& path, const std::vector<std::string>& names, const std::vector<int32_t>& D) {
-    const size_t n = names.size();
-    std::ofstream out(path, std::ios::out);
-    out << n << "\n";
-    std::string line;
-    for (size_t i = 0; i < n; i++) {
-        line = names[i];
-        for (size_t j = 0; j < n; j++) {
-            line += ' ';
-            line += std::to_string(D[i * n + j]);
-        }
-        line += '\n';
-        out << line;
+// PREFIX_dist_matrix.csv / .txt (src/lazac.cxx:107-131): byte-identical to the reference's value-by-value streaming, written
+// as blocks of rows formatted straight into one preallocated buffer with a hand-rolled integer formatter (SURVEY.md 8(f)
+// rank 3: cfg3's matrix is 4e8 numbers, written twice; std::to_string + string append per value took minutes there).
+static inline char* put_int(char* p, long long v) {
+    if (v < 0) {
+        *p++ = '-';
+        v = -v;
     }
+    char digits[20];
+    int nd = 0;
+    do {
+        digits[nd++] = (char)('0' + v % 10);
+        v /= 10;
+    } while (v);
+    while (nd) *p++ = digits[--nd];
+    return p;
+}
+
+static void write_matrix(const std::string& path, const std::vector<std::string>& names, const std::vector<int32_t>& D, char sep, bool csv_header) {
+    const auto t0 = std::chrono::steady_clock::now();
+    const size_t n = names.size();
+    FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("Cannot open file " + path);
+    std::string head;
+    if (csv_header) {
+        for (size_t i = 0; i < n; i++) {
+            if (i != 0) head += ',';
+            head += names[i];
+        }
+        head += '\n';
+    } else {
+        head = std::to_string(n) + "\n";
+    }
+    std::fwrite(head.data(), 1, head.size(), f);
+    size_t longest = 0;
+    for (const auto& nm : names) longest = std::max(longest, nm.size());
+    const size_t row_cap = longest + 1 + n * 12;                       // name, then n x (separator + up to 11 characters)
+    const size_t rows_per_block = std::max<size_t>(1, ((size_t)8 << 20) / row_cap);
+    std::vector<char> buf(row_cap * std::min(rows_per_block, std::max<size_t>(n, 1)));
+    for (size_t i0 = 0; i0 < n; i0 += rows_per_block) {
+        char* p = buf.data();
+        for (size_t i = i0; i < std::min(n, i0 + rows_per_block); i++) {
+            std::memcpy(p, names[i].data(), names[i].size());
+            p += names[i].size();
+            const int32_t* row = D.data() + i * n;
+            for (size_t j = 0; j < n; j++) {
+                *p++ = sep;
+                p = put_int(p, row[j]);
+            }
+            *p++ = '\n';
+        }
+        std::fwrite(buf.data(), 1, (size_t)(p - buf.data()), f);
+    }
+    std::fclose(f);
+    if (getenv("LAZAC_TIMING"))
+        std::cerr << "[lazac timing] " << path << ": " << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() << " ms" << std::endl;
+}
+
+void write_matrix_txt(const std::string& path, const std::vector<std::string>& names, const std::vector<int32_t>& D) {
+    write_matrix(path, names, D, ' ', false);
 }
 
 void write_matrix_csv(const std::string& path, const std::vector<std::string>& names, const std::vector<int32_t>& D) {
-    const size_t n = names.size();
-    std::ofstream out(path, std::ios::out);
-    std::string line;
-    for (size_t i = 0; i < n; i++) {
-        if (i != 0) line += ',';
-        line += names[i];
-    }
-    line += '\n';
-    out << line;
-    for (size_t i = 0; i < n; i++) {
-        line = names[i];
-        for (size_t j = 0; j < n; j++) {
-            line += ',';
-            line += std::to_string(D[i * n + j]);
-        }
-        line += '\n';
-        out << line;
-    }
+    write_matrix(path, names, D, ',', true);
 }
 
 // CSV -> breakpoint set; LAZAC_TIMING=1 logs how long the two steps took.
-BreakpointSet ingest(const std::string& path) {
+BreakpointSet ingest(const std::string& path, bool cache = false) {
     const auto t0 = std::chrono::steady_clock::now();
+    if (cache) {
+        BreakpointSet cached;
+        if (load_breakpoint_cache(path + ".lzbp", path, cached)) {
+            if (getenv("LAZAC_TIMING"))
+                fprintf(stderr, "[lazac timing] profile cache %s.lzbp %.0f ms\n", path.c_str(), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+            return cached;
+        }
+    }
     const std::map<std::string, CellProfile> cells = read_cn_profiles(path);
     const auto t1 = std::chrono::steady_clock::now();
     BreakpointSet set = to_breakpoint_set(cells);
@@ -235,6 +275,7 @@ BreakpointSet ingest(const std::string& path) {
     if (getenv("LAZAC_TIMING"))
         fprintf(stderr, "[lazac timing] read_cn_profiles %.0f ms, to_breakpoint_set %.0f ms\n", std::chrono::duration<double, std::milli>(t1 - t0).count(),
                 std::chrono::duration<double, std::milli>(t2 - t1).count());
+    if (cache && !save_breakpoint_cache(path + ".lzbp", path, set)) fprintf(stderr, "lazac: could not write %s.lzbp\n", path.c_str());
     return set;
 }
 
@@ -248,7 +289,7 @@ std::future<std::unique_ptr<Gpu>> open_gpu_async(const Args& a) {
 
 void do_distance(const Args& a) {
     auto gpu_opening = open_gpu_async(a);
-    const BreakpointSet set = ingest(a.cn_profile);
+    const BreakpointSet set = ingest(a.cn_profile, a.cache);
     const std::unique_ptr<Gpu> gpu_owner = gpu_opening.get();
     Gpu& gpu = *gpu_owner;
     const std::vector<int32_t> D = build_distance_matrix(gpu, set, nullptr);
@@ -303,7 +344,7 @@ void do_nni(const Args& a) {
     } total{t_start};
     /* Load copy number profiles */
     auto gpu_opening = open_gpu_async(a);
-    const BreakpointSet set = ingest(a.cn_profile);
+    const BreakpointSet set = ingest(a.cn_profile, a.cache);
     const int n_cells = (int)set.names.size();
     const std::unique_ptr<Gpu> gpu_owner = gpu_opening.get();
     Gpu& gpu = *gpu_owner;
@@ -557,8 +598,32 @@ void do_nj(const Args& a) {  // helper: PREFIX_dist_matrix.txt -> Newick; on the
     }
 }
 
+void do_writebench(const Args& a) {  // helper: time the two matrix writers on an N x N matrix of distance-sized values, no GPU
+    const size_t n = (size_t)std::stoul(a.cn_profile);
+    std::vector<std::string> names(n);
+    for (size_t i = 0; i < n; i++) {
+        char nm[32];
+        std::snprintf(nm, sizeof nm, "cell_%06zu", i);
+        names[i] = nm;
+    }
+    std::vector<int32_t> D(n * n);
+    uint32_t x = 12345;
+    for (auto& v : D) {
+        x = x * 1664525u + 1013904223u;
+        v = (int32_t)(x >> 20);  // 0 .. 4095, the size of cfg3's distances
+    }
+    using clk = std::chrono::steady_clock;
+    auto t0 = clk::now();
+    write_matrix_csv(a.output + "_dist_matrix.csv", names, D);
+    auto t1 = clk::now();
+    write_matrix_txt(a.output + "_dist_matrix.txt", names, D);
+    auto t2 = clk::now();
+    std::printf("{\"n\": %zu, \"values\": %zu, \"csv_s\": %.3f, \"txt_s\": %.3f}\n", n, n * n, std::chrono::duration<double>(t1 - t0).count(),
+                std::chrono::duration<double>(t2 - t1).count());
+}
+
 void do_bp(const Args& a) {  // helper: CSV -> names + breakpoint matrix (text), no GPU
-    const BreakpointSet set = ingest(a.cn_profile);
+    const BreakpointSet set = ingest(a.cn_profile, a.cache);
     std::ofstream out(a.output, std::ios::out);
     out << set.names.size() << " " << set.L << "\n";
     for (size_t i = 0; i < set.names.size(); i++) {
@@ -595,6 +660,7 @@ int main(int argc, char** argv) {
         if (a.command == "nni") do_nni(a);
         else if (a.command == "distance") do_distance(a);
         else if (a.command == "nj") do_nj(a);
+        else if (a.command == "writebench") do_writebench(a);
         else do_bp(a);
     } catch (const std::exception& e) {
         // the reference lets these terminate the process (std::terminate); we report and exit non-zero

@@ -1,6 +1,8 @@
 // host/profiles.cpp -- see profiles.hpp.
 #include "profiles.hpp"
 
+#include <sys/stat.h>
+
 #include <algorithm>
 #include <fstream>
 #include <cstring>
@@ -296,6 +298,102 @@ BreakpointSet to_breakpoint_set(const std::map<std::string, CellProfile>& cells)
         out.bp.insert(out.bp.end(), bp.begin(), bp.end());
     }
     return out;
+}
+
+// ---- binary profile cache -------------------------------------------------------------------------------
+namespace {
+const char kCacheMagic[8] = {'L', 'Z', 'B', 'P', 'v', '1', 0, 0};
+
+bool csv_identity(const std::string& path, uint64_t& size, int64_t& mtime_ns) {
+    struct stat st;
+    if (stat(path.c_str(), &st) != 0) return false;
+    size = (uint64_t)st.st_size;
+    mtime_ns = (int64_t)st.st_mtim.tv_sec * 1000000000ll + st.st_mtim.tv_nsec;
+    return true;
+}
+void put_str(std::vector<char>& out, const std::string& s) {
+    const uint32_t n = (uint32_t)s.size();
+    out.insert(out.end(), (const char*)&n, (const char*)&n + 4);
+    out.insert(out.end(), s.begin(), s.end());
+}
+bool get_str(const char*& p, const char* end, std::string& s) {
+    if (end - p < 4) return false;
+    uint32_t n;
+    memcpy(&n, p, 4);
+    p += 4;
+    if ((size_t)(end - p) < n) return false;
+    s.assign(p, n);
+    p += n;
+    return true;
+}
+}  // namespace
+
+bool save_breakpoint_cache(const std::string& cache_path, const std::string& csv_path, const BreakpointSet& set) {
+    uint64_t size = 0;
+    int64_t mtime = 0;
+    if (!csv_identity(csv_path, size, mtime)) return false;
+    std::vector<char> head(kCacheMagic, kCacheMagic + 8);
+    const uint64_t n = set.names.size(), L = (uint64_t)set.L, nb = set.bins.size();
+    for (const uint64_t v : {size, (uint64_t)mtime, n, L, nb}) head.insert(head.end(), (const char*)&v, (const char*)&v + 8);
+    for (const auto& nm : set.names) put_str(head, nm);
+    for (const auto& b : set.bins) {
+        put_str(head, b.chromosome);
+        put_str(head, b.allele);
+        const int32_t se[2] = {b.start, b.end};
+        head.insert(head.end(), (const char*)se, (const char*)se + 8);
+    }
+    while (head.size() % 8) head.push_back(0);
+    const std::string tmp = cache_path + ".tmp";
+    FILE* f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return false;
+    bool ok = std::fwrite(head.data(), 1, head.size(), f) == head.size();
+    ok = ok && std::fwrite(set.bp.data(), sizeof(int32_t), set.bp.size(), f) == set.bp.size();
+    ok = (std::fclose(f) == 0) && ok;
+    if (ok) ok = std::rename(tmp.c_str(), cache_path.c_str()) == 0;
+    if (!ok) std::remove(tmp.c_str());
+    return ok;
+}
+
+bool load_breakpoint_cache(const std::string& cache_path, const std::string& csv_path, BreakpointSet& set) {
+    uint64_t size = 0;
+    int64_t mtime = 0;
+    if (!csv_identity(csv_path, size, mtime)) return false;
+    FILE* f = std::fopen(cache_path.c_str(), "rb");
+    if (!f) return false;
+    std::fseek(f, 0, SEEK_END);
+    const long total = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    std::vector<char> data((size_t)std::max(0l, total));
+    const bool read_ok = total > 0 && std::fread(data.data(), 1, data.size(), f) == data.size();
+    std::fclose(f);
+    if (!read_ok || data.size() < 48 || memcmp(data.data(), kCacheMagic, 8) != 0) return false;
+    uint64_t h[5];
+    memcpy(h, data.data() + 8, 40);
+    if (h[0] != size || (int64_t)h[1] != mtime) return false;  // the CSV changed since the cache was written
+    const uint64_t n = h[2], L = h[3], nb = h[4];
+    if (L > (1ull << 31) || n > (1ull << 31) || nb > (1ull << 31)) return false;
+    const char* p = data.data() + 48;
+    const char* end = data.data() + data.size();
+    BreakpointSet out;
+    out.L = (int)L;
+    out.names.resize(n);
+    for (auto& nm : out.names)
+        if (!get_str(p, end, nm)) return false;
+    out.bins.resize(nb);
+    for (auto& b : out.bins) {
+        if (!get_str(p, end, b.chromosome) || !get_str(p, end, b.allele) || end - p < 8) return false;
+        int32_t se[2];
+        memcpy(se, p, 8);
+        p += 8;
+        b.start = se[0], b.end = se[1];
+    }
+    size_t off = (size_t)(p - data.data());
+    off = (off + 7) / 8 * 8;
+    if (data.size() - off != n * L * sizeof(int32_t)) return false;
+    out.bp.resize(n * L);
+    memcpy(out.bp.data(), data.data() + off, n * L * sizeof(int32_t));
+    set = std::move(out);
+    return true;
 }
 
 }  // namespace lazac_host

@@ -35,6 +35,13 @@ struct BreakpointSet {
 // convert_to_breakpoint_profile(cn, 2) for every cell.
 BreakpointSet to_breakpoint_set(const std::map<std::string, CellProfile>& cells);
 
+// Binary profile cache: the BreakpointSet of a CSV as one file next to it -- a header with the
+// size and modification time of the CSV it was made from, the cell names, the bins, the int32 matrix -- so that a second
+// run over the same input skips the CSV parse and the per-cell transform.  load returns false when the cache is missing,
+// stale (the CSV changed) or malformed; nothing but `lazac --cache` reads or writes it.
+bool save_breakpoint_cache(const std::string& cache_path, const std::string& csv_path, const BreakpointSet& set);
+bool load_breakpoint_cache(const std::string& cache_path, const std::string& csv_path, BreakpointSet& set);
+
 // Position order of convert_to_breakpoint_profile / convert_to_copynumber_profile: positions grouped
 // by (chromosome, allele) in std::map order, each group stable-sorted by bin (src/copy_number.cxx:28-41).
 struct SegmentOrder {

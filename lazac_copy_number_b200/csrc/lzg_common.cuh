@@ -14,7 +14,7 @@
 // Persistent-grid work schedule of the distance kernel for one (tile size, shard) (lzg_distance.cu).
 struct lzg_schedule {
     int n = 0, l_pad = 0;           // the input shape it was built for (schedules are cached per context)
-    int bm = 0, shard = 0, n_shards = 0, row_lo = 0, row_hi = 0;
+    int bm = 0, shard = 0, n_shards = 0, row_lo = 0, row_hi = 0, own_mode = 0;
     int n_ctas = 0, n_segs = 0, n_split = 0;
     int64_t pairs = 0;
     void* d_block = nullptr;        // one pooled allocation holding the three arrays below
@@ -93,7 +93,9 @@ int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuc
 // d_row_base (optional, device array of one pointer per tile row): where the output rows of each tile row live
 // instead of the one N x N matrix d_D (the row blocks of several GPUs, lzg_multi.cu)
 int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int row_lo, int row_hi,
-                     int32_t* d_D, int64_t* pairs_done, int32_t* const* d_row_base = nullptr);
+                     int32_t* d_D, int64_t* pairs_done, int32_t* const* d_row_base = nullptr, int own_mode = 0);
+// owner of a tile row's output rows under own_mode 1 (snake order): what lzg_multi.cu's phases use
+inline int lzg_snake_owner(int r, int n_shards) { const int k = r % n_shards; return (r / n_shards) % 2 == 0 ? k : n_shards - 1 - k; }
 int lzg_pack_rows_i32(lzg_ctx* ctx, const int32_t* d_src, uint8_t* d_dst, int rows, int L, int l_pad, int width = 1);
 int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v);
 int lzg_fill_pad(lzg_ctx* ctx, uint8_t* d, size_t n_bytes, int width);

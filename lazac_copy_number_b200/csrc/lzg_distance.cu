@@ -411,16 +411,24 @@ struct lzg_plan {
 };
 
 // Host only (no CUDA call): lzg_distance_plan exports it so the CPU tests can check coverage and balance.
+// own_mode 0: tile rows dealt in pairs (r, R-1-r) -- equal area over the WHOLE triangle; own_mode 1: in snake order
+// (0 .. G-1, G-1 .. 0, ...) -- equal area over every block of 2 G consecutive tile rows, which is what lets several
+// GPUs work through the triangle in row-group phases (lzg_multi.cu).
+static inline int tile_row_owner(int r, int R, int n_shards, int own_mode) {
+    if (own_mode == 0) return std::min(r, R - 1 - r) % n_shards;
+    const int k = r % n_shards;
+    return (r / n_shards) % 2 == 0 ? k : n_shards - 1 - k;
+}
+
 void plan_schedule(int n, int l_pad, int bm, int sm_count, int slots_per_sm, int shard, int n_shards, int row_lo, int row_hi,
-                   lzg_plan& out) {
+                   lzg_plan& out, int own_mode = 0) {
     const int R = (n + bm - 1) / bm;
     const int K = l_pad / 16;  // chunks per row
     std::vector<int2> tiles;
     int64_t pairs = 0, units = 0;
     auto rows_in = [&](int r) { return (int64_t)(std::min(n, (r + 1) * bm) - r * bm); };
     for (int r = 0; r < R; r++) {
-        int pr = std::min(r, R - 1 - r);
-        if (pr % n_shards != shard || r < row_lo || r >= row_hi) continue;
+        if (tile_row_owner(r, R, n_shards, own_mode) != shard || r < row_lo || r >= row_hi) continue;
         for (int c = r; c < R; c++) {
             tiles.push_back(make_int2(r, c));
             pairs += (c == r) ? rows_in(r) * (rows_in(r) + 1) / 2 : rows_in(r) * rows_in(c);
@@ -448,8 +456,7 @@ void plan_schedule(int n, int l_pad, int bm, int sm_count, int slots_per_sm, int
     if (reorder) {
         std::vector<int> rank_of(R, 0);
         for (int r = 0, k = 0; r < R; r++) {
-            int pr = std::min(r, R - 1 - r);
-            if (pr % n_shards != shard || r < row_lo || r >= row_hi) continue;
+            if (tile_row_owner(r, R, n_shards, own_mode) != shard || r < row_lo || r >= row_hi) continue;
             rank_of[r] = k++;
         }
         for (const int2& t : tiles)
@@ -581,11 +588,11 @@ void plan_schedule(int n, int l_pad, int bm, int sm_count, int slots_per_sm, int
 }
 
 const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slots_per_sm, int shard, int n_shards,
-                                 int row_lo, int row_hi, int* status) {
+                                 int row_lo, int row_hi, int* status, int own_mode) {
     for (auto& sc : ctx->schedules)
-        if (sc.n == p->n && sc.l_pad == p->pitch && sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi) return &sc;
+        if (sc.n == p->n && sc.l_pad == p->pitch && sc.bm == bm && sc.shard == shard && sc.n_shards == n_shards && sc.row_lo == row_lo && sc.row_hi == row_hi && sc.own_mode == own_mode) return &sc;
     lzg_plan plan;
-    plan_schedule(p->n, p->pitch, bm, ctx->sm_count, slots_per_sm, shard, n_shards, row_lo, row_hi, plan);
+    plan_schedule(p->n, p->pitch, bm, ctx->sm_count, slots_per_sm, shard, n_shards, row_lo, row_hi, plan, own_mode);
     std::vector<lzg_seg>& segs = plan.segs;
     std::vector<int32_t>& seg_off = plan.seg_off;
     std::vector<int2>& split = plan.split;
@@ -594,6 +601,7 @@ const lzg_schedule* get_schedule(lzg_ctx* ctx, lzg_profiles* p, int bm, int slot
     sc.l_pad = p->pitch;  // the plan is cut in 16-byte chunks of a row
     sc.bm = bm;
     sc.shard = shard;
+    sc.own_mode = own_mode;
     sc.n_shards = n_shards;
     sc.row_lo = row_lo;
     sc.row_hi = row_hi;
@@ -695,14 +703,14 @@ int lzg_fill_bytes(lzg_ctx* ctx, uint8_t* d, size_t n, uint8_t v) {
 // Computes the shard's tiles of tile rows [row_lo, row_hi) into the full N x N device matrix d_D
 // (asynchronous on ctx->stream).
 int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int row_lo, int row_hi, int32_t* d_D,
-                     int64_t* pairs_done, int32_t* const* d_row_base) {
+                     int64_t* pairs_done, int32_t* const* d_row_base, int own_mode) {
     if (pairs_done) *pairs_done = 0;
     if (p->n == 0) return LZG_OK;
     int status = LZG_OK;
     const int bm = lzg_distance_tile(p);
     // one persistent CTA per SM: 8 warps x 254 registers fill the register file (3 CTAs of 2 warps for
     // the single-tile 64 x 64 case)
-    const lzg_schedule* sc = get_schedule(ctx, p, bm, bm == 64 ? 3 : 1, shard, n_shards, row_lo, row_hi, &status);
+    const lzg_schedule* sc = get_schedule(ctx, p, bm, bm == 64 ? 3 : 1, shard, n_shards, row_lo, row_hi, &status, own_mode);
     if (!sc) return status;
     if (pairs_done) *pairs_done = sc->pairs;
     if (sc->n_segs == 0) return LZG_OK;

@@ -6,16 +6,18 @@
 //   1. profiles: GPU g receives rows [g n / G, (g+1) n / G) over ITS OWN PCIe link, packs them (bias /
 //      padding) and pushes the packed block to every peer over NVLink (cudaMemcpyPeerAsync) -- an
 //      all-gather that replaces G full uploads through host memory;
-//   2. tiles: tile rows are dealt in pairs (r, R-1-r) as lzg_distance_shard does (equal triangle area per
-//      GPU, no communication during the compute);
+//   2. tiles: tile rows are dealt in snake order (0 .. G-1, G-1 .. 0, ...): equal triangle area per GPU over
+//      every 2 G consecutive tile rows, no communication during the compute;
 //   3. output: GPU g OWNS the output rows of its tile rows.  The kernel writes a tile into the owner's
 //      row block and the MIRROR of the tile straight into the row block of the tile column's owner --
 //      a peer store over NVLink from the epilogue (a table of one base pointer per tile row) -- so when
 //      all kernels are done every GPU holds whole, final rows of D;
 //   4. gather: every GPU copies its row blocks to their place in the host matrix over its own PCIe link,
-//      all GPUs at once (10 MB contiguous per tile row at cfg3).
+//      all GPUs at once (10 MB contiguous per tile row at cfg3) -- in phases of tile rows, so that the
+//      copies of one phase run while the next one computes.
 // Nothing here computes: the kernels are lzg_distance.cu's.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -175,7 +177,7 @@ static int distance_multi_width(lzg_multi* m, const void* host, bool is_i8, int3
     lzg_profiles shape;  // for lzg_distance_tile / the schedule cache
     shape.n = n, shape.L = L, shape.n_pad = n_pad, shape.l_pad = l_pad, shape.width = width, shape.pitch = pitch;
     const int bm = lzg_distance_tile(&shape), R = (n + bm - 1) / bm;
-    auto owner = [&](int r) { return std::min(r, R - 1 - r) % G; };
+    auto owner = [&](int r) { return lzg_snake_owner(r, G); };  // equal triangle area over every 2 G consecutive tile rows
     // output rows: slot of every tile row inside its owner's block
     std::vector<int> slot(R, 0), owned(G, 0);
     for (int r = 0; r < R; r++) slot[r] = owned[owner(r)]++;
@@ -232,33 +234,54 @@ static int distance_multi_width(lzg_multi* m, const void* host, bool is_i8, int3
         }
         LZM_CUDA(m, cudaEventRecord(m->ev_up[g], c->stream));
     }
-    // ---- 2. + 3. every GPU: wait for all blocks, run its tile rows; the epilogue writes into the owners' row blocks ----
+    // ---- 2. - 4. in PHASES of tile rows: every GPU computes its tile rows of the phase (the epilogue writes into the owners'
+    // row blocks, mirrors over NVLink); once all GPUs are through a phase the output rows of its tile rows are final -- they
+    // only receive mirrors from tile rows above them -- and every GPU copies the ones it owns to the host matrix while the
+    // next phase computes.  Phase boundaries are multiples of 2 G tile rows (the snake deal is balanced there); as many phases
+    // as leave a few tiles per CTA.
     int64_t pairs = 0;
+    const int blocks2g = (R + 2 * G - 1) / (2 * G);
+    const long long tiles_per_gpu = (long long)R * (R + 1) / 2 / G;
+    const int sm = m->ctx[0]->sm_count;
+    int phases = (int)std::max<long long>(1, std::min<long long>(8, tiles_per_gpu / std::max(1, 4 * sm)));
+    if (getenv("LZG_MULTI_PHASES")) phases = std::max(1, atoi(getenv("LZG_MULTI_PHASES")));
+    phases = std::min(phases, blocks2g);
     for (int g = 0; g < G && rc == LZG_OK; g++) {
         lzg_ctx* c = m->ctx[g];
         LZM_CUDA(m, cudaSetDevice(c->device));
         for (int h = 0; h < G; h++)
             if (h != g) LZM_CUDA(m, cudaStreamWaitEvent(c->stream, m->ev_up[h], 0));
-        lzg_profiles p = shape;
-        p.ctx = c;
-        p.d = m->d_prof[g];
-        p.d_bytes = (size_t)n_pad * pitch;
-        int64_t mine = 0;
-        rc = lzg_distance_run(c, &p, g, G, 0, INT32_MAX, nullptr, &mine, m->d_table[g]);
-        if (rc != LZG_OK) m->err = c->err;
-        pairs += mine;
-        LZM_CUDA(m, cudaEventRecord(m->ev_done[g], c->stream));
     }
-    // ---- 4. gather: the mirrors a GPU's rows receive come from every GPU, so its copies wait for all kernels ----
+    for (int ph = 0; ph < phases && rc == LZG_OK; ph++) {
+        const int ra = std::min(R, (int)((long long)blocks2g * ph / phases) * 2 * G);
+        const int rb = ph + 1 == phases ? R : std::min(R, (int)((long long)blocks2g * (ph + 1) / phases) * 2 * G);
+        for (int g = 0; g < G && rc == LZG_OK; g++) {
+            lzg_ctx* c = m->ctx[g];
+            LZM_CUDA(m, cudaSetDevice(c->device));
+            lzg_profiles p = shape;
+            p.ctx = c;
+            p.d = m->d_prof[g];
+            p.d_bytes = (size_t)n_pad * pitch;
+            int64_t mine = 0;
+            rc = lzg_distance_run(c, &p, g, G, ra, rb, nullptr, &mine, m->d_table[g], 1);
+            if (rc != LZG_OK) m->err = c->err;
+            pairs += mine;
+            LZM_CUDA(m, cudaEventRecord(m->ev_done[g], c->stream));
+        }
+        for (int g = 0; g < G && rc == LZG_OK; g++) {
+            lzg_ctx* c = m->ctx[g];
+            LZM_CUDA(m, cudaSetDevice(c->device));
+            for (int h = 0; h < G; h++) LZM_CUDA(m, cudaStreamWaitEvent(c->copy_stream, m->ev_done[h], 0));
+            for (int r = ra; r < rb; r++) {
+                if (owner(r) != g) continue;
+                const size_t row0 = (size_t)r * bm, nr = std::min<size_t>(n, row0 + bm) - row0;
+                LZM_CUDA(m, cudaMemcpyAsync(D_host + row0 * n, table[r], sizeof(int32_t) * nr * n, cudaMemcpyDeviceToHost, c->copy_stream));
+            }
+        }
+    }
     for (int g = 0; g < G && rc == LZG_OK; g++) {
         lzg_ctx* c = m->ctx[g];
         LZM_CUDA(m, cudaSetDevice(c->device));
-        for (int h = 0; h < G; h++) LZM_CUDA(m, cudaStreamWaitEvent(c->copy_stream, m->ev_done[h], 0));
-        for (int r = 0; r < R; r++) {
-            if (owner(r) != g) continue;
-            const size_t row0 = (size_t)r * bm, nr = std::min<size_t>(n, row0 + bm) - row0;
-            LZM_CUDA(m, cudaMemcpyAsync(D_host + row0 * n, table[r], sizeof(int32_t) * nr * n, cudaMemcpyDeviceToHost, c->copy_stream));
-        }
         LZM_CUDA(m, cudaMemcpyAsync(c->h_pinned, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->copy_stream));
     }
     bool out_of_range = false;

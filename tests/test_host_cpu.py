@@ -110,3 +110,33 @@ def test_csv_fast_path_equals_general_reader(lazac, tmp_path):
     assert first[0] == "3 5" and first[1].split()[0] == "a1"
     # a1: chrom "1": cn 2,4 -> [0, -2]; chrom "10": cn 2 -> single bin = first rule [0]; chrom "2": 5,2 -> [3, 0]
     assert [int(x) for x in first[1].split()[1:]] == [0, -2, 0, 3, 0]
+
+
+def test_binary_profile_cache(tmp_path):
+    """--cache: the second run reads CSV.lzbp instead of the CSV and yields the same breakpoint
+    matrix; a changed CSV invalidates the cache."""
+    import shutil
+    import subprocess
+    import time
+    src = tmp_path / "c.csv"
+    shutil.copy(os.path.join(ROOT, "tests", "golden", "synth_cli", "synth_cn_profile.csv"), src)
+    lazac = os.path.join(ROOT, "host", "lazac")
+    env = dict(os.environ, LAZAC_TIMING="1")
+
+    def run(out):
+        r = subprocess.run([lazac, "bp", str(src), "-o", str(tmp_path / out), "--cache"], capture_output=True, text=True, env=env, check=True)
+        return r.stderr, (tmp_path / out).read_bytes()
+    err1, b1 = run("b1")
+    assert "read_cn_profiles" in err1 and (tmp_path / "c.csv.lzbp").exists()
+    err2, b2 = run("b2")
+    assert "profile cache" in err2 and "read_cn_profiles" not in err2 and b1 == b2
+    plain = subprocess.run([lazac, "bp", str(src), "-o", str(tmp_path / "b0")], capture_output=True, text=True, check=True)
+    assert (tmp_path / "b0").read_bytes() == b1 and plain.returncode == 0
+    time.sleep(0.01)
+    text = src.read_text().splitlines()
+    text[1] = text[1].rsplit(",", 1)[0] + ",7"          # another copy number in the first row
+    src.write_text("\n".join(text) + "\n")
+    err3, b3 = run("b3")
+    assert "read_cn_profiles" in err3 and b3 != b1        # stale cache ignored, rewritten
+    err4, b4 = run("b4")
+    assert "profile cache" in err4 and b4 == b3
