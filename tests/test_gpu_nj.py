@@ -100,3 +100,20 @@ def test_nj_gpu_equals_host_library(ctx):
         left, right = ctx.nj_seed_tree(D, perm)
         cl, cr = search.nj_seed_tree_cpu(D, perm)
         assert np.array_equal(left, cl) and np.array_equal(right, cr), n
+
+
+@pytest.mark.parametrize("n,seed,hi", [(1500, 21, 400), (2500, 22, 3)])
+def test_nj_persistent_kernel_on_larger_matrices(ctx, monkeypatch, n, seed, hi):
+    """All joins in one cooperative launch (k_nj_persistent: grid barriers, the sequential row sum overlapped with the next
+    scan) against the CPU restatement and against the two-launches-per-join form; hi = 3 makes almost every scan a tie."""
+    from lazac_copy_number_b200 import search
+    rng = np.random.default_rng(seed)
+    D = rng.integers(1, hi + 1, (n, n)).astype(np.int32)
+    D = np.triu(D, 1) + np.triu(D, 1).T
+    perm = search.clearcut_shuffle(n, seed)
+    left, right = ctx.nj_seed_tree(D, perm)
+    cl, cr = search.nj_seed_tree_cpu(D, perm)
+    assert np.array_equal(left, cl) and np.array_equal(right, cr)
+    monkeypatch.setenv("LZG_NJ_PERSISTENT", "0")
+    l2, r2 = ctx.nj_seed_tree(D, perm)
+    assert np.array_equal(l2, cl) and np.array_equal(r2, cr)
