@@ -17,6 +17,7 @@
 //     dropped (here: a base offset into the square matrix, as host/seed_tree.cpp does).
 // Distances are integers below 2^24 (checked), so their float32 images are exact.
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -41,20 +42,20 @@ __device__ __forceinline__ uint32_t float_order(float f) {  // monotone map floa
 }
 
 // m[i][j] = (float)D[perm[i]][perm[j]], zero diagonal (NJ_shuffle_distance_matrix + dmat parse).
-__global__ void k_nj_gather(const int32_t* __restrict__ D, const int32_t* __restrict__ perm, float* __restrict__ m, int n) {
+__global__ void k_nj_gather(const int32_t* __restrict__ D, const int32_t* __restrict__ perm, float* __restrict__ m, int n, int ld) {
     const int i = blockIdx.y;
     const size_t src = (size_t)perm[i] * n;
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
-        m[(size_t)i * n + j] = i == j ? 0.0f : (float)D[src + perm[j]];
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < ld; j += gridDim.x * blockDim.x)
+        m[(size_t)i * ld + j] = i == j || j >= n ? 0.0f : (float)D[src + perm[j]];
 }
 
 // NJ_init_r: r[k] = sequential float32 sum of d(k, j) in increasing j (rows above k first, then
 // row k itself); r2[k] = r[k] / (n - 2) for all but the last index, which is never initialised.
-__global__ void k_nj_init_r(const float* __restrict__ m, int n, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node) {
+__global__ void k_nj_init_r(const float* __restrict__ m, int n, int ld, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     float s = 0.0f;
-    for (int j = 0; j < n; j++) s = __fadd_rn(s, m[(size_t)j * n + k]);  // column k == row k; the zero diagonal changes nothing
+    for (int j = 0; j < n; j++) s = __fadd_rn(s, m[(size_t)j * ld + k]);  // column k == row k; the zero diagonal changes nothing
     r[k] = s;
     r2[k] = k < n - 1 ? __fdiv_rn(s, (float)(n - 2)) : 0.0f;
     node[k] = k;
@@ -62,10 +63,10 @@ __global__ void k_nj_init_r(const float* __restrict__ m, int n, float* __restric
 
 // NJ_min_transform over the active triangle (logical indices, physical = logical + base).
 __global__ void __launch_bounds__(256)
-k_nj_argmin(const float* __restrict__ m, int n0, int base, int size, const float* __restrict__ r2, unsigned long long* __restrict__ key) {
+k_nj_argmin(const float* __restrict__ m, int n0, int ld, int base, int size, const float* __restrict__ r2, unsigned long long* __restrict__ key) {
     unsigned long long best = ~0ull;
     for (int i = blockIdx.x; i < size - 1; i += gridDim.x) {
-        const float* row = m + (size_t)(i + base) * n0 + base;
+        const float* row = m + (size_t)(i + base) * ld + base;
         const float r2i = r2[i + base];
         for (int j = i + 1 + threadIdx.x; j < size; j += blockDim.x) {
             const float cur = __fadd_rn(__fsub_rn(__ldg(row + j), __fadd_rn(r2i, r2[j + base])), 0.0f);  // + 0: no negative zero
@@ -89,7 +90,7 @@ k_nj_argmin(const float* __restrict__ m, int n0, int base, int size, const float
 
 // One join: NJ_compute_r + NJ_collapse + the index-0-to-b relabelling, a single CTA (O(size) work).
 __global__ void __launch_bounds__(1024)
-k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node,
+k_nj_join(float* __restrict__ m, int n0, int ld, int base, int size, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node,
           unsigned long long* __restrict__ key, int32_t* __restrict__ left, int32_t* __restrict__ right, int joined) {
     __shared__ int s_a, s_b;
     __shared__ float s_a2, s_b2;
@@ -97,7 +98,7 @@ k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__
     if (tid == 0) {
         const unsigned idx = (unsigned)(*key & 0xffffffffull);
         const int a = (int)(idx / (unsigned)n0), b = (int)(idx % (unsigned)n0);
-        const float dab = m[(size_t)(a + base) * n0 + b + base];
+        const float dab = m[(size_t)(a + base) * ld + b + base];
         const float r2a = r2[a + base], r2b = r2[b + base];
         s_a = a;
         s_b = b;
@@ -111,8 +112,8 @@ k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__
     const int a = s_a, b = s_b;
     const float a2 = s_a2, b2 = s_b2;
     const float denom = (float)(size - 3);
-    float* row_a = m + (size_t)(a + base) * n0 + base;
-    float* row_b = m + (size_t)(b + base) * n0 + base;
+    float* row_a = m + (size_t)(a + base) * ld + base;
+    float* row_b = m + (size_t)(b + base) * ld + base;
     // Every index but a: two subtractions (NJ_compute_r), the joined distance, one addition
     // (NJ_collapse).  Indices are visited in the order the reference sums the joined row's r --
     // i = a+1 .. size-1, then 0 .. a-1 -- in chunks of blockDim.x staged in shared memory, so
@@ -129,7 +130,7 @@ k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__
             const float c = (float)((double)__fadd_rn(__fsub_rn(da, a2), __fsub_rn(db, b2)) / 2.0);
             s_cv[buf][tid] = c;
             row_a[i] = c;
-            m[(size_t)(i + base) * n0 + a + base] = c;
+            m[(size_t)(i + base) * ld + a + base] = c;
             float ri = __fsub_rn(__fsub_rn(r[i + base], da), db);
             ri = __fadd_rn(ri, c);
             r[i + base] = ri;
@@ -149,12 +150,12 @@ k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__
     }
     __syncthreads();
     // index 0 takes over index b; index 0 is dropped by the caller (base + 1)
-    const float* row_0 = m + (size_t)base * n0 + base;
+    const float* row_0 = m + (size_t)base * ld + base;
     for (int i = tid; i < size; i += blockDim.x) {
         if (i == b) continue;
         const float v = row_0[i];
         row_b[i] = v;
-        m[(size_t)(i + base) * n0 + b + base] = v;
+        m[(size_t)(i + base) * ld + b + base] = v;
     }
     if (tid == 0) {
         row_b[b] = 0.0f;
@@ -178,8 +179,7 @@ k_nj_join(float* __restrict__ m, int n0, int base, int size, float* __restrict__
 struct lzg_nj_state {
     unsigned bar_count, bar_gen;
     unsigned long long key[2];
-    int pend_phys, pend_terms, err;
-    float pend_denom;
+    int err;
     // the join's operands, read by the LAST CTA to reach the barrier behind the scan (every minimum is in by then) and before it
     // lets the others go: the update overwrites d(a, b) and r2[b] while other threads would still be reading them
     int a, b;
@@ -187,31 +187,30 @@ struct lzg_nj_state {
     unsigned long long t_scan, t_wait1, t_update, t_wait2;  // LZG_NJ_DEBUG: ns spent per phase by CTA 1 (summed over the joins)
 };
 
-// snap != nullptr: the barrier behind the scan -- the last arriver reads the winning pair and its operands into *st.
-__device__ __forceinline__ bool nj_barrier(lzg_nj_state* st, unsigned n_ctas, const float* snap_m = nullptr, const float* snap_r2 = nullptr, int n0 = 0,
-                                           int base = 0, int parity = 0) {
+// Grid barrier number `phase` (1, 2, ... -- every CTA counts its own barriers, so nothing is read before arriving): arrivals
+// accumulate in bar_count, the CTA that brings it to phase * n_ctas publishes bar_gen = phase.
+// snap_m != nullptr: the barrier behind the scan -- the last arriver reads the winning pair and its operands into *st.
+__device__ __forceinline__ bool nj_barrier(lzg_nj_state* st, unsigned n_ctas, unsigned phase, const float* snap_m = nullptr, const float* snap_r2 = nullptr,
+                                           int n0 = 0, int ld = 0, int base = 0, int parity = 0) {
     __syncthreads();
     __shared__ int s_ok;
     if (threadIdx.x == 0) {
         int ok = 1;
-        const unsigned gen = (unsigned)ld_acquire_i(reinterpret_cast<const int*>(&st->bar_gen));
-        __threadfence();
-        if (atomicAdd(&st->bar_count, 1u) == n_ctas - 1) {
+        unsigned old;
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(&st->bar_count) : "memory");
+        if (old == phase * n_ctas - 1) {
             if (snap_m) {
-                __threadfence();
                 const unsigned idx = (unsigned)(__ldcg(&st->key[parity]) & 0xffffffffull);
                 const int a = (int)(idx / (unsigned)n0), b = (int)(idx % (unsigned)n0);
                 st->a = a, st->b = b;
-                st->dab = __ldcg(snap_m + (size_t)(a + base) * n0 + b + base);
+                st->dab = __ldcg(snap_m + (size_t)(a + base) * ld + b + base);
                 st->r2a = __ldcg(snap_r2 + a + base);
                 st->r2b = __ldcg(snap_r2 + b + base);
             }
-            st->bar_count = 0;
-            __threadfence();
-            st_release_i(reinterpret_cast<int*>(&st->bar_gen), (int)(gen + 1));
+            st_release_i(reinterpret_cast<int*>(&st->bar_gen), (int)phase);
         } else {
             long long spins = 0;
-            while ((unsigned)ld_acquire_i(reinterpret_cast<const int*>(&st->bar_gen)) == gen) {
+            while ((unsigned)ld_acquire_i(reinterpret_cast<const int*>(&st->bar_gen)) != phase) {
                 if (++spins > (1ll << 27)) {  // seconds: a CTA is missing -- give up instead of hanging the device
                     st->err = 1;
                     ok = 0;
@@ -236,31 +235,186 @@ __device__ __forceinline__ unsigned long long nj_key(float d, float r2i, float r
     return ((unsigned long long)float_order(cur) << 32) | ((unsigned)i * (unsigned)n0 + (unsigned)j);
 }
 
+// sum + v[0] + v[1] + ... + v[cnt-1], one float32 add after the other (the reference's order), v in shared memory and 16-byte
+// aligned.  Software pipeline: the next 32 terms are loaded (8 x LDS.128) while the 32 dependent adds of the current ones run;
+// volatile asm keeps ptxas from sinking each load next to its use (it did: 10 instead of 4 cycles per term).
+#define NJ_LDS8(dst, addr)                                                                                                                   \
+    _Pragma("unroll") for (int u = 0; u < 8; u++) asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"                                  \
+                                                               : "=f"(dst[u].x), "=f"(dst[u].y), "=f"(dst[u].z), "=f"(dst[u].w)           \
+                                                               : "r"((addr) + 16 * u))
+#define NJ_ADD32(sum, src)                                                       \
+    _Pragma("unroll") for (int u = 0; u < 8; u++) {                              \
+        asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(sum) : "f"(src[u].x));      \
+        asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(sum) : "f"(src[u].y));      \
+        asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(sum) : "f"(src[u].z));      \
+        asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(sum) : "f"(src[u].w));      \
+    }
+__device__ __forceinline__ float nj_sum_in_order(const float* v_smem, int cnt, float sum) {
+    int q = 0;
+    if (cnt >= 64) {
+        float4 v[8], w[8];  // two register sets in turn: no copies on the chain
+        const unsigned sa = (unsigned)__cvta_generic_to_shared(v_smem);
+        NJ_LDS8(v, sa);
+#pragma unroll 1
+        for (; q + 64 <= cnt; q += 64) {
+            NJ_LDS8(w, sa + 4 * (q + 32));
+            NJ_ADD32(sum, v);
+            NJ_LDS8(v, sa + 4 * (q + 128 <= cnt ? q + 64 : 0));  // the last round re-reads the first block (unused)
+            NJ_ADD32(sum, w);
+        }
+    }
+    for (; q < cnt; q++) sum = __fadd_rn(sum, v_smem[q]);
+    return sum;
+}
+#undef NJ_LDS8
+#undef NJ_ADD32
+
+// NJ_min_transform over the active triangle, all CTAs but CTA 0; returns this thread's best key.
+// Physical indices p = logical + base: the active block is rows / columns [base, n0) whatever the join, so a row's pairs end at
+// column n0 - 1 and rows are read as aligned float4 groups (the pitch is a multiple of 4, pad columns hold zeros).  A task is one
+// chunk of 128 groups (2 KB) of one row: 32 lanes x 4 independent 16-byte loads.  Rows are paired -- p1 = base + v with
+// p2 = n0 - 2 - v -- so that every virtual row has (at most) C chunks and task t -> v = t / C, chunk t % C; warps take tasks round
+// robin.  SMEM: r2 comes from shared memory where the pending node and the pad columns hold -inf (their pairs evaluate to +inf).
+template <bool SMEM>
+__device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ m, int n0, int ld, int base, int size, int pendp, const float* __restrict__ r2,
+                                                      const float* s_r2, int r2_org, int n_scan, int scan_rank) {
+    const float inf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
+    const int lane = threadIdx.x & 31;
+    const unsigned CGL = (unsigned)(n0 - 1) >> 2;  // last column group
+    const unsigned V = (unsigned)size / 2;         // ceil((size - 1) / 2) virtual rows
+    const unsigned C = (2 * CGL + 3 - ((unsigned)(base + n0) >> 2) + 254) >> 7;
+    const unsigned T = V * C;
+    const unsigned n_warps = (unsigned)n_scan * 16, warp = (unsigned)scan_rank * 16 + (threadIdx.x >> 5);
+    unsigned long long best = ~0ull;
+    float bestv = inf;
+    for (unsigned t = warp; t < T; t += n_warps) {
+        const unsigned v = t / C;
+        unsigned ch = t - v * C;
+        int p = base + (int)v;
+        unsigned f = (unsigned)(p + 1) >> 2, nch = (CGL - f + 128) >> 7;
+        if (ch >= nch) {  // the partner row's chunks
+            ch -= nch;
+            const int p2 = n0 - 2 - (int)v;
+            if (p2 == p) continue;
+            p = p2;
+            f = (unsigned)(p + 1) >> 2, nch = (CGL - f + 128) >> 7;
+            if (ch >= nch) continue;
+        }
+        if (p == pendp) continue;
+        const unsigned cg0 = f + ch * 128 + lane;
+        const float* row = m + (size_t)p * ld;
+        const float ri = SMEM ? s_r2[p - r2_org] : __ldcg(r2 + p);
+        float4 d[4], rj[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const unsigned cg = cg0 + 32 * u;
+            if (cg <= CGL) {
+                d[u] = __ldcg(reinterpret_cast<const float4*>(row + 4 * cg));
+                rj[u] = SMEM ? *reinterpret_cast<const float4*>(s_r2 + ((int)(4 * cg) - r2_org)) : __ldcg(reinterpret_cast<const float4*>(r2 + 4 * cg));
+            } else {
+                d[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                rj[u] = make_float4(ninf, ninf, ninf, ninf);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int c0 = (int)(4 * (cg0 + 32 * u));
+            float c[4];
+            c[0] = __fsub_rn(d[u].x, __fadd_rn(ri, rj[u].x));
+            c[1] = __fsub_rn(d[u].y, __fadd_rn(ri, rj[u].y));
+            c[2] = __fsub_rn(d[u].z, __fadd_rn(ri, rj[u].z));
+            c[3] = __fsub_rn(d[u].w, __fadd_rn(ri, rj[u].w));
+            if (u == 0 && c0 <= p) {  // the row's first group reaches back to the diagonal
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    if (c0 + e <= p) c[e] = inf;
+            }
+            if (!SMEM) {
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    if (c0 + e >= n0 || c0 + e == pendp) c[e] = inf;
+            }
+            const float g4 = fminf(fminf(c[0], c[1]), fminf(c[2], c[3]));
+            if (g4 <= bestv && g4 < inf) {  // rare once a thread has seen a few groups; on a tie the index decides
+                const int e4 = c[0] == g4 ? 0 : c[1] == g4 ? 1 : c[2] == g4 ? 2 : 3;  // the first column wins a tie
+                const unsigned long long key =
+                    ((unsigned long long)float_order(__fadd_rn(g4, 0.0f)) << 32) | ((unsigned)(p - base) * (unsigned)n0 + (unsigned)(c0 + e4 - base));
+                if (key < best) best = key, bestv = g4;
+            }
+        }
+    }
+    return best;
+}
+
 __global__ void __launch_bounds__(512, 2)
-k_nj_persistent(float* __restrict__ m, int n0, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node, float* __restrict__ cvec,
-                int32_t* __restrict__ left, int32_t* __restrict__ right, lzg_nj_state* __restrict__ st, int r2_in_smem) {
+k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node, float* __restrict__ cvec,
+                int32_t* __restrict__ left, int32_t* __restrict__ right, lzg_nj_state* __restrict__ st, int r2_in_smem, unsigned long long* __restrict__ dbg, int* __restrict__ smid) {
     const int tid = threadIdx.x, n_ctas = gridDim.x;
-    const int n_scan = n_ctas - 1;  // CTA 0 owns the joined node (its row sum and its pairs); the others share the triangle
+    // CTA 0 owns the joined node (its row sum and its pairs); the others share the triangle -- except a CTA that landed on CTA 0's
+    // SM: it only takes part in the updates, so that the lane adding the row sum (one dependent float add after the other, the
+    // serial part of every join) does not compete for issue slots with sixteen scanning warps.
+    int n_scan = n_ctas - 1, scan_rank = (int)blockIdx.x - 1;
+    unsigned phase = 0;  // barriers passed
+    bool scans = blockIdx.x != 0;
+    if (smid) {  // n_ctas <= 512
+        if (tid == 0) {
+            unsigned id;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(id));
+            smid[blockIdx.x] = (int)id;
+        }
+        if (!nj_barrier(st, n_ctas, ++phase)) return;
+        const int sm0 = __ldcg(smid);
+        const bool other = tid > 0 && tid < n_ctas && __ldcg(smid + tid) != sm0;  // a scanning CTA
+        n_scan = __syncthreads_count(other);
+        scan_rank = __syncthreads_count(other && tid < (int)blockIdx.x);
+        scans = blockIdx.x != 0 && __ldcg(smid + blockIdx.x) != sm0;
+        if (n_scan == 0) n_scan = n_ctas - 1, scan_rank = (int)blockIdx.x - 1, scans = blockIdx.x != 0;  // a single SM: nothing to separate
+    }
     __shared__ unsigned long long s_best[16];
     __shared__ __align__(16) float s_sum[256];
     __shared__ float s_r2p;
-    extern __shared__ float s_r2[];  // r2 of the active indices (logical), when n0 floats fit
-    const bool timed = blockIdx.x == 1 && tid == 0;
-    int base = 0, joined = n0;
+    extern __shared__ __align__(16) float s_r2[];  // r2 of the active indices (logical), when n0 floats fit
+    const bool timed = scans && scan_rank == 0 && tid == 0;
+    int base = 0, joined = n0, pend = -1;
     for (int size = n0; size > 2; size--, base++, joined++) {
         const int parity = joined & 1;
-        unsigned long long t0 = 0;
+        unsigned long long t0 = 0, ts0 = 0;
         if (timed) t0 = nj_now();
+        if (dbg && tid == 0) ts0 = nj_now();
         // the node joined last time: its row sum is not known yet (CTA 0 adds it up now)
-        const int pend = __ldcg(&st->pend_phys) - base;  // logical index now; < 0: none
+        // pend: the logical index (in this join's numbering) of the node joined last time; < 0: none
         unsigned long long best = ~0ull;
         if (blockIdx.x == 0) {
             if (pend >= 0) {
-                if (tid < 32) {
-                    const int terms = __ldcg(&st->pend_terms);
+                const int terms = size;                    // the join before this one ran at size + 1: size terms,
+                const float pend_denom = (float)(size - 2);  // and divided by (size + 1) - 3
+                // the pairs of the new node: its row of the (symmetric) matrix.  The operands of the first 2048 are fetched now,
+                // before the row sum they wait for is known
+                const float* row_p = m + (size_t)(pend + base) * ld + base;
+                float d0[4], rq0[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int q = tid + 512 * u;
+                    const bool ok = q < size && q != pend;
+                    d0[u] = ok ? __ldcg(row_p + q) : 0.0f;
+                    rq0[u] = ok ? __ldcg(r2 + q + base) : 0.0f;
+                }
+                if (r2_in_smem) {
+                    // every thread of the CTA fetches its share of the terms (independent L2 loads), then one lane adds them in order
+#pragma unroll 8
+                    for (int c = tid; c < terms; c += 512) s_r2[c] = __ldcg(cvec + c);
+                    __syncthreads();
+                    if (tid == 0) {
+                        const float sum = nj_sum_in_order(s_r2, terms, 0.0f);
+                        const float r2p = __fdiv_rn(sum, pend_denom);
+                        r[pend + base] = sum;
+                        r2[pend + base] = r2p;
+                        s_r2p = r2p;
+                        if (dbg) dbg[n_ctas] += nj_now() - ts0;
+                    }
+                } else if (tid < 32) {
+                    // the terms come through shared memory in chunks of 256: all 32 lanes fetch the NEXT chunk while lane 0 adds
                     float sum = 0.0f;
-                    // the terms come through shared memory in chunks of 256: all 32 lanes fetch the NEXT chunk (independent L2 loads)
-                    // while lane 0 adds the current one in order -- the chain of dependent float adds is then the only cost
                     float nxt[8];
 #pragma unroll
                     for (int q = 0; q < 8; q++) nxt[q] = tid + 32 * q < terms ? __ldcg(cvec + tid + 32 * q) : 0.0f;
@@ -271,29 +425,28 @@ k_nj_persistent(float* __restrict__ m, int n0, float* __restrict__ r, float* __r
                         const int p1 = p0 + 256;
 #pragma unroll
                         for (int q = 0; q < 8; q++) nxt[q] = p1 + tid + 32 * q < terms ? __ldcg(cvec + p1 + tid + 32 * q) : 0.0f;
-                        if (tid == 0) {
-                            const int cnt = min(256, terms - p0);
-                            int q = 0;
-                            for (; q + 4 <= cnt; q += 4) {
-                                const float4 v = *reinterpret_cast<const float4*>(s_sum + q);
-                                sum = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(sum, v.x), v.y), v.z), v.w);
-                            }
-                            for (; q < cnt; q++) sum = __fadd_rn(sum, s_sum[q]);
-                        }
+                        if (tid == 0) sum = nj_sum_in_order(s_sum, min(256, terms - p0), sum);
                         __syncwarp();
                     }
                     if (tid == 0) {
-                        const float r2p = __fdiv_rn(sum, __ldcg(&st->pend_denom));
+                        const float r2p = __fdiv_rn(sum, pend_denom);
                         r[pend + base] = sum;
                         r2[pend + base] = r2p;
                         s_r2p = r2p;
+                        if (dbg) dbg[n_ctas] += nj_now() - ts0;
                     }
                 }
                 __syncthreads();
-                // the pairs of the new node: its row of the (symmetric) matrix, the whole CTA, every load independent
                 const float r2p = s_r2p;
-                const float* row_p = m + (size_t)(pend + base) * n0 + base;
-                for (int q0 = tid; q0 < size; q0 += 4 * 512) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int q = tid + 512 * u;
+                    if (q < size && q != pend) {
+                        const unsigned long long k = nj_key(d0[u], q < pend ? rq0[u] : r2p, q < pend ? r2p : rq0[u], min(q, pend), max(q, pend), n0);
+                        best = k < best ? k : best;
+                    }
+                }
+                for (int q0 = tid + 4 * 512; q0 < size; q0 += 4 * 512) {
                     float d[4], rq[4];
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
@@ -312,47 +465,16 @@ k_nj_persistent(float* __restrict__ m, int n0, float* __restrict__ r, float* __r
                     }
                 }
             }
-        } else {
-            // The triangle as V = ceil((size-1)/2) rows of exactly `size` elements: row v (size-1-v pairs) followed by row
-            // size-2-v (v+1 pairs).  Element e of that rectangle -> v = e / size, k = e % size; every CTA takes an equal
-            // contiguous range of e, every thread eight independent loads at a time -- short rows cost no extra round trips.
+        } else if (scans) {
+            const int pendp = pend >= 0 ? pend + base : -1;
+            const int r2_org = base & ~3;  // s_r2[c - r2_org] = r2 of physical column c
             if (r2_in_smem) {
-                for (int q = tid; q < size; q += 512) s_r2[q] = __ldcg(r2 + q + base);
+                // minus infinity for the pending node and the pad columns: d - (r2_i + r2_j) is then +inf and never the minimum
+                for (int c = r2_org + tid; c < ld; c += 512) s_r2[c - r2_org] = c >= base && c < n0 && c != pendp ? __ldcg(r2 + c) : __int_as_float(0xff800000);
                 __syncthreads();
-            }
-            const unsigned V = (unsigned)size / 2;  // ceil((size - 1) / 2)
-            const unsigned long long E = (unsigned long long)V * (unsigned)size;
-            const unsigned lo = (unsigned)(E * (unsigned)(blockIdx.x - 1) / (unsigned)n_scan);
-            const unsigned hi = (unsigned)(E * (unsigned)blockIdx.x / (unsigned)n_scan);
-            for (unsigned e0 = lo + tid; e0 < hi; e0 += 8 * 512) {
-                float d[8], ri[8], rj[8];
-                int ii[8], jj[8];
-#pragma unroll
-                for (int q = 0; q < 8; q++) {
-                    const unsigned e = e0 + q * 512;
-                    const unsigned v = e / (unsigned)size, k = e - v * (unsigned)size;
-                    const int w = size - 2 - (int)v;
-                    const bool first = (int)k < size - 1 - (int)v;
-                    const int i = first ? (int)v : w, j = first ? (int)(v + 1 + k) : (int)k;
-                    const bool ok = e < hi && (first || w != (int)v) && i != pend && j != pend;
-                    ii[q] = ok ? i : -1;
-                    jj[q] = j;
-                    d[q] = ok ? __ldcg(m + (size_t)(i + base) * n0 + j + base) : 0.0f;
-                    if (r2_in_smem) {
-                        ri[q] = ok ? s_r2[i] : 0.0f;
-                        rj[q] = ok ? s_r2[j] : 0.0f;
-                    } else {
-                        ri[q] = ok ? __ldcg(r2 + i + base) : 0.0f;
-                        rj[q] = ok ? __ldcg(r2 + j + base) : 0.0f;
-                    }
-                }
-#pragma unroll
-                for (int q = 0; q < 8; q++) {
-                    if (ii[q] >= 0) {
-                        const unsigned long long k = nj_key(d[q], ri[q], rj[q], ii[q], jj[q], n0);
-                        best = k < best ? k : best;
-                    }
-                }
+                best = nj_scan<true>(m, n0, ld, base, size, pendp, r2, s_r2, r2_org, n_scan, scan_rank);
+            } else {
+                best = nj_scan<false>(m, n0, ld, base, size, pendp, r2, s_r2, r2_org, n_scan, scan_rank);
             }
         }
 #pragma unroll
@@ -365,16 +487,17 @@ k_nj_persistent(float* __restrict__ m, int n0, float* __restrict__ r, float* __r
         if (tid == 0) {
             for (int w = 1; w < (int)(blockDim.x >> 5); w++) best = s_best[w] < best ? s_best[w] : best;
             if (best != ~0ull) atomicMin(&st->key[parity], best);
+            if (dbg) dbg[blockIdx.x] += nj_now() - ts0;
         }
         unsigned long long t1 = 0, t2 = 0, t3 = 0;
         if (timed) t1 = nj_now();
-        if (!nj_barrier(st, n_ctas, m, r2, n0, base, parity)) return;
+        if (!nj_barrier(st, n_ctas, ++phase, m, r2, n0, ld, base, parity)) return;
         if (timed) t2 = nj_now();
         // ---- update: the join (NJ_compute_r + NJ_collapse) and the relabelling, one thread per index ----
         const int a = __ldcg(&st->a), b = __ldcg(&st->b);
-        float* row_a = m + (size_t)(a + base) * n0 + base;
-        float* row_b = m + (size_t)(b + base) * n0 + base;
-        const float* row_0 = m + (size_t)base * n0 + base;
+        float* row_a = m + (size_t)(a + base) * ld + base;
+        float* row_b = m + (size_t)(b + base) * ld + base;
+        const float* row_0 = m + (size_t)base * ld + base;
         const float dab = __ldcg(&st->dab);
         const float r2a = __ldcg(&st->r2a), r2b = __ldcg(&st->r2b);
         const float a2 = (float)((double)__fadd_rn(dab, __fsub_rn(r2a, r2b)) / 2.0);
@@ -389,7 +512,7 @@ k_nj_persistent(float* __restrict__ m, int n0, float* __restrict__ r, float* __r
             cvec[i > a ? i - a - 1 : size - a - 1 + i] = c;  // the order the reference adds them in
             if (i == b) continue;  // index b is overwritten by the relabelling below
             row_a[i] = c;
-            m[(size_t)(i + base) * n0 + a + base] = c;
+            m[(size_t)(i + base) * ld + a + base] = c;
             float ri = __fsub_rn(__fsub_rn(__ldcg(r + i + base), da), db);
             ri = __fadd_rn(ri, c);
             r[i + base] = ri;
@@ -398,7 +521,7 @@ k_nj_persistent(float* __restrict__ m, int n0, float* __restrict__ r, float* __r
             // index 0 (after the update) takes over index b; index 0 itself is dropped by base + 1
             const float v = a == 0 ? c : __ldcg(row_0 + i);
             row_b[i] = v;
-            m[(size_t)(i + base) * n0 + b + base] = v;
+            m[(size_t)(i + base) * ld + b + base] = v;
             if (i == 0) {  // a != 0 here: the updated row 0 also holds c_0 at column a
                 row_b[a] = c;
                 row_a[b] = c;
@@ -412,13 +535,11 @@ k_nj_persistent(float* __restrict__ m, int n0, float* __restrict__ r, float* __r
             const int where = a == 0 ? b : a;  // where the joined node lives from now on
             if (a != 0) node[b + base] = __ldcg(node + base);
             node[where + base] = joined;
-            st->pend_phys = where + base;
-            st->pend_terms = size - 1;
-            st->pend_denom = denom;
             st->key[parity ^ 1] = ~0ull;  // the next join's minimum; nobody touches it before the barrier below
         }
+        pend = (a == 0 ? b : a) - 1;  // where the joined node lives, in the next join's numbering (base moves on by one)
         if (timed) t3 = nj_now();
-        if (!nj_barrier(st, n_ctas)) return;
+        if (!nj_barrier(st, n_ctas, ++phase)) return;
         if (timed) {
             const unsigned long long t4 = nj_now();
             st->t_scan += t1 - t0, st->t_wait1 += t2 - t1, st->t_update += t3 - t2, st->t_wait2 += t4 - t3;
@@ -459,7 +580,10 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     unsigned long long* d_key = nullptr;
     float* d_cvec = nullptr;
     lzg_nj_state* d_state = nullptr;
+    unsigned long long* d_dbg = nullptr;
+    int* d_smid = nullptr;
     const size_t nn = (size_t)n * n;
+    const int ld = (n + 3) & ~3;  // row pitch of the float matrix: rows start 16-byte aligned
     auto release = [&]() {
         lzg_dev_free(ctx, d_D);
         lzg_dev_free(ctx, d_perm);
@@ -472,15 +596,18 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
         lzg_dev_free(ctx, d_key);
         lzg_dev_free(ctx, d_cvec);
         lzg_dev_free(ctx, d_state);
+        lzg_dev_free(ctx, d_dbg);
+        lzg_dev_free(ctx, d_smid);
     };
+    const auto t_begin = std::chrono::steady_clock::now();
     cudaError_t e = lzg_dev_alloc(ctx, (void**)&d_D, sizeof(int32_t) * nn);
-    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_m, sizeof(float) * nn);
+    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_m, sizeof(float) * (size_t)n * ld);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_perm, sizeof(int32_t) * n);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_left, sizeof(int32_t) * total);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_right, sizeof(int32_t) * total);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_node, sizeof(int) * n);
-    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r, sizeof(float) * n);
-    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r2, sizeof(float) * n);
+    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r, sizeof(float) * ld);
+    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r2, sizeof(float) * ld);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_key, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_D, D_host, sizeof(int32_t) * nn, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_perm, perm, sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream);
@@ -489,29 +616,41 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
         release();
         return lzg_fail(ctx, LZG_ERR_CUDA, "lzg_nj_seed_tree: setup", e);
     }
-    k_nj_gather<<<dim3(std::max(1, std::min(32, (n + 255) / 256)), n), 256, 0, ctx->stream>>>(d_D, d_perm, d_m, n);
+    k_nj_gather<<<dim3(std::max(1, std::min(32, (n + 255) / 256)), n), 256, 0, ctx->stream>>>(d_D, d_perm, d_m, n, ld);
     ctx->launches++;
-    k_nj_init_r<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_m, n, d_r, d_r2, d_node);
+    k_nj_init_r<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_m, n, ld, d_r, d_r2, d_node);
     ctx->launches++;
+    if (getenv("LZG_NJ_DEBUG")) {
+        cudaStreamSynchronize(ctx->stream);
+        fprintf(stderr, "[lzg nj] upload + gather + row sums: %.1f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
+    }
     // one persistent cooperative launch for all joins; LZG_NJ_PERSISTENT=0 keeps the two-launches-per-join form (the cross-check)
     const bool persistent = !(getenv("LZG_NJ_PERSISTENT") && atoi(getenv("LZG_NJ_PERSISTENT")) == 0);
     bool done = false;
     if (persistent && n >= 4) {
         int per_sm = 0;
-        const size_t smem_r2 = n <= 12000 ? sizeof(float) * (size_t)n : 0;  // r2 staged in shared memory under the 48 KB default
+        size_t smem_r2 = sizeof(float) * (size_t)(ld + 4);  // r2 (scanning CTAs) / the joined row's terms (CTA 0) in shared memory
+        if (smem_r2 > 110 * 1024) smem_r2 = 0;               // two CTAs per SM must fit; beyond n = 28,000 both come from L2
+        if (getenv("LZG_NJ_SMEM") && atoi(getenv("LZG_NJ_SMEM")) == 0) smem_r2 = 0;  // tests: the path of very large n
+        if (smem_r2 > 48 * 1024) cudaFuncSetAttribute(k_nj_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r2);
         cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nj_persistent, 512, smem_r2);
         if (ce == cudaSuccess && per_sm >= 1) ce = lzg_dev_alloc(ctx, (void**)&d_cvec, sizeof(float) * (size_t)n);
         if (ce == cudaSuccess && per_sm >= 1) ce = lzg_dev_alloc(ctx, (void**)&d_state, sizeof(lzg_nj_state));
+        const int max_grid = ctx->sm_count * 2 + 1;
+        if (ce == cudaSuccess && per_sm >= 1 && max_grid <= 512) ce = lzg_dev_alloc(ctx, (void**)&d_smid, sizeof(int) * max_grid);
+        if (ce == cudaSuccess && per_sm >= 1 && getenv("LZG_NJ_DEBUG")) {
+            ce = lzg_dev_alloc(ctx, (void**)&d_dbg, sizeof(unsigned long long) * (max_grid + 1));
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(d_dbg, 0, sizeof(unsigned long long) * (max_grid + 1), ctx->stream);
+        }
         if (ce == cudaSuccess && per_sm >= 1) {
             lzg_nj_state init;
             memset(&init, 0, sizeof(init));
             init.key[0] = init.key[1] = ~0ull;
-            init.pend_phys = -1;
             ce = cudaMemcpyAsync(d_state, &init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream);
             int grid = std::min(ctx->sm_count * std::min(per_sm, 2), 1 + std::max(1, n / 2));
             grid = std::max(grid, 2);  // CTA 0 owns the joined node, the others scan
-            int n_arg = n, in_smem = smem_r2 > 0;
-            void* args[] = {(void*)&d_m, (void*)&n_arg, (void*)&d_r, (void*)&d_r2, (void*)&d_node, (void*)&d_cvec, (void*)&d_left, (void*)&d_right, (void*)&d_state, (void*)&in_smem};
+            int n_arg = n, ld_arg = ld, in_smem = smem_r2 > 0;
+            void* args[] = {(void*)&d_m, (void*)&n_arg, (void*)&ld_arg, (void*)&d_r, (void*)&d_r2, (void*)&d_node, (void*)&d_cvec, (void*)&d_left, (void*)&d_right, (void*)&d_state, (void*)&in_smem, (void*)&d_dbg, (void*)&d_smid};
             if (ce == cudaSuccess) ce = cudaLaunchCooperativeKernel((void*)k_nj_persistent, dim3(grid), dim3(512), args, smem_r2, ctx->stream);
             if (ce == cudaSuccess) {
                 ctx->launches++;
@@ -521,6 +660,18 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
                 if (ce == cudaSuccess && getenv("LZG_NJ_DEBUG"))
                     fprintf(stderr, "[lzg nj] n %d, %d CTAs: scan %.1f ms, wait behind the scan %.1f ms, update %.1f ms, wait behind the update %.1f ms\n", n, grid,
                             back.t_scan * 1e-6, back.t_wait1 * 1e-6, back.t_update * 1e-6, back.t_wait2 * 1e-6);
+                if (ce == cudaSuccess && d_dbg) {
+                    std::vector<unsigned long long> h(grid + 1);
+                    cudaMemcpy(h.data(), d_dbg, sizeof(unsigned long long) * (grid + 1), cudaMemcpyDeviceToHost);
+                    unsigned long long lo = ~0ull, hi = 0, sum = 0;
+                    int arg = 1;
+                    for (int c = 1; c < grid; c++) {
+                        lo = std::min(lo, h[c]), sum += h[c];
+                        if (h[c] > hi) hi = h[c], arg = c;
+                    }
+                    fprintf(stderr, "[lzg nj] scan phase per CTA: min %.1f, mean %.1f, max %.1f ms (CTA %d); CTA 0: %.1f ms of which the row sum %.1f ms\n", lo * 1e-6,
+                            sum * 1e-6 / std::max(1, grid - 1), hi * 1e-6, arg, h[0] * 1e-6, h[grid] * 1e-6);
+                }
                 if (ce == cudaSuccess && back.err) {
                     release();
                     return lzg_fail(ctx, LZG_ERR_STATE, "lzg_nj_seed_tree: a grid barrier timed out");
@@ -534,8 +685,8 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
         int base = 0, joined = n;
         for (int size = n; size > 2; size--, base++, joined++) {
             const int grid = std::max(1, std::min(size - 1, ctx->sm_count * 8));
-            k_nj_argmin<<<grid, 256, 0, ctx->stream>>>(d_m, n, base, size, d_r2, d_key);
-            k_nj_join<<<1, 1024, 0, ctx->stream>>>(d_m, n, base, size, d_r, d_r2, d_node, d_key, d_left, d_right, joined);
+            k_nj_argmin<<<grid, 256, 0, ctx->stream>>>(d_m, n, ld, base, size, d_r2, d_key);
+            k_nj_join<<<1, 1024, 0, ctx->stream>>>(d_m, n, ld, base, size, d_r, d_r2, d_node, d_key, d_left, d_right, joined);
             ctx->launches += 2;
         }
         k_nj_finish<<<1, 1, 0, ctx->stream>>>(d_node, base, d_left, d_right, joined);

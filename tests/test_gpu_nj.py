@@ -102,7 +102,7 @@ def test_nj_gpu_equals_host_library(ctx):
         assert np.array_equal(left, cl) and np.array_equal(right, cr), n
 
 
-@pytest.mark.parametrize("n,seed,hi", [(1500, 21, 400), (2500, 22, 3)])
+@pytest.mark.parametrize("n,seed,hi", [(1500, 21, 400), (2500, 22, 3), (1026, 23, 50), (13001, 24, 9)])
 def test_nj_persistent_kernel_on_larger_matrices(ctx, monkeypatch, n, seed, hi):
     """All joins in one cooperative launch (k_nj_persistent: grid barriers, the sequential row sum overlapped with the next
     scan) against the CPU restatement and against the two-launches-per-join form; hi = 3 makes almost every scan a tie."""
@@ -112,8 +112,17 @@ def test_nj_persistent_kernel_on_larger_matrices(ctx, monkeypatch, n, seed, hi):
     D = np.triu(D, 1) + np.triu(D, 1).T
     perm = search.clearcut_shuffle(n, seed)
     left, right = ctx.nj_seed_tree(D, perm)
-    cl, cr = search.nj_seed_tree_cpu(D, perm)
+    if n <= 3000:
+        cl, cr = search.nj_seed_tree_cpu(D, perm)
+    else:  # minutes on one core: the per-join kernels (pinned to the CPU restatement above) stand in
+        monkeypatch.setenv("LZG_NJ_PERSISTENT", "0")
+        cl, cr = ctx.nj_seed_tree(D, perm)
+        monkeypatch.delenv("LZG_NJ_PERSISTENT")
     assert np.array_equal(left, cl) and np.array_equal(right, cr)
+    monkeypatch.setenv("LZG_NJ_SMEM", "0")  # the form for n > 28,000: r2 and the joined row's terms straight from L2
+    l3, r3 = ctx.nj_seed_tree(D, perm)
+    assert np.array_equal(l3, cl) and np.array_equal(r3, cr)
+    monkeypatch.delenv("LZG_NJ_SMEM")
     monkeypatch.setenv("LZG_NJ_PERSISTENT", "0")
     l2, r2 = ctx.nj_seed_tree(D, perm)
     assert np.array_equal(l2, cl) and np.array_equal(r2, cr)

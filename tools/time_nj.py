@@ -16,8 +16,11 @@ from lazac_copy_number_b200.api import Context, Profiles  # noqa: E402
 sizes = [int(x) for x in sys.argv[1:]] or [2000, 10000]
 with Context(0) as ctx:
     for k, n in enumerate(sizes):
-        prof = synth.make_profiles(n, 2000, 2, seed=0)
-        bp = synth.bp_from_cn(prof["cn"], prof["seg"]).astype(np.int8)
+        if os.environ.get("NJ_RANDOM_PROFILES"):  # seconds instead of a minute of tree simulation in Python
+            bp = (np.random.default_rng(0).integers(0, 40, (n, 4000)) == 0).astype(np.int8) * np.random.default_rng(1).integers(-2, 3, (n, 4000)).astype(np.int8)
+        else:
+            prof = synth.make_profiles(n, 2000, 2, seed=0)
+            bp = synth.bp_from_cn(prof["cn"], prof["seg"]).astype(np.int8)
         gp = Profiles(ctx, bp)
         D = gp.distance_matrix()
         gp.free()
@@ -27,7 +30,7 @@ with Context(0) as ctx:
         left, right = ctx.nj_seed_tree(D, perm)
         dt = time.perf_counter() - t0
         print("n = %d: GPU NJ %.3f s (%.1f G matrix elements scanned/s incl. upload)" % (n, dt, n ** 3 / 6 / dt / 1e9), flush=True)
-        if k == 0:
+        if k == 0 and not os.environ.get("NJ_SKIP_CLI"):
             lazac = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "host", "lazac")
             with tempfile.TemporaryDirectory() as d:
                 src = os.path.join(d, "m.txt")
