@@ -178,6 +178,7 @@ k_nj_join(float* __restrict__ m, int n0, int ld, int base, int size, float* __re
 // Every load of data another CTA may have written goes through L2 (ld.cg): L1 is not coherent across the barriers.
 struct lzg_nj_state {
     unsigned bar_count, bar_gen;
+    unsigned staged;  // k_nj_fused: CTAs that have read the rows the last join's deferred stores overwrite
     unsigned long long key[2];
     int err;
     // the join's operands, read by the LAST CTA to reach the barrier behind the scan (every minimum is in by then) and before it
@@ -191,7 +192,7 @@ struct lzg_nj_state {
 // accumulate in bar_count, the CTA that brings it to phase * n_ctas publishes bar_gen = phase.
 // snap_m != nullptr: the barrier behind the scan -- the last arriver reads the winning pair and its operands into *st.
 __device__ __forceinline__ bool nj_barrier(lzg_nj_state* st, unsigned n_ctas, unsigned phase, const float* snap_m = nullptr, const float* snap_r2 = nullptr,
-                                           int n0 = 0, int ld = 0, int base = 0, int parity = 0) {
+                                           int n0 = 0, int ld = 0, int base = 0, int parity = 0, const float* snap_r = nullptr, float snap_denom = 1.0f) {
     __syncthreads();
     __shared__ int s_ok;
     if (threadIdx.x == 0) {
@@ -204,8 +205,13 @@ __device__ __forceinline__ bool nj_barrier(lzg_nj_state* st, unsigned n_ctas, un
                 const int a = (int)(idx / (unsigned)n0), b = (int)(idx % (unsigned)n0);
                 st->a = a, st->b = b;
                 st->dab = __ldcg(snap_m + (size_t)(a + base) * ld + b + base);
-                st->r2a = __ldcg(snap_r2 + a + base);
-                st->r2b = __ldcg(snap_r2 + b + base);
+                if (snap_r2) {
+                    st->r2a = __ldcg(snap_r2 + a + base);
+                    st->r2b = __ldcg(snap_r2 + b + base);
+                } else {  // k_nj_fused keeps r only: r2 = r / (size - 2)
+                    st->r2a = __fdiv_rn(__ldcg(snap_r + a + base), snap_denom);
+                    st->r2b = __fdiv_rn(__ldcg(snap_r + b + base), snap_denom);
+                }
             }
             st_release_i(reinterpret_cast<int*>(&st->bar_gen), (int)phase);
         } else {
@@ -251,6 +257,7 @@ __device__ __forceinline__ unsigned long long nj_key(float d, float r2i, float r
     }
 __device__ __forceinline__ float nj_sum_in_order(const float* v_smem, int cnt, float sum) {
     int q = 0;
+    while (cnt > 0 && ((unsigned)__cvta_generic_to_shared(v_smem) & 15u)) sum = __fadd_rn(sum, *v_smem++), cnt--;  // up to a 16-byte boundary
     if (cnt >= 64) {
         float4 v[8], w[8];  // two register sets in turn: no copies on the chain
         const unsigned sa = (unsigned)__cvta_generic_to_shared(v_smem);
@@ -277,7 +284,8 @@ __device__ __forceinline__ float nj_sum_in_order(const float* v_smem, int cnt, f
 // robin.  SMEM: r2 comes from shared memory where the pending node and the pad columns hold -inf (their pairs evaluate to +inf).
 template <bool SMEM>
 __device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ m, int n0, int ld, int base, int size, int pendp, const float* __restrict__ r2,
-                                                      const float* s_r2, int r2_org, int n_scan, int scan_rank) {
+                                                      const float* s_r2, int r2_org, int n_scan, int scan_rank, int bp = -1,
+                                                      const float* __restrict__ row_standin = nullptr) {
     const float inf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
     const int lane = threadIdx.x & 31;
     const unsigned CGL = (unsigned)(n0 - 1) >> 2;  // last column group
@@ -302,7 +310,9 @@ __device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ 
         }
         if (p == pendp) continue;
         const unsigned cg0 = f + ch * 128 + lane;
-        const float* row = m + (size_t)p * ld;
+        // bp >= 0 (the fused kernel): physical index bp is taking over the data of the index dropped by the last join, whose row
+        // (row_standin) is still in place while the copy into row / column bp is under way -- read it from there
+        const float* row = p == bp ? row_standin : m + (size_t)p * ld;
         const float ri = SMEM ? s_r2[p - r2_org] : __ldcg(r2 + p);
         float4 d[4], rj[4];
 #pragma unroll
@@ -310,6 +320,14 @@ __device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ 
             const unsigned cg = cg0 + 32 * u;
             if (cg <= CGL) {
                 d[u] = __ldcg(reinterpret_cast<const float4*>(row + 4 * cg));
+                if (p < bp && (unsigned)bp >> 2 == cg) {  // column bp of this row: the stand-in row's element at column p (symmetry)
+                    const float sub = __ldcg(row_standin + p);
+                    const int e = bp & 3;
+                    if (e == 0) d[u].x = sub;
+                    if (e == 1) d[u].y = sub;
+                    if (e == 2) d[u].z = sub;
+                    if (e == 3) d[u].w = sub;
+                }
                 rj[u] = SMEM ? *reinterpret_cast<const float4*>(s_r2 + ((int)(4 * cg) - r2_org)) : __ldcg(reinterpret_cast<const float4*>(r2 + 4 * cg));
             } else {
                 d[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -551,6 +569,232 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
     }
 }
 
+// The last join's effect on four consecutive physical columns c0 .. c0+3 (k_nj_fused): the joined distance c and the new r2 of
+// each, from the rows a and b and the row sums of the state BEFORE the update.  x * 0.5f is the reference's (float)((double)x / 2.0)
+// bit for bit (halving is exact, or rounds once into the subnormals either way).
+__device__ __forceinline__ void nj_virtual4(const float* __restrict__ rowA, const float* __restrict__ rowB, const float* __restrict__ rin, int c0, float a2, float b2,
+                                            float denom, float (&c)[4], float (&r2n)[4]) {
+    const float4 da = __ldcg(reinterpret_cast<const float4*>(rowA + c0)), db = __ldcg(reinterpret_cast<const float4*>(rowB + c0));
+    const float4 r = __ldcg(reinterpret_cast<const float4*>(rin + c0));
+    const float vda[4] = {da.x, da.y, da.z, da.w}, vdb[4] = {db.x, db.y, db.z, db.w}, vr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+        c[e] = __fmul_rn(__fadd_rn(__fsub_rn(vda[e], a2), __fsub_rn(vdb[e], b2)), 0.5f);
+        r2n[e] = __fdiv_rn(__fadd_rn(__fsub_rn(__fsub_rn(vr[e], vda[e]), vdb[e]), c[e]), denom);
+    }
+}
+
+// ---- all joins in one launch, ONE grid barrier per join ------------------------------------------------------
+// k_nj_persistent spends about 9 us of every join in its update phase and the barrier behind it.  Here the update of join t-1 is
+// VIRTUAL while join t is scanned: once the winning pair (a, b) is known, every CTA derives what it needs from the state before
+// the update --
+//   * the scanning CTAs compute r2 of every index themselves (the same float operations on r, d(a, i), d(b, i)) while staging it
+//     in shared memory, skip the pairs of the joined node (CTA 0 scores them), and read the relabelled index ("index 0 takes over
+//     index b") from the dropped row, which nobody overwrites;
+//   * CTA 0 computes the joined row c_i into shared memory straight from the old rows a and b, adds the row sum in the
+//     reference's order, and scores the joined node's pairs from shared memory;
+//   * the threads that own an index i keep (c_i, r_i, d(0, i)) in registers through the scan and store them afterwards -- the
+//     in-place update -- once every CTA has announced (st->staged) that it no longer reads the old rows a and b; r is double
+//     buffered.  The barrier that ends the scan publishes the stores together with the minimum.
+// At every barrier the global state is exactly the reference's state after the join, so the last arriver snapshots the next pair.
+__global__ void __launch_bounds__(512, 2)
+k_nj_fused(float* __restrict__ m, int n0, int ld, float* __restrict__ rb, const float* __restrict__ r2_init, int* __restrict__ node,
+           int32_t* __restrict__ left, int32_t* __restrict__ right, lzg_nj_state* __restrict__ st, unsigned long long* __restrict__ dbg, int* __restrict__ smid) {
+    const int tid = threadIdx.x, n_ctas = gridDim.x;
+    const float ninf = __int_as_float(0xff800000);
+    int n_scan = n_ctas - 1, scan_rank = (int)blockIdx.x - 1;
+    unsigned phase = 0;  // barriers passed
+    bool scans = blockIdx.x != 0;
+    if (smid) {  // n_ctas <= 512: the CTA sharing CTA 0's SM does not scan (see k_nj_persistent)
+        if (tid == 0) {
+            unsigned id;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(id));
+            smid[blockIdx.x] = (int)id;
+        }
+        if (!nj_barrier(st, n_ctas, ++phase)) return;
+        const int sm0 = __ldcg(smid);
+        const bool other = tid > 0 && tid < n_ctas && __ldcg(smid + tid) != sm0;
+        n_scan = __syncthreads_count(other);
+        scan_rank = __syncthreads_count(other && tid < (int)blockIdx.x);
+        scans = blockIdx.x != 0 && __ldcg(smid + blockIdx.x) != sm0;
+        if (n_scan == 0) n_scan = n_ctas - 1, scan_rank = (int)blockIdx.x - 1, scans = blockIdx.x != 0;
+    }
+    __shared__ unsigned long long s_best[16];
+    __shared__ float s_r2p;
+    extern __shared__ __align__(16) float s_dyn[];
+    float* s_r2 = s_dyn;           // scanning CTAs: r2 by physical column; CTA 0: r2 by the index numbering of the last join
+    float* s_c = s_dyn + ld + 4;   // CTA 0: the joined row, same numbering
+    // the last join (none before the first scan): the pair in the numbering it was found in, and its operands
+    int a = -1, b = -1;
+    float dab = 0.0f, r2a = 0.0f, r2b = 0.0f;
+    int base = 0, joined = n0;
+    for (int size = n0; size > 2; size--, base++, joined++) {
+        const int parity = joined & 1, t = n0 - size;
+        const bool prev = t > 0;
+        const float* rin = rb + (size_t)((t + 1) & 1) * ld;  // r before the last join's update
+        float* rout = rb + (size_t)(t & 1) * ld;             // r after it (t = 0: the initial sums)
+        const int Bp = base - 1;                             // the base the last join ran at
+        const int pend = prev ? (a == 0 ? b : a) - 1 : -1;   // the joined node and
+        const int bq = prev && a != 0 ? b - 1 : -1;          // the index that takes over the dropped one, in THIS join's numbering
+        const float a2 = (float)((double)__fadd_rn(dab, __fsub_rn(r2a, r2b)) / 2.0);
+        const float b2 = (float)((double)__fadd_rn(dab, __fsub_rn(r2b, r2a)) / 2.0);
+        const float denom = (float)(size - 2);  // (size + 1) - 3: the last join ran at size + 1
+        const float* rowA = prev ? m + (size_t)(a + Bp) * ld : m;  // rows a, b and 0 of the last join's numbering, by physical column
+        const float* rowB = prev ? m + (size_t)(b + Bp) * ld : m;
+        const float* row0 = prev ? m + (size_t)Bp * ld : m;
+        unsigned long long ts0 = 0;
+        if (dbg && tid == 0) ts0 = nj_now();
+        unsigned long long best = ~0ull;
+        // ---- this thread's share of the in-place update: index i of the last join's numbering, held in registers until the scan is over
+        const int ui = blockIdx.x * 512 + tid;
+        const bool upd = prev && ui <= size && ui != a;
+        float u_da = 0.0f, u_db = 0.0f, u_r = 0.0f, u_v = 0.0f;
+        if (upd) {
+            u_da = __ldcg(rowA + ui + Bp);  // at ui == b: d(a, b) and the zero diagonal d(b, b), as the reference reads them
+            u_db = __ldcg(rowB + ui + Bp);
+            u_r = __ldcg(rin + ui + Bp);
+            u_v = a == 0 ? 0.0f : __ldcg(row0 + ui + Bp);
+        }
+        if (blockIdx.x == 0) {
+            if (prev) {
+                // the joined row and r2 of every index, in the last join's numbering (i = c - Bp = 0 .. size), four columns a thread
+                for (int g0 = (Bp >> 2) + tid; 4 * g0 < n0; g0 += 2 * 512) {
+                    float c[2][4], r2n[2][4];
+#pragma unroll
+                    for (int u = 0; u < 2; u++)
+                        if (4 * (g0 + 512 * u) < n0) nj_virtual4(rowA, rowB, rin, 4 * (g0 + 512 * u), a2, b2, denom, c[u], r2n[u]);
+#pragma unroll
+                    for (int u = 0; u < 2; u++)
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const int i = 4 * (g0 + 512 * u) + e - Bp;
+                            if (i >= 0 && i <= size) s_c[i] = i == a ? 0.0f : c[u][e], s_r2[i] = r2n[u][e];
+                        }
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&st->staged) : "memory");
+                    // the reference's order: i = a+1 .. size, then 0 .. a-1 (the term at i = b included)
+                    float sum = nj_sum_in_order(s_c + a + 1, size - a, 0.0f);
+                    sum = nj_sum_in_order(s_c, a, sum);
+                    rout[pend + base] = sum;
+                    s_r2p = __fdiv_rn(sum, denom);
+                    if (dbg) dbg[n_ctas] += nj_now() - ts0;
+                }
+                if (tid == 32) {  // the tree: children of the new node, then the relabelling
+                    left[joined - 1] = node[a + Bp];
+                    right[joined - 1] = node[b + Bp];
+                    if (a != 0) node[b + Bp] = node[Bp];
+                    node[(a == 0 ? b : a) + Bp] = joined - 1;
+                }
+                __syncthreads();
+                const float r2p = s_r2p;
+                for (int q = tid; q < size; q += 512) {  // the pairs of the joined node, from shared memory
+                    if (q == pend) continue;
+                    const int src = q == bq ? 0 : q + 1;
+                    const unsigned long long k = nj_key(s_c[src], s_r2[src], r2p, min(q, pend), max(q, pend), n0);
+                    best = k < best ? k : best;
+                }
+            }
+        } else {
+            const int r2_org = base & ~3;  // s_r2[c - r2_org] = r2 of physical column c
+            if (prev) {
+                const int cb = bq >= 0 ? bq + base : -1;  // this column takes the values of the dropped index (physical column Bp)
+                for (int g0 = (r2_org >> 2) + tid; 4 * g0 < ld; g0 += 2 * 512) {
+                    float c[2][4], r2n[2][4];
+                    float sub = 0.0f;
+#pragma unroll
+                    for (int u = 0; u < 2; u++) {
+                        const int c0 = 4 * (g0 + 512 * u);
+                        if (c0 < ld) nj_virtual4(rowA, rowB, rin, c0, a2, b2, denom, c[u], r2n[u]);
+                        if (cb >= c0 && cb < c0 + 4) {
+                            const float da = __ldcg(rowA + Bp), db = __ldcg(rowB + Bp);
+                            const float cc = __fmul_rn(__fadd_rn(__fsub_rn(da, a2), __fsub_rn(db, b2)), 0.5f);
+                            sub = __fdiv_rn(__fadd_rn(__fsub_rn(__fsub_rn(__ldcg(rin + Bp), da), db), cc), denom);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 2; u++)
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const int col = 4 * (g0 + 512 * u) + e;
+                            if (col < ld) s_r2[col - r2_org] = col < base || col >= n0 || col - base == pend ? ninf : col == cb ? sub : r2n[u][e];
+                        }
+                }
+            } else {
+                for (int c = r2_org + tid; c < ld; c += 512) s_r2[c - r2_org] = c >= base && c < n0 ? __ldcg(r2_init + c) : ninf;
+            }
+            __syncthreads();
+            if (prev && tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&st->staged) : "memory");
+            if (dbg && tid == 0) dbg[n_ctas + 1 + blockIdx.x] += nj_now() - ts0;
+            if (scans) best = nj_scan<true>(m, n0, ld, base, size, pend >= 0 ? pend + base : -1, nullptr, s_r2, r2_org, n_scan, scan_rank, bq >= 0 ? bq + base : -1, prev ? m + (size_t)Bp * ld : m);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other < best ? other : best;
+        }
+        if ((tid & 31) == 0) s_best[tid >> 5] = best;
+        __syncthreads();
+        if (tid == 0) {
+            for (int w = 1; w < 16; w++) best = s_best[w] < best ? s_best[w] : best;
+            if (best != ~0ull) atomicMin(&st->key[parity], best);
+            if (dbg) dbg[blockIdx.x] += nj_now() - ts0;
+        }
+        // ---- the deferred stores of the last join: NJ_compute_r + NJ_collapse + the relabelling (k_nj_persistent's update phase)
+        if (prev && blockIdx.x * 512 <= size) {
+            if (tid == 0) {  // every CTA has staged what it needs of the old rows a and b
+                const unsigned want = (unsigned)t * (unsigned)n_ctas;
+                long long spins = 0;
+                while ((int)((unsigned)ld_acquire_i(reinterpret_cast<const int*>(&st->staged)) - want) < 0)
+                    if (++spins > (1ll << 27)) {
+                        st->err = 1;
+                        break;
+                    }
+            }
+            __syncthreads();
+            if (upd) {
+                const int i = ui;
+                const float c = __fmul_rn(__fadd_rn(__fsub_rn(u_da, a2), __fsub_rn(u_db, b2)), 0.5f);
+                if (i != b) {  // index b is overwritten by the relabelling
+                    float* row_a = m + (size_t)(a + Bp) * ld + Bp;
+                    float* row_b = m + (size_t)(b + Bp) * ld + Bp;
+                    row_a[i] = c;
+                    m[(size_t)(i + Bp) * ld + a + Bp] = c;
+                    const float ri = __fadd_rn(__fsub_rn(__fsub_rn(u_r, u_da), u_db), c);
+                    rout[i + Bp] = ri;
+                    // index 0 (after the update) takes over index b; index 0 itself is dropped
+                    const float v = a == 0 ? c : u_v;
+                    row_b[i] = v;
+                    m[(size_t)(i + Bp) * ld + b + Bp] = v;
+                    if (i == 0) {  // a != 0 here: the updated row 0 also holds c_0 at column a
+                        row_b[a] = c;
+                        row_a[b] = c;
+                        rout[b + Bp] = ri;
+                    }
+                }
+            }
+        }
+        if (blockIdx.x == 0 && tid == 0) st->key[parity ^ 1] = ~0ull;  // the next join's minimum
+        // the initial r2 leaves its last index at zero (NJ_init_r), so the first join snapshots r2 itself
+        if (!nj_barrier(st, n_ctas, ++phase, m, prev ? nullptr : r2_init, n0, ld, base, parity, rout, (float)(size - 2))) return;
+        a = __ldcg(&st->a), b = __ldcg(&st->b);
+        dab = __ldcg(&st->dab), r2a = __ldcg(&st->r2a), r2b = __ldcg(&st->r2b);
+    }
+    // the last join's bookkeeping and the final edge between the two nodes left
+    if (blockIdx.x == 0 && tid == 0) {
+        const int Bp = base - 1;
+        if (n0 > 2) {
+            left[joined - 1] = node[a + Bp];
+            right[joined - 1] = node[b + Bp];
+            if (a != 0) node[b + Bp] = node[Bp];
+            node[(a == 0 ? b : a) + Bp] = joined - 1;
+        }
+        left[joined] = node[base];
+        right[joined] = node[base + 1];
+    }
+}
+
 __global__ void k_nj_finish(const int* __restrict__ node, int base, int32_t* __restrict__ left, int32_t* __restrict__ right, int joined) {
     left[joined] = node[base];
     right[joined] = node[base + 1];
@@ -606,7 +850,7 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_left, sizeof(int32_t) * total);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_right, sizeof(int32_t) * total);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_node, sizeof(int) * n);
-    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r, sizeof(float) * ld);
+    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r, sizeof(float) * 2 * ld);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r2, sizeof(float) * ld);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_key, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_D, D_host, sizeof(int32_t) * nn, cudaMemcpyHostToDevice, ctx->stream);
@@ -625,22 +869,33 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
         fprintf(stderr, "[lzg nj] upload + gather + row sums: %.1f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
     }
     // one persistent cooperative launch for all joins; LZG_NJ_PERSISTENT=0 keeps the two-launches-per-join form (the cross-check)
-    const bool persistent = !(getenv("LZG_NJ_PERSISTENT") && atoi(getenv("LZG_NJ_PERSISTENT")) == 0);
+    // LZG_NJ_PERSISTENT: 0 = two launches per join, 1 = k_nj_persistent (two grid barriers per join), otherwise k_nj_fused (one)
+    // where its shared memory fits -- the older forms stay as cross-checks and for very large n
+    // (2 forces it).  Measured on B200: fused 0.031 / 0.116 / 0.209 s at n = 2,000 / 5,000 / 7,000 against 0.036 / 0.123 / 0.213 s,
+    // but 0.455 s against 0.385 s at n = 10,000, where every CTA recomputing r2 costs more than the barrier it saves.
+    const int mode = getenv("LZG_NJ_PERSISTENT") ? atoi(getenv("LZG_NJ_PERSISTENT")) : 3;
+    const bool persistent = mode != 0;
+    bool fused = mode != 1 && (mode == 2 || n <= 8000) && sizeof(float) * 2 * (size_t)(ld + 4) <= 110 * 1024;  // two CTAs per SM: n <= 14,000
     bool done = false;
     if (persistent && n >= 4) {
         int per_sm = 0;
         size_t smem_r2 = sizeof(float) * (size_t)(ld + 4);  // r2 (scanning CTAs) / the joined row's terms (CTA 0) in shared memory
+        if (fused) {
+            const size_t smem_fused = 2 * smem_r2;
+            if (smem_fused > 48 * 1024) cudaFuncSetAttribute(k_nj_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fused);
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nj_fused, 512, smem_fused) != cudaSuccess || per_sm < 1) fused = false, cudaGetLastError();
+        }
         if (smem_r2 > 110 * 1024) smem_r2 = 0;               // two CTAs per SM must fit; beyond n = 28,000 both come from L2
         if (getenv("LZG_NJ_SMEM") && atoi(getenv("LZG_NJ_SMEM")) == 0) smem_r2 = 0;  // tests: the path of very large n
         if (smem_r2 > 48 * 1024) cudaFuncSetAttribute(k_nj_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r2);
-        cudaError_t ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nj_persistent, 512, smem_r2);
+        cudaError_t ce = fused ? cudaSuccess : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nj_persistent, 512, smem_r2);
         if (ce == cudaSuccess && per_sm >= 1) ce = lzg_dev_alloc(ctx, (void**)&d_cvec, sizeof(float) * (size_t)n);
         if (ce == cudaSuccess && per_sm >= 1) ce = lzg_dev_alloc(ctx, (void**)&d_state, sizeof(lzg_nj_state));
         const int max_grid = ctx->sm_count * 2 + 1;
         if (ce == cudaSuccess && per_sm >= 1 && max_grid <= 512) ce = lzg_dev_alloc(ctx, (void**)&d_smid, sizeof(int) * max_grid);
         if (ce == cudaSuccess && per_sm >= 1 && getenv("LZG_NJ_DEBUG")) {
-            ce = lzg_dev_alloc(ctx, (void**)&d_dbg, sizeof(unsigned long long) * (max_grid + 1));
-            if (ce == cudaSuccess) ce = cudaMemsetAsync(d_dbg, 0, sizeof(unsigned long long) * (max_grid + 1), ctx->stream);
+            ce = lzg_dev_alloc(ctx, (void**)&d_dbg, sizeof(unsigned long long) * (2 * max_grid + 2));
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(d_dbg, 0, sizeof(unsigned long long) * (2 * max_grid + 2), ctx->stream);
         }
         if (ce == cudaSuccess && per_sm >= 1) {
             lzg_nj_state init;
@@ -651,18 +906,23 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
             grid = std::max(grid, 2);  // CTA 0 owns the joined node, the others scan
             int n_arg = n, ld_arg = ld, in_smem = smem_r2 > 0;
             void* args[] = {(void*)&d_m, (void*)&n_arg, (void*)&ld_arg, (void*)&d_r, (void*)&d_r2, (void*)&d_node, (void*)&d_cvec, (void*)&d_left, (void*)&d_right, (void*)&d_state, (void*)&in_smem, (void*)&d_dbg, (void*)&d_smid};
-            if (ce == cudaSuccess) ce = cudaLaunchCooperativeKernel((void*)k_nj_persistent, dim3(grid), dim3(512), args, smem_r2, ctx->stream);
+            void* fargs[] = {(void*)&d_m, (void*)&n_arg, (void*)&ld_arg, (void*)&d_r, (void*)&d_r2, (void*)&d_node, (void*)&d_left, (void*)&d_right, (void*)&d_state, (void*)&d_dbg, (void*)&d_smid};
+            if (ce == cudaSuccess)
+                ce = fused ? cudaLaunchCooperativeKernel((void*)k_nj_fused, dim3(grid), dim3(512), fargs, 2 * smem_r2, ctx->stream)
+                           : cudaLaunchCooperativeKernel((void*)k_nj_persistent, dim3(grid), dim3(512), args, smem_r2, ctx->stream);
             if (ce == cudaSuccess) {
                 ctx->launches++;
                 lzg_nj_state back;
                 ce = cudaMemcpyAsync(&back, d_state, sizeof(back), cudaMemcpyDeviceToHost, ctx->stream);
                 if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
-                if (ce == cudaSuccess && getenv("LZG_NJ_DEBUG"))
+                if (ce == cudaSuccess && getenv("LZG_NJ_DEBUG") && !fused)
                     fprintf(stderr, "[lzg nj] n %d, %d CTAs: scan %.1f ms, wait behind the scan %.1f ms, update %.1f ms, wait behind the update %.1f ms\n", n, grid,
                             back.t_scan * 1e-6, back.t_wait1 * 1e-6, back.t_update * 1e-6, back.t_wait2 * 1e-6);
                 if (ce == cudaSuccess && d_dbg) {
-                    std::vector<unsigned long long> h(grid + 1);
-                    cudaMemcpy(h.data(), d_dbg, sizeof(unsigned long long) * (grid + 1), cudaMemcpyDeviceToHost);
+                    fprintf(stderr, "[lzg nj] n %d: %s, %d CTAs of 512 threads (%d per SM)\n", n, fused ? "k_nj_fused" : "k_nj_persistent", grid, per_sm);
+                    std::vector<unsigned long long> h(2 * grid + 2);
+                    cudaMemcpy(h.data(), d_dbg, sizeof(unsigned long long) * (2 * grid + 2), cudaMemcpyDeviceToHost);
+                    if (fused) fprintf(stderr, "[lzg nj] of the scan phase, staging r2: %.1f ms (CTA 1), %.1f ms (CTA %d)\n", h[grid + 2] * 1e-6, h[2 * grid] * 1e-6, grid - 1);
                     unsigned long long lo = ~0ull, hi = 0, sum = 0;
                     int arg = 1;
                     for (int c = 1; c < grid; c++) {

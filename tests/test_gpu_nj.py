@@ -104,14 +104,16 @@ def test_nj_gpu_equals_host_library(ctx):
 
 @pytest.mark.parametrize("n,seed,hi", [(1500, 21, 400), (2500, 22, 3), (1026, 23, 50), (13001, 24, 9)])
 def test_nj_persistent_kernel_on_larger_matrices(ctx, monkeypatch, n, seed, hi):
-    """All joins in one cooperative launch (k_nj_persistent: grid barriers, the sequential row sum overlapped with the next
-    scan) against the CPU restatement and against the two-launches-per-join form; hi = 3 makes almost every scan a tie."""
+    """All joins in one cooperative launch (k_nj_fused: one grid barrier per join, the update of the last join virtual
+    during the scan; k_nj_persistent: two barriers; the sequential row sum overlapped with the next scan) against the CPU restatement and against the two-launches-per-join form; hi = 3 makes almost every scan a tie."""
     from lazac_copy_number_b200 import search
     rng = np.random.default_rng(seed)
     D = rng.integers(1, hi + 1, (n, n)).astype(np.int32)
     D = np.triu(D, 1) + np.triu(D, 1).T
     perm = search.clearcut_shuffle(n, seed)
+    monkeypatch.setenv("LZG_NJ_PERSISTENT", "2")  # k_nj_fused at every size it has shared memory for
     left, right = ctx.nj_seed_tree(D, perm)
+    monkeypatch.delenv("LZG_NJ_PERSISTENT")
     if n <= 3000:
         cl, cr = search.nj_seed_tree_cpu(D, perm)
     else:  # minutes on one core: the per-join kernels (pinned to the CPU restatement above) stand in
@@ -119,7 +121,10 @@ def test_nj_persistent_kernel_on_larger_matrices(ctx, monkeypatch, n, seed, hi):
         cl, cr = ctx.nj_seed_tree(D, perm)
         monkeypatch.delenv("LZG_NJ_PERSISTENT")
     assert np.array_equal(left, cl) and np.array_equal(right, cr)
-    monkeypatch.setenv("LZG_NJ_SMEM", "0")  # the form for n > 28,000: r2 and the joined row's terms straight from L2
+    monkeypatch.setenv("LZG_NJ_PERSISTENT", "1")  # two grid barriers per join (k_nj_persistent): the form for n > 14,000
+    l4, r4 = ctx.nj_seed_tree(D, perm)
+    assert np.array_equal(l4, cl) and np.array_equal(r4, cr)
+    monkeypatch.setenv("LZG_NJ_SMEM", "0")  # ... and for n > 28,000: r2 and the joined row's terms straight from L2
     l3, r3 = ctx.nj_seed_tree(D, perm)
     assert np.array_equal(l3, cl) and np.array_equal(r3, cr)
     monkeypatch.delenv("LZG_NJ_SMEM")
