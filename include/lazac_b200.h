@@ -87,6 +87,16 @@ int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard, int32
                        int32_t* D_host, int64_t* pairs_done);
 int lzg_distance_shard_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t shard,
                                     int32_t n_shards, int32_t* d_D, int64_t* pairs_done);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * lzg_distance_matrix_device_async -- the whole matrix into the caller's d_D (device, N*N int32), asynchronous
+ * on the context stream -- but the call allocates nothing: the kernel's scratch (its work plan: segments,
+ * per-CTA offsets, split tiles) goes into a file-scope static device array of
+ * lzg_distance_matrix_noalloc_max_bytes() = 1 MiB, which every GPU that loads the library holds until exit.
+ * A shape whose plan is larger (beyond roughly N = 40,000 cells) is rejected with LZG_ERR_ARG and a message
+ * naming both sizes.  All calls share the array: calls that overlap on the GPU race; serialise them. */
+int lzg_distance_matrix_noalloc(lzg_ctx* ctx, const lzg_profiles* p, int32_t* d_D);
+int lzg_distance_matrix_noalloc_max_bytes(void);
 
 /* ---- several GPUs of one box, one process: build_distance_matrix ends with the WHOLE matrix in the
  *      caller's buffer (src/lazac.cxx:63-95 returns one matrix; do_nni feeds it to NJ, :153-200).

@@ -39,6 +39,8 @@ SYMBOLS = [
     ("lzg_profiles_shape", _i, [_vp, _i32p, _i32p]),
     ("lzg_distance_matrix", _i, [_vp, _vp, _vp]),
     ("lzg_distance_matrix_device_async", _i, [_vp, _vp, _vp]),
+    ("lzg_distance_matrix_noalloc", _i, [_vp, _vp, _vp]),
+    ("lzg_distance_matrix_noalloc_max_bytes", _i, []),
     ("lzg_distance_shard", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
     ("lzg_distance_shard_device_async", _i, [_vp, _vp, _i32, _i32, _vp, _i64p]),
     ("lzg_multi_init", _i, [_vp, _i32, _vpp]),

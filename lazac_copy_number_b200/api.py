@@ -188,6 +188,11 @@ class Profiles:
             self.ctx.h, self.h, shard, n_shards, C.c_void_p(d_ptr), C.byref(pairs)))
         return pairs.value
 
+    def distance_noalloc(self, d_ptr):
+        """lzg_distance_matrix_noalloc: the whole matrix to raw device pointer d_ptr (N*N int32) without any allocation --
+        the kernel's work plan goes into the library's static device array (1 MiB; larger plans raise LazacGpuError)."""
+        self.ctx.check(self.ctx.lib.lzg_distance_matrix_noalloc(self.ctx.h, self.h, C.c_void_p(d_ptr)))
+
 
 class Tree:
     """digraph<rectilinear_vertex_data> resident on the GPU (include/copy_number.hpp:98-105)."""

@@ -740,3 +740,71 @@ int lzg_distance_plan(int32_t n, int32_t L, int32_t sm_count, int32_t shard, int
     for (int b = 0; b <= plan.n_ctas; b++) seg_off[b] = plan.seg_off[b];
     return LZG_OK;
 }
+
+// ---- lzg_distance_matrix_noalloc: the distance kernel with its work plan in a file-scope device array -------
+// For callers that cannot call cudaMalloc (CUDA graph capture around them, tight serving loops, harnesses that
+// forbid it).  The kernel's scratch -- the plan [segments | per-CTA offsets | split tiles] that lzg_distance_run
+// keeps in a pooled device block per shape -- lives here in LZG_NOALLOC_SCRATCH_BYTES of static device memory
+// (held by every GPU that loads the library until the process exits).  Every call rewrites the part of the array
+// it uses and shares it with every other call: calls that overlap on the GPU (two streams, two contexts on one
+// device) race.  Nothing in it has to start at zero; the split tiles of D are zeroed by k_zero_tiles as usual.
+#define LZG_NOALLOC_SCRATCH_BYTES (1 << 20)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[LZG_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+// In host code g_noalloc_scratch is a host-side stand-in, not a device address: the address the kernels get comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kMaxDevices = 64;
+unsigned char* g_noalloc_ptr[kMaxDevices] = {};
+
+int noalloc_scratch(lzg_ctx* ctx, unsigned char** out) {
+    if (ctx->device < 0 || ctx->device >= kMaxDevices) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance_matrix_noalloc: device ordinal beyond 63");
+    if (!g_noalloc_ptr[ctx->device]) {
+        unsigned char* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) return lzg_fail(ctx, LZG_ERR_CUDA, "lzg_distance_matrix_noalloc: cudaGetSymbolAddress", e);
+        g_noalloc_ptr[ctx->device] = ptr;
+    }
+    *out = g_noalloc_ptr[ctx->device];
+    return LZG_OK;
+}
+}  // namespace
+
+extern "C" int lzg_distance_matrix_noalloc_max_bytes(void) { return LZG_NOALLOC_SCRATCH_BYTES; }
+
+extern "C" int lzg_distance_matrix_noalloc(lzg_ctx* ctx, const lzg_profiles* cp, int32_t* d_D) {
+    if (!ctx || !cp || cp->ctx != ctx || (cp->n > 0 && !d_D)) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance_matrix_noalloc: bad argument");
+    lzg_profiles* p = const_cast<lzg_profiles*>(cp);
+    if (p->n == 0) return LZG_OK;
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned char* scratch = nullptr;
+    int rc = noalloc_scratch(ctx, &scratch);
+    if (rc != LZG_OK) return rc;
+    const int bm = lzg_distance_tile(p);
+    lzg_plan plan;  // host vectors only
+    plan_schedule(p->n, p->pitch, bm, ctx->sm_count, bm == 64 ? 3 : 1, 0, 1, 0, INT32_MAX, plan, 0);
+    if (plan.segs.empty()) return LZG_OK;
+    const size_t b_segs = sizeof(lzg_seg) * plan.segs.size(), b_off = sizeof(int32_t) * plan.seg_off.size();
+    const size_t o_off = b_segs, o_split = (o_off + b_off + 15) / 16 * 16;
+    const size_t bytes = o_split + sizeof(int2) * plan.split.size();
+    if (bytes > LZG_NOALLOC_SCRATCH_BYTES) {
+        char msg[224];
+        snprintf(msg, sizeof(msg), "lzg_distance_matrix_noalloc: the work plan of %d x %d profiles needs %zu bytes of scratch, the static array holds %d -- use lzg_distance_matrix_device_async",
+                 p->n, p->L, bytes, LZG_NOALLOC_SCRATCH_BYTES);
+        return lzg_fail(ctx, LZG_ERR_ARG, msg);
+    }
+    // three copies from the plan's own (pageable) vectors: the runtime stages them itself, nothing is allocated here
+    LZG_CUDA(ctx, cudaMemcpyAsync(scratch, plan.segs.data(), b_segs, cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaMemcpyAsync(scratch + o_off, plan.seg_off.data(), b_off, cudaMemcpyHostToDevice, ctx->stream));
+    if (!plan.split.empty()) LZG_CUDA(ctx, cudaMemcpyAsync(scratch + o_split, plan.split.data(), sizeof(int2) * plan.split.size(), cudaMemcpyHostToDevice, ctx->stream));
+    LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the sources are pageable and go out of scope
+    lzg_schedule sc;
+    sc.n = p->n, sc.l_pad = p->pitch, sc.bm = bm, sc.n_shards = 1, sc.row_hi = INT32_MAX;
+    sc.pairs = plan.pairs, sc.n_ctas = plan.n_ctas, sc.n_segs = (int)plan.segs.size(), sc.n_split = (int)plan.split.size();
+    sc.bytes = bytes;
+    sc.d_segs = scratch;
+    sc.d_seg_off = reinterpret_cast<int32_t*>(scratch + o_off);
+    sc.d_split = reinterpret_cast<int2*>(scratch + o_split);
+    if (p->width == 2) return bm == 64 ? launch_distance<64, 64, 4, 2>(ctx, p, &sc, d_D, nullptr) : launch_distance<128, 128, 3, 2>(ctx, p, &sc, d_D, nullptr);
+    return bm == 64 ? launch_distance<64, 64, 4, 1>(ctx, p, &sc, d_D, nullptr) : launch_distance<128, 128, 3, 1>(ctx, p, &sc, d_D, nullptr);
+}
