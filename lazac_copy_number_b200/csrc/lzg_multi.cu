@@ -243,7 +243,7 @@ static int distance_multi_width(lzg_multi* m, const void* host, bool is_i8, int3
     const int blocks2g = (R + 2 * G - 1) / (2 * G);
     const long long tiles_per_gpu = (long long)R * (R + 1) / 2 / G;
     const int sm = m->ctx[0]->sm_count;
-    int phases = (int)std::max<long long>(1, std::min<long long>(8, tiles_per_gpu / std::max(1, 4 * sm)));
+    int phases = (int)std::max<long long>(1, std::min<long long>(G >= 4 ? 16 : 8, tiles_per_gpu / std::max(1, sm)));  // at least a tile per CTA and phase: the copies, not the kernels, set the pace (profiles/r02_multi_phases_n8.txt)
     if (getenv("LZG_MULTI_PHASES")) phases = std::max(1, atoi(getenv("LZG_MULTI_PHASES")));
     phases = std::min(phases, blocks2g);
     for (int g = 0; g < G && rc == LZG_OK; g++) {

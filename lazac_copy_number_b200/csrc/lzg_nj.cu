@@ -282,7 +282,7 @@ __device__ __forceinline__ float nj_sum_in_order(const float* v_smem, int cnt, f
 // chunk of 128 groups (2 KB) of one row: 32 lanes x 4 independent 16-byte loads.  Rows are paired -- p1 = base + v with
 // p2 = n0 - 2 - v -- so that every virtual row has (at most) C chunks and task t -> v = t / C, chunk t % C; warps take tasks round
 // robin.  SMEM: r2 comes from shared memory where the pending node and the pad columns hold -inf (their pairs evaluate to +inf).
-template <bool SMEM>
+template <bool SMEM, bool STANDIN = false>
 __device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ m, int n0, int ld, int base, int size, int pendp, const float* __restrict__ r2,
                                                       const float* s_r2, int r2_org, int n_scan, int scan_rank, int bp = -1,
                                                       const float* __restrict__ row_standin = nullptr) {
@@ -312,7 +312,7 @@ __device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ 
         const unsigned cg0 = f + ch * 128 + lane;
         // bp >= 0 (the fused kernel): physical index bp is taking over the data of the index dropped by the last join, whose row
         // (row_standin) is still in place while the copy into row / column bp is under way -- read it from there
-        const float* row = p == bp ? row_standin : m + (size_t)p * ld;
+        const float* row = STANDIN && p == bp ? row_standin : m + (size_t)p * ld;
         const float ri = SMEM ? s_r2[p - r2_org] : __ldcg(r2 + p);
         float4 d[4], rj[4];
 #pragma unroll
@@ -320,7 +320,7 @@ __device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ 
             const unsigned cg = cg0 + 32 * u;
             if (cg <= CGL) {
                 d[u] = __ldcg(reinterpret_cast<const float4*>(row + 4 * cg));
-                if (p < bp && (unsigned)bp >> 2 == cg) {  // column bp of this row: the stand-in row's element at column p (symmetry)
+                if (STANDIN && p < bp && (unsigned)bp >> 2 == cg) {  // column bp of this row: the stand-in row's element at column p (symmetry)
                     const float sub = __ldcg(row_standin + p);
                     const int e = bp & 3;
                     if (e == 0) d[u].x = sub;
@@ -727,7 +727,7 @@ k_nj_fused(float* __restrict__ m, int n0, int ld, float* __restrict__ rb, const 
             __syncthreads();
             if (prev && tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&st->staged) : "memory");
             if (dbg && tid == 0) dbg[n_ctas + 1 + blockIdx.x] += nj_now() - ts0;
-            if (scans) best = nj_scan<true>(m, n0, ld, base, size, pend >= 0 ? pend + base : -1, nullptr, s_r2, r2_org, n_scan, scan_rank, bq >= 0 ? bq + base : -1, prev ? m + (size_t)Bp * ld : m);
+            if (scans) best = nj_scan<true, true>(m, n0, ld, base, size, pend >= 0 ? pend + base : -1, nullptr, s_r2, r2_org, n_scan, scan_rank, bq >= 0 ? bq + base : -1, prev ? m + (size_t)Bp * ld : m);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
