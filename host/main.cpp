@@ -367,7 +367,7 @@ void do_nni(const Args& a) {
         // LAZAC_NJ=host: the Clearcut restatement on the CPU (what the parity tests compare the GPU with)
         const char* nj_env = getenv("LAZAC_NJ");
         const SeedTree nj = nj_env && std::string(nj_env) == "host" ? neighbor_joining_clearcut(D, set.names, (uint32_t)a.seed)
-                                                                   : neighbor_joining_gpu(gpu.ctx, D, set.names, (uint32_t)a.seed);
+                                                                   : neighbor_joining_gpu(gpu.ctx, D, set.names, (uint32_t)a.seed, prof);
         log_info("Outputting NJ tree to file: " + output_tree);
         {
             std::ofstream out(output_tree, std::ios::out);

@@ -68,13 +68,15 @@ static std::vector<long> clearcut_shuffle(long n, uint32_t seed) {
     return perm;
 }
 
-SeedTree neighbor_joining_gpu(lzg_ctx* ctx, const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed) {
+SeedTree neighbor_joining_gpu(lzg_ctx* ctx, const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed, const lzg_profiles* prof) {
     const long n = (long)names.size();
     if ((size_t)n * n != D.size()) throw std::runtime_error("distance matrix size mismatch");
     if (n == 0) throw std::runtime_error("Failed to parse distance matrix.");
     const std::vector<long> perm = clearcut_shuffle(n, seed);
     std::vector<int32_t> p32(perm.begin(), perm.end()), left(2 * n - 1), right(2 * n - 1);
-    const int rc = lzg_nj_seed_tree(ctx, D.data(), (int32_t)n, p32.data(), left.data(), right.data());
+    // prof: the uploaded profiles D was computed from -- its device copy of the matrix is used, no second trip over PCIe
+    const int rc = prof ? lzg_nj_seed_tree_profiles(ctx, prof, p32.data(), left.data(), right.data())
+                        : lzg_nj_seed_tree(ctx, D.data(), (int32_t)n, p32.data(), left.data(), right.data());
     if (rc != LZG_OK) throw std::runtime_error(std::string("lzg_nj_seed_tree: ") + lzg_last_error(ctx));
     SeedTree out;
     out.left.assign(left.begin(), left.end());

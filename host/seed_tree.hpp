@@ -24,6 +24,7 @@ SeedTree neighbor_joining_perm(const std::vector<int32_t>& D, const std::vector<
 std::vector<long> clearcut_taxon_shuffle(long n, uint32_t seed);
 
 // The same tree from the GPU (lzg_nj_seed_tree): the O(n^3) minimum scans run as device reductions.
-SeedTree neighbor_joining_gpu(lzg_ctx* ctx, const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed);
+SeedTree neighbor_joining_gpu(lzg_ctx* ctx, const std::vector<int32_t>& D, const std::vector<std::string>& names, uint32_t seed,
+                              const lzg_profiles* prof = nullptr);
 
 }  // namespace lazac_host

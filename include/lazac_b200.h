@@ -252,6 +252,15 @@ int lzg_tree_last_nni_traffic(const lzg_tree* t, int64_t* cand_bytes, int64_t* u
  * nodes N .. 2N-2 in creation order, the root is node 2N-2. */
 int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, const int32_t* perm, int32_t* left,
                      int32_t* right);
+/* The same with the matrix already in HBM (d_D: device pointer to N*N int32, e.g. what
+ * lzg_distance_matrix_device_async left there; not modified): the matrix do_nni hands from
+ * build_distance_matrix to NJ (src/lazac.cxx:153-200) never crosses PCIe. */
+int lzg_nj_seed_tree_device(lzg_ctx* ctx, const int32_t* d_D, int32_t n, const int32_t* perm, int32_t* left,
+                            int32_t* right);
+/* ... and of the uploaded profiles' own matrix: the device copy lzg_distance_matrix left behind if there is
+ * one, else computed now (do_nni: build_distance_matrix -> NJ, src/lazac.cxx:153-200, in one call). */
+int lzg_nj_seed_tree_profiles(lzg_ctx* ctx, const lzg_profiles* p, const int32_t* perm, int32_t* left,
+                              int32_t* right);
 
 #ifdef __cplusplus
 }

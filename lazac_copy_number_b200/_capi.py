@@ -75,6 +75,8 @@ SYMBOLS = [
     ("lzg_tree_last_nni_work", _i, [_vp, _i64p, _i64p]),
     ("lzg_tree_last_nni_traffic", _i, [_vp, _i64p, _i64p]),
     ("lzg_nj_seed_tree", _i, [_vp, _vp, _i32, _vp, _vp, _vp]),
+    ("lzg_nj_seed_tree_device", _i, [_vp, _vp, _i32, _vp, _vp, _vp]),
+    ("lzg_nj_seed_tree_profiles", _i, [_vp, _vp, _vp, _vp, _vp]),
 ]
 
 

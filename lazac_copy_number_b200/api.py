@@ -86,6 +86,13 @@ class Context:
         self.check(self.lib.lzg_nj_seed_tree(self.h, ptr(D), n, ptr(perm), ptr(left), ptr(right)))
         return left, right
 
+    def nj_seed_tree_device(self, d_ptr, n, perm):
+        """nj_seed_tree on a matrix already in HBM (raw device pointer to n*n int32, not modified)."""
+        perm = i32(perm)
+        left, right = np.zeros(2 * n - 1, np.int32), np.zeros(2 * n - 1, np.int32)
+        self.check(self.lib.lzg_nj_seed_tree_device(self.h, C.c_void_p(d_ptr), n, ptr(perm), ptr(left), ptr(right)))
+        return left, right
+
     # -- reference-named entry points -------------------------------------------------------------
     def upload_profiles(self, bp):
         return Profiles(self, bp)
@@ -187,6 +194,13 @@ class Profiles:
         self.ctx.check(self.ctx.lib.lzg_distance_shard_device_async(
             self.ctx.h, self.h, shard, n_shards, C.c_void_p(d_ptr), C.byref(pairs)))
         return pairs.value
+
+    def nj_seed_tree(self, perm):
+        """lzg_nj_seed_tree_profiles: NJ on these profiles' distance matrix, which stays in HBM."""
+        perm = i32(perm)
+        left, right = np.zeros(2 * self.n - 1, np.int32), np.zeros(2 * self.n - 1, np.int32)
+        self.ctx.check(self.ctx.lib.lzg_nj_seed_tree_profiles(self.ctx.h, self.h, ptr(perm), ptr(left), ptr(right)))
+        return left, right
 
     def distance_noalloc(self, d_ptr):
         """lzg_distance_matrix_noalloc: the whole matrix to raw device pointer d_ptr (N*N int32) without any allocation --

@@ -331,8 +331,10 @@ int lzg_distance_matrix(lzg_ctx* ctx, const lzg_profiles* cp, int32_t* D) {
         if (rc != LZG_OK) return rc;
         LZG_CUDA(ctx, cudaMemcpyAsync(D, p->d_D, bytes, cudaMemcpyDeviceToHost, ctx->stream));
         LZG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        p->d_D_whole = true;
         return LZG_OK;
     }
+    p->d_D_whole = false;
     for (int g = 0; g < groups; g++) {
         const int ra = (int)((int64_t)R * g / groups), rb = (int)((int64_t)R * (g + 1) / groups);
         if (ra == rb) continue;
@@ -349,7 +351,24 @@ int lzg_distance_matrix(lzg_ctx* ctx, const lzg_profiles* cp, int32_t* D) {
     }
     cudaError_t e1 = cudaStreamSynchronize(ctx->copy_stream), e2 = cudaStreamSynchronize(ctx->stream);
     if (rc == LZG_OK && (e1 != cudaSuccess || e2 != cudaSuccess)) rc = lzg_fail(ctx, LZG_ERR_CUDA, "lzg_distance_matrix", e1 != cudaSuccess ? e1 : e2);
+    p->d_D_whole = rc == LZG_OK;
     return rc;
+}
+
+// NJ seed tree of the profiles' own distance matrix without the matrix leaving HBM: the copy lzg_distance_matrix left on the
+// device if there is one, else computed now.
+int lzg_nj_seed_tree_profiles(lzg_ctx* ctx, const lzg_profiles* cp, const int32_t* perm, int32_t* left, int32_t* right) {
+    if (!ctx || !cp || cp->ctx != ctx || cp->n < 1) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nj_seed_tree_profiles: bad argument");
+    lzg_profiles* p = const_cast<lzg_profiles*>(cp);
+    LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = ensure_dD(ctx, p);
+    if (rc != LZG_OK) return rc;
+    if (!p->d_D_whole) {
+        rc = lzg_distance_run(ctx, p, 0, 1, 0, INT32_MAX, p->d_D, nullptr);
+        if (rc != LZG_OK) return rc;
+        p->d_D_whole = true;
+    }
+    return lzg_nj_seed_tree_device(ctx, p->d_D, p->n, perm, left, right);
 }
 
 int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* cp, int32_t shard, int32_t n_shards, int32_t* D, int64_t* pairs_done) {
@@ -361,6 +380,7 @@ int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* cp, int32_t shard, int3
     LZG_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = ensure_dD(ctx, p);
     if (rc != LZG_OK) return rc;
+    p->d_D_whole = false;
     rc = lzg_distance_run(ctx, p, shard, n_shards, 0, INT32_MAX, p->d_D, pairs_done);
     if (rc != LZG_OK) return rc;
     // copy back the strips this shard owns: for tile row r the row strip [r*bm, ..) x [r*bm, n) and

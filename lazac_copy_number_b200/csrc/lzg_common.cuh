@@ -72,6 +72,7 @@ struct lzg_profiles {
     uint8_t* d = nullptr;          // [n_pad][pitch]
     size_t d_bytes = 0;
     int32_t* d_D = nullptr;        // lazily allocated N x N result used by the host-output entry points
+    bool d_D_whole = false;        // d_D holds the whole matrix (set by lzg_distance_matrix; lzg_nj_seed_tree_profiles reads it)
 };
 
 int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuccess);

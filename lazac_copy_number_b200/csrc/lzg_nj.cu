@@ -42,11 +42,18 @@ __device__ __forceinline__ uint32_t float_order(float f) {  // monotone map floa
 }
 
 // m[i][j] = (float)D[perm[i]][perm[j]], zero diagonal (NJ_shuffle_distance_matrix + dmat parse).
-__global__ void k_nj_gather(const int32_t* __restrict__ D, const int32_t* __restrict__ perm, float* __restrict__ m, int n, int ld) {
+__global__ void k_nj_gather(const int32_t* __restrict__ D, const int32_t* __restrict__ perm, float* __restrict__ m, int n, int ld, int* __restrict__ flag) {
     const int i = blockIdx.y;
     const size_t src = (size_t)perm[i] * n;
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < ld; j += gridDim.x * blockDim.x)
-        m[(size_t)i * ld + j] = i == j || j >= n ? 0.0f : (float)D[src + perm[j]];
+    {
+        int v = 0;
+        if (i != j && j < n) {
+            v = D[src + perm[j]];
+            if (v < 0 || v >= (1 << 24)) *flag = 1;  // its float32 image would not be exact
+        }
+        m[(size_t)i * ld + j] = (float)v;
+    }
 }
 
 // NJ_init_r: r[k] = sequential float32 sum of d(k, j) in increasing j (rows above k first, then
@@ -283,7 +290,7 @@ __device__ __forceinline__ float nj_sum_in_order(const float* v_smem, int cnt, f
 // p2 = n0 - 2 - v -- so that every virtual row has (at most) C chunks and task t -> v = t / C, chunk t % C; warps take tasks round
 // robin.  SMEM: r2 comes from shared memory where the pending node and the pad columns hold -inf (their pairs evaluate to +inf).
 template <bool SMEM, bool STANDIN = false>
-__device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ m, int n0, int ld, int base, int size, int pendp, const float* __restrict__ r2,
+__device__ __noinline__ unsigned long long nj_scan(const float* __restrict__ m, int n0, int ld, int base, int size, int pendp, const float* __restrict__ r2,
                                                       const float* s_r2, int r2_org, int n_scan, int scan_rank, int bp = -1,
                                                       const float* __restrict__ row_standin = nullptr) {
     const float inf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
@@ -364,9 +371,48 @@ __device__ __forceinline__ unsigned long long nj_scan(const float* __restrict__ 
     return best;
 }
 
+// CTA 0 of k_nj_persistent (early form): the joined row c and the new r2 of every index into shared memory, from the rows a and b
+// and the row sums BEFORE the update.  Aligned groups of four physical columns (rows start 16-byte aligned, pad columns hold
+// zeros), two groups a thread in flight: three L2 round trips at n = 10,000.  Its own function so that its registers do not
+// weigh on the scan loop.
+__device__ __noinline__ void nj_stage_join(const float* __restrict__ m, const float* __restrict__ r, int n0, int ld, int base, int size, int a, int b, float dab,
+                                           float a2, float b2, float denom, float* s_c, float* s_r2) {
+    const int tid = threadIdx.x;
+    const float4* pa = reinterpret_cast<const float4*>(m + (size_t)(a + base) * ld);
+    const float4* pb = reinterpret_cast<const float4*>(m + (size_t)(b + base) * ld);
+    const float4* pr = reinterpret_cast<const float4*>(r);
+    const int gbeg = base >> 2, gend = (n0 + 3) >> 2;
+    for (int g0 = gbeg + tid; g0 < gend; g0 += 2 * 512) {
+        float4 A[2], B[2], R[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            const int g = g0 + 512 * u;
+            if (g < gend) A[u] = __ldcg(pa + g), B[u] = __ldcg(pb + g), R[u] = __ldcg(pr + g);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            const int g = g0 + 512 * u;
+            if (g < gend) {
+                const float va[4] = {A[u].x, A[u].y, A[u].z, A[u].w}, vb[4] = {B[u].x, B[u].y, B[u].z, B[u].w}, vr[4] = {R[u].x, R[u].y, R[u].z, R[u].w};
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const int i = 4 * g + e - base;
+                    if (i >= 0 && i < size) {
+                        const float da = i == b ? dab : va[e], db = i == b ? 0.0f : vb[e];
+                        const float c = (float)((double)__fadd_rn(__fsub_rn(da, a2), __fsub_rn(db, b2)) / 2.0);
+                        const float ri = __fadd_rn(__fsub_rn(__fsub_rn(vr[e], da), db), c);
+                        s_c[i] = i == a ? 0.0f : c;
+                        s_r2[i] = __fdiv_rn(ri, denom);
+                    }
+                }
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(512, 2)
 k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, float* __restrict__ r2, int* __restrict__ node, float* __restrict__ cvec,
-                int32_t* __restrict__ left, int32_t* __restrict__ right, lzg_nj_state* __restrict__ st, int r2_in_smem, unsigned long long* __restrict__ dbg, int* __restrict__ smid) {
+                int32_t* __restrict__ left, int32_t* __restrict__ right, lzg_nj_state* __restrict__ st, int r2_in_smem, int early, unsigned long long* __restrict__ dbg, int* __restrict__ smid) {
     const int tid = threadIdx.x, n_ctas = gridDim.x;
     // CTA 0 owns the joined node (its row sum and its pairs); the others share the triangle -- except a CTA that landed on CTA 0's
     // SM: it only takes part in the updates, so that the lane adding the row sum (one dependent float add after the other, the
@@ -394,6 +440,8 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
     extern __shared__ __align__(16) float s_r2[];  // r2 of the active indices (logical), when n0 floats fit
     const bool timed = scans && scan_rank == 0 && tid == 0;
     int base = 0, joined = n0, pend = -1;
+    int ja = 0, jb = 0;  // the pair joined last, in the numbering it was found in (early)
+    float* s_c = s_r2 + ld + 4;  // early, CTA 0: the joined row by the last join's index; s_r2: r2 after that join, same index
     for (int size = n0; size > 2; size--, base++, joined++) {
         const int parity = joined & 1;
         unsigned long long t0 = 0, ts0 = 0;
@@ -408,6 +456,28 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
                 const float pend_denom = (float)(size - 2);  // and divided by (size + 1) - 3
                 // the pairs of the new node: its row of the (symmetric) matrix.  The operands of the first 2048 are fetched now,
                 // before the row sum they wait for is known
+                if (early) {
+                    // c and r2 of the last join were staged in shared memory right behind the barrier that published the pair (below),
+                    // so this chain of adds ran alongside the other CTAs' update, their barrier and their scan
+                    if (tid == 0) {
+                        float sum = nj_sum_in_order(s_c + ja + 1, size - ja, 0.0f);  // i = a+1 .. size (the last join's numbering), then 0 .. a-1
+                        sum = nj_sum_in_order(s_c, ja, sum);
+                        const float r2p = __fdiv_rn(sum, pend_denom);
+                        r[pend + base] = sum;
+                        r2[pend + base] = r2p;
+                        s_r2p = r2p;
+                        if (dbg) dbg[n_ctas] += nj_now() - ts0;
+                    }
+                    __syncthreads();
+                    const float r2p = s_r2p;
+                    const int bq = ja != 0 ? jb - 1 : -1;  // this index took over the data of the dropped index 0
+                    for (int q = tid; q < size; q += 512) {
+                        if (q == pend) continue;
+                        const int src = q == bq ? 0 : q + 1;
+                        const unsigned long long k = nj_key(s_c[src], s_r2[src], r2p, min(q, pend), max(q, pend), n0);
+                        best = k < best ? k : best;
+                    }
+                } else {
                 const float* row_p = m + (size_t)(pend + base) * ld + base;
                 float d0[4], rq0[4];
 #pragma unroll
@@ -482,6 +552,7 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
                         }
                     }
                 }
+                }
             }
         } else if (scans) {
             const int pendp = pend >= 0 ? pend + base : -1;
@@ -504,6 +575,14 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
         __syncthreads();
         if (tid == 0) {
             for (int w = 1; w < (int)(blockDim.x >> 5); w++) best = s_best[w] < best ? s_best[w] : best;
+            if (early && blockIdx.x == 0) {  // the barrier behind the update, which this CTA only signed: the key was reset before it
+                long long spins = 0;
+                while ((unsigned)ld_acquire_i(reinterpret_cast<const int*>(&st->bar_gen)) != phase)
+                    if (++spins > (1ll << 27)) {
+                        st->err = 1;
+                        break;
+                    }
+            }
             if (best != ~0ull) atomicMin(&st->key[parity], best);
             if (dbg) dbg[blockIdx.x] += nj_now() - ts0;
         }
@@ -521,8 +600,60 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
         const float a2 = (float)((double)__fadd_rn(dab, __fsub_rn(r2a, r2b)) / 2.0);
         const float b2 = (float)((double)__fadd_rn(dab, __fsub_rn(r2b, r2a)) / 2.0);
         const float denom = (float)(size - 3);
-        const int gid = blockIdx.x * blockDim.x + tid, gstride = n_ctas * blockDim.x;
-        for (int i = gid; i < size; i += gstride) {
+        // CTA 0 keeps out of the update: ugid over the other CTAs
+        const int ugid = ((int)blockIdx.x - 1) * 512 + tid, ustride = (n_ctas - 1) * 512;
+        if (early && blockIdx.x == 0) {
+            // the joined row c and the new r2 of every index, from the rows a and b and the row sums BEFORE the update (the
+            // updating threads hold their stores back until st->staged says these reads are done)
+            nj_stage_join(m, r, n0, ld, base, size, a, b, dab, a2, b2, denom, s_c, s_r2);
+            __syncthreads();
+            ++phase;  // the barrier behind the update: signed here, waited for only before this CTA's next atomicMin
+            if (tid == 0) st_release_i(reinterpret_cast<int*>(&st->staged), n0 - size + 1);
+            if (tid == 32) {
+                unsigned old;
+                asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(&st->bar_count) : "memory");
+                if (old == phase * n_ctas - 1) st_release_i(reinterpret_cast<int*>(&st->bar_gen), (int)phase);
+            }
+        } else if (early) {  // one index per thread (the host checked ustride >= n0): loads, the wait, stores
+            const int i = ugid;
+            const bool act = i < size && i != a;
+            float da = 0.0f, db = 0.0f, ro = 0.0f, v0 = 0.0f;
+            if (act) {
+                da = i == b ? dab : __ldcg(row_a + i), db = i == b ? 0.0f : __ldcg(row_b + i);
+                ro = __ldcg(r + i + base);
+                v0 = a == 0 ? 0.0f : __ldcg(row_0 + i);
+            }
+            if (((int)blockIdx.x - 1) * 512 < size) {
+                if (tid == 0) {
+                    long long spins = 0;
+                    while (ld_acquire_i(reinterpret_cast<const int*>(&st->staged)) < n0 - size + 1)
+                        if (++spins > (1ll << 27)) {
+                            st->err = 1;
+                            break;
+                        }
+                }
+                __syncthreads();
+            }
+            if (act && i != b) {
+                const float c = (float)((double)__fadd_rn(__fsub_rn(da, a2), __fsub_rn(db, b2)) / 2.0);
+                row_a[i] = c;
+                m[(size_t)(i + base) * ld + a + base] = c;
+                const float ri = __fadd_rn(__fsub_rn(__fsub_rn(ro, da), db), c);
+                r[i + base] = ri;
+                const float r2i = __fdiv_rn(ri, denom);
+                r2[i + base] = r2i;
+                const float v = a == 0 ? c : v0;
+                row_b[i] = v;
+                m[(size_t)(i + base) * ld + b + base] = v;
+                if (i == 0) {
+                    row_b[a] = c;
+                    row_a[b] = c;
+                    r[b + base] = ri;
+                    r2[b + base] = r2i;
+                }
+            }
+        } else if (blockIdx.x != 0) {
+        for (int i = ugid; i < size; i += ustride) {
             if (i == a) continue;
             // i == b: d(a, b) from the snapshot (thread 0 rewrites that cell below) and d(b, b) = 0, as the reference reads them
             const float da = i == b ? dab : __ldcg(row_a + i), db = i == b ? 0.0f : __ldcg(row_b + i);
@@ -547,7 +678,8 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
                 r2[b + base] = r2i;
             }
         }
-        if (gid == 0) {
+        }
+        if (blockIdx.x == 1 && tid == 0) {
             left[joined] = __ldcg(node + a + base);
             right[joined] = __ldcg(node + b + base);
             const int where = a == 0 ? b : a;  // where the joined node lives from now on
@@ -555,15 +687,16 @@ k_nj_persistent(float* __restrict__ m, int n0, int ld, float* __restrict__ r, fl
             node[where + base] = joined;
             st->key[parity ^ 1] = ~0ull;  // the next join's minimum; nobody touches it before the barrier below
         }
+        ja = a, jb = b;
         pend = (a == 0 ? b : a) - 1;  // where the joined node lives, in the next join's numbering (base moves on by one)
         if (timed) t3 = nj_now();
-        if (!nj_barrier(st, n_ctas, ++phase)) return;
+        if (!(early && blockIdx.x == 0) && !nj_barrier(st, n_ctas, ++phase)) return;
         if (timed) {
             const unsigned long long t4 = nj_now();
             st->t_scan += t1 - t0, st->t_wait1 += t2 - t1, st->t_update += t3 - t2, st->t_wait2 += t4 - t3;
         }
     }
-    if (blockIdx.x == 0 && tid == 0) {
+    if (blockIdx.x == 1 && tid == 0) {  // the CTA that kept the node table, behind the last barrier
         left[joined] = __ldcg(node + base);
         right[joined] = __ldcg(node + base + 1);
     }
@@ -802,8 +935,9 @@ __global__ void k_nj_finish(const int* __restrict__ node, int base, int32_t* __r
 
 }  // namespace
 
-extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, const int32_t* perm, int32_t* left, int32_t* right) {
-    if (!ctx || !D_host || !perm || !left || !right || n < 1 || n > 65535) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nj_seed_tree: bad argument");
+// D_host or d_D_in (device, n x n int32, left untouched): one of the two
+static int nj_seed_tree_impl(lzg_ctx* ctx, const int32_t* D_host, const int32_t* d_D_in, int32_t n, const int32_t* perm, int32_t* left, int32_t* right) {
+    if (!ctx || (!D_host && !d_D_in) || !perm || !left || !right || n < 1 || n > 65535) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nj_seed_tree: bad argument");
     LZG_CUDA(ctx, cudaSetDevice(ctx->device));
     const int total = 2 * n - 1;
     for (int i = 0; i < n; i++) left[i] = right[i] = -1;
@@ -814,9 +948,6 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
             if (perm[i] < 0 || perm[i] >= n || seen[perm[i]]) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nj_seed_tree: perm is not a permutation");
             seen[perm[i]] = 1;
         }
-        const size_t nn = (size_t)n * n;
-        for (size_t q = 0; q < nn; q++)
-            if (D_host[q] < 0 || D_host[q] >= (1 << 24)) return lzg_fail(ctx, LZG_ERR_RANGE, "distance does not fit float32 exactly");
     }
     int32_t *d_D = nullptr, *d_perm = nullptr, *d_left = nullptr, *d_right = nullptr;
     int* d_node = nullptr;
@@ -829,7 +960,7 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     const size_t nn = (size_t)n * n;
     const int ld = (n + 3) & ~3;  // row pitch of the float matrix: rows start 16-byte aligned
     auto release = [&]() {
-        lzg_dev_free(ctx, d_D);
+        if (!d_D_in) lzg_dev_free(ctx, d_D);
         lzg_dev_free(ctx, d_perm);
         lzg_dev_free(ctx, d_left);
         lzg_dev_free(ctx, d_right);
@@ -844,7 +975,9 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
         lzg_dev_free(ctx, d_smid);
     };
     const auto t_begin = std::chrono::steady_clock::now();
-    cudaError_t e = lzg_dev_alloc(ctx, (void**)&d_D, sizeof(int32_t) * nn);
+    cudaError_t e = cudaSuccess;
+    if (d_D_in) d_D = const_cast<int32_t*>(d_D_in);
+    else e = lzg_dev_alloc(ctx, (void**)&d_D, sizeof(int32_t) * nn);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_m, sizeof(float) * (size_t)n * ld);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_perm, sizeof(int32_t) * n);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_left, sizeof(int32_t) * total);
@@ -853,17 +986,25 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r, sizeof(float) * 2 * ld);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_r2, sizeof(float) * ld);
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&d_key, sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_D, D_host, sizeof(int32_t) * nn, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && !d_D_in) e = cudaMemcpyAsync(d_D, D_host, sizeof(int32_t) * nn, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_perm, perm, sizeof(int32_t) * n, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d_key, 0xff, sizeof(unsigned long long), ctx->stream);
     if (e != cudaSuccess) {
         release();
         return lzg_fail(ctx, LZG_ERR_CUDA, "lzg_nj_seed_tree: setup", e);
     }
-    k_nj_gather<<<dim3(std::max(1, std::min(32, (n + 255) / 256)), n), 256, 0, ctx->stream>>>(d_D, d_perm, d_m, n, ld);
+    k_nj_gather<<<dim3(std::max(1, std::min(32, (n + 255) / 256)), n), 256, 0, ctx->stream>>>(d_D, d_perm, d_m, n, ld, ctx->d_flag);
     ctx->launches++;
     k_nj_init_r<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_m, n, ld, d_r, d_r2, d_node);
     ctx->launches++;
+    // the range check rode along with the gather (a host loop over n^2 values cost 57 ms at n = 10,000)
+    e = cudaMemcpyAsync(ctx->h_pinned, ctx->d_flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess || ctx->h_pinned[0]) {
+        release();
+        return e != cudaSuccess ? lzg_fail(ctx, LZG_ERR_CUDA, "lzg_nj_seed_tree: gather", e) : lzg_fail(ctx, LZG_ERR_RANGE, "distance does not fit float32 exactly");
+    }
     if (getenv("LZG_NJ_DEBUG")) {
         cudaStreamSynchronize(ctx->stream);
         fprintf(stderr, "[lzg nj] upload + gather + row sums: %.1f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
@@ -879,14 +1020,18 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     bool done = false;
     if (persistent && n >= 4) {
         int per_sm = 0;
-        size_t smem_r2 = sizeof(float) * (size_t)(ld + 4);  // r2 (scanning CTAs) / the joined row's terms (CTA 0) in shared memory
+        const size_t smem_one = sizeof(float) * (size_t)(ld + 4);  // r2 by column (scanning CTAs) / the joined row (CTA 0)
+        const size_t smem_fused = 2 * smem_one;
+        const bool no_smem = getenv("LZG_NJ_SMEM") && atoi(getenv("LZG_NJ_SMEM")) == 0;  // tests: the path of very large n
         if (fused) {
-            const size_t smem_fused = 2 * smem_r2;
             if (smem_fused > 48 * 1024) cudaFuncSetAttribute(k_nj_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fused);
             if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nj_fused, 512, smem_fused) != cudaSuccess || per_sm < 1) fused = false, cudaGetLastError();
         }
-        if (smem_r2 > 110 * 1024) smem_r2 = 0;               // two CTAs per SM must fit; beyond n = 28,000 both come from L2
-        if (getenv("LZG_NJ_SMEM") && atoi(getenv("LZG_NJ_SMEM")) == 0) smem_r2 = 0;  // tests: the path of very large n
+        // k_nj_persistent, early form (CTA 0 stages the joined row and the new r2 itself and adds the row sum while the others
+        // update): two arrays of shared memory, two CTAs per SM -> n <= 14,000; LZG_NJ_EARLY=0 keeps the form for larger n
+        bool early = !no_smem && smem_fused <= 110 * 1024 && !(getenv("LZG_NJ_EARLY") && atoi(getenv("LZG_NJ_EARLY")) == 0);
+        size_t smem_r2 = early ? smem_fused : smem_one;
+        if (smem_r2 > 110 * 1024 || no_smem) smem_r2 = 0;  // beyond n = 28,000 r2 and the joined row's terms come from L2
         if (smem_r2 > 48 * 1024) cudaFuncSetAttribute(k_nj_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r2);
         cudaError_t ce = fused ? cudaSuccess : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nj_persistent, 512, smem_r2);
         if (ce == cudaSuccess && per_sm >= 1) ce = lzg_dev_alloc(ctx, (void**)&d_cvec, sizeof(float) * (size_t)n);
@@ -904,11 +1049,12 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
             ce = cudaMemcpyAsync(d_state, &init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream);
             int grid = std::min(ctx->sm_count * std::min(per_sm, 2), 1 + std::max(1, n / 2));
             grid = std::max(grid, 2);  // CTA 0 owns the joined node, the others scan
-            int n_arg = n, ld_arg = ld, in_smem = smem_r2 > 0;
-            void* args[] = {(void*)&d_m, (void*)&n_arg, (void*)&ld_arg, (void*)&d_r, (void*)&d_r2, (void*)&d_node, (void*)&d_cvec, (void*)&d_left, (void*)&d_right, (void*)&d_state, (void*)&in_smem, (void*)&d_dbg, (void*)&d_smid};
+            if ((long long)(grid - 1) * 512 < n) early = false;  // one index per updating thread
+            int n_arg = n, ld_arg = ld, in_smem = smem_r2 > 0, early_arg = early;
+            void* args[] = {(void*)&d_m, (void*)&n_arg, (void*)&ld_arg, (void*)&d_r, (void*)&d_r2, (void*)&d_node, (void*)&d_cvec, (void*)&d_left, (void*)&d_right, (void*)&d_state, (void*)&in_smem, (void*)&early_arg, (void*)&d_dbg, (void*)&d_smid};
             void* fargs[] = {(void*)&d_m, (void*)&n_arg, (void*)&ld_arg, (void*)&d_r, (void*)&d_r2, (void*)&d_node, (void*)&d_left, (void*)&d_right, (void*)&d_state, (void*)&d_dbg, (void*)&d_smid};
             if (ce == cudaSuccess)
-                ce = fused ? cudaLaunchCooperativeKernel((void*)k_nj_fused, dim3(grid), dim3(512), fargs, 2 * smem_r2, ctx->stream)
+                ce = fused ? cudaLaunchCooperativeKernel((void*)k_nj_fused, dim3(grid), dim3(512), fargs, smem_fused, ctx->stream)
                            : cudaLaunchCooperativeKernel((void*)k_nj_persistent, dim3(grid), dim3(512), args, smem_r2, ctx->stream);
             if (ce == cudaSuccess) {
                 ctx->launches++;
@@ -919,7 +1065,7 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
                     fprintf(stderr, "[lzg nj] n %d, %d CTAs: scan %.1f ms, wait behind the scan %.1f ms, update %.1f ms, wait behind the update %.1f ms\n", n, grid,
                             back.t_scan * 1e-6, back.t_wait1 * 1e-6, back.t_update * 1e-6, back.t_wait2 * 1e-6);
                 if (ce == cudaSuccess && d_dbg) {
-                    fprintf(stderr, "[lzg nj] n %d: %s, %d CTAs of 512 threads (%d per SM)\n", n, fused ? "k_nj_fused" : "k_nj_persistent", grid, per_sm);
+                    fprintf(stderr, "[lzg nj] n %d: %s, %d CTAs of 512 threads (%d per SM)\n", n, fused ? "k_nj_fused" : early ? "k_nj_persistent (early)" : "k_nj_persistent", grid, per_sm);
                     std::vector<unsigned long long> h(2 * grid + 2);
                     cudaMemcpy(h.data(), d_dbg, sizeof(unsigned long long) * (2 * grid + 2), cudaMemcpyDeviceToHost);
                     if (fused) fprintf(stderr, "[lzg nj] of the scan phase, staging r2: %.1f ms (CTA 1), %.1f ms (CTA %d)\n", h[grid + 2] * 1e-6, h[2 * grid] * 1e-6, grid - 1);
@@ -959,4 +1105,15 @@ extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, 
     release();
     if (e != cudaSuccess) return lzg_fail(ctx, LZG_ERR_CUDA, "lzg_nj_seed_tree", e);
     return LZG_OK;
+}
+
+extern "C" int lzg_nj_seed_tree(lzg_ctx* ctx, const int32_t* D_host, int32_t n, const int32_t* perm, int32_t* left, int32_t* right) {
+    if (!D_host) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nj_seed_tree: bad argument");
+    return nj_seed_tree_impl(ctx, D_host, nullptr, n, perm, left, right);
+}
+
+// The matrix already in HBM (d_D: n x n int32, e.g. what lzg_distance_matrix_device_async left there): no upload.
+extern "C" int lzg_nj_seed_tree_device(lzg_ctx* ctx, const int32_t* d_D, int32_t n, const int32_t* perm, int32_t* left, int32_t* right) {
+    if (!d_D) return lzg_fail(ctx, LZG_ERR_ARG, "lzg_nj_seed_tree_device: bad argument");
+    return nj_seed_tree_impl(ctx, nullptr, d_D, n, perm, left, right);
 }

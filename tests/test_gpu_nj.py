@@ -89,6 +89,32 @@ def test_nj_api_shapes_and_errors(ctx):
         ctx.nj_seed_tree(big, np.arange(9))                     # not exact in float32
 
 
+def test_nj_from_device_matrix_and_from_profiles(ctx):
+    """lzg_nj_seed_tree_device / lzg_nj_seed_tree_profiles (the matrix never leaves HBM) against lzg_nj_seed_tree on the host copy;
+    the profiles form both after lzg_distance_matrix (device copy reused) and on fresh profiles (computed now)."""
+    import torch
+    from lazac_copy_number_b200 import search, synth
+    from lazac_copy_number_b200.api import Profiles
+    from lazac_copy_number_b200._capi import LazacGpuError
+    for n, L, seed in ((5, 40, 1), (200, 333, 2), (1100, 600, 3)):
+        bp = synth.random_bp(n, L, seed=seed, lo=-4, hi=4, density=0.3)
+        perm = search.clearcut_shuffle(n, seed)
+        fresh = Profiles(ctx, bp)
+        l0, r0 = fresh.nj_seed_tree(perm)            # no matrix yet: computed on the device now
+        D = fresh.distance_matrix()
+        l1, r1 = fresh.nj_seed_tree(perm)            # the copy lzg_distance_matrix left in HBM
+        fresh.free()
+        want_l, want_r = ctx.nj_seed_tree(D, perm)
+        d = torch.from_numpy(D).to("cuda:0")
+        l2, r2 = ctx.nj_seed_tree_device(d.data_ptr(), n, perm)
+        assert np.array_equal(d.cpu().numpy(), D)    # left untouched
+        for left, right in ((l0, r0), (l1, r1), (l2, r2)):
+            assert np.array_equal(left, want_l) and np.array_equal(right, want_r), n
+    big = torch.full((9, 9), 1 << 24, dtype=torch.int32, device="cuda:0")
+    with pytest.raises(LazacGpuError):
+        ctx.nj_seed_tree_device(big.data_ptr(), 9, np.arange(9))   # not exact in float32: flagged by the gather
+
+
 def test_nj_gpu_equals_host_library(ctx):
     """lzg_nj_seed_tree against liblazac_host.so's CPU neighbour joining (the code `lazac` links) with the same taxon order."""
     from lazac_copy_number_b200 import search
@@ -124,6 +150,10 @@ def test_nj_persistent_kernel_on_larger_matrices(ctx, monkeypatch, n, seed, hi):
     monkeypatch.setenv("LZG_NJ_PERSISTENT", "1")  # two grid barriers per join (k_nj_persistent): the form for n > 14,000
     l4, r4 = ctx.nj_seed_tree(D, perm)
     assert np.array_equal(l4, cl) and np.array_equal(r4, cr)
+    monkeypatch.setenv("LZG_NJ_EARLY", "0")  # ... for n > 14,000: the joined row's terms through a device vector
+    l5, r5 = ctx.nj_seed_tree(D, perm)
+    assert np.array_equal(l5, cl) and np.array_equal(r5, cr)
+    monkeypatch.delenv("LZG_NJ_EARLY")
     monkeypatch.setenv("LZG_NJ_SMEM", "0")  # ... and for n > 28,000: r2 and the joined row's terms straight from L2
     l3, r3 = ctx.nj_seed_tree(D, perm)
     assert np.array_equal(l3, cl) and np.array_equal(r3, cr)

@@ -23,13 +23,17 @@ with Context(0) as ctx:
             bp = synth.bp_from_cn(prof["cn"], prof["seg"]).astype(np.int8)
         gp = Profiles(ctx, bp)
         D = gp.distance_matrix()
-        gp.free()
         perm = np.random.default_rng(1).permutation(n).astype(np.int32)
         ctx.nj_seed_tree(D[:64, :64].copy(), np.arange(64, dtype=np.int32))  # warm-up
         t0 = time.perf_counter()
         left, right = ctx.nj_seed_tree(D, perm)
         dt = time.perf_counter() - t0
         print("n = %d: GPU NJ %.3f s (%.1f G matrix elements scanned/s incl. upload)" % (n, dt, n ** 3 / 6 / dt / 1e9), flush=True)
+        t0 = time.perf_counter()
+        l2, r2 = gp.nj_seed_tree(perm)
+        dt = time.perf_counter() - t0
+        print("   the matrix already on the device (lzg_nj_seed_tree_profiles): %.3f s, same tree: %s" % (dt, bool((l2 == left).all() and (r2 == right).all())), flush=True)
+        gp.free()
         if k == 0 and not os.environ.get("NJ_SKIP_CLI"):
             lazac = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "host", "lazac")
             with tempfile.TemporaryDirectory() as d:
