@@ -468,6 +468,37 @@ def climb_section(ctx, name, bp, c0, c1, leaf_row, seed_note, reps, max_moves, p
         out["cpu_baseline"] = {"value": v, "unit": "candidates/s", "cores": 1, "kind": kind,
                                "sample": "%d candidates of the same neighbourhood (%.1f s of the reference's candidate loop)" % (cnt, dt),
                                "scores_equal_gpu": bool(np.array_equal(sc, allsc) and np.array_equal(mv, moves))}
+    # the calls around the climb: the bottom-up scoring pass (lzg_tree_score) and the ancestral labelling + download
+    # (lzg_tree_ancestral), each behind an L2 flush; bytes = rows read + rows written of the device format (1 byte per value here)
+    import ctypes as C
+    ms_score = []
+    for _ in range(3):
+        ctx.flush_l2()
+        ctx.sync()
+        ctx.timer_start()
+        base.small_rectilinear()
+        ms_score.append(ctx.timer_stop())
+    lab = np.zeros((n, L), np.int32)   # touched: the page faults of a fresh buffer are not the library's
+    br = np.zeros(n, np.int32)
+    wall_anc = []
+    for _ in range(3):
+        ctx.flush_l2()
+        ctx.sync()
+        t0 = time.perf_counter()
+        ctx.check(ctx.lib.lzg_tree_ancestral(ctx.h, base.h, lab.ctypes.data_as(C.c_void_p), br.ctypes.data_as(C.c_void_p)))
+        wall_anc.append(time.perf_counter() - t0)
+    n_int = len(internal) + 1
+    score_bytes = n_int * 6 * L            # two children's start/end rows read, the node's start/end written
+    anc_dev_bytes = n * 4 * L              # per node: its interval (2 rows) and the parent's label read, its label written
+    out["tail"] = {
+        "lzg_tree_score": {"ms": float(min(ms_score)), "algorithmic_bytes": int(score_bytes),
+                           "roofline": {"bound": "hbm", "achieved": score_bytes / (min(ms_score) * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                        "frac": score_bytes / (min(ms_score) * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                                        "note": "one kernel per tree level (a level waits for the one below): %d levels" % (int(dep.max()) + 1)}},
+        "lzg_tree_ancestral": {"ms": 1e3 * float(min(wall_anc)), "d2h_bytes": int(n * L), "host_int32_bytes_written": int(4 * n * L),
+                               "device_algorithmic_bytes": int(anc_dev_bytes),
+                               "note": "wall clock of the call: labelling kernels level by level, the labels cross PCIe as bytes into pinned staging and "
+                                       "host threads widen them into the caller's int32 matrix while the next block is copied"}}
     base.free()
     gp.free()
     return out

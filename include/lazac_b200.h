@@ -72,6 +72,11 @@ int lzg_profiles_upload_i8(lzg_ctx* ctx, const int8_t* bp, int32_t n_cells, int3
                            lzg_profiles** out);
 int lzg_profiles_free(lzg_profiles* p);
 int lzg_profiles_shape(const lzg_profiles* p, int32_t* n_cells, int32_t* n_pos);
+/* Which kernel the whole-matrix distance of these profiles runs on one GPU (decided at the first distance call from
+ * the value range): info[0] = 1 the exact tensor-core product (thermometer code, tcgen05 kind::i8), 0 the VABSDIFF4
+ * kernel; info[1] = K = sum over positions of (max - min); info[2] = padded code width; info[3] = tensor-core
+ * launches so far.  int64 info[4]. */
+int lzg_profiles_distance_path(const lzg_profiles* p, int64_t* info);
 
 /* ---- all-pairs ZCNT distance: replaces the pair loop of build_distance_matrix,
  *      src/lazac.cxx:81-91 (operator- include/copy_number.hpp:74-83 + breakpoint_magnitude

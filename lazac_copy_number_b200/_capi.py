@@ -37,6 +37,7 @@ SYMBOLS = [
     ("lzg_profiles_upload_i8", _i, [_vp, _vp, _i32, _i32, _vpp]),
     ("lzg_profiles_free", _i, [_vp]),
     ("lzg_profiles_shape", _i, [_vp, _i32p, _i32p]),
+    ("lzg_profiles_distance_path", _i, [_vp, _vp]),
     ("lzg_distance_matrix", _i, [_vp, _vp, _vp]),
     ("lzg_distance_matrix_device_async", _i, [_vp, _vp, _vp]),
     ("lzg_distance_matrix_noalloc", _i, [_vp, _vp, _vp]),

@@ -202,6 +202,12 @@ class Profiles:
         self.ctx.check(self.ctx.lib.lzg_nj_seed_tree_profiles(self.ctx.h, self.h, ptr(perm), ptr(left), ptr(right)))
         return left, right
 
+    def distance_path(self):
+        """{'tensor_core': bool, 'K': summed value range, 'k_pad': code width, 'launches': k_tc_distance launches so far}."""
+        info = (C.c_int64 * 4)()
+        self.ctx.check(self.ctx.lib.lzg_profiles_distance_path(self.h, info))
+        return {"tensor_core": bool(info[0]), "K": int(info[1]), "k_pad": int(info[2]), "launches": int(info[3])}
+
     def distance_noalloc(self, d_ptr):
         """lzg_distance_matrix_noalloc: the whole matrix to raw device pointer d_ptr (N*N int32) without any allocation --
         the kernel's work plan goes into the library's static device array (1 MiB; larger plans raise LazacGpuError)."""

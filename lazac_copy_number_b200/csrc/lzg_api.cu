@@ -283,8 +283,19 @@ int lzg_profiles_free(lzg_profiles* p) {
     cudaSetDevice(ctx->device);
     // stream-ordered frees: no synchronisation, the blocks go back to the pool
     lzg_dev_free(ctx, p->d_D);
+    lzg_distance_tc_free(ctx, p);
     lzg_dev_free(ctx, p->d);
     delete p;
+    return LZG_OK;
+}
+
+// Which kernel lzg_distance_* runs for these profiles' whole matrix on one GPU: info[0] = 1 the tensor-core product
+// (k_tc_distance), 0 k_zcnt_distance; info[1] = K, the summed value range of the positions (0 before the first distance call
+// and for the 16-bit format); info[2] = the thermometer code's padded width; info[3] = k_tc_distance launches so far.
+int lzg_profiles_distance_path(const lzg_profiles* p, int64_t* info) {
+    if (!p || !info) return LZG_ERR_ARG;
+    info[0] = info[1] = info[2] = info[3] = 0;
+    if (p->tc) info[0] = p->tc->usable, info[1] = p->tc->K, info[2] = p->tc->k_pad, info[3] = p->tc->launches;
     return LZG_OK;
 }
 
@@ -300,6 +311,8 @@ int lzg_distance_shard_device_async(lzg_ctx* ctx, const lzg_profiles* p, int32_t
     if (!ctx || !p || p->ctx != ctx || n_shards < 1 || shard < 0 || shard >= n_shards || (p->n > 0 && !d_D))
         return lzg_fail(ctx, LZG_ERR_ARG, "lzg_distance: bad argument");
     LZG_CUDA(ctx, cudaSetDevice(ctx->device));
+    // the thermometer code of the tensor-core path is part of every call's work, not a cache across calls
+    lzg_distance_tc_free(ctx, const_cast<lzg_profiles*>(p));
     return lzg_distance_run(ctx, const_cast<lzg_profiles*>(p), shard, n_shards, 0, INT32_MAX, d_D, pairs_done);
 }
 
@@ -323,6 +336,7 @@ int lzg_distance_matrix(lzg_ctx* ctx, const lzg_profiles* cp, int32_t* D) {
     LZG_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = ensure_dD(ctx, p);
     if (rc != LZG_OK) return rc;
+    lzg_distance_tc_free(ctx, p);  // rebuilt by the first row group below: part of this call's work
     const int n = p->n, bm = lzg_distance_tile(p), R = (n + bm - 1) / bm;
     const size_t bytes = sizeof(int32_t) * (size_t)n * n;
     const int groups = bytes < ((size_t)64 << 20) ? 1 : std::min(16, R);
@@ -364,6 +378,7 @@ int lzg_nj_seed_tree_profiles(lzg_ctx* ctx, const lzg_profiles* cp, const int32_
     int rc = ensure_dD(ctx, p);
     if (rc != LZG_OK) return rc;
     if (!p->d_D_whole) {
+        lzg_distance_tc_free(ctx, p);
         rc = lzg_distance_run(ctx, p, 0, 1, 0, INT32_MAX, p->d_D, nullptr);
         if (rc != LZG_OK) return rc;
         p->d_D_whole = true;
@@ -381,6 +396,7 @@ int lzg_distance_shard(lzg_ctx* ctx, const lzg_profiles* cp, int32_t shard, int3
     int rc = ensure_dD(ctx, p);
     if (rc != LZG_OK) return rc;
     p->d_D_whole = false;
+    lzg_distance_tc_free(ctx, p);
     rc = lzg_distance_run(ctx, p, shard, n_shards, 0, INT32_MAX, p->d_D, pairs_done);
     if (rc != LZG_OK) return rc;
     // copy back the strips this shard owns: for tile row r the row strip [r*bm, ..) x [r*bm, n) and

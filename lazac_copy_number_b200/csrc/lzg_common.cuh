@@ -73,7 +73,30 @@ struct lzg_profiles {
     size_t d_bytes = 0;
     int32_t* d_D = nullptr;        // lazily allocated N x N result used by the host-output entry points
     bool d_D_whole = false;        // d_D holds the whole matrix (set by lzg_distance_matrix; lzg_nj_seed_tree_profiles reads it)
+    struct lzg_tc_state* tc = nullptr;  // the tensor-core form of these profiles (lzg_distance_tc.cu), built on first use
 };
+
+// Thermometer-coded profiles for the tensor-core distance (lzg_distance_tc.cu).
+struct lzg_tc_state {
+    int usable = 0;                 // 0: the value range rules the path out (k_zcnt_distance runs)
+    int begun = 0;                  // the range kernel is queued, lzg_distance_tc_prepare_finish has not run yet
+    int64_t K = 0;                  // sum over positions of (max - min)
+    int k_pad = 0, n_pad = 0;       // columns padded to 128, rows to 256
+    uint8_t* d_T = nullptr;         // [n_pad][k_pad] bytes 0 / 1
+    int32_t* d_s = nullptr;         // [n_pad] row sums of T
+    int2* d_tiles = nullptr;        // (row block of 128, column block of 256) of the current launch
+    int tiles_cap = 0;
+    std::vector<int2> h_tiles;
+    std::vector<uint32_t> col;      // host copy of the column table
+    alignas(64) unsigned char tmap[128];  // CUtensorMap of T
+    int64_t launches = 0;           // k_tc_distance launches so far (tests, bench)
+};
+int lzg_distance_tc_prepare(lzg_ctx* ctx, lzg_profiles* p);  // 1: usable, 0: not for these profiles, < 0: error
+int lzg_distance_tc_prepare_begin(lzg_ctx* ctx, lzg_profiles* p);   // 2: queued, call _finish
+int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p);
+int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int own_mode, int row_lo, int row_hi, int32_t* d_D, int32_t* const* d_row_base,
+                        int64_t* pairs_done);
+void lzg_distance_tc_free(lzg_ctx* ctx, lzg_profiles* p);
 
 int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuccess);
 

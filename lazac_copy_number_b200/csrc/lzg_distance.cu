@@ -706,6 +706,12 @@ int lzg_distance_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int
                      int64_t* pairs_done, int32_t* const* d_row_base, int own_mode) {
     if (pairs_done) *pairs_done = 0;
     if (p->n == 0) return LZG_OK;
+    // narrow value ranges: the exact tensor-core product (lzg_distance_tc.cu)
+    {
+        const int tc = lzg_distance_tc_prepare(ctx, p);
+        if (tc < 0) return -tc;
+        if (tc == 1) return lzg_distance_tc_run(ctx, p, shard, n_shards, own_mode, row_lo, row_hi, d_D, d_row_base, pairs_done);
+    }
     int status = LZG_OK;
     const int bm = lzg_distance_tile(p);
     // one persistent CTA per SM: 8 warps x 254 registers fill the register file (3 CTAs of 2 warps for

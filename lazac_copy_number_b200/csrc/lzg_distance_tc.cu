@@ -1,0 +1,417 @@
+// lzg_distance_tc.cu -- the all-pairs ZCNT distance as an exact integer GEMM on the 5th-generation tensor cores (sm_100a).
+//
+// |a - b| is not a contraction, but it becomes one under a thermometer code.  Per position p let lo_p = min over the cells and
+// w_p = max - min; code the value v as the w_p bits t_k(v) = [v - lo_p > k], k = 0 .. w_p-1.  Then |a - b| = sum_k t_k(a) xor t_k(b),
+// and over a whole profile
+//        D[i][j] = s_i + s_j - 2 * (T T^t)[i][j],      T in {0,1}^(n x K), K = sum_p w_p, s_i = sum of row i of T,
+// bit-identical to the reference's loop (operator- include/copy_number.hpp:74-83 + breakpoint_magnitude src/copy_number.cxx:100-113)
+// because every quantity is an integer below 2^31: tcgen05.mma kind::i8 multiplies unsigned bytes into int32 accumulators.
+// Breakpoint profiles are sparse and narrow (cfg3: K = 2.02 L), so the product is ~10x fewer tensor-core cycles than the
+// VABSDIFF4 kernel has ALU cycles; lzg_distance_run dispatches here by value range (K <= 8 L, the 8-bit format, whole matrix on
+// one GPU) and keeps k_zcnt_distance for everything else.  LZG_TC=0 switches the path off, LZG_TC=1 forces it where it can run.
+//
+// Kernels: k_tc_colrange (lo_p, w_p), k_tc_expand (T and s), k_tc_distance: persistent CTAs over 128 x 256 tiles of the upper
+// triangle, operands by TMA (128-byte swizzle, 4 stages of 48 KB) issued by one thread, tcgen05.mma (M 128, N 256, K 32) issued
+// by one thread into 256 TMEM columns, epilogue of all four warps: tcgen05.ld -> s_i + s_j - 2 g -> D[i][j] and the mirror D[j][i].
+#include <cuda.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "lzg_common.cuh"
+
+namespace {
+
+constexpr int TC_BM = 128, TC_BN = 256, TC_BK = 128, TC_STAGES = 4, TC_UMMA_K = 32;
+constexpr int TC_STAGE_A = TC_BM * TC_BK, TC_STAGE_B = TC_BN * TC_BK, TC_STAGE = TC_STAGE_A + TC_STAGE_B;
+constexpr int TC_SMEM = TC_STAGES * TC_STAGE + 1024 /* alignment slack */ + 256 /* barriers, TMEM pointer */;
+constexpr int TC_TMEM_COLS = 256;
+
+// ---- per-position range over the cells: lo_p (biased byte) and hi_p ------------------------------------------------
+__global__ void k_tc_colrange(const uint8_t* __restrict__ d, int n, int pitch, int L, unsigned* __restrict__ lo_hi) {
+    // one thread per group of four positions, rows strided over blockIdx.y; lo_hi[2p] = 255 - lo, lo_hi[2p+1] = hi, both merged with atomicMax
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (4 * g >= L) return;
+    unsigned lo[4] = {255, 255, 255, 255}, hi[4] = {0, 0, 0, 0};
+    for (int i = blockIdx.y; i < n; i += gridDim.y) {
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(d + (size_t)i * pitch + 4 * g);
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const unsigned v = (w >> (8 * e)) & 255u;
+            lo[e] = min(lo[e], v), hi[e] = max(hi[e], v);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 4; e++)
+        if (4 * g + e < L) atomicMax(lo_hi + 2 * (4 * g + e), 255u - lo[e]), atomicMax(lo_hi + 2 * (4 * g + e) + 1, hi[e]);
+}
+
+// ---- T and its row sums ------------------------------------------------------------------------------------------
+// col[c] = (position << 9) | threshold: T[i][c] = [byte(i, position) >= threshold]; threshold 256 for the padding columns.
+__global__ void __launch_bounds__(256) k_tc_expand(const uint8_t* __restrict__ d, int n, int pitch, const uint32_t* __restrict__ col, int k_pad,
+                                                    uint8_t* __restrict__ T, int32_t* __restrict__ s) {
+    const int i = blockIdx.x;  // rows n .. n_pad-1 are zero rows
+    const uint8_t* row = d + (size_t)i * pitch;
+    int sum = 0;
+    for (int g = threadIdx.x; 16 * g < k_pad; g += blockDim.x) {
+        uint32_t out[4] = {0, 0, 0, 0};
+        if (i < n) {
+            const uint4* cp = reinterpret_cast<const uint4*>(col + 16 * g);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint4 c4 = __ldg(cp + q);
+                const uint32_t cc[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const unsigned thr = cc[e] & 511u;
+                    const unsigned bit = thr < 256u && row[cc[e] >> 9] >= thr ? 1u : 0u;
+                    out[q] |= bit << (8 * e);
+                    sum += (int)bit;
+                }
+            }
+        }
+        *reinterpret_cast<uint4*>(T + (size_t)i * k_pad + 16 * g) = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+    __shared__ int s_sum[8];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < 8; w++) t += s_sum[w];
+        s[i] = t;
+    }
+}
+
+// ---- PTX helpers ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bounded wait: a wrong descriptor or a lost arrival must end in an error, not in a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    const long long t0 = clock64();
+    for (;;) {
+        uint32_t done;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+        if (clock64() - t0 > 2000000000ll) __trap();  // about a second
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst), "l"(map), "r"(c0), "r"(c1),
+                 "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], unsigned bytes into int32
+__device__ __forceinline__ void tc_mma_i8(uint32_t d_tmem, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// shared-memory operand descriptor: K-major tile, 128-byte swizzle, rows of 128 bytes, groups of 8 rows 1024 bytes apart
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr) {
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) /* leading byte offset: unused with a swizzle */ | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) /* sm_100 */ |
+           (2ull << 61) /* SWIZZLE_128B */;
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, "
+        "%24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]),
+          "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// ---- the product and the epilogue --------------------------------------------------------------------------------------
+// tiles[t] = (row block of 128, column block of 256); every tile runs the whole K.  Thread 0 is the TMA producer, thread 32 the
+// MMA issuer; then all four warps read their 32 TMEM lanes (= tile rows) and write D.  Mirrors D[j][i] are written only for rows
+// j beyond this tile's row block, so a finished group of row blocks never changes again (lzg_distance_matrix copies it out
+// while later groups compute).
+__global__ void __launch_bounds__(128, 1)
+k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__ tiles, int n_tiles, int k_blocks, const int32_t* __restrict__ s,
+              int32_t* __restrict__ D, int32_t* const* __restrict__ row_base, int n) {
+    extern __shared__ uint8_t tc_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const uint32_t bar_full = smem_base + TC_STAGES * TC_STAGE, bar_empty = bar_full + 8 * TC_STAGES, bar_tmem = bar_empty + 8 * TC_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_STAGES * TC_STAGE + 8 * (2 * TC_STAGES + 1));
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (tid == 0) {
+        for (int q = 0; q < TC_STAGES; q++) mbar_init(bar_full + 8 * q, 1), mbar_init(bar_empty + 8 * q, 1);
+        mbar_init(bar_tmem, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    // instruction descriptor: D int32, A and B unsigned 8-bit, both K-major, N = 256, M = 128
+    constexpr uint32_t idesc = (2u << 4) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    uint32_t it = 0, tile_parity = 0;  // k-blocks issued so far (stage = it % STAGES, phase = it / STAGES & 1)
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int2 tile = tiles[t];
+        const int row0 = tile.x * TC_BM, col0 = tile.y * TC_BN;
+        if (tid == 0) {
+            uint32_t q = it;
+            for (int kb = 0; kb < k_blocks; kb++, q++) {
+                const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
+                mbar_wait(bar_empty + 8 * st, ph ^ 1u);
+                mbar_expect_tx(bar_full + 8 * st, TC_STAGE);
+                const uint32_t a = smem_base + st * TC_STAGE, b = a + TC_STAGE_A;
+                tma_load_2d(a, &tmap, kb * TC_BK, row0, bar_full + 8 * st);
+                tma_load_2d(b, &tmap, kb * TC_BK, col0, bar_full + 8 * st);
+                tma_load_2d(b + TC_STAGE_A, &tmap, kb * TC_BK, col0 + 128, bar_full + 8 * st);
+            }
+        } else if (tid == 32) {
+            uint32_t q = it;
+            for (int kb = 0; kb < k_blocks; kb++, q++) {
+                const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
+                mbar_wait(bar_full + 8 * st, ph);
+                tc_fence_after();
+                const uint32_t a = smem_base + st * TC_STAGE, b = a + TC_STAGE_A;
+#pragma unroll
+                for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
+                    tc_mma_i8(tmem, tc_smem_desc(a + k * TC_UMMA_K), tc_smem_desc(b + k * TC_UMMA_K), idesc, (kb | k) != 0);
+                tc_commit(bar_empty + 8 * st);  // the stage is free once these MMAs have read it
+            }
+            tc_commit(bar_tmem);  // the accumulator is complete
+        }
+        it += k_blocks;
+        __syncwarp();
+        mbar_wait(bar_tmem, tile_parity);
+        tile_parity ^= 1u;
+        tc_fence_after();
+        // ---- epilogue: thread = tile row i (TMEM lane), 32 columns at a time
+        const int i = row0 + tid;
+        const int si = i < n ? s[i] : 0;
+        // row_base (several GPUs, lzg_multi.cu): one pointer per block of 128 output rows instead of the one matrix
+        int32_t* drow = row_base ? row_base[tile.x] + (size_t)tid * n : D + (size_t)i * n;
+        const bool vec = (n & 3) == 0;
+        const int mirror_from = row0 + TC_BM;  // rows below this tile's row block only
+        for (int c = 0; c < TC_BN; c += 32) {
+            uint32_t g[32];
+            tc_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c, g);
+            const int j0 = col0 + c;
+            if (j0 >= n) continue;  // uniform over the CTA
+            int v[32];
+#pragma unroll
+            for (int e = 0; e < 32; e++) v[e] = si + (j0 + e < n ? __ldg(s + j0 + e) : 0) - 2 * (int)g[e];
+            if (i < n) {
+                if (vec && j0 + 32 <= n) {
+#pragma unroll
+                    for (int e = 0; e < 32; e += 4) *reinterpret_cast<int4*>(drow + j0 + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; e++)
+                        if (j0 + e < n) drow[j0 + e] = v[e];
+                }
+#pragma unroll
+                for (int e = 0; e < 32; e++) {
+                    const int j = j0 + e;
+                    if (j >= mirror_from && j < n) {  // lanes = consecutive i: coalesced
+                        if (row_base) row_base[j >> 7][(size_t)(j & 127) * n + i] = v[e];
+                        else D[(size_t)j * n + i] = v[e];
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+        __syncthreads();  // every warp is done with the accumulator before the next tile's first MMA overwrites it
+        tc_fence_after();
+    }
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_TMEM_COLS) : "memory");
+}
+
+}  // namespace
+
+// ---- host side ---------------------------------------------------------------------------------------------------------
+typedef CUresult (*tc_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                 CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static tc_encode_fn tc_encoder() {
+    static tc_encode_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (tc_encode_fn)sym;
+        else cudaGetLastError();
+    }
+    return fn;
+}
+
+void lzg_distance_tc_free(lzg_ctx* ctx, lzg_profiles* p) {
+    if (!p->tc) return;
+    lzg_dev_free(ctx, p->tc->d_T);
+    lzg_dev_free(ctx, p->tc->d_s);
+    lzg_dev_free(ctx, p->tc->d_tiles);
+    delete p->tc;
+    p->tc = nullptr;
+}
+
+// Two steps so that several GPUs (lzg_multi.cu) overlap: _begin queues the range kernel and its read-back, _finish waits for
+// it, lays the code out on the host (a loop over the positions) and queues the expansion.  Returns 1: usable, 0: these profiles
+// stay with k_zcnt_distance, < 0: minus an LZG_ERR_* status.
+int lzg_distance_tc_prepare_begin(lzg_ctx* ctx, lzg_profiles* p) {
+    if (p->tc) return p->tc->usable;
+    const char* env = getenv("LZG_TC");
+    const int mode = env ? atoi(env) : -1;  // 0 off, 1 forced, otherwise by value range
+    lzg_tc_state* tc = new lzg_tc_state;
+    p->tc = tc;
+    // fewer tiles than SMs (n below ~2,700): one tile per CTA would leave most of the GPU idle, and k_zcnt_distance splits K
+    const long long whole_tiles = (long long)((p->n + TC_BM - 1) / TC_BM) * ((p->n + TC_BN - 1) / TC_BN) / 2;
+    if (mode == 0 || p->width != 1 || p->n < 256 || p->L < 1 || !tc_encoder()) return 0;
+    if (mode != 1 && whole_tiles < (long long)ctx->sm_count * 3 / 4) return 0;
+    const int n = p->n, L = p->L;
+    int rc = lzg_ensure_pinned(ctx, 16 + 2 * (size_t)L);
+    if (rc != LZG_OK) return -rc;
+    unsigned* d_lohi = nullptr;
+    cudaError_t e = lzg_dev_alloc(ctx, (void**)&d_lohi, sizeof(unsigned) * 2 * (size_t)L);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_lohi, 0, sizeof(unsigned) * 2 * (size_t)L, ctx->stream);
+    if (e == cudaSuccess) {
+        const int groups = (L + 3) / 4;
+        k_tc_colrange<<<dim3((groups + 127) / 128, std::max(1, std::min(n, 4 * ctx->sm_count * 128 / std::max(128, groups)))), 128, 0, ctx->stream>>>(p->d, n, p->pitch, L,
+                                                                                                                                                    d_lohi);
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->h_pinned + 16, d_lohi, sizeof(unsigned) * 2 * (size_t)L, cudaMemcpyDeviceToHost, ctx->stream);
+    lzg_dev_free(ctx, d_lohi);
+    if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: value ranges", e);
+    tc->begun = 1;
+    return 2;  // _finish decides
+}
+
+int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
+    lzg_tc_state* tc = p->tc;
+    if (!tc || !tc->begun) return tc ? tc->usable : 0;
+    tc->begun = 0;
+    const char* env = getenv("LZG_TC");
+    const int mode = env ? atoi(env) : -1;
+    const int n = p->n, L = p->L;
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: value ranges", e);
+    const unsigned* lohi = reinterpret_cast<const unsigned*>(ctx->h_pinned + 16);
+    int64_t K = 0;
+    for (int q = 0; q < L; q++) K += (int64_t)lohi[2 * q + 1] - (255 - (int64_t)lohi[2 * q]);
+    tc->K = K;
+    const int64_t k_pad = std::max<int64_t>(TC_BK, (K + TC_BK - 1) / TC_BK * TC_BK), n_pad = ((int64_t)n + 255) / 256 * 256;
+    size_t free_b = 0, total_b = 0;
+    cudaMemGetInfo(&free_b, &total_b);
+    const bool fits = k_pad < (1ll << 30) && (uint64_t)(n_pad * k_pad) < free_b / 2;
+    if (!fits || (mode != 1 && K > 8ll * L)) return 0;  // wide values: the VABSDIFF4 kernel is the faster one
+    // the column table: (position << 9) | threshold byte; 256 = never for the padding columns
+    tc->col.assign((size_t)k_pad, 256u);
+    {
+        size_t c = 0;
+        for (int q = 0; q < L; q++) {
+            const unsigned lo = 255u - lohi[2 * q], hi = lohi[2 * q + 1];
+            for (unsigned thr = lo + 1; thr <= hi; thr++) tc->col[c++] = ((uint32_t)q << 9) | thr;
+        }
+    }
+    uint32_t* d_col = nullptr;
+    e = lzg_dev_alloc(ctx, (void**)&d_col, sizeof(uint32_t) * (size_t)k_pad);
+    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_T, (size_t)(n_pad * k_pad));
+    if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_s, sizeof(int32_t) * (size_t)n_pad);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_col, tc->col.data(), sizeof(uint32_t) * (size_t)k_pad, cudaMemcpyHostToDevice, ctx->stream);  // pageable: staged before the call returns
+    if (e == cudaSuccess) {
+        k_tc_expand<<<(unsigned)n_pad, 256, 0, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
+    lzg_dev_free(ctx, d_col);
+    if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: thermometer code", e);
+    // the TMA descriptor of T: bytes, [n_pad][k_pad], boxes of 128 rows x 128 bytes, 128-byte swizzle
+    const cuuint64_t dims[2] = {(cuuint64_t)k_pad, (cuuint64_t)n_pad}, strides[1] = {(cuuint64_t)k_pad};
+    const cuuint32_t box[2] = {TC_BK, 128}, estr[2] = {1, 1};
+    const CUresult cr = tc_encoder()(reinterpret_cast<CUtensorMap*>(tc->tmap), CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, tc->d_T, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) {
+        lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: cuTensorMapEncodeTiled");
+        return -LZG_ERR_CUDA;
+    }
+    e = cudaFuncSetAttribute(k_tc_distance, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+    if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: shared memory", e);
+    tc->k_pad = (int)k_pad, tc->n_pad = (int)n_pad;
+    tc->usable = 1;
+    return 1;
+}
+
+int lzg_distance_tc_prepare(lzg_ctx* ctx, lzg_profiles* p) {
+    const int r = lzg_distance_tc_prepare_begin(ctx, p);
+    return r == 2 ? lzg_distance_tc_prepare_finish(ctx, p) : r;
+}
+
+// Tiles of the row blocks (128 rows, = the tile rows of k_zcnt_distance) that `shard` owns in [row_lo, row_hi), into the whole
+// matrix d_D or into the row blocks of d_row_base.  owner(r): the deal of lzg_distance.cu (pairs (r, R-1-r) or snake order).
+int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int own_mode, int row_lo, int row_hi, int32_t* d_D, int32_t* const* d_row_base,
+                        int64_t* pairs_done) {
+    lzg_tc_state* tc = p->tc;
+    const int n = p->n, RB = (n + TC_BM - 1) / TC_BM, CB = (n + TC_BN - 1) / TC_BN;
+    auto owner = [&](int r) { return own_mode == 0 ? std::min(r, RB - 1 - r) % n_shards : lzg_snake_owner(r, n_shards); };
+    std::vector<int> mine;
+    for (int rb = std::max(0, row_lo); rb < std::min(RB, row_hi); rb++)
+        if (owner(rb) == shard) mine.push_back(rb);
+    // bands of 12 of these row blocks, column blocks swept inside a band: the ~148 tiles in flight share 12 row blocks and ~12
+    // column blocks, and run through K side by side -- the operands come from L2, not from DRAM
+    tc->h_tiles.clear();
+    int64_t pairs = 0;
+    for (size_t b0 = 0; b0 < mine.size(); b0 += 12) {
+        const size_t b1 = std::min(mine.size(), b0 + 12);
+        for (int cb = mine[b0] / 2; cb < CB; cb++)
+            for (size_t q = b0; q < b1; q++)
+                if (cb >= mine[q] / 2) tc->h_tiles.push_back(make_int2(mine[q], cb));
+    }
+    for (int rb : mine) {
+        const int64_t i0 = (int64_t)rb * TC_BM, i1 = std::min<int64_t>(n, i0 + TC_BM);
+        pairs += (i1 - i0) * n - (i0 + i1 - 1) * (i1 - i0) / 2;  // sum over the rows of (n - i)
+    }
+    if (pairs_done) *pairs_done = pairs;
+    const int n_tiles = (int)tc->h_tiles.size();
+    if (n_tiles == 0) return LZG_OK;
+    if (n_tiles > tc->tiles_cap) {
+        lzg_dev_free(ctx, tc->d_tiles);
+        tc->d_tiles = nullptr;
+        const int cap = std::max(n_tiles, RB * CB);
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&tc->d_tiles, sizeof(int2) * (size_t)cap));
+        tc->tiles_cap = cap;
+    }
+    LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tc->h_tiles.data(), sizeof(int2) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));
+    CUtensorMap map;
+    memcpy(&map, tc->tmap, sizeof(map));
+    k_tc_distance<<<std::min(n_tiles, ctx->sm_count), 128, TC_SMEM, ctx->stream>>>(map, tc->d_tiles, n_tiles, tc->k_pad / TC_BK, tc->d_s, d_D, d_row_base, n);
+    LZG_LAUNCH_CHECK(ctx);
+    tc->launches++;
+    return LZG_OK;
+}

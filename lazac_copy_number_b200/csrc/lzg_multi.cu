@@ -252,18 +252,32 @@ static int distance_multi_width(lzg_multi* m, const void* host, bool is_i8, int3
         for (int h = 0; h < G; h++)
             if (h != g) LZM_CUDA(m, cudaStreamWaitEvent(c->stream, m->ev_up[h], 0));
     }
+    // per-GPU profile handles for the whole call: the tensor-core path keeps its thermometer code in them.  The range
+    // kernels of all GPUs are queued first, then each GPU's code is laid out and its expansion queued.
+    std::vector<lzg_profiles> profs(G, shape);
+    for (int g = 0; g < G && rc == LZG_OK; g++) {
+        lzg_ctx* c = m->ctx[g];
+        LZM_CUDA(m, cudaSetDevice(c->device));
+        profs[g].ctx = c;
+        profs[g].d = m->d_prof[g];
+        profs[g].d_bytes = (size_t)n_pad * pitch;
+        const int tc = lzg_distance_tc_prepare_begin(c, &profs[g]);
+        if (tc < 0) rc = -tc, m->err = c->err;
+    }
+    for (int g = 0; g < G && rc == LZG_OK; g++) {
+        lzg_ctx* c = m->ctx[g];
+        LZM_CUDA(m, cudaSetDevice(c->device));
+        const int tc = lzg_distance_tc_prepare_finish(c, &profs[g]);
+        if (tc < 0) rc = -tc, m->err = c->err;
+    }
     for (int ph = 0; ph < phases && rc == LZG_OK; ph++) {
         const int ra = std::min(R, (int)((long long)blocks2g * ph / phases) * 2 * G);
         const int rb = ph + 1 == phases ? R : std::min(R, (int)((long long)blocks2g * (ph + 1) / phases) * 2 * G);
         for (int g = 0; g < G && rc == LZG_OK; g++) {
             lzg_ctx* c = m->ctx[g];
             LZM_CUDA(m, cudaSetDevice(c->device));
-            lzg_profiles p = shape;
-            p.ctx = c;
-            p.d = m->d_prof[g];
-            p.d_bytes = (size_t)n_pad * pitch;
             int64_t mine = 0;
-            rc = lzg_distance_run(c, &p, g, G, ra, rb, nullptr, &mine, m->d_table[g], 1);
+            rc = lzg_distance_run(c, &profs[g], g, G, ra, rb, nullptr, &mine, m->d_table[g], 1);
             if (rc != LZG_OK) m->err = c->err;
             pairs += mine;
             LZM_CUDA(m, cudaEventRecord(m->ev_done[g], c->stream));
@@ -288,6 +302,7 @@ static int distance_multi_width(lzg_multi* m, const void* host, bool is_i8, int3
     for (int g = 0; g < G; g++) {
         lzg_ctx* c = m->ctx[g];
         cudaSetDevice(c->device);
+        lzg_distance_tc_free(c, &profs[g]);  // stream-ordered frees behind the last kernel
         cudaError_t e1 = cudaStreamSynchronize(c->stream), e2 = cudaStreamSynchronize(c->copy_stream);
         if (rc == LZG_OK && (e1 != cudaSuccess || e2 != cudaSuccess)) rc = multi_fail(m, LZG_ERR_CUDA, "lzg_distance_matrix_multi", e1 != cudaSuccess ? e1 : e2);
         if (rc == LZG_OK && L > 0 && c->h_pinned[0]) out_of_range = true;

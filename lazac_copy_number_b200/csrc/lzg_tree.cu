@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 
 namespace {
 
@@ -773,26 +774,59 @@ int lzg_tree_apply(lzg_ctx* ctx, lzg_tree* t, int u, int w, int v, int z) {
     return LZG_OK;
 }
 
-static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, int L, int l_pad, int32_t* h_dst, int width) {
-    // convert on the device in row blocks of <= 64 MiB of int32, then copy out
-    const size_t max_ints = (size_t)16 << 20;
-    int block_rows = (int)std::max<size_t>(1, std::min<size_t>(rows, max_ints / std::max(1, L)));
-    int32_t* d_tmp = nullptr;
-    LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&d_tmp, sizeof(int32_t) * (size_t)block_rows * L));
-    for (int r0 = 0; r0 < rows; r0 += block_rows) {
-        int nr = std::min(block_rows, rows - r0);
-        dim3 grid(std::max(1, std::min(64, (L + 255) / 256)), nr);
-        LZG_BY_WIDTH(width, k_unpack_i32<W><<<grid, 256, 0, ctx->stream>>>(d_src + (size_t)r0 * l_pad, d_tmp, L, l_pad));
-        ctx->launches++;
-        cudaError_t e = cudaGetLastError();
-        if (e == cudaSuccess) e = cudaMemcpyAsync(h_dst + (size_t)r0 * L, d_tmp, sizeof(int32_t) * (size_t)nr * L, cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) {
-            lzg_dev_free(ctx, d_tmp);
-            return lzg_fail(ctx, LZG_ERR_CUDA, "interval download", e);
+// Rows of the device format (bytes v + 128, or 16-bit words v + 32768) to the caller's int32 matrix: the narrow values cross
+// PCIe (a quarter or half of the int32 bytes) into two halves of the pinned staging area in turn -- the copy of block k + 1 runs
+// while a few host threads widen block k -- instead of a device-side widening, a pageable int32 copy and a sync per block
+// (98 ms for cfg4's 39 MB of labels in round 1).
+static void widen_rows(const uint8_t* src, size_t src_pitch, int32_t* dst, int rows, int L, int width) {
+    for (int r = 0; r < rows; r++) {
+        const uint8_t* s = src + (size_t)r * src_pitch;
+        int32_t* d = dst + (size_t)r * L;
+        if (width == 1)
+            for (int j = 0; j < L; j++) d[j] = (int32_t)s[j] - LZG_BIAS;
+        else {
+            const uint16_t* s16 = reinterpret_cast<const uint16_t*>(s);
+            for (int j = 0; j < L; j++) d[j] = (int32_t)s16[j] - LZG_BIAS16;
         }
     }
-    lzg_dev_free(ctx, d_tmp);
+}
+
+static int download_bytes_as_i32(lzg_ctx* ctx, const uint8_t* d_src, int rows, int L, int l_pad, int32_t* h_dst, int width) {
+    if (rows <= 0 || L <= 0) return LZG_OK;
+    const size_t row_bytes = ((size_t)L * width + 15) / 16 * 16;  // staged pitch
+    const size_t half = std::max<size_t>((size_t)8 << 20, row_bytes);
+    int rc = lzg_ensure_pinned(ctx, 16 + 2 * half / sizeof(int32_t));
+    if (rc != LZG_OK) return rc;
+    uint8_t* stage[2] = {reinterpret_cast<uint8_t*>(ctx->h_pinned + 16), reinterpret_cast<uint8_t*>(ctx->h_pinned + 16) + half};
+    const int block_rows = (int)std::max<size_t>(1, std::min<size_t>(rows, half / row_bytes));
+    const int n_blocks = (rows + block_rows - 1) / block_rows;
+    auto issue = [&](int k) {
+        const int r0 = k * block_rows, nr = std::min(block_rows, rows - r0);
+        return cudaMemcpy2DAsync(stage[k & 1], row_bytes, d_src + (size_t)r0 * l_pad, l_pad, (size_t)L * width, nr, cudaMemcpyDeviceToHost, ctx->stream);
+    };
+    cudaError_t e = issue(0);
+    const int max_threads = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+    for (int k = 0; k < n_blocks && e == cudaSuccess; k++) {
+        e = cudaStreamSynchronize(ctx->stream);  // block k is in its half
+        if (e == cudaSuccess && k + 1 < n_blocks) e = issue(k + 1);
+        if (e != cudaSuccess) break;
+        const int r0 = k * block_rows, nr = std::min(block_rows, rows - r0);
+        const int n_thr = (size_t)nr * L < ((size_t)1 << 18) ? 1 : std::min(max_threads, nr);
+        if (n_thr == 1) {
+            widen_rows(stage[k & 1], row_bytes, h_dst + (size_t)r0 * L, nr, L, width);
+        } else {
+            std::vector<std::thread> pool;
+            for (int w = 0; w < n_thr; w++) {
+                const int a = (int)((long long)nr * w / n_thr), b = (int)((long long)nr * (w + 1) / n_thr);
+                pool.emplace_back(widen_rows, stage[k & 1] + (size_t)a * row_bytes, row_bytes, h_dst + (size_t)(r0 + a) * L, b - a, L, width);
+            }
+            for (auto& th : pool) th.join();
+        }
+    }
+    if (e != cudaSuccess) {
+        cudaStreamSynchronize(ctx->stream);
+        return lzg_fail(ctx, LZG_ERR_CUDA, "interval download", e);
+    }
     return LZG_OK;
 }
 
