@@ -126,7 +126,7 @@ def measured_peaks():
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
             return json.load(f), "measured (MEASURED_PEAKS.json)"
     except Exception:
-        return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -473,6 +473,7 @@ def climb_section(ctx, name, bp, c0, c1, leaf_row, seed_note, reps, max_moves, p
     import ctypes as C
     ms_score = []
     for _ in range(3):
+        base.set_topology(p0, p1)          # same topology: drops the cached scores so that the pass runs again
         ctx.flush_l2()
         ctx.sync()
         ctx.timer_start()
@@ -674,6 +675,35 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
         dev_ms_max, pairs_total = dev_ms, my_pairs
     assert pairs_total == P, (pairs_total, P)
     value = P * args.steps / (dev_ms_max * 1e-3)
+    # which kernel ran (dispatch by value range), and -- outside the timed region -- the tensor-core kernel's own duration and
+    # the other kernel on the same input
+    path = gp.distance_path()
+    tc_detail, alu_ms = None, None
+    if path["tensor_core"]:
+        os.environ["LZG_TC_TIMING"] = "1"
+        prep, kern, tiles = [], [], 0
+        for _ in range(5):
+            ctx.flush_l2()
+            gp.distance_device_async(d_D.data_ptr(), shard, n_shards)
+            ctx.sync()
+            q = gp.distance_path()
+            prep.append(q.get("prepare_us", 0) / 1e3)
+            kern.append(q.get("kernel_us", 0) / 1e3)
+            tiles = q.get("tiles", 0)
+        del os.environ["LZG_TC_TIMING"]
+        tc_detail = {"prepare_ms": float(np.median(prep)), "kernel_ms": float(np.median(kern)), "tiles": int(tiles), "K": path["K"], "k_pad": path["k_pad"]}
+        if rank == 0 and world == 1:
+            os.environ["LZG_TC"] = "0"
+            q = Profiles(ctx, bp)
+            ts = []
+            for _ in range(4):
+                ctx.flush_l2()
+                ctx.timer_start()
+                q.distance_device_async(d_D.data_ptr(), 0, 1)
+                ts.append(ctx.timer_stop())
+            q.free()
+            del os.environ["LZG_TC"]
+            alu_ms = float(np.median(ts[1:]))
     del d_D
 
     # ---- e2e: host buffers through the C ABI, the WHOLE matrix in one pinned host buffer at the end of every step ----
@@ -730,7 +760,7 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
         achieved = lane_instr / world / (ms_step * 1e-3)  # per GPU
         hbm_bytes = n * L + 4 * n * n
         sad_peak, sad_file, sad_row = microbench_rate("VABSDIFF4")
-        ncu_file = latest("r*_ncu_dist_%s*.txt" % name)
+        ncu_file = latest("r*_ncu_dist_%s%s*.txt" % ("tc_" if tc_detail else "", name)) or latest("r*_ncu_dist_%s*.txt" % name)
         traffic = ncu_dram_bytes(ncu_file)
         line = {
             "metric": "zcnt_cell_pairs_per_sec", "value": value, "unit": "cell-pairs/s", "n_gpus": world,
@@ -753,6 +783,30 @@ def distance_section(ctx, args, name, rank, local, world, peaks, peaks_kind, cpu
                                  "frac": hbm_bytes / world / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_kind": peaks_kind}},
             "wall_s_timed_region": wall,
         }
+        if tc_detail:
+            # the exact tensor-core product: algorithmic operations = 2 x pairs x K (K = summed value range of the positions);
+            # executed = 2 x tiles x 128 x 256 x k_pad (whole tiles along the diagonal, K padded to 128)
+            int8_peak = 2.0 * peaks.get("bf16_tflops", 0.0)     # dense int8 = twice the measured dense bf16 rate (burst: the kernel is timed alone)
+            k_s = tc_detail["kernel_ms"] * 1e-3
+            alg_ops = 2.0 * P * tc_detail["K"] / world
+            exe_ops = 2.0 * tc_detail["tiles"] * 128 * 256 * tc_detail["k_pad"]
+            line["dtype"] = "u8 thermometer code x u8 -> int32 (tcgen05.mma kind::i8), int32 epilogue"
+            line["roofline"] = {
+                "bound": "tensor", "kernel": "k_tc_distance", "achieved": alg_ops / k_s / 1e12 if k_s else None, "peak": int8_peak, "unit": "TOP/s (int8, dense) per GPU",
+                "frac": alg_ops / k_s / 1e12 / int8_peak if k_s and int8_peak else None,
+                "peak_kind": "2 x the measured dense bf16 rate (%s): int8 runs at twice the bf16 rate on sm_100a" % peaks_kind,
+                "kernel_ms": tc_detail["kernel_ms"], "prepare_ms": tc_detail["prepare_ms"],
+                "algorithmic_ops": alg_ops, "executed_ops": exe_ops, "executed_frac": exe_ops / k_s / 1e12 / int8_peak if k_s and int8_peak else None,
+                "K": tc_detail["K"], "k_pad": tc_detail["k_pad"], "K_per_position": tc_detail["K"] / float(L), "tiles": tc_detail["tiles"],
+                "traffic": traffic, "traffic_source": os.path.relpath(ncu_file, ROOT) if ncu_file else None,
+                "note": "ms_per_step (and value) time the whole call: value ranges + thermometer code (prepare_ms) + the product (kernel_ms, CUDA events "
+                        "inside the library around the launch, measured after the timed region); dispatched by value range beside k_zcnt_distance",
+                "hbm": line["roofline"]["hbm"]}
+            if alu_ms:
+                alu_ach = P * (L / 4.0) / (alu_ms * 1e-3)
+                line["roofline"]["k_zcnt_distance_same_input"] = {
+                    "ms": alu_ms, "bound": "int_alu", "achieved": alu_ach / 1e9, "peak": (sad_peak or 0) / 1e9, "frac": alu_ach / sad_peak if sad_peak else None,
+                    "unit": "G lane-instr/s (VABSDIFF4.U8.ACC)", "peak_source": sad_file, "note": "LZG_TC=0: the kernel that runs for wide value ranges"}
         if n1_same:
             line["n1_same_workload"] = n1_same
     if world == 1 and cpu:

@@ -75,7 +75,8 @@ int lzg_profiles_shape(const lzg_profiles* p, int32_t* n_cells, int32_t* n_pos);
 /* Which kernel the whole-matrix distance of these profiles runs on one GPU (decided at the first distance call from
  * the value range): info[0] = 1 the exact tensor-core product (thermometer code, tcgen05 kind::i8), 0 the VABSDIFF4
  * kernel; info[1] = K = sum over positions of (max - min); info[2] = padded code width; info[3] = tensor-core
- * launches so far.  int64 info[4]. */
+ * launches so far; with LZG_TC_TIMING=1 in the environment info[4] / info[5] = microseconds of the code's preparation
+ * and of the last product launch (CUDA events; call lzg_sync first), else 0; info[6] = tiles run.  int64 info[8]. */
 int lzg_profiles_distance_path(const lzg_profiles* p, int64_t* info);
 
 /* ---- all-pairs ZCNT distance: replaces the pair loop of build_distance_matrix,

@@ -204,9 +204,12 @@ class Profiles:
 
     def distance_path(self):
         """{'tensor_core': bool, 'K': summed value range, 'k_pad': code width, 'launches': k_tc_distance launches so far}."""
-        info = (C.c_int64 * 4)()
+        info = (C.c_int64 * 8)()
         self.ctx.check(self.ctx.lib.lzg_profiles_distance_path(self.h, info))
-        return {"tensor_core": bool(info[0]), "K": int(info[1]), "k_pad": int(info[2]), "launches": int(info[3])}
+        out = {"tensor_core": bool(info[0]), "K": int(info[1]), "k_pad": int(info[2]), "launches": int(info[3])}
+        if info[4] or info[5]:
+            out.update(prepare_us=int(info[4]), kernel_us=int(info[5]), tiles=int(info[6]))
+        return out
 
     def distance_noalloc(self, d_ptr):
         """lzg_distance_matrix_noalloc: the whole matrix to raw device pointer d_ptr (N*N int32) without any allocation --

@@ -291,11 +291,13 @@ int lzg_profiles_free(lzg_profiles* p) {
 
 // Which kernel lzg_distance_* runs for these profiles' whole matrix on one GPU: info[0] = 1 the tensor-core product
 // (k_tc_distance), 0 k_zcnt_distance; info[1] = K, the summed value range of the positions (0 before the first distance call
-// and for the 16-bit format); info[2] = the thermometer code's padded width; info[3] = k_tc_distance launches so far.
+// and for the 16-bit format); info[2] = the thermometer code's padded width; info[3] = k_tc_distance launches so far;
+// info[4], info[5] = microseconds of the preparation and of the last k_tc_distance launch (LZG_TC_TIMING=1, else 0); info[6] = tiles run.
 int lzg_profiles_distance_path(const lzg_profiles* p, int64_t* info) {
     if (!p || !info) return LZG_ERR_ARG;
     info[0] = info[1] = info[2] = info[3] = 0;
     if (p->tc) info[0] = p->tc->usable, info[1] = p->tc->K, info[2] = p->tc->k_pad, info[3] = p->tc->launches;
+    lzg_distance_tc_timing(p, info);
     return LZG_OK;
 }
 

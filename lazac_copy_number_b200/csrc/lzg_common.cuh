@@ -90,6 +90,8 @@ struct lzg_tc_state {
     std::vector<uint32_t> col;      // host copy of the column table
     alignas(64) unsigned char tmap[128];  // CUtensorMap of T
     int64_t launches = 0;           // k_tc_distance launches so far (tests, bench)
+    int64_t tiles_run = 0;          // tiles of those launches
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // LZG_TC_TIMING=1: around the preparation and around the last k_tc_distance
 };
 int lzg_distance_tc_prepare(lzg_ctx* ctx, lzg_profiles* p);  // 1: usable, 0: not for these profiles, < 0: error
 int lzg_distance_tc_prepare_begin(lzg_ctx* ctx, lzg_profiles* p);   // 2: queued, call _finish
@@ -97,6 +99,7 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p);
 int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, int own_mode, int row_lo, int row_hi, int32_t* d_D, int32_t* const* d_row_base,
                         int64_t* pairs_done);
 void lzg_distance_tc_free(lzg_ctx* ctx, lzg_profiles* p);
+void lzg_distance_tc_timing(const lzg_profiles* p, int64_t* info);
 
 int lzg_fail(lzg_ctx* ctx, int status, const char* what, cudaError_t e = cudaSuccess);
 

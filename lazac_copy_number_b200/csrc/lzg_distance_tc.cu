@@ -12,7 +12,8 @@
 //
 // Kernels: k_tc_colrange (lo_p, w_p), k_tc_expand (T and s), k_tc_distance: persistent CTAs over 128 x 256 tiles of the upper
 // triangle, operands by TMA (128-byte swizzle, 4 stages of 48 KB) issued by one thread, tcgen05.mma (M 128, N 256, K 32) issued
-// by one thread into 256 TMEM columns, epilogue of all four warps: tcgen05.ld -> s_i + s_j - 2 g -> D[i][j] and the mirror D[j][i].
+// by one thread into two alternating accumulators of 256 TMEM columns, four epilogue warps: tcgen05.ld -> s_i + s_j - 2 g ->
+// D[i][j] and the mirror D[j][i] while the next tile's product runs.
 #include <cuda.h>
 
 #include <algorithm>
@@ -32,58 +33,89 @@ constexpr int TC_TMEM_COLS = 256;
 
 // ---- per-position range over the cells: lo_p (biased byte) and hi_p ------------------------------------------------
 __global__ void k_tc_colrange(const uint8_t* __restrict__ d, int n, int pitch, int L, unsigned* __restrict__ lo_hi) {
-    // one thread per group of four positions, rows strided over blockIdx.y; lo_hi[2p] = 255 - lo, lo_hi[2p+1] = hi, both merged with atomicMax
+    // one thread per group of four positions, rows strided over blockIdx.y (eight loads in flight); lo_hi[2p] = 255 - lo,
+    // lo_hi[2p+1] = hi, both merged with atomicMax
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (4 * g >= L) return;
-    unsigned lo[4] = {255, 255, 255, 255}, hi[4] = {0, 0, 0, 0};
-    for (int i = blockIdx.y; i < n; i += gridDim.y) {
-        const uint32_t w = *reinterpret_cast<const uint32_t*>(d + (size_t)i * pitch + 4 * g);
+    uint32_t lo4 = 0xffffffffu, hi4 = 0u;  // per-byte minima / maxima (__vminu4 / __vmaxu4)
+    const uint8_t* col = d + 4 * (size_t)g;
+    int i = blockIdx.y;
+    for (; i + 7 * (int)gridDim.y < n; i += 8 * gridDim.y) {
+        uint32_t w[8];
 #pragma unroll
-        for (int e = 0; e < 4; e++) {
-            const unsigned v = (w >> (8 * e)) & 255u;
-            lo[e] = min(lo[e], v), hi[e] = max(hi[e], v);
-        }
+        for (int u = 0; u < 8; u++) w[u] = __ldg(reinterpret_cast<const uint32_t*>(col + (size_t)(i + u * gridDim.y) * pitch));
+#pragma unroll
+        for (int u = 0; u < 8; u++) lo4 = __vminu4(lo4, w[u]), hi4 = __vmaxu4(hi4, w[u]);
+    }
+    for (; i < n; i += gridDim.y) {
+        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(col + (size_t)i * pitch));
+        lo4 = __vminu4(lo4, w), hi4 = __vmaxu4(hi4, w);
     }
 #pragma unroll
     for (int e = 0; e < 4; e++)
-        if (4 * g + e < L) atomicMax(lo_hi + 2 * (4 * g + e), 255u - lo[e]), atomicMax(lo_hi + 2 * (4 * g + e) + 1, hi[e]);
+        if (4 * g + e < L) atomicMax(lo_hi + 2 * (4 * g + e), 255u - ((lo4 >> (8 * e)) & 255u)), atomicMax(lo_hi + 2 * (4 * g + e) + 1, (hi4 >> (8 * e)) & 255u);
 }
 
 // ---- T and its row sums ------------------------------------------------------------------------------------------
 // col[c] = (position << 9) | threshold: T[i][c] = [byte(i, position) >= threshold]; threshold 256 for the padding columns.
+// A CTA codes R consecutive rows: the rows are staged in shared memory (the byte gathers of neighbouring columns hit
+// neighbouring positions) and every column-table entry is fetched once for the R rows.  R = 0: rows read from global memory
+// (rows too long for shared memory).
+template <int R>
 __global__ void __launch_bounds__(256) k_tc_expand(const uint8_t* __restrict__ d, int n, int pitch, const uint32_t* __restrict__ col, int k_pad,
                                                     uint8_t* __restrict__ T, int32_t* __restrict__ s) {
-    const int i = blockIdx.x;  // rows n .. n_pad-1 are zero rows
-    const uint8_t* row = d + (size_t)i * pitch;
-    int sum = 0;
+    constexpr int RR = R > 0 ? R : 1;
+    extern __shared__ __align__(16) uint8_t x_rows[];
+    const int i0 = blockIdx.x * RR;  // rows n .. n_pad-1 are zero rows
+    const uint8_t* rows[RR];
+#pragma unroll
+    for (int r = 0; r < RR; r++) rows[r] = R > 0 ? x_rows + (size_t)r * pitch : d + (size_t)(i0 + r) * pitch;
+    if (R > 0) {
+        for (int q = threadIdx.x; q < RR * (pitch / 16); q += blockDim.x) {
+            const int r = q / (pitch / 16), c = q - r * (pitch / 16);
+            reinterpret_cast<uint4*>(x_rows)[q] = i0 + r < n ? __ldg(reinterpret_cast<const uint4*>(d + (size_t)(i0 + r) * pitch) + c) : make_uint4(0, 0, 0, 0);
+        }
+        __syncthreads();
+    }
+    int sum[RR];
+#pragma unroll
+    for (int r = 0; r < RR; r++) sum[r] = 0;
     for (int g = threadIdx.x; 16 * g < k_pad; g += blockDim.x) {
-        uint32_t out[4] = {0, 0, 0, 0};
-        if (i < n) {
-            const uint4* cp = reinterpret_cast<const uint4*>(col + 16 * g);
+        uint32_t out[RR][4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const uint4 c4 = __ldg(cp + q);
-                const uint32_t cc[4] = {c4.x, c4.y, c4.z, c4.w};
+        for (int r = 0; r < RR; r++) out[r][0] = out[r][1] = out[r][2] = out[r][3] = 0;
+        const uint4* cp = reinterpret_cast<const uint4*>(col + 16 * g);
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const unsigned thr = cc[e] & 511u;
-                    const unsigned bit = thr < 256u && row[cc[e] >> 9] >= thr ? 1u : 0u;
-                    out[q] |= bit << (8 * e);
-                    sum += (int)bit;
+        for (int q = 0; q < 4; q++) {
+            const uint4 c4 = __ldg(cp + q);
+            const uint32_t cc[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const unsigned thr = cc[e] & 511u, pos = cc[e] >> 9;
+#pragma unroll
+                for (int r = 0; r < RR; r++) {
+                    const unsigned bit = thr < 256u && i0 + r < n && rows[r][pos] >= thr ? 1u : 0u;
+                    out[r][q] |= bit << (8 * e);
+                    sum[r] += (int)bit;
                 }
             }
         }
-        *reinterpret_cast<uint4*>(T + (size_t)i * k_pad + 16 * g) = make_uint4(out[0], out[1], out[2], out[3]);
-    }
-    __shared__ int s_sum[8];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = sum;
+        for (int r = 0; r < RR; r++) *reinterpret_cast<uint4*>(T + (size_t)(i0 + r) * k_pad + 16 * g) = make_uint4(out[r][0], out[r][1], out[r][2], out[r][3]);
+    }
+    __shared__ int s_sum[RR][8];
+#pragma unroll
+    for (int r = 0; r < RR; r++) {
+        int v = sum[r];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) s_sum[r][threadIdx.x >> 5] = v;
+    }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < RR) {
         int t = 0;
-        for (int w = 0; w < 8; w++) t += s_sum[w];
-        s[i] = t;
+        for (int w = 0; w < 8; w++) t += s_sum[threadIdx.x][w];
+        s[i0 + threadIdx.x] = t;
     }
 }
 
@@ -149,26 +181,29 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 }
 
 // ---- the product and the epilogue --------------------------------------------------------------------------------------
-// tiles[t] = (row block of 128, column block of 256); every tile runs the whole K.  Thread 0 is the TMA producer, thread 32 the
-// MMA issuer; then all four warps read their 32 TMEM lanes (= tile rows) and write D.  Mirrors D[j][i] are written only for rows
-// j beyond this tile's row block, so a finished group of row blocks never changes again (lzg_distance_matrix copies it out
-// while later groups compute).
-__global__ void __launch_bounds__(128, 1)
+// tiles[t] = (row block of 128, column block of 256); every tile runs the whole K.  Warp 0 (one lane) is the TMA producer, warp 1
+// (one lane) the MMA issuer, warps 2 .. 5 the epilogue: each reads its 32 TMEM lanes (= tile rows) and writes D.  Two
+// accumulators of 256 TMEM columns alternate, so the product of the next tile runs while this one is written out, and the
+// producer keeps the four stages full across tile boundaries.  Mirrors D[j][i] are written only for rows j beyond this tile's
+// row block, so a finished group of row blocks never changes again (lzg_distance_matrix copies it out while later groups compute).
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+
+__global__ void __launch_bounds__(192, 1)
 k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__ tiles, int n_tiles, int k_blocks, const int32_t* __restrict__ s,
               int32_t* __restrict__ D, int32_t* const* __restrict__ row_base, int n) {
     extern __shared__ uint8_t tc_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t smem_base = smem_u32(smem);
-    const uint32_t bar_full = smem_base + TC_STAGES * TC_STAGE, bar_empty = bar_full + 8 * TC_STAGES, bar_tmem = bar_empty + 8 * TC_STAGES;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_STAGES * TC_STAGE + 8 * (2 * TC_STAGES + 1));
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t bar_full = smem_base + TC_STAGES * TC_STAGE, bar_empty = bar_full + 8 * TC_STAGES, bar_tfull = bar_empty + 8 * TC_STAGES, bar_tempty = bar_tfull + 16;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_STAGES * TC_STAGE + 8 * (2 * TC_STAGES + 4));
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int q = 0; q < TC_STAGES; q++) mbar_init(bar_full + 8 * q, 1), mbar_init(bar_empty + 8 * q, 1);
-        mbar_init(bar_tmem, 1);
+        for (int q = 0; q < 2; q++) mbar_init(bar_tfull + 8 * q, 1), mbar_init(bar_tempty + 8 * q, 4);  // one arrival per epilogue warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * TC_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -177,79 +212,93 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
     const uint32_t tmem = *tmem_slot;
     // instruction descriptor: D int32, A and B unsigned 8-bit, both K-major, N = 256, M = 128
     constexpr uint32_t idesc = (2u << 4) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-    uint32_t it = 0, tile_parity = 0;  // k-blocks issued so far (stage = it % STAGES, phase = it / STAGES & 1)
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const int2 tile = tiles[t];
-        const int row0 = tile.x * TC_BM, col0 = tile.y * TC_BN;
-        if (tid == 0) {
-            uint32_t q = it;
-            for (int kb = 0; kb < k_blocks; kb++, q++) {
-                const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
-                mbar_wait(bar_empty + 8 * st, ph ^ 1u);
-                mbar_expect_tx(bar_full + 8 * st, TC_STAGE);
-                const uint32_t a = smem_base + st * TC_STAGE, b = a + TC_STAGE_A;
-                tma_load_2d(a, &tmap, kb * TC_BK, row0, bar_full + 8 * st);
-                tma_load_2d(b, &tmap, kb * TC_BK, col0, bar_full + 8 * st);
-                tma_load_2d(b + TC_STAGE_A, &tmap, kb * TC_BK, col0 + 128, bar_full + 8 * st);
-            }
-        } else if (tid == 32) {
-            uint32_t q = it;
-            for (int kb = 0; kb < k_blocks; kb++, q++) {
-                const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
-                mbar_wait(bar_full + 8 * st, ph);
-                tc_fence_after();
-                const uint32_t a = smem_base + st * TC_STAGE, b = a + TC_STAGE_A;
-#pragma unroll
-                for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
-                    tc_mma_i8(tmem, tc_smem_desc(a + k * TC_UMMA_K), tc_smem_desc(b + k * TC_UMMA_K), idesc, (kb | k) != 0);
-                tc_commit(bar_empty + 8 * st);  // the stage is free once these MMAs have read it
-            }
-            tc_commit(bar_tmem);  // the accumulator is complete
-        }
-        it += k_blocks;
-        __syncwarp();
-        mbar_wait(bar_tmem, tile_parity);
-        tile_parity ^= 1u;
-        tc_fence_after();
-        // ---- epilogue: thread = tile row i (TMEM lane), 32 columns at a time
-        const int i = row0 + tid;
-        const int si = i < n ? s[i] : 0;
-        // row_base (several GPUs, lzg_multi.cu): one pointer per block of 128 output rows instead of the one matrix
-        int32_t* drow = row_base ? row_base[tile.x] + (size_t)tid * n : D + (size_t)i * n;
-        const bool vec = (n & 3) == 0;
-        const int mirror_from = row0 + TC_BM;  // rows below this tile's row block only
-        for (int c = 0; c < TC_BN; c += 32) {
-            uint32_t g[32];
-            tc_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c, g);
-            const int j0 = col0 + c;
-            if (j0 >= n) continue;  // uniform over the CTA
-            int v[32];
-#pragma unroll
-            for (int e = 0; e < 32; e++) v[e] = si + (j0 + e < n ? __ldg(s + j0 + e) : 0) - 2 * (int)g[e];
-            if (i < n) {
-                if (vec && j0 + 32 <= n) {
-#pragma unroll
-                    for (int e = 0; e < 32; e += 4) *reinterpret_cast<int4*>(drow + j0 + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 32; e++)
-                        if (j0 + e < n) drow[j0 + e] = v[e];
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t q = 0;  // k-blocks issued so far (stage = q % STAGES, phase = q / STAGES & 1)
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int2 tile = tiles[t];
+                const int row0 = tile.x * TC_BM, col0 = tile.y * TC_BN;
+                for (int kb = 0; kb < k_blocks; kb++, q++) {
+                    const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
+                    mbar_wait(bar_empty + 8 * st, ph ^ 1u);
+                    mbar_expect_tx(bar_full + 8 * st, TC_STAGE);
+                    const uint32_t a = smem_base + st * TC_STAGE, b = a + TC_STAGE_A;
+                    tma_load_2d(a, &tmap, kb * TC_BK, row0, bar_full + 8 * st);
+                    tma_load_2d(b, &tmap, kb * TC_BK, col0, bar_full + 8 * st);
+                    tma_load_2d(b + TC_STAGE_A, &tmap, kb * TC_BK, col0 + 128, bar_full + 8 * st);
                 }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            uint32_t q = 0, lt = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, lt++) {
+                const uint32_t acc = lt & 1u;
+                mbar_wait(bar_tempty + 8 * acc, ((lt >> 1) & 1u) ^ 1u);  // the epilogue has drained this accumulator
+                tc_fence_after();
+                for (int kb = 0; kb < k_blocks; kb++, q++) {
+                    const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
+                    mbar_wait(bar_full + 8 * st, ph);
+                    tc_fence_after();
+                    const uint32_t a = smem_base + st * TC_STAGE, b = a + TC_STAGE_A;
 #pragma unroll
-                for (int e = 0; e < 32; e++) {
-                    const int j = j0 + e;
-                    if (j >= mirror_from && j < n) {  // lanes = consecutive i: coalesced
-                        if (row_base) row_base[j >> 7][(size_t)(j & 127) * n + i] = v[e];
-                        else D[(size_t)j * n + i] = v[e];
+                    for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
+                        tc_mma_i8(tmem + acc * TC_TMEM_COLS, tc_smem_desc(a + k * TC_UMMA_K), tc_smem_desc(b + k * TC_UMMA_K), idesc, (kb | k) != 0);
+                    tc_commit(bar_empty + 8 * st);  // the stage is free once these MMAs have read it
+                }
+                tc_commit(bar_tfull + 8 * acc);  // the accumulator is complete
+            }
+        }
+    } else {
+        const int quad = warp & 3, trow = quad * 32 + lane;  // a warp reads the TMEM lanes of its quadrant
+        const bool vec = (n & 3) == 0;
+        uint32_t lt = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, lt++) {
+            const int2 tile = tiles[t];
+            const int row0 = tile.x * TC_BM, col0 = tile.y * TC_BN;
+            const uint32_t acc = lt & 1u;
+            const int i = row0 + trow;
+            const int si = i < n ? __ldg(s + i) : 0;
+            // row_base (several GPUs, lzg_multi.cu): one pointer per block of 128 output rows instead of the one matrix
+            int32_t* drow = row_base ? row_base[tile.x] + (size_t)trow * n : D + (size_t)i * n;
+            const int mirror_from = row0 + TC_BM;  // rows below this tile's row block only
+            mbar_wait(bar_tfull + 8 * acc, (lt >> 1) & 1u);
+            tc_fence_after();
+            for (int c = 0; c < TC_BN; c += 32) {
+                const int j0 = col0 + c;
+                if (j0 >= n) break;  // uniform over the CTA
+                uint32_t g[32];
+                tc_ld32(tmem + acc * TC_TMEM_COLS + ((uint32_t)(quad * 32) << 16) + c, g);
+                int v[32];
+#pragma unroll
+                for (int e = 0; e < 32; e++) v[e] = si + (j0 + e < n ? __ldg(s + j0 + e) : 0) - 2 * (int)g[e];
+                if (i < n) {
+                    if (vec && j0 + 32 <= n) {
+#pragma unroll
+                        for (int e = 0; e < 32; e += 4) *reinterpret_cast<int4*>(drow + j0 + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 32; e++)
+                            if (j0 + e < n) drow[j0 + e] = v[e];
+                    }
+#pragma unroll
+                    for (int e = 0; e < 32; e++) {
+                        const int j = j0 + e;
+                        if (j >= mirror_from && j < n) {  // lanes = consecutive i: coalesced
+                            if (row_base) row_base[j >> 7][(size_t)(j & 127) * n + i] = v[e];
+                            else D[(size_t)j * n + i] = v[e];
+                        }
                     }
                 }
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);  // this warp's lanes of the accumulator are read
         }
-        tc_fence_before();
-        __syncthreads();  // every warp is done with the accumulator before the next tile's first MMA overwrites it
-        tc_fence_after();
     }
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_TMEM_COLS) : "memory");
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * TC_TMEM_COLS) : "memory");
 }
 
 }  // namespace
@@ -273,6 +322,8 @@ static tc_encode_fn tc_encoder() {
 
 void lzg_distance_tc_free(lzg_ctx* ctx, lzg_profiles* p) {
     if (!p->tc) return;
+    for (cudaEvent_t ev : p->tc->ev)
+        if (ev) cudaEventDestroy(ev);
     lzg_dev_free(ctx, p->tc->d_T);
     lzg_dev_free(ctx, p->tc->d_s);
     lzg_dev_free(ctx, p->tc->d_tiles);
@@ -296,13 +347,18 @@ int lzg_distance_tc_prepare_begin(lzg_ctx* ctx, lzg_profiles* p) {
     const int n = p->n, L = p->L;
     int rc = lzg_ensure_pinned(ctx, 16 + 2 * (size_t)L);
     if (rc != LZG_OK) return -rc;
+    if (getenv("LZG_TC_TIMING") && atoi(getenv("LZG_TC_TIMING"))) {
+        for (cudaEvent_t& ev : tc->ev) cudaEventCreate(&ev);
+        cudaEventRecord(tc->ev[0], ctx->stream);
+    }
     unsigned* d_lohi = nullptr;
     cudaError_t e = lzg_dev_alloc(ctx, (void**)&d_lohi, sizeof(unsigned) * 2 * (size_t)L);
     if (e == cudaSuccess) e = cudaMemsetAsync(d_lohi, 0, sizeof(unsigned) * 2 * (size_t)L, ctx->stream);
     if (e == cudaSuccess) {
         const int groups = (L + 3) / 4;
-        k_tc_colrange<<<dim3((groups + 127) / 128, std::max(1, std::min(n, 4 * ctx->sm_count * 128 / std::max(128, groups)))), 128, 0, ctx->stream>>>(p->d, n, p->pitch, L,
-                                                                                                                                                    d_lohi);
+        // about 16 warps per SM in flight, every thread eight rows at a time
+        const int slabs = std::max(1, std::min((n + 7) / 8, 16 * 32 * ctx->sm_count / std::max(128, groups)));
+        k_tc_colrange<<<dim3((groups + 127) / 128, slabs), 128, 0, ctx->stream>>>(p->d, n, p->pitch, L, d_lohi);
         ctx->launches++;
         e = cudaGetLastError();
     }
@@ -346,7 +402,15 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_s, sizeof(int32_t) * (size_t)n_pad);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_col, tc->col.data(), sizeof(uint32_t) * (size_t)k_pad, cudaMemcpyHostToDevice, ctx->stream);  // pageable: staged before the call returns
     if (e == cudaSuccess) {
-        k_tc_expand<<<(unsigned)n_pad, 256, 0, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
+        if (4 * (size_t)p->pitch <= 96 * 1024) {  // n_pad is a multiple of 256: whole groups of four rows
+            if (4 * (size_t)p->pitch > 48 * 1024) cudaFuncSetAttribute(k_tc_expand<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * p->pitch);
+            k_tc_expand<4><<<(unsigned)(n_pad / 4), 256, 4 * (size_t)p->pitch, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
+        } else if ((size_t)p->pitch <= 200 * 1024) {
+            cudaFuncSetAttribute(k_tc_expand<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->pitch);
+            k_tc_expand<1><<<(unsigned)n_pad, 256, (size_t)p->pitch, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
+        } else {
+            k_tc_expand<0><<<(unsigned)n_pad, 256, 0, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
+        }
         ctx->launches++;
         e = cudaGetLastError();
     }
@@ -365,6 +429,7 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: shared memory", e);
     tc->k_pad = (int)k_pad, tc->n_pad = (int)n_pad;
     tc->usable = 1;
+    if (tc->ev[1]) cudaEventRecord(tc->ev[1], ctx->stream);
     return 1;
 }
 
@@ -410,8 +475,24 @@ int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, 
     LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tc->h_tiles.data(), sizeof(int2) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));
     CUtensorMap map;
     memcpy(&map, tc->tmap, sizeof(map));
-    k_tc_distance<<<std::min(n_tiles, ctx->sm_count), 128, TC_SMEM, ctx->stream>>>(map, tc->d_tiles, n_tiles, tc->k_pad / TC_BK, tc->d_s, d_D, d_row_base, n);
+    if (tc->ev[2]) cudaEventRecord(tc->ev[2], ctx->stream);
+    k_tc_distance<<<std::min(n_tiles, ctx->sm_count), 192, TC_SMEM, ctx->stream>>>(map, tc->d_tiles, n_tiles, tc->k_pad / TC_BK, tc->d_s, d_D, d_row_base, n);
     LZG_LAUNCH_CHECK(ctx);
+    if (tc->ev[3]) cudaEventRecord(tc->ev[3], ctx->stream);
     tc->launches++;
+    tc->tiles_run += n_tiles;
     return LZG_OK;
+}
+
+// info[4], info[5]: microseconds of the preparation (range kernel, host layout, expansion) and of the last k_tc_distance launch,
+// measured with events on the stream when LZG_TC_TIMING=1 (the stream must be idle); info[6] = tiles run so far.
+void lzg_distance_tc_timing(const lzg_profiles* p, int64_t* info) {
+    info[4] = info[5] = info[6] = 0;
+    const lzg_tc_state* tc = p->tc;
+    if (!tc) return;
+    info[6] = tc->tiles_run;
+    float ms = 0.0f;
+    if (tc->ev[1] && cudaEventElapsedTime(&ms, tc->ev[0], tc->ev[1]) == cudaSuccess) info[4] = (int64_t)(ms * 1e3f);
+    if (tc->ev[3] && tc->launches && cudaEventElapsedTime(&ms, tc->ev[2], tc->ev[3]) == cudaSuccess) info[5] = (int64_t)(ms * 1e3f);
+    cudaGetLastError();
 }

@@ -62,3 +62,31 @@ def test_multi_gpu_equals_one_gpu(ctx, port, n, L):
             assert D.tobytes() == one.tobytes(), devices
     if n <= 1000:
         assert np.array_equal(one, port.distance_matrix(bp.astype(np.int32)))
+
+
+def test_tensor_core_path_through_the_row_table(ctx, monkeypatch):
+    """Narrow value ranges and enough tiles: every GPU of lzg_distance_matrix_multi runs k_tc_distance on its row blocks (direct
+    rows and mirrors through the row-block table, peers included); same bytes as k_zcnt_distance on one GPU."""
+    n, L = 3300, 500
+    bp = synth.random_bp(n, L, seed=17, lo=-2, hi=2, density=0.06).astype(np.int8)
+    monkeypatch.setenv("LZG_TC", "0")
+    prof = Profiles(ctx, bp)
+    want = prof.distance_matrix()
+    prof.free()
+    monkeypatch.delenv("LZG_TC")
+    prof = Profiles(ctx, bp)
+    one = prof.distance_matrix()
+    assert prof.distance_path()["tensor_core"]
+    prof.free()
+    assert one.tobytes() == want.tobytes()
+    g = n_gpus()
+    for devices in ([0], [0, 1], list(range(g))):
+        if len(devices) > g:
+            continue
+        with MultiContext(devices) as m:
+            for phases in ("1", "3"):
+                monkeypatch.setenv("LZG_MULTI_PHASES", phases)
+                D = np.full((n, n), -1, np.int32)
+                _, pairs = m.distance_matrix(bp, out=D)
+                assert pairs == n * (n + 1) // 2
+                assert D.tobytes() == want.tobytes(), (devices, phases)
