@@ -87,7 +87,7 @@ struct lzg_tc_state {
     int2* d_tiles = nullptr;        // (row block of 128, column block of 256) of the current launch
     int tiles_cap = 0;
     std::vector<int2> h_tiles;
-    std::vector<uint32_t> col;      // host copy of the column table
+    std::vector<uint4> table;       // host copy of the word table of k_tc_expand
     alignas(64) unsigned char tmap[128];  // CUtensorMap of T
     int64_t launches = 0;           // k_tc_distance launches so far (tests, bench)
     int64_t tiles_run = 0;          // tiles of those launches

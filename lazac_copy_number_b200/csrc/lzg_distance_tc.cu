@@ -57,62 +57,53 @@ __global__ void k_tc_colrange(const uint8_t* __restrict__ d, int n, int pitch, i
 }
 
 // ---- T and its row sums ------------------------------------------------------------------------------------------
-// col[c] = (position << 9) | threshold: T[i][c] = [byte(i, position) >= threshold]; threshold 256 for the padding columns.
-// A CTA codes R consecutive rows: the rows are staged in shared memory (the byte gathers of neighbouring columns hit
-// neighbouring positions) and every column-table entry is fetched once for the R rows.  R = 0: rows read from global memory
-// (rows too long for shared memory).
+// The host lays the columns out four to an output word such that the (up to four) positions of a word lie within eight bytes
+// of a 4-byte-aligned base (it starts a new word, leaving never-set columns, where they do not); a word's table entry is
+// {base word index, PRMT selector, four threshold bytes, 0x01 per valid column}.  T[i][4 w + e] = [byte(i, position) >= threshold]:
+// two 32-bit loads of the row (staged in shared memory), one PRMT gathers the four bytes, a SWAR compare makes the four
+// results.  A CTA codes R consecutive rows with every table entry fetched once.
 template <int R>
-__global__ void __launch_bounds__(256) k_tc_expand(const uint8_t* __restrict__ d, int n, int pitch, const uint32_t* __restrict__ col, int k_pad,
+__global__ void __launch_bounds__(256) k_tc_expand(const uint8_t* __restrict__ d, int n, int pitch, const uint4* __restrict__ table, int k_pad,
                                                     uint8_t* __restrict__ T, int32_t* __restrict__ s) {
-    constexpr int RR = R > 0 ? R : 1;
-    extern __shared__ __align__(16) uint8_t x_rows[];
-    const int i0 = blockIdx.x * RR;  // rows n .. n_pad-1 are zero rows
-    const uint8_t* rows[RR];
-#pragma unroll
-    for (int r = 0; r < RR; r++) rows[r] = R > 0 ? x_rows + (size_t)r * pitch : d + (size_t)(i0 + r) * pitch;
-    if (R > 0) {
-        for (int q = threadIdx.x; q < RR * (pitch / 16); q += blockDim.x) {
-            const int r = q / (pitch / 16), c = q - r * (pitch / 16);
-            reinterpret_cast<uint4*>(x_rows)[q] = i0 + r < n ? __ldg(reinterpret_cast<const uint4*>(d + (size_t)(i0 + r) * pitch) + c) : make_uint4(0, 0, 0, 0);
-        }
-        __syncthreads();
+    extern __shared__ __align__(16) uint8_t x_rows[];  // R rows of `pitch` bytes + 16
+    const int i0 = blockIdx.x * R;                      // rows n .. n_pad-1 are zero rows
+    for (int q = threadIdx.x; q < R * (pitch / 16) + 1; q += blockDim.x) {
+        const int r = q / (pitch / 16), c = q - r * (pitch / 16);
+        reinterpret_cast<uint4*>(x_rows)[q] = r < R && i0 + r < n ? __ldg(reinterpret_cast<const uint4*>(d + (size_t)(i0 + r) * pitch) + c) : make_uint4(0, 0, 0, 0);
     }
-    int sum[RR];
+    __syncthreads();
+    int sum[R];
 #pragma unroll
-    for (int r = 0; r < RR; r++) sum[r] = 0;
+    for (int r = 0; r < R; r++) sum[r] = 0;
     for (int g = threadIdx.x; 16 * g < k_pad; g += blockDim.x) {
-        uint32_t out[RR][4];
+        uint4 ent[4];
 #pragma unroll
-        for (int r = 0; r < RR; r++) out[r][0] = out[r][1] = out[r][2] = out[r][3] = 0;
-        const uint4* cp = reinterpret_cast<const uint4*>(col + 16 * g);
+        for (int q = 0; q < 4; q++) ent[q] = __ldg(table + 4 * g + q);
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-            const uint4 c4 = __ldg(cp + q);
-            const uint32_t cc[4] = {c4.x, c4.y, c4.z, c4.w};
+        for (int r = 0; r < R; r++) {
+            const uint32_t* roww = reinterpret_cast<const uint32_t*>(x_rows + (size_t)r * pitch);
+            uint32_t out[4];
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
-                const unsigned thr = cc[e] & 511u, pos = cc[e] >> 9;
-#pragma unroll
-                for (int r = 0; r < RR; r++) {
-                    const unsigned bit = thr < 256u && i0 + r < n && rows[r][pos] >= thr ? 1u : 0u;
-                    out[r][q] |= bit << (8 * e);
-                    sum[r] += (int)bit;
-                }
+            for (int q = 0; q < 4; q++) {
+                const uint32_t x = __byte_perm(roww[ent[q].x], roww[ent[q].x + 1], ent[q].y), y = ent[q].z;
+                const uint32_t dlt = (x | 0x80808080u) - (y & 0x7f7f7f7fu);      // bit 7 of a byte: low seven bits of x >= those of y
+                const uint32_t ge = (x & ~y) | (~(x ^ y) & dlt);                  // bit 7 of a byte: x >= y
+                out[q] = (ge >> 7) & ent[q].w;
+                sum[r] += __popc(out[q]);
             }
+            *reinterpret_cast<uint4*>(T + (size_t)(i0 + r) * k_pad + 16 * g) = make_uint4(out[0], out[1], out[2], out[3]);
         }
-#pragma unroll
-        for (int r = 0; r < RR; r++) *reinterpret_cast<uint4*>(T + (size_t)(i0 + r) * k_pad + 16 * g) = make_uint4(out[r][0], out[r][1], out[r][2], out[r][3]);
     }
-    __shared__ int s_sum[RR][8];
+    __shared__ int s_sum[R][8];
 #pragma unroll
-    for (int r = 0; r < RR; r++) {
+    for (int r = 0; r < R; r++) {
         int v = sum[r];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         if ((threadIdx.x & 31) == 0) s_sum[r][threadIdx.x >> 5] = v;
     }
     __syncthreads();
-    if (threadIdx.x < RR) {
+    if (threadIdx.x < R) {
         int t = 0;
         for (int w = 0; w < 8; w++) t += s_sum[threadIdx.x][w];
         s[i0 + threadIdx.x] = t;
@@ -382,39 +373,55 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     int64_t K = 0;
     for (int q = 0; q < L; q++) K += (int64_t)lohi[2 * q + 1] - (255 - (int64_t)lohi[2 * q]);
     tc->K = K;
-    const int64_t k_pad = std::max<int64_t>(TC_BK, (K + TC_BK - 1) / TC_BK * TC_BK), n_pad = ((int64_t)n + 255) / 256 * 256;
-    size_t free_b = 0, total_b = 0;
-    cudaMemGetInfo(&free_b, &total_b);
-    const bool fits = k_pad < (1ll << 30) && (uint64_t)(n_pad * k_pad) < free_b / 2;
-    if (!fits || (mode != 1 && K > 8ll * L)) return 0;  // wide values: the VABSDIFF4 kernel is the faster one
-    // the column table: (position << 9) | threshold byte; 256 = never for the padding columns
-    tc->col.assign((size_t)k_pad, 256u);
+    if (mode != 1 && K > 8ll * L) return 0;  // wide values: the VABSDIFF4 kernel is the faster one
+    if ((size_t)p->pitch + 16 > 200 * 1024) return 0;  // a row must fit shared memory (positions beyond 200,000)
+    // the word table: four columns per word, positions within eight bytes of the word's 4-byte-aligned base
+    std::vector<uint4>& table = tc->table;
+    table.clear();
+    table.reserve((size_t)(K / 4 + 64));
     {
-        size_t c = 0;
+        uint4 cur = make_uint4(0, 0, 0, 0);
+        int fill = 0;
         for (int q = 0; q < L; q++) {
             const unsigned lo = 255u - lohi[2 * q], hi = lohi[2 * q + 1];
-            for (unsigned thr = lo + 1; thr <= hi; thr++) tc->col[c++] = ((uint32_t)q << 9) | thr;
+            for (unsigned thr = lo + 1; thr <= hi; thr++) {
+                if (fill == 4 || (fill > 0 && q >= 4 * (int)cur.x + 8)) {
+                    table.push_back(cur);
+                    cur = make_uint4(0, 0, 0, 0), fill = 0;
+                }
+                if (fill == 0) cur.x = (unsigned)q >> 2;
+                cur.y |= (unsigned)(q - 4 * (int)cur.x) << (4 * fill);
+                cur.z |= thr << (8 * fill);
+                cur.w |= 1u << (8 * fill);
+                fill++;
+            }
         }
+        if (fill) table.push_back(cur);
     }
-    uint32_t* d_col = nullptr;
-    e = lzg_dev_alloc(ctx, (void**)&d_col, sizeof(uint32_t) * (size_t)k_pad);
+    const int64_t k_used = 4 * (int64_t)table.size();
+    const int64_t k_pad = std::max<int64_t>(TC_BK, (k_used + TC_BK - 1) / TC_BK * TC_BK), n_pad = ((int64_t)n + 255) / 256 * 256;
+    table.resize((size_t)(k_pad / 4), make_uint4(0, 0, 0, 0));
+    size_t free_b = 0, total_b = 0;
+    cudaMemGetInfo(&free_b, &total_b);
+    if (k_pad >= (1ll << 30) || (uint64_t)(n_pad * k_pad) >= free_b / 2) return 0;
+    uint4* d_table = nullptr;
+    e = lzg_dev_alloc(ctx, (void**)&d_table, sizeof(uint4) * table.size());
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_T, (size_t)(n_pad * k_pad));
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_s, sizeof(int32_t) * (size_t)n_pad);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_col, tc->col.data(), sizeof(uint32_t) * (size_t)k_pad, cudaMemcpyHostToDevice, ctx->stream);  // pageable: staged before the call returns
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_table, table.data(), sizeof(uint4) * table.size(), cudaMemcpyHostToDevice, ctx->stream);  // pageable: staged before the call returns
     if (e == cudaSuccess) {
-        if (4 * (size_t)p->pitch <= 96 * 1024) {  // n_pad is a multiple of 256: whole groups of four rows
-            if (4 * (size_t)p->pitch > 48 * 1024) cudaFuncSetAttribute(k_tc_expand<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * p->pitch);
-            k_tc_expand<4><<<(unsigned)(n_pad / 4), 256, 4 * (size_t)p->pitch, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
-        } else if ((size_t)p->pitch <= 200 * 1024) {
-            cudaFuncSetAttribute(k_tc_expand<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->pitch);
-            k_tc_expand<1><<<(unsigned)n_pad, 256, (size_t)p->pitch, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
+        const size_t sm2 = 2 * (size_t)p->pitch + 16, sm1 = (size_t)p->pitch + 16;
+        if (sm2 <= 100 * 1024) {  // n_pad is a multiple of 256: whole pairs of rows
+            if (sm2 > 48 * 1024) cudaFuncSetAttribute(k_tc_expand<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+            k_tc_expand<2><<<(unsigned)(n_pad / 2), 256, sm2, ctx->stream>>>(p->d, n, p->pitch, d_table, (int)k_pad, tc->d_T, tc->d_s);
         } else {
-            k_tc_expand<0><<<(unsigned)n_pad, 256, 0, ctx->stream>>>(p->d, n, p->pitch, d_col, (int)k_pad, tc->d_T, tc->d_s);
+            cudaFuncSetAttribute(k_tc_expand<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+            k_tc_expand<1><<<(unsigned)n_pad, 256, sm1, ctx->stream>>>(p->d, n, p->pitch, d_table, (int)k_pad, tc->d_T, tc->d_s);
         }
         ctx->launches++;
         e = cudaGetLastError();
     }
-    lzg_dev_free(ctx, d_col);
+    lzg_dev_free(ctx, d_table);
     if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: thermometer code", e);
     // the TMA descriptor of T: bytes, [n_pad][k_pad], boxes of 128 rows x 128 bytes, 128-byte swizzle
     const cuuint64_t dims[2] = {(cuuint64_t)k_pad, (cuuint64_t)n_pad}, strides[1] = {(cuuint64_t)k_pad};
