@@ -401,9 +401,12 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     const int64_t k_used = 4 * (int64_t)table.size();
     const int64_t k_pad = std::max<int64_t>(TC_BK, (k_used + TC_BK - 1) / TC_BK * TC_BK), n_pad = ((int64_t)n + 255) / 256 * 256;
     table.resize((size_t)(k_pad / 4), make_uint4(0, 0, 0, 0));
-    size_t free_b = 0, total_b = 0;
-    cudaMemGetInfo(&free_b, &total_b);
-    if (k_pad >= (1ll << 30) || (uint64_t)(n_pad * k_pad) >= free_b / 2) return 0;
+    if (k_pad >= (1ll << 30)) return 0;
+    if ((uint64_t)(n_pad * k_pad) > ((uint64_t)1 << 30)) {  // beyond 1 GB: only if it leaves half of the free memory
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        if ((uint64_t)(n_pad * k_pad) >= free_b / 2) return 0;
+    }
     uint4* d_table = nullptr;
     e = lzg_dev_alloc(ctx, (void**)&d_table, sizeof(uint4) * table.size());
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_T, (size_t)(n_pad * k_pad));
