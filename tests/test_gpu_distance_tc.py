@@ -41,7 +41,7 @@ def test_constant_columns_and_identical_rows(ctx, port, monkeypatch):
     bp = np.tile(np.arange(-3, 4, dtype=np.int32).repeat(20), (400, 1))  # K = 0: every distance is zero
     p = Profiles(ctx, bp)
     assert not p.distance_matrix().any()
-    assert p.distance_path() == {"tensor_core": True, "K": 0, "k_pad": 128, "launches": 1}
+    assert p.distance_path() == {"tensor_core": True, "K": 0, "k_pad": 512, "launches": 1}
     p.free()
     bp = bp.copy()
     bp[7, 5] = 100   # one cell differs at one position
