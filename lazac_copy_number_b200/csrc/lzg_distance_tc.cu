@@ -302,7 +302,7 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
         }
     } else {
         const int quad = warp & 3, trow = quad * 32 + lane;  // a warp reads the TMEM lanes of its quadrant
-        const bool vec = (n & 3) == 0;
+        const bool vec = (n & 3) == 0, vec8 = (n & 7) == 0;
         uint32_t lt = 0;
         for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, lt++) {
             const int2 tile = tiles[t];
@@ -324,7 +324,13 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
 #pragma unroll
                 for (int e = 0; e < 32; e++) v[e] = si + (j0 + e < n ? __ldg(s + j0 + e) : 0) - 2 * (int)g[e];
                 if (i < n && !(prefetch & 0x100)) {
-                    if (vec && j0 + 32 <= n) {
+                    if (vec8 && j0 + 32 <= n) {  // 32-byte stores: one whole sector per lane and instruction
+#pragma unroll
+                        for (int e = 0; e < 32; e += 8)
+                            asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(drow + j0 + e), "r"(v[e]), "r"(v[e + 1]), "r"(v[e + 2]), "r"(v[e + 3]),
+                                         "r"(v[e + 4]), "r"(v[e + 5]), "r"(v[e + 6]), "r"(v[e + 7])
+                                         : "memory");
+                    } else if (vec && j0 + 32 <= n) {
 #pragma unroll
                         for (int e = 0; e < 32; e += 4) *reinterpret_cast<int4*>(drow + j0 + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
                     } else {
