@@ -117,6 +117,27 @@ int lzg_nni_best_sharded(lzg_ctx* ctx, lzg_comm* c, lzg_tree* t, int32_t n_moves
     if (!t->scored) return lzg_fail(ctx, LZG_ERR_STATE, "tree must be scored (lzg_tree_score) before lzg_nni_best_sharded");
     LZG_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = lzg_tree_nni_launch(ctx, t, n_moves, moves);
+    if (c->comm && lzg_comm_world(c) > 1) {
+        // The ranks agree on the launch status BEFORE the data collective: a rank whose launch failed (not a move of its
+        // topology, an allocation failure) must not leave the others waiting in ncclAllReduce.  One int, summed.
+        int32_t* d_status = reinterpret_cast<int32_t*>(ctx->d_flag);
+        ctx->h_pinned[1] = rc == LZG_OK ? 0 : 1;
+        cudaError_t e = cudaMemcpyAsync(d_status, ctx->h_pinned + 1, sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream);
+        int nrc = e == cudaSuccess ? nccl_api()->all_reduce(d_status, d_status, 1, LZG_NCCL_INT32, LZG_NCCL_SUM, c->comm, ctx->stream) : 0;
+        if (e == cudaSuccess && nrc == 0) e = cudaMemcpyAsync(ctx->h_pinned + 1, d_status, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        const int failed = ctx->h_pinned[1];
+        cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), ctx->stream);  // the range-check flag's resting value
+        if (e != cudaSuccess || nrc != 0) return lzg_fail(ctx, LZG_ERR_STATE, "lzg_nni_best_sharded: status exchange failed");
+        if (rc != LZG_OK) return rc;
+        if (failed) {
+            if (n_moves > 0) {  // drop the pass this rank queued
+                int32_t bi, bs;
+                lzg_tree_nni_finish(ctx, t, greedy, &bi, &bs, nullptr);
+            }
+            return lzg_fail(ctx, LZG_ERR_STATE, "lzg_nni_best_sharded: the pass failed to launch on another rank");
+        }
+    }
     if (rc != LZG_OK) return rc;
     if (n_moves > 0 && c->comm) {
         int32_t* vec = lzg_tree_exchange_vector(t);
