@@ -78,6 +78,13 @@ int lzg_profiles_shape(const lzg_profiles* p, int32_t* n_cells, int32_t* n_pos);
  * launches so far; with LZG_TC_TIMING=1 in the environment info[4] / info[5] = microseconds of the code's preparation
  * and of the last product launch (CUDA events; call lzg_sync first), else 0; info[6] = tiles run.  int64 info[8]. */
 int lzg_profiles_distance_path(const lzg_profiles* p, int64_t* info);
+/* Host only -- no GPU, no context: the column layout of the thermometer code behind the tensor-core path, for tests.
+ * lo / hi = lowest / highest value of every position (-128 .. 127).  Column c = 4 w + e of the code belongs to word w;
+ * words[4w .. 4w+3] = {word index of the word's 4-byte-aligned base position, selector (nibble e = byte offset of
+ * column e's position from the base, 0 .. 7), four threshold bytes (value + 128), 0x01 per valid column}:
+ * T[i][c] = [bp[i][position] + 128 >= threshold].  Returns the number of words (entries beyond cap_words are not
+ * written), -1 on a bad argument; *K = sum of (hi - lo). */
+int64_t lzg_distance_tc_layout(const int32_t* lo, const int32_t* hi, int32_t L, uint32_t* words, int64_t cap_words, int64_t* K);
 
 /* ---- all-pairs ZCNT distance: replaces the pair loop of build_distance_matrix,
  *      src/lazac.cxx:81-91 (operator- include/copy_number.hpp:74-83 + breakpoint_magnitude

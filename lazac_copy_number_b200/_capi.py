@@ -38,6 +38,7 @@ SYMBOLS = [
     ("lzg_profiles_free", _i, [_vp]),
     ("lzg_profiles_shape", _i, [_vp, _i32p, _i32p]),
     ("lzg_profiles_distance_path", _i, [_vp, _vp]),
+    ("lzg_distance_tc_layout", C.c_int64, [_vp, _vp, _i32, _vp, C.c_int64, _vp]),
     ("lzg_distance_matrix", _i, [_vp, _vp, _vp]),
     ("lzg_distance_matrix_device_async", _i, [_vp, _vp, _vp]),
     ("lzg_distance_matrix_noalloc", _i, [_vp, _vp, _vp]),

@@ -377,6 +377,50 @@ static tc_encode_fn tc_encoder() {
     return fn;
 }
 
+// Host only: the word table of k_tc_expand from the per-position ranges (lohi[2q] = 255 - lowest byte, lohi[2q+1] = highest
+// byte; bytes are values + 128).  Entry {x: word index of the 4-byte-aligned base position, y: PRMT selector (nibble e = byte
+// offset of column e's position from the base, 0 .. 7), z: the four threshold bytes, w: 0x01 per valid column}.
+static void tc_layout(const unsigned* lohi, int L, std::vector<uint4>& table) {
+    table.clear();
+    uint4 cur = make_uint4(0, 0, 0, 0);
+    int fill = 0;
+    for (int q = 0; q < L; q++) {
+        const unsigned lo = 255u - lohi[2 * q], hi = lohi[2 * q + 1];
+        for (unsigned thr = lo + 1; thr <= hi; thr++) {
+            if (fill == 4 || (fill > 0 && q >= 4 * (int)cur.x + 8)) {  // full, or this position is out of the word's reach
+                table.push_back(cur);
+                cur = make_uint4(0, 0, 0, 0), fill = 0;
+            }
+            if (fill == 0) cur.x = (unsigned)q >> 2;
+            cur.y |= (unsigned)(q - 4 * (int)cur.x) << (4 * fill);
+            cur.z |= thr << (8 * fill);
+            cur.w |= 1u << (8 * fill);
+            fill++;
+        }
+    }
+    if (fill) table.push_back(cur);
+}
+
+// The same for tests (no GPU, no context): lo / hi = lowest / highest VALUE of every position (-128 .. 127).  Writes up to
+// cap_words entries of four uint32 and returns the number of words the code needs (call again with a larger buffer if it is
+// more than cap_words); *K = sum of (hi - lo).
+extern "C" int64_t lzg_distance_tc_layout(const int32_t* lo, const int32_t* hi, int32_t L, uint32_t* words, int64_t cap_words, int64_t* K) {
+    if (!lo || !hi || L < 0) return -1;
+    std::vector<unsigned> lohi(2 * (size_t)L);
+    int64_t k = 0;
+    for (int q = 0; q < L; q++) {
+        if (lo[q] < -128 || hi[q] > 127 || lo[q] > hi[q]) return -1;
+        lohi[2 * q] = 255u - (unsigned)(lo[q] + 128), lohi[2 * q + 1] = (unsigned)(hi[q] + 128);
+        k += hi[q] - lo[q];
+    }
+    if (K) *K = k;
+    std::vector<uint4> table;
+    tc_layout(lohi.data(), L, table);
+    for (size_t w = 0; w < table.size() && (int64_t)w < cap_words && words; w++)
+        words[4 * w] = table[w].x, words[4 * w + 1] = table[w].y, words[4 * w + 2] = table[w].z, words[4 * w + 3] = table[w].w;
+    return (int64_t)table.size();
+}
+
 void lzg_distance_tc_free(lzg_ctx* ctx, lzg_profiles* p) {
     if (!p->tc) return;
     for (cudaEvent_t ev : p->tc->ev)
@@ -443,27 +487,7 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     if ((size_t)p->pitch + 16 > 200 * 1024) return 0;  // a row must fit shared memory (positions beyond 200,000)
     // the word table: four columns per word, positions within eight bytes of the word's 4-byte-aligned base
     std::vector<uint4>& table = tc->table;
-    table.clear();
-    table.reserve((size_t)(K / 4 + 64));
-    {
-        uint4 cur = make_uint4(0, 0, 0, 0);
-        int fill = 0;
-        for (int q = 0; q < L; q++) {
-            const unsigned lo = 255u - lohi[2 * q], hi = lohi[2 * q + 1];
-            for (unsigned thr = lo + 1; thr <= hi; thr++) {
-                if (fill == 4 || (fill > 0 && q >= 4 * (int)cur.x + 8)) {
-                    table.push_back(cur);
-                    cur = make_uint4(0, 0, 0, 0), fill = 0;
-                }
-                if (fill == 0) cur.x = (unsigned)q >> 2;
-                cur.y |= (unsigned)(q - 4 * (int)cur.x) << (4 * fill);
-                cur.z |= thr << (8 * fill);
-                cur.w |= 1u << (8 * fill);
-                fill++;
-            }
-        }
-        if (fill) table.push_back(cur);
-    }
+    tc_layout(lohi, L, table);
     const int64_t k_used = 4 * (int64_t)table.size();
     // a multiple of STAGES k-blocks per tile: the issuer's loop is unrolled over the stages with compile-time descriptors
     constexpr int64_t KQ = (int64_t)TC_BK * TC_STAGES;
