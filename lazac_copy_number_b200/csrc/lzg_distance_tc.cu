@@ -358,6 +358,196 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * TC_TMEM_COLS) : "memory");
 }
 
+
+// ---- the same product on CTA PAIRS (tcgen05 cta_group::2) ------------------------------------------------------------------
+// What limits k_tc_distance is the operand stream into the SM: 48 KB of shared memory filled per 128 x 256 x 128 block of
+// products.  Here two CTAs of a cluster share a column block: each loads its own 128 rows of A and HALF of the 256 B rows
+// (32 KB per block and SM, six stages), one thread of the leader CTA issues M = 256 instructions that read both CTAs' shared
+// memory and accumulate into both CTAs' TMEM, and every CTA writes out its own 128 rows.  The two row blocks of a pair need not
+// be neighbours: tiles2[t] = (row block of CTA 0, row block of CTA 1 or -1, column block).
+constexpr int TC2_STAGES = 6, TC2_STAGE = 2 * TC_STAGE_A;  // A 16 KB + half of B 16 KB
+constexpr int TC2_SMEM = TC2_STAGES * TC2_STAGE + 1024 + 256;
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// both CTAs of a pair issue their loads; the bytes count on the LEADER's barrier (its address with the peer bit cleared)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst), "l"(map), "r"(c0),
+                 "r"(c1), "r"(bar & 0xFEFFFFFFu)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {  // arrives on the barrier at this offset in BOTH CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_i8_pair(uint32_t d_tmem, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cta(uint32_t bar, uint32_t cta) {  // on the barrier at this offset in CTA `cta` of the cluster
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar),
+        "r"(cta)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    const long long t0 = clock64();
+    for (;;) {
+        uint32_t done;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+        if (clock64() - t0 > 2000000000ll) __trap();
+    }
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
+k_tc_distance2(const __grid_constant__ CUtensorMap tmap, const int4* __restrict__ tiles, int n_tiles, int k_blocks, const int32_t* __restrict__ s,
+               int32_t* __restrict__ D, int32_t* const* __restrict__ row_base, int n) {
+    extern __shared__ uint8_t tc_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const uint32_t bar_full = smem_base + TC2_STAGES * TC2_STAGE, bar_empty = bar_full + 8 * TC2_STAGES, bar_tfull = bar_empty + 8 * TC2_STAGES, bar_tempty = bar_tfull + 16;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC2_STAGES * TC2_STAGE + 8 * (2 * TC2_STAGES + 4));
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = cluster_rank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    if (tid == 0) {
+        for (int q = 0; q < TC2_STAGES; q++) mbar_init(bar_full + 8 * q, 1), mbar_init(bar_empty + 8 * q, 1);
+        for (int q = 0; q < 2; q++) mbar_init(bar_tfull + 8 * q, 1), mbar_init(bar_tempty + 8 * q, 8);  // four epilogue warps of each CTA
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    cluster_sync();  // both CTAs' barriers exist before anything arrives on them
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    // instruction descriptor: D int32, A and B unsigned 8-bit, both K-major, N = 256, M = 256 over the pair
+    constexpr uint32_t idesc = (2u << 4) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t q = 0;
+            for (int t = pair; t < n_tiles; t += n_pairs) {
+                const int4 tile = tiles[t];
+                const int rb = rank == 0 || tile.y < 0 ? tile.x : tile.y;  // a missing second row block: its CTA loads the first one's rows (unused)
+                const int row0 = rb * TC_BM, colh = tile.z * TC_BN + 128 * (int)rank;  // this CTA's half of the column block
+                for (int kb = 0; kb < k_blocks; kb++, q++) {
+                    const uint32_t st = q % TC2_STAGES, ph = (q / TC2_STAGES) & 1u;
+                    mbar_wait_cluster(bar_empty + 8 * st, ph ^ 1u);
+                    if (rank == 0) mbar_expect_tx(bar_full + 8 * st, 2 * TC2_STAGE);  // both CTAs' bytes
+                    const uint32_t a = smem_base + st * TC2_STAGE, b = a + TC_STAGE_A;
+                    tma_load_2d_pair(a, &tmap, kb * TC_BK, row0, bar_full + 8 * st);
+                    tma_load_2d_pair(b, &tmap, kb * TC_BK, colh, bar_full + 8 * st);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (rank == 0) {
+            const uint64_t desc_a0 = tc_smem_desc(smem_base), desc_b0 = tc_smem_desc(smem_base + TC_STAGE_A);
+            uint32_t q = 0, lt = 0;
+            for (int t = pair; t < n_tiles; t += n_pairs, lt++) {
+                const uint32_t acc = lt & 1u;
+                mbar_wait_cluster(bar_tempty + 8 * acc, ((lt >> 1) & 1u) ^ 1u);  // both CTAs' epilogues have drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem + acc * TC_TMEM_COLS;
+                for (int kb = 0; kb < k_blocks; kb++, q++) {
+                    const uint32_t st = q % TC2_STAGES, ph = (q / TC2_STAGES) & 1u;
+                    mbar_wait_cluster(bar_full + 8 * st, ph);
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint64_t off0 = (uint64_t)((st * TC2_STAGE) >> 4);
+#pragma unroll
+                        for (int k = 0; k < TC_BK / TC_UMMA_K; k++)
+                            tc_mma_i8_pair(d_tmem, desc_a0 + off0 + 2 * k, desc_b0 + off0 + 2 * k, idesc, (kb | k) != 0);
+                        tc_commit_pair(bar_empty + 8 * st);
+                    }
+                    __syncwarp();
+                }
+                if (elect_one()) tc_commit_pair(bar_tfull + 8 * acc);
+                __syncwarp();
+            }
+        }
+    } else {
+        const int quad = warp & 3, trow = quad * 32 + lane;
+        const bool vec = (n & 3) == 0, vec8 = (n & 7) == 0;
+        uint32_t lt = 0;
+        for (int t = pair; t < n_tiles; t += n_pairs, lt++) {
+            const int4 tile = tiles[t];
+            const int rb = rank == 0 ? tile.x : tile.y;  // -1: nothing to write for this CTA
+            const int row0 = rb * TC_BM, col0 = tile.z * TC_BN;
+            const uint32_t acc = lt & 1u;
+            const int i = row0 + trow;
+            const bool live = rb >= 0 && i < n;
+            const int si = live ? __ldg(s + i) : 0;
+            int32_t* drow = !live ? nullptr : row_base ? row_base[rb] + (size_t)trow * n : D + (size_t)i * n;
+            const int mirror_from = row0 + TC_BM;
+            mbar_wait_cluster(bar_tfull + 8 * acc, (lt >> 1) & 1u);
+            tc_fence_after();
+            if (rb >= 0) {
+                for (int c = 0; c < TC_BN; c += 32) {
+                    const int j0 = col0 + c;
+                    if (j0 >= n) break;
+                    uint32_t g[32];
+                    tc_ld32(tmem + acc * TC_TMEM_COLS + ((uint32_t)(quad * 32) << 16) + c, g);
+                    int v[32];
+#pragma unroll
+                    for (int e = 0; e < 32; e++) v[e] = si + (j0 + e < n ? __ldg(s + j0 + e) : 0) - 2 * (int)g[e];
+                    if (live) {
+                        if (vec8 && j0 + 32 <= n) {
+#pragma unroll
+                            for (int e = 0; e < 32; e += 8)
+                                asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(drow + j0 + e), "r"(v[e]), "r"(v[e + 1]), "r"(v[e + 2]),
+                                             "r"(v[e + 3]), "r"(v[e + 4]), "r"(v[e + 5]), "r"(v[e + 6]), "r"(v[e + 7])
+                                             : "memory");
+                        } else if (vec && j0 + 32 <= n) {
+#pragma unroll
+                            for (int e = 0; e < 32; e += 4) *reinterpret_cast<int4*>(drow + j0 + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 32; e++)
+                                if (j0 + e < n) drow[j0 + e] = v[e];
+                        }
+#pragma unroll
+                        for (int e = 0; e < 32; e++) {
+                            const int j = j0 + e;
+                            if (j >= mirror_from && j < n) {
+                                if (row_base) row_base[j >> 7][(size_t)(j & 127) * n + i] = v[e];
+                                else D[(size_t)j * n + i] = v[e];
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cta(bar_tempty + 8 * acc, 0);  // on the leader's barrier
+        }
+    }
+    tc_fence_before();
+    cluster_sync();  // no CTA leaves while its partner may still read its shared memory or signal its barriers
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * TC_TMEM_COLS) : "memory");
+}
+
 }  // namespace
 
 // ---- host side ---------------------------------------------------------------------------------------------------------
@@ -529,6 +719,7 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     }
     e = cudaFuncSetAttribute(k_tc_distance<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance2, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM);
     if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: shared memory", e);
     tc->k_pad = (int)k_pad, tc->n_pad = (int)n_pad;
     tc->usable = 1;
@@ -561,23 +752,60 @@ int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, 
             for (size_t q = b0; q < b1; q++)
                 if (cb >= mine[q] / 2) tc->h_tiles.push_back(make_int2(mine[q], cb));
     }
+    const bool pairs_mode = !(getenv("LZG_TC_2CTA") && atoi(getenv("LZG_TC_2CTA")) == 0) && mine.size() >= 2;
+    std::vector<int4> tiles2;
+    if (pairs_mode) {
+        // CTA pairs: consecutive owned row blocks share their column blocks; bands of six pairs
+        tc->h_tiles.clear();
+        for (size_t b0 = 0; b0 < mine.size(); b0 += 12) {
+            const size_t b1 = std::min(mine.size(), b0 + 12);
+            for (int cb = mine[b0] / 2; cb < CB; cb++)
+                for (size_t q = b0; q < b1; q += 2) {
+                    const int r0 = mine[q], r1 = q + 1 < b1 ? mine[q + 1] : -1;
+                    if (cb >= r0 / 2) tiles2.push_back(make_int4(r0, r1, cb, 0));
+                }
+        }
+    }
     for (int rb : mine) {
         const int64_t i0 = (int64_t)rb * TC_BM, i1 = std::min<int64_t>(n, i0 + TC_BM);
         pairs += (i1 - i0) * n - (i0 + i1 - 1) * (i1 - i0) / 2;  // sum over the rows of (n - i)
     }
     if (pairs_done) *pairs_done = pairs;
-    const int n_tiles = (int)tc->h_tiles.size();
+    const int n_tiles = pairs_mode ? (int)tiles2.size() : (int)tc->h_tiles.size();
     if (n_tiles == 0) return LZG_OK;
     if (n_tiles > tc->tiles_cap) {
         lzg_dev_free(ctx, tc->d_tiles);
         tc->d_tiles = nullptr;
         const int cap = std::max(n_tiles, RB * CB);
-        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&tc->d_tiles, sizeof(int2) * (size_t)cap));
+        LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&tc->d_tiles, sizeof(int4) * (size_t)cap));  // int2 tiles or int4 pair tiles
         tc->tiles_cap = cap;
     }
-    LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tc->h_tiles.data(), sizeof(int2) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));
     CUtensorMap map;
     memcpy(&map, tc->tmap, sizeof(map));
+    if (pairs_mode) {
+        LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tiles2.data(), sizeof(int4) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));  // pageable: staged before the call returns
+        static int max_clusters = -1;  // resident CTA pairs of this kernel on this GPU
+        if (max_clusters < 0) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(ctx->sm_count & ~1), cfg.blockDim = dim3(192), cfg.dynamicSmemBytes = TC2_SMEM;
+            cudaLaunchAttribute at;
+            at.id = cudaLaunchAttributeClusterDimension;
+            at.val.clusterDim.x = 2, at.val.clusterDim.y = 1, at.val.clusterDim.z = 1;
+            cfg.attrs = &at, cfg.numAttrs = 1;
+            int nc = 0;
+            if (cudaOccupancyMaxActiveClusters(&nc, k_tc_distance2, &cfg) != cudaSuccess || nc < 1) nc = ctx->sm_count / 2, cudaGetLastError();
+            max_clusters = std::min(nc, ctx->sm_count / 2);
+        }
+        if (tc->ev[2]) cudaEventRecord(tc->ev[2], ctx->stream);
+        k_tc_distance2<<<2 * std::min(n_tiles, max_clusters), 192, TC2_SMEM, ctx->stream>>>(map, reinterpret_cast<const int4*>(tc->d_tiles), n_tiles, tc->k_pad / TC_BK, tc->d_s,
+                                                                                          d_D, d_row_base, n);
+        LZG_LAUNCH_CHECK(ctx);
+        if (tc->ev[3]) cudaEventRecord(tc->ev[3], ctx->stream);
+        tc->launches++;
+        tc->tiles_run += 2 * (int64_t)n_tiles;
+        return LZG_OK;
+    }
+    LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tc->h_tiles.data(), sizeof(int2) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));
     if (tc->ev[2]) cudaEventRecord(tc->ev[2], ctx->stream);
     // LZG_TC_PREFETCH (k-blocks of L2 prefetch ahead of the loads) is an experiment knob, off by default: the prefetches go
     // through the same TMA unit as the loads and HALVE the kernel's speed (4.9 -> 11.3 ms at cfg3 with 4 .. 8 blocks ahead) --
