@@ -717,9 +717,13 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
         lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: cuTensorMapEncodeTiled");
         return -LZG_ERR_CUDA;
     }
-    e = cudaFuncSetAttribute(k_tc_distance<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance2, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM);
+    static bool attrs_set[64] = {};  // per device, once
+    if (ctx->device >= 64 || !attrs_set[ctx->device]) {
+        e = cudaFuncSetAttribute(k_tc_distance<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance2, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM);
+        if (e == cudaSuccess && ctx->device < 64) attrs_set[ctx->device] = true;
+    }
     if (e != cudaSuccess) return -lzg_fail(ctx, LZG_ERR_CUDA, "tensor-core distance: shared memory", e);
     tc->k_pad = (int)k_pad, tc->n_pad = (int)n_pad;
     tc->usable = 1;
@@ -784,8 +788,9 @@ int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, 
     memcpy(&map, tc->tmap, sizeof(map));
     if (pairs_mode) {
         LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tiles2.data(), sizeof(int4) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));  // pageable: staged before the call returns
-        static int max_clusters = -1;  // resident CTA pairs of this kernel on this GPU
-        if (max_clusters < 0) {
+        static int max_clusters_of[64];  // resident CTA pairs of this kernel, per device (0 = not asked yet)
+        int& max_clusters = max_clusters_of[ctx->device & 63];
+        if (max_clusters <= 0) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(ctx->sm_count & ~1), cfg.blockDim = dim3(192), cfg.dynamicSmemBytes = TC2_SMEM;
             cudaLaunchAttribute at;
