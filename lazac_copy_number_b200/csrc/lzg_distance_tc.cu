@@ -7,13 +7,17 @@
 // bit-identical to the reference's loop (operator- include/copy_number.hpp:74-83 + breakpoint_magnitude src/copy_number.cxx:100-113)
 // because every quantity is an integer below 2^31: tcgen05.mma kind::i8 multiplies unsigned bytes into int32 accumulators.
 // Breakpoint profiles are sparse and narrow (cfg3: K = 2.02 L), so the product is ~10x fewer tensor-core cycles than the
-// VABSDIFF4 kernel has ALU cycles; lzg_distance_run dispatches here by value range (K <= 8 L, the 8-bit format, whole matrix on
-// one GPU) and keeps k_zcnt_distance for everything else.  LZG_TC=0 switches the path off, LZG_TC=1 forces it where it can run.
+// VABSDIFF4 kernel has ALU cycles; lzg_distance_run dispatches here by value range (K <= 8 L, the 8-bit format, enough tiles to
+// fill the GPU) -- whole matrices, shards and the multi-GPU row-block table alike -- and keeps k_zcnt_distance for everything
+// else.  LZG_TC=0 switches the path off, LZG_TC=1 forces it where it can run.
 //
-// Kernels: k_tc_colrange (lo_p, w_p), k_tc_expand (T and s), k_tc_distance: persistent CTAs over 128 x 256 tiles of the upper
-// triangle, operands by TMA (128-byte swizzle, 4 stages of 48 KB) issued by one thread, tcgen05.mma (M 128, N 256, K 32) issued
-// by one thread into two alternating accumulators of 256 TMEM columns, four epilogue warps: tcgen05.ld -> s_i + s_j - 2 g ->
-// D[i][j] and the mirror D[j][i] while the next tile's product runs.
+// Kernels: k_tc_colrange (lo_p, w_p), k_tc_expand (T and s), and the product in two forms over 128 x 256 tiles of the upper
+// triangle, persistent, operands by TMA (128-byte swizzle) issued by one thread, tcgen05.mma kind::i8 issued by one thread into
+// two alternating accumulators of 256 TMEM columns, four epilogue warps (tcgen05.ld -> s_i + s_j - 2 g -> D[i][j] and the
+// mirror D[j][i]) working on one tile while the next tile's product runs:
+//   k_tc_distance2 (default): CTA pairs, cta_group::2 -- M = 256 instructions over two SMs that share the column block, six
+//                             stages of 32 KB per SM; 3.74 ms at cfg3, tensor pipe 93 % active;
+//   k_tc_distance:            single CTAs, M = 128, four stages of 48 KB; 4.68 ms (LZG_TC_2CTA=0, and fewer than two row blocks).
 #include <cuda.h>
 
 #include <algorithm>
@@ -32,28 +36,40 @@ constexpr int TC_SMEM = TC_STAGES * TC_STAGE + 1024 /* alignment slack */ + 256 
 constexpr int TC_TMEM_COLS = 256;
 
 // ---- per-position range over the cells: lo_p (biased byte) and hi_p ------------------------------------------------
-__global__ void k_tc_colrange(const uint8_t* __restrict__ d, int n, int pitch, int L, unsigned* __restrict__ lo_hi) {
-    // one thread per group of four positions, rows strided over blockIdx.y (eight loads in flight); lo_hi[2p] = 255 - lo,
-    // lo_hi[2p+1] = hi, both merged with atomicMax
+__global__ void __launch_bounds__(128) k_tc_colrange(const uint8_t* __restrict__ d, int n, int pitch, int L, unsigned* __restrict__ lo_hi) {
+    // one thread per group of sixteen positions (one 16-byte load per row, eight rows in flight), rows strided over blockIdx.y;
+    // lo_hi[2p] = 255 - lo, lo_hi[2p+1] = hi, both merged with atomicMax
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (4 * g >= L) return;
-    uint32_t lo4 = 0xffffffffu, hi4 = 0u;  // per-byte minima / maxima (__vminu4 / __vmaxu4)
-    const uint8_t* col = d + 4 * (size_t)g;
+    if (16 * g >= pitch) return;  // the padding positions of a row are read too (never reported)
+    uint32_t lo4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu}, hi4[4] = {0u, 0u, 0u, 0u};  // per-byte minima / maxima
+    const uint8_t* col = d + 16 * (size_t)g;
     int i = blockIdx.y;
     for (; i + 7 * (int)gridDim.y < n; i += 8 * gridDim.y) {
-        uint32_t w[8];
+        uint4 w[8];
 #pragma unroll
-        for (int u = 0; u < 8; u++) w[u] = __ldg(reinterpret_cast<const uint32_t*>(col + (size_t)(i + u * gridDim.y) * pitch));
+        for (int u = 0; u < 8; u++) w[u] = __ldg(reinterpret_cast<const uint4*>(col + (size_t)(i + u * gridDim.y) * pitch));
 #pragma unroll
-        for (int u = 0; u < 8; u++) lo4 = __vminu4(lo4, w[u]), hi4 = __vmaxu4(hi4, w[u]);
+        for (int u = 0; u < 8; u++) {
+            lo4[0] = __vminu4(lo4[0], w[u].x), hi4[0] = __vmaxu4(hi4[0], w[u].x);
+            lo4[1] = __vminu4(lo4[1], w[u].y), hi4[1] = __vmaxu4(hi4[1], w[u].y);
+            lo4[2] = __vminu4(lo4[2], w[u].z), hi4[2] = __vmaxu4(hi4[2], w[u].z);
+            lo4[3] = __vminu4(lo4[3], w[u].w), hi4[3] = __vmaxu4(hi4[3], w[u].w);
+        }
     }
     for (; i < n; i += gridDim.y) {
-        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(col + (size_t)i * pitch));
-        lo4 = __vminu4(lo4, w), hi4 = __vmaxu4(hi4, w);
+        const uint4 w = __ldg(reinterpret_cast<const uint4*>(col + (size_t)i * pitch));
+        lo4[0] = __vminu4(lo4[0], w.x), hi4[0] = __vmaxu4(hi4[0], w.x);
+        lo4[1] = __vminu4(lo4[1], w.y), hi4[1] = __vmaxu4(hi4[1], w.y);
+        lo4[2] = __vminu4(lo4[2], w.z), hi4[2] = __vmaxu4(hi4[2], w.z);
+        lo4[3] = __vminu4(lo4[3], w.w), hi4[3] = __vmaxu4(hi4[3], w.w);
     }
 #pragma unroll
-    for (int e = 0; e < 4; e++)
-        if (4 * g + e < L) atomicMax(lo_hi + 2 * (4 * g + e), 255u - ((lo4 >> (8 * e)) & 255u)), atomicMax(lo_hi + 2 * (4 * g + e) + 1, (hi4 >> (8 * e)) & 255u);
+    for (int q = 0; q < 4; q++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int pos = 16 * g + 4 * q + e;
+            if (pos < L) atomicMax(lo_hi + 2 * pos, 255u - ((lo4[q] >> (8 * e)) & 255u)), atomicMax(lo_hi + 2 * pos + 1, (hi4[q] >> (8 * e)) & 255u);
+        }
 }
 
 // ---- T and its row sums ------------------------------------------------------------------------------------------
@@ -265,8 +281,6 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
                     if (elect_one()) {
 #pragma unroll
                         for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {
-                            constexpr int dummy = 0;
-                            (void)dummy;
                             const uint64_t off = (uint64_t)((st * TC_STAGE + k * TC_UMMA_K) >> 4);
                             tc_mma_i8(d_tmem, desc_a0 + off, desc_b0 + off, idesc, (kb | st | k) != 0);
                         }
@@ -646,10 +660,10 @@ int lzg_distance_tc_prepare_begin(lzg_ctx* ctx, lzg_profiles* p) {
     cudaError_t e = lzg_dev_alloc(ctx, (void**)&d_lohi, sizeof(unsigned) * 2 * (size_t)L);
     if (e == cudaSuccess) e = cudaMemsetAsync(d_lohi, 0, sizeof(unsigned) * 2 * (size_t)L, ctx->stream);
     if (e == cudaSuccess) {
-        const int groups = (L + 3) / 4;
-        // about 16 warps per SM in flight, every thread eight rows at a time
-        const int slabs = std::max(1, std::min((n + 7) / 8, 16 * 32 * ctx->sm_count / std::max(128, groups)));
-        k_tc_colrange<<<dim3((groups + 127) / 128, slabs), 128, 0, ctx->stream>>>(p->d, n, p->pitch, L, d_lohi);
+        // about 40 KB of loads in flight per SM: groups of sixteen positions x row slabs, eight rows a thread at a time
+        const int blocks_x = (p->pitch / 16 + 127) / 128;
+        const int slabs = std::max(1, std::min((n + 7) / 8, 3 * ctx->sm_count / blocks_x));
+        k_tc_colrange<<<dim3(blocks_x, slabs), 128, 0, ctx->stream>>>(p->d, n, p->pitch, L, d_lohi);
         ctx->launches++;
         e = cudaGetLastError();
     }
