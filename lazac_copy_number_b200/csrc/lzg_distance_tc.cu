@@ -76,53 +76,50 @@ __global__ void __launch_bounds__(128) k_tc_colrange(const uint8_t* __restrict__
 // The host lays the columns out four to an output word such that the (up to four) positions of a word lie within eight bytes
 // of a 4-byte-aligned base (it starts a new word, leaving never-set columns, where they do not); a word's table entry is
 // {base word index, PRMT selector, four threshold bytes, 0x01 per valid column}.  T[i][4 w + e] = [byte(i, position) >= threshold]:
-// two 32-bit loads of the row (staged in shared memory), one PRMT gathers the four bytes, a SWAR compare makes the four
-// results.  A CTA codes R consecutive rows with every table entry fetched once.
-template <int R>
+// two 32-bit loads of the row, one PRMT gathers the four bytes, a SWAR compare makes the four results.
+// A thread owns sixteen columns (four words: its table entries stay in registers) and walks TC_XROWS rows, four at a time;
+// neighbouring threads read neighbouring positions (L1 serves the overlap), every 16-byte store is final.  s[i] (zeroed by the
+// caller) collects the ones of row i: a warp reduction and one atomic per warp and row.
+constexpr int TC_XROWS = 64;
 __global__ void __launch_bounds__(256) k_tc_expand(const uint8_t* __restrict__ d, int n, int pitch, const uint4* __restrict__ table, int k_pad,
                                                     uint8_t* __restrict__ T, int32_t* __restrict__ s) {
-    extern __shared__ __align__(16) uint8_t x_rows[];  // R rows of `pitch` bytes + 16
-    const int i0 = blockIdx.x * R;                      // rows n .. n_pad-1 are zero rows
-    for (int q = threadIdx.x; q < R * (pitch / 16) + 1; q += blockDim.x) {
-        const int r = q / (pitch / 16), c = q - r * (pitch / 16);
-        reinterpret_cast<uint4*>(x_rows)[q] = r < R && i0 + r < n ? __ldg(reinterpret_cast<const uint4*>(d + (size_t)(i0 + r) * pitch) + c) : make_uint4(0, 0, 0, 0);
-    }
-    __syncthreads();
-    int sum[R];
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;  // 16-byte group of a row of T
+    const bool active = 16 * g < k_pad;
+    uint4 ent[4];
 #pragma unroll
-    for (int r = 0; r < R; r++) sum[r] = 0;
-    for (int g = threadIdx.x; 16 * g < k_pad; g += blockDim.x) {
-        uint4 ent[4];
+    for (int q = 0; q < 4; q++) ent[q] = active ? __ldg(table + 4 * g + q) : make_uint4(0, 0, 0, 0);
+    const int last_word = pitch / 4 - 1;
+    const int i0 = blockIdx.y * TC_XROWS;  // rows n .. n_pad-1 are zero rows
+    for (int r = 0; r < TC_XROWS; r += 4) {
+        uint32_t lo[4][4], hi[4][4];
 #pragma unroll
-        for (int q = 0; q < 4; q++) ent[q] = __ldg(table + 4 * g + q);
-#pragma unroll
-        for (int r = 0; r < R; r++) {
-            const uint32_t* roww = reinterpret_cast<const uint32_t*>(x_rows + (size_t)r * pitch);
-            uint32_t out[4];
+        for (int u = 0; u < 4; u++) {
+            const int i = i0 + r + u;
+            const uint32_t* roww = reinterpret_cast<const uint32_t*>(d + (size_t)i * pitch);
 #pragma unroll
             for (int q = 0; q < 4; q++) {
-                const uint32_t x = __byte_perm(roww[ent[q].x], roww[ent[q].x + 1], ent[q].y), y = ent[q].z;
+                lo[u][q] = i < n ? __ldg(roww + ent[q].x) : 0u;
+                hi[u][q] = i < n ? __ldg(roww + min((int)ent[q].x + 1, last_word)) : 0u;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = i0 + r + u;
+            uint32_t out[4];
+            int ones = 0;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint32_t x = __byte_perm(lo[u][q], hi[u][q], ent[q].y), y = ent[q].z;
                 const uint32_t dlt = (x | 0x80808080u) - (y & 0x7f7f7f7fu);      // bit 7 of a byte: low seven bits of x >= those of y
                 const uint32_t ge = (x & ~y) | (~(x ^ y) & dlt);                  // bit 7 of a byte: x >= y
-                out[q] = (ge >> 7) & ent[q].w;
-                sum[r] += __popc(out[q]);
+                out[q] = i < n ? (ge >> 7) & ent[q].w : 0u;
+                ones += __popc(out[q]);
             }
-            *reinterpret_cast<uint4*>(T + (size_t)(i0 + r) * k_pad + 16 * g) = make_uint4(out[0], out[1], out[2], out[3]);
+            if (active) *reinterpret_cast<uint4*>(T + (size_t)i * k_pad + 16 * g) = make_uint4(out[0], out[1], out[2], out[3]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) ones += __shfl_xor_sync(0xffffffffu, ones, o);
+            if ((threadIdx.x & 31) == 0 && ones) atomicAdd(s + i, ones);
         }
-    }
-    __shared__ int s_sum[R][8];
-#pragma unroll
-    for (int r = 0; r < R; r++) {
-        int v = sum[r];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) s_sum[r][threadIdx.x >> 5] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < R) {
-        int t = 0;
-        for (int w = 0; w < 8; w++) t += s_sum[threadIdx.x][w];
-        s[i0 + threadIdx.x] = t;
     }
 }
 
@@ -688,7 +685,6 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     for (int q = 0; q < L; q++) K += (int64_t)lohi[2 * q + 1] - (255 - (int64_t)lohi[2 * q]);
     tc->K = K;
     if (mode != 1 && K > 8ll * L) return 0;  // wide values: the VABSDIFF4 kernel is the faster one
-    if ((size_t)p->pitch + 16 > 200 * 1024) return 0;  // a row must fit shared memory (positions beyond 200,000)
     // the word table: four columns per word, positions within eight bytes of the word's 4-byte-aligned base
     std::vector<uint4>& table = tc->table;
     tc_layout(lohi, L, table);
@@ -708,15 +704,9 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_T, (size_t)(n_pad * k_pad));
     if (e == cudaSuccess) e = lzg_dev_alloc(ctx, (void**)&tc->d_s, sizeof(int32_t) * (size_t)n_pad);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_table, table.data(), sizeof(uint4) * table.size(), cudaMemcpyHostToDevice, ctx->stream);  // pageable: staged before the call returns
+    if (e == cudaSuccess) e = cudaMemsetAsync(tc->d_s, 0, sizeof(int32_t) * (size_t)n_pad, ctx->stream);
     if (e == cudaSuccess) {
-        const size_t sm2 = 2 * (size_t)p->pitch + 16, sm1 = (size_t)p->pitch + 16;
-        if (sm2 <= 100 * 1024) {  // n_pad is a multiple of 256: whole pairs of rows
-            if (sm2 > 48 * 1024) cudaFuncSetAttribute(k_tc_expand<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-            k_tc_expand<2><<<(unsigned)(n_pad / 2), 256, sm2, ctx->stream>>>(p->d, n, p->pitch, d_table, (int)k_pad, tc->d_T, tc->d_s);
-        } else {
-            cudaFuncSetAttribute(k_tc_expand<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-            k_tc_expand<1><<<(unsigned)n_pad, 256, sm1, ctx->stream>>>(p->d, n, p->pitch, d_table, (int)k_pad, tc->d_T, tc->d_s);
-        }
+        k_tc_expand<<<dim3((unsigned)((k_pad / 16 + 255) / 256), (unsigned)(n_pad / TC_XROWS)), 256, 0, ctx->stream>>>(p->d, n, p->pitch, d_table, (int)k_pad, tc->d_T, tc->d_s);
         ctx->launches++;
         e = cudaGetLastError();
     }
