@@ -583,6 +583,7 @@ static tc_encode_fn tc_encoder() {
 // offset of column e's position from the base, 0 .. 7), z: the four threshold bytes, w: 0x01 per valid column}.
 static void tc_layout(const unsigned* lohi, int L, std::vector<uint4>& table) {
     table.clear();
+    table.reserve((size_t)L / 2 + 64);
     uint4 cur = make_uint4(0, 0, 0, 0);
     int fill = 0;
     for (int q = 0; q < L; q++) {
