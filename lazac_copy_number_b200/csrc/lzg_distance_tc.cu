@@ -761,11 +761,11 @@ int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, 
             for (size_t q = b0; q < b1; q++)
                 if (cb >= mine[q] / 2) tc->h_tiles.push_back(make_int2(mine[q], cb));
     }
-    const bool pairs_mode = !(getenv("LZG_TC_2CTA") && atoi(getenv("LZG_TC_2CTA")) == 0) && mine.size() >= 2;
+    static bool pairs_refused = false;  // a cluster launch failed once in this process: single CTAs from then on
+    bool pairs_mode = !(getenv("LZG_TC_2CTA") && atoi(getenv("LZG_TC_2CTA")) == 0) && mine.size() >= 2 && !pairs_refused;
     std::vector<int4> tiles2;
     if (pairs_mode) {
         // CTA pairs: consecutive owned row blocks share their column blocks; bands of six pairs
-        tc->h_tiles.clear();
         for (size_t b0 = 0; b0 < mine.size(); b0 += 12) {
             const size_t b1 = std::min(mine.size(), b0 + 12);
             for (int cb = mine[b0] / 2; cb < CB; cb++)
@@ -780,12 +780,12 @@ int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, 
         pairs += (i1 - i0) * n - (i0 + i1 - 1) * (i1 - i0) / 2;  // sum over the rows of (n - i)
     }
     if (pairs_done) *pairs_done = pairs;
-    const int n_tiles = pairs_mode ? (int)tiles2.size() : (int)tc->h_tiles.size();
+    int n_tiles = pairs_mode ? (int)tiles2.size() : (int)tc->h_tiles.size();
     if (n_tiles == 0) return LZG_OK;
-    if (n_tiles > tc->tiles_cap) {
+    if (std::max(n_tiles, (int)tc->h_tiles.size()) > tc->tiles_cap) {
         lzg_dev_free(ctx, tc->d_tiles);
         tc->d_tiles = nullptr;
-        const int cap = std::max(n_tiles, RB * CB);
+        const int cap = std::max(std::max(n_tiles, (int)tc->h_tiles.size()), RB * CB);
         LZG_CUDA(ctx, lzg_dev_alloc(ctx, (void**)&tc->d_tiles, sizeof(int4) * (size_t)cap));  // int2 tiles or int4 pair tiles
         tc->tiles_cap = cap;
     }
@@ -809,11 +809,16 @@ int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, 
         if (tc->ev[2]) cudaEventRecord(tc->ev[2], ctx->stream);
         k_tc_distance2<<<2 * std::min(n_tiles, max_clusters), 192, TC2_SMEM, ctx->stream>>>(map, reinterpret_cast<const int4*>(tc->d_tiles), n_tiles, tc->k_pad / TC_BK, tc->d_s,
                                                                                           d_D, d_row_base, n);
-        LZG_LAUNCH_CHECK(ctx);
-        if (tc->ev[3]) cudaEventRecord(tc->ev[3], ctx->stream);
-        tc->launches++;
-        tc->tiles_run += 2 * (int64_t)n_tiles;
-        return LZG_OK;
+        if (cudaGetLastError() == cudaSuccess) {
+            ctx->launches++;
+            if (tc->ev[3]) cudaEventRecord(tc->ev[3], ctx->stream);
+            tc->launches++;
+            tc->tiles_run += 2 * (int64_t)n_tiles;
+            return LZG_OK;
+        }
+        pairs_refused = true;  // no clusters here (a partitioned GPU, a driver limit): the single-CTA kernel below
+        pairs_mode = false;
+        n_tiles = (int)tc->h_tiles.size();
     }
     LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tc->h_tiles.data(), sizeof(int2) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));
     if (tc->ev[2]) cudaEventRecord(tc->ev[2], ctx->stream);
