@@ -153,9 +153,6 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
                  "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int c0, int c1) {
-    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
-}
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
@@ -200,10 +197,9 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 // row block, so a finished group of row blocks never changes again (lzg_distance_matrix copies it out while later groups compute).
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 
-template <bool ALSU>
-__global__ void __launch_bounds__(ALSU ? 320 : 192, 1)
+__global__ void __launch_bounds__(192, 1)
 k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__ tiles, int n_tiles, int k_blocks, const int32_t* __restrict__ s,
-              int32_t* __restrict__ D, int32_t* const* __restrict__ row_base, int n, int prefetch, const uint8_t* __restrict__ T, int k_pad) {
+              int32_t* __restrict__ D, int32_t* const* __restrict__ row_base, int n) {
     extern __shared__ uint8_t tc_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t smem_base = smem_u32(smem);
@@ -211,7 +207,7 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TC_STAGES * TC_STAGE + 8 * (2 * TC_STAGES + 4));
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
-        for (int q = 0; q < TC_STAGES; q++) mbar_init(bar_full + 8 * q, ALSU ? 129 : 1), mbar_init(bar_empty + 8 * q, 1);  // ALSU: + the 128 loader threads
+        for (int q = 0; q < TC_STAGES; q++) mbar_init(bar_full + 8 * q, 1), mbar_init(bar_empty + 8 * q, 1);
         for (int q = 0; q < 2; q++) mbar_init(bar_tfull + 8 * q, 1), mbar_init(bar_tempty + 8 * q, 4);  // one arrival per epilogue warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -228,31 +224,15 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
     if (warp == 0) {
         if (lane == 0) {
             uint32_t q = 0;  // k-blocks issued so far (stage = q % STAGES, phase = q / STAGES & 1)
-            // an L2 prefetch cursor runs `prefetch` k-blocks ahead of the loads, across tile boundaries: the operand boxes are
-            // in L2 by the time their TMA load is issued (the four stages cover an L2 hit, not a DRAM miss)
-            int pt = blockIdx.x, pkb = 0, ahead = 0;
-            int2 ptile = pt < n_tiles ? tiles[pt] : make_int2(0, 0);
-            auto prefetch_step = [&]() {
-                if (pt >= n_tiles) return;
-                tma_prefetch_2d(&tmap, pkb * TC_BK, ptile.x * TC_BM);
-                tma_prefetch_2d(&tmap, pkb * TC_BK, ptile.y * TC_BN);
-                tma_prefetch_2d(&tmap, pkb * TC_BK, ptile.y * TC_BN + 128);
-                if (++pkb == k_blocks) {
-                    pkb = 0, pt += gridDim.x;
-                    if (pt < n_tiles) ptile = tiles[pt];
-                }
-            };
-            for (; ahead < (prefetch & 0xff); ahead++) prefetch_step();
             for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
                 const int2 tile = tiles[t];
                 const int row0 = tile.x * TC_BM, col0 = tile.y * TC_BN;
                 for (int kb = 0; kb < k_blocks; kb++, q++) {
-                    if ((prefetch & 0xff) > 0) prefetch_step();
                     const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
                     mbar_wait(bar_empty + 8 * st, ph ^ 1u);
-                    mbar_expect_tx(bar_full + 8 * st, ALSU ? TC_STAGE_B : TC_STAGE);
+                    mbar_expect_tx(bar_full + 8 * st, TC_STAGE);
                     const uint32_t a = smem_base + st * TC_STAGE, b = a + TC_STAGE_A;
-                    if (!ALSU) tma_load_2d(a, &tmap, kb * TC_BK, row0, bar_full + 8 * st);
+                    tma_load_2d(a, &tmap, kb * TC_BK, row0, bar_full + 8 * st);
                     tma_load_2d(b, &tmap, kb * TC_BK, col0, bar_full + 8 * st);
                     tma_load_2d(b + TC_STAGE_A, &tmap, kb * TC_BK, col0 + 128, bar_full + 8 * st);
                 }
@@ -273,7 +253,6 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
 #pragma unroll
                 for (int st = 0; st < TC_STAGES; st++) {
                     mbar_wait(bar_full + 8 * st, rounds & 1u);
-                    if (ALSU) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the A tile was written through the generic proxy
                     tc_fence_after();
                     if (elect_one()) {
 #pragma unroll
@@ -288,28 +267,6 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
             }
             if (elect_one()) tc_commit(bar_tfull + 8 * acc);  // the accumulator is complete
             __syncwarp();
-        }
-    } else if (ALSU && warp >= 6) {
-        // ---- A tiles through the LSU (cp.async, 16 bytes a thread, eight per k-block): the TMA unit's request rate caps the
-        // kernel, so a third of the operand bytes takes the other road.  Same layout as the TMA's 128-byte swizzle:
-        // 16-byte chunk c of row r at r * 128 + ((c ^ (r & 7)) << 4).
-        const int lt = tid - 192;
-        uint32_t q = 0;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-            const int row0 = tiles[t].x * TC_BM;
-            const uint8_t* src0 = T + (size_t)row0 * k_pad;
-            for (int kb = 0; kb < k_blocks; kb++, q++) {
-                const uint32_t st = q % TC_STAGES, ph = (q / TC_STAGES) & 1u;
-                mbar_wait(bar_empty + 8 * st, ph ^ 1u);
-                const uint32_t a = smem_base + st * TC_STAGE;
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const int idx = j * 128 + lt, r = idx >> 3, c = idx & 7;
-                    const uint8_t* src = src0 + (size_t)r * k_pad + kb * TC_BK + c * 16;
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a + r * 128 + ((c ^ (r & 7)) << 4)), "l"(src) : "memory");
-                }
-                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar_full + 8 * st) : "memory");
-            }
         }
     } else {
         const int quad = warp & 3, trow = quad * 32 + lane;  // a warp reads the TMEM lanes of its quadrant
@@ -334,7 +291,7 @@ k_tc_distance(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__
                 int v[32];
 #pragma unroll
                 for (int e = 0; e < 32; e++) v[e] = si + (j0 + e < n ? __ldg(s + j0 + e) : 0) - 2 * (int)g[e];
-                if (i < n && !(prefetch & 0x100)) {
+                if (i < n) {
                     if (vec8 && j0 + 32 <= n) {  // 32-byte stores: one whole sector per lane and instruction
 #pragma unroll
                         for (int e = 0; e < 32; e += 8)
@@ -724,8 +681,7 @@ int lzg_distance_tc_prepare_finish(lzg_ctx* ctx, lzg_profiles* p) {
     }
     static bool attrs_set[64] = {};  // per device, once
     if (ctx->device >= 64 || !attrs_set[ctx->device]) {
-        e = cudaFuncSetAttribute(k_tc_distance<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+        e = cudaFuncSetAttribute(k_tc_distance, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_distance2, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM);
         if (e == cudaSuccess && ctx->device < 64) attrs_set[ctx->device] = true;
     }
@@ -822,18 +778,7 @@ int lzg_distance_tc_run(lzg_ctx* ctx, lzg_profiles* p, int shard, int n_shards, 
     }
     LZG_CUDA(ctx, cudaMemcpyAsync(tc->d_tiles, tc->h_tiles.data(), sizeof(int2) * (size_t)n_tiles, cudaMemcpyHostToDevice, ctx->stream));
     if (tc->ev[2]) cudaEventRecord(tc->ev[2], ctx->stream);
-    // LZG_TC_PREFETCH (k-blocks of L2 prefetch ahead of the loads) is an experiment knob, off by default: the prefetches go
-    // through the same TMA unit as the loads and HALVE the kernel's speed (4.9 -> 11.3 ms at cfg3 with 4 .. 8 blocks ahead) --
-    // the unit's request rate (one 128-byte row per ~1.4 clk), not the latency of the loads, is what limits this kernel
-    int prefetch = getenv("LZG_TC_PREFETCH") ? std::max(0, std::min(64, atoi(getenv("LZG_TC_PREFETCH")))) : 0;
-    if (getenv("LZG_TC_NOSTORE")) prefetch |= 0x100;  // experiment: the product without the epilogue's stores (wrong results)
-    const bool a_by_lsu = getenv("LZG_TC_A_LSU") && atoi(getenv("LZG_TC_A_LSU")) == 1;  // experiment: A tiles by cp.async (no gain: 4.90 against 4.76 ms)
-    if (a_by_lsu)
-        k_tc_distance<true><<<std::min(n_tiles, ctx->sm_count), 320, TC_SMEM, ctx->stream>>>(map, tc->d_tiles, n_tiles, tc->k_pad / TC_BK, tc->d_s, d_D, d_row_base, n, prefetch,
-                                                                                            tc->d_T, tc->k_pad);
-    else
-        k_tc_distance<false><<<std::min(n_tiles, ctx->sm_count), 192, TC_SMEM, ctx->stream>>>(map, tc->d_tiles, n_tiles, tc->k_pad / TC_BK, tc->d_s, d_D, d_row_base, n, prefetch,
-                                                                                             tc->d_T, tc->k_pad);
+    k_tc_distance<<<std::min(n_tiles, ctx->sm_count), 192, TC_SMEM, ctx->stream>>>(map, tc->d_tiles, n_tiles, tc->k_pad / TC_BK, tc->d_s, d_D, d_row_base, n);
     LZG_LAUNCH_CHECK(ctx);
     if (tc->ev[3]) cudaEventRecord(tc->ev[3], ctx->stream);
     tc->launches++;
