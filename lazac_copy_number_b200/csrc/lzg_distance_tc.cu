@@ -539,25 +539,30 @@ static tc_encode_fn tc_encoder() {
 // byte; bytes are values + 128).  Entry {x: word index of the 4-byte-aligned base position, y: PRMT selector (nibble e = byte
 // offset of column e's position from the base, 0 .. 7), z: the four threshold bytes, w: 0x01 per valid column}.
 static void tc_layout(const unsigned* lohi, int L, std::vector<uint4>& table) {
-    table.clear();
-    table.reserve((size_t)L / 2 + 64);
-    uint4 cur = make_uint4(0, 0, 0, 0);
+    // at most one word per column: size once, write through a pointer, shrink at the end
+    size_t k = 0;
+    for (int q = 0; q < L; q++) k += lohi[2 * q + 1] - (255u - lohi[2 * q]);
+    table.resize(k + 1);
+    uint4* out = table.data();
+    size_t n_words = 0;
+    unsigned base = 0, sel = 0, thr4 = 0, mask = 0;
     int fill = 0;
     for (int q = 0; q < L; q++) {
         const unsigned lo = 255u - lohi[2 * q], hi = lohi[2 * q + 1];
         for (unsigned thr = lo + 1; thr <= hi; thr++) {
-            if (fill == 4 || (fill > 0 && q >= 4 * (int)cur.x + 8)) {  // full, or this position is out of the word's reach
-                table.push_back(cur);
-                cur = make_uint4(0, 0, 0, 0), fill = 0;
+            if (fill == 4 || (fill > 0 && (unsigned)q >= 4 * base + 8)) {  // full, or this position is out of the word's reach
+                out[n_words++] = make_uint4(base, sel, thr4, mask);
+                sel = thr4 = mask = 0, fill = 0;
             }
-            if (fill == 0) cur.x = (unsigned)q >> 2;
-            cur.y |= (unsigned)(q - 4 * (int)cur.x) << (4 * fill);
-            cur.z |= thr << (8 * fill);
-            cur.w |= 1u << (8 * fill);
+            if (fill == 0) base = (unsigned)q >> 2;
+            sel |= ((unsigned)q - 4 * base) << (4 * fill);
+            thr4 |= thr << (8 * fill);
+            mask |= 1u << (8 * fill);
             fill++;
         }
     }
-    if (fill) table.push_back(cur);
+    if (fill) out[n_words++] = make_uint4(base, sel, thr4, mask);
+    table.resize(n_words);
 }
 
 // The same for tests (no GPU, no context): lo / hi = lowest / highest VALUE of every position (-128 .. 127).  Writes up to
