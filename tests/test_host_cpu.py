@@ -140,3 +140,28 @@ def test_binary_profile_cache(tmp_path):
     assert "read_cn_profiles" in err3 and b3 != b1        # stale cache ignored, rewritten
     err4, b4 = run("b4")
     assert "profile cache" in err4 and b4 == b3
+
+
+def test_matrix_writers_across_thread_blocks(lazac, tmp_path):
+    """write_matrix_csv / _txt format blocks of rows on several threads and write them in order: the files of a matrix that
+    spans several blocks (2,500 rows of ~30 KB) must be what a plain loop writes (`lazac writebench` fills the matrix with
+    a linear congruential sequence, restated here)."""
+    n = 2500
+    out = subprocess.run([lazac, "writebench", str(n), "-o", str(tmp_path / "wb")], capture_output=True, text=True, check=True)
+    assert '"n": %d' % n in out.stdout
+    x = np.empty(n * n, np.uint64)
+    v = 12345
+    a, c, m = 1664525, 1013904223, (1 << 32) - 1
+    # the recurrence x <- a x + c (mod 2^32), vectorised by jumping: x_k = A_k x_0 + C_k
+    A, Cc = np.empty(n * n, np.uint64), np.empty(n * n, np.uint64)
+    ak, ck = 1, 0
+    for k in range(n * n):
+        ak, ck = (ak * a) & m, (ck * a + c) & m
+        A[k], Cc[k] = ak, ck
+    x = (A * np.uint64(v) + Cc) & np.uint64(m)
+    D = (x >> np.uint64(20)).astype(np.int64).reshape(n, n)
+    names = ["cell_%06d" % i for i in range(n)]
+    csv = ",".join(names) + "\n" + "".join(names[i] + "," + ",".join(map(str, D[i].tolist())) + "\n" for i in range(n))
+    txt = "%d\n" % n + "".join(names[i] + " " + " ".join(map(str, D[i].tolist())) + "\n" for i in range(n))
+    assert (tmp_path / "wb_dist_matrix.csv").read_text() == csv
+    assert (tmp_path / "wb_dist_matrix.txt").read_text() == txt
