@@ -70,3 +70,21 @@ def test_layout_rejects_bad_ranges():
     assert lib.lzg_distance_tc_layout(lo.ctypes.data_as(C.c_void_p), hi.ctypes.data_as(C.c_void_p), 1, None, 0, None) == -1
     lo, hi = np.array([-200], np.int32), np.array([2], np.int32)
     assert lib.lzg_distance_tc_layout(lo.ctypes.data_as(C.c_void_p), hi.ctypes.data_as(C.c_void_p), 1, None, 0, None) == -1
+
+
+def test_identity_on_random_shapes_and_ranges(port):
+    """Seeded sweep over shapes, value ranges and densities (isolated wide positions far apart, constant columns, full-range
+    columns next to narrow ones): the code's identity must reproduce the oracle's matrix every time."""
+    rng = np.random.default_rng(2024)
+    for case in range(40):
+        n, L = int(rng.integers(2, 24)), int(rng.integers(1, 400))
+        bp = np.zeros((n, L), np.int32)
+        for q in rng.choice(L, size=int(rng.integers(0, L + 1)), replace=False):
+            lo = int(rng.integers(-128, 128))
+            hi = int(rng.integers(lo, min(127, lo + int(rng.choice([0, 1, 2, 7, 255]))) + 1))
+            bp[:, q] = rng.integers(lo, hi + 1, n)
+        words, K = layout(bp)
+        assert K == int((bp.max(0).astype(np.int64) - bp.min(0)).sum())
+        T = expand(bp, words).astype(np.int64)
+        s = T.sum(1)
+        assert np.array_equal(s[:, None] + s[None, :] - 2 * (T @ T.T), port.distance_matrix(bp)), case
